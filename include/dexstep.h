@@ -1,0 +1,331 @@
+/*
+ * dexstep.h — C ABI of libdexstep.so: the B200-native per-step tensor pipeline of dexhand_env.
+ *
+ * The reference (CloudEngineHub/dexrobot_isaac) has NO FFI for this path: it is eager PyTorch
+ * behind Python component classes.  This ABI is new and sits *below* those classes; each entry
+ * point names the reference method(s) it replaces (paths relative to dexhand_env/):
+ *
+ *   dex_pre_physics      ActionProcessor.process_actions        components/action/action_processor.py:284-352
+ *                        (+ DefaultActionRules                  components/action/default_rules.py:33-112,
+ *                           ActionRules post filters            components/action/rules.py:113-190,
+ *                           ActionProcessor.apply_coupling      components/action/action_processor.py:571-614,
+ *                           ObservationEncoder.update_prev_actions  components/observation/observation_encoder.py:287-296)
+ *   dex_post_physics     StepProcessor.process_physics_step     components/step_processor.py:37-131
+ *                        (= TensorManager.refresh_tensors gather components/physics/tensor_manager.py:441-446,
+ *                           ObservationEncoder.compute_observations/concatenate_observations
+ *                                                               components/observation/observation_encoder.py:442-494,576-986,1483-1521,
+ *                           BlindGraspingTask.get_task_observations/check_*_criteria/compute_task_reward_terms
+ *                                                               tasks/blind_grasping_task.py:549-1364,
+ *                           TerminationManager.evaluate         components/termination/termination_manager.py:120-321,
+ *                           RewardCalculator.compute_common_reward_terms/compute_total_reward
+ *                                                               components/reward/reward_calculator.py:66-275,
+ *                           and, for envs whose reset flag fires, DexHandBase.reset_idx -> ResetManager.reset_idx
+ *                                                               tasks/dexhand_base.py:743-756, components/reset/reset_manager.py:92-190)
+ *   dex_reset_idx        DexHandBase.reset_idx (masked)         tasks/dexhand_base.py:743-756 (+ reset_manager.py:92-190,
+ *                                                               blind_grasping_task.py:433-547, action_processor.py:524-568,616-666,
+ *                                                               observation_encoder.py:363-383, termination_manager.py:341-357)
+ *   dex_step_epilogue    torch.nonzero(reset_buf) + termination rates + update_consecutive_successes
+ *                                                               step_processor.py:109-111, termination_manager.py:259-266,323-339
+ *   dex_apply_coupling / dex_extract_active_targets
+ *                        ActionProcessor.apply_coupling / extract_active_targets_from_full_dof
+ *                                                               action_processor.py:571-614 / 616-666
+ *   dex_point_in_hand_frame  utils/coordinate_transforms.py:17-35 (known-answer tests)
+ *   (DexOutBuffers.episode_sums/.stat_totals: RewardComponentObserver accumulation, rl/reward_observer.py:160-293,
+ *    fused into dex_post_physics; the totals vector is the payload of the single NCCL all-reduce)
+ *
+ * Conventions
+ *   - extern "C", POD structs only, raw device pointers, element counts as int32.  No torch types.
+ *   - All pointers are DEVICE pointers unless a parameter is documented as host.  The caller
+ *     (PyTorch / Isaac Gym) owns every buffer; the library never allocates or frees device memory.
+ *   - Every function is asynchronous w.r.t. the host, ordered on the passed cudaStream_t
+ *     (passed as void*), performs no allocation and no synchronisation and reads no device result on
+ *     the host => safe to capture in a CUDA graph.  Pointers must stay valid/fixed while a captured
+ *     graph that contains the call is alive.
+ *   - Return value: 0 on success, a negative DEX_ERR_* for argument errors detected before launch,
+ *     or a positive cudaError_t from the launch.  dex_strerror() maps both.
+ *   - Layouts.  Buffers dictated by Isaac Gym / the policy are row-major AoS exactly as the reference
+ *     has them: dof_state [N,26,2], rigid_body_state [N,NB,13], net_contact_force [N,NB,3],
+ *     actor_root_state [N,NA,13], actions [N,NACT], obs_buf [N,obs_dim], full_dof_targets [N,26].
+ *     Path-internal persistent state is stored TRANSPOSED (SoA, [K][N], env index fastest) so that a
+ *     thread-per-env kernel reads and writes it fully coalesced; the Python layer exposes it as
+ *     [N,K] strided views.
+ */
+#ifndef DEXSTEP_H_
+#define DEXSTEP_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DEX_ABI_VERSION 3
+
+#define DEX_NUM_DOF 26          /* constants.py:8-10: 6 base + 20 finger DOFs */
+#define DEX_NUM_BASE 6
+#define DEX_NUM_ACTIVE 18       /* 6 base + 12 finger controls */
+#define DEX_NUM_ACTIVE_FINGER 12
+#define DEX_NUM_FINGER_DOF 20
+#define DEX_NUM_FINGERS 5
+#define DEX_NUM_UNIFORMS 29     /* box x,y,yaw | hand translation 3 | hand rotation 3 | finger DOFs 20 */
+
+/* error codes (negative); positive values are cudaError_t */
+#define DEX_OK 0
+#define DEX_ERR_NULL -1
+#define DEX_ERR_SIZE -2
+#define DEX_ERR_ALIGN -3
+#define DEX_ERR_PARAM -4
+#define DEX_ERR_VERSION -5
+
+/* task / mode enums */
+#define DEX_TASK_BASE 0
+#define DEX_TASK_BLIND_GRASPING 1
+#define DEX_CONTROL_POSITION 0
+#define DEX_CONTROL_POSITION_DELTA 1
+#define DEX_MODE_FULL 0      /* StepProcessor.process_physics_step */
+#define DEX_MODE_OBS_ONLY 1  /* ObservationEncoder.compute_observations + concatenate (first pass of reset()) */
+
+/* flags for dex_post_physics */
+#define DEX_FLAG_FIRST_REWARD_CALL 1u  /* RewardCalculator prev-state is None (reward_calculator.py:149-153,189-190) */
+#define DEX_FLAG_STALE_CONTACTS 2u     /* read monitored contact forces from state.contact_forces instead of gathering
+                                          (reset() computes its first obs pass without refresh_tensors, dexhand_base.py:813) */
+#define DEX_FLAG_NO_FUSED_RESET 4u     /* compute reset_buf but leave the reset to a later dex_reset_idx call */
+
+/* observation keys (obs_dict entries of the reference, observation_encoder.py:613-756,
+ * step_processor.py:73, blind_grasping_task.py:569-652,702-746,895-899) */
+enum DexObsKey {
+  DEX_K_BASE_DOF_POS = 0, DEX_K_BASE_DOF_VEL, DEX_K_ACTIVE_FINGER_DOF_POS, DEX_K_ACTIVE_FINGER_DOF_VEL,
+  DEX_K_ALL_FINGER_DOF_POS, DEX_K_ALL_FINGER_DOF_VEL, DEX_K_HAND_POSE, DEX_K_HAND_POSE_ARR_ALIGNED,
+  DEX_K_CONTACT_FORCES, DEX_K_PREV_ACTIONS, DEX_K_ACTIVE_PREV_TARGETS, DEX_K_BASE_DOF_TARGET,
+  DEX_K_ACTIVE_FINGER_DOF_TARGET, DEX_K_ALL_FINGER_DOF_TARGET, DEX_K_CONTACT_FORCE_MAGNITUDE,
+  DEX_K_CONTACT_BINARY, DEX_K_CONTACT_DURATION, DEX_K_FINGERTIP_POSES_WORLD, DEX_K_FINGERTIP_POSES_HAND,
+  DEX_K_FINGERPAD_POSES_WORLD, DEX_K_FINGERPAD_POSES_HAND, DEX_K_EPISODE_TIME, DEX_K_ACTIVE_RULE_TARGETS,
+  /* BlindGrasping task observations */
+  DEX_K_OBJECT_POS, DEX_K_OBJECT_VEL, DEX_K_FINGER_TO_OBJECT_DISTANCES, DEX_K_AVG_FINGER_TO_OBJECT_DISTANCE,
+  DEX_K_FINGER_TO_OBJECT_HEIGHT_DIFF, DEX_K_AVG_FINGER_TO_OBJECT_HEIGHT_DIFF, DEX_K_HAND_TO_OBJECT_DISTANCE,
+  DEX_K_FINGERPAD_DISTANCES, DEX_K_FIRST_THREE_FINGERPAD_CENTROID, DEX_K_THUMB_CONTACT,
+  DEX_K_OTHER_FINGERS_CONTACT, DEX_K_GRASP_STATE, DEX_K_GRASP_DURATION, DEX_K_CURRENT_STAGE,
+  DEX_K_TIME_IN_STAGE, DEX_K_STAGE_PROGRESS,
+  DEX_NUM_OBS_KEYS
+};
+
+/* reward terms, in the reference's dict order: common (reward_calculator.py:66-221) then task
+ * (blind_grasping_task.py:980-1053); termination rewards (termination_manager.py:280-321) last */
+enum DexRewardTerm {
+  DEX_R_ALIVE = 0, DEX_R_HEIGHT_SAFETY, DEX_R_FINGER_VELOCITY, DEX_R_HAND_VELOCITY, DEX_R_HAND_ANGULAR_VELOCITY,
+  DEX_R_JOINT_LIMIT, DEX_R_FINGER_ACCELERATION, DEX_R_HAND_ACCELERATION, DEX_R_HAND_ANGULAR_ACCELERATION,
+  DEX_R_CONTACT_STABILITY,
+  DEX_R_S1_HEIGHT_ALIGNMENT, DEX_R_S1_CENTROID_POSITIONING, DEX_R_S1_OBJECT_STABILITY,
+  DEX_R_S1_FINGER_HEIGHT_CONSISTENCY, DEX_R_S1_THUMB_ROTATION,
+  DEX_R_S2_THUMB_CONTACT, DEX_R_S2_OTHER_FINGERS_CONTACT, DEX_R_S2_GRASP_ACHIEVEMENT, DEX_R_S2_FINGERPAD_PROXIMITY,
+  DEX_R_S2_BASE_STABILITY,
+  DEX_R_S3_OBJECT_HEIGHT, DEX_R_S3_GRASP_MAINTENANCE, DEX_R_S3_GRASP_DURATION,
+  DEX_R_S1_COMPLETION, DEX_R_S2_COMPLETION, DEX_R_PENETRATION_PENALTY,
+  DEX_NUM_REWARD_TERMS
+};
+#define DEX_NUM_COMMON_TERMS 10
+
+/* termination criteria (termination_manager.py:160-227; dict order: builtin first, then task) */
+enum DexCriterion {
+  DEX_C_GRASP_LIFT_SUCCESS = 0,  /* success */
+  DEX_C_HITTING_GROUND,          /* failures ... */
+  DEX_C_BOX_TOO_FAR, DEX_C_STAGE1_PREGRASP_FAILED, DEX_C_STAGE2_CONTACT_FAILED, DEX_C_STAGE3_GRASP_LOST,
+  DEX_NUM_CRITERIA
+};
+
+/* int32 counters accumulated by dex_post_physics (zeroed by dex_step_epilogue after it consumed them) */
+enum DexCounter {
+  DEX_CNT_SUCCESS = 0, DEX_CNT_FAILURE, DEX_CNT_TIMEOUT, DEX_CNT_RESET,
+  DEX_CNT_CRIT0, /* .. DEX_CNT_CRIT0 + DEX_NUM_CRITERIA - 1: raw criterion hit counts */
+  DEX_NUM_COUNTERS = 16
+};
+
+/* floats written by dex_step_epilogue */
+enum DexStat {
+  DEX_STAT_SUCCESS_RATE = 0, DEX_STAT_FAILURE_RATE, DEX_STAT_TIMEOUT_RATE,
+  DEX_STAT_CRIT0, /* .. + DEX_NUM_CRITERIA - 1: mean of the raw criterion */
+  DEX_NUM_STATS = 16
+};
+
+/* ------------------------------------------------------------------------------------------------
+ * Parameter block: everything the reference reads from cfg / derives once at init.  Filled on the
+ * host (double arithmetic as Python does, then narrowed to float exactly where torch narrows).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct DexParams {
+  int32_t abi_version;            /* must be DEX_ABI_VERSION */
+  int32_t task;                   /* DEX_TASK_* */
+  /* --- layout of the sim buffers (hand_initializer.py:439-560, blind_grasping_task.py:388-419) --- */
+  int32_t num_bodies;             /* NB: rigid bodies per env */
+  int32_t num_actors;             /* NA: actors per env */
+  int32_t hand_body;              /* right_hand_base */
+  int32_t tip_body[DEX_NUM_FINGERS];      /* r_f_link{1..5}_tip */
+  int32_t pad_body[DEX_NUM_FINGERS];      /* r_f_link{1..5}_pad */
+  int32_t contact_body[DEX_NUM_FINGERS];  /* contact_force_bodies */
+  int32_t box_body;               /* -1 without box */
+  int32_t box_actor;              /* -1 without box */
+  /* --- action pipeline (action_processor.py:181-247,380-503) --- */
+  int32_t num_actions;            /* NACT = 18 / 12 / 6 */
+  int32_t control_mode;           /* DEX_CONTROL_* */
+  int32_t policy_controls_base;
+  int32_t policy_controls_fingers;
+  int32_t filter_velocity_clamp;  /* post_action_filters contains "velocity_clamp" */
+  int32_t filter_position_clamp;
+  int32_t dof_to_active[DEX_NUM_DOF];   /* per DOF: index into the 18 active targets, -1 = forced 0 (r_f_joint3_1) */
+  float dof_coupling_scale[DEX_NUM_DOF];
+  int32_t inverse_src_dof[DEX_NUM_ACTIVE]; /* per active target: DOF whose position resets it (last DOF of the group) */
+  float inverse_scale[DEX_NUM_ACTIVE];
+  float active_lower[DEX_NUM_ACTIVE];
+  float active_upper[DEX_NUM_ACTIVE];
+  float max_deltas[DEX_NUM_ACTIVE];
+  /* --- observations --- */
+  int32_t active_finger_dof[DEX_NUM_ACTIVE_FINGER]; /* observation_encoder.py:496-574 */
+  int32_t obs_dim;
+  int32_t obs_offset[DEX_NUM_OBS_KEYS];   /* column of the key in obs_buf, -1 = not a policy key */
+  int32_t dict_dim;
+  int32_t dict_offset[DEX_NUM_OBS_KEYS];  /* column of the key in the optional obs_dict buffer */
+  float control_dt;
+  float contact_binary_threshold;
+  /* --- termination --- */
+  int32_t max_episode_length;
+  int32_t has_height_safety;
+  float handbase_threshold;
+  float fingertip_threshold;
+  int32_t criterion_active[DEX_NUM_CRITERIA];
+  float success_reward;           /* +termination_success */
+  float failure_reward;           /* -termination_failure_penalty */
+  float timeout_reward;           /* -termination_timeout_penalty */
+  int32_t max_consecutive_successes;
+  /* --- rewards --- */
+  float reward_weight[DEX_NUM_REWARD_TERMS];
+  int32_t component_row[DEX_NUM_REWARD_TERMS]; /* row of the raw term in reward_components (weighted = row+1), -1 if weight == 0 */
+  int32_t total_row;                           /* row of "total" */
+  int32_t termination_row;                     /* first of 6 rows: success, success_w, failure_penalty, .._w, timeout_penalty, .._w */
+  int32_t num_component_rows;
+  int32_t need_common_rewards;                 /* any common weight != 0 */
+  float dof_lower[DEX_NUM_DOF];
+  float dof_upper[DEX_NUM_DOF];
+  /* --- BlindGrasping (blind_grasping_task.py:114-205) --- */
+  float box_size, box_z, box_xy_range;
+  float success_height_threshold;
+  float contact_duration_threshold_s;
+  int32_t contact_duration_threshold_steps;
+  int32_t min_fingers_for_grasp;
+  float max_box_distance;
+  float stage1_duration, stage2_duration, stage2_contact_success_threshold;
+  float hand_translation_range, hand_rotation_range, thumb_rotation_range, other_finger_range;
+  float height_alignment_decay, centroid_positioning_decay, object_stability_decay;
+  float height_consistency_decay, fingerpad_proximity_decay, base_stability_decay;
+  float height_tolerance, centroid_tolerance, position_drift_tolerance, velocity_tolerance;
+  float proximity_threshold;       /* sqrt(3)*size/2*1.2 */
+  float penetration_threshold;     /* size/2*geometricPenetrationFactor */
+  float min_reward_distance;       /* size/2*proximityMinDistanceFactor */
+  float penetration_depth_scale;
+  float lift_height_range;         /* success_height_threshold - box_z (double, then narrowed) */
+  float half_pi;                   /* (float)(pi/2) */
+  float pi;                        /* (float)pi */
+} DexParams;
+
+/* Isaac Gym tensor-API buffers, zero-copy (tensor_manager.py:173-328). */
+typedef struct DexSimViews {
+  float* dof_state;               /* [N,26,2]  read; rows of reset envs are written (reset_manager.py:121-124) */
+  const float* rigid_body_state;  /* [N,NB,13] read only */
+  const float* net_contact_force; /* [N,NB,3]  read only */
+  float* actor_root_state;        /* [N,NA,13] box row read; written on reset (blind_grasping_task.py:475-490) */
+} DexSimViews;
+
+/* Persistent path state.  [K][N] = transposed/SoA.  Pointers marked (BG) may be NULL
+ * for DEX_TASK_BASE; (common) may be NULL when need_common_rewards == 0. */
+typedef struct DexStateBuffers {
+  float* active_prev_targets;     /* [18][N]  ActionProcessor.active_prev_targets */
+  float* active_rule_targets;     /* [18][N]  obs_dict["active_rule_targets"] */
+  float* full_dof_targets;        /* [N,26]   AoS: handed to gym.set_dof_position_target_tensor */
+  float* prev_actions;            /* [NACT][N] ObservationEncoder.prev_actions */
+  float* prev_dof_pos;            /* [26][N] */
+  float* contact_duration_steps;  /* [5][N] */
+  float* prev_contact_binary;     /* [5][N] */
+  float* contact_forces;          /* [15][N] gathered monitored forces (tensor_manager.contact_forces); may be NULL */
+  int64_t* episode_step_count;    /* [N] */
+  float* prev_finger_dof_vel;     /* [20][N] (common) */
+  float* prev_hand_vel;           /* [3][N]  (common) */
+  float* prev_hand_ang_vel;       /* [3][N]  (common) */
+  uint8_t* prev_contacts;         /* [5][N]  (common) */
+  int64_t* success_duration_steps;        /* [N] (BG) */
+  uint8_t* success_conditions_met;        /* [N] (BG) */
+  int64_t* current_stage;                 /* [N] (BG) */
+  float* time_in_stage;                   /* [N] (BG) */
+  float* stage_contact_duration;          /* [N] (BG) */
+  uint8_t* just_transitioned_to_stage2;   /* [N] (BG) */
+  uint8_t* just_transitioned_to_stage3;   /* [N] (BG) */
+  float* initial_box_positions;           /* [3][N] (BG) */
+  uint8_t* failure_tensors;               /* [3][N] (BG) stage1_pregrasp_failed, stage2_contact_failed, stage3_grasp_lost */
+} DexStateBuffers;
+
+typedef struct DexOutBuffers {
+  float* obs_buf;                 /* [N,obs_dim] */
+  float* obs_dict;                /* [N,dict_dim] optional full obs_dict materialisation (NULL = skip) */
+  float* rew_buf;                 /* [N] */
+  uint8_t* reset_buf;             /* [N] bool */
+  uint8_t* success;               /* [N] termination_info["success"] */
+  uint8_t* failure;               /* [N] */
+  uint8_t* timeout;               /* [N] */
+  float* reward_components;       /* [num_component_rows][N] */
+  uint32_t* reset_bits;           /* [ceil(N/32)] ballot words of reset_buf */
+  int32_t* counters;              /* [DEX_NUM_COUNTERS] */
+  /* Optional device-side RewardComponentObserver (rl/reward_observer.py:160-293); all NULL = off.
+   * Fused into the post-physics pass so the per-step component arrays need not be re-read. */
+  float* episode_sums;            /* [num_component_rows][N] running per-episode sum of each component */
+  int32_t* episode_lengths;       /* [N] observer-side episode length (reward_observer.py:166) */
+  double* stat_totals;            /* [4][2 + num_component_rows], classes {all, success, failure, timeout}:
+                                     n_episodes, sum(episode_length), sum of each component's episode sum.
+                                     This vector is the payload of the single NCCL all-reduce. */
+} DexOutBuffers;
+
+typedef struct DexEpilogueBuffers {
+  const uint32_t* reset_bits;     /* [ceil(N/32)] */
+  int32_t* counters;              /* [DEX_NUM_COUNTERS] consumed and zeroed */
+  int32_t* env_ids;               /* [N] ascending ids of the reset envs (== torch.nonzero(reset_buf)) */
+  int32_t* num_reset;             /* [1] */
+  float* stats;                   /* [DEX_NUM_STATS] */
+  int32_t* consecutive_successes; /* [1] persistent */
+} DexEpilogueBuffers;
+
+const char* dex_strerror(int code);
+int dex_abi_version(void);
+/* sizeof(DexParams) as compiled, so a binding can verify its struct mirror */
+int dex_sizeof_params(void);
+
+/* Pre-physics: actions -> 26 DOF position targets.  `actions` [N,NACT] row-major.  Optional debug
+ * outputs (may be NULL): active_raw_targets [18][N] (ActionProcessor.active_raw_targets). */
+int dex_pre_physics(const DexParams* params, const DexStateBuffers* state, const float* actions,
+                    float* active_raw_targets, int32_t n_envs, void* stream);
+
+/* Post-physics: one pass per env over the sim buffers; see header comment.  `uniforms` [N,29]
+ * (row-major) are the reset randoms in [0,1); if NULL they are generated in-kernel (Philox4x32-10
+ * keyed by (seed, step_index, env)). */
+int dex_post_physics(const DexParams* params, const DexSimViews* sim, const DexStateBuffers* state,
+                     const DexOutBuffers* out, int32_t n_envs, int32_t mode, uint32_t flags,
+                     const float* uniforms, uint64_t seed, uint64_t step_index, void* stream);
+
+/* Masked reset of envs with reset_mask[env] != 0 (NULL = all envs). */
+int dex_reset_idx(const DexParams* params, const DexSimViews* sim, const DexStateBuffers* state,
+                  const uint8_t* reset_mask, int32_t n_envs, const float* uniforms, uint64_t seed,
+                  uint64_t step_index, void* stream);
+
+/* Ordered compaction of the reset mask + termination statistics + consecutive-success counter. */
+int dex_step_epilogue(const DexParams* params, const DexEpilogueBuffers* ep, int32_t n_envs, void* stream);
+
+/* Stand-alone coupling helpers; active [18][N] SoA, full [N,26] AoS. */
+int dex_apply_coupling(const DexParams* params, const float* active, float* full, int32_t n_envs, void* stream);
+int dex_extract_active_targets(const DexParams* params, const float* full, float* active, int32_t n_envs,
+                               void* stream);
+
+/* Known-answer entry: p_hand = R(q)^-1 (p_world - hand_pos); all [n,3]/[n,4] row-major. */
+int dex_point_in_hand_frame(const float* p_world, const float* hand_pos, const float* hand_quat, float* out,
+                            int32_t n, void* stream);
+/* q_out = conj(a) (x) b  and  q_out = a (x) conj([0,s,0,s]) helpers used by the same tests. */
+int dex_quat_mul(const float* a, const float* b, float* out, int32_t n, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DEXSTEP_H_ */
