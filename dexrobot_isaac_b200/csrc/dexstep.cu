@@ -771,7 +771,7 @@ __global__ void __launch_bounds__(TILE) post_physics_kernel(const __grid_constan
 
       // ---------------- fused reset (dexhand_base.py:743-756) -----------------------------------
       if (should_reset && !(A.flags & DEX_FLAG_NO_FUSED_RESET)) {
-        const ResetCtx rc{A.uniforms, A.seed, A.step};
+        const ResetCtx rc{A.uniforms, A.seed, st.rng_step ? *st.rng_step : A.step};
         reset_env<BG>(P, A.sim, st, rc, env, N);
       }
     }
@@ -830,7 +830,7 @@ __global__ void __launch_bounds__(128) reset_kernel(const __grid_constant__ Rese
   const int env = blockIdx.x * blockDim.x + threadIdx.x;
   if (env >= A.n) return;
   if (A.mask != nullptr && A.mask[env] == 0) return;
-  const ResetCtx rc{A.uniforms, A.seed, A.step};
+  const ResetCtx rc{A.uniforms, A.seed, A.st.rng_step ? *A.st.rng_step : A.step};
   reset_env<BG>(A.p, A.sim, A.st, rc, env, (size_t)A.n);
 }
 
@@ -976,6 +976,7 @@ __global__ void __launch_bounds__(1024) epilogue_kernel(const __grid_constant__ 
     cs = (c[DEX_CNT_SUCCESS] > 0) ? cs + 1 : 0;
     *A.ep.consecutive_successes = min(cs, A.max_consecutive);
     for (int k = 0; k < DEX_NUM_COUNTERS; ++k) c[k] = 0;
+    if (A.ep.rng_step != nullptr) *A.ep.rng_step += 1;
   }
 }
 

@@ -1,0 +1,168 @@
+"""DexStepEnv — the caller-side wiring DexHandBase does around the step pipeline, without Isaac Gym.
+
+It plays the role of the reference's ``parent`` object (tasks/dexhand_base.py): it owns (or is
+bound to) the four sim-state tensors, constructs the reference-named components around one
+``StepPipeline`` and exposes the call sequence of dexhand_base.py:
+
+    reset()                 :805-838   reset_idx(all) -> obs pass (stale contact gather) -> full pass
+    pre_physics_step(a)     :840-887   ActionProcessor.process_actions + update_prev_actions
+    post_physics_step()     :921       StepProcessor.process_physics_step (+ fused reset_idx)
+    step(a)                 :893-942   pre -> physics callable -> post
+
+With Isaac Gym present, pass the gymtorch-wrapped tensors as ``sim`` (zero-copy) and a ``physics``
+callable that runs gym.simulate/fetch_results/refresh_*; here tests and the bench pass a callable
+that writes the next synthetic state.
+"""
+from __future__ import annotations
+
+from typing import Callable, Dict, Optional, Sequence
+
+import torch
+
+from . import _lib as L
+from .params import FAILURE_CRITERIA, SUCCESS_CRITERIA, BodyLayout
+from .pipeline import (FLAG_STALE_CONTACTS, MODE_FULL, MODE_OBS_ONLY, NUM_UNIFORMS, StepPipeline)
+
+C = L.CONSTS
+
+
+class DexStepEnv:
+    def __init__(self, cfg: dict, num_envs: int, layout: Optional[BodyLayout] = None,
+                 dof_props: Optional[torch.Tensor] = None, device="cuda:0",
+                 sim: Optional[Dict[str, torch.Tensor]] = None, materialize_obs_dict: bool = False,
+                 observer: bool = True, seed: int = 1234, init_uniforms: Optional[torch.Tensor] = None,
+                 physics: Optional[Callable[[], None]] = None):
+        self.cfg, self.env_cfg, self.task_cfg, self.sim_cfg = cfg, cfg["env"], cfg["task"], cfg["sim"]
+        self.task_name = self.task_cfg.get("name", "BaseTask")
+        self.num_envs = int(num_envs)
+        dev = torch.device(device)
+        if dev.type == "cuda" and dev.index is None:
+            dev = torch.device("cuda", torch.cuda.current_device())
+        self.device = dev
+        self.layout = layout or BodyLayout.default(with_box=self.task_name == "BlindGrasping")
+        if dof_props is None:
+            raise ValueError("dof_props [26,6] (lower/upper limits in columns 4,5; tensor_manager.py:242) is required")
+        self.dof_props = dof_props.detach().to("cpu", torch.float32)
+        self.physics = physics
+        self.pipeline = StepPipeline(cfg, num_envs, self.layout, self.dof_props[:, 4].tolist(),
+                                     self.dof_props[:, 5].tolist(), device=dev, sim=sim,
+                                     materialize_obs_dict=materialize_obs_dict, observer=observer, seed=seed)
+        p = self.pipeline
+        self.spec = p.spec
+        self.num_actions = p.spec.num_actions
+        self.num_observations = p.spec.obs_dim
+        self.control_dt = p.spec.control_dt
+        # buffers the reference's parent exposes (initialization_manager.py:34-117)
+        self.dof_state = p.sim_tensors["dof_state"].view(self.num_envs, 26, 2)
+        self.dof_pos, self.dof_vel = self.dof_state[..., 0], self.dof_state[..., 1]
+        self.rigid_body_states = p.sim_tensors["rigid_body_state"].view(self.num_envs, self.layout.num_bodies, 13)
+        self.contact_forces_all = p.sim_tensors["net_contact_force"].view(self.num_envs, self.layout.num_bodies, 3)
+        self.actor_root_state_tensor = p.sim_tensors["actor_root_state"].view(self.num_envs, self.layout.num_actors, 13)
+        self.obs_buf, self.rew_buf, self.reset_buf = p.out["obs_buf"], p.out["rew_buf"], p.out["reset_buf"]
+        self.episode_step_count = p.state["episode_step_count"]
+        self.extras: Dict = {}
+        self._zero_mask = torch.zeros(self.num_envs, dtype=torch.bool, device=dev)
+        self._actions = torch.zeros(self.num_envs, self.num_actions, device=dev)
+        # control-cycle measurement of the reference (dexhand_base.py:270-320) does one full reset with
+        # whatever the global RNG yields; here: uniforms 0.5 unless given.
+        u = init_uniforms if init_uniforms is not None else torch.full((self.num_envs, NUM_UNIFORMS), 0.5)
+        p.reset_idx(None, u.to(dev, torch.float32).contiguous())
+
+    # ------------------------------------------------------------------ reference call sequence
+    def reset_idx(self, env_ids):
+        """dexhand_base.py:743-756 (masked form of the index list)."""
+        if len(env_ids) == 0:
+            return
+        mask = torch.zeros(self.num_envs, dtype=torch.bool, device=self.device)
+        mask[env_ids.to(self.device)] = True
+        self.pipeline.reset_idx(mask)
+
+    def reset(self, uniforms: Optional[torch.Tensor] = None):
+        p = self.pipeline
+        if uniforms is not None:
+            p.uniforms = uniforms.to(self.device, torch.float32).contiguous()
+        p.reset_idx(None)
+        p.post_physics(MODE_OBS_ONLY, FLAG_STALE_CONTACTS)  # first pass: no refresh_tensors (dexhand_base.py:813)
+        p.post_physics(MODE_FULL)
+        p.epilogue()
+        self._update_extras()
+        return self.obs_buf
+
+    def pre_physics_step(self, actions: torch.Tensor):
+        a = actions.to(self.device, torch.float32)
+        self._actions.copy_(a)
+        self.pipeline.pre_physics(self._actions)
+
+    def post_physics_step(self, uniforms: Optional[torch.Tensor] = None):
+        p = self.pipeline
+        if uniforms is not None:
+            p.uniforms = uniforms.to(self.device, torch.float32).contiguous()
+        p.post_physics(MODE_FULL)
+        p.epilogue()
+        self._update_extras()
+        return self.obs_buf, self.rew_buf, self.reset_buf, self.extras
+
+    def step(self, actions: torch.Tensor):
+        self.pre_physics_step(actions)
+        if self.physics is not None:
+            self.physics()
+        return self.post_physics_step()
+
+    # ------------------------------------------------------------------ extras (step_processor.py:221-232)
+    def _update_extras(self):
+        """Lazy: tensors are views/slices of device buffers, no host sync happens here."""
+        p, sp = self.pipeline, self.spec
+        stats = p.epi["stats"]
+        ex = {"consecutive_successes": p.epi["consecutive_successes"][0],
+              "episode_length": p.state["episode_step_count"],
+              "success": p.out["success"], "failure": p.out["failure"], "timeout": p.out["timeout"],
+              "success_rate": stats[C["DEX_STAT_SUCCESS_RATE"]], "failure_rate": stats[C["DEX_STAT_FAILURE_RATE"]],
+              "timeout_rate": stats[C["DEX_STAT_TIMEOUT_RATE"]]}
+        crit = SUCCESS_CRITERIA + FAILURE_CRITERIA
+        for c, name in enumerate(crit):
+            kind = "success" if name in SUCCESS_CRITERIA else "failure"
+            if name in (sp.active_success if kind == "success" else sp.active_failure):
+                ex[f"{kind}_{name}"] = stats[C["DEX_STAT_CRIT0"] + c]
+                # termination_manager.py:353-357 + step_processor.py:109-111: every env whose criterion
+                # fired was reset in the same step, which clears its sticky reason bit before extras are
+                # built -> the masks that reach extras are all-False.
+                ex[f"{kind}_reason_{name}"] = self._zero_mask
+        ex["reward_components"] = p.reward_components()
+        self.extras = ex
+
+    # ------------------------------------------------------------------ test driver API (oracle/driver.py)
+    def load_state(self, state: Dict[str, torch.Tensor]):
+        """Fake PhysX step: overwrite the sim buffers in place."""
+        t = self.pipeline.sim_tensors
+        t["dof_state"].copy_(state["dof_state"].reshape(t["dof_state"].shape))
+        t["rigid_body_state"].copy_(state["rigid_body_states"].reshape(t["rigid_body_state"].shape))
+        t["net_contact_force"].copy_(state["net_contact_force"].reshape(t["net_contact_force"].shape))
+        t["actor_root_state"].copy_(state["actor_root_state"].reshape(t["actor_root_state"].shape))
+
+    @property
+    def initial_box_positions(self):
+        return self.pipeline.view("initial_box_positions")
+
+    def snapshot(self) -> Dict[str, torch.Tensor]:
+        p = self.pipeline
+        out = {"obs_buf": self.obs_buf, "rew_buf": self.rew_buf, "reset_buf": self.reset_buf,
+               "episode_step_count": self.episode_step_count, "dof_state": self.dof_state,
+               "actor_root_state": self.actor_root_state_tensor}
+        for k in ("active_prev_targets", "full_dof_targets", "prev_actions", "prev_dof_pos", "contact_duration_steps",
+                  "prev_contact_binary", "active_rule_targets"):
+            out[k] = p.view(k)
+        for k, v in self.extras.items():
+            if k == "reward_components":
+                for ck, cv in v.items():
+                    out[f"rc/{ck}"] = cv
+            else:
+                out[f"extras/{k}"] = v
+        if self.spec.is_blind_grasping:
+            for k in ("success_duration_steps", "success_conditions_met", "current_stage", "time_in_stage",
+                      "stage_contact_duration", "just_transitioned_to_stage2", "just_transitioned_to_stage3",
+                      "initial_box_positions"):
+                out[f"task/{k}"] = p.view(k)
+        if p.out["obs_dict"] is not None:
+            for k, v in p.obs_dict().items():
+                out[f"obs/{k}"] = v
+        return {k: v.detach().clone() for k, v in out.items()}

@@ -1,0 +1,254 @@
+"""StepPipeline — owns the persistent path state in HBM and drives libdexstep.so (C ABI, raw pointers).
+
+This is the single object the reference-named component classes (components/*.py) delegate to.
+PyTorch is used for device memory, streams and CUDA-graph capture only; every arithmetic op of
+the path runs in the hand-written kernels of csrc/dexstep.cu.  There is no eager/CPU fallback:
+constructing a StepPipeline on a non-CUDA device raises.
+
+HBM layout:
+  * buffers dictated from outside stay row-major AoS exactly as Isaac Gym / the policy hand them
+    over: dof_state [N,26,2], rigid_body_state [N,NB,13], net_contact_force [N,NB,3],
+    actor_root_state [N,NA,13], actions [N,NACT], obs_buf [N,obs_dim], full_dof_targets [N,26];
+  * path-internal persistent state is SoA [K,N] (env index fastest); it is exposed to callers as
+    [N,K] strided *views* (``.t()``), so reference-style indexing ``state[env_ids, k]`` works.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Dict, Optional, Sequence
+
+import torch
+
+from . import _lib as L
+from .params import NUM_ACTIVE, NUM_DOF, NUM_FINGERS, BodyLayout, PipelineSpec, make_params
+
+C = L.CONSTS
+MODE_FULL, MODE_OBS_ONLY = C["DEX_MODE_FULL"], C["DEX_MODE_OBS_ONLY"]
+FLAG_FIRST_REWARD_CALL = C["DEX_FLAG_FIRST_REWARD_CALL"]
+FLAG_STALE_CONTACTS = C["DEX_FLAG_STALE_CONTACTS"]
+FLAG_NO_FUSED_RESET = C["DEX_FLAG_NO_FUSED_RESET"]
+NUM_UNIFORMS = C["DEX_NUM_UNIFORMS"]
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+class StepPipeline:
+    def __init__(self, cfg: dict, num_envs: int, layout: BodyLayout, dof_lower: Sequence[float],
+                 dof_upper: Sequence[float], device="cuda:0", sim: Optional[Dict[str, torch.Tensor]] = None,
+                 materialize_obs_dict: bool = False, observer: bool = True, seed: int = 1234,
+                 post_action_filters: Sequence[str] = ("velocity_clamp", "position_clamp"),
+                 physics_steps_per_control_step: int = 2):
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise L.DexStepError("StepPipeline needs a CUDA device: this path has no CPU or eager fallback")
+        self.lib = L.load()
+        self.n = self.num_envs = int(num_envs)
+        if self.n <= 0:
+            raise ValueError("num_envs must be positive")
+        self.layout = layout
+        self.cfg = cfg
+        self.params, self.spec = make_params(cfg, layout, dof_lower, dof_upper, post_action_filters,
+                                             physics_steps_per_control_step)
+        self.spec: PipelineSpec
+        self.seed = int(seed)
+        self.host_step = 0
+        self._reward_initialized = False
+        self._graph = None
+        n, dev, sp = self.n, self.device, self.spec
+        f32, i64, u8 = torch.float32, torch.int64, torch.uint8
+
+        def z(*shape, dtype=f32):
+            return torch.zeros(*shape, dtype=dtype, device=dev)
+
+        # ---- sim views (own storage unless bound to external, e.g. gymtorch-wrapped, tensors) ----
+        self.sim_tensors: Dict[str, torch.Tensor] = {}
+        self._sim = L.DexSimViews()
+        self.bind_sim(sim or {
+            "dof_state": z(n, NUM_DOF, 2), "rigid_body_state": z(n, layout.num_bodies, 13),
+            "net_contact_force": z(n, layout.num_bodies, 3), "actor_root_state": z(n, layout.num_actors, 13)})
+
+        # ---- persistent state, SoA [K,N] ----
+        nact = sp.num_actions
+        s = self.state = {
+            "active_prev_targets": z(NUM_ACTIVE, n), "active_rule_targets": z(NUM_ACTIVE, n),
+            "full_dof_targets": z(n, NUM_DOF), "prev_actions": z(nact, n), "prev_dof_pos": z(NUM_DOF, n),
+            "contact_duration_steps": z(NUM_FINGERS, n), "prev_contact_binary": z(NUM_FINGERS, n),
+            "contact_forces": z(3 * NUM_FINGERS, n), "episode_step_count": z(n, dtype=i64),
+            "prev_finger_dof_vel": z(20, n), "prev_hand_vel": z(3, n), "prev_hand_ang_vel": z(3, n),
+            "prev_contacts": z(NUM_FINGERS, n, dtype=torch.bool),
+            "rng_step": z(1, dtype=i64),
+        }
+        if sp.is_blind_grasping:
+            s.update({
+                "success_duration_steps": z(n, dtype=i64), "success_conditions_met": z(n, dtype=torch.bool),
+                "current_stage": z(n, dtype=i64), "time_in_stage": z(n), "stage_contact_duration": z(n),
+                "just_transitioned_to_stage2": z(n, dtype=torch.bool),
+                "just_transitioned_to_stage3": z(n, dtype=torch.bool),
+                "initial_box_positions": z(3, n), "failure_tensors": z(3, n, dtype=torch.bool)})
+            s["initial_box_positions"][2].fill_(float(self.params.box_z))  # blind_grasping_task.py:424-428
+        self._state = L.DexStateBuffers()
+        for name, _ in L.DexStateBuffers._fields_:
+            setattr(self._state, name, _ptr(s.get(name)))
+
+        # ---- outputs ----
+        rows = self.params.num_component_rows
+        o = self.out = {
+            "obs_buf": z(n, sp.obs_dim), "obs_dict": z(n, sp.dict_dim) if materialize_obs_dict else None,
+            "rew_buf": z(n), "reset_buf": z(n, dtype=torch.bool), "success": z(n, dtype=torch.bool),
+            "failure": z(n, dtype=torch.bool), "timeout": z(n, dtype=torch.bool),
+            "reward_components": z(rows, n), "reset_bits": z((n + 31) // 32, dtype=torch.int32),
+            "counters": z(C["DEX_NUM_COUNTERS"], dtype=torch.int32),
+            "episode_sums": z(rows, n) if observer else None,
+            "episode_lengths": z(n, dtype=torch.int32) if observer else None,
+            "stat_totals": z(4, 2 + rows, dtype=torch.float64) if observer else None,
+        }
+        self._out = L.DexOutBuffers()
+        for name, _ in L.DexOutBuffers._fields_:
+            setattr(self._out, name, _ptr(o.get(name)))
+        e = self.epi = {"env_ids": z(n, dtype=torch.int32), "num_reset": z(1, dtype=torch.int32),
+                        "stats": z(C["DEX_NUM_STATS"]), "consecutive_successes": z(1, dtype=torch.int32)}
+        self._epi = L.DexEpilogueBuffers()
+        self._epi.reset_bits, self._epi.counters = _ptr(o["reset_bits"]), _ptr(o["counters"])
+        self._epi.env_ids, self._epi.num_reset = _ptr(e["env_ids"]), _ptr(e["num_reset"])
+        self._epi.stats, self._epi.consecutive_successes = _ptr(e["stats"]), _ptr(e["consecutive_successes"])
+        self._epi.rng_step = _ptr(s["rng_step"])
+        self.uniforms: Optional[torch.Tensor] = None  # [N,29] injected reset randoms (None = in-kernel Philox)
+        self.launches = 0  # kernels launched through the C ABI (bench.py's gpu_launches)
+
+    # ------------------------------------------------------------------ sim binding (zero-copy)
+    def bind_sim(self, sim: Dict[str, torch.Tensor]):
+        """Point the kernels at the caller's sim tensors.  With Isaac Gym these are the
+        gymtorch.wrap_tensor views (tensor_manager.py:173-328): no copy is ever made."""
+        n, lay = self.n, self.layout
+        want = {"dof_state": n * NUM_DOF * 2, "rigid_body_state": n * lay.num_bodies * 13,
+                "net_contact_force": n * lay.num_bodies * 3, "actor_root_state": n * lay.num_actors * 13}
+        for k, numel in want.items():
+            t = sim.get(k)
+            if t is None:
+                raise L.DexStepError(f"sim tensor '{k}' missing")
+            if t.device != self.device or t.dtype != torch.float32 or not t.is_contiguous() or t.numel() != numel:
+                raise L.DexStepError(f"sim tensor '{k}': need contiguous float32 on {self.device} with {numel} "
+                                     f"elements, got {t.dtype} {tuple(t.shape)} on {t.device}")
+            self.sim_tensors[k] = t
+            setattr(self._sim, k, t.data_ptr())
+        self._graph = None
+
+    # ------------------------------------------------------------------ [N,K] views of SoA state
+    def view(self, name: str) -> torch.Tensor:
+        t = self.state[name]
+        return t.t() if t.dim() == 2 and name != "full_dof_targets" else t
+
+    def _stream(self) -> int:
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    # ------------------------------------------------------------------ kernel launches
+    def pre_physics(self, actions: torch.Tensor, raw_out: Optional[torch.Tensor] = None):
+        """dex_pre_physics: ActionProcessor.process_actions + update_prev_actions (1 launch)."""
+        if actions.shape != (self.n, self.spec.num_actions):
+            raise RuntimeError(f"actions shape {tuple(actions.shape)} != {(self.n, self.spec.num_actions)}")
+        if actions.dtype != torch.float32 or actions.device != self.device or not actions.is_contiguous():
+            raise RuntimeError("actions must be a contiguous float32 tensor on the pipeline's device")
+        L.check(self.lib.dex_pre_physics(ctypes.byref(self.params), ctypes.byref(self._state), actions.data_ptr(),
+                                         _ptr(raw_out), self.n, self._stream()), "dex_pre_physics")
+        self.launches += 1
+
+    def post_physics(self, mode: int = MODE_FULL, flags: int = 0, uniforms: Optional[torch.Tensor] = None):
+        """dex_post_physics: StepProcessor.process_physics_step incl. the fused reset (1 launch)."""
+        u = uniforms if uniforms is not None else self.uniforms
+        if u is not None and (u.shape != (self.n, NUM_UNIFORMS) or u.dtype != torch.float32 or not u.is_contiguous()
+                              or u.device != self.device):
+            raise RuntimeError(f"uniforms must be contiguous float32 [{self.n},{NUM_UNIFORMS}] on {self.device}")
+        if mode == MODE_FULL and not self._reward_initialized:
+            flags |= FLAG_FIRST_REWARD_CALL
+            self._reward_initialized = True
+        L.check(self.lib.dex_post_physics(ctypes.byref(self.params), ctypes.byref(self._sim), ctypes.byref(self._state),
+                                          ctypes.byref(self._out), self.n, mode, flags, _ptr(u), self.seed,
+                                          self.host_step, self._stream()), "dex_post_physics")
+        self.launches += 1
+
+    def reset_idx(self, mask: Optional[torch.Tensor] = None, uniforms: Optional[torch.Tensor] = None):
+        """dex_reset_idx: masked reset (mask None = all envs)."""
+        u = uniforms if uniforms is not None else self.uniforms
+        if mask is not None and (mask.shape != (self.n,) or mask.dtype not in (torch.bool, torch.uint8)
+                                 or mask.device != self.device):
+            raise RuntimeError("reset mask must be a bool/uint8 [N] tensor on the pipeline's device")
+        L.check(self.lib.dex_reset_idx(ctypes.byref(self.params), ctypes.byref(self._sim), ctypes.byref(self._state),
+                                       _ptr(mask), self.n, _ptr(u), self.seed, self.host_step, self._stream()),
+                "dex_reset_idx")
+        self.launches += 1
+
+    def epilogue(self):
+        """dex_step_epilogue: env_ids = nonzero(reset_buf), rates, consecutive_successes (1 launch)."""
+        L.check(self.lib.dex_step_epilogue(ctypes.byref(self.params), ctypes.byref(self._epi), self.n, self._stream()),
+                "dex_step_epilogue")
+        self.host_step += 1
+        self.launches += 1
+
+    def apply_coupling(self, active_soa: torch.Tensor, full_out: torch.Tensor):
+        L.check(self.lib.dex_apply_coupling(ctypes.byref(self.params), active_soa.data_ptr(), full_out.data_ptr(),
+                                            active_soa.shape[1], self._stream()), "dex_apply_coupling")
+        self.launches += 1
+
+    def extract_active_targets(self, full: torch.Tensor, active_soa_out: torch.Tensor):
+        L.check(self.lib.dex_extract_active_targets(ctypes.byref(self.params), full.data_ptr(), active_soa_out.data_ptr(),
+                                                    full.shape[0], self._stream()), "dex_extract_active_targets")
+        self.launches += 1
+
+    # ------------------------------------------------------------------ whole control step
+    def step(self, actions: torch.Tensor, physics=None):
+        """pre-physics -> physics(callable, may be None) -> post-physics (+fused reset) -> epilogue."""
+        self.pre_physics(actions)
+        if physics is not None:
+            physics()
+        self.post_physics()
+        self.epilogue()
+
+    def capture_step_graph(self, actions: torch.Tensor, physics=None):
+        """Capture one control step (3 launches + the physics callable's work) in a CUDA graph.
+        ``actions`` and every bound buffer must keep their addresses.  The first reward call must
+        already have happened (its flag differs), and in-kernel Philox uses the device-resident
+        step counter so replays draw fresh randoms."""
+        if not self._reward_initialized:
+            raise RuntimeError("run at least one eager step before capturing (first reward call initialises prev-state)")
+        side = torch.cuda.Stream(self.device)
+        side.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(side):
+            self.step(actions, physics)  # warm-up on the side stream
+        torch.cuda.current_stream(self.device).wait_stream(side)
+        torch.cuda.synchronize(self.device)
+        g = torch.cuda.CUDAGraph()
+        before = self.launches
+        with torch.cuda.graph(g):
+            self.step(actions, physics)
+        self.launches_per_graph = self.launches - before
+        self._graph = g
+        return g
+
+    def replay(self):
+        if self._graph is None:
+            raise RuntimeError("capture_step_graph() first")
+        self._graph.replay()
+        self.host_step += 1
+        self.launches += self.launches_per_graph
+
+    # ------------------------------------------------------------------ results
+    def env_ids(self) -> torch.Tensor:
+        """== torch.nonzero(reset_buf).flatten() of the last step (host sync: reads the count)."""
+        k = int(self.epi["num_reset"].item())
+        return self.epi["env_ids"][:k].to(torch.int64)
+
+    def reward_components(self) -> Dict[str, torch.Tensor]:
+        rc = self.out["reward_components"]
+        return {name: rc[i] for i, name in enumerate(self.spec.component_names)}
+
+    def obs_dict(self) -> Dict[str, torch.Tensor]:
+        d = self.out["obs_dict"]
+        if d is None:
+            raise RuntimeError("construct the pipeline with materialize_obs_dict=True to read obs_dict")
+        from .params import OBS_KEYS_1D
+        out = {}
+        for k, (a, b) in self.spec.dict_slices.items():
+            out[k] = d[:, a] if k in OBS_KEYS_1D else d[:, a:b]
+        return out

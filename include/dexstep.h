@@ -59,7 +59,7 @@
 extern "C" {
 #endif
 
-#define DEX_ABI_VERSION 3
+#define DEX_ABI_VERSION 4
 
 #define DEX_NUM_DOF 26          /* constants.py:8-10: 6 base + 20 finger DOFs */
 #define DEX_NUM_BASE 6
@@ -258,6 +258,9 @@ typedef struct DexStateBuffers {
   uint8_t* just_transitioned_to_stage3;   /* [N] (BG) */
   float* initial_box_positions;           /* [3][N] (BG) */
   uint8_t* failure_tensors;               /* [3][N] (BG) stage1_pregrasp_failed, stage2_contact_failed, stage3_grasp_lost */
+  uint64_t* rng_step;                     /* [1] optional device-resident Philox step counter: when non-NULL it replaces the
+                                             by-value step_index (which a captured CUDA graph would freeze);
+                                             dex_step_epilogue increments it */
 } DexStateBuffers;
 
 typedef struct DexOutBuffers {
@@ -287,6 +290,7 @@ typedef struct DexEpilogueBuffers {
   int32_t* num_reset;             /* [1] */
   float* stats;                   /* [DEX_NUM_STATS] */
   int32_t* consecutive_successes; /* [1] persistent */
+  uint64_t* rng_step;             /* [1] optional: incremented once per call (see DexStateBuffers.rng_step) */
 } DexEpilogueBuffers;
 
 const char* dex_strerror(int code);
