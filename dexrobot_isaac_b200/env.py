@@ -135,7 +135,8 @@ class DexStepEnv:
         """Fake PhysX step: overwrite the sim buffers in place."""
         t = self.pipeline.sim_tensors
         t["dof_state"].copy_(state["dof_state"].reshape(t["dof_state"].shape))
-        t["rigid_body_state"].copy_(state["rigid_body_states"].reshape(t["rigid_body_state"].shape))
+        rb = state["rigid_body_state"] if "rigid_body_state" in state else state["rigid_body_states"]
+        t["rigid_body_state"].copy_(rb.reshape(t["rigid_body_state"].shape))
         t["net_contact_force"].copy_(state["net_contact_force"].reshape(t["net_contact_force"].shape))
         t["actor_root_state"].copy_(state["actor_root_state"].reshape(t["actor_root_state"].shape))
 
