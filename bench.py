@@ -1,0 +1,511 @@
+#!/usr/bin/env python
+"""bench.py — env-steps/s of the fused step pipeline (BASELINE.json metric) on N B200s of one node.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload NAME]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+One "step" = one control step of the path over one batch of N_env synthetic environments:
+dex_pre_physics + dex_post_physics (with the fused reset of finished envs) + dex_step_epilogue,
+physics replaced by nothing (PhysX is out of scope; the sim-state tensors are static synthetic
+data already resident in HBM).  Default workload = BASELINE.json configs[3]: BlindGrasping,
+16 384 envs per GPU (the config the 1/2/4/8-GPU metric is quoted on); envs shard across ranks with
+no collective on the step path ("weak" scaling) and ONE NCCL all-reduce of the statistics vector
+per timed region.
+
+L2 protocol: the timed loop rotates over a ring of R independent env replicas (each with its own
+sim tensors, path state and outputs) whose total footprint exceeds 2x the 126 MB L2, so every step
+streams its inputs from HBM ("inputs larger than L2").
+
+The CPU oracle (oracle/) is imported ONLY by the cpu_baseline leg and by --impl reference.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+METRIC = "env_steps_per_s_fused_step_pipeline"
+UNIT = "env-steps/s"
+L2_BYTES = 126 * 1024 * 1024
+
+# name -> (task, envs per GPU, algorithmic bytes per env-step: pre, post)   (SURVEY §8d / BASELINE.md §3)
+WORKLOADS = {
+    "blindgrasping_16384": ("BlindGrasping", 16384, 464, 1997),
+    "blindgrasping_4096": ("BlindGrasping", 4096, 464, 1997),
+    "basetask_4096": ("BaseTask", 4096, 464, 2455),
+    "basetask_64": ("BaseTask", 64, 464, 2455),
+}
+DEFAULT_WORKLOAD = "blindgrasping_16384"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=4000)
+    ap.add_argument("--warmup", type=int, default=200)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--envs", type=int, default=0, help="override envs per GPU")
+    ap.add_argument("--observer", type=int, default=0, help="1 = fused RewardComponentObserver on (SURVEY §8f N1)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--sweep", action="store_true", help="also print the post-physics num_envs sweep (configs[4])")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the bounded CPU-baseline sample")
+    return ap.parse_args()
+
+
+def measured_peak_hbm():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """Samples SM clock / throttle reasons through NVML while a timed region runs."""
+
+    def __init__(self, index: int, period_s: float = 0.01):
+        self.index, self.period, self.samples, self._stop = index, period_s, [], threading.Event()
+        self.sm_max, self._thread, self._nvml = None, None, None
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self._nvml = pynvml
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.sm_max = int(pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self._nvml = None
+
+    def _read(self):
+        n = self._nvml
+        mhz = int(n.nvmlDeviceGetClockInfo(self._h, n.NVML_CLOCK_SM))
+        try:
+            reasons = int(n.nvmlDeviceGetCurrentClocksEventReasons(self._h))
+        except Exception:
+            reasons = int(n.nvmlDeviceGetCurrentClocksThrottleReasons(self._h))
+        return mhz, reasons
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                self.samples.append(self._read())
+            except Exception:
+                pass
+            self._stop.wait(self.period)
+
+    def start(self):
+        if self._nvml is not None:
+            self._stop.clear()
+            self._thread = threading.Thread(target=self._run, daemon=True)
+            self._thread.start()
+
+    def stop(self):
+        if self._thread is not None:
+            self._stop.set()
+            self._thread.join()
+            self._thread = None
+
+    def summary(self):
+        if self._nvml is None:
+            return _clocks_from_nvidia_smi(self.index)
+        names = {0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x10: "sync_boost",
+                 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown", 0x80: "hw_power_brake_slowdown",
+                 0x100: "display_clock_setting"}
+        if not self.samples:
+            try:
+                self.samples.append(self._read())
+            except Exception:
+                return {"sm_mhz": None, "sm_max_mhz": self.sm_max, "reasons": [], "samples": 0}
+        mhz = sorted(s[0] for s in self.samples)
+        bits = 0
+        for _, r in self.samples:
+            bits |= r
+        return {"sm_mhz": mhz[len(mhz) // 2], "sm_max_mhz": self.sm_max,
+                "reasons": [v for k, v in names.items() if bits & k], "samples": len(self.samples)}
+
+
+def _clocks_from_nvidia_smi(index):
+    try:
+        out = subprocess.run(["nvidia-smi", f"--id={index}", "--query-gpu=clocks.sm,clocks.max.sm,"
+                              "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+                              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap",
+                              "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=10).stdout
+        f = [x.strip() for x in out.strip().split(",")]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        return {"sm_mhz": int(f[0]), "sm_max_mhz": int(f[1]),
+                "reasons": [n for n, v in zip(names, f[2:]) if v.lower().startswith("active")], "samples": 1}
+    except Exception:
+        return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+
+
+# ------------------------------------------------------------------------------------------------
+# product arm: ring of env replicas on one GPU
+# ------------------------------------------------------------------------------------------------
+class Ring:
+    """R independent replicas of the workload (own sim tensors, path state, outputs, actions)."""
+
+    def __init__(self, task, n, device, seed, observer, min_bytes=2 * L2_BYTES, max_replicas=64):
+        from dexrobot_isaac_b200 import synthetic
+        from dexrobot_isaac_b200.config import load_task_config
+        from dexrobot_isaac_b200.env import DexStepEnv
+        from dexrobot_isaac_b200.params import BodyLayout
+
+        self.task, self.n, self.device = task, n, device
+        self.layout = BodyLayout.default(with_box=task == "BlindGrasping")
+        self.cfg = load_task_config(task, num_envs=n)
+        gen = torch.Generator(device=device).manual_seed(seed)
+        self.envs, self.actions = [], []
+
+        def add():
+            env = DexStepEnv(self.cfg, n, self.layout, synthetic.dof_props(), device=device, observer=bool(observer),
+                             seed=seed + len(self.envs), sim=synthetic.random_state(n, self.layout, gen, device))
+            env.pipeline.uniforms = None  # resets draw from the in-kernel Philox stream
+            env.reset()
+            a = synthetic.random_actions(n, env.num_actions, gen, device).contiguous()
+            for _ in range(2):
+                env.pipeline.step(a)
+            self.envs.append(env)
+            self.actions.append(a)
+
+        add()
+        self.footprint = self.replica_bytes(self.envs[0])
+        r = max(2, -(-min_bytes // self.footprint))
+        self.l2_note = "ring of %d replicas, %.0f MB total > 2x L2 (inputs larger than L2)"
+        if r > max_replicas:
+            r = max_replicas
+            self.l2_note = "ring of %d replicas, %.0f MB total (SMALLER than L2: L2-resident run)"
+        while len(self.envs) < r:
+            add()
+        self.l2_note = self.l2_note % (r, r * self.footprint / 1e6)
+        torch.cuda.synchronize(device)
+
+    @staticmethod
+    def replica_bytes(env):
+        p = env.pipeline
+        ts = list(p.sim_tensors.values()) + list(p.state.values()) + [v for v in p.out.values() if v is not None]
+        return sum(t.numel() * t.element_size() for t in ts)
+
+    def __len__(self):
+        return len(self.envs)
+
+    def launches(self):
+        return sum(e.pipeline.launches for e in self.envs)
+
+    def capture(self, fn, count, start=0):
+        """Capture `count` consecutive ring steps (replica start, start+1, ...) running fn(env, actions)."""
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for i in range(count):
+                j = (start + i) % len(self.envs)
+                fn(self.envs[j], self.actions[j])
+        return g
+
+
+def timed_replays(plan, device, dist_barrier=None):
+    """plan = [(graph, replays)]; returns device milliseconds between two events on the current stream."""
+    if dist_barrier is not None:
+        dist_barrier()
+    torch.cuda.synchronize(device)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for g, reps in plan:
+        for _ in range(reps):
+            g.replay()
+    e1.record()
+    torch.cuda.synchronize(device)
+    if dist_barrier is not None:
+        dist_barrier()
+    return e0.elapsed_time(e1)
+
+
+def make_plan(ring, fn, steps, group):
+    """Graphs that together run exactly `steps` ring steps: q replays of a `group`-step graph + one remainder graph."""
+    plan, per_launch = [], []
+    q, r = divmod(steps, group)
+    if q:
+        plan.append((ring.capture(fn, group), q))
+    if r:
+        plan.append((ring.capture(fn, r, start=(q * group) % len(ring)), 1))
+    return plan
+
+
+def full_step(env, a):
+    env.pipeline.step(a)
+
+
+def post_only(env, a):
+    env.pipeline.post_physics()
+
+
+def pre_only(env, a):
+    env.pipeline.pre_physics(a)
+
+
+def epi_only(env, a):
+    env.pipeline.epilogue()
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU baseline: the oracle (CPU restatement of the reference's torch components) on the host cores.
+# The ONLY place bench.py touches oracle/.
+# ------------------------------------------------------------------------------------------------
+def cpu_reference_run(task, n, steps, warmup, seed, budget_s=None):
+    """Time `steps` control steps of the oracle at `n` envs (after `warmup`); if budget_s is given,
+    run as many steps as fit (>= 3).  Returns (env_steps_per_s, ms_per_step, steps_done, threads)."""
+    from oracle import synth as osynth
+    from oracle.dexstep_oracle import OracleEnv
+    from dexrobot_isaac_b200 import synthetic
+    from dexrobot_isaac_b200.config import load_task_config
+    from dexrobot_isaac_b200.params import BodyLayout
+
+    lay = BodyLayout.default(with_box=task == "BlindGrasping")
+    olay = osynth.BodyLayout(with_box=task == "BlindGrasping")
+    env = OracleEnv(load_task_config(task, num_envs=n), n, olay, synthetic.dof_props())
+    gen = torch.Generator().manual_seed(seed)
+    ring = []
+    for _ in range(4):  # pre-generated ring of states: generation is outside the timed region
+        st = synthetic.random_state(n, lay, gen, "cpu")
+        st["rigid_body_states"] = st.pop("rigid_body_state")
+        ring.append((st, synthetic.random_actions(n, env.num_actions, gen), synthetic.random_uniforms(n, gen)))
+    env.load_state(ring[0][0])
+    env.reset(ring[0][2])
+
+    def one(i):
+        st, a, u = ring[i % len(ring)]
+        env.pre_physics_step(a)
+        env.load_state(st)  # stand-in for the physics step (a memcpy)
+        env.post_physics_step(u)
+
+    for i in range(max(1, warmup)):
+        one(i)
+    t0, done = time.perf_counter(), 0
+    while True:
+        one(done)
+        done += 1
+        el = time.perf_counter() - t0
+        if budget_s is None:
+            if done >= steps:
+                break
+        elif done >= 3 and (el >= budget_s or done >= steps):
+            break
+    return n * done / el, 1e3 * el / done, done, torch.get_num_threads()
+
+
+def run_reference_arm(args, task, n_env, rank, world):
+    """--impl reference: the reference's CPU implementation of the path (oracle port; the reference is
+    pure Python and /root/reference does not travel) on the host cores.  Rank 0 only."""
+    if rank != 0:
+        return
+    total = args.steps + args.warmup
+    # bounded sample: shrink the env batch per step so the whole run ends within ~2 minutes
+    _, ms_full, _, _ = cpu_reference_run(task, n_env, 2, 1, 1234)
+    n_s = n_env
+    while n_s > 64 and total * ms_full * (n_s / n_env) > 120e3:
+        n_s //= 2
+    value, ms, done, threads = cpu_reference_run(task, n_s, args.steps, min(args.warmup, 3), 1234)
+    sample = f"{done} steps x {n_s} envs of {task} (oracle port of the reference's torch components, {threads} threads)"
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": done,
+            "warmup": min(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": args.workload, "task": task, "envs_per_step": n_s, "device": "cpu"},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# end-to-end: host buffers in, host buffers out, copies inside the timed region
+# ------------------------------------------------------------------------------------------------
+def run_e2e(ring, steps, device, barrier):
+    envs = ring.envs[:2]
+    bufs = [e.alloc_host_buffers() for e in envs]
+    for e, a, (hin, _) in zip(envs, ring.actions, bufs):
+        for k, v in e.pipeline.sim_tensors.items():
+            hin[k].copy_(v)
+        hin["actions"].copy_(a)
+    streams = [torch.cuda.Stream(device) for _ in envs]
+    main = torch.cuda.current_stream(device)
+    h2d = d2h = 0
+
+    def loop(k):
+        nonlocal h2d, d2h
+        for i in range(k):
+            j = i % len(envs)
+            with torch.cuda.stream(streams[j]):
+                h2d, d2h = envs[j].step_host(*bufs[j])
+
+    loop(4)
+    torch.cuda.synchronize(device)
+    if barrier is not None:
+        barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(main)
+    for s in streams:
+        s.wait_event(e0)
+    loop(steps)
+    for s in streams:
+        main.wait_stream(s)
+    e1.record(main)
+    torch.cuda.synchronize(device)
+    if barrier is not None:
+        barrier()
+    return e0.elapsed_time(e1), h2d, d2h
+
+
+def kernel_avg_us(ring, fn, launches, group, device):
+    plan = make_plan(ring, fn, launches, group)
+    timed_replays(make_plan(ring, fn, min(launches, group), group), device)  # warm
+    return 1e3 * timed_replays(plan, device) / launches
+
+
+def main():
+    args = parse_args()
+    rank, local, world = (int(os.environ.get(k, d)) for k, d in (("RANK", 0), ("LOCAL_RANK", 0), ("WORLD_SIZE", 1)))
+    task, n_env, b_pre, b_post = WORKLOADS[args.workload]
+    if args.envs:
+        n_env = args.envs
+    if args.impl == "reference":
+        run_reference_arm(args, task, n_env, rank, world)
+        return 0
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: the step pipeline has no CPU fallback")
+    device = torch.device("cuda", local)
+    torch.cuda.set_device(device)
+    barrier = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=device)
+        barrier = lambda: dist.barrier(device_ids=[local])  # noqa: E731
+    from dexrobot_isaac_b200 import _lib
+
+    _lib.load()  # fails loudly when the CUDA library is missing
+    ring = Ring(task, n_env, device, 1234 + rank, args.observer)
+    R = len(ring)
+    group = R * max(1, -(-32 // R))
+    if args.warmup > 0:
+        timed_replays(make_plan(ring, full_step, args.warmup, group), device, barrier)
+    plan = make_plan(ring, full_step, args.steps, group)
+    for e in ring.envs:
+        e.pipeline.epi["totals"].zero_()
+        if e.pipeline.out["stat_totals"] is not None:
+            e.pipeline.out["stat_totals"].zero_()
+    side = torch.cuda.Stream(device)
+    sampler = ClockSampler(torch.cuda._get_nvml_device_index(device) if hasattr(torch.cuda, "_get_nvml_device_index") else local)
+
+    # ---- the timed region: exactly K steps, barrier + synchronize on both sides, device events ----
+    if barrier is not None:
+        barrier()
+    torch.cuda.synchronize(device)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for g, reps in plan:
+        for _ in range(reps):
+            g.replay()
+    e1.record()
+    # the single statistics all-reduce of the logging interval, on a side stream
+    side.wait_event(e1)
+    with torch.cuda.stream(side):
+        payload = torch.stack([e.pipeline.epi["totals"] for e in ring.envs]).sum(dim=0).double()
+        if ring.envs[0].pipeline.out["stat_totals"] is not None:
+            payload = torch.cat([payload, torch.stack([e.pipeline.out["stat_totals"] for e in ring.envs]).sum(0).flatten()])
+        if world > 1:
+            dist.all_reduce(payload)
+    torch.cuda.synchronize(device)
+    if barrier is not None:
+        barrier()
+    sampler.stop()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], device=device, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    stats = payload.cpu().tolist()
+    C = _lib.CONSTS
+    value = n_env * world * args.steps / (ms * 1e-3)
+
+    # ---- dominant-kernel timing for the roofline (post-physics launches only, same ring, graph replay) ----
+    kl = max(R, min(args.steps, 2000))
+    post_us = kernel_avg_us(ring, post_only, kl, group, device)
+    pre_us = kernel_avg_us(ring, pre_only, kl, group, device)
+    epi_us = kernel_avg_us(ring, epi_only, kl, group, device)
+    peak, peak_src = measured_peak_hbm()
+    achieved = b_post * n_env / (post_us * 1e-6) / 1e9
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            traffic = json.load(f).get(f"{task}_{n_env}")
+    except Exception:
+        pass
+    roofline = {"bound": "hbm", "kernel": "post_physics_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                "algorithmic_bytes_per_env": b_post, "launch_us": post_us,
+                "step_frac": (b_pre + b_post) * n_env * args.steps / (ms * 1e-3) / 1e9 / peak}
+
+    # ---- end to end through DexStepEnv.step_host (host buffers, copies inside the timed region) ----
+    ke = max(2, min(args.steps, 200))
+    sampler.start()
+    ems, h2d, d2h = run_e2e(ring, ke, device, barrier)
+    sampler.stop()
+    if world > 1:
+        t = torch.tensor([ems], device=device, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ems = float(t.item())
+    e2e = {"value": n_env * world * ke / (ems * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
+           "d2h_bytes_per_step": d2h, "steps": ke, "ms_per_step": ems / ke,
+           "api": "DexStepEnv.step_host (pinned host buffers, 2 streams)"}
+    clocks = sampler.summary()
+
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": args.workload, "task": task, "envs_per_gpu": n_env, "envs_total": n_env * world,
+                       "obs_dim": ring.envs[0].num_observations, "num_bodies": ring.layout.num_bodies,
+                       "observer": bool(args.observer), "l2": ring.l2_note, "graph_steps": group,
+                       "parallelism": f"env-sharded x{world}, no step-path collective, 1 NCCL all-reduce of stats"},
+            "roofline": roofline, "e2e": e2e, "gpu_launches": 3 * args.steps, "clocks": clocks,
+            "kernels_us": {"pre_physics": pre_us, "post_physics": post_us, "epilogue": epi_us},
+            "episode_stats": {"steps": stats[C["DEX_NUM_COUNTERS"]], "resets": stats[C["DEX_CNT_RESET"]],
+                              "success": stats[C["DEX_CNT_SUCCESS"]], "failure": stats[C["DEX_CNT_FAILURE"]],
+                              "timeout": stats[C["DEX_CNT_TIMEOUT"]],
+                              "episode_length_sum": stats[C["DEX_CNT_EPISODE_LENGTH"]]}}
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        v, cms, done, threads = cpu_reference_run(task, n_env, 10**9, 2, 1234, budget_s=args.cpu_seconds)
+        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "ms_per_step": cms,
+                                "sample": f"{done} steps x {n_env} envs of {task} (same workload; oracle port of the "
+                                          f"reference's torch components; os.cpu_count()={os.cpu_count()})"}
+    if args.sweep and rank == 0:
+        sweep = []
+        for n in (1024, 2048, 4096, 8192, 16384, 32768, 65536, 131072, 262144):
+            r = Ring(task, n, device, 99, args.observer)
+            g = len(r) * max(1, -(-32 // len(r)))
+            us = kernel_avg_us(r, post_only, max(len(r), 600), g, device)
+            sus = kernel_avg_us(r, full_step, max(len(r), 600), g, device)
+            sweep.append({"envs": n, "post_us": us, "post_frac": b_post * n / (us * 1e-6) / 1e9 / peak,
+                          "step_us": sus, "env_steps_per_s": n / (sus * 1e-6), "replicas": len(r)})
+            del r
+            torch.cuda.empty_cache()
+        line["sweep"] = sweep
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

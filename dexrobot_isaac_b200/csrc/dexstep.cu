@@ -308,6 +308,7 @@ __global__ void __launch_bounds__(TILE) post_physics_kernel(const __grid_constan
   const int env = e0 + tid;
   const bool full = (A.mode == DEX_MODE_FULL);
   bool should_reset = false, t_success = false, t_failure = false, t_timeout = false;
+  int ep_len_done = 0;
   bool crit[DEX_NUM_CRITERIA];
 #pragma unroll
   for (int c = 0; c < DEX_NUM_CRITERIA; ++c) crit[c] = false;
@@ -579,6 +580,7 @@ __global__ void __launch_bounds__(TILE) post_physics_kernel(const __grid_constan
       // step_processor.py:80
       const int64_t step_now = step_before + 1;
       st.episode_step_count[env] = step_now;
+      ep_len_done = (int)step_now;
 
       // ---------------- termination (step_processor.py:133-181, termination_manager.py:120-278) ----
       if (P.has_height_safety)
@@ -797,6 +799,12 @@ __global__ void __launch_bounds__(TILE) post_physics_kernel(const __grid_constan
       for (int c = 0; c < DEX_NUM_CRITERIA; ++c)
         if (bc[c]) atomicAdd(A.out.counters + DEX_CNT_CRIT0 + c, __popc(bc[c]));
     }
+    if (rbits) {  // sum of the finished episodes' lengths (warp-uniform branch)
+      int len = should_reset ? ep_len_done : 0;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) len += __shfl_xor_sync(fullmask, len, o);
+      if (lane == 0) atomicAdd(A.out.counters + DEX_CNT_EPISODE_LENGTH, len);
+    }
   }
 
   // ---- stage out: obs tile, coalesced -------------------------------------------------------
@@ -975,6 +983,10 @@ __global__ void __launch_bounds__(1024) epilogue_kernel(const __grid_constant__ 
     int cs = *A.ep.consecutive_successes;
     cs = (c[DEX_CNT_SUCCESS] > 0) ? cs + 1 : 0;
     *A.ep.consecutive_successes = min(cs, A.max_consecutive);
+    if (A.ep.totals != nullptr) {
+      for (int k = 0; k < DEX_NUM_COUNTERS; ++k) A.ep.totals[k] += c[k];
+      A.ep.totals[DEX_NUM_COUNTERS] += 1;
+    }
     for (int k = 0; k < DEX_NUM_COUNTERS; ++k) c[k] = 0;
     if (A.ep.rng_step != nullptr) *A.ep.rng_step += 1;
   }

@@ -108,6 +108,33 @@ class DexStepEnv:
             self.physics()
         return self.post_physics_step()
 
+    # ------------------------------------------------------------------ host-buffer entry (end-to-end path)
+    def alloc_host_buffers(self):
+        """Pinned host mirrors of one step's inputs (sim tensors + actions) and results (obs, rew, reset)."""
+        p = self.pipeline
+        pin = lambda t: torch.empty(t.shape, dtype=t.dtype, pin_memory=True)  # noqa: E731
+        inputs = {k: pin(v) for k, v in p.sim_tensors.items()}
+        inputs["actions"] = pin(self._actions)
+        outputs = {"obs_buf": pin(self.obs_buf), "rew_buf": pin(self.rew_buf), "reset_buf": pin(self.reset_buf)}
+        return inputs, outputs
+
+    def step_host(self, host_inputs: Dict[str, torch.Tensor], host_outputs: Dict[str, torch.Tensor]):
+        """One control step fed from HOST buffers: H2D of the sim state + actions, the three kernel
+        launches, D2H of obs/rew/reset — all asynchronous on the current stream (synchronise the stream
+        before reading ``host_outputs``).  Returns (h2d_bytes, d2h_bytes)."""
+        p = self.pipeline
+        h2d = d2h = 0
+        for k, dst in p.sim_tensors.items():
+            dst.copy_(host_inputs[k], non_blocking=True)
+            h2d += dst.numel() * dst.element_size()
+        self._actions.copy_(host_inputs["actions"], non_blocking=True)
+        h2d += self._actions.numel() * 4
+        p.step(self._actions)
+        for k, src in (("obs_buf", self.obs_buf), ("rew_buf", self.rew_buf), ("reset_buf", self.reset_buf)):
+            host_outputs[k].copy_(src, non_blocking=True)
+            d2h += src.numel() * src.element_size()
+        return h2d, d2h
+
     # ------------------------------------------------------------------ extras (step_processor.py:221-232)
     def _update_extras(self):
         """Lazy: tensors are views/slices of device buffers, no host sync happens here."""

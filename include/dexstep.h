@@ -59,7 +59,7 @@
 extern "C" {
 #endif
 
-#define DEX_ABI_VERSION 4
+#define DEX_ABI_VERSION 5
 
 #define DEX_NUM_DOF 26          /* constants.py:8-10: 6 base + 20 finger DOFs */
 #define DEX_NUM_BASE 6
@@ -137,6 +137,7 @@ enum DexCriterion {
 enum DexCounter {
   DEX_CNT_SUCCESS = 0, DEX_CNT_FAILURE, DEX_CNT_TIMEOUT, DEX_CNT_RESET,
   DEX_CNT_CRIT0, /* .. DEX_CNT_CRIT0 + DEX_NUM_CRITERIA - 1: raw criterion hit counts */
+  DEX_CNT_EPISODE_LENGTH = 10, /* sum of episode_step_count over the envs that reset this step */
   DEX_NUM_COUNTERS = 16
 };
 
@@ -291,6 +292,9 @@ typedef struct DexEpilogueBuffers {
   float* stats;                   /* [DEX_NUM_STATS] */
   int32_t* consecutive_successes; /* [1] persistent */
   uint64_t* rng_step;             /* [1] optional: incremented once per call (see DexStateBuffers.rng_step) */
+  int64_t* totals;                /* [DEX_NUM_COUNTERS + 1] optional running totals since the caller last zeroed them:
+                                     totals[k] += counters[k], totals[DEX_NUM_COUNTERS] += 1 (steps).  Together with
+                                     DexOutBuffers.stat_totals this is the payload of the NCCL all-reduce */
 } DexEpilogueBuffers;
 
 const char* dex_strerror(int code);
