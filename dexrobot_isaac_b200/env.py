@@ -169,6 +169,8 @@ class DexStepEnv:
 
     @property
     def initial_box_positions(self):
+        if not self.spec.is_blind_grasping:
+            raise AttributeError("initial_box_positions exists only for BlindGrasping")
         return self.pipeline.view("initial_box_positions")
 
     def snapshot(self) -> Dict[str, torch.Tensor]:
