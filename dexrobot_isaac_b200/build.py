@@ -15,8 +15,10 @@ import sys
 
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 REPO_ROOT = os.path.dirname(PKG_DIR)
-SOURCES = [os.path.join(PKG_DIR, "csrc", "dexstep.cu")]
-HEADERS = [os.path.join(REPO_ROOT, "include", "dexstep.h")]
+CSRC = os.path.join(PKG_DIR, "csrc")
+SOURCES = [os.path.join(CSRC, "dexstep.cu")]
+HEADERS = [os.path.join(REPO_ROOT, "include", "dexstep.h")] + sorted(
+    os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cuh"))
 LIB_PATH = os.path.join(PKG_DIR, "libdexstep.so")
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-fmad=false", "-std=c++17",

@@ -83,8 +83,7 @@ class DexStepEnv:
             p.uniforms = uniforms.to(self.device, torch.float32).contiguous()
         p.reset_idx(None)
         p.post_physics(MODE_OBS_ONLY, FLAG_STALE_CONTACTS)  # first pass: no refresh_tensors (dexhand_base.py:813)
-        p.post_physics(MODE_FULL)
-        p.epilogue()
+        p.post_step()
         self._update_extras()
         return self.obs_buf
 
@@ -97,8 +96,7 @@ class DexStepEnv:
         p = self.pipeline
         if uniforms is not None:
             p.uniforms = uniforms.to(self.device, torch.float32).contiguous()
-        p.post_physics(MODE_FULL)
-        p.epilogue()
+        p.post_step()
         self._update_extras()
         return self.obs_buf, self.rew_buf, self.reset_buf, self.extras
 

@@ -39,7 +39,7 @@ class StepPipeline:
                  dof_upper: Sequence[float], device="cuda:0", sim: Optional[Dict[str, torch.Tensor]] = None,
                  materialize_obs_dict: bool = False, observer: bool = True, seed: int = 1234,
                  post_action_filters: Sequence[str] = ("velocity_clamp", "position_clamp"),
-                 physics_steps_per_control_step: int = 2):
+                 physics_steps_per_control_step: int = 2, fuse_epilogue: bool = True):
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise L.DexStepError("StepPipeline needs a CUDA device: this path has no CPU or eager fallback")
@@ -56,6 +56,7 @@ class StepPipeline:
         self.host_step = 0
         self._reward_initialized = False
         self._graph = None
+        self.fuse_epilogue = bool(fuse_epilogue)  # epilogue done by the last CTA of the post-physics launch
         n, dev, sp = self.n, self.device, self.spec
         f32, i64, u8 = torch.float32, torch.int64, torch.uint8
 
@@ -109,12 +110,13 @@ class StepPipeline:
             setattr(self._out, name, _ptr(o.get(name)))
         e = self.epi = {"env_ids": z(n, dtype=torch.int32), "num_reset": z(1, dtype=torch.int32),
                         "stats": z(C["DEX_NUM_STATS"]), "consecutive_successes": z(1, dtype=torch.int32),
-                        "totals": z(C["DEX_NUM_COUNTERS"] + 1, dtype=i64)}
+                        "totals": z(C["DEX_NUM_COUNTERS"] + 1, dtype=i64), "ticket": z(1, dtype=torch.int32)}
         self._epi = L.DexEpilogueBuffers()
         self._epi.reset_bits, self._epi.counters = _ptr(o["reset_bits"]), _ptr(o["counters"])
         self._epi.env_ids, self._epi.num_reset = _ptr(e["env_ids"]), _ptr(e["num_reset"])
         self._epi.stats, self._epi.consecutive_successes = _ptr(e["stats"]), _ptr(e["consecutive_successes"])
         self._epi.rng_step, self._epi.totals = _ptr(s["rng_step"]), _ptr(e["totals"])
+        self._epi.ticket = _ptr(e["ticket"])
         self.uniforms: Optional[torch.Tensor] = None  # [N,29] injected reset randoms (None = in-kernel Philox)
         self.launches = 0  # kernels launched through the C ABI (bench.py's gpu_launches)
 
@@ -155,8 +157,10 @@ class StepPipeline:
                                          _ptr(raw_out), self.n, self._stream()), "dex_pre_physics")
         self.launches += 1
 
-    def post_physics(self, mode: int = MODE_FULL, flags: int = 0, uniforms: Optional[torch.Tensor] = None):
-        """dex_post_physics: StepProcessor.process_physics_step incl. the fused reset (1 launch)."""
+    def post_physics(self, mode: int = MODE_FULL, flags: int = 0, uniforms: Optional[torch.Tensor] = None,
+                     fused_epilogue: bool = False):
+        """dex_post_physics: StepProcessor.process_physics_step incl. the fused reset (1 launch).
+        ``fused_epilogue``: the last CTA also does dex_step_epilogue's work (do not call epilogue() then)."""
         u = uniforms if uniforms is not None else self.uniforms
         if u is not None and (u.shape != (self.n, NUM_UNIFORMS) or u.dtype != torch.float32 or not u.is_contiguous()
                               or u.device != self.device):
@@ -165,9 +169,13 @@ class StepPipeline:
             flags |= FLAG_FIRST_REWARD_CALL
             self._reward_initialized = True
         L.check(self.lib.dex_post_physics(ctypes.byref(self.params), ctypes.byref(self._sim), ctypes.byref(self._state),
-                                          ctypes.byref(self._out), self.n, mode, flags, _ptr(u), self.seed,
-                                          self.host_step, self._stream()), "dex_post_physics")
+                                          ctypes.byref(self._out),
+                                          ctypes.byref(self._epi) if fused_epilogue and mode == MODE_FULL else None,
+                                          self.n, mode, flags, _ptr(u), self.seed, self.host_step, self._stream()),
+                "dex_post_physics")
         self.launches += 1
+        if fused_epilogue and mode == MODE_FULL:
+            self.host_step += 1
 
     def reset_idx(self, mask: Optional[torch.Tensor] = None, uniforms: Optional[torch.Tensor] = None):
         """dex_reset_idx: masked reset (mask None = all envs)."""
@@ -203,11 +211,18 @@ class StepPipeline:
         self.pre_physics(actions)
         if physics is not None:
             physics()
-        self.post_physics()
-        self.epilogue()
+        self.post_step()
+
+    def post_step(self, uniforms: Optional[torch.Tensor] = None):
+        """post-physics + step epilogue: one launch when fuse_epilogue, else two."""
+        if self.fuse_epilogue:
+            self.post_physics(uniforms=uniforms, fused_epilogue=True)
+        else:
+            self.post_physics(uniforms=uniforms)
+            self.epilogue()
 
     def capture_step_graph(self, actions: torch.Tensor, physics=None):
-        """Capture one control step (3 launches + the physics callable's work) in a CUDA graph.
+        """Capture one control step (2-3 launches + the physics callable's work) in a CUDA graph.
         ``actions`` and every bound buffer must keep their addresses.  The first reward call must
         already have happened (its flag differs), and in-kernel Philox uses the device-resident
         step counter so replays draw fresh randoms."""

@@ -59,7 +59,7 @@
 extern "C" {
 #endif
 
-#define DEX_ABI_VERSION 5
+#define DEX_ABI_VERSION 6
 
 #define DEX_NUM_DOF 26          /* constants.py:8-10: 6 base + 20 finger DOFs */
 #define DEX_NUM_BASE 6
@@ -295,6 +295,8 @@ typedef struct DexEpilogueBuffers {
   int64_t* totals;                /* [DEX_NUM_COUNTERS + 1] optional running totals since the caller last zeroed them:
                                      totals[k] += counters[k], totals[DEX_NUM_COUNTERS] += 1 (steps).  Together with
                                      DexOutBuffers.stat_totals this is the payload of the NCCL all-reduce */
+  uint32_t* ticket;               /* [1] zero-initialised by the caller; required only when the epilogue is fused into
+                                     dex_post_physics (last-CTA-done ticket; the library leaves it at zero) */
 } DexEpilogueBuffers;
 
 const char* dex_strerror(int code);
@@ -309,10 +311,12 @@ int dex_pre_physics(const DexParams* params, const DexStateBuffers* state, const
 
 /* Post-physics: one pass per env over the sim buffers; see header comment.  `uniforms` [N,29]
  * (row-major) are the reset randoms in [0,1); if NULL they are generated in-kernel (Philox4x32-10
- * keyed by (seed, step_index, env)). */
+ * keyed by (seed, step_index, env)).  `epilogue` (may be NULL): when given and mode == DEX_MODE_FULL,
+ * the work of dex_step_epilogue is done by the last thread block of the same launch (no second
+ * kernel); the caller must then NOT call dex_step_epilogue for this step. */
 int dex_post_physics(const DexParams* params, const DexSimViews* sim, const DexStateBuffers* state,
-                     const DexOutBuffers* out, int32_t n_envs, int32_t mode, uint32_t flags,
-                     const float* uniforms, uint64_t seed, uint64_t step_index, void* stream);
+                     const DexOutBuffers* out, const DexEpilogueBuffers* epilogue, int32_t n_envs, int32_t mode,
+                     uint32_t flags, const float* uniforms, uint64_t seed, uint64_t step_index, void* stream);
 
 /* Masked reset of envs with reset_mask[env] != 0 (NULL = all envs). */
 int dex_reset_idx(const DexParams* params, const DexSimViews* sim, const DexStateBuffers* state,

@@ -64,8 +64,8 @@ def test_error_codes():
     assert lib.dex_pre_physics(ctypes.byref(bad), ctypes.byref(p._state), a.data_ptr(), None, 8, stream) == C["DEX_ERR_PARAM"]
     sim = L.DexSimViews.from_buffer_copy(p._sim)
     sim.dof_state = p._sim.dof_state + 4
-    rc = lib.dex_post_physics(ctypes.byref(p.params), ctypes.byref(sim), ctypes.byref(p._state), ctypes.byref(p._out), 8, 0,
-                              0, None, 0, 0, stream)
+    rc = lib.dex_post_physics(ctypes.byref(p.params), ctypes.byref(sim), ctypes.byref(p._state), ctypes.byref(p._out), None,
+                              8, 0, 0, None, 0, 0, stream)
     assert rc == C["DEX_ERR_ALIGN"]
     assert b"aligned" in lib.dex_strerror(rc)
     with pytest.raises(RuntimeError):
