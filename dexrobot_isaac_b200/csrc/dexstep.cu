@@ -307,8 +307,19 @@ int dex_post_physics(const DexParams* params, const DexSimViews* sim, const DexS
     if (epilogue->ticket == nullptr || epilogue->reset_bits != out->reset_bits || epilogue->counters != out->counters)
       return DEX_ERR_NULL;
   }
-  PostArgs a{*params, *sim, *state, *out, fused ? *epilogue : DexEpilogueBuffers{}, n_envs, mode, flags, fused ? 1 : 0,
-             uniforms, seed, step_index};
+  static thread_local PostArgs a;  // ~7 KB of launch arguments: keep it off the stack
+  a.p = *params;
+  a.sim = *sim;
+  a.st = *state;
+  a.out = *out;
+  a.ep = fused ? *epilogue : DexEpilogueBuffers{};
+  a.n = n_envs;
+  a.mode = mode;
+  a.flags = flags;
+  a.fused_epilogue = fused ? 1 : 0;
+  a.uniforms = uniforms;
+  a.seed = seed;
+  a.step = step_index;
   return launch_post(a, (cudaStream_t)stream);
 }
 

@@ -1,30 +1,95 @@
 // post_physics.cuh — the fused post-physics kernel (StepProcessor.process_physics_step, step_processor.py:37-131).
 //
-// Mapping: one CTA of kPostThreads (8 warps) owns a tile of 32 consecutive envs.
-//   phase 0  stage-in   every input of the tile is copied global -> shared with cp.async (LDGSTS): AoS sim
-//                       buffers row-per-warp (consecutive lanes = consecutive floats of one env row, so each
-//                       request is one or two sectors), SoA state rows lane-per-env (128 B per request).
-//                       All copies are in flight at once; one wait.
-//   phase 1  items      the per-env work is cut into independent *items* (one DOF, one fingertip/pad pose, one
-//                       contact sensor, one pad pair, ...).  Warps take items round-robin; inside a warp
-//                       lane = env, so every branch on the item type is warp-uniform and every shared-memory
-//                       access `slab[lane * stride + const]` (stride odd) is bank-conflict free.  Items write
-//                       observation columns into the shared obs tile, state rows straight to global (128 B
-//                       coalesced) and a few per-env scalars into a scratch area.
-//   phase 2  scalar     warp 0 (lane = env) runs the short serial part: finger-box contact logic, stage FSM,
-//                       termination, reward terms, masks, counters (warp ballots), fused reset of finished envs.
-//   phase 3  stage-out  obs tile shared -> global, row-per-warp, fully coalesced.
-//   phase 4  epilogue   optional: the last CTA to finish (atomic ticket) compacts the reset mask into the
-//                       ordered env-id list and finalises the termination statistics (no extra launch).
+// Design: "gather table -> compute on a shared-memory slab -> scatter table".
+//   One CTA of 256 threads (8 warps) owns a tile of 32 consecutive envs.  Every env of the tile has a SLAB of
+//   floats in shared memory (odd stride, so `slab[lane * stride + const]` never bank-conflicts when lane = env).
+//   phase 0  stage-in    cp.async (LDGSTS) copies, all in flight at once, one wait:
+//                        * the Isaac Gym AoS rows (dof_state row, 11 rigid-body rows, 5(+1) contact rows, box root
+//                          row, full_dof_targets row) row-per-warp: consecutive lanes = consecutive floats of a row;
+//                        * the path's SoA state rows through a host-built IN TABLE (row pointer, slab slot, type):
+//                          lane = env, one 128 B line per request.
+//   phase 1  items       the per-env arithmetic is cut into independent work items (one fingertip/pad pose, one
+//                        contact sensor, one pad pair, one DOF velocity, hand, box).  Warps take items round-robin,
+//                        lane = env: item-type branches are warp-uniform, all shared accesses conflict-free.
+//                        Items read slab slots and write slab slots - no global memory, no layout logic.
+//   phase 2  scalar      warp 0, lane = env: contact logic, stage FSM, termination, reward terms, masks -> slab;
+//                        cross-env counters via warp ballots.
+//   phase 3  stage-out   * obs_buf rows (and the optional obs_dict rows) are GATHERED from the slab through a
+//                          host-built column map (obs column -> slab slot), row-per-warp, coalesced;
+//                        * every updated state / output row leaves through the OUT TABLE (f32 / u8 / i64 rows),
+//                          lane = env, 128 B per request.
+//   phase 4  reset       tiles that contain finished envs (CTA-uniform vote) apply the fused reset.
+//   phase 5  epilogue    optional: the last CTA to finish (atomic ticket) compacts the reset mask into the ordered
+//                        env-id list and finalises the termination statistics (no extra launch).
 #pragma once
 #include "dexstep_common.cuh"
 
 namespace {
 
-constexpr int kTile = 32;          // envs per CTA == warp width (lane = env in phases 1-2)
+constexpr int kTile = 32;          // envs per CTA == warp width (lane = env)
 constexpr int kPostThreads = 256;  // 8 warps
 constexpr int kPostWarps = kPostThreads / 32;
 constexpr int kRbW = 13 + 10 * 7;  // hand row (13) + 5 tips + 5 pads (7 each) = 83
+constexpr int kMaxIn = 128, kMaxOut = 192, kMaxObs = 256, kMaxDict = 512;
+
+// ---- slab slots (floats).  Fixed part; the optional sections follow at run-time offsets (PostArgs.o_*). ----
+enum : int {
+  I_DOF = 0,                 // 52  dof_state row (pos, vel interleaved)
+  I_RB = I_DOF + 52,         // 83  hand row (13) | 5 tip poses | 5 pad poses
+  I_CF = I_RB + kRbW,        // 18  5 monitored contact forces | box contact force
+  I_BOX = I_CF + 18,         // 6   box pos | box linvel
+  S_PDP = I_BOX + 6,         // 26  prev_dof_pos in  -> finite-difference velocity out (in place)
+  S_APT = S_PDP + 26,        // 18  active_prev_targets
+  S_PACT = S_APT + 18,       // 18  prev_actions
+  S_CDUR = S_PACT + 18,      // 5   contact_duration_steps (updated in place)
+  S_PBIN = S_CDUR + 5,       // 5   prev_contact_binary in -> contact_binary out (in place)
+  S_BOX0 = S_PBIN + 5,       // 3   initial_box_positions
+  S_STEP = S_BOX0 + 3,       // int episode_step_count (updated in place)
+  S_SDS = S_STEP + 1,        // int success_duration_steps
+  S_STAGE = S_SDS + 1,       // int current_stage
+  S_TIS = S_STAGE + 1,       // time_in_stage
+  S_SCD = S_TIS + 1,         // stage_contact_duration
+  C_CMAG = S_SCD + 1,        // 5   contact force magnitude
+  C_CDURS = C_CMAG + 5,      // 5   contact duration in seconds
+  C_PADBOX = C_CDURS + 5,    // 5   pad -> box distance
+  C_HDIFF = C_PADBOX + 5,    // 5   |pad_z - box_z|
+  C_TIPBOX = C_HDIFF + 5,    // 5   tip -> box distance
+  C_PAIR = C_TIPBOX + 5,     // 10  pad pair distances
+  C_CEN = C_PAIR + 10,       // 3   centroid of the first three pads
+  C_HANDBOX = C_CEN + 3,
+  C_CDIST,
+  C_DRIFT,
+  C_VMAG,
+  C_BOXHAS,
+  C_AVGDIST,
+  C_AVGHDIFF,
+  C_THUMB,
+  C_OTHERS,
+  C_GRASP,
+  C_GRASPDUR,
+  C_STAGEF,
+  C_PROG,
+  C_EPTIME,
+  M_RESET,  // masks as float 0/1 (they leave as u8 rows)
+  M_SUCC,
+  M_FAIL,
+  M_TIMEOUT,
+  M_SCM,
+  M_J2,
+  M_J3,
+  M_FT0,
+  M_FT1,
+  M_FT2,
+  C_REW,
+  C_COMP  // num_component_rows reward components; the optional sections follow
+};
+// offsets inside the optional sections
+enum : int { HF_TIP = 0, HF_PAD = 35, HF_ARR = 70, HF_SIZE = 74 };  // hand-frame poses, ARR-aligned quaternion
+enum : int {                                                         // common-reward state and partial terms
+  CP_PFDV = 0, CP_PHV = 20, CP_PHA = 23, CP_PCON = 26, CP_CNOW = 31, CP_CHG = 36, CP_RHAND = 41,
+  CP_FV2 = 45, CP_FA2 = 65, CP_JL = 85, CP_SIZE = 105
+};
+enum : int { ROW_F32 = 0, ROW_U8 = 1, ROW_I64 = 2 };
 
 struct PostArgs {
   DexParams p;
@@ -39,73 +104,218 @@ struct PostArgs {
   const float* uniforms;
   uint64_t seed;
   uint64_t step;
+  // ---- derived on the host at launch (build_post_tables) ----
+  int32_t stride;                       // slab stride (odd)
+  int32_t o_tgt, o_hf, o_cpv;           // optional sections (-1 = absent)
+  int32_t want_hf_tip, want_hf_pad, want_arr, common, dict_dim;
+  int32_t n_in, n_out;
+  uint64_t in_ptr[kMaxIn];              // row base pointers
+  uint16_t in_meta[kMaxIn];             // slot | type << 12
+  uint64_t out_ptr[kMaxOut];
+  uint16_t out_meta[kMaxOut];
+  int16_t obs_src[kMaxObs];             // obs column -> slab slot
+  int16_t dict_src[kMaxDict];           // obs_dict column -> slab slot
 };
 
-// Per-env slab in shared memory (float offsets).  Computed identically on host (smem size) and device.
-struct Slab {
-  int dof;   // 52  dof_state row (pos, vel interleaved)
-  int rb;    // 83  hand row + 5 tip + 5 pad poses
-  int cf;    // 18  5 monitored contact forces + box contact force
-  int box;   // 6   box pos + linvel
-  int vel;   // 26  prev_dof_pos in, finite-difference velocity out (in place)
-  int st;    // 49  active_prev_targets 18 | prev_actions 18 | contact_duration 5 | prev_contact_binary 5 | box0 3
-  int tgt;   // 26  full_dof_targets row (only when a *_dof_target key is wanted)
-  int cpv;   // 26  common-reward prev state: finger dof vel 20 | hand vel 3 | hand ang vel 3
-  int obs;   // obs_dim
-  int scr;   // scratch scalars
-  int stride;
-};
-
-// scratch slots
-enum {
-  SC_CBIN = 0,      // 5 contact_binary (0/1)
-  SC_CMAG = 5,      // 5 contact force magnitude
-  SC_CHG = 10,      // 5 contact change flags (common rewards)
-  SC_PADBOX = 15,   // 5 pad -> box distance
-  SC_HDIFF = 20,    // 5 |pad_z - box_z|
-  SC_TIPBOX = 25,   // 5 tip -> box distance
-  SC_HANDBOX = 30,  // hand -> box distance
-  SC_CDIST = 31,    // |centroid - box|
-  SC_DRIFT = 32,    // |box - box0|
-  SC_VMAG = 33,     // |v_box|
-  SC_BOXHAS = 34,   // box contact force above threshold (0/1)
-  SC_RHAND = 35,    // 4 hand velocity / acceleration reward terms (common)
-  SC_BASE = 39,
-  SC_FV2 = 39,      // 20 squared finger dof velocities (common)
-  SC_FA2 = 59,      // 20 squared finger dof accelerations
-  SC_JL = 79,       // 20 joint-limit terms
-  SC_COMMON_END = 99
-};
-
-__host__ __device__ inline bool post_want_targets(const DexParams& P, bool dict) {
-  return dict || P.obs_offset[DEX_K_BASE_DOF_TARGET] >= 0 || P.obs_offset[DEX_K_ACTIVE_FINGER_DOF_TARGET] >= 0 ||
-         P.obs_offset[DEX_K_ALL_FINGER_DOF_TARGET] >= 0;
+// ------------------------------------------------------------------------------------------------
+// host: slab layout, IN / OUT tables, observation column maps
+// ------------------------------------------------------------------------------------------------
+inline int obs_key_dim(const DexParams& P, const int key) {
+  switch (key) {
+    case DEX_K_BASE_DOF_POS: case DEX_K_BASE_DOF_VEL: case DEX_K_BASE_DOF_TARGET: return 6;
+    case DEX_K_ACTIVE_FINGER_DOF_POS: case DEX_K_ACTIVE_FINGER_DOF_VEL: case DEX_K_ACTIVE_FINGER_DOF_TARGET: return 12;
+    case DEX_K_ALL_FINGER_DOF_POS: case DEX_K_ALL_FINGER_DOF_VEL: case DEX_K_ALL_FINGER_DOF_TARGET: return 20;
+    case DEX_K_HAND_POSE: case DEX_K_HAND_POSE_ARR_ALIGNED: return 7;
+    case DEX_K_CONTACT_FORCES: return 15;
+    case DEX_K_PREV_ACTIONS: return P.num_actions;
+    case DEX_K_ACTIVE_PREV_TARGETS: case DEX_K_ACTIVE_RULE_TARGETS: return 18;
+    case DEX_K_CONTACT_FORCE_MAGNITUDE: case DEX_K_CONTACT_BINARY: case DEX_K_CONTACT_DURATION: return 5;
+    case DEX_K_FINGERTIP_POSES_WORLD: case DEX_K_FINGERTIP_POSES_HAND: case DEX_K_FINGERPAD_POSES_WORLD:
+    case DEX_K_FINGERPAD_POSES_HAND: return 35;
+    case DEX_K_OBJECT_POS: case DEX_K_OBJECT_VEL: case DEX_K_FIRST_THREE_FINGERPAD_CENTROID: return 3;
+    case DEX_K_FINGER_TO_OBJECT_DISTANCES: case DEX_K_FINGER_TO_OBJECT_HEIGHT_DIFF: return 5;
+    case DEX_K_FINGERPAD_DISTANCES: return 10;
+    default: return 1;
+  }
 }
 
-__host__ __device__ inline Slab make_slab(const DexParams& P, bool dict) {
-  Slab s;
-  int o = 0;
-  s.dof = o; o += 2 * DEX_NUM_DOF;
-  s.rb = o; o += kRbW;
-  s.cf = o; o += 18;
-  s.box = o; o += 6;
-  s.vel = o; o += DEX_NUM_DOF;
-  s.st = o; o += 49;
-  s.tgt = o; o += post_want_targets(P, dict) ? DEX_NUM_DOF : 0;
-  s.cpv = o; o += P.need_common_rewards ? 26 : 0;
-  s.obs = o; o += P.obs_dim;
-  s.scr = o; o += P.need_common_rewards ? SC_COMMON_END : SC_BASE;
-  s.stride = o | 1;  // odd stride: lane-per-env accesses hit 32 different banks
-  return s;
+// slab slot that holds element j of observation key `key`
+inline int obs_key_slot(const PostArgs& a, const int key, const int j) {
+  const DexParams& P = a.p;
+  switch (key) {
+    case DEX_K_BASE_DOF_POS: return I_DOF + 2 * j;
+    case DEX_K_BASE_DOF_VEL: return S_PDP + j;
+    case DEX_K_ACTIVE_FINGER_DOF_POS: return I_DOF + 2 * P.active_finger_dof[j];
+    case DEX_K_ACTIVE_FINGER_DOF_VEL: return S_PDP + P.active_finger_dof[j];
+    case DEX_K_ALL_FINGER_DOF_POS: return I_DOF + 2 * (DEX_NUM_BASE + j);
+    case DEX_K_ALL_FINGER_DOF_VEL: return S_PDP + DEX_NUM_BASE + j;
+    case DEX_K_HAND_POSE: return I_RB + j;
+    case DEX_K_HAND_POSE_ARR_ALIGNED: return j < 3 ? I_RB + j : a.o_hf + HF_ARR + (j - 3);
+    case DEX_K_CONTACT_FORCES: return I_CF + j;
+    case DEX_K_PREV_ACTIONS: return S_PACT + j;
+    case DEX_K_ACTIVE_PREV_TARGETS: case DEX_K_ACTIVE_RULE_TARGETS: return S_APT + j;
+    case DEX_K_BASE_DOF_TARGET: return a.o_tgt + j;
+    case DEX_K_ACTIVE_FINGER_DOF_TARGET: return a.o_tgt + P.active_finger_dof[j];
+    case DEX_K_ALL_FINGER_DOF_TARGET: return a.o_tgt + DEX_NUM_BASE + j;
+    case DEX_K_CONTACT_FORCE_MAGNITUDE: return C_CMAG + j;
+    case DEX_K_CONTACT_BINARY: return S_PBIN + j;
+    case DEX_K_CONTACT_DURATION: return C_CDURS + j;
+    case DEX_K_FINGERTIP_POSES_WORLD: return I_RB + 13 + j;
+    case DEX_K_FINGERTIP_POSES_HAND: return a.o_hf + HF_TIP + j;
+    case DEX_K_FINGERPAD_POSES_WORLD: return I_RB + 13 + 35 + j;
+    case DEX_K_FINGERPAD_POSES_HAND: return a.o_hf + HF_PAD + j;
+    case DEX_K_EPISODE_TIME: return C_EPTIME;
+    case DEX_K_OBJECT_POS: return I_BOX + j;
+    case DEX_K_OBJECT_VEL: return I_BOX + 3 + j;
+    case DEX_K_FINGER_TO_OBJECT_DISTANCES: return C_PADBOX + j;
+    case DEX_K_AVG_FINGER_TO_OBJECT_DISTANCE: return C_AVGDIST;
+    case DEX_K_FINGER_TO_OBJECT_HEIGHT_DIFF: return C_HDIFF + j;
+    case DEX_K_AVG_FINGER_TO_OBJECT_HEIGHT_DIFF: return C_AVGHDIFF;
+    case DEX_K_HAND_TO_OBJECT_DISTANCE: return C_HANDBOX;
+    case DEX_K_FINGERPAD_DISTANCES: return C_PAIR + j;
+    case DEX_K_FIRST_THREE_FINGERPAD_CENTROID: return C_CEN + j;
+    case DEX_K_THUMB_CONTACT: return C_THUMB;
+    case DEX_K_OTHER_FINGERS_CONTACT: return C_OTHERS;
+    case DEX_K_GRASP_STATE: return C_GRASP;
+    case DEX_K_GRASP_DURATION: return C_GRASPDUR;
+    case DEX_K_CURRENT_STAGE: return C_STAGEF;
+    case DEX_K_TIME_IN_STAGE: return S_TIS;
+    case DEX_K_STAGE_PROGRESS: return C_PROG;
+    default: return -1;
+  }
 }
 
-__host__ __device__ inline size_t post_smem_bytes(const DexParams& P, bool dict) {
-  return (size_t)make_slab(P, dict).stride * kTile * sizeof(float);
+// Fills the derived part of PostArgs.  Returns DEX_OK or DEX_ERR_SIZE when a table overflows.
+inline int build_post_tables(PostArgs& a) {
+  const DexParams& P = a.p;
+  const DexStateBuffers& st = a.st;
+  const bool bg = P.task == DEX_TASK_BLIND_GRASPING, dict = a.out.obs_dict != nullptr;
+  const bool full = a.mode == DEX_MODE_FULL;
+  const bool stale = (a.flags & DEX_FLAG_STALE_CONTACTS) != 0;
+  const size_t N = (size_t)a.n;
+  auto wanted = [&](int key) { return dict || P.obs_offset[key] >= 0; };
+  a.common = (full && P.need_common_rewards) ? 1 : 0;
+  a.want_hf_tip = wanted(DEX_K_FINGERTIP_POSES_HAND);
+  a.want_hf_pad = wanted(DEX_K_FINGERPAD_POSES_HAND);
+  a.want_arr = wanted(DEX_K_HAND_POSE_ARR_ALIGNED);
+  const bool want_tgt = wanted(DEX_K_BASE_DOF_TARGET) || wanted(DEX_K_ACTIVE_FINGER_DOF_TARGET) ||
+                        wanted(DEX_K_ALL_FINGER_DOF_TARGET);
+  int o = C_COMP + P.num_component_rows;
+  a.o_tgt = want_tgt ? o : -1;
+  o += want_tgt ? DEX_NUM_DOF : 0;
+  const bool want_hf = a.want_hf_tip || a.want_hf_pad || a.want_arr;
+  a.o_hf = want_hf ? o : -1;
+  o += want_hf ? HF_SIZE : 0;
+  a.o_cpv = P.need_common_rewards ? o : -1;
+  o += P.need_common_rewards ? CP_SIZE : 0;
+  a.stride = o | 1;
+  if (a.stride >= 4096) return DEX_ERR_SIZE;
+
+  // ---- IN table ----
+  int ni = 0;
+  bool ok = true;
+  auto in = [&](const void* base, size_t row, int elem, int slot, int type) {
+    if (ni >= kMaxIn) { ok = false; return; }
+    a.in_ptr[ni] = (uint64_t)(uintptr_t)((const char*)base + row * N * elem);
+    a.in_meta[ni] = (uint16_t)(slot | (type << 12));
+    ++ni;
+  };
+  for (int d = 0; d < DEX_NUM_DOF; ++d) in(st.prev_dof_pos, d, 4, S_PDP + d, ROW_F32);
+  for (int k = 0; k < DEX_NUM_ACTIVE; ++k) in(st.active_prev_targets, k, 4, S_APT + k, ROW_F32);
+  for (int k = 0; k < P.num_actions; ++k) in(st.prev_actions, k, 4, S_PACT + k, ROW_F32);
+  for (int f = 0; f < DEX_NUM_FINGERS; ++f) in(st.contact_duration_steps, f, 4, S_CDUR + f, ROW_F32);
+  for (int f = 0; f < DEX_NUM_FINGERS; ++f) in(st.prev_contact_binary, f, 4, S_PBIN + f, ROW_F32);
+  in(st.episode_step_count, 0, 8, S_STEP, ROW_I64);
+  if (bg) {
+    for (int c = 0; c < 3; ++c) in(st.initial_box_positions, c, 4, S_BOX0 + c, ROW_F32);
+    in(st.success_duration_steps, 0, 8, S_SDS, ROW_I64);
+    in(st.current_stage, 0, 8, S_STAGE, ROW_I64);
+    in(st.time_in_stage, 0, 4, S_TIS, ROW_F32);
+    in(st.stage_contact_duration, 0, 4, S_SCD, ROW_F32);
+  }
+  if (a.common && !(a.flags & DEX_FLAG_FIRST_REWARD_CALL)) {
+    for (int j = 0; j < DEX_NUM_FINGER_DOF; ++j) in(st.prev_finger_dof_vel, j, 4, a.o_cpv + CP_PFDV + j, ROW_F32);
+    for (int c = 0; c < 3; ++c) in(st.prev_hand_vel, c, 4, a.o_cpv + CP_PHV + c, ROW_F32);
+    for (int c = 0; c < 3; ++c) in(st.prev_hand_ang_vel, c, 4, a.o_cpv + CP_PHA + c, ROW_F32);
+    for (int f = 0; f < DEX_NUM_FINGERS; ++f) in(st.prev_contacts, f, 1, a.o_cpv + CP_PCON + f, ROW_U8);
+  }
+  if (stale)
+    for (int i = 0; i < 15; ++i) in(st.contact_forces, i, 4, I_CF + i, ROW_F32);
+  a.n_in = ni;
+
+  // ---- OUT table ----
+  int no = 0;
+  auto out = [&](void* base, size_t row, int elem, int slot, int type) {
+    if (no >= kMaxOut) { ok = false; return; }
+    a.out_ptr[no] = (uint64_t)(uintptr_t)((char*)base + row * N * elem);
+    a.out_meta[no] = (uint16_t)(slot | (type << 12));
+    ++no;
+  };
+  for (int d = 0; d < DEX_NUM_DOF; ++d) out(st.prev_dof_pos, d, 4, I_DOF + 2 * d, ROW_F32);  // prev_dof_pos <- pos
+  for (int k = 0; k < DEX_NUM_ACTIVE; ++k) out(st.active_rule_targets, k, 4, S_APT + k, ROW_F32);  // rules.py:78-95
+  for (int f = 0; f < DEX_NUM_FINGERS; ++f) out(st.contact_duration_steps, f, 4, S_CDUR + f, ROW_F32);
+  for (int f = 0; f < DEX_NUM_FINGERS; ++f) out(st.prev_contact_binary, f, 4, S_PBIN + f, ROW_F32);
+  if (st.contact_forces != nullptr && !stale)
+    for (int i = 0; i < 15; ++i) out(st.contact_forces, i, 4, I_CF + i, ROW_F32);
+  if (bg) {
+    out(st.success_duration_steps, 0, 8, S_SDS, ROW_I64);
+    out(st.success_conditions_met, 0, 1, M_SCM, ROW_U8);
+    out(st.current_stage, 0, 8, S_STAGE, ROW_I64);
+    out(st.time_in_stage, 0, 4, S_TIS, ROW_F32);
+    out(st.stage_contact_duration, 0, 4, S_SCD, ROW_F32);
+    out(st.just_transitioned_to_stage2, 0, 1, M_J2, ROW_U8);
+    out(st.just_transitioned_to_stage3, 0, 1, M_J3, ROW_U8);
+  }
+  if (full) {
+    out(st.episode_step_count, 0, 8, S_STEP, ROW_I64);
+    if (bg)
+      for (int c = 0; c < 3; ++c) out(st.failure_tensors, c, 1, M_FT0 + c, ROW_U8);
+    for (int r = 0; r < P.num_component_rows; ++r) out(a.out.reward_components, r, 4, C_COMP + r, ROW_F32);
+    out(a.out.rew_buf, 0, 4, C_REW, ROW_F32);
+    out(a.out.reset_buf, 0, 1, M_RESET, ROW_U8);
+    out(a.out.success, 0, 1, M_SUCC, ROW_U8);
+    out(a.out.failure, 0, 1, M_FAIL, ROW_U8);
+    out(a.out.timeout, 0, 1, M_TIMEOUT, ROW_U8);
+    if (a.common) {
+      for (int j = 0; j < DEX_NUM_FINGER_DOF; ++j)
+        out(st.prev_finger_dof_vel, j, 4, I_DOF + 2 * (DEX_NUM_BASE + j) + 1, ROW_F32);  // Isaac dof_vel
+      for (int c = 0; c < 3; ++c) out(st.prev_hand_vel, c, 4, I_RB + 7 + c, ROW_F32);
+      for (int c = 0; c < 3; ++c) out(st.prev_hand_ang_vel, c, 4, I_RB + 10 + c, ROW_F32);
+      for (int f = 0; f < DEX_NUM_FINGERS; ++f) out(st.prev_contacts, f, 1, a.o_cpv + CP_CNOW + f, ROW_U8);
+    }
+  }
+  a.n_out = no;
+
+  // ---- observation column maps ----
+  if (P.obs_dim > kMaxObs) return DEX_ERR_SIZE;
+  for (int c = 0; c < kMaxObs; ++c) a.obs_src[c] = 0;
+  const int nkeys = bg ? DEX_NUM_OBS_KEYS : DEX_K_OBJECT_POS;
+  for (int key = 0; key < DEX_NUM_OBS_KEYS; ++key) {
+    const int off = P.obs_offset[key];
+    if (off < 0) continue;
+    const int dim = obs_key_dim(P, key);
+    if (key >= nkeys || off + dim > P.obs_dim) return DEX_ERR_PARAM;
+    for (int j = 0; j < dim; ++j) a.obs_src[off + j] = (int16_t)obs_key_slot(a, key, j);
+  }
+  a.dict_dim = 0;
+  if (dict) {
+    if (P.dict_dim > kMaxDict) return DEX_ERR_SIZE;
+    a.dict_dim = P.dict_dim;
+    for (int c = 0; c < kMaxDict; ++c) a.dict_src[c] = 0;
+    for (int key = 0; key < nkeys; ++key) {
+      const int off = P.dict_offset[key], dim = obs_key_dim(P, key);
+      if (off < 0 || off + dim > P.dict_dim) return DEX_ERR_PARAM;
+      for (int j = 0; j < dim; ++j) a.dict_src[off + j] = (int16_t)obs_key_slot(a, key, j);
+    }
+  }
+  return ok ? DEX_OK : DEX_ERR_SIZE;
 }
 
-__device__ __forceinline__ void cp_async4(float* smem_dst, const float* gsrc) {
-  const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(s), "l"(gsrc) : "memory");
+// ------------------------------------------------------------------------------------------------
+// device helpers
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void cp_async4(const unsigned smem_dst, const void* gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(smem_dst), "l"(gsrc) : "memory");
 }
 __device__ __forceinline__ void cp_async_wait_all() {
   asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;\n" ::: "memory");
@@ -128,343 +338,235 @@ __device__ __forceinline__ int rb_slot_offset(const DexParams& P, const int s) {
 // phase 0: stage-in
 // ------------------------------------------------------------------------------------------------
 template <bool BG>
-__device__ __forceinline__ void post_stage_in(const PostArgs& A, const Slab& L, float* smem, const int e0, const int ne,
-                                              const bool want_tgt) {
+__device__ __forceinline__ void post_stage_in(const PostArgs& A, float* smem, const int e0, const int ne) {
   const DexParams& P = A.p;
-  const DexStateBuffers& st = A.st;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const size_t N = (size_t)A.n;
-  const int S = L.stride;
-  const bool full = A.mode == DEX_MODE_FULL;
-  const bool common = full && P.need_common_rewards;
-
-  // ---- SoA state rows: lane = env, warps take rows round-robin (each request = one 128 B line) ----
-  if (lane < ne) {
-    float* E = smem + lane * S;
-    const size_t col = (size_t)e0 + lane;
-    int r = warp;
-    for (; r < DEX_NUM_DOF; r += kPostWarps) cp_async4(E + L.vel + r, st.prev_dof_pos + r * N + col);
-    r -= DEX_NUM_DOF;
-    for (; r < DEX_NUM_ACTIVE; r += kPostWarps) cp_async4(E + L.st + r, st.active_prev_targets + r * N + col);
-    r -= DEX_NUM_ACTIVE;
-    for (; r < P.num_actions; r += kPostWarps) cp_async4(E + L.st + 18 + r, st.prev_actions + r * N + col);
-    r -= P.num_actions;
-    for (; r < DEX_NUM_FINGERS; r += kPostWarps) cp_async4(E + L.st + 36 + r, st.contact_duration_steps + r * N + col);
-    r -= DEX_NUM_FINGERS;
-    for (; r < DEX_NUM_FINGERS; r += kPostWarps) cp_async4(E + L.st + 41 + r, st.prev_contact_binary + r * N + col);
-    r -= DEX_NUM_FINGERS;
-    if (BG) {
-      for (; r < 3; r += kPostWarps) cp_async4(E + L.st + 46 + r, st.initial_box_positions + r * N + col);
-      r -= 3;
-    }
-    if (common) {
-      for (; r < DEX_NUM_FINGER_DOF; r += kPostWarps) cp_async4(E + L.cpv + r, st.prev_finger_dof_vel + r * N + col);
-      r -= DEX_NUM_FINGER_DOF;
-      for (; r < 3; r += kPostWarps) cp_async4(E + L.cpv + 20 + r, st.prev_hand_vel + r * N + col);
-      r -= 3;
-      for (; r < 3; r += kPostWarps) cp_async4(E + L.cpv + 23 + r, st.prev_hand_ang_vel + r * N + col);
-      r -= 3;
-    }
-    if (A.flags & DEX_FLAG_STALE_CONTACTS) {
-      for (; r < 15; r += kPostWarps) cp_async4(E + L.cf + r, st.contact_forces + r * N + col);
-    }
-  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int S = A.stride;
+  const unsigned sbase = (unsigned)__cvta_generic_to_shared(smem);
 
   // ---- AoS sim rows: warps take env rows round-robin, consecutive lanes = consecutive floats ----
-  const int nb = P.num_bodies;
-  // per-lane gather offsets (depend on the lane only): rigid slots lane, lane+32, lane+64; contact slot lane
-  const int rbo0 = rb_slot_offset(P, lane), rbo1 = rb_slot_offset(P, lane + 32);
-  const int rbo2 = (lane + 64 < kRbW) ? rb_slot_offset(P, lane + 64) : 0;
-  const bool need_hand_vel = common;  // hand velocities only feed the common reward terms
-  int cfo = 0;
   {
-    const int f = lane / 3, c = lane - f * 3;
-    int body = 0;
+    const int nb = P.num_bodies;
+    const int rbo0 = rb_slot_offset(P, lane), rbo1 = rb_slot_offset(P, lane + 32);
+    const int rbo2 = rb_slot_offset(P, min(lane + 64, kRbW - 1));
+    int cfo = 0;
+    {
+      const int f = lane / 3, c = lane - f * 3;
+      int body = 0;
 #pragma unroll
-    for (int k = 0; k < DEX_NUM_FINGERS; ++k)
-      if (f == k) body = P.contact_body[k];
-    if (BG && f == DEX_NUM_FINGERS) body = P.box_body;
-    cfo = body * 3 + c;
+      for (int k = 0; k < DEX_NUM_FINGERS; ++k)
+        if (f == k) body = P.contact_body[k];
+      if (BG && f == DEX_NUM_FINGERS) body = P.box_body;
+      cfo = body * 3 + c;
+    }
+    const bool stale = (A.flags & DEX_FLAG_STALE_CONTACTS) != 0;
+    const bool p_rb0 = lane < 7 || lane >= 13 || A.common;  // hand velocities only feed the common reward terms
+    const bool p_rb2 = lane + 64 < kRbW;
+    const bool p_dof1 = lane + 32 < 2 * DEX_NUM_DOF;
+    const bool p_cf = lane < (BG ? 18 : 15) && (lane >= 15 || !stale);
+    const bool p_box = BG && lane < 6;
+    const bool p_tgt = A.o_tgt >= 0 && lane < DEX_NUM_DOF;
+    const int boxo = BG ? P.box_actor * 13 + (lane < 3 ? lane : lane + 4) : 0;
+    const float* g_dof = A.sim.dof_state + (size_t)e0 * (2 * DEX_NUM_DOF) + lane;
+    const float* g_rb = A.sim.rigid_body_state + (size_t)e0 * nb * 13;
+    const float* g_cf = A.sim.net_contact_force + (size_t)e0 * nb * 3 + cfo;
+    const float* g_box = BG ? A.sim.actor_root_state + (size_t)e0 * P.num_actors * 13 + boxo : nullptr;
+    const float* g_tgt = A.st.full_dof_targets + (size_t)e0 * DEX_NUM_DOF + lane;
+    const int rb_row = nb * 13, cf_row = nb * 3, box_row = P.num_actors * 13;
+#pragma unroll 4
+    for (int e = warp; e < ne; e += kPostWarps) {
+      const unsigned E = sbase + (unsigned)(e * S + lane) * 4u;
+      cp_async4(E + I_DOF * 4, g_dof + e * (2 * DEX_NUM_DOF));
+      if (p_dof1) cp_async4(E + (I_DOF + 32) * 4, g_dof + e * (2 * DEX_NUM_DOF) + 32);
+      const float* rb = g_rb + (size_t)e * rb_row;
+      if (p_rb0) cp_async4(E + I_RB * 4, rb + rbo0);
+      cp_async4(E + (I_RB + 32) * 4, rb + rbo1);
+      if (p_rb2) cp_async4(E + (I_RB + 64) * 4, rb + rbo2);
+      if (p_cf) cp_async4(E + I_CF * 4, g_cf + (size_t)e * cf_row);
+      if (p_box) cp_async4(E + I_BOX * 4, g_box + (size_t)e * box_row);
+      if (p_tgt) cp_async4(E + (unsigned)A.o_tgt * 4u, g_tgt + e * DEX_NUM_DOF);
+    }
   }
-  const int ncf = BG ? 18 : 15;
-  for (int e = warp; e < ne; e += kPostWarps) {
-    float* E = smem + e * S;
-    const size_t env = (size_t)e0 + e;
-    {  // dof_state row: 52 contiguous floats
-      const float* src = A.sim.dof_state + env * (2 * DEX_NUM_DOF);
-      cp_async4(E + L.dof + lane, src + lane);
-      if (lane + 32 < 2 * DEX_NUM_DOF) cp_async4(E + L.dof + lane + 32, src + lane + 32);
+
+  // ---- SoA state rows through the IN table: lane = env, one 128 B line per request ----
+  if (lane < ne) {
+    const unsigned E = sbase + (unsigned)(lane * S) * 4u;
+    const size_t col = (size_t)e0 + lane;
+    float* Ef = smem + lane * S;
+    bool converted = false;
+    for (int r = warp; r < A.n_in; r += kPostWarps) {
+      const unsigned meta = A.in_meta[r];
+      const unsigned slot = meta & 0xfffu, type = meta >> 12;
+      const char* base = reinterpret_cast<const char*>(A.in_ptr[r]);
+      if (type == ROW_F32) {
+        cp_async4(E + slot * 4u, base + col * 4);
+      } else if (type == ROW_I64) {  // int64 state is small: keep the low word (counts, stage)
+        Ef[slot] = __int_as_float((int)__ldg(reinterpret_cast<const long long*>(base) + col));
+        converted = true;
+      } else {
+        Ef[slot] = __ldg(reinterpret_cast<const unsigned char*>(base) + col) ? 1.0f : 0.0f;
+        converted = true;
+      }
     }
-    {  // rigid-body rows
-      const float* src = A.sim.rigid_body_state + env * (size_t)nb * 13;
-      if (lane < 7 || lane >= 13 || need_hand_vel) cp_async4(E + L.rb + lane, src + rbo0);
-      cp_async4(E + L.rb + lane + 32, src + rbo1);
-      if (lane + 64 < kRbW) cp_async4(E + L.rb + lane + 64, src + rbo2);
-    }
-    if (lane < ncf && (lane >= 15 || !(A.flags & DEX_FLAG_STALE_CONTACTS)))
-      cp_async4(E + L.cf + lane, A.sim.net_contact_force + env * (size_t)nb * 3 + cfo);
-    if (BG && lane < 6)
-      cp_async4(E + L.box + lane,
-                A.sim.actor_root_state + (env * P.num_actors + P.box_actor) * 13 + (lane < 3 ? lane : lane + 4));
-    if (want_tgt && lane < DEX_NUM_DOF) cp_async4(E + L.tgt + lane, st.full_dof_targets + env * DEX_NUM_DOF + lane);
+    (void)converted;
   }
   cp_async_wait_all();
 }
 
 // ------------------------------------------------------------------------------------------------
-// phase 1: items (lane = env, item type warp-uniform)
+// phase 1: items (lane = env, item type warp-uniform; slab in, slab out)
 // ------------------------------------------------------------------------------------------------
-template <bool DICT>
-struct Emitter {
-  const DexParams& P;
-  float* obs;   // shared obs row of this env
-  float* dict;  // global obs_dict row of this env (DICT only)
-  __device__ __forceinline__ void operator()(const int key, const int j, const float v) const {
-    const int o = P.obs_offset[key];
-    if (o >= 0) obs[o + j] = v;
-    if (DICT) dict[P.dict_offset[key] + j] = v;
-  }
-  __device__ __forceinline__ bool want(const int key) const { return DICT || P.obs_offset[key] >= 0; }
-};
-
-template <bool BG, bool DICT>
-__device__ __forceinline__ void post_items(const PostArgs& A, const Slab& L, float* smem, const int* s_dof2fin,
-                                           const int e0, const int ne, const bool want_tgt) {
+template <bool BG>
+__device__ __forceinline__ void post_items(const PostArgs& A, float* smem, const int ne) {
   const DexParams& P = A.p;
-  const DexStateBuffers& st = A.st;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (lane >= ne) return;
-  const size_t N = (size_t)A.n;
-  const size_t env = (size_t)e0 + lane;
-  float* E = smem + lane * L.stride;
-  float* scr = E + L.scr;
-  const Emitter<DICT> emit{P, E + L.obs, DICT ? A.out.obs_dict + env * P.dict_dim : nullptr};
+  float* E = smem + lane * A.stride;
+  const float* rb = E + I_RB;
   const float dt = P.control_dt;
-  const bool full = A.mode == DEX_MODE_FULL;
-  const bool common = full && P.need_common_rewards;
+  const bool common = A.common != 0;
   const bool first = (A.flags & DEX_FLAG_FIRST_REWARD_CALL) != 0;
-  const float* rb = E + L.rb;
 
   // item ranges (heavy items first so the round-robin spreads them over the warps)
-  const int i_pose = 0, i_contact = 10, i_pair = 15, i_hand = BG ? 25 : 15, i_box = i_hand + 1;
-  const int i_dof = BG ? i_box + 1 : i_box, i_apt = i_dof + DEX_NUM_DOF, i_pact = i_apt + DEX_NUM_ACTIVE;
-  const int i_tgt = i_pact + P.num_actions, n_items = i_tgt + (want_tgt ? DEX_NUM_DOF : 0);
+  const int i_contact = 10, i_pair = 15, i_hand = BG ? 25 : 15, i_box = i_hand + 1;
+  const int i_dof = BG ? i_box + 1 : i_box, n_items = i_dof + DEX_NUM_DOF;
 
   for (int it = warp; it < n_items; it += kPostWarps) {
     if (it < i_contact) {
-      // ---- tip / pad pose: world + hand frame (observation_encoder.py:737-751, 915-986) ----
-      const int f = it - i_pose;
+      // ---- tip / pad pose f: hand-frame pose (observation_encoder.py:915-986), distances to the box ----
+      const int f = it;
       const bool is_pad = f >= DEX_NUM_FINGERS;
       const int g = is_pad ? f - DEX_NUM_FINGERS : f;
       const float* p = rb + 13 + 7 * f;
       const float px = p[0], py = p[1], pz = p[2];
-      const Quat q{p[3], p[4], p[5], p[6]};
-      const int kw = is_pad ? DEX_K_FINGERPAD_POSES_WORLD : DEX_K_FINGERTIP_POSES_WORLD;
-      const int kh = is_pad ? DEX_K_FINGERPAD_POSES_HAND : DEX_K_FINGERTIP_POSES_HAND;
-      emit(kw, 7 * g + 0, px);
-      emit(kw, 7 * g + 1, py);
-      emit(kw, 7 * g + 2, pz);
-      emit(kw, 7 * g + 3, q.x);
-      emit(kw, 7 * g + 4, q.y);
-      emit(kw, 7 * g + 5, q.z);
-      emit(kw, 7 * g + 6, q.w);
-      if (emit.want(kh)) {
+      if (is_pad ? A.want_hf_pad : A.want_hf_tip) {
         const Quat hq{rb[3], rb[4], rb[5], rb[6]};
         const Vec3 ph = quat_rotate_inverse(hq, Vec3{px - rb[0], py - rb[1], pz - rb[2]});
-        const Quat qh = quat_mul(quat_conj(hq), q);
-        emit(kh, 7 * g + 0, ph.x);
-        emit(kh, 7 * g + 1, ph.y);
-        emit(kh, 7 * g + 2, ph.z);
-        emit(kh, 7 * g + 3, qh.x);
-        emit(kh, 7 * g + 4, qh.y);
-        emit(kh, 7 * g + 5, qh.z);
-        emit(kh, 7 * g + 6, qh.w);
+        const Quat qh = quat_mul(quat_conj(hq), Quat{p[3], p[4], p[5], p[6]});
+        float* o = E + A.o_hf + (is_pad ? HF_PAD : HF_TIP) + 7 * g;
+        o[0] = ph.x;
+        o[1] = ph.y;
+        o[2] = ph.z;
+        o[3] = qh.x;
+        o[4] = qh.y;
+        o[5] = qh.z;
+        o[6] = qh.w;
       }
       if (BG) {  // blind_grasping_task.py:684-724, 1178-1192
-        const float* box = E + L.box;
+        const float* box = E + I_BOX;
         const float d = norm3(px - box[0], py - box[1], pz - box[2]);
         if (is_pad) {
-          const float hd = fabsf(pz - box[2]);
-          scr[SC_PADBOX + g] = d;
-          scr[SC_HDIFF + g] = hd;
-          emit(DEX_K_FINGER_TO_OBJECT_DISTANCES, g, d);
-          emit(DEX_K_FINGER_TO_OBJECT_HEIGHT_DIFF, g, hd);
+          E[C_PADBOX + g] = d;
+          E[C_HDIFF + g] = fabsf(pz - box[2]);
         } else {
-          scr[SC_TIPBOX + g] = d;
+          E[C_TIPBOX + g] = d;
         }
       }
     } else if (it < i_pair) {
       // ---- contact sensor f (observation_encoder.py:658-735, 323-361; reward_calculator.py:183-199) ----
       const int f = it - i_contact;
-      const float* cf = E + L.cf + 3 * f;
-      const float fx = cf[0], fy = cf[1], fz = cf[2];
-      emit(DEX_K_CONTACT_FORCES, 3 * f, fx);
-      emit(DEX_K_CONTACT_FORCES, 3 * f + 1, fy);
-      emit(DEX_K_CONTACT_FORCES, 3 * f + 2, fz);
-      if (st.contact_forces != nullptr && !(A.flags & DEX_FLAG_STALE_CONTACTS)) {
-        st.contact_forces[(size_t)(3 * f) * N + env] = fx;
-        st.contact_forces[(size_t)(3 * f + 1) * N + env] = fy;
-        st.contact_forces[(size_t)(3 * f + 2) * N + env] = fz;
-      }
-      const float mag = norm3(fx, fy, fz);
+      const float* cf = E + I_CF + 3 * f;
+      const float mag = norm3(cf[0], cf[1], cf[2]);
       const bool bin = mag > P.contact_binary_threshold;
-      emit(DEX_K_CONTACT_FORCE_MAGNITUDE, f, mag);
-      emit(DEX_K_CONTACT_BINARY, f, bin ? 1.0f : 0.0f);
-      const float dur = E[L.st + 36 + f], prevb = E[L.st + 41 + f];
+      const float dur = E[S_CDUR + f], prevb = E[S_PBIN + f];
       const float ndur = (bin && prevb == 0.0f) ? 1.0f : (bin ? dur + 1.0f : 0.0f);
-      st.contact_duration_steps[f * N + env] = ndur;
-      st.prev_contact_binary[f * N + env] = bin ? 1.0f : 0.0f;
-      emit(DEX_K_CONTACT_DURATION, f, ndur * dt);
-      scr[SC_CBIN + f] = bin ? 1.0f : 0.0f;
-      scr[SC_CMAG + f] = mag;
+      E[S_CDUR + f] = ndur;
+      E[S_PBIN + f] = bin ? 1.0f : 0.0f;
+      E[C_CMAG + f] = mag;
+      E[C_CDURS + f] = ndur * dt;
       if (common) {
+        float* cp = E + A.o_cpv;
         const bool c_now = mag > 0.1f;  // hard-coded 0.1 N (reward_calculator.py:186)
-        const bool c_prev = first ? c_now : (st.prev_contacts[f * N + env] != 0);
-        st.prev_contacts[f * N + env] = c_now ? 1 : 0;
-        scr[SC_CHG + f] = (c_now != c_prev) ? 1.0f : 0.0f;
+        const bool c_prev = first ? c_now : (cp[CP_PCON + f] != 0.0f);
+        cp[CP_CNOW + f] = c_now ? 1.0f : 0.0f;
+        cp[CP_CHG + f] = (c_now != c_prev) ? 1.0f : 0.0f;
       }
     } else if (BG && it < i_hand) {
       // ---- pad pair distance, triu order (blind_grasping_task.py:726-771) ----
       const int k = it - i_pair;
-      int a = 0, b = 0, c = 0;
-#pragma unroll
-      for (int x = 0; x < DEX_NUM_FINGERS; ++x)
-#pragma unroll
-        for (int y = x + 1; y < DEX_NUM_FINGERS; ++y) {
-          if (c == k) {
-            a = x;
-            b = y;
-          }
-          ++c;
-        }
+      // k -> (a, b): rows of the strict upper triangle of a 5x5 matrix start at 0, 4, 7, 9
+      const int a = (k >= 4) + (k >= 7) + (k >= 9);
+      const int b = k - (a == 0 ? 0 : a == 1 ? 4 : a == 2 ? 7 : 9) + a + 1;
       const float* pa = rb + 13 + 35 + 7 * a;
       const float* pb = rb + 13 + 35 + 7 * b;
-      emit(DEX_K_FINGERPAD_DISTANCES, k, norm3(pa[0] - pb[0], pa[1] - pb[1], pa[2] - pb[2]));
+      E[C_PAIR + k] = norm3(pa[0] - pb[0], pa[1] - pb[1], pa[2] - pb[2]);
     } else if (it == i_hand) {
-      // ---- hand pose (:632-656), ARR-aligned pose (:1483-1521), hand velocity reward terms ----
-#pragma unroll
-      for (int c = 0; c < 7; ++c) emit(DEX_K_HAND_POSE, c, rb[c]);
-      if (emit.want(DEX_K_HAND_POSE_ARR_ALIGNED)) {
+      // ---- ARR-aligned pose (:1483-1521), hand -> box distance, hand velocity reward terms ----
+      if (A.want_arr) {
         const float sh = 0.7071067811865476f;
         const Quat qa = quat_mul(Quat{rb[3], rb[4], rb[5], rb[6]}, Quat{-0.0f, -sh, -0.0f, sh});
-        emit(DEX_K_HAND_POSE_ARR_ALIGNED, 0, rb[0]);
-        emit(DEX_K_HAND_POSE_ARR_ALIGNED, 1, rb[1]);
-        emit(DEX_K_HAND_POSE_ARR_ALIGNED, 2, rb[2]);
-        emit(DEX_K_HAND_POSE_ARR_ALIGNED, 3, qa.x);
-        emit(DEX_K_HAND_POSE_ARR_ALIGNED, 4, qa.y);
-        emit(DEX_K_HAND_POSE_ARR_ALIGNED, 5, qa.z);
-        emit(DEX_K_HAND_POSE_ARR_ALIGNED, 6, qa.w);
+        float* o = E + A.o_hf + HF_ARR;
+        o[0] = qa.x;
+        o[1] = qa.y;
+        o[2] = qa.z;
+        o[3] = qa.w;
       }
       if (BG) {
-        const float* box = E + L.box;
-        const float d = norm3(rb[0] - box[0], rb[1] - box[1], rb[2] - box[2]);
-        scr[SC_HANDBOX] = d;
-        emit(DEX_K_HAND_TO_OBJECT_DISTANCE, 0, d);
+        const float* box = E + I_BOX;
+        E[C_HANDBOX] = norm3(rb[0] - box[0], rb[1] - box[1], rb[2] - box[2]);
       }
       if (common) {  // reward_calculator.py:100-181
+        float* cp = E + A.o_cpv;
         float hv[3], ha[3], phv[3], pha[3];
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
           hv[c] = rb[7 + c];
           ha[c] = rb[10 + c];
-          phv[c] = first ? hv[c] : E[L.cpv + 20 + c];
-          pha[c] = first ? ha[c] : E[L.cpv + 23 + c];
-          st.prev_hand_vel[c * N + env] = hv[c];
-          st.prev_hand_ang_vel[c * N + env] = ha[c];
+          phv[c] = first ? hv[c] : cp[CP_PHV + c];
+          pha[c] = first ? ha[c] : cp[CP_PHA + c];
         }
-        scr[SC_RHAND + 0] = expf(-0.2f * norm3(hv[0], hv[1], hv[2]));
-        scr[SC_RHAND + 1] = expf(-0.2f * norm3(ha[0], ha[1], ha[2]));
-        scr[SC_RHAND + 2] = expf(-0.5f * norm3(hv[0] - phv[0], hv[1] - phv[1], hv[2] - phv[2]));
-        scr[SC_RHAND + 3] = expf(-0.5f * norm3(ha[0] - pha[0], ha[1] - pha[1], ha[2] - pha[2]));
+        cp[CP_RHAND + 0] = expf(-0.2f * norm3(hv[0], hv[1], hv[2]));
+        cp[CP_RHAND + 1] = expf(-0.2f * norm3(ha[0], ha[1], ha[2]));
+        cp[CP_RHAND + 2] = expf(-0.5f * norm3(hv[0] - phv[0], hv[1] - phv[1], hv[2] - phv[2]));
+        cp[CP_RHAND + 3] = expf(-0.5f * norm3(ha[0] - pha[0], ha[1] - pha[1], ha[2] - pha[2]));
       }
     } else if (BG && it == i_box) {
-      // ---- box state, pad centroid, stability inputs (blind_grasping_task.py:569-600, 746-771, 1334-1364) ----
-      const float* box = E + L.box;
-#pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        emit(DEX_K_OBJECT_POS, c, box[c]);
-        emit(DEX_K_OBJECT_VEL, c, box[3 + c]);
-      }
+      // ---- pad centroid, box stability inputs (blind_grasping_task.py:746-771, 1334-1364) ----
+      const float* box = E + I_BOX;
       float cen[3];
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
         cen[c] = (rb[13 + 35 + c] + rb[13 + 35 + 7 + c] + rb[13 + 35 + 14 + c]) / 3.0f;
-        emit(DEX_K_FIRST_THREE_FINGERPAD_CENTROID, c, cen[c]);
+        E[C_CEN + c] = cen[c];
       }
-      scr[SC_CDIST] = norm3(cen[0] - box[0], cen[1] - box[1], cen[2] - box[2]);
-      const float* b0 = E + L.st + 46;
-      scr[SC_DRIFT] = norm3(box[0] - b0[0], box[1] - b0[1], box[2] - b0[2]);
-      scr[SC_VMAG] = norm3(box[3], box[4], box[5]);
-      const float* cfb = E + L.cf + 15;
-      scr[SC_BOXHAS] = (norm3(cfb[0], cfb[1], cfb[2]) > P.contact_binary_threshold) ? 1.0f : 0.0f;
-    } else if (it < i_apt) {
-      // ---- DOF d: finite-difference velocity (:298-321), position / velocity slices (:612-630) ----
-      const int d = it - i_dof;
-      const float pos = E[L.dof + 2 * d];
-      const float v = (pos - E[L.vel + d]) / dt;
-      E[L.vel + d] = v;
-      st.prev_dof_pos[d * N + env] = pos;
-      if (d < DEX_NUM_BASE) {
-        emit(DEX_K_BASE_DOF_POS, d, pos);
-        emit(DEX_K_BASE_DOF_VEL, d, v);
-      } else {
-        const int j = d - DEX_NUM_BASE;
-        emit(DEX_K_ALL_FINGER_DOF_POS, j, pos);
-        emit(DEX_K_ALL_FINGER_DOF_VEL, j, v);
-        if (common) {  // reward_calculator.py:94-98,138-160: Isaac dof_vel, not the finite difference
-          const float iv = E[L.dof + 2 * d + 1];
-          const float pv = first ? iv : E[L.cpv + j];
-          st.prev_finger_dof_vel[j * N + env] = iv;
-          scr[SC_FV2 + j] = iv * iv;
-          const float acc = iv - pv;
-          scr[SC_FA2 + j] = acc * acc;
-          const float nj = 2.0f * (pos - P.dof_lower[d]) / (P.dof_upper[d] - P.dof_lower[d]) - 1.0f;
-          scr[SC_JL + j] = clampf(fabsf(nj) - 0.8f, 0.0f, 1.0f);
-        }
-      }
-      const int af = s_dof2fin[d];
-      if (af >= 0) {
-        emit(DEX_K_ACTIVE_FINGER_DOF_POS, af, pos);
-        emit(DEX_K_ACTIVE_FINGER_DOF_VEL, af, v);
-      }
-    } else if (it < i_pact) {
-      // ---- active target a: identity pre-action rule (rules.py:78-95) ----
-      const int a = it - i_apt;
-      const float t = E[L.st + a];
-      st.active_rule_targets[a * N + env] = t;
-      emit(DEX_K_ACTIVE_PREV_TARGETS, a, t);
-      emit(DEX_K_ACTIVE_RULE_TARGETS, a, t);
-    } else if (it < i_tgt) {
-      const int k = it - i_pact;
-      emit(DEX_K_PREV_ACTIONS, k, E[L.st + 18 + k]);
+      E[C_CDIST] = norm3(cen[0] - box[0], cen[1] - box[1], cen[2] - box[2]);
+      const float* b0 = E + S_BOX0;
+      E[C_DRIFT] = norm3(box[0] - b0[0], box[1] - b0[1], box[2] - b0[2]);
+      E[C_VMAG] = norm3(box[3], box[4], box[5]);
+      const float* cfb = E + I_CF + 15;
+      E[C_BOXHAS] = (norm3(cfb[0], cfb[1], cfb[2]) > P.contact_binary_threshold) ? 1.0f : 0.0f;
     } else {
-      // ---- DOF target d (:664-701) ----
-      const int d = it - i_tgt;
-      const float t = E[L.tgt + d];
-      if (d < DEX_NUM_BASE)
-        emit(DEX_K_BASE_DOF_TARGET, d, t);
-      else
-        emit(DEX_K_ALL_FINGER_DOF_TARGET, d - DEX_NUM_BASE, t);
-      const int af = s_dof2fin[d];
-      if (af >= 0) emit(DEX_K_ACTIVE_FINGER_DOF_TARGET, af, t);
+      // ---- DOF d: finite-difference velocity (observation_encoder.py:298-321), common-reward partial terms ----
+      const int d = it - i_dof;
+      const float pos = E[I_DOF + 2 * d];
+      E[S_PDP + d] = (pos - E[S_PDP + d]) / dt;
+      if (common && d >= DEX_NUM_BASE) {  // reward_calculator.py:94-98,138-160: Isaac dof_vel, not the finite difference
+        float* cp = E + A.o_cpv;
+        const int j = d - DEX_NUM_BASE;
+        const float iv = E[I_DOF + 2 * d + 1];
+        const float pv = first ? iv : cp[CP_PFDV + j];
+        cp[CP_FV2 + j] = iv * iv;
+        const float acc = iv - pv;
+        cp[CP_FA2 + j] = acc * acc;
+        const float nj = 2.0f * (pos - P.dof_lower[d]) / (P.dof_upper[d] - P.dof_lower[d]) - 1.0f;
+        cp[CP_JL + j] = clampf(fabsf(nj) - 0.8f, 0.0f, 1.0f);
+      }
     }
   }
 }
 
 // ------------------------------------------------------------------------------------------------
-// phase 2: per-env scalar part (warp 0, lane = env)
+// phase 2: per-env scalar part (warp 0, lane = env).  Returns should_reset of this lane.
 // ------------------------------------------------------------------------------------------------
-template <bool BG, bool DICT>
-__device__ __forceinline__ void post_scalar(const PostArgs& A, const Slab& L, float* smem, const int e0, const int ne) {
+template <bool BG>
+__device__ __forceinline__ bool post_scalar(const PostArgs& A, float* smem, const int e0, const int ne) {
   const DexParams& P = A.p;
-  const DexStateBuffers& st = A.st;
   const int lane = threadIdx.x & 31;
   const bool active = lane < ne;
   const size_t N = (size_t)A.n;
   const size_t env = (size_t)e0 + lane;
-  float* E = smem + lane * L.stride;
-  const float* scr = E + L.scr;
-  const float* rb = E + L.rb;
+  float* E = smem + lane * A.stride;
+  const float* rb = E + I_RB;
   const float dt = P.control_dt;
   const bool full = A.mode == DEX_MODE_FULL;
 
@@ -475,10 +577,9 @@ __device__ __forceinline__ void post_scalar(const PostArgs& A, const Slab& L, fl
   for (int c = 0; c < DEX_NUM_CRITERIA; ++c) crit[c] = false;
 
   if (active) {
-    const Emitter<DICT> emit{P, E + L.obs, DICT ? A.out.obs_dict + env * P.dict_dim : nullptr};
     // episode_time from the PRE-increment step count (dexhand_base.py:703-712)
-    const int64_t step_before = st.episode_step_count[env];
-    emit(DEX_K_EPISODE_TIME, 0, (float)step_before * dt);
+    const int step_before = __float_as_int(E[S_STEP]);
+    E[C_EPTIME] = (float)step_before * dt;
     float min_tip_z = rb[13 + 2];
 #pragma unroll
     for (int f = 1; f < DEX_NUM_FINGERS; ++f) min_tip_z = fminf(min_tip_z, rb[13 + 7 * f + 2]);
@@ -486,45 +587,45 @@ __device__ __forceinline__ void post_scalar(const PostArgs& A, const Slab& L, fl
     // ---------------- BlindGrasping task observations + FSM (blind_grasping_task.py:549-978) ----
     float avg_hdiff = 0.0f, grasp_duration = 0.0f, min_tip_box = 0.0f, box_z = 0.0f;
     bool thumb_c = false, others_c = false, grasp = false, j2 = false, j3 = false;
-    int64_t stage = 0, sds = 0;
+    int stage = 0, sds = 0;
     if (BG) {
-      box_z = E[L.box + 2];
+      box_z = E[I_BOX + 2];
       float dsum = 0.0f, hsum = 0.0f;
 #pragma unroll
       for (int f = 0; f < DEX_NUM_FINGERS; ++f) {
-        dsum += scr[SC_PADBOX + f];
-        hsum += scr[SC_HDIFF + f];
+        dsum += E[C_PADBOX + f];
+        hsum += E[C_HDIFF + f];
       }
       avg_hdiff = hsum / 5.0f;
-      emit(DEX_K_AVG_FINGER_TO_OBJECT_DISTANCE, 0, dsum / 5.0f);
-      emit(DEX_K_AVG_FINGER_TO_OBJECT_HEIGHT_DIFF, 0, avg_hdiff);
+      E[C_AVGDIST] = dsum / 5.0f;
+      E[C_AVGHDIFF] = avg_hdiff;
       // finger-box contacts :773-833
-      const bool box_has = scr[SC_BOXHAS] != 0.0f;
+      const bool box_has = E[C_BOXHAS] != 0.0f;
       bool cbin[DEX_NUM_FINGERS], fbc[DEX_NUM_FINGERS];
       int n_on_box = 0;
 #pragma unroll
       for (int f = 0; f < DEX_NUM_FINGERS; ++f) {
-        cbin[f] = scr[SC_CBIN + f] != 0.0f;
-        fbc[f] = cbin[f] && box_has && (scr[SC_PADBOX + f] < P.proximity_threshold);
+        cbin[f] = E[S_PBIN + f] != 0.0f;
+        fbc[f] = cbin[f] && box_has && (E[C_PADBOX + f] < P.proximity_threshold);
         n_on_box += fbc[f] ? 1 : 0;
       }
       thumb_c = fbc[0];
       others_c = fbc[1] || fbc[2] || fbc[3] || fbc[4];
       grasp = thumb_c && others_c;
-      emit(DEX_K_THUMB_CONTACT, 0, thumb_c ? 1.0f : 0.0f);
-      emit(DEX_K_OTHER_FINGERS_CONTACT, 0, others_c ? 1.0f : 0.0f);
-      emit(DEX_K_GRASP_STATE, 0, grasp ? 1.0f : 0.0f);
+      E[C_THUMB] = thumb_c ? 1.0f : 0.0f;
+      E[C_OTHERS] = others_c ? 1.0f : 0.0f;
+      E[C_GRASP] = grasp ? 1.0f : 0.0f;
       // success duration :626-648
       const bool cond = (box_z > P.success_height_threshold) && (n_on_box >= P.min_fingers_for_grasp);
-      sds = cond ? st.success_duration_steps[env] + 1 : 0;
-      st.success_duration_steps[env] = sds;
-      st.success_conditions_met[env] = cond ? 1 : 0;
+      sds = cond ? __float_as_int(E[S_SDS]) + 1 : 0;
+      E[S_SDS] = __int_as_float(sds);
+      E[M_SCM] = cond ? 1.0f : 0.0f;
       grasp_duration = (float)sds * dt;
-      emit(DEX_K_GRASP_DURATION, 0, grasp_duration);
+      E[C_GRASPDUR] = grasp_duration;
       // stage FSM :835-956 (plain fp32 accumulation of (float)control_dt decides the transition step)
-      stage = st.current_stage[env];
-      float tis = st.time_in_stage[env] + dt;
-      float scd = st.stage_contact_duration[env];
+      stage = __float_as_int(E[S_STAGE]);
+      float tis = E[S_TIS] + dt;
+      float scd = E[S_SCD];
       const bool thumb_other = cbin[0] && (cbin[1] || cbin[2] || cbin[3] || cbin[4]);
       if (stage == 2) scd = thumb_other ? scd + dt : 0.0f;
       const bool s1_done = (stage == 1) && (tis >= P.stage1_duration);
@@ -537,41 +638,40 @@ __device__ __forceinline__ void post_scalar(const PostArgs& A, const Slab& L, fl
         tis = 0.0f;
         scd = 0.0f;
       }
-      st.current_stage[env] = stage;
-      st.time_in_stage[env] = tis;
-      st.stage_contact_duration[env] = scd;
-      st.just_transitioned_to_stage2[env] = j2 ? 1 : 0;
-      st.just_transitioned_to_stage3[env] = j3 ? 1 : 0;
+      E[S_STAGE] = __int_as_float(stage);
+      E[S_TIS] = tis;
+      E[S_SCD] = scd;
+      E[M_J2] = j2 ? 1.0f : 0.0f;
+      E[M_J3] = j3 ? 1.0f : 0.0f;
       float prog = 0.0f;  // :958-978
       if (stage == 1) prog = clampf(tis / P.stage1_duration, 0.0f, 1.0f);
       if (stage == 2) prog = clampf(tis / P.stage2_duration, 0.0f, 1.0f);
       if (stage == 3) prog = 1.0f;
-      emit(DEX_K_CURRENT_STAGE, 0, (float)stage);
-      emit(DEX_K_TIME_IN_STAGE, 0, tis);
-      emit(DEX_K_STAGE_PROGRESS, 0, prog);
-      min_tip_box = scr[SC_TIPBOX];
+      E[C_STAGEF] = (float)stage;
+      E[C_PROG] = prog;
+      min_tip_box = E[C_TIPBOX];
 #pragma unroll
-      for (int f = 1; f < DEX_NUM_FINGERS; ++f) min_tip_box = fminf(min_tip_box, scr[SC_TIPBOX + f]);
+      for (int f = 1; f < DEX_NUM_FINGERS; ++f) min_tip_box = fminf(min_tip_box, E[C_TIPBOX + f]);
     }
 
     if (full) {
       // step_processor.py:80
-      const int64_t step_now = step_before + 1;
-      st.episode_step_count[env] = step_now;
-      ep_len_done = (int)step_now;
+      const int step_now = step_before + 1;
+      E[S_STEP] = __int_as_float(step_now);
+      ep_len_done = step_now;
 
       // ---------------- termination (step_processor.py:133-181, termination_manager.py:120-278) ----
       if (P.has_height_safety)
         crit[DEX_C_HITTING_GROUND] = (rb[2] < P.handbase_threshold) || (min_tip_z < P.fingertip_threshold);
       bool pregrasp_failed = false, contact_failed = false, grasp_lost = false;
       if (BG) {
-        crit[DEX_C_GRASP_LIFT_SUCCESS] = sds >= (int64_t)P.contact_duration_threshold_steps;
-        crit[DEX_C_BOX_TOO_FAR] = scr[SC_HANDBOX] > P.max_box_distance;
+        crit[DEX_C_GRASP_LIFT_SUCCESS] = sds >= P.contact_duration_threshold_steps;
+        crit[DEX_C_BOX_TOO_FAR] = E[C_HANDBOX] > P.max_box_distance;
         if (j2) {  // _evaluate_pregrasp_quality :1334-1364
-          const bool h_ok = (scr[SC_HDIFF + 0] <= P.height_tolerance) && (scr[SC_HDIFF + 1] <= P.height_tolerance) &&
-                            (scr[SC_HDIFF + 2] <= P.height_tolerance);
-          const bool c_ok = scr[SC_CDIST] <= P.centroid_tolerance;
-          const bool s_ok = (scr[SC_DRIFT] <= P.position_drift_tolerance) && (scr[SC_VMAG] <= P.velocity_tolerance);
+          const bool h_ok = (E[C_HDIFF + 0] <= P.height_tolerance) && (E[C_HDIFF + 1] <= P.height_tolerance) &&
+                            (E[C_HDIFF + 2] <= P.height_tolerance);
+          const bool c_ok = E[C_CDIST] <= P.centroid_tolerance;
+          const bool s_ok = (E[C_DRIFT] <= P.position_drift_tolerance) && (E[C_VMAG] <= P.velocity_tolerance);
           pregrasp_failed = !(h_ok && c_ok && s_ok);
         }
         if (j3) contact_failed = !grasp;
@@ -579,9 +679,9 @@ __device__ __forceinline__ void post_scalar(const PostArgs& A, const Slab& L, fl
         crit[DEX_C_STAGE1_PREGRASP_FAILED] = pregrasp_failed;
         crit[DEX_C_STAGE2_CONTACT_FAILED] = contact_failed;
         crit[DEX_C_STAGE3_GRASP_LOST] = grasp_lost;
-        st.failure_tensors[0 * N + env] = pregrasp_failed ? 1 : 0;
-        st.failure_tensors[1 * N + env] = contact_failed ? 1 : 0;
-        st.failure_tensors[2 * N + env] = grasp_lost ? 1 : 0;
+        E[M_FT0] = pregrasp_failed ? 1.0f : 0.0f;
+        E[M_FT1] = contact_failed ? 1.0f : 0.0f;
+        E[M_FT2] = grasp_lost ? 1.0f : 0.0f;
       }
       bool ep_s = false, ep_f = false;
 #pragma unroll
@@ -592,7 +692,7 @@ __device__ __forceinline__ void post_scalar(const PostArgs& A, const Slab& L, fl
         else
           ep_f = ep_f || crit[c];
       }
-      const bool timeout = step_now >= (int64_t)(P.max_episode_length - 1);
+      const bool timeout = step_now >= (P.max_episode_length - 1);
       should_reset = ep_s || ep_f || timeout;
       t_success = ep_s;
       t_failure = ep_f && !ep_s;
@@ -603,33 +703,34 @@ __device__ __forceinline__ void post_scalar(const PostArgs& A, const Slab& L, fl
 #pragma unroll
       for (int i = 0; i < DEX_NUM_REWARD_TERMS; ++i) r[i] = 0.0f;
       if (P.need_common_rewards) {
+        const float* cp = E + A.o_cpv;
         r[DEX_R_ALIVE] = 1.0f;
         r[DEX_R_HEIGHT_SAFETY] = clampf(1.0f - expf(-(min_tip_z - 0.02f) * 20.0f), 0.0f, 1.0f);
         float fv2 = 0.0f, fa2 = 0.0f, jl = 0.0f;
 #pragma unroll
         for (int j = 0; j < DEX_NUM_FINGER_DOF; ++j) {
-          fv2 += scr[SC_FV2 + j];
-          fa2 += scr[SC_FA2 + j];
-          jl += scr[SC_JL + j];
+          fv2 += cp[CP_FV2 + j];
+          fa2 += cp[CP_FA2 + j];
+          jl += cp[CP_JL + j];
         }
         r[DEX_R_FINGER_VELOCITY] = expf(-0.1f * sqrtf(fv2));
         r[DEX_R_JOINT_LIMIT] = 1.0f - jl / 20.0f;
         r[DEX_R_FINGER_ACCELERATION] = expf(-2.0f * sqrtf(fa2));
-        r[DEX_R_HAND_VELOCITY] = scr[SC_RHAND + 0];
-        r[DEX_R_HAND_ANGULAR_VELOCITY] = scr[SC_RHAND + 1];
-        r[DEX_R_HAND_ACCELERATION] = scr[SC_RHAND + 2];
-        r[DEX_R_HAND_ANGULAR_ACCELERATION] = scr[SC_RHAND + 3];
+        r[DEX_R_HAND_VELOCITY] = cp[CP_RHAND + 0];
+        r[DEX_R_HAND_ANGULAR_VELOCITY] = cp[CP_RHAND + 1];
+        r[DEX_R_HAND_ACCELERATION] = cp[CP_RHAND + 2];
+        r[DEX_R_HAND_ANGULAR_ACCELERATION] = cp[CP_RHAND + 3];
         float changes = 0.0f;
 #pragma unroll
-        for (int f = 0; f < DEX_NUM_FINGERS; ++f) changes += scr[SC_CHG + f];
+        for (int f = 0; f < DEX_NUM_FINGERS; ++f) changes += cp[CP_CHG + f];
         r[DEX_R_CONTACT_STABILITY] = expf(-changes);
       }
       if (BG) {
         const float m1 = (stage == 1) ? 1.0f : 0.0f, m2 = (stage == 2) ? 1.0f : 0.0f, m3 = (stage == 3) ? 1.0f : 0.0f;
         // stage 1 :1055-1112
         r[DEX_R_S1_HEIGHT_ALIGNMENT] = expf(-P.height_alignment_decay * avg_hdiff) * m1;
-        r[DEX_R_S1_CENTROID_POSITIONING] = expf(-P.centroid_positioning_decay * scr[SC_CDIST]) * m1;
-        r[DEX_R_S1_OBJECT_STABILITY] = expf(-P.object_stability_decay * (scr[SC_DRIFT] + scr[SC_VMAG])) * m1;
+        r[DEX_R_S1_CENTROID_POSITIONING] = expf(-P.centroid_positioning_decay * E[C_CDIST]) * m1;
+        r[DEX_R_S1_OBJECT_STABILITY] = expf(-P.object_stability_decay * (E[C_DRIFT] + E[C_VMAG])) * m1;
         {  // torch.var(dim=1), unbiased, over the z of the first three pads
           const float z0 = rb[13 + 35 + 2], z1 = rb[13 + 35 + 7 + 2], z2 = rb[13 + 35 + 14 + 2];
           const float mean = (z0 + z1 + z2) / 3.0f;
@@ -637,7 +738,7 @@ __device__ __forceinline__ void post_scalar(const PostArgs& A, const Slab& L, fl
           const float var = (d0 * d0 + d1 * d1 + d2 * d2) / 2.0f;
           r[DEX_R_S1_FINGER_HEIGHT_CONSISTENCY] = expf(-P.height_consistency_decay * var) * m1;
         }
-        r[DEX_R_S1_THUMB_ROTATION] = expf(-5.0f * fabsf(E[L.dof + 2 * DEX_NUM_BASE] - P.half_pi)) * m1;
+        r[DEX_R_S1_THUMB_ROTATION] = expf(-5.0f * fabsf(E[I_DOF + 2 * DEX_NUM_BASE] - P.half_pi)) * m1;
         // stage 2 :1114-1150
         r[DEX_R_S2_THUMB_CONTACT] = (thumb_c ? 1.0f : 0.0f) * m2;
         r[DEX_R_S2_OTHER_FINGERS_CONTACT] = (others_c ? 1.0f : 0.0f) * m2;
@@ -646,7 +747,7 @@ __device__ __forceinline__ void post_scalar(const PostArgs& A, const Slab& L, fl
         {
           float bv2 = 0.0f;
 #pragma unroll
-          for (int d = 0; d < DEX_NUM_BASE; ++d) bv2 += E[L.vel + d] * E[L.vel + d];  // finite-difference base velocity
+          for (int d = 0; d < DEX_NUM_BASE; ++d) bv2 += E[S_PDP + d] * E[S_PDP + d];  // finite-difference base velocity
           r[DEX_R_S2_BASE_STABILITY] = expf(-P.base_stability_decay * sqrtf(bv2)) * m2;
         }
         // stage 3 :1152-1176
@@ -659,7 +760,7 @@ __device__ __forceinline__ void post_scalar(const PostArgs& A, const Slab& L, fl
         r[DEX_R_PENETRATION_PENALTY] = fmaxf(P.penetration_threshold - min_tip_box, 0.0f) * P.penetration_depth_scale;
       }
       // weighted sum in dict order (reward_calculator.py:223-275)
-      float* comp = A.out.reward_components;
+      float* comp = E + C_COMP;
       float total = 0.0f;
 #pragma unroll
       for (int i = 0; i < DEX_NUM_REWARD_TERMS; ++i) {
@@ -668,11 +769,11 @@ __device__ __forceinline__ void post_scalar(const PostArgs& A, const Slab& L, fl
         if (w != 0.0f) {
           const float weighted = r[i] * w;
           total += weighted;
-          comp[(size_t)P.component_row[i] * N + env] = r[i];
-          comp[(size_t)(P.component_row[i] + 1) * N + env] = weighted;
+          comp[P.component_row[i]] = r[i];
+          comp[P.component_row[i] + 1] = weighted;
         }
       }
-      comp[(size_t)P.total_row * N + env] = total;
+      comp[P.total_row] = total;
       // termination rewards (termination_manager.py:280-321, step_processor.py:204-219)
       const float rs = t_success ? P.success_reward : 0.0f;
       const float rf = t_failure ? P.failure_reward : 0.0f;
@@ -682,19 +783,19 @@ __device__ __forceinline__ void post_scalar(const PostArgs& A, const Slab& L, fl
       rew += rf;
       rew += rt;
       {
-        const size_t tr = (size_t)P.termination_row;
-        comp[(tr + 0) * N + env] = t_success ? 1.0f : 0.0f;
-        comp[(tr + 1) * N + env] = rs;
-        comp[(tr + 2) * N + env] = t_failure ? 1.0f : 0.0f;
-        comp[(tr + 3) * N + env] = rf;
-        comp[(tr + 4) * N + env] = t_timeout ? 1.0f : 0.0f;
-        comp[(tr + 5) * N + env] = rt;
+        float* tr = comp + P.termination_row;
+        tr[0] = t_success ? 1.0f : 0.0f;
+        tr[1] = rs;
+        tr[2] = t_failure ? 1.0f : 0.0f;
+        tr[3] = rf;
+        tr[4] = t_timeout ? 1.0f : 0.0f;
+        tr[5] = rt;
       }
-      A.out.rew_buf[env] = rew;
-      A.out.reset_buf[env] = should_reset ? 1 : 0;
-      A.out.success[env] = t_success ? 1 : 0;
-      A.out.failure[env] = t_failure ? 1 : 0;
-      A.out.timeout[env] = t_timeout ? 1 : 0;
+      E[C_REW] = rew;
+      E[M_RESET] = should_reset ? 1.0f : 0.0f;
+      E[M_SUCC] = t_success ? 1.0f : 0.0f;
+      E[M_FAIL] = t_failure ? 1.0f : 0.0f;
+      E[M_TIMEOUT] = t_timeout ? 1.0f : 0.0f;
 
       // ---------------- fused RewardComponentObserver (rl/reward_observer.py:160-293) -----------
       if (A.out.episode_sums != nullptr) {
@@ -710,7 +811,7 @@ __device__ __forceinline__ void post_scalar(const PostArgs& A, const Slab& L, fl
           atomicAdd(tot + cls * stride + 1, (double)len);
         }
         for (int c = 0; c < rows; ++c) {
-          const float s = A.out.episode_sums[(size_t)c * N + env] + comp[(size_t)c * N + env];
+          const float s = A.out.episode_sums[(size_t)c * N + env] + comp[c];
           if (should_reset) {
             atomicAdd(tot + 2 + c, (double)s);
             atomicAdd(tot + cls * stride + 2 + c, (double)s);
@@ -718,12 +819,6 @@ __device__ __forceinline__ void post_scalar(const PostArgs& A, const Slab& L, fl
           A.out.episode_sums[(size_t)c * N + env] = should_reset ? 0.0f : s;
         }
         A.out.episode_lengths[env] = should_reset ? 0 : len;
-      }
-
-      // ---------------- fused reset (dexhand_base.py:743-756) -----------------------------------
-      if (should_reset && !(A.flags & DEX_FLAG_NO_FUSED_RESET)) {
-        const ResetCtx rc{A.uniforms, A.seed, st.rng_step ? *st.rng_step : A.step};
-        reset_env<BG>(P, A.sim, st, rc, (int)env, N);
       }
     }
   }
@@ -753,6 +848,49 @@ __device__ __forceinline__ void post_scalar(const PostArgs& A, const Slab& L, fl
       for (int o = 16; o > 0; o >>= 1) len += __shfl_xor_sync(fullmask, len, o);
       if (lane == 0) atomicAdd(A.out.counters + DEX_CNT_EPISODE_LENGTH, len);
     }
+  }
+  return should_reset;
+}
+
+// ------------------------------------------------------------------------------------------------
+// phase 3: stage-out
+// ------------------------------------------------------------------------------------------------
+// rows of a [N, W] row-major buffer gathered from the slab through a column map (shared copy of the map)
+template <int MAXJ>
+__device__ __forceinline__ void gather_rows_out(float* __restrict__ dst, const int W, const short* s_map,
+                                                const float* smem, const int S, const int e0, const int ne) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int m[MAXJ];
+#pragma unroll
+  for (int j = 0; j < MAXJ; ++j) {
+    const int k = lane + 32 * j;
+    m[j] = (k < W) ? (int)s_map[k] : -1;
+  }
+  for (int e = warp; e < ne; e += kPostWarps) {
+    const float* src = smem + e * S;
+    float* d = dst + ((size_t)e0 + e) * W + lane;
+#pragma unroll
+    for (int j = 0; j < MAXJ; ++j)
+      if (m[j] >= 0) d[32 * j] = src[m[j]];
+  }
+}
+
+__device__ __forceinline__ void post_rows_out(const PostArgs& A, const float* smem, const int e0, const int ne) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane >= ne) return;
+  const float* E = smem + lane * A.stride;
+  const size_t col = (size_t)e0 + lane;
+  for (int r = warp; r < A.n_out; r += kPostWarps) {
+    const unsigned meta = A.out_meta[r];
+    const unsigned slot = meta & 0xfffu, type = meta >> 12;
+    char* base = reinterpret_cast<char*>(A.out_ptr[r]);
+    const float v = E[slot];
+    if (type == ROW_F32)
+      reinterpret_cast<float*>(base)[col] = v;
+    else if (type == ROW_U8)
+      reinterpret_cast<unsigned char*>(base)[col] = (v != 0.0f) ? 1 : 0;
+    else
+      reinterpret_cast<long long*>(base)[col] = (long long)__float_as_int(v);
   }
 }
 
@@ -831,38 +969,37 @@ __device__ void epilogue_body(const DexEpilogueBuffers& ep, const int n, const i
 // the kernel
 // ------------------------------------------------------------------------------------------------
 template <bool BG, bool DICT>
-__global__ void __launch_bounds__(kPostThreads) post_physics_kernel(const __grid_constant__ PostArgs A) {
+__global__ void __launch_bounds__(kPostThreads, DICT ? 1 : 4) post_physics_kernel(const __grid_constant__ PostArgs A) {
   extern __shared__ __align__(16) float smem[];
-  __shared__ int s_dof2fin[DEX_NUM_DOF];
+  __shared__ short s_obs_map[kMaxObs];
+  __shared__ short s_dict_map[DICT ? kMaxDict : 1];
   __shared__ int s_epi_warp[kPostWarps];
   __shared__ int s_epi_base;
   __shared__ int s_last;
-  const DexParams& P = A.p;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tid = threadIdx.x, warp = tid >> 5;
   const int e0 = blockIdx.x * kTile;
   const int ne = min(kTile, A.n - e0);
-  const Slab L = make_slab(P, DICT);
-  const bool want_tgt = post_want_targets(P, DICT);
 
-  if (tid < DEX_NUM_DOF) {  // DOF -> column inside active_finger_dof_* (observation_encoder.py:496-574), -1 = none
-    int j = -1;
-#pragma unroll
-    for (int k = 0; k < DEX_NUM_ACTIVE_FINGER; ++k)
-      if (P.active_finger_dof[k] == tid) j = k;
-    s_dof2fin[tid] = j;
+  s_obs_map[tid] = A.obs_src[tid];  // kMaxObs == kPostThreads
+  if (DICT) {
+    s_dict_map[tid] = A.dict_src[tid];
+    s_dict_map[tid + kPostThreads] = A.dict_src[tid + kPostThreads];
   }
-  post_stage_in<BG>(A, L, smem, e0, ne, want_tgt);
+  post_stage_in<BG>(A, smem, e0, ne);
   __syncthreads();
-  post_items<BG, DICT>(A, L, smem, s_dof2fin, e0, ne, want_tgt);
+  post_items<BG>(A, smem, ne);
   __syncthreads();
-  if (warp == 0) post_scalar<BG, DICT>(A, L, smem, e0, ne);
-  __syncthreads();
-  {  // stage-out: obs rows, consecutive lanes = consecutive columns
-    const int W = P.obs_dim;
-    for (int e = warp; e < ne; e += kPostWarps) {
-      const float* src = smem + e * L.stride + L.obs;
-      float* dst = A.out.obs_buf + ((size_t)e0 + e) * W;
-      for (int k = lane; k < W; k += 32) dst[k] = src[k];
+  bool sr = false;
+  if (warp == 0) sr = post_scalar<BG>(A, smem, e0, ne);
+  const int any_reset = __syncthreads_or(sr ? 1 : 0);
+  gather_rows_out<kMaxObs / 32>(A.out.obs_buf, A.p.obs_dim, s_obs_map, smem, A.stride, e0, ne);
+  if (DICT) gather_rows_out<kMaxDict / 32>(A.out.obs_dict, A.dict_dim, s_dict_map, smem, A.stride, e0, ne);
+  post_rows_out(A, smem, e0, ne);
+  if (any_reset && !(A.flags & DEX_FLAG_NO_FUSED_RESET)) {  // fused reset (dexhand_base.py:743-756), CTA-uniform branch
+    __syncthreads();
+    if (sr) {
+      const ResetCtx rc{A.uniforms, A.seed, A.st.rng_step ? *A.st.rng_step : A.step};
+      reset_env<BG>(A.p, A.sim, A.st, rc, e0 + (tid & 31), (size_t)A.n);
     }
   }
   if (A.fused_epilogue) {
@@ -875,7 +1012,7 @@ __global__ void __launch_bounds__(kPostThreads) post_physics_kernel(const __grid
     __syncthreads();
     if (s_last) {
       __threadfence();
-      epilogue_body<kPostThreads>(A.ep, A.n, P.max_consecutive_successes, s_epi_warp, &s_epi_base);
+      epilogue_body<kPostThreads>(A.ep, A.n, A.p.max_consecutive_successes, s_epi_warp, &s_epi_base);
       if (tid == 0) *A.ep.ticket = 0u;
     }
   }
@@ -889,12 +1026,12 @@ __global__ void __launch_bounds__(1024) epilogue_kernel(const DexEpilogueBuffers
 
 template <bool BG, bool DICT>
 int launch_post_t(const PostArgs& a, cudaStream_t s) {
-  const size_t smem = post_smem_bytes(a.p, DICT);
-  if (smem > 220 * 1024) return DEX_ERR_SIZE;
+  const size_t smem = (size_t)a.stride * kTile * sizeof(float);
+  if (smem > 200 * 1024) return DEX_ERR_SIZE;
   static bool configured = false;  // per template instance
   if (!configured) {
     const cudaError_t e = cudaFuncSetAttribute(post_physics_kernel<BG, DICT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                               220 * 1024);
+                                               200 * 1024);
     if (e != cudaSuccess) return (int)e;
     configured = true;
   }
@@ -904,7 +1041,9 @@ int launch_post_t(const PostArgs& a, cudaStream_t s) {
   return e == cudaSuccess ? DEX_OK : (int)e;
 }
 
-inline int launch_post(const PostArgs& a, cudaStream_t s) {
+inline int launch_post(PostArgs& a, cudaStream_t s) {
+  const int rc = build_post_tables(a);
+  if (rc) return rc;
   const bool bg = a.p.task == DEX_TASK_BLIND_GRASPING, dict = a.out.obs_dict != nullptr;
   if (bg) return dict ? launch_post_t<true, true>(a, s) : launch_post_t<true, false>(a, s);
   return dict ? launch_post_t<false, true>(a, s) : launch_post_t<false, false>(a, s);
