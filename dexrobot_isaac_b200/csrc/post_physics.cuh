@@ -108,9 +108,12 @@ struct PostArgs {
   int32_t stride;                       // slab stride (odd)
   int32_t o_tgt, o_hf, o_cpv;           // optional sections (-1 = absent)
   int32_t want_hf_tip, want_hf_pad, want_arr, common, dict_dim;
-  int32_t n_in, n_out;
+  int32_t n_in_f32, n_in_i64, n_in;     // IN table, sorted by type: [0,n_in_f32) f32 | [..,n_in_i64) i64 | [..,n_in) u8
+  int32_t n_out_f32, n_out_i64, n_out;  // OUT table, same order
+  int32_t rb_off[11];                   // float offset of the hand / 5 tip / 5 pad rows inside one env's [NB,13] slab
+  int32_t cf_off[6];                    // float offset of the 5 monitored contact rows (+ box) inside [NB,3]
   uint64_t in_ptr[kMaxIn];              // row base pointers
-  uint16_t in_meta[kMaxIn];             // slot | type << 12
+  uint16_t in_meta[kMaxIn];             // slab slot
   uint64_t out_ptr[kMaxOut];
   uint16_t out_meta[kMaxOut];
   int16_t obs_src[kMaxObs];             // obs column -> slab slot
@@ -211,15 +214,24 @@ inline int build_post_tables(PostArgs& a) {
   a.stride = o | 1;
   if (a.stride >= 4096) return DEX_ERR_SIZE;
 
-  // ---- IN table ----
-  int ni = 0;
+  a.rb_off[0] = P.hand_body * 13;
+  for (int f = 0; f < DEX_NUM_FINGERS; ++f) {
+    a.rb_off[1 + f] = P.tip_body[f] * 13;
+    a.rb_off[6 + f] = P.pad_body[f] * 13;
+    a.cf_off[f] = P.contact_body[f] * 3;
+  }
+  a.cf_off[5] = bg ? P.box_body * 3 : 0;
+
+  // ---- IN table (filled per type, then concatenated f32 | i64 | u8) ----
+  struct Row { uint64_t ptr; uint16_t slot; };
+  Row rows[3][kMaxOut];
+  int cnt[3] = {0, 0, 0};
   bool ok = true;
-  auto in = [&](const void* base, size_t row, int elem, int slot, int type) {
-    if (ni >= kMaxIn) { ok = false; return; }
-    a.in_ptr[ni] = (uint64_t)(uintptr_t)((const char*)base + row * N * elem);
-    a.in_meta[ni] = (uint16_t)(slot | (type << 12));
-    ++ni;
+  auto add = [&](const void* base, size_t row, int elem, int slot, int type) {
+    if (cnt[type] >= kMaxOut) { ok = false; return; }
+    rows[type][cnt[type]++] = Row{(uint64_t)(uintptr_t)((const char*)base + row * N * elem), (uint16_t)slot};
   };
+  auto in = add;
   for (int d = 0; d < DEX_NUM_DOF; ++d) in(st.prev_dof_pos, d, 4, S_PDP + d, ROW_F32);
   for (int k = 0; k < DEX_NUM_ACTIVE; ++k) in(st.active_prev_targets, k, 4, S_APT + k, ROW_F32);
   for (int k = 0; k < P.num_actions; ++k) in(st.prev_actions, k, 4, S_PACT + k, ROW_F32);
@@ -241,16 +253,24 @@ inline int build_post_tables(PostArgs& a) {
   }
   if (stale)
     for (int i = 0; i < 15; ++i) in(st.contact_forces, i, 4, I_CF + i, ROW_F32);
-  a.n_in = ni;
+  {
+    int k = 0;
+    const int order[3] = {ROW_F32, ROW_I64, ROW_U8};
+    if (cnt[0] + cnt[1] + cnt[2] > kMaxIn) return DEX_ERR_SIZE;
+    for (int t = 0; t < 3; ++t) {
+      for (int i = 0; i < cnt[order[t]]; ++i, ++k) {
+        a.in_ptr[k] = rows[order[t]][i].ptr;
+        a.in_meta[k] = rows[order[t]][i].slot;
+      }
+      if (t == 0) a.n_in_f32 = k;
+      if (t == 1) a.n_in_i64 = k;
+    }
+    a.n_in = k;
+    cnt[0] = cnt[1] = cnt[2] = 0;
+  }
 
   // ---- OUT table ----
-  int no = 0;
-  auto out = [&](void* base, size_t row, int elem, int slot, int type) {
-    if (no >= kMaxOut) { ok = false; return; }
-    a.out_ptr[no] = (uint64_t)(uintptr_t)((char*)base + row * N * elem);
-    a.out_meta[no] = (uint16_t)(slot | (type << 12));
-    ++no;
-  };
+  auto out = add;
   for (int d = 0; d < DEX_NUM_DOF; ++d) out(st.prev_dof_pos, d, 4, I_DOF + 2 * d, ROW_F32);  // prev_dof_pos <- pos
   for (int k = 0; k < DEX_NUM_ACTIVE; ++k) out(st.active_rule_targets, k, 4, S_APT + k, ROW_F32);  // rules.py:78-95
   for (int f = 0; f < DEX_NUM_FINGERS; ++f) out(st.contact_duration_steps, f, 4, S_CDUR + f, ROW_F32);
@@ -284,7 +304,20 @@ inline int build_post_tables(PostArgs& a) {
       for (int f = 0; f < DEX_NUM_FINGERS; ++f) out(st.prev_contacts, f, 1, a.o_cpv + CP_CNOW + f, ROW_U8);
     }
   }
-  a.n_out = no;
+  {
+    int k = 0;
+    const int order[3] = {ROW_F32, ROW_I64, ROW_U8};
+    if (cnt[0] + cnt[1] + cnt[2] > kMaxOut) return DEX_ERR_SIZE;
+    for (int t = 0; t < 3; ++t) {
+      for (int i = 0; i < cnt[order[t]]; ++i, ++k) {
+        a.out_ptr[k] = rows[order[t]][i].ptr;
+        a.out_meta[k] = rows[order[t]][i].slot;
+      }
+      if (t == 0) a.n_out_f32 = k;
+      if (t == 1) a.n_out_i64 = k;
+    }
+    a.n_out = k;
+  }
 
   // ---- observation column maps ----
   if (P.obs_dim > kMaxObs) return DEX_ERR_SIZE;
@@ -312,105 +345,102 @@ inline int build_post_tables(PostArgs& a) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// device helpers
-// ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void cp_async4(const unsigned smem_dst, const void* gsrc) {
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(smem_dst), "l"(gsrc) : "memory");
-}
-__device__ __forceinline__ void cp_async_wait_all() {
-  asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;\n" ::: "memory");
-}
-
-// rigid-body slot (0..82) -> float offset inside one env's [NB,13] slab
-__device__ __forceinline__ int rb_slot_offset(const DexParams& P, const int s) {
-  if (s < 13) return P.hand_body * 13 + s;
-  const int t = s - 13, f = t / 7, c = t - f * 7;
-  int body = 0;
-#pragma unroll
-  for (int k = 0; k < DEX_NUM_FINGERS; ++k) {
-    if (f == k) body = P.tip_body[k];
-    if (f == k + DEX_NUM_FINGERS) body = P.pad_body[k];
-  }
-  return body * 13 + c;
-}
-
-// ------------------------------------------------------------------------------------------------
-// phase 0: stage-in
+// phase 0: stage-in.  Plain LDG -> STS batches (all loads of a batch issued before the first store), no
+// cp.async: on sm_100a every 4-byte LDGSTS costs four issue slots, and this kernel is issue-bound.
 // ------------------------------------------------------------------------------------------------
 template <bool BG>
 __device__ __forceinline__ void post_stage_in(const PostArgs& A, float* smem, const int e0, const int ne) {
   const DexParams& P = A.p;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int S = A.stride;
-  const unsigned sbase = (unsigned)__cvta_generic_to_shared(smem);
 
-  // ---- AoS sim rows: warps take env rows round-robin, consecutive lanes = consecutive floats ----
+  // ---- AoS sim rows: warps take env rows round-robin (4 each), consecutive lanes = consecutive floats ----
   {
     const int nb = P.num_bodies;
-    const int rbo0 = rb_slot_offset(P, lane), rbo1 = rb_slot_offset(P, lane + 32);
-    const int rbo2 = rb_slot_offset(P, min(lane + 64, kRbW - 1));
-    int cfo = 0;
-    {
-      const int f = lane / 3, c = lane - f * 3;
-      int body = 0;
-#pragma unroll
-      for (int k = 0; k < DEX_NUM_FINGERS; ++k)
-        if (f == k) body = P.contact_body[k];
-      if (BG && f == DEX_NUM_FINGERS) body = P.box_body;
-      cfo = body * 3 + c;
-    }
+    auto rbo = [&](int s) {  // rigid slot (0..82) -> float offset inside the env's [NB,13] slab
+      s = min(s, kRbW - 1);
+      const int row = s < 13 ? 0 : 1 + (s - 13) / 7;
+      return A.rb_off[row] + (s < 13 ? s : (s - 13) - (row - 1) * 7);
+    };
+    const int rbo0 = rbo(lane), rbo1 = rbo(lane + 32), rbo2 = rbo(lane + 64);
     const bool stale = (A.flags & DEX_FLAG_STALE_CONTACTS) != 0;
     const bool p_rb0 = lane < 7 || lane >= 13 || A.common;  // hand velocities only feed the common reward terms
     const bool p_rb2 = lane + 64 < kRbW;
     const bool p_dof1 = lane + 32 < 2 * DEX_NUM_DOF;
-    const bool p_cf = lane < (BG ? 18 : 15) && (lane >= 15 || !stale);
-    const bool p_box = BG && lane < 6;
     const bool p_tgt = A.o_tgt >= 0 && lane < DEX_NUM_DOF;
-    const int boxo = BG ? P.box_actor * 13 + (lane < 3 ? lane : lane + 4) : 0;
-    const float* g_dof = A.sim.dof_state + (size_t)e0 * (2 * DEX_NUM_DOF) + lane;
-    const float* g_rb = A.sim.rigid_body_state + (size_t)e0 * nb * 13;
-    const float* g_cf = A.sim.net_contact_force + (size_t)e0 * nb * 3 + cfo;
-    const float* g_box = BG ? A.sim.actor_root_state + (size_t)e0 * P.num_actors * 13 + boxo : nullptr;
-    const float* g_tgt = A.st.full_dof_targets + (size_t)e0 * DEX_NUM_DOF + lane;
-    const int rb_row = nb * 13, cf_row = nb * 3, box_row = P.num_actors * 13;
-#pragma unroll 4
-    for (int e = warp; e < ne; e += kPostWarps) {
-      const unsigned E = sbase + (unsigned)(e * S + lane) * 4u;
-      cp_async4(E + I_DOF * 4, g_dof + e * (2 * DEX_NUM_DOF));
-      if (p_dof1) cp_async4(E + (I_DOF + 32) * 4, g_dof + e * (2 * DEX_NUM_DOF) + 32);
-      const float* rb = g_rb + (size_t)e * rb_row;
-      if (p_rb0) cp_async4(E + I_RB * 4, rb + rbo0);
-      cp_async4(E + (I_RB + 32) * 4, rb + rbo1);
-      if (p_rb2) cp_async4(E + (I_RB + 64) * 4, rb + rbo2);
-      if (p_cf) cp_async4(E + I_CF * 4, g_cf + (size_t)e * cf_row);
-      if (p_box) cp_async4(E + I_BOX * 4, g_box + (size_t)e * box_row);
-      if (p_tgt) cp_async4(E + (unsigned)A.o_tgt * 4u, g_tgt + e * DEX_NUM_DOF);
+    // lanes 0..17: contact rows (5 monitored + box), lanes 18..23: box root state (pos, linvel); slots I_CF + lane
+    const bool is_box = BG && lane >= 18 && lane < 24;
+    const bool p_x = is_box || (lane < (BG ? 18 : 15) && (lane >= 15 || !stale));
+    const int xrow = is_box ? P.num_actors * 13 : nb * 3;
+    int xoff;
+    if (is_box) {
+      const int k = lane - 18;
+      xoff = P.box_actor * 13 + (k < 3 ? k : k + 4);
+    } else {
+      const int f = min(lane / 3, 5);
+      xoff = A.cf_off[f] + (lane - 3 * f);
+    }
+    const float* gx = (is_box ? A.sim.actor_root_state : A.sim.net_contact_force) + (size_t)(e0 + warp) * xrow + xoff;
+    const float* g_dof = A.sim.dof_state + (size_t)(e0 + warp) * (2 * DEX_NUM_DOF) + lane;
+    const float* g_rb = A.sim.rigid_body_state + (size_t)(e0 + warp) * nb * 13;
+    const float* g_tgt = A.st.full_dof_targets + (size_t)(e0 + warp) * DEX_NUM_DOF + lane;
+    const int rb_step = kPostWarps * nb * 13, x_step = kPostWarps * xrow;
+    constexpr int R = kTile / kPostWarps;  // env rows per warp
+    float v[R][7];
+#pragma unroll
+    for (int i = 0; i < R; ++i) {
+      if (warp + kPostWarps * i < ne) {
+        v[i][0] = __ldg(g_dof + i * (kPostWarps * 2 * DEX_NUM_DOF));
+        if (p_dof1) v[i][1] = __ldg(g_dof + i * (kPostWarps * 2 * DEX_NUM_DOF) + 32);
+        const float* rb = g_rb + (size_t)i * rb_step;
+        if (p_rb0) v[i][2] = __ldg(rb + rbo0);
+        v[i][3] = __ldg(rb + rbo1);
+        if (p_rb2) v[i][4] = __ldg(rb + rbo2);
+        if (p_x) v[i][5] = __ldg(gx + (size_t)i * x_step);
+        if (p_tgt) v[i][6] = __ldg(g_tgt + i * (kPostWarps * DEX_NUM_DOF));
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < R; ++i) {
+      if (warp + kPostWarps * i < ne) {
+        float* E = smem + (warp + kPostWarps * i) * S + lane;
+        E[I_DOF] = v[i][0];
+        if (p_dof1) E[I_DOF + 32] = v[i][1];
+        if (p_rb0) E[I_RB] = v[i][2];
+        E[I_RB + 32] = v[i][3];
+        if (p_rb2) E[I_RB + 64] = v[i][4];
+        if (p_x) E[I_CF] = v[i][5];
+        if (p_tgt) E[A.o_tgt] = v[i][6];
+      }
     }
   }
 
   // ---- SoA state rows through the IN table: lane = env, one 128 B line per request ----
   if (lane < ne) {
-    const unsigned E = sbase + (unsigned)(lane * S) * 4u;
-    const size_t col = (size_t)e0 + lane;
     float* Ef = smem + lane * S;
-    bool converted = false;
-    for (int r = warp; r < A.n_in; r += kPostWarps) {
-      const unsigned meta = A.in_meta[r];
-      const unsigned slot = meta & 0xfffu, type = meta >> 12;
-      const char* base = reinterpret_cast<const char*>(A.in_ptr[r]);
-      if (type == ROW_F32) {
-        cp_async4(E + slot * 4u, base + col * 4);
-      } else if (type == ROW_I64) {  // int64 state is small: keep the low word (counts, stage)
-        Ef[slot] = __int_as_float((int)__ldg(reinterpret_cast<const long long*>(base) + col));
-        converted = true;
-      } else {
-        Ef[slot] = __ldg(reinterpret_cast<const unsigned char*>(base) + col) ? 1.0f : 0.0f;
-        converted = true;
+    const size_t col = (size_t)e0 + lane;
+    const size_t colb = col * 4;
+    constexpr int U = 4;
+    for (int r0 = warp; r0 < A.n_in_f32; r0 += kPostWarps * U) {
+      float v[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int r = r0 + kPostWarps * u;
+        if (r < A.n_in_f32) v[u] = __ldg(reinterpret_cast<const float*>(A.in_ptr[r] + colb));
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int r = r0 + kPostWarps * u;
+        if (r < A.n_in_f32) Ef[A.in_meta[r]] = v[u];
       }
     }
-    (void)converted;
+    for (int r = A.n_in_f32 + warp; r < A.n_in; r += kPostWarps) {
+      if (r < A.n_in_i64)  // int64 state is small (counts, stage): keep the low word
+        Ef[A.in_meta[r]] = __int_as_float((int)__ldg(reinterpret_cast<const long long*>(A.in_ptr[r]) + col));
+      else
+        Ef[A.in_meta[r]] = __ldg(reinterpret_cast<const unsigned char*>(A.in_ptr[r]) + col) ? 1.0f : 0.0f;
+    }
   }
-  cp_async_wait_all();
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -539,7 +569,8 @@ __device__ __forceinline__ void post_items(const PostArgs& A, float* smem, const
       // ---- DOF d: finite-difference velocity (observation_encoder.py:298-321), common-reward partial terms ----
       const int d = it - i_dof;
       const float pos = E[I_DOF + 2 * d];
-      E[S_PDP + d] = (pos - E[S_PDP + d]) / dt;
+      const float dp = pos - E[S_PDP + d];
+      E[S_PDP + d] = (dp == 0.0f) ? dp : dp / dt;  // 0/dt == 0 exactly; skips the IEEE-division slow path for joints at rest
       if (common && d >= DEX_NUM_BASE) {  // reward_calculator.py:94-98,138-160: Isaac dof_vel, not the finite difference
         float* cp = E + A.o_cpv;
         const int j = d - DEX_NUM_BASE;
@@ -855,42 +886,138 @@ __device__ __forceinline__ bool post_scalar(const PostArgs& A, float* smem, cons
 // ------------------------------------------------------------------------------------------------
 // phase 3: stage-out
 // ------------------------------------------------------------------------------------------------
-// rows of a [N, W] row-major buffer gathered from the slab through a column map (shared copy of the map)
-template <int MAXJ>
+// rows of a [N, W] row-major buffer gathered from the slab through a column map (shared copy of the map):
+// a warp owns 4 env rows; lane = column (mod 32), so every global store is a full coalesced 128 B request
 __device__ __forceinline__ void gather_rows_out(float* __restrict__ dst, const int W, const short* s_map,
                                                 const float* smem, const int S, const int e0, const int ne) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  int m[MAXJ];
+  constexpr int R = kTile / kPostWarps;
+  float* d0 = dst + ((size_t)e0 + warp) * W;
+  const float* s0 = smem + warp * S;
+  for (int k = lane; k < W; k += 32) {
+    const float* src = s0 + s_map[k];
+    float v[R];
 #pragma unroll
-  for (int j = 0; j < MAXJ; ++j) {
-    const int k = lane + 32 * j;
-    m[j] = (k < W) ? (int)s_map[k] : -1;
-  }
-  for (int e = warp; e < ne; e += kPostWarps) {
-    const float* src = smem + e * S;
-    float* d = dst + ((size_t)e0 + e) * W + lane;
+    for (int i = 0; i < R; ++i)
+      if (warp + kPostWarps * i < ne) v[i] = src[i * kPostWarps * S];
 #pragma unroll
-    for (int j = 0; j < MAXJ; ++j)
-      if (m[j] >= 0) d[32 * j] = src[m[j]];
+    for (int i = 0; i < R; ++i)
+      if (warp + kPostWarps * i < ne) d0[(size_t)(i * kPostWarps * W + k)] = v[i];
   }
 }
 
+// every updated state / output row through the OUT table: lane = env, one 128 B (f32) request per row
 __device__ __forceinline__ void post_rows_out(const PostArgs& A, const float* smem, const int e0, const int ne) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (lane >= ne) return;
   const float* E = smem + lane * A.stride;
   const size_t col = (size_t)e0 + lane;
-  for (int r = warp; r < A.n_out; r += kPostWarps) {
-    const unsigned meta = A.out_meta[r];
-    const unsigned slot = meta & 0xfffu, type = meta >> 12;
-    char* base = reinterpret_cast<char*>(A.out_ptr[r]);
-    const float v = E[slot];
-    if (type == ROW_F32)
-      reinterpret_cast<float*>(base)[col] = v;
-    else if (type == ROW_U8)
-      reinterpret_cast<unsigned char*>(base)[col] = (v != 0.0f) ? 1 : 0;
+  const size_t colb = col * 4;
+  constexpr int U = 4;
+  for (int r0 = warp; r0 < A.n_out_f32; r0 += kPostWarps * U) {
+    float v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int r = r0 + kPostWarps * u;
+      if (r < A.n_out_f32) v[u] = E[A.out_meta[r]];
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int r = r0 + kPostWarps * u;
+      if (r < A.n_out_f32) *reinterpret_cast<float*>(A.out_ptr[r] + colb) = v[u];
+    }
+  }
+  for (int r = A.n_out_f32 + warp; r < A.n_out; r += kPostWarps) {
+    const float v = E[A.out_meta[r]];
+    if (r < A.n_out_i64)
+      reinterpret_cast<long long*>(A.out_ptr[r])[col] = (long long)__float_as_int(v);
     else
-      reinterpret_cast<long long*>(base)[col] = (long long)__float_as_int(v);
+      reinterpret_cast<unsigned char*>(A.out_ptr[r])[col] = (v != 0.0f) ? 1 : 0;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// phase 4: fused reset of ONE finished env by the whole CTA (ResetManager.reset_idx reset_manager.py:92-190,
+// BlindGraspingTask.reset_task_state blind_grasping_task.py:433-547, ActionProcessor.reset_targets
+// action_processor.py:524-568,616-666, ObservationEncoder.reset_observer_state observation_encoder.py:363-383).
+// Same arithmetic as reset_env() (dexstep_common.cuh), one element per thread.  Called CTA-uniformly.
+// ------------------------------------------------------------------------------------------------
+template <bool BG>
+__device__ __forceinline__ void reset_env_coop(const PostArgs& A, const int env, float* s_u, float* s_pos) {
+  const DexParams& P = A.p;
+  const DexStateBuffers& st = A.st;
+  const int tid = threadIdx.x;
+  const size_t N = (size_t)A.n;
+  if (BG) {
+    if (A.uniforms != nullptr) {
+      if (tid < DEX_NUM_UNIFORMS) s_u[tid] = A.uniforms[(size_t)env * DEX_NUM_UNIFORMS + tid];
+    } else if (tid < 8) {
+      const uint64_t step = st.rng_step ? *st.rng_step : A.step;
+      uint32_t r[4];
+      philox4x32_10((uint32_t)env, (uint32_t)tid, (uint32_t)step, (uint32_t)(step >> 32), (uint32_t)A.seed,
+                    (uint32_t)(A.seed >> 32), r);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) s_u[4 * tid + k] = (float)(r[k] >> 8) * (1.0f / 16777216.0f);
+    }
+    __syncthreads();
+  }
+  if (tid < DEX_NUM_DOF) {
+    float p = 0.0f;
+    if (BG) {  // blind_grasping_task.py:511-547 (all 20 finger DOFs, including r_f_joint3_1)
+      if (tid < 3)
+        p = (s_u[3 + tid] * 2.0f - 1.0f) * P.hand_translation_range;
+      else if (tid < 6)
+        p = (s_u[3 + tid] * 2.0f - 1.0f) * P.hand_rotation_range;
+      else if (tid == 6)
+        p = s_u[9] * P.thumb_rotation_range;
+      else
+        p = s_u[3 + tid] * P.other_finger_range;
+    }
+    s_pos[tid] = p;
+    float* dof = A.sim.dof_state + (size_t)env * (DEX_NUM_DOF * 2);
+    dof[2 * tid] = p;
+    dof[2 * tid + 1] = 0.0f;
+    st.full_dof_targets[(size_t)env * DEX_NUM_DOF + tid] = p;  // action_processor.py:553 (verbatim, DOF 14 included)
+    st.prev_dof_pos[tid * N + env] = 0.0f;                     // observation_encoder.py:375-376 (zero, not the new pose)
+  }
+  __syncthreads();
+  if (tid >= 32 && tid < 32 + DEX_NUM_ACTIVE) {  // inverse coupling: the last DOF of a coupling group wins
+    const int a = tid - 32;
+    const float v = s_pos[P.inverse_src_dof[a]];
+    st.active_prev_targets[a * N + env] = (a < DEX_NUM_BASE) ? v : v / P.inverse_scale[a];
+  } else if (tid >= 64 && tid < 64 + DEX_NUM_FINGERS) {
+    st.contact_duration_steps[(tid - 64) * N + env] = 0.0f;
+    st.prev_contact_binary[(tid - 64) * N + env] = 0.0f;
+  } else if (tid >= 96 && tid < 96 + P.num_actions) {
+    st.prev_actions[(tid - 96) * N + env] = 0.0f;
+  } else if (tid == 128) {
+    st.episode_step_count[env] = 0;
+    if (BG) {  // blind_grasping_task.py:492-509
+      st.success_duration_steps[env] = 0;
+      st.success_conditions_met[env] = 0;
+      st.current_stage[env] = 1;
+      st.time_in_stage[env] = 0.0f;
+      st.stage_contact_duration[env] = 0.0f;
+      st.just_transitioned_to_stage2[env] = 0;
+      st.just_transitioned_to_stage3[env] = 0;
+    }
+  } else if (BG && tid == 160) {  // blind_grasping_task.py:449-490: box pose
+    const float bx = (s_u[0] * 2.0f - 1.0f) * P.box_xy_range;
+    const float by = (s_u[1] * 2.0f - 1.0f) * P.box_xy_range;
+    const float ang = (s_u[2] * 2.0f - 1.0f) * P.pi;
+    st.initial_box_positions[0 * N + env] = bx;
+    st.initial_box_positions[1 * N + env] = by;
+    st.initial_box_positions[2 * N + env] = P.box_z;
+    float* root = A.sim.actor_root_state + ((size_t)env * P.num_actors + P.box_actor) * 13;
+    root[0] = bx;
+    root[1] = by;
+    root[2] = P.box_z;
+    root[3] = 0.0f;
+    root[4] = 0.0f;
+    root[5] = sinf(ang / 2.0f);
+    root[6] = cosf(ang / 2.0f);
+#pragma unroll
+    for (int i = 7; i < 13; ++i) root[i] = 0.0f;
   }
 }
 
@@ -976,6 +1103,8 @@ __global__ void __launch_bounds__(kPostThreads, DICT ? 1 : 4) post_physics_kerne
   __shared__ int s_epi_warp[kPostWarps];
   __shared__ int s_epi_base;
   __shared__ int s_last;
+  __shared__ float s_reset_u[32];
+  __shared__ float s_reset_pos[DEX_NUM_DOF];
   const int tid = threadIdx.x, warp = tid >> 5;
   const int e0 = blockIdx.x * kTile;
   const int ne = min(kTile, A.n - e0);
@@ -992,14 +1121,17 @@ __global__ void __launch_bounds__(kPostThreads, DICT ? 1 : 4) post_physics_kerne
   bool sr = false;
   if (warp == 0) sr = post_scalar<BG>(A, smem, e0, ne);
   const int any_reset = __syncthreads_or(sr ? 1 : 0);
-  gather_rows_out<kMaxObs / 32>(A.out.obs_buf, A.p.obs_dim, s_obs_map, smem, A.stride, e0, ne);
-  if (DICT) gather_rows_out<kMaxDict / 32>(A.out.obs_dict, A.dict_dim, s_dict_map, smem, A.stride, e0, ne);
+  gather_rows_out(A.out.obs_buf, A.p.obs_dim, s_obs_map, smem, A.stride, e0, ne);
+  if (DICT) gather_rows_out(A.out.obs_dict, A.dict_dim, s_dict_map, smem, A.stride, e0, ne);
   post_rows_out(A, smem, e0, ne);
   if (any_reset && !(A.flags & DEX_FLAG_NO_FUSED_RESET)) {  // fused reset (dexhand_base.py:743-756), CTA-uniform branch
-    __syncthreads();
-    if (sr) {
-      const ResetCtx rc{A.uniforms, A.seed, A.st.rng_step ? *A.st.rng_step : A.step};
-      reset_env<BG>(A.p, A.sim, A.st, rc, e0 + (tid & 31), (size_t)A.n);
+    __syncthreads();  // the OUT-table rows of the tile are written before the reset overwrites some of them
+    unsigned mask = __ldcg(A.out.reset_bits + (e0 >> 5));  // written by warp 0 before the vote barrier
+    while (mask) {
+      const int e = __ffs(mask) - 1;
+      mask &= mask - 1;
+      reset_env_coop<BG>(A, e0 + e, s_reset_u, s_reset_pos);
+      __syncthreads();
     }
   }
   if (A.fused_epilogue) {
