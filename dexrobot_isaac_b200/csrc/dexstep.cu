@@ -389,4 +389,11 @@ int dex_quat_mul(const float* a, const float* b, float* out, int32_t n, void* st
   return launch_status();
 }
 
+#ifdef DEXSTEP_TIMELINE
+/* debug builds only: device buffer [grid][8] of uint64 that receives per-CTA phase timestamps */
+int dex_debug_set_timeline(void* dev_ptr) {
+  return (int)cudaMemcpyToSymbol(g_timeline, &dev_ptr, sizeof(dev_ptr));
+}
+#endif
+
 }  // extern "C"

@@ -30,7 +30,9 @@ constexpr int kTile = 32;          // envs per CTA == warp width (lane = env)
 constexpr int kPostThreads = 256;  // 8 warps
 constexpr int kPostWarps = kPostThreads / 32;
 constexpr int kRbW = 13 + 10 * 7;  // hand row (13) + 5 tips + 5 pads (7 each) = 83
-constexpr int kMaxIn = 128, kMaxOut = 192, kMaxObs = 256, kMaxDict = 512;
+constexpr int kMaxIn = 160, kMaxOut = 192, kMaxObs = 256, kMaxDict = 512;
+constexpr int kRowU = 4;                          // table rows per warp per batch (loads issued before stores)
+constexpr int kRowBatch = kPostWarps * kRowU;     // f32 table segments are padded to a multiple of this
 
 // ---- slab slots (floats).  Fixed part; the optional sections follow at run-time offsets (PostArgs.o_*). ----
 enum : int {
@@ -70,6 +72,8 @@ enum : int {
   C_STAGEF,
   C_PROG,
   C_EPTIME,
+  C_MINTIPZ,
+  C_MINTIPBOX,
   M_RESET,  // masks as float 0/1 (they leave as u8 rows)
   M_SUCC,
   M_FAIL,
@@ -256,13 +260,20 @@ inline int build_post_tables(PostArgs& a) {
   {
     int k = 0;
     const int order[3] = {ROW_F32, ROW_I64, ROW_U8};
-    if (cnt[0] + cnt[1] + cnt[2] > kMaxIn) return DEX_ERR_SIZE;
+    if (cnt[0] + cnt[1] + cnt[2] + kRowBatch > kMaxIn) return DEX_ERR_SIZE;
     for (int t = 0; t < 3; ++t) {
       for (int i = 0; i < cnt[order[t]]; ++i, ++k) {
         a.in_ptr[k] = rows[order[t]][i].ptr;
         a.in_meta[k] = rows[order[t]][i].slot;
       }
-      if (t == 0) a.n_in_f32 = k;
+      if (t == 0) {  // pad the f32 segment to a multiple of kRowBatch rows (repeat the last row: idempotent)
+        while (k > 0 && k % kRowBatch != 0 && k < kMaxIn) {
+          a.in_ptr[k] = a.in_ptr[k - 1];
+          a.in_meta[k] = a.in_meta[k - 1];
+          ++k;
+        }
+        a.n_in_f32 = k;
+      }
       if (t == 1) a.n_in_i64 = k;
     }
     a.n_in = k;
@@ -290,8 +301,11 @@ inline int build_post_tables(PostArgs& a) {
     out(st.episode_step_count, 0, 8, S_STEP, ROW_I64);
     if (bg)
       for (int c = 0; c < 3; ++c) out(st.failure_tensors, c, 1, M_FT0 + c, ROW_U8);
-    for (int r = 0; r < P.num_component_rows; ++r) out(a.out.reward_components, r, 4, C_COMP + r, ROW_F32);
-    out(a.out.rew_buf, 0, 4, C_REW, ROW_F32);
+    for (int i = 0; i < DEX_NUM_REWARD_TERMS; ++i)  // raw + weighted rows of the non-zero-weight terms; the total,
+      if (P.component_row[i] >= 0) {                // termination rows and rew_buf leave from post_total()
+        out(a.out.reward_components, P.component_row[i], 4, C_COMP + P.component_row[i], ROW_F32);
+        out(a.out.reward_components, P.component_row[i] + 1, 4, C_COMP + P.component_row[i] + 1, ROW_F32);
+      }
     out(a.out.reset_buf, 0, 1, M_RESET, ROW_U8);
     out(a.out.success, 0, 1, M_SUCC, ROW_U8);
     out(a.out.failure, 0, 1, M_FAIL, ROW_U8);
@@ -307,13 +321,20 @@ inline int build_post_tables(PostArgs& a) {
   {
     int k = 0;
     const int order[3] = {ROW_F32, ROW_I64, ROW_U8};
-    if (cnt[0] + cnt[1] + cnt[2] > kMaxOut) return DEX_ERR_SIZE;
+    if (cnt[0] + cnt[1] + cnt[2] + kRowBatch > kMaxOut) return DEX_ERR_SIZE;
     for (int t = 0; t < 3; ++t) {
       for (int i = 0; i < cnt[order[t]]; ++i, ++k) {
         a.out_ptr[k] = rows[order[t]][i].ptr;
         a.out_meta[k] = rows[order[t]][i].slot;
       }
-      if (t == 0) a.n_out_f32 = k;
+      if (t == 0) {
+        while (k > 0 && k % kRowBatch != 0 && k < kMaxOut) {
+          a.out_ptr[k] = a.out_ptr[k - 1];
+          a.out_meta[k] = a.out_meta[k - 1];
+          ++k;
+        }
+        a.n_out_f32 = k;
+      }
       if (t == 1) a.n_out_i64 = k;
     }
     a.n_out = k;
@@ -348,11 +369,22 @@ inline int build_post_tables(PostArgs& a) {
 // phase 0: stage-in.  Plain LDG -> STS batches (all loads of a batch issued before the first store), no
 // cp.async: on sm_100a every 4-byte LDGSTS costs four issue slots, and this kernel is issue-bound.
 // ------------------------------------------------------------------------------------------------
-template <bool BG>
+__device__ __forceinline__ float lds_f32(const unsigned a) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void sts_f32(const unsigned a, const float v) {
+  asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v) : "memory");
+}
+
+// FULL = the tile holds 32 envs (every tile but a ragged last one): no per-row predicates
+template <bool BG, bool FULL>
 __device__ __forceinline__ void post_stage_in(const PostArgs& A, float* smem, const int e0, const int ne) {
   const DexParams& P = A.p;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int S = A.stride;
+  const unsigned sbase = (unsigned)__cvta_generic_to_shared(smem);
 
   // ---- AoS sim rows: warps take env rows round-robin (4 each), consecutive lanes = consecutive floats ----
   {
@@ -384,61 +416,83 @@ __device__ __forceinline__ void post_stage_in(const PostArgs& A, float* smem, co
     const float* g_dof = A.sim.dof_state + (size_t)(e0 + warp) * (2 * DEX_NUM_DOF) + lane;
     const float* g_rb = A.sim.rigid_body_state + (size_t)(e0 + warp) * nb * 13;
     const float* g_tgt = A.st.full_dof_targets + (size_t)(e0 + warp) * DEX_NUM_DOF + lane;
-    const int rb_step = kPostWarps * nb * 13, x_step = kPostWarps * xrow;
+    const unsigned rb_step = kPostWarps * nb * 13, x_step = kPostWarps * xrow;
     constexpr int R = kTile / kPostWarps;  // env rows per warp
+    // ---- SoA state rows (IN table, lane = env, one 128 B line per request) are issued FIRST and the AoS rows
+    // right behind them, so that every load of the tile is in flight before the first store: one DRAM round
+    // trip for the whole stage-in instead of one per batch.
+    const bool act = FULL || lane < ne;
+    const size_t col = (size_t)e0 + (act ? lane : 0);
+    const size_t colb = col * 4;
+    constexpr int MAXB = kMaxIn / kRowBatch;  // 5 batches of 4 rows per warp
+    const int nbatch = A.n_in_f32 / kRowBatch;
+    float w[MAXB][kRowU];
+#pragma unroll
+    for (int b = 0; b < MAXB; ++b) {
+      if (b < nbatch && act) {
+#pragma unroll
+        for (int u = 0; u < kRowU; ++u)
+          w[b][u] = __ldg(reinterpret_cast<const float*>(A.in_ptr[b * kRowBatch + warp + kPostWarps * u] + colb));
+      }
+    }
+    // typed rows (int64 counters, bool flags): at most a few per warp, loaded as 32-bit values
+    const int r_typed = A.n_in_f32 + warp;
+    float wt = 0.0f;
+    if (act && r_typed < A.n_in) {
+      if (r_typed < A.n_in_i64)  // int64 state is small (counts, stage): keep the low word
+        wt = __int_as_float((int)__ldg(reinterpret_cast<const long long*>(A.in_ptr[r_typed]) + col));
+      else
+        wt = __ldg(reinterpret_cast<const unsigned char*>(A.in_ptr[r_typed]) + col) ? 1.0f : 0.0f;
+    }
     float v[R][7];
 #pragma unroll
     for (int i = 0; i < R; ++i) {
-      if (warp + kPostWarps * i < ne) {
+      if (FULL || warp + kPostWarps * i < ne) {
         v[i][0] = __ldg(g_dof + i * (kPostWarps * 2 * DEX_NUM_DOF));
         if (p_dof1) v[i][1] = __ldg(g_dof + i * (kPostWarps * 2 * DEX_NUM_DOF) + 32);
-        const float* rb = g_rb + (size_t)i * rb_step;
+        const float* rb = g_rb + i * rb_step;
         if (p_rb0) v[i][2] = __ldg(rb + rbo0);
         v[i][3] = __ldg(rb + rbo1);
         if (p_rb2) v[i][4] = __ldg(rb + rbo2);
-        if (p_x) v[i][5] = __ldg(gx + (size_t)i * x_step);
+        if (p_x) v[i][5] = __ldg(gx + i * x_step);
         if (p_tgt) v[i][6] = __ldg(g_tgt + i * (kPostWarps * DEX_NUM_DOF));
       }
     }
+    // ---- stores ----
+    const unsigned Eb = sbase + (unsigned)(lane * S) * 4u;
+#pragma unroll
+    for (int b = 0; b < MAXB; ++b) {
+      if (b < nbatch && act) {
+#pragma unroll
+        for (int u = 0; u < kRowU; ++u)
+          sts_f32(Eb + (unsigned)A.in_meta[b * kRowBatch + warp + kPostWarps * u] * 4u, w[b][u]);
+      }
+    }
+    if (act && r_typed < A.n_in) sts_f32(Eb + (unsigned)A.in_meta[r_typed] * 4u, wt);
+    const unsigned E0 = sbase + (unsigned)(warp * S + lane) * 4u;
+    const unsigned estep = (unsigned)(kPostWarps * S) * 4u;
+    const unsigned otgt = (unsigned)A.o_tgt * 4u;
 #pragma unroll
     for (int i = 0; i < R; ++i) {
-      if (warp + kPostWarps * i < ne) {
-        float* E = smem + (warp + kPostWarps * i) * S + lane;
-        E[I_DOF] = v[i][0];
-        if (p_dof1) E[I_DOF + 32] = v[i][1];
-        if (p_rb0) E[I_RB] = v[i][2];
-        E[I_RB + 32] = v[i][3];
-        if (p_rb2) E[I_RB + 64] = v[i][4];
-        if (p_x) E[I_CF] = v[i][5];
-        if (p_tgt) E[A.o_tgt] = v[i][6];
+      if (FULL || warp + kPostWarps * i < ne) {
+        const unsigned E = E0 + i * estep;
+        sts_f32(E + I_DOF * 4, v[i][0]);
+        if (p_dof1) sts_f32(E + (I_DOF + 32) * 4, v[i][1]);
+        if (p_rb0) sts_f32(E + I_RB * 4, v[i][2]);
+        sts_f32(E + (I_RB + 32) * 4, v[i][3]);
+        if (p_rb2) sts_f32(E + (I_RB + 64) * 4, v[i][4]);
+        if (p_x) sts_f32(E + I_CF * 4, v[i][5]);
+        if (p_tgt) sts_f32(E + otgt, v[i][6]);
       }
     }
-  }
-
-  // ---- SoA state rows through the IN table: lane = env, one 128 B line per request ----
-  if (lane < ne) {
-    float* Ef = smem + lane * S;
-    const size_t col = (size_t)e0 + lane;
-    const size_t colb = col * 4;
-    constexpr int U = 4;
-    for (int r0 = warp; r0 < A.n_in_f32; r0 += kPostWarps * U) {
-      float v[U];
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const int r = r0 + kPostWarps * u;
-        if (r < A.n_in_f32) v[u] = __ldg(reinterpret_cast<const float*>(A.in_ptr[r] + colb));
-      }
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const int r = r0 + kPostWarps * u;
-        if (r < A.n_in_f32) Ef[A.in_meta[r]] = v[u];
-      }
-    }
-    for (int r = A.n_in_f32 + warp; r < A.n_in; r += kPostWarps) {
-      if (r < A.n_in_i64)  // int64 state is small (counts, stage): keep the low word
-        Ef[A.in_meta[r]] = __int_as_float((int)__ldg(reinterpret_cast<const long long*>(A.in_ptr[r]) + col));
+    // more than one typed row per warp (only with the common-reward state): the rest, after the burst
+    for (int r = r_typed + kPostWarps; act && r < A.n_in; r += kPostWarps) {
+      float t;
+      if (r < A.n_in_i64)
+        t = __int_as_float((int)__ldg(reinterpret_cast<const long long*>(A.in_ptr[r]) + col));
       else
-        Ef[A.in_meta[r]] = __ldg(reinterpret_cast<const unsigned char*>(A.in_ptr[r]) + col) ? 1.0f : 0.0f;
+        t = __ldg(reinterpret_cast<const unsigned char*>(A.in_ptr[r]) + col) ? 1.0f : 0.0f;
+      sts_f32(Eb + (unsigned)A.in_meta[r] * 4u, t);
     }
   }
 }
@@ -570,7 +624,10 @@ __device__ __forceinline__ void post_items(const PostArgs& A, float* smem, const
       const int d = it - i_dof;
       const float pos = E[I_DOF + 2 * d];
       const float dp = pos - E[S_PDP + d];
-      E[S_PDP + d] = (dp == 0.0f) ? dp : dp / dt;  // 0/dt == 0 exactly; skips the IEEE-division slow path for joints at rest
+      // 0/dt == 0 exactly: keep a zero numerator away from the divider (its exponent check sends the whole
+      // warp through the IEEE slow path), joints at rest are the common case
+      const float q = ((dp == 0.0f) ? 1.0f : dp) / dt;
+      E[S_PDP + d] = (dp == 0.0f) ? dp : q;
       if (common && d >= DEX_NUM_BASE) {  // reward_calculator.py:94-98,138-160: Isaac dof_vel, not the finite difference
         float* cp = E + A.o_cpv;
         const int j = d - DEX_NUM_BASE;
@@ -590,12 +647,11 @@ __device__ __forceinline__ void post_items(const PostArgs& A, float* smem, const
 // phase 2: per-env scalar part (warp 0, lane = env).  Returns should_reset of this lane.
 // ------------------------------------------------------------------------------------------------
 template <bool BG>
-__device__ __forceinline__ bool post_scalar(const PostArgs& A, float* smem, const int e0, const int ne) {
+__device__ __forceinline__ bool post_scalar(const PostArgs& A, float* smem, const int e0, const int ne,
+                                            unsigned& ticket_old) {
   const DexParams& P = A.p;
   const int lane = threadIdx.x & 31;
   const bool active = lane < ne;
-  const size_t N = (size_t)A.n;
-  const size_t env = (size_t)e0 + lane;
   float* E = smem + lane * A.stride;
   const float* rb = E + I_RB;
   const float dt = P.control_dt;
@@ -729,128 +785,12 @@ __device__ __forceinline__ bool post_scalar(const PostArgs& A, float* smem, cons
       t_failure = ep_f && !ep_s;
       t_timeout = timeout && !ep_s && !ep_f;
 
-      // ---------------- rewards (reward_calculator.py:66-275, blind_grasping_task.py:980-1208) ----
-      float r[DEX_NUM_REWARD_TERMS];
-#pragma unroll
-      for (int i = 0; i < DEX_NUM_REWARD_TERMS; ++i) r[i] = 0.0f;
-      if (P.need_common_rewards) {
-        const float* cp = E + A.o_cpv;
-        r[DEX_R_ALIVE] = 1.0f;
-        r[DEX_R_HEIGHT_SAFETY] = clampf(1.0f - expf(-(min_tip_z - 0.02f) * 20.0f), 0.0f, 1.0f);
-        float fv2 = 0.0f, fa2 = 0.0f, jl = 0.0f;
-#pragma unroll
-        for (int j = 0; j < DEX_NUM_FINGER_DOF; ++j) {
-          fv2 += cp[CP_FV2 + j];
-          fa2 += cp[CP_FA2 + j];
-          jl += cp[CP_JL + j];
-        }
-        r[DEX_R_FINGER_VELOCITY] = expf(-0.1f * sqrtf(fv2));
-        r[DEX_R_JOINT_LIMIT] = 1.0f - jl / 20.0f;
-        r[DEX_R_FINGER_ACCELERATION] = expf(-2.0f * sqrtf(fa2));
-        r[DEX_R_HAND_VELOCITY] = cp[CP_RHAND + 0];
-        r[DEX_R_HAND_ANGULAR_VELOCITY] = cp[CP_RHAND + 1];
-        r[DEX_R_HAND_ACCELERATION] = cp[CP_RHAND + 2];
-        r[DEX_R_HAND_ANGULAR_ACCELERATION] = cp[CP_RHAND + 3];
-        float changes = 0.0f;
-#pragma unroll
-        for (int f = 0; f < DEX_NUM_FINGERS; ++f) changes += cp[CP_CHG + f];
-        r[DEX_R_CONTACT_STABILITY] = expf(-changes);
-      }
-      if (BG) {
-        const float m1 = (stage == 1) ? 1.0f : 0.0f, m2 = (stage == 2) ? 1.0f : 0.0f, m3 = (stage == 3) ? 1.0f : 0.0f;
-        // stage 1 :1055-1112
-        r[DEX_R_S1_HEIGHT_ALIGNMENT] = expf(-P.height_alignment_decay * avg_hdiff) * m1;
-        r[DEX_R_S1_CENTROID_POSITIONING] = expf(-P.centroid_positioning_decay * E[C_CDIST]) * m1;
-        r[DEX_R_S1_OBJECT_STABILITY] = expf(-P.object_stability_decay * (E[C_DRIFT] + E[C_VMAG])) * m1;
-        {  // torch.var(dim=1), unbiased, over the z of the first three pads
-          const float z0 = rb[13 + 35 + 2], z1 = rb[13 + 35 + 7 + 2], z2 = rb[13 + 35 + 14 + 2];
-          const float mean = (z0 + z1 + z2) / 3.0f;
-          const float d0 = z0 - mean, d1 = z1 - mean, d2 = z2 - mean;
-          const float var = (d0 * d0 + d1 * d1 + d2 * d2) / 2.0f;
-          r[DEX_R_S1_FINGER_HEIGHT_CONSISTENCY] = expf(-P.height_consistency_decay * var) * m1;
-        }
-        r[DEX_R_S1_THUMB_ROTATION] = expf(-5.0f * fabsf(E[I_DOF + 2 * DEX_NUM_BASE] - P.half_pi)) * m1;
-        // stage 2 :1114-1150
-        r[DEX_R_S2_THUMB_CONTACT] = (thumb_c ? 1.0f : 0.0f) * m2;
-        r[DEX_R_S2_OTHER_FINGERS_CONTACT] = (others_c ? 1.0f : 0.0f) * m2;
-        r[DEX_R_S2_GRASP_ACHIEVEMENT] = (grasp ? 1.0f : 0.0f) * m2;
-        r[DEX_R_S2_FINGERPAD_PROXIMITY] = expf(-P.fingerpad_proximity_decay * fmaxf(min_tip_box, P.min_reward_distance)) * m2;
-        {
-          float bv2 = 0.0f;
-#pragma unroll
-          for (int d = 0; d < DEX_NUM_BASE; ++d) bv2 += E[S_PDP + d] * E[S_PDP + d];  // finite-difference base velocity
-          r[DEX_R_S2_BASE_STABILITY] = expf(-P.base_stability_decay * sqrtf(bv2)) * m2;
-        }
-        // stage 3 :1152-1176
-        r[DEX_R_S3_OBJECT_HEIGHT] = clampf((box_z - P.box_z) / P.lift_height_range, 0.0f, 1.0f) * m3;
-        r[DEX_R_S3_GRASP_MAINTENANCE] = (grasp ? 1.0f : 0.0f) * m3;
-        r[DEX_R_S3_GRASP_DURATION] = clampf(grasp_duration / P.contact_duration_threshold_s, 0.0f, 1.0f) * m3;
-        // completion bonuses :1025-1048, penetration :1194-1208
-        r[DEX_R_S1_COMPLETION] = (j2 && !pregrasp_failed) ? 1.0f : 0.0f;
-        r[DEX_R_S2_COMPLETION] = (j3 && !contact_failed) ? 1.0f : 0.0f;
-        r[DEX_R_PENETRATION_PENALTY] = fmaxf(P.penetration_threshold - min_tip_box, 0.0f) * P.penetration_depth_scale;
-      }
-      // weighted sum in dict order (reward_calculator.py:223-275)
-      float* comp = E + C_COMP;
-      float total = 0.0f;
-#pragma unroll
-      for (int i = 0; i < DEX_NUM_REWARD_TERMS; ++i) {
-        if (!BG && i >= DEX_NUM_COMMON_TERMS) break;
-        const float w = P.reward_weight[i];
-        if (w != 0.0f) {
-          const float weighted = r[i] * w;
-          total += weighted;
-          comp[P.component_row[i]] = r[i];
-          comp[P.component_row[i] + 1] = weighted;
-        }
-      }
-      comp[P.total_row] = total;
-      // termination rewards (termination_manager.py:280-321, step_processor.py:204-219)
-      const float rs = t_success ? P.success_reward : 0.0f;
-      const float rf = t_failure ? P.failure_reward : 0.0f;
-      const float rt = t_timeout ? P.timeout_reward : 0.0f;
-      float rew = total;
-      rew += rs;
-      rew += rf;
-      rew += rt;
-      {
-        float* tr = comp + P.termination_row;
-        tr[0] = t_success ? 1.0f : 0.0f;
-        tr[1] = rs;
-        tr[2] = t_failure ? 1.0f : 0.0f;
-        tr[3] = rf;
-        tr[4] = t_timeout ? 1.0f : 0.0f;
-        tr[5] = rt;
-      }
-      E[C_REW] = rew;
+      E[C_MINTIPZ] = min_tip_z;
+      if (BG) E[C_MINTIPBOX] = min_tip_box;
       E[M_RESET] = should_reset ? 1.0f : 0.0f;
       E[M_SUCC] = t_success ? 1.0f : 0.0f;
       E[M_FAIL] = t_failure ? 1.0f : 0.0f;
       E[M_TIMEOUT] = t_timeout ? 1.0f : 0.0f;
-
-      // ---------------- fused RewardComponentObserver (rl/reward_observer.py:160-293) -----------
-      if (A.out.episode_sums != nullptr) {
-        const int rows = P.num_component_rows;
-        const int len = A.out.episode_lengths[env] + 1;
-        const int stride = 2 + rows;
-        double* tot = A.out.stat_totals;
-        const int cls = t_success ? 1 : (t_failure ? 2 : 3);
-        if (should_reset) {
-          atomicAdd(tot + 0, 1.0);
-          atomicAdd(tot + 1, (double)len);
-          atomicAdd(tot + cls * stride + 0, 1.0);
-          atomicAdd(tot + cls * stride + 1, (double)len);
-        }
-        for (int c = 0; c < rows; ++c) {
-          const float s = A.out.episode_sums[(size_t)c * N + env] + comp[c];
-          if (should_reset) {
-            atomicAdd(tot + 2 + c, (double)s);
-            atomicAdd(tot + cls * stride + 2 + c, (double)s);
-          }
-          A.out.episode_sums[(size_t)c * N + env] = should_reset ? 0.0f : s;
-        }
-        A.out.episode_lengths[env] = should_reset ? 0 : len;
-      }
     }
   }
 
@@ -879,8 +819,178 @@ __device__ __forceinline__ bool post_scalar(const PostArgs& A, float* smem, cons
       for (int o = 16; o > 0; o >>= 1) len += __shfl_xor_sync(fullmask, len, o);
       if (lane == 0) atomicAdd(A.out.counters + DEX_CNT_EPISODE_LENGTH, len);
     }
+    // Last-CTA-done ticket for the fused epilogue.  Everything the epilogue reads from this CTA (its reset
+    // word, its counter contributions) was written by THIS thread, so a release RMW orders it; taken here,
+    // early, its round trip overlaps the stage-out instead of sitting behind a full memory fence at the end.
+    if (A.fused_epilogue && lane == 0)
+      asm volatile("atom.add.acq_rel.gpu.u32 %0, [%1], 1;" : "=r"(ticket_old) : "l"(A.ep.ticket) : "memory");
   }
   return should_reset;
+}
+
+// ------------------------------------------------------------------------------------------------
+// phase 2b: reward terms as work items (all warps; lane = env, term index warp-uniform).
+// reward_calculator.py:66-221 (common terms), blind_grasping_task.py:980-1208 (task terms).
+// Writes the raw term and the weighted term into the component rows of the slab.
+// ------------------------------------------------------------------------------------------------
+template <bool BG>
+__device__ __forceinline__ void post_reward_terms(const PostArgs& A, float* smem, const int ne) {
+  const DexParams& P = A.p;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane >= ne) return;
+  float* E = smem + lane * A.stride;
+  const float* rb = E + I_RB;
+  float* comp = E + C_COMP;
+  const int nterms = BG ? DEX_NUM_REWARD_TERMS : DEX_NUM_COMMON_TERMS;
+  for (int i = warp; i < nterms; i += kPostWarps) {
+    const float w = P.reward_weight[i];
+    if (w == 0.0f) continue;  // reward_calculator.py:247-251: zero-weight terms are not materialised
+    float r = 0.0f;
+    if (i < DEX_NUM_COMMON_TERMS) {
+      const float* cp = E + A.o_cpv;
+      switch (i) {
+        case DEX_R_ALIVE: r = 1.0f; break;
+        case DEX_R_HEIGHT_SAFETY: r = clampf(1.0f - expf(-(E[C_MINTIPZ] - 0.02f) * 20.0f), 0.0f, 1.0f); break;
+        case DEX_R_FINGER_VELOCITY: {
+          float a = 0.0f;
+#pragma unroll
+          for (int j = 0; j < DEX_NUM_FINGER_DOF; ++j) a += cp[CP_FV2 + j];
+          r = expf(-0.1f * sqrtf(a));
+        } break;
+        case DEX_R_HAND_VELOCITY: r = cp[CP_RHAND + 0]; break;
+        case DEX_R_HAND_ANGULAR_VELOCITY: r = cp[CP_RHAND + 1]; break;
+        case DEX_R_JOINT_LIMIT: {
+          float a = 0.0f;
+#pragma unroll
+          for (int j = 0; j < DEX_NUM_FINGER_DOF; ++j) a += cp[CP_JL + j];
+          r = 1.0f - a / 20.0f;
+        } break;
+        case DEX_R_FINGER_ACCELERATION: {
+          float a = 0.0f;
+#pragma unroll
+          for (int j = 0; j < DEX_NUM_FINGER_DOF; ++j) a += cp[CP_FA2 + j];
+          r = expf(-2.0f * sqrtf(a));
+        } break;
+        case DEX_R_HAND_ACCELERATION: r = cp[CP_RHAND + 2]; break;
+        case DEX_R_HAND_ANGULAR_ACCELERATION: r = cp[CP_RHAND + 3]; break;
+        default: {  // DEX_R_CONTACT_STABILITY
+          float a = 0.0f;
+#pragma unroll
+          for (int f = 0; f < DEX_NUM_FINGERS; ++f) a += cp[CP_CHG + f];
+          r = expf(-a);
+        } break;
+      }
+    } else if (BG) {
+      const int stage = __float_as_int(E[S_STAGE]);
+      const float m1 = (stage == 1) ? 1.0f : 0.0f, m2 = (stage == 2) ? 1.0f : 0.0f, m3 = (stage == 3) ? 1.0f : 0.0f;
+      switch (i) {
+        // stage 1 :1055-1112
+        case DEX_R_S1_HEIGHT_ALIGNMENT: r = expf(-P.height_alignment_decay * E[C_AVGHDIFF]) * m1; break;
+        case DEX_R_S1_CENTROID_POSITIONING: r = expf(-P.centroid_positioning_decay * E[C_CDIST]) * m1; break;
+        case DEX_R_S1_OBJECT_STABILITY: r = expf(-P.object_stability_decay * (E[C_DRIFT] + E[C_VMAG])) * m1; break;
+        case DEX_R_S1_FINGER_HEIGHT_CONSISTENCY: {  // torch.var(dim=1), unbiased, z of the first three pads
+          const float z0 = rb[13 + 35 + 2], z1 = rb[13 + 35 + 7 + 2], z2 = rb[13 + 35 + 14 + 2];
+          const float mean = (z0 + z1 + z2) / 3.0f;
+          const float d0 = z0 - mean, d1 = z1 - mean, d2 = z2 - mean;
+          const float var = (d0 * d0 + d1 * d1 + d2 * d2) / 2.0f;
+          r = expf(-P.height_consistency_decay * var) * m1;
+        } break;
+        case DEX_R_S1_THUMB_ROTATION: r = expf(-5.0f * fabsf(E[I_DOF + 2 * DEX_NUM_BASE] - P.half_pi)) * m1; break;
+        // stage 2 :1114-1150
+        case DEX_R_S2_THUMB_CONTACT: r = E[C_THUMB] * m2; break;
+        case DEX_R_S2_OTHER_FINGERS_CONTACT: r = E[C_OTHERS] * m2; break;
+        case DEX_R_S2_GRASP_ACHIEVEMENT: r = E[C_GRASP] * m2; break;
+        case DEX_R_S2_FINGERPAD_PROXIMITY:
+          r = expf(-P.fingerpad_proximity_decay * fmaxf(E[C_MINTIPBOX], P.min_reward_distance)) * m2;
+          break;
+        case DEX_R_S2_BASE_STABILITY: {
+          float bv2 = 0.0f;
+#pragma unroll
+          for (int d = 0; d < DEX_NUM_BASE; ++d) bv2 += E[S_PDP + d] * E[S_PDP + d];  // finite-difference base velocity
+          r = expf(-P.base_stability_decay * sqrtf(bv2)) * m2;
+        } break;
+        // stage 3 :1152-1176
+        case DEX_R_S3_OBJECT_HEIGHT: r = clampf((E[I_BOX + 2] - P.box_z) / P.lift_height_range, 0.0f, 1.0f) * m3; break;
+        case DEX_R_S3_GRASP_MAINTENANCE: r = E[C_GRASP] * m3; break;
+        case DEX_R_S3_GRASP_DURATION:
+          r = clampf(E[C_GRASPDUR] / P.contact_duration_threshold_s, 0.0f, 1.0f) * m3;
+          break;
+        // completion bonuses :1025-1048, penetration :1194-1208
+        case DEX_R_S1_COMPLETION: r = (E[M_J2] != 0.0f && E[M_FT0] == 0.0f) ? 1.0f : 0.0f; break;
+        case DEX_R_S2_COMPLETION: r = (E[M_J3] != 0.0f && E[M_FT1] == 0.0f) ? 1.0f : 0.0f; break;
+        default:  // DEX_R_PENETRATION_PENALTY
+          r = fmaxf(P.penetration_threshold - E[C_MINTIPBOX], 0.0f) * P.penetration_depth_scale;
+          break;
+      }
+    }
+    const int row = P.component_row[i];
+    comp[row] = r;
+    comp[row + 1] = r * w;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// phase 2c: ordered weighted sum (reward_calculator.py:223-275), termination rewards
+// (termination_manager.py:280-321, step_processor.py:204-219), optional fused RewardComponentObserver.
+// Warp 0, lane = env.  The rows it produces leave straight from registers (coalesced).
+// ------------------------------------------------------------------------------------------------
+template <bool BG>
+__device__ __forceinline__ void post_total(const PostArgs& A, float* smem, const int e0, const int ne) {
+  const DexParams& P = A.p;
+  const int lane = threadIdx.x & 31;
+  if (lane >= ne) return;
+  const size_t N = (size_t)A.n;
+  const size_t env = (size_t)e0 + lane;
+  float* E = smem + lane * A.stride;
+  float* comp = E + C_COMP;
+  float total = 0.0f;
+#pragma unroll
+  for (int i = 0; i < DEX_NUM_REWARD_TERMS; ++i) {
+    if (!BG && i >= DEX_NUM_COMMON_TERMS) break;
+    if (P.reward_weight[i] != 0.0f) total += comp[P.component_row[i] + 1];  // dict order: common, then task
+  }
+  const bool t_success = E[M_SUCC] != 0.0f, t_failure = E[M_FAIL] != 0.0f, t_timeout = E[M_TIMEOUT] != 0.0f;
+  const float rs = t_success ? P.success_reward : 0.0f;
+  const float rf = t_failure ? P.failure_reward : 0.0f;
+  const float rt = t_timeout ? P.timeout_reward : 0.0f;
+  float rew = total;
+  rew += rs;
+  rew += rf;
+  rew += rt;
+  float* g = A.out.reward_components + env;
+  const float tv[7] = {total, t_success ? 1.0f : 0.0f, rs, t_failure ? 1.0f : 0.0f, rf, t_timeout ? 1.0f : 0.0f, rt};
+  g[(size_t)P.total_row * N] = tv[0];
+#pragma unroll
+  for (int k = 0; k < 6; ++k) g[(size_t)(P.termination_row + k) * N] = tv[1 + k];
+  A.out.rew_buf[env] = rew;
+
+  // ---------------- fused RewardComponentObserver (rl/reward_observer.py:160-293) -----------
+  if (A.out.episode_sums != nullptr) {
+    comp[P.total_row] = tv[0];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) comp[P.termination_row + k] = tv[1 + k];
+    const bool should_reset = E[M_RESET] != 0.0f;
+    const int rows = P.num_component_rows;
+    const int len = A.out.episode_lengths[env] + 1;
+    const int stride = 2 + rows;
+    double* tot = A.out.stat_totals;
+    const int cls = t_success ? 1 : (t_failure ? 2 : 3);
+    if (should_reset) {
+      atomicAdd(tot + 0, 1.0);
+      atomicAdd(tot + 1, (double)len);
+      atomicAdd(tot + cls * stride + 0, 1.0);
+      atomicAdd(tot + cls * stride + 1, (double)len);
+    }
+    for (int c = 0; c < rows; ++c) {
+      const float s = A.out.episode_sums[(size_t)c * N + env] + comp[c];
+      if (should_reset) {
+        atomicAdd(tot + 2 + c, (double)s);
+        atomicAdd(tot + cls * stride + 2 + c, (double)s);
+      }
+      A.out.episode_sums[(size_t)c * N + env] = should_reset ? 0.0f : s;
+    }
+    A.out.episode_lengths[env] = should_reset ? 0 : len;
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -888,47 +998,45 @@ __device__ __forceinline__ bool post_scalar(const PostArgs& A, float* smem, cons
 // ------------------------------------------------------------------------------------------------
 // rows of a [N, W] row-major buffer gathered from the slab through a column map (shared copy of the map):
 // a warp owns 4 env rows; lane = column (mod 32), so every global store is a full coalesced 128 B request
+template <bool FULL>
 __device__ __forceinline__ void gather_rows_out(float* __restrict__ dst, const int W, const short* s_map,
                                                 const float* smem, const int S, const int e0, const int ne) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   constexpr int R = kTile / kPostWarps;
+  const unsigned s0 = (unsigned)__cvta_generic_to_shared(smem) + (unsigned)(warp * S) * 4u;
+  const unsigned sstep = (unsigned)(kPostWarps * S) * 4u;
   float* d0 = dst + ((size_t)e0 + warp) * W;
-  const float* s0 = smem + warp * S;
+  const unsigned dstep = (unsigned)(kPostWarps * W);
   for (int k = lane; k < W; k += 32) {
-    const float* src = s0 + s_map[k];
+    const unsigned a = s0 + (unsigned)s_map[k] * 4u;
     float v[R];
 #pragma unroll
     for (int i = 0; i < R; ++i)
-      if (warp + kPostWarps * i < ne) v[i] = src[i * kPostWarps * S];
+      if (FULL || warp + kPostWarps * i < ne) v[i] = lds_f32(a + i * sstep);
+    float* d = d0 + k;
 #pragma unroll
     for (int i = 0; i < R; ++i)
-      if (warp + kPostWarps * i < ne) d0[(size_t)(i * kPostWarps * W + k)] = v[i];
+      if (FULL || warp + kPostWarps * i < ne) d[i * dstep] = v[i];
   }
 }
 
 // every updated state / output row through the OUT table: lane = env, one 128 B (f32) request per row
+template <bool FULL>
 __device__ __forceinline__ void post_rows_out(const PostArgs& A, const float* smem, const int e0, const int ne) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  if (lane >= ne) return;
-  const float* E = smem + lane * A.stride;
+  if (!FULL && lane >= ne) return;
+  const unsigned Eb = (unsigned)__cvta_generic_to_shared(smem) + (unsigned)(lane * A.stride) * 4u;
   const size_t col = (size_t)e0 + lane;
   const size_t colb = col * 4;
-  constexpr int U = 4;
-  for (int r0 = warp; r0 < A.n_out_f32; r0 += kPostWarps * U) {
-    float v[U];
+  for (int r0 = warp; r0 < A.n_out_f32; r0 += kRowBatch) {  // padded segment: no bounds checks
+    float v[kRowU];
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int r = r0 + kPostWarps * u;
-      if (r < A.n_out_f32) v[u] = E[A.out_meta[r]];
-    }
+    for (int u = 0; u < kRowU; ++u) v[u] = lds_f32(Eb + (unsigned)A.out_meta[r0 + kPostWarps * u] * 4u);
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int r = r0 + kPostWarps * u;
-      if (r < A.n_out_f32) *reinterpret_cast<float*>(A.out_ptr[r] + colb) = v[u];
-    }
+    for (int u = 0; u < kRowU; ++u) *reinterpret_cast<float*>(A.out_ptr[r0 + kPostWarps * u] + colb) = v[u];
   }
   for (int r = A.n_out_f32 + warp; r < A.n_out; r += kPostWarps) {
-    const float v = E[A.out_meta[r]];
+    const float v = lds_f32(Eb + (unsigned)A.out_meta[r] * 4u);
     if (r < A.n_out_i64)
       reinterpret_cast<long long*>(A.out_ptr[r])[col] = (long long)__float_as_int(v);
     else
@@ -943,7 +1051,8 @@ __device__ __forceinline__ void post_rows_out(const PostArgs& A, const float* sm
 // Same arithmetic as reset_env() (dexstep_common.cuh), one element per thread.  Called CTA-uniformly.
 // ------------------------------------------------------------------------------------------------
 template <bool BG>
-__device__ __forceinline__ void reset_env_coop(const PostArgs& A, const int env, float* s_u, float* s_pos) {
+__device__ __forceinline__ void reset_env_coop(const PostArgs& A, const int env, const uint64_t step, float* s_u,
+                                               float* s_pos) {
   const DexParams& P = A.p;
   const DexStateBuffers& st = A.st;
   const int tid = threadIdx.x;
@@ -952,7 +1061,6 @@ __device__ __forceinline__ void reset_env_coop(const PostArgs& A, const int env,
     if (A.uniforms != nullptr) {
       if (tid < DEX_NUM_UNIFORMS) s_u[tid] = A.uniforms[(size_t)env * DEX_NUM_UNIFORMS + tid];
     } else if (tid < 8) {
-      const uint64_t step = st.rng_step ? *st.rng_step : A.step;
       uint32_t r[4];
       philox4x32_10((uint32_t)env, (uint32_t)tid, (uint32_t)step, (uint32_t)(step >> 32), (uint32_t)A.seed,
                     (uint32_t)(A.seed >> 32), r);
@@ -1033,68 +1141,85 @@ __device__ void epilogue_body(const DexEpilogueBuffers& ep, const int n, const i
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   constexpr int NW = T / 32;
   const int words = (n + 31) >> 5;
-  if (tid == 0) *s_base = 0;
+  // thread t owns the contiguous word range [t*K, (t+1)*K): one block scan for any n
+  const int K = (words + T - 1) / T;
+  const int w_begin = min(tid * K, words), w_end = min(w_begin + K, words);
+  int cnt = 0;
+  for (int w = w_begin; w < w_end; ++w) cnt += __popc(__ldcg(ep.reset_bits + w));
+  int incl = cnt;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int v = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += v;
+  }
+  if (lane == 31) s_warp[warp] = incl;
   __syncthreads();
-  for (int w0 = 0; w0 < words; w0 += T) {
-    const int w = w0 + tid;
-    unsigned bits = (w < words) ? __ldcg(ep.reset_bits + w) : 0u;
-    const int cnt = __popc(bits);
-    int incl = cnt;
+  if (warp == 0) {
+    int v = (lane < NW) ? s_warp[lane] : 0;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-      const int v = __shfl_up_sync(0xffffffffu, incl, o);
-      if (lane >= o) incl += v;
+      const int u = __shfl_up_sync(0xffffffffu, v, o);
+      if (lane >= o) v += u;
     }
-    if (lane == 31) s_warp[warp] = incl;
-    __syncthreads();
-    if (warp == 0) {
-      int v = (lane < NW) ? s_warp[lane] : 0;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const int u = __shfl_up_sync(0xffffffffu, v, o);
-        if (lane >= o) v += u;
-      }
-      if (lane < NW) s_warp[lane] = v;
-    }
-    __syncthreads();
-    int pos = *s_base + (warp > 0 ? s_warp[warp - 1] : 0) + incl - cnt;
+    if (lane < NW) s_warp[lane] = v;
+    if (lane == NW - 1) *s_base = v;
+  }
+  __syncthreads();
+  int pos = (warp > 0 ? s_warp[warp - 1] : 0) + incl - cnt;
+  for (int w = w_begin; w < w_end; ++w) {
+    unsigned bits = __ldcg(ep.reset_bits + w);
     while (bits) {
       const int b = __ffs(bits) - 1;
       ep.env_ids[pos++] = w * 32 + b;
       bits &= bits - 1;
     }
-    __syncthreads();
-    if (tid == 0) *s_base += s_warp[NW - 1];
-    __syncthreads();
   }
-  if (tid == 0) {
-    *ep.num_reset = *s_base;
-    int32_t c[DEX_NUM_COUNTERS];
-#pragma unroll
-    for (int k = 0; k < DEX_NUM_COUNTERS; ++k) c[k] = __ldcg(ep.counters + k);
+  // counters -> rates (termination_manager.py:259-266); thread k owns counter k
+  if (warp == 0) {
+    const int c = (lane < DEX_NUM_COUNTERS) ? __ldcg(ep.counters + lane) : 0;
     const float fn = (float)n;
-    ep.stats[DEX_STAT_SUCCESS_RATE] = (float)c[DEX_CNT_SUCCESS] / fn;
-    ep.stats[DEX_STAT_FAILURE_RATE] = (float)c[DEX_CNT_FAILURE] / fn;
-    ep.stats[DEX_STAT_TIMEOUT_RATE] = (float)c[DEX_CNT_TIMEOUT] / fn;
-#pragma unroll
-    for (int k = 0; k < DEX_NUM_CRITERIA; ++k) ep.stats[DEX_STAT_CRIT0 + k] = (float)c[DEX_CNT_CRIT0 + k] / fn;
-    int cs = *ep.consecutive_successes;
-    cs = (c[DEX_CNT_SUCCESS] > 0) ? cs + 1 : 0;
-    *ep.consecutive_successes = min(cs, max_consecutive);
-    if (ep.totals != nullptr) {
-#pragma unroll
-      for (int k = 0; k < DEX_NUM_COUNTERS; ++k) ep.totals[k] += c[k];
-      ep.totals[DEX_NUM_COUNTERS] += 1;
+    if (lane == DEX_CNT_SUCCESS) ep.stats[DEX_STAT_SUCCESS_RATE] = (float)c / fn;
+    if (lane == DEX_CNT_FAILURE) ep.stats[DEX_STAT_FAILURE_RATE] = (float)c / fn;
+    if (lane == DEX_CNT_TIMEOUT) ep.stats[DEX_STAT_TIMEOUT_RATE] = (float)c / fn;
+    if (lane >= DEX_CNT_CRIT0 && lane < DEX_CNT_CRIT0 + DEX_NUM_CRITERIA)
+      ep.stats[DEX_STAT_CRIT0 + (lane - DEX_CNT_CRIT0)] = (float)c / fn;
+    if (lane < DEX_NUM_COUNTERS) {
+      if (ep.totals != nullptr) ep.totals[lane] += c;
+      ep.counters[lane] = 0;
     }
-#pragma unroll
-    for (int k = 0; k < DEX_NUM_COUNTERS; ++k) ep.counters[k] = 0;
-    if (ep.rng_step != nullptr) *ep.rng_step += 1;
+    const int n_success = __shfl_sync(0xffffffffu, c, DEX_CNT_SUCCESS);
+    if (lane == 0) {
+      *ep.num_reset = *s_base;
+      int cs = *ep.consecutive_successes;  // termination_manager.py:323-339
+      cs = (n_success > 0) ? cs + 1 : 0;
+      *ep.consecutive_successes = min(cs, max_consecutive);
+      if (ep.totals != nullptr) ep.totals[DEX_NUM_COUNTERS] += 1;
+      if (ep.rng_step != nullptr) *ep.rng_step += 1;
+    }
   }
 }
 
 // ------------------------------------------------------------------------------------------------
 // the kernel
 // ------------------------------------------------------------------------------------------------
+#ifdef DEXSTEP_TIMELINE  // debug build only (tools/timeline.py): per-CTA phase timestamps, [grid][8] ns + smid
+__device__ unsigned long long* g_timeline = nullptr;
+__device__ __forceinline__ void tl_mark(const int k) {
+  if (threadIdx.x == 0 && g_timeline != nullptr) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    g_timeline[(size_t)blockIdx.x * 8 + k] = t;
+    if (k == 0) {
+      unsigned sm;
+      asm volatile("mov.u32 %0, %%smid;" : "=r"(sm));
+      g_timeline[(size_t)blockIdx.x * 8 + 7] = sm;
+    }
+  }
+}
+#define TL_MARK(k) tl_mark(k)
+#else
+#define TL_MARK(k)
+#endif
 template <bool BG, bool DICT>
 __global__ void __launch_bounds__(kPostThreads, DICT ? 1 : 4) post_physics_kernel(const __grid_constant__ PostArgs A) {
   extern __shared__ __align__(16) float smem[];
@@ -1109,45 +1234,68 @@ __global__ void __launch_bounds__(kPostThreads, DICT ? 1 : 4) post_physics_kerne
   const int e0 = blockIdx.x * kTile;
   const int ne = min(kTile, A.n - e0);
 
+  TL_MARK(0);
+  // Philox step counter: read before this CTA takes its ticket, i.e. before the fused epilogue can advance it
+  const uint64_t rng_step = A.st.rng_step ? *A.st.rng_step : A.step;
   s_obs_map[tid] = A.obs_src[tid];  // kMaxObs == kPostThreads
   if (DICT) {
     s_dict_map[tid] = A.dict_src[tid];
     s_dict_map[tid + kPostThreads] = A.dict_src[tid + kPostThreads];
   }
-  post_stage_in<BG>(A, smem, e0, ne);
+  const bool full_tile = ne == kTile;  // CTA-uniform
+  if (full_tile)
+    post_stage_in<BG, true>(A, smem, e0, ne);
+  else
+    post_stage_in<BG, false>(A, smem, e0, ne);
   __syncthreads();
+  TL_MARK(1);
   post_items<BG>(A, smem, ne);
   __syncthreads();
+  TL_MARK(2);
   bool sr = false;
-  if (warp == 0) sr = post_scalar<BG>(A, smem, e0, ne);
+  unsigned ticket_old = 0;
+  if (warp == 0) sr = post_scalar<BG>(A, smem, e0, ne, ticket_old);
   const int any_reset = __syncthreads_or(sr ? 1 : 0);
-  gather_rows_out(A.out.obs_buf, A.p.obs_dim, s_obs_map, smem, A.stride, e0, ne);
-  if (DICT) gather_rows_out(A.out.obs_dict, A.dict_dim, s_dict_map, smem, A.stride, e0, ne);
-  post_rows_out(A, smem, e0, ne);
+  TL_MARK(3);
+  const bool full_mode = A.mode == DEX_MODE_FULL;
+  if (full_mode) post_reward_terms<BG>(A, smem, ne);
+  if (full_tile) {
+    gather_rows_out<true>(A.out.obs_buf, A.p.obs_dim, s_obs_map, smem, A.stride, e0, ne);
+    if (DICT) gather_rows_out<true>(A.out.obs_dict, A.dict_dim, s_dict_map, smem, A.stride, e0, ne);
+  } else {
+    gather_rows_out<false>(A.out.obs_buf, A.p.obs_dim, s_obs_map, smem, A.stride, e0, ne);
+    if (DICT) gather_rows_out<false>(A.out.obs_dict, A.dict_dim, s_dict_map, smem, A.stride, e0, ne);
+  }
+  if (full_mode) {
+    __syncthreads();  // the reward-term rows of the slab are complete
+    if (warp == 0) post_total<BG>(A, smem, e0, ne);
+  }
+  if (full_tile)
+    post_rows_out<true>(A, smem, e0, ne);
+  else
+    post_rows_out<false>(A, smem, e0, ne);
+  TL_MARK(4);
   if (any_reset && !(A.flags & DEX_FLAG_NO_FUSED_RESET)) {  // fused reset (dexhand_base.py:743-756), CTA-uniform branch
     __syncthreads();  // the OUT-table rows of the tile are written before the reset overwrites some of them
     unsigned mask = __ldcg(A.out.reset_bits + (e0 >> 5));  // written by warp 0 before the vote barrier
     while (mask) {
       const int e = __ffs(mask) - 1;
       mask &= mask - 1;
-      reset_env_coop<BG>(A, e0 + e, s_reset_u, s_reset_pos);
+      reset_env_coop<BG>(A, e0 + e, rng_step, s_reset_u, s_reset_pos);
       __syncthreads();
     }
   }
+  TL_MARK(5);
   if (A.fused_epilogue) {
+    // the CTA that drew the last ticket: every other CTA has published its reset word and counters
+    if (tid == 0) s_last = (ticket_old == gridDim.x - 1) ? 1 : 0;
     __syncthreads();
-    if (tid == 0) {
-      __threadfence();
-      const unsigned t = atomicAdd(A.ep.ticket, 1u);
-      s_last = (t == gridDim.x - 1) ? 1 : 0;
-    }
-    __syncthreads();
-    if (s_last) {
-      __threadfence();
+    if (s_last) {  // acquire side: tid 0's acq_rel ticket RMW + the barrier above order these (L2) reads
       epilogue_body<kPostThreads>(A.ep, A.n, A.p.max_consecutive_successes, s_epi_warp, &s_epi_base);
       if (tid == 0) *A.ep.ticket = 0u;
     }
   }
+  TL_MARK(6);
 }
 
 __global__ void __launch_bounds__(1024) epilogue_kernel(const DexEpilogueBuffers ep, const int n, const int max_consecutive) {
