@@ -58,73 +58,95 @@ struct PreArgs {
   int32_t n;
 };
 
-constexpr int kPreTile = 128;
-constexpr int kActS = 19;   // odd smem row stride for <=18 actions
-constexpr int kFullS = 27;  // odd smem row stride for 26 DOF targets
+// One CTA of 8 warps owns 32 consecutive envs.  The 18 active targets are work items taken round-robin by the
+// warps with lane = env: the SoA state rows (prev / rule targets in, new targets out, prev_actions out) move as
+// full 128 B lines, the branch on the target index is warp-uniform.  The AoS tiles (actions in,
+// full_dof_targets out) are contiguous in global memory and cross a small shared tile with odd row stride.
+constexpr int kPreTile = 32;
+constexpr int kPreThreads = 256;
+constexpr int kPreWarps = kPreThreads / 32;
+constexpr int kActS = 19;  // odd smem row stride for <=18 actions / 18 active targets
 
-__global__ void __launch_bounds__(kPreTile) pre_physics_kernel(const __grid_constant__ PreArgs A) {
+__global__ void __launch_bounds__(kPreThreads) pre_physics_kernel(const __grid_constant__ PreArgs A) {
   __shared__ float s_act[kPreTile * kActS];
   __shared__ float s_next[kPreTile * kActS];
-  __shared__ float s_full[kPreTile * kFullS];
   const DexParams& P = A.p;
   const DexStateBuffers& st = A.st;
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int e0 = blockIdx.x * kPreTile;
   const int ne = min(kPreTile, A.n - e0);
   const size_t N = (size_t)A.n;
   const int NA = P.num_actions;
-  {  // stage the action tile (row-major [N,NACT]) with coalesced loads
-    const float* src = A.actions + (size_t)e0 * NA;
-    for (int i = tid; i < ne * NA; i += kPreTile) {
+  const size_t env = (size_t)e0 + lane;
+  const bool act_lane = lane < ne;
+
+  // issue every global load of the tile first: the action tile (contiguous [ne, NACT]) ...
+  const float* asrc = A.actions + (size_t)e0 * NA;
+  const int nact = ne * NA;
+  float av[3];
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    const int i = tid + j * kPreThreads;
+    av[j] = (i < nact) ? __ldg(asrc + i) : 0.0f;
+  }
+  // ... and the prev / rule target rows of this warp's items (a = warp, warp + 8, warp + 16)
+  float prev[3], rule[3];
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    const int a = warp + j * kPreWarps;
+    if (a < DEX_NUM_ACTIVE && act_lane) {
+      prev[j] = st.active_prev_targets[a * N + env];
+      rule[j] = st.active_rule_targets[a * N + env];
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    const int i = tid + j * kPreThreads;
+    if (i < nact) {
       const int e = i / NA, k = i - e * NA;
-      s_act[e * kActS + k] = __ldg(src + i);
+      s_act[e * kActS + k] = av[j];
     }
   }
   __syncthreads();
-  if (tid < ne) {
-    const int env = e0 + tid;
-    const float* act = s_act + tid * kActS;
-    float* nxt = s_next + tid * kActS;
-    const int fs = P.policy_controls_base ? DEX_NUM_BASE : 0;  // default_rules.py:53,97
+
+  const int fs = P.policy_controls_base ? DEX_NUM_BASE : 0;  // default_rules.py:53,97
 #pragma unroll
-    for (int a = 0; a < DEX_NUM_ACTIVE; ++a) {
-      const float prev = st.active_prev_targets[a * N + env];
-      const float rule = st.active_rule_targets[a * N + env];
+  for (int j = 0; j < 3; ++j) {
+    const int a = warp + j * kPreWarps;
+    if (a < DEX_NUM_ACTIVE && act_lane) {
       const float lo = P.active_lower[a], hi = P.active_upper[a], md = P.max_deltas[a];
       const bool controlled = (a < DEX_NUM_BASE) ? (P.policy_controls_base != 0) : (P.policy_controls_fingers != 0);
-      float t = rule;
+      float t = rule[j];
       if (controlled) {
-        const float x = act[(a < DEX_NUM_BASE) ? a : fs + (a - DEX_NUM_BASE)];
+        const float x = s_act[lane * kActS + ((a < DEX_NUM_BASE) ? a : fs + (a - DEX_NUM_BASE))];
         if (P.control_mode == DEX_CONTROL_POSITION)
           t = (x + 1.0f) * 0.5f * (hi - lo) + lo;  // scaling.py:28-45
         else
-          t = prev + x * md;  // scaling.py:48-63
+          t = prev[j] + x * md;  // scaling.py:48-63
       }
       if (P.control_mode == DEX_CONTROL_POSITION_DELTA) t = clampf(t, lo, hi);  // default_rules.py:107-110
       if (A.raw_out != nullptr) A.raw_out[a * N + env] = t;
-      if (P.filter_velocity_clamp) t = prev + clampf(t - prev, -md, md);  // rules.py:141-166
-      if (P.filter_position_clamp) t = clampf(t, lo, hi);                  // rules.py:168-190
-      nxt[a] = t;
+      if (P.filter_velocity_clamp) t = prev[j] + clampf(t - prev[j], -md, md);  // rules.py:141-166
+      if (P.filter_position_clamp) t = clampf(t, lo, hi);                      // rules.py:168-190
+      s_next[lane * kActS + a] = t;
       st.active_prev_targets[a * N + env] = t;  // action_processor.py:342
     }
-    for (int k = 0; k < NA; ++k) st.prev_actions[k * N + env] = act[k];  // observation_encoder.py:287-296
-    // coupling 18 -> 26 (action_processor.py:571-614)
-    float* fullrow = s_full + tid * kFullS;
-#pragma unroll
-    for (int d = 0; d < DEX_NUM_DOF; ++d) {
-      const int a = P.dof_to_active[d];
-      float v = 0.0f;
-      if (a >= 0) v = (d < DEX_NUM_BASE) ? nxt[a] : nxt[a] * P.dof_coupling_scale[d];
-      fullrow[d] = v;
-    }
   }
+  // prev_actions rows (observation_encoder.py:287-296): row k for 32 envs = one 128 B line
+  if (act_lane)
+    for (int k = warp; k < NA; k += kPreWarps) st.prev_actions[k * N + env] = s_act[lane * kActS + k];
   __syncthreads();
-  {
-    float* dst = st.full_dof_targets + (size_t)e0 * DEX_NUM_DOF;
-    for (int i = tid; i < ne * DEX_NUM_DOF; i += kPreTile) {
-      const int e = i / DEX_NUM_DOF, k = i - e * DEX_NUM_DOF;
-      dst[i] = s_full[e * kFullS + k];
+  // coupling 18 -> 26 (action_processor.py:571-614) straight into the contiguous full_dof_targets tile
+  float* dst = st.full_dof_targets + (size_t)e0 * DEX_NUM_DOF;
+  for (int i = tid; i < ne * DEX_NUM_DOF; i += kPreThreads) {
+    const int e = i / DEX_NUM_DOF, d = i - e * DEX_NUM_DOF;
+    const int a = P.dof_to_active[d];
+    float v = 0.0f;
+    if (a >= 0) {
+      v = s_next[e * kActS + a];
+      if (d >= DEX_NUM_BASE) v = v * P.dof_coupling_scale[d];
     }
+    dst[i] = v;
   }
 }
 
@@ -271,7 +293,7 @@ int dex_pre_physics(const DexParams* params, const DexStateBuffers* state, const
   if (n_envs <= 0) return DEX_ERR_SIZE;
   PreArgs a{*params, *state, actions, active_raw_targets, n_envs};
   const int grid = (n_envs + kPreTile - 1) / kPreTile;
-  pre_physics_kernel<<<grid, kPreTile, 0, (cudaStream_t)stream>>>(a);
+  pre_physics_kernel<<<grid, kPreThreads, 0, (cudaStream_t)stream>>>(a);
   return launch_status();
 }
 

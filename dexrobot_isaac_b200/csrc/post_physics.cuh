@@ -1144,8 +1144,17 @@ __device__ void epilogue_body(const DexEpilogueBuffers& ep, const int n, const i
   // thread t owns the contiguous word range [t*K, (t+1)*K): one block scan for any n
   const int K = (words + T - 1) / T;
   const int w_begin = min(tid * K, words), w_end = min(w_begin + K, words);
+  // all L2 reads of the epilogue are issued up front (one round trip): the counters and, when a thread owns at
+  // most kCache words (n <= 32768 with 256 threads), its reset words
+  constexpr int kCache = 4;
+  const int c = (warp == 0 && lane < DEX_NUM_COUNTERS) ? __ldcg(ep.counters + lane) : 0;
+  unsigned cache[kCache];
+#pragma unroll
+  for (int i = 0; i < kCache; ++i) cache[i] = (w_begin + i < w_end) ? __ldcg(ep.reset_bits + w_begin + i) : 0u;
   int cnt = 0;
-  for (int w = w_begin; w < w_end; ++w) cnt += __popc(__ldcg(ep.reset_bits + w));
+#pragma unroll
+  for (int i = 0; i < kCache; ++i) cnt += __popc(cache[i]);
+  for (int w = w_begin + kCache; w < w_end; ++w) cnt += __popc(__ldcg(ep.reset_bits + w));
   int incl = cnt;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
@@ -1167,7 +1176,9 @@ __device__ void epilogue_body(const DexEpilogueBuffers& ep, const int n, const i
   __syncthreads();
   int pos = (warp > 0 ? s_warp[warp - 1] : 0) + incl - cnt;
   for (int w = w_begin; w < w_end; ++w) {
-    unsigned bits = __ldcg(ep.reset_bits + w);
+    const int i = w - w_begin;
+    unsigned bits = (i < kCache) ? (i == 0 ? cache[0] : i == 1 ? cache[1] : i == 2 ? cache[2] : cache[3])
+                                 : __ldcg(ep.reset_bits + w);
     while (bits) {
       const int b = __ffs(bits) - 1;
       ep.env_ids[pos++] = w * 32 + b;
@@ -1176,7 +1187,6 @@ __device__ void epilogue_body(const DexEpilogueBuffers& ep, const int n, const i
   }
   // counters -> rates (termination_manager.py:259-266); thread k owns counter k
   if (warp == 0) {
-    const int c = (lane < DEX_NUM_COUNTERS) ? __ldcg(ep.counters + lane) : 0;
     const float fn = (float)n;
     if (lane == DEX_CNT_SUCCESS) ep.stats[DEX_STAT_SUCCESS_RATE] = (float)c / fn;
     if (lane == DEX_CNT_FAILURE) ep.stats[DEX_STAT_FAILURE_RATE] = (float)c / fn;
