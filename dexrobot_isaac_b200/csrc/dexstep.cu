@@ -70,6 +70,8 @@ constexpr int kActS = 19;  // odd smem row stride for <=18 actions / 18 active t
 __global__ void __launch_bounds__(kPreThreads) pre_physics_kernel(const __grid_constant__ PreArgs A) {
   __shared__ float s_act[kPreTile * kActS];
   __shared__ float s_next[kPreTile * kActS];
+  __shared__ int s_d2a[DEX_NUM_DOF];
+  __shared__ float s_scale[DEX_NUM_DOF];
   const DexParams& P = A.p;
   const DexStateBuffers& st = A.st;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -80,15 +82,18 @@ __global__ void __launch_bounds__(kPreThreads) pre_physics_kernel(const __grid_c
   const size_t env = (size_t)e0 + lane;
   const bool act_lane = lane < ne;
 
-  // issue every global load of the tile first: the action tile (contiguous [ne, NACT]) ...
-  const float* asrc = A.actions + (size_t)e0 * NA;
-  const int nact = ne * NA;
-  float av[3];
-#pragma unroll
-  for (int j = 0; j < 3; ++j) {
-    const int i = tid + j * kPreThreads;
-    av[j] = (i < nact) ? __ldg(asrc + i) : 0.0f;
+  // coupling tables -> shared (a per-lane index into the constant bank would serialise)
+  if (tid < DEX_NUM_DOF) {
+    s_d2a[tid] = P.dof_to_active[tid];
+    s_scale[tid] = (tid < DEX_NUM_BASE) ? 1.0f : P.dof_coupling_scale[tid];
   }
+  // issue every global load of the tile first: the action rows (warp w: env rows w, w+8, ..; lane = column) ...
+  constexpr int R = kPreTile / kPreWarps;
+  const float* asrc = A.actions + ((size_t)e0 + warp) * NA + lane;
+  float av[R];
+#pragma unroll
+  for (int j = 0; j < R; ++j)
+    av[j] = (lane < NA && warp + j * kPreWarps < ne) ? __ldg(asrc + j * kPreWarps * NA) : 0.0f;
   // ... and the prev / rule target rows of this warp's items (a = warp, warp + 8, warp + 16)
   float prev[3], rule[3];
 #pragma unroll
@@ -100,13 +105,8 @@ __global__ void __launch_bounds__(kPreThreads) pre_physics_kernel(const __grid_c
     }
   }
 #pragma unroll
-  for (int j = 0; j < 3; ++j) {
-    const int i = tid + j * kPreThreads;
-    if (i < nact) {
-      const int e = i / NA, k = i - e * NA;
-      s_act[e * kActS + k] = av[j];
-    }
-  }
+  for (int j = 0; j < R; ++j)
+    if (lane < NA && warp + j * kPreWarps < ne) s_act[(warp + j * kPreWarps) * kActS + lane] = av[j];
   __syncthreads();
 
   const int fs = P.policy_controls_base ? DEX_NUM_BASE : 0;  // default_rules.py:53,97
@@ -140,13 +140,8 @@ __global__ void __launch_bounds__(kPreThreads) pre_physics_kernel(const __grid_c
   float* dst = st.full_dof_targets + (size_t)e0 * DEX_NUM_DOF;
   for (int i = tid; i < ne * DEX_NUM_DOF; i += kPreThreads) {
     const int e = i / DEX_NUM_DOF, d = i - e * DEX_NUM_DOF;
-    const int a = P.dof_to_active[d];
-    float v = 0.0f;
-    if (a >= 0) {
-      v = s_next[e * kActS + a];
-      if (d >= DEX_NUM_BASE) v = v * P.dof_coupling_scale[d];
-    }
-    dst[i] = v;
+    const int a = s_d2a[d];
+    dst[i] = (a >= 0) ? s_next[e * kActS + a] * s_scale[d] : 0.0f;
   }
 }
 
