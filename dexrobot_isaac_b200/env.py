@@ -67,38 +67,57 @@ class DexStepEnv:
         # whatever the global RNG yields; here: uniforms 0.5 unless given.
         u = init_uniforms if init_uniforms is not None else torch.full((self.num_envs, NUM_UNIFORMS), 0.5)
         p.reset_idx(None, u.to(dev, torch.float32).contiguous())
+        # ---- the reference's components (dexhand_base.py:453-537), facades over the pipeline ----
+        from .components import (ActionProcessor, ObservationEncoder, ResetManager, RewardCalculator, StepProcessor,
+                                 TerminationManager)
+        self.obs_dict: Dict = {}
+        self.last_reward_components: Dict = {}
+        self.action_processor = ActionProcessor(self)
+        self.action_processor.initialize_from_config({
+            "control_mode": self.task_cfg["controlMode"], "num_dof": 26,
+            "policy_controls_hand_base": self.task_cfg["policy_controls_hand_base"],
+            "policy_controls_fingers": self.task_cfg["policy_controls_fingers"],
+            "finger_vel_limit": self.task_cfg["max_finger_joint_velocity"],
+            "base_lin_vel_limit": self.task_cfg["max_base_linear_velocity"],
+            "base_ang_vel_limit": self.task_cfg["max_base_angular_velocity"],
+            "post_action_filters": ["velocity_clamp", "position_clamp"]})
+        self.observation_encoder = ObservationEncoder(self)
+        self.observation_encoder.initialize(observation_keys=self.task_cfg["policy_observation_keys"],
+                                            num_actions=self.num_actions, action_processor=self.action_processor)
+        self.termination_manager = TerminationManager(self, self.task_cfg)
+        self.reward_calculator = RewardCalculator(self, self.task_cfg)
+        self.reset_manager = ResetManager(self, self.dof_state, self.actor_root_state_tensor, 0,
+                                          torch.zeros(26, device=dev), task=None)
+        self.step_processor = StepProcessor(self)
+        self.action_processor.finalize_setup()
 
     # ------------------------------------------------------------------ reference call sequence
     def reset_idx(self, env_ids):
         """dexhand_base.py:743-756 (masked form of the index list)."""
         if len(env_ids) == 0:
             return
-        mask = torch.zeros(self.num_envs, dtype=torch.bool, device=self.device)
-        mask[env_ids.to(self.device)] = True
-        self.pipeline.reset_idx(mask)
+        self.reset_manager.reset_idx(env_ids)
 
     def reset(self, uniforms: Optional[torch.Tensor] = None):
         p = self.pipeline
         if uniforms is not None:
             p.uniforms = uniforms.to(self.device, torch.float32).contiguous()
-        p.reset_idx(None)
-        p.post_physics(MODE_OBS_ONLY, FLAG_STALE_CONTACTS)  # first pass: no refresh_tensors (dexhand_base.py:813)
-        p.post_step()
-        self._update_extras()
+        self.reset_manager.reset_all()                                      # dexhand_base.py:805-811
+        self.observation_encoder.compute_observations(stale_contacts=True)  # :813, no refresh_tensors before it
+        self.step_processor.process_physics_step()                          # :815-838
         return self.obs_buf
 
     def pre_physics_step(self, actions: torch.Tensor):
-        a = actions.to(self.device, torch.float32)
-        self._actions.copy_(a)
-        self.pipeline.pre_physics(self._actions)
+        """dexhand_base.py:840-887."""
+        self.action_processor.process_actions(actions=actions,
+                                              active_rule_targets=self.action_processor.active_rule_targets)
+        self.observation_encoder.update_prev_actions(self._actions)
 
     def post_physics_step(self, uniforms: Optional[torch.Tensor] = None):
         p = self.pipeline
         if uniforms is not None:
             p.uniforms = uniforms.to(self.device, torch.float32).contiguous()
-        p.post_step()
-        self._update_extras()
-        return self.obs_buf, self.rew_buf, self.reset_buf, self.extras
+        return self.step_processor.process_physics_step()
 
     def step(self, actions: torch.Tensor):
         self.pre_physics_step(actions)
@@ -151,7 +170,9 @@ class DexStepEnv:
                 # termination_manager.py:353-357 + step_processor.py:109-111: every env whose criterion
                 # fired was reset in the same step, which clears its sticky reason bit before extras are
                 # built -> the masks that reach extras are all-False.
-                ex[f"{kind}_reason_{name}"] = self._zero_mask
+                tm = getattr(self, "termination_manager", None)
+                ex[f"{kind}_reason_{name}"] = self._zero_mask if tm is None else \
+                    (tm.success_reasons if kind == "success" else tm.failure_reasons)[name]
         ex["reward_components"] = p.reward_components()
         self.extras = ex
 
