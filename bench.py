@@ -391,6 +391,7 @@ def main():
         dist.init_process_group("nccl", device_id=device)
         barrier = lambda: dist.barrier(device_ids=[local])  # noqa: E731
     from dexrobot_isaac_b200 import _lib
+    from dexrobot_isaac_b200 import stats as dex_stats
 
     _lib.load()  # fails loudly when the CUDA library is missing
     ring = Ring(task, n_env, device, 1234 + rank, args.observer)
@@ -420,11 +421,8 @@ def main():
     # the single statistics all-reduce of the logging interval, on a side stream
     side.wait_event(e1)
     with torch.cuda.stream(side):
-        payload = torch.stack([e.pipeline.epi["totals"] for e in ring.envs]).sum(dim=0).double()
-        if ring.envs[0].pipeline.out["stat_totals"] is not None:
-            payload = torch.cat([payload, torch.stack([e.pipeline.out["stat_totals"] for e in ring.envs]).sum(0).flatten()])
-        if world > 1:
-            dist.all_reduce(payload)
+        payload = dex_stats.pack_pipelines([e.pipeline for e in ring.envs])
+        dex_stats.all_reduce(payload)  # NCCL over NVLink when world > 1, no-op on one GPU
     torch.cuda.synchronize(device)
     if barrier is not None:
         barrier()
