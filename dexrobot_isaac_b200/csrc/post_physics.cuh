@@ -624,10 +624,7 @@ __device__ __forceinline__ void post_items(const PostArgs& A, float* smem, const
       const int d = it - i_dof;
       const float pos = E[I_DOF + 2 * d];
       const float dp = pos - E[S_PDP + d];
-      // 0/dt == 0 exactly: keep a zero numerator away from the divider (its exponent check sends the whole
-      // warp through the IEEE slow path), joints at rest are the common case
-      const float q = ((dp == 0.0f) ? 1.0f : dp) / dt;
-      E[S_PDP + d] = (dp == 0.0f) ? dp : q;
+      E[S_PDP + d] = div_rn(dp, dt);  // joints at rest (dp == 0) are the common case: see div_rn
       if (common && d >= DEX_NUM_BASE) {  // reward_calculator.py:94-98,138-160: Isaac dof_vel, not the finite difference
         float* cp = E + A.o_cpv;
         const int j = d - DEX_NUM_BASE;
@@ -636,7 +633,7 @@ __device__ __forceinline__ void post_items(const PostArgs& A, float* smem, const
         cp[CP_FV2 + j] = iv * iv;
         const float acc = iv - pv;
         cp[CP_FA2 + j] = acc * acc;
-        const float nj = 2.0f * (pos - P.dof_lower[d]) / (P.dof_upper[d] - P.dof_lower[d]) - 1.0f;
+        const float nj = div_rn(2.0f * (pos - P.dof_lower[d]), P.dof_upper[d] - P.dof_lower[d]) - 1.0f;
         cp[CP_JL + j] = clampf(fabsf(nj) - 0.8f, 0.0f, 1.0f);
       }
     }
@@ -683,8 +680,8 @@ __device__ __forceinline__ bool post_scalar(const PostArgs& A, float* smem, cons
         dsum += E[C_PADBOX + f];
         hsum += E[C_HDIFF + f];
       }
-      avg_hdiff = hsum / 5.0f;
-      E[C_AVGDIST] = dsum / 5.0f;
+      avg_hdiff = div_rn(hsum, 5.0f);
+      E[C_AVGDIST] = div_rn(dsum, 5.0f);
       E[C_AVGHDIFF] = avg_hdiff;
       // finger-box contacts :773-833
       const bool box_has = E[C_BOXHAS] != 0.0f;
@@ -731,8 +728,8 @@ __device__ __forceinline__ bool post_scalar(const PostArgs& A, float* smem, cons
       E[M_J2] = j2 ? 1.0f : 0.0f;
       E[M_J3] = j3 ? 1.0f : 0.0f;
       float prog = 0.0f;  // :958-978
-      if (stage == 1) prog = clampf(tis / P.stage1_duration, 0.0f, 1.0f);
-      if (stage == 2) prog = clampf(tis / P.stage2_duration, 0.0f, 1.0f);
+      if (stage == 1) prog = clampf(div_rn(tis, P.stage1_duration), 0.0f, 1.0f);
+      if (stage == 2) prog = clampf(div_rn(tis, P.stage2_duration), 0.0f, 1.0f);
       if (stage == 3) prog = 1.0f;
       E[C_STAGEF] = (float)stage;
       E[C_PROG] = prog;
@@ -823,7 +820,7 @@ __device__ __forceinline__ bool post_scalar(const PostArgs& A, float* smem, cons
     // word, its counter contributions) was written by THIS thread, so a release RMW orders it; taken here,
     // early, its round trip overlaps the stage-out instead of sitting behind a full memory fence at the end.
     if (A.fused_epilogue && lane == 0)
-      asm volatile("atom.add.acq_rel.gpu.u32 %0, [%1], 1;" : "=r"(ticket_old) : "l"(A.ep.ticket) : "memory");
+      asm volatile("atom.add.release.gpu.u32 %0, [%1], 1;" : "=r"(ticket_old) : "l"(A.ep.ticket) : "memory");
   }
   return should_reset;
 }
@@ -863,7 +860,7 @@ __device__ __forceinline__ void post_reward_terms(const PostArgs& A, float* smem
           float a = 0.0f;
 #pragma unroll
           for (int j = 0; j < DEX_NUM_FINGER_DOF; ++j) a += cp[CP_JL + j];
-          r = 1.0f - a / 20.0f;
+          r = 1.0f - div_rn(a, 20.0f);
         } break;
         case DEX_R_FINGER_ACCELERATION: {
           float a = 0.0f;
@@ -910,10 +907,10 @@ __device__ __forceinline__ void post_reward_terms(const PostArgs& A, float* smem
           r = expf(-P.base_stability_decay * sqrtf(bv2)) * m2;
         } break;
         // stage 3 :1152-1176
-        case DEX_R_S3_OBJECT_HEIGHT: r = clampf((E[I_BOX + 2] - P.box_z) / P.lift_height_range, 0.0f, 1.0f) * m3; break;
+        case DEX_R_S3_OBJECT_HEIGHT: r = clampf(div_rn(E[I_BOX + 2] - P.box_z, P.lift_height_range), 0.0f, 1.0f) * m3; break;
         case DEX_R_S3_GRASP_MAINTENANCE: r = E[C_GRASP] * m3; break;
         case DEX_R_S3_GRASP_DURATION:
-          r = clampf(E[C_GRASPDUR] / P.contact_duration_threshold_s, 0.0f, 1.0f) * m3;
+          r = clampf(div_rn(E[C_GRASPDUR], P.contact_duration_threshold_s), 0.0f, 1.0f) * m3;
           break;
         // completion bonuses :1025-1048, penetration :1194-1208
         case DEX_R_S1_COMPLETION: r = (E[M_J2] != 0.0f && E[M_FT0] == 0.0f) ? 1.0f : 0.0f; break;
@@ -1045,60 +1042,59 @@ __device__ __forceinline__ void post_rows_out(const PostArgs& A, const float* sm
 }
 
 // ------------------------------------------------------------------------------------------------
-// phase 4: fused reset of ONE finished env by the whole CTA (ResetManager.reset_idx reset_manager.py:92-190,
+// phase 4: fused reset of ONE finished env by ONE warp (ResetManager.reset_idx reset_manager.py:92-190,
 // BlindGraspingTask.reset_task_state blind_grasping_task.py:433-547, ActionProcessor.reset_targets
 // action_processor.py:524-568,616-666, ObservationEncoder.reset_observer_state observation_encoder.py:363-383).
-// Same arithmetic as reset_env() (dexstep_common.cuh), one element per thread.  Called CTA-uniformly.
+// Same arithmetic as reset_env() (dexstep_common.cuh), lane = element; the warps of the CTA reset different
+// envs of the tile concurrently, no CTA barrier inside.  s_u: this warp's 32-float scratch.
 // ------------------------------------------------------------------------------------------------
 template <bool BG>
-__device__ __forceinline__ void reset_env_coop(const PostArgs& A, const int env, const uint64_t step, float* s_u,
-                                               float* s_pos) {
+__device__ __forceinline__ void reset_env_warp(const PostArgs& A, const int env, const uint64_t step, float* s_u) {
   const DexParams& P = A.p;
   const DexStateBuffers& st = A.st;
-  const int tid = threadIdx.x;
+  const int lane = threadIdx.x & 31;
   const size_t N = (size_t)A.n;
+  const unsigned full = 0xffffffffu;
   if (BG) {
     if (A.uniforms != nullptr) {
-      if (tid < DEX_NUM_UNIFORMS) s_u[tid] = A.uniforms[(size_t)env * DEX_NUM_UNIFORMS + tid];
-    } else if (tid < 8) {
+      if (lane < DEX_NUM_UNIFORMS) s_u[lane] = A.uniforms[(size_t)env * DEX_NUM_UNIFORMS + lane];
+    } else if (lane < 8) {
       uint32_t r[4];
-      philox4x32_10((uint32_t)env, (uint32_t)tid, (uint32_t)step, (uint32_t)(step >> 32), (uint32_t)A.seed,
+      philox4x32_10((uint32_t)env, (uint32_t)lane, (uint32_t)step, (uint32_t)(step >> 32), (uint32_t)A.seed,
                     (uint32_t)(A.seed >> 32), r);
 #pragma unroll
-      for (int k = 0; k < 4; ++k) s_u[4 * tid + k] = (float)(r[k] >> 8) * (1.0f / 16777216.0f);
+      for (int k = 0; k < 4; ++k) s_u[4 * lane + k] = (float)(r[k] >> 8) * (1.0f / 16777216.0f);
     }
-    __syncthreads();
+    __syncwarp();
   }
-  if (tid < DEX_NUM_DOF) {
-    float p = 0.0f;
+  float p = 0.0f;  // new position of DOF `lane`
+  if (lane < DEX_NUM_DOF) {
     if (BG) {  // blind_grasping_task.py:511-547 (all 20 finger DOFs, including r_f_joint3_1)
-      if (tid < 3)
-        p = (s_u[3 + tid] * 2.0f - 1.0f) * P.hand_translation_range;
-      else if (tid < 6)
-        p = (s_u[3 + tid] * 2.0f - 1.0f) * P.hand_rotation_range;
-      else if (tid == 6)
-        p = s_u[9] * P.thumb_rotation_range;
+      const float u = s_u[3 + lane];
+      if (lane < 3)
+        p = (u * 2.0f - 1.0f) * P.hand_translation_range;
+      else if (lane < 6)
+        p = (u * 2.0f - 1.0f) * P.hand_rotation_range;
+      else if (lane == 6)
+        p = u * P.thumb_rotation_range;
       else
-        p = s_u[3 + tid] * P.other_finger_range;
+        p = u * P.other_finger_range;
     }
-    s_pos[tid] = p;
     float* dof = A.sim.dof_state + (size_t)env * (DEX_NUM_DOF * 2);
-    dof[2 * tid] = p;
-    dof[2 * tid + 1] = 0.0f;
-    st.full_dof_targets[(size_t)env * DEX_NUM_DOF + tid] = p;  // action_processor.py:553 (verbatim, DOF 14 included)
-    st.prev_dof_pos[tid * N + env] = 0.0f;                     // observation_encoder.py:375-376 (zero, not the new pose)
+    reinterpret_cast<float2*>(dof)[lane] = make_float2(p, 0.0f);
+    st.full_dof_targets[(size_t)env * DEX_NUM_DOF + lane] = p;  // action_processor.py:553 (verbatim, DOF 14 included)
+    st.prev_dof_pos[lane * N + env] = 0.0f;                     // observation_encoder.py:375-376 (zero, not the new pose)
   }
-  __syncthreads();
-  if (tid >= 32 && tid < 32 + DEX_NUM_ACTIVE) {  // inverse coupling: the last DOF of a coupling group wins
-    const int a = tid - 32;
-    const float v = s_pos[P.inverse_src_dof[a]];
-    st.active_prev_targets[a * N + env] = (a < DEX_NUM_BASE) ? v : v / P.inverse_scale[a];
-  } else if (tid >= 64 && tid < 64 + DEX_NUM_FINGERS) {
-    st.contact_duration_steps[(tid - 64) * N + env] = 0.0f;
-    st.prev_contact_binary[(tid - 64) * N + env] = 0.0f;
-  } else if (tid >= 96 && tid < 96 + P.num_actions) {
-    st.prev_actions[(tid - 96) * N + env] = 0.0f;
-  } else if (tid == 128) {
+  // inverse coupling: the last DOF of a coupling group wins (action_processor.py:616-666)
+  const int src = (lane < DEX_NUM_ACTIVE) ? P.inverse_src_dof[lane] : 0;
+  const float v = __shfl_sync(full, p, src);
+  if (lane < DEX_NUM_ACTIVE) st.active_prev_targets[lane * N + env] = (lane < DEX_NUM_BASE) ? v : v / P.inverse_scale[lane];
+  if (lane < DEX_NUM_FINGERS) {
+    st.contact_duration_steps[lane * N + env] = 0.0f;
+    st.prev_contact_binary[lane * N + env] = 0.0f;
+  }
+  if (lane < P.num_actions) st.prev_actions[lane * N + env] = 0.0f;
+  if (lane == 26) {
     st.episode_step_count[env] = 0;
     if (BG) {  // blind_grasping_task.py:492-509
       st.success_duration_steps[env] = 0;
@@ -1109,7 +1105,7 @@ __device__ __forceinline__ void reset_env_coop(const PostArgs& A, const int env,
       st.just_transitioned_to_stage2[env] = 0;
       st.just_transitioned_to_stage3[env] = 0;
     }
-  } else if (BG && tid == 160) {  // blind_grasping_task.py:449-490: box pose
+  } else if (BG && lane == 27) {  // blind_grasping_task.py:449-490: box pose
     const float bx = (s_u[0] * 2.0f - 1.0f) * P.box_xy_range;
     const float by = (s_u[1] * 2.0f - 1.0f) * P.box_xy_range;
     const float ang = (s_u[2] * 2.0f - 1.0f) * P.pi;
@@ -1127,6 +1123,7 @@ __device__ __forceinline__ void reset_env_coop(const PostArgs& A, const int env,
 #pragma unroll
     for (int i = 7; i < 13; ++i) root[i] = 0.0f;
   }
+  __syncwarp();  // s_u is reused by this warp's next env
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1148,6 +1145,11 @@ __device__ void epilogue_body(const DexEpilogueBuffers& ep, const int n, const i
   // most kCache words (n <= 32768 with 256 threads), its reset words
   constexpr int kCache = 4;
   const int c = (warp == 0 && lane < DEX_NUM_COUNTERS) ? __ldcg(ep.counters + lane) : 0;
+  const bool has_tot = warp == 0 && lane <= DEX_NUM_COUNTERS && ep.totals != nullptr;
+  const long long tot0 = has_tot ? __ldcg(reinterpret_cast<const long long*>(ep.totals) + lane) : 0;
+  const bool l0 = warp == 0 && lane == 0;
+  const int cs0 = l0 ? __ldcg(ep.consecutive_successes) : 0;
+  const unsigned long long rs0 = (l0 && ep.rng_step != nullptr) ? __ldcg(reinterpret_cast<const unsigned long long*>(ep.rng_step)) : 0ull;
   unsigned cache[kCache];
 #pragma unroll
   for (int i = 0; i < kCache; ++i) cache[i] = (w_begin + i < w_end) ? __ldcg(ep.reset_bits + w_begin + i) : 0u;
@@ -1193,18 +1195,14 @@ __device__ void epilogue_body(const DexEpilogueBuffers& ep, const int n, const i
     if (lane == DEX_CNT_TIMEOUT) ep.stats[DEX_STAT_TIMEOUT_RATE] = (float)c / fn;
     if (lane >= DEX_CNT_CRIT0 && lane < DEX_CNT_CRIT0 + DEX_NUM_CRITERIA)
       ep.stats[DEX_STAT_CRIT0 + (lane - DEX_CNT_CRIT0)] = (float)c / fn;
-    if (lane < DEX_NUM_COUNTERS) {
-      if (ep.totals != nullptr) ep.totals[lane] += c;
-      ep.counters[lane] = 0;
-    }
+    if (has_tot) ep.totals[lane] = tot0 + (lane < DEX_NUM_COUNTERS ? c : 1);  // [DEX_NUM_COUNTERS] counts steps
+    if (lane < DEX_NUM_COUNTERS) ep.counters[lane] = 0;
     const int n_success = __shfl_sync(0xffffffffu, c, DEX_CNT_SUCCESS);
     if (lane == 0) {
       *ep.num_reset = *s_base;
-      int cs = *ep.consecutive_successes;  // termination_manager.py:323-339
-      cs = (n_success > 0) ? cs + 1 : 0;
+      const int cs = (n_success > 0) ? cs0 + 1 : 0;  // termination_manager.py:323-339
       *ep.consecutive_successes = min(cs, max_consecutive);
-      if (ep.totals != nullptr) ep.totals[DEX_NUM_COUNTERS] += 1;
-      if (ep.rng_step != nullptr) *ep.rng_step += 1;
+      if (ep.rng_step != nullptr) *ep.rng_step = rs0 + 1;
     }
   }
 }
@@ -1238,15 +1236,13 @@ __global__ void __launch_bounds__(kPostThreads, DICT ? 1 : 4) post_physics_kerne
   __shared__ int s_epi_warp[kPostWarps];
   __shared__ int s_epi_base;
   __shared__ int s_last;
-  __shared__ float s_reset_u[32];
-  __shared__ float s_reset_pos[DEX_NUM_DOF];
+  __shared__ float s_reset_u[32 * kPostWarps];
+  __shared__ unsigned long long s_rng_step;
   const int tid = threadIdx.x, warp = tid >> 5;
   const int e0 = blockIdx.x * kTile;
   const int ne = min(kTile, A.n - e0);
 
   TL_MARK(0);
-  // Philox step counter: read before this CTA takes its ticket, i.e. before the fused epilogue can advance it
-  const uint64_t rng_step = A.st.rng_step ? *A.st.rng_step : A.step;
   s_obs_map[tid] = A.obs_src[tid];  // kMaxObs == kPostThreads
   if (DICT) {
     s_dict_map[tid] = A.dict_src[tid];
@@ -1257,6 +1253,9 @@ __global__ void __launch_bounds__(kPostThreads, DICT ? 1 : 4) post_physics_kerne
     post_stage_in<BG, true>(A, smem, e0, ne);
   else
     post_stage_in<BG, false>(A, smem, e0, ne);
+  // Philox step counter: read before this CTA takes its ticket (scalar phase), i.e. before the fused epilogue can
+  // advance it - but by ONE thread and after the stage-in loads are in flight (it is an HBM miss of its own)
+  if (tid == 64) s_rng_step = A.st.rng_step ? *A.st.rng_step : A.step;
   __syncthreads();
   TL_MARK(1);
   post_items<BG>(A, smem, ne);
@@ -1288,19 +1287,23 @@ __global__ void __launch_bounds__(kPostThreads, DICT ? 1 : 4) post_physics_kerne
   if (any_reset && !(A.flags & DEX_FLAG_NO_FUSED_RESET)) {  // fused reset (dexhand_base.py:743-756), CTA-uniform branch
     __syncthreads();  // the OUT-table rows of the tile are written before the reset overwrites some of them
     unsigned mask = __ldcg(A.out.reset_bits + (e0 >> 5));  // written by warp 0 before the vote barrier
-    while (mask) {
+    const uint64_t rng_step = s_rng_step;
+    // warp w resets the (w)th, (w+8)th, ... finished env of the tile
+    for (int k = 0; mask; ++k) {
       const int e = __ffs(mask) - 1;
       mask &= mask - 1;
-      reset_env_coop<BG>(A, e0 + e, rng_step, s_reset_u, s_reset_pos);
-      __syncthreads();
+      if ((k & (kPostWarps - 1)) == warp) reset_env_warp<BG>(A, e0 + e, rng_step, s_reset_u + 32 * warp);
     }
   }
   TL_MARK(5);
   if (A.fused_epilogue) {
     // the CTA that drew the last ticket: every other CTA has published its reset word and counters
-    if (tid == 0) s_last = (ticket_old == gridDim.x - 1) ? 1 : 0;
+    if (tid == 0) {
+      s_last = (ticket_old == gridDim.x - 1) ? 1 : 0;
+      if (s_last) __threadfence();  // acquire side of the release tickets of all other CTAs
+    }
     __syncthreads();
-    if (s_last) {  // acquire side: tid 0's acq_rel ticket RMW + the barrier above order these (L2) reads
+    if (s_last) {  // tid 0's fence + the barrier above order these (L2, ld.cg) reads
       epilogue_body<kPostThreads>(A.ep, A.n, A.p.max_consecutive_successes, s_epi_warp, &s_epi_base);
       if (tid == 0) *A.ep.ticket = 0u;
     }

@@ -19,7 +19,7 @@ from dexrobot_isaac_b200 import _lib as L  # noqa: E402
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 16384
 task = sys.argv[2] if len(sys.argv) > 2 else "BlindGrasping"
 tl_path = os.path.join(B.PKG_DIR, "libdexstep_tl.so")
-cmd = [B.find_nvcc()] + B.NVCC_FLAGS + ["-DDEXSTEP_TIMELINE", "-I", os.path.join(ROOT, "include")] + B.SOURCES + ["-o", tl_path]
+cmd = [B.find_nvcc()] + B.NVCC_FLAGS + ["-DDEXSTEP_TIMELINE"] + os.environ.get("TL_FLAGS", "").split() + ["-I", os.path.join(ROOT, "include")] + B.SOURCES + ["-o", tl_path]
 subprocess.run(cmd, check=True)
 L._lib = L.load(tl_path)  # every pipeline created from here on uses the instrumented library
 lib = L._lib
@@ -48,19 +48,31 @@ for _ in range(3):
         e.pipeline.step(a)
 torch.cuda.synchronize()
 assert lib.dex_debug_set_timeline(tl.data_ptr()) == 0
-e, a = envs[0]
-e.pipeline.post_step()
-torch.cuda.synchronize()
+runs = []
+for e, a in envs:  # one L2-cold launch per replica (6 x ~63 MB > L2)
+    tl.zero_()
+    e.pipeline.post_step()
+    torch.cuda.synchronize()
+    runs.append(tl.cpu().double())
 assert lib.dex_debug_set_timeline(None) == 0
-t = tl.cpu().double()
-t0 = t[:, 0].min()
 names = ["start", "stage-in done", "items done", "scalar done", "stage-out done", "reset done", "end"]
-print(f"envs {n} task {task} grid {grid}; times in us relative to the first CTA start")
+print(f"envs {n} task {task} grid {grid}; times in us relative to the first CTA start; median over {len(runs)} launches")
+import statistics as st_
+def med(f):
+    return st_.median(f(t) for t in runs)
 for k, nm in enumerate(names):
-    c = (t[:, k] - t0) / 1e3
-    print(f"{nm:16s} min {c.min():7.2f}  median {c.median():7.2f}  p90 {c.quantile(0.9):7.2f}  max {c.max():7.2f}")
-d = (t[:, 1:7] - t[:, 0:6]) / 1e3
+    print(f"{nm:16s} median {med(lambda t: float(((t[:, k] - t[:, 0].min()) / 1e3).median())):7.2f}  "
+          f"max {med(lambda t: float(((t[:, k] - t[:, 0].min()) / 1e3).max())):7.2f}")
 for k, nm in enumerate(["stage-in", "items", "scalar", "stage-out", "reset", "epilogue"]):
-    print(f"phase {nm:10s} median {d[:, k].median():6.2f}  p90 {d[:, k].quantile(0.9):6.2f}  max {d[:, k].max():6.2f}")
-sm = t[:, 7].long()
-print("CTAs per SM: min", int(torch.bincount(sm).min()), "max", int(torch.bincount(sm).max()), "SMs used", int((torch.bincount(sm) > 0).sum()))
+    print(f"phase {nm:10s} median {med(lambda t: float(((t[:, k + 1] - t[:, k]) / 1e3).median())):6.2f}  "
+          f"max {med(lambda t: float(((t[:, k + 1] - t[:, k]) / 1e3).max())):6.2f}")
+# event-timed average of the (instrumentation-free path of the) same library: ring over the replicas
+e0_, e1_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+reps = 40
+e0_.record()
+for _ in range(reps):
+    for e, a in envs:
+        e.pipeline.post_step()
+e1_.record()
+torch.cuda.synchronize()
+print(f"post-physics launch avg (stream-ordered, eager launches): {1e3 * e0_.elapsed_time(e1_) / (reps * len(envs)):.2f} us")
