@@ -113,7 +113,10 @@ struct PostArgs {
   int32_t o_tgt, o_hf, o_cpv;           // optional sections (-1 = absent)
   int32_t want_hf_tip, want_hf_pad, want_arr, common, dict_dim;
   int32_t n_in_f32, n_in_i64, n_in;     // IN table, sorted by type: [0,n_in_f32) f32 | [..,n_in_i64) i64 | [..,n_in) u8
-  int32_t n_out_f32, n_out_i64, n_out;  // OUT table, same order
+  // OUT table: [0,n_out_early) f32 rows that are final after the items phase | [..,n_out_f32) f32 rows that the scalar
+  // phase / the reward terms write | [..,n_out_i64) int64 rows | [..,n_out) bool rows
+  int32_t n_out_early, n_out_f32, n_out_i64, n_out;
+  uint32_t obs_late, dict_late;         // bit c: columns [32c, 32c+32) read a slot that the scalar phase writes
   int32_t rb_off[11];                   // float offset of the hand / 5 tip / 5 pad rows inside one env's [NB,13] slab
   int32_t cf_off[6];                    // float offset of the 5 monitored contact rows (+ box) inside [NB,3]
   uint64_t in_ptr[kMaxIn];              // row base pointers
@@ -322,18 +325,22 @@ inline int build_post_tables(PostArgs& a) {
     int k = 0;
     const int order[3] = {ROW_F32, ROW_I64, ROW_U8};
     if (cnt[0] + cnt[1] + cnt[2] + kRowBatch > kMaxOut) return DEX_ERR_SIZE;
-    for (int t = 0; t < 3; ++t) {
+    auto late = [&](int slot) {
+      return slot == S_TIS || slot == S_SCD || (slot >= C_COMP && slot < C_COMP + P.num_component_rows);
+    };
+    for (int pass = 0; pass < 2; ++pass) {  // f32 rows: early ones first
+      for (int i = 0; i < cnt[ROW_F32]; ++i)
+        if (late(rows[ROW_F32][i].slot) == (pass == 1)) {
+          a.out_ptr[k] = rows[ROW_F32][i].ptr;
+          a.out_meta[k++] = rows[ROW_F32][i].slot;
+        }
+      if (pass == 0) a.n_out_early = k;
+    }
+    a.n_out_f32 = k;
+    for (int t = 1; t < 3; ++t) {
       for (int i = 0; i < cnt[order[t]]; ++i, ++k) {
         a.out_ptr[k] = rows[order[t]][i].ptr;
         a.out_meta[k] = rows[order[t]][i].slot;
-      }
-      if (t == 0) {
-        while (k > 0 && k % kRowBatch != 0 && k < kMaxOut) {
-          a.out_ptr[k] = a.out_ptr[k - 1];
-          a.out_meta[k] = a.out_meta[k - 1];
-          ++k;
-        }
-        a.n_out_f32 = k;
       }
       if (t == 1) a.n_out_i64 = k;
     }
@@ -351,6 +358,14 @@ inline int build_post_tables(PostArgs& a) {
     if (key >= nkeys || off + dim > P.obs_dim) return DEX_ERR_PARAM;
     for (int j = 0; j < dim; ++j) a.obs_src[off + j] = (int16_t)obs_key_slot(a, key, j);
   }
+  auto slot_is_late = [](int s) {  // slots that the scalar phase (warp 0) writes
+    return s == C_AVGDIST || s == C_AVGHDIFF || s == C_THUMB || s == C_OTHERS || s == C_GRASP || s == C_GRASPDUR ||
+           s == C_STAGEF || s == S_TIS || s == C_PROG || s == C_EPTIME || s == S_STEP || s == S_SDS || s == S_STAGE ||
+           s == S_SCD;
+  };
+  a.obs_late = a.dict_late = 0;
+  for (int c = 0; c < P.obs_dim; ++c)
+    if (slot_is_late(a.obs_src[c])) a.obs_late |= 1u << (c >> 5);
   a.dict_dim = 0;
   if (dict) {
     if (P.dict_dim > kMaxDict) return DEX_ERR_SIZE;
@@ -361,6 +376,8 @@ inline int build_post_tables(PostArgs& a) {
       if (off < 0 || off + dim > P.dict_dim) return DEX_ERR_PARAM;
       for (int j = 0; j < dim; ++j) a.dict_src[off + j] = (int16_t)obs_key_slot(a, key, j);
     }
+    for (int c = 0; c < P.dict_dim; ++c)
+      if (slot_is_late(a.dict_src[c])) a.dict_late |= 1u << (c >> 5);
   }
   return ok ? DEX_OK : DEX_ERR_SIZE;
 }
@@ -994,44 +1011,65 @@ __device__ __forceinline__ void post_total(const PostArgs& A, float* smem, const
 // phase 3: stage-out
 // ------------------------------------------------------------------------------------------------
 // rows of a [N, W] row-major buffer gathered from the slab through a column map (shared copy of the map):
-// a warp owns 4 env rows; lane = column (mod 32), so every global store is a full coalesced 128 B request
-template <bool FULL>
+// lane = column (mod 32), so every global store is a full coalesced 128 B request.  Only the 32-column chunks
+// whose bit is set in `chunks` are written; the env rows are spread over NW warps, this warp is number `w`.
+template <int NW>
 __device__ __forceinline__ void gather_rows_out(float* __restrict__ dst, const int W, const short* s_map,
-                                                const float* smem, const int S, const int e0, const int ne) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  constexpr int R = kTile / kPostWarps;
-  const unsigned s0 = (unsigned)__cvta_generic_to_shared(smem) + (unsigned)(warp * S) * 4u;
-  const unsigned sstep = (unsigned)(kPostWarps * S) * 4u;
-  float* d0 = dst + ((size_t)e0 + warp) * W;
-  const unsigned dstep = (unsigned)(kPostWarps * W);
-  for (int k = lane; k < W; k += 32) {
-    const unsigned a = s0 + (unsigned)s_map[k] * 4u;
-    float v[R];
+                                                const float* smem, const int S, const int e0, const int ne,
+                                                unsigned chunks, const int w) {
+  const int lane = threadIdx.x & 31;
+  constexpr int R = (kTile + NW - 1) / NW;  // env rows per warp
+  const unsigned s0 = (unsigned)__cvta_generic_to_shared(smem) + (unsigned)(w * S) * 4u;
+  const unsigned sstep = (unsigned)(NW * S) * 4u;
+  float* d0 = dst + ((size_t)e0 + w) * W + lane;
+  const size_t dstep = (size_t)NW * W;
+  const int nchunk = (W + 31) >> 5;
+  if (nchunk < 32) chunks &= (1u << nchunk) - 1u;
+  while (chunks) {
+    const int c = __ffs(chunks) - 1;
+    chunks &= chunks - 1;
+    const int k = 32 * c + lane;
+    if (k < W) {
+      const unsigned a = s0 + (unsigned)s_map[k] * 4u;
+      float v[R];
 #pragma unroll
-    for (int i = 0; i < R; ++i)
-      if (FULL || warp + kPostWarps * i < ne) v[i] = lds_f32(a + i * sstep);
-    float* d = d0 + k;
+      for (int i = 0; i < R; ++i)
+        if (w + NW * i < ne) v[i] = lds_f32(a + i * sstep);
+      float* d = d0 + 32 * c;
 #pragma unroll
-    for (int i = 0; i < R; ++i)
-      if (FULL || warp + kPostWarps * i < ne) d[i * dstep] = v[i];
+      for (int i = 0; i < R; ++i) {
+        if (w + NW * i < ne) *d = v[i];
+        d += dstep;
+      }
+    }
   }
 }
 
-// every updated state / output row through the OUT table: lane = env, one 128 B (f32) request per row
-template <bool FULL>
-__device__ __forceinline__ void post_rows_out(const PostArgs& A, const float* smem, const int e0, const int ne) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  if (!FULL && lane >= ne) return;
+// f32 rows [r_begin, r_end) of the OUT table: lane = env, one 128 B request per row; rows spread over NW warps
+template <int NW>
+__device__ __forceinline__ void post_rows_f32(const PostArgs& A, const float* smem, const int e0, const int ne,
+                                              const int r_begin, const int r_end, const int w) {
+  const int lane = threadIdx.x & 31;
+  if (lane >= ne) return;
   const unsigned Eb = (unsigned)__cvta_generic_to_shared(smem) + (unsigned)(lane * A.stride) * 4u;
-  const size_t col = (size_t)e0 + lane;
-  const size_t colb = col * 4;
-  for (int r0 = warp; r0 < A.n_out_f32; r0 += kRowBatch) {  // padded segment: no bounds checks
+  const size_t colb = ((size_t)e0 + lane) * 4;
+  for (int r0 = r_begin + w; r0 < r_end; r0 += NW * kRowU) {
     float v[kRowU];
 #pragma unroll
-    for (int u = 0; u < kRowU; ++u) v[u] = lds_f32(Eb + (unsigned)A.out_meta[r0 + kPostWarps * u] * 4u);
+    for (int u = 0; u < kRowU; ++u)
+      if (r0 + NW * u < r_end) v[u] = lds_f32(Eb + (unsigned)A.out_meta[r0 + NW * u] * 4u);
 #pragma unroll
-    for (int u = 0; u < kRowU; ++u) *reinterpret_cast<float*>(A.out_ptr[r0 + kPostWarps * u] + colb) = v[u];
+    for (int u = 0; u < kRowU; ++u)
+      if (r0 + NW * u < r_end) *reinterpret_cast<float*>(A.out_ptr[r0 + NW * u] + colb) = v[u];
   }
+}
+
+// int64 / bool rows of the OUT table (counters, stage, masks)
+__device__ __forceinline__ void post_rows_typed(const PostArgs& A, const float* smem, const int e0, const int ne) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane >= ne) return;
+  const unsigned Eb = (unsigned)__cvta_generic_to_shared(smem) + (unsigned)(lane * A.stride) * 4u;
+  const size_t col = (size_t)e0 + lane;
   for (int r = A.n_out_f32 + warp; r < A.n_out; r += kPostWarps) {
     const float v = lds_f32(Eb + (unsigned)A.out_meta[r] * 4u);
     if (r < A.n_out_i64)
@@ -1263,26 +1301,26 @@ __global__ void __launch_bounds__(kPostThreads, DICT ? 1 : 4) post_physics_kerne
   TL_MARK(2);
   bool sr = false;
   unsigned ticket_old = 0;
-  if (warp == 0) sr = post_scalar<BG>(A, smem, e0, ne, ticket_old);
+  if (warp == 0) {
+    sr = post_scalar<BG>(A, smem, e0, ne, ticket_old);
+  } else {  // meanwhile everything that is final after the items phase leaves through warps 1..7
+    constexpr int NW = kPostWarps - 1;
+    post_rows_f32<NW>(A, smem, e0, ne, 0, A.n_out_early, warp - 1);
+    gather_rows_out<NW>(A.out.obs_buf, A.p.obs_dim, s_obs_map, smem, A.stride, e0, ne, ~A.obs_late, warp - 1);
+    if (DICT) gather_rows_out<NW>(A.out.obs_dict, A.dict_dim, s_dict_map, smem, A.stride, e0, ne, ~A.dict_late, warp - 1);
+  }
   const int any_reset = __syncthreads_or(sr ? 1 : 0);
   TL_MARK(3);
   const bool full_mode = A.mode == DEX_MODE_FULL;
   if (full_mode) post_reward_terms<BG>(A, smem, ne);
-  if (full_tile) {
-    gather_rows_out<true>(A.out.obs_buf, A.p.obs_dim, s_obs_map, smem, A.stride, e0, ne);
-    if (DICT) gather_rows_out<true>(A.out.obs_dict, A.dict_dim, s_dict_map, smem, A.stride, e0, ne);
-  } else {
-    gather_rows_out<false>(A.out.obs_buf, A.p.obs_dim, s_obs_map, smem, A.stride, e0, ne);
-    if (DICT) gather_rows_out<false>(A.out.obs_dict, A.dict_dim, s_dict_map, smem, A.stride, e0, ne);
-  }
+  gather_rows_out<kPostWarps>(A.out.obs_buf, A.p.obs_dim, s_obs_map, smem, A.stride, e0, ne, A.obs_late, warp);
+  if (DICT) gather_rows_out<kPostWarps>(A.out.obs_dict, A.dict_dim, s_dict_map, smem, A.stride, e0, ne, A.dict_late, warp);
+  post_rows_typed(A, smem, e0, ne);
   if (full_mode) {
     __syncthreads();  // the reward-term rows of the slab are complete
     if (warp == 0) post_total<BG>(A, smem, e0, ne);
   }
-  if (full_tile)
-    post_rows_out<true>(A, smem, e0, ne);
-  else
-    post_rows_out<false>(A, smem, e0, ne);
+  post_rows_f32<kPostWarps>(A, smem, e0, ne, A.n_out_early, A.n_out_f32, warp);
   TL_MARK(4);
   if (any_reset && !(A.flags & DEX_FLAG_NO_FUSED_RESET)) {  // fused reset (dexhand_base.py:743-756), CTA-uniform branch
     __syncthreads();  // the OUT-table rows of the tile are written before the reset overwrites some of them
