@@ -662,7 +662,7 @@ __device__ __forceinline__ void post_items(const PostArgs& A, float* smem, const
 // ------------------------------------------------------------------------------------------------
 template <bool BG>
 __device__ __forceinline__ bool post_scalar(const PostArgs& A, float* smem, const int e0, const int ne,
-                                            unsigned& ticket_old) {
+                                            unsigned& ticket_old, unsigned* s_rbits) {
   const DexParams& P = A.p;
   const int lane = threadIdx.x & 31;
   const bool active = lane < ne;
@@ -812,7 +812,10 @@ __device__ __forceinline__ bool post_scalar(const PostArgs& A, float* smem, cons
     // reset ballot word + cross-env counters (termination_manager.py:164-185,259-266)
     const unsigned fullmask = 0xffffffffu;
     const unsigned rbits = __ballot_sync(fullmask, should_reset);
-    if (lane == 0) A.out.reset_bits[e0 >> 5] = rbits;
+    if (lane == 0) {
+      A.out.reset_bits[e0 >> 5] = rbits;
+      *s_rbits = rbits;  // the CTA's own copy for the fused reset (no L2 round trip)
+    }
     const unsigned bs = __ballot_sync(fullmask, t_success), bf = __ballot_sync(fullmask, t_failure),
                    bt = __ballot_sync(fullmask, t_timeout);
     unsigned bc[DEX_NUM_CRITERIA];
@@ -1170,10 +1173,19 @@ __device__ __forceinline__ void reset_env_warp(const PostArgs& A, const int env,
 // successes (:323-339), running totals.  Runs in ONE CTA of T threads: either the stand-alone
 // epilogue kernel or the last CTA of the post-physics kernel.
 // ------------------------------------------------------------------------------------------------
-template <int T>
+// T threads take part (tid = 0..T-1 within the group); BAR = 0: the whole CTA (__syncthreads), else the id of a
+// named barrier for a T-thread warp group of a larger CTA.
+template <int T, int BAR>
+__device__ __forceinline__ void epilogue_sync() {
+  if (BAR == 0)
+    __syncthreads();
+  else
+    asm volatile("bar.sync %0, %1;" ::"n"(BAR), "n"(T) : "memory");
+}
+template <int T, int BAR>
 __device__ void epilogue_body(const DexEpilogueBuffers& ep, const int n, const int max_consecutive, int* s_warp,
-                              int* s_base) {
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+                              int* s_base, const int tid) {
+  const int lane = tid & 31, warp = tid >> 5;
   constexpr int NW = T / 32;
   const int words = (n + 31) >> 5;
   // thread t owns the contiguous word range [t*K, (t+1)*K): one block scan for any n
@@ -1202,7 +1214,7 @@ __device__ void epilogue_body(const DexEpilogueBuffers& ep, const int n, const i
     if (lane >= o) incl += v;
   }
   if (lane == 31) s_warp[warp] = incl;
-  __syncthreads();
+  epilogue_sync<T, BAR>();
   if (warp == 0) {
     int v = (lane < NW) ? s_warp[lane] : 0;
 #pragma unroll
@@ -1213,7 +1225,7 @@ __device__ void epilogue_body(const DexEpilogueBuffers& ep, const int n, const i
     if (lane < NW) s_warp[lane] = v;
     if (lane == NW - 1) *s_base = v;
   }
-  __syncthreads();
+  epilogue_sync<T, BAR>();
   int pos = (warp > 0 ? s_warp[warp - 1] : 0) + incl - cnt;
   for (int w = w_begin; w < w_end; ++w) {
     const int i = w - w_begin;
@@ -1276,6 +1288,7 @@ __global__ void __launch_bounds__(kPostThreads, DICT ? 1 : 4) post_physics_kerne
   __shared__ int s_last;
   __shared__ float s_reset_u[32 * kPostWarps];
   __shared__ unsigned long long s_rng_step;
+  __shared__ unsigned s_rbits;
   const int tid = threadIdx.x, warp = tid >> 5;
   const int e0 = blockIdx.x * kTile;
   const int ne = min(kTile, A.n - e0);
@@ -1302,7 +1315,7 @@ __global__ void __launch_bounds__(kPostThreads, DICT ? 1 : 4) post_physics_kerne
   bool sr = false;
   unsigned ticket_old = 0;
   if (warp == 0) {
-    sr = post_scalar<BG>(A, smem, e0, ne, ticket_old);
+    sr = post_scalar<BG>(A, smem, e0, ne, ticket_old, &s_rbits);
   } else {  // meanwhile everything that is final after the items phase leaves through warps 1..7
     constexpr int NW = kPostWarps - 1;
     post_rows_f32<NW>(A, smem, e0, ne, 0, A.n_out_early, warp - 1);
@@ -1316,15 +1329,32 @@ __global__ void __launch_bounds__(kPostThreads, DICT ? 1 : 4) post_physics_kerne
   gather_rows_out<kPostWarps>(A.out.obs_buf, A.p.obs_dim, s_obs_map, smem, A.stride, e0, ne, A.obs_late, warp);
   if (DICT) gather_rows_out<kPostWarps>(A.out.obs_dict, A.dict_dim, s_dict_map, smem, A.stride, e0, ne, A.dict_late, warp);
   post_rows_typed(A, smem, e0, ne);
+  bool epi_warp = false;  // this warp runs the fused step epilogue
   if (full_mode) {
-    __syncthreads();  // the reward-term rows of the slab are complete
+    // the CTA that drew the last ticket (scalar phase; the value has long arrived): every other CTA has published
+    // its reset word and counters, so warps 4..7 of this CTA run the step epilogue NOW, next to the rest of the
+    // stage-out (warps 0..3), instead of after it
+    if (A.fused_epilogue && tid == 0) {
+      s_last = (ticket_old == gridDim.x - 1) ? 1 : 0;
+      if (s_last) __threadfence();  // acquire side of the release tickets of all other CTAs
+    }
+    __syncthreads();  // the reward-term rows of the slab are complete; s_last is visible
     if (warp == 0) post_total<BG>(A, smem, e0, ne);
+    epi_warp = A.fused_epilogue && s_last && warp >= kPostWarps / 2;
   }
-  post_rows_f32<kPostWarps>(A, smem, e0, ne, A.n_out_early, A.n_out_f32, warp);
+  if (epi_warp) {  // tid 0's fence + the barrier above order these (L2, ld.cg) reads
+    epilogue_body<kPostThreads / 2, 1>(A.ep, A.n, A.p.max_consecutive_successes, s_epi_warp, &s_epi_base,
+                                       tid - kPostThreads / 2);
+    if (tid == kPostThreads / 2) *A.ep.ticket = 0u;
+  } else if (full_mode && A.fused_epilogue && s_last) {
+    post_rows_f32<kPostWarps / 2>(A, smem, e0, ne, A.n_out_early, A.n_out_f32, warp);
+  } else {
+    post_rows_f32<kPostWarps>(A, smem, e0, ne, A.n_out_early, A.n_out_f32, warp);
+  }
   TL_MARK(4);
   if (any_reset && !(A.flags & DEX_FLAG_NO_FUSED_RESET)) {  // fused reset (dexhand_base.py:743-756), CTA-uniform branch
     __syncthreads();  // the OUT-table rows of the tile are written before the reset overwrites some of them
-    unsigned mask = __ldcg(A.out.reset_bits + (e0 >> 5));  // written by warp 0 before the vote barrier
+    unsigned mask = s_rbits;  // written by warp 0 before the vote barrier
     const uint64_t rng_step = s_rng_step;
     // warp w resets the (w)th, (w+8)th, ... finished env of the tile
     for (int k = 0; mask; ++k) {
@@ -1334,25 +1364,13 @@ __global__ void __launch_bounds__(kPostThreads, DICT ? 1 : 4) post_physics_kerne
     }
   }
   TL_MARK(5);
-  if (A.fused_epilogue) {
-    // the CTA that drew the last ticket: every other CTA has published its reset word and counters
-    if (tid == 0) {
-      s_last = (ticket_old == gridDim.x - 1) ? 1 : 0;
-      if (s_last) __threadfence();  // acquire side of the release tickets of all other CTAs
-    }
-    __syncthreads();
-    if (s_last) {  // tid 0's fence + the barrier above order these (L2, ld.cg) reads
-      epilogue_body<kPostThreads>(A.ep, A.n, A.p.max_consecutive_successes, s_epi_warp, &s_epi_base);
-      if (tid == 0) *A.ep.ticket = 0u;
-    }
-  }
   TL_MARK(6);
 }
 
 __global__ void __launch_bounds__(1024) epilogue_kernel(const DexEpilogueBuffers ep, const int n, const int max_consecutive) {
   __shared__ int s_warp[32];
   __shared__ int s_base;
-  epilogue_body<1024>(ep, n, max_consecutive, s_warp, &s_base);
+  epilogue_body<1024, 0>(ep, n, max_consecutive, s_warp, &s_base, threadIdx.x);
 }
 
 template <bool BG, bool DICT>

@@ -31,6 +31,7 @@ from dexrobot_isaac_b200.env import DexStepEnv  # noqa: E402
 from dexrobot_isaac_b200.params import BodyLayout  # noqa: E402
 
 dev = torch.device("cuda:0")
+torch.zeros(1, device=dev)
 lay = BodyLayout.default(with_box=task == "BlindGrasping")
 cfg = load_task_config(task, num_envs=n)
 gen = torch.Generator(device=dev).manual_seed(1)
