@@ -87,6 +87,8 @@ __global__ void __launch_bounds__(kPreThreads) pre_physics_kernel(const __grid_c
     s_d2a[tid] = P.dof_to_active[tid];
     s_scale[tid] = (tid < DEX_NUM_BASE) ? 1.0f : P.dof_coupling_scale[tid];
   }
+  pdl_wait();               // the previous kernel of the stream (post-physics of the last step) has completed
+  pdl_launch_dependents();  // the next kernel's CTAs may be scheduled as this grid drains
   // issue every global load of the tile first: the action rows (warp w: env rows w, w+8, ..; lane = column) ...
   constexpr int R = kPreTile / kPreWarps;
   const float* asrc = A.actions + ((size_t)e0 + warp) * NA + lane;
@@ -288,8 +290,9 @@ int dex_pre_physics(const DexParams* params, const DexStateBuffers* state, const
   if (n_envs <= 0) return DEX_ERR_SIZE;
   PreArgs a{*params, *state, actions, active_raw_targets, n_envs};
   const int grid = (n_envs + kPreTile - 1) / kPreTile;
-  pre_physics_kernel<<<grid, kPreThreads, 0, (cudaStream_t)stream>>>(a);
-  return launch_status();
+  const cudaError_t e = launch_step_kernel(pre_physics_kernel, grid, kPreThreads, 0, (cudaStream_t)stream, a);
+  if (e != cudaSuccess) (void)cudaGetLastError();
+  return e == cudaSuccess ? DEX_OK : (int)e;
 }
 
 static int check_epilogue(const DexEpilogueBuffers* ep) {

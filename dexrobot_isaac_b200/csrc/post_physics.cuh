@@ -1300,6 +1300,7 @@ __global__ void __launch_bounds__(kPostThreads, DICT ? 1 : 4) post_physics_kerne
     s_dict_map[tid + kPostThreads] = A.dict_src[tid + kPostThreads];
   }
   const bool full_tile = ne == kTile;  // CTA-uniform
+  pdl_wait();  // everything above touched only kernel parameters and shared memory
   if (full_tile)
     post_stage_in<BG, true>(A, smem, e0, ne);
   else
@@ -1308,6 +1309,7 @@ __global__ void __launch_bounds__(kPostThreads, DICT ? 1 : 4) post_physics_kerne
   // advance it - but by ONE thread and after the stage-in loads are in flight (it is an HBM miss of its own)
   if (tid == 64) s_rng_step = A.st.rng_step ? *A.st.rng_step : A.step;
   __syncthreads();
+  pdl_launch_dependents();
   TL_MARK(1);
   post_items<BG>(A, smem, ne);
   __syncthreads();
@@ -1385,8 +1387,8 @@ int launch_post_t(const PostArgs& a, cudaStream_t s) {
     configured = true;
   }
   const int grid = (a.n + kTile - 1) / kTile;
-  post_physics_kernel<BG, DICT><<<grid, kPostThreads, smem, s>>>(a);
-  const cudaError_t e = cudaGetLastError();
+  const cudaError_t e = launch_step_kernel(post_physics_kernel<BG, DICT>, grid, kPostThreads, smem, s, a);
+  if (e != cudaSuccess) (void)cudaGetLastError();
   return e == cudaSuccess ? DEX_OK : (int)e;
 }
 
