@@ -42,7 +42,7 @@ def needs_build() -> bool:
 def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not needs_build():
         return LIB_PATH
-    cmd = [find_nvcc()] + NVCC_FLAGS + ["-I", os.path.join(REPO_ROOT, "include")]
+    cmd = [find_nvcc()] + NVCC_FLAGS + os.environ.get("DEXSTEP_NVCC_FLAGS", "").split() + ["-I", os.path.join(REPO_ROOT, "include")]
     if verbose:
         cmd += ["-Xptxas", "-v"]
     cmd += SOURCES + ["-o", LIB_PATH]

@@ -324,7 +324,8 @@ int dex_post_physics(const DexParams* params, const DexSimViews* sim, const DexS
   if (fused) {
     rc = check_epilogue(epilogue);
     if (rc) return rc;
-    if (epilogue->ticket == nullptr || epilogue->reset_bits != out->reset_bits || epilogue->counters != out->counters)
+    if (epilogue->tile_records == nullptr || epilogue->rng_step == nullptr || epilogue->rng_step != state->rng_step ||
+        epilogue->reset_bits != out->reset_bits || epilogue->counters != out->counters)
       return DEX_ERR_NULL;
   }
   static thread_local PostArgs a;  // ~7 KB of launch arguments: keep it off the stack

@@ -382,6 +382,31 @@ inline int build_post_tables(PostArgs& a) {
   return ok ? DEX_OK : DEX_ERR_SIZE;
 }
 
+#ifdef DEXSTEP_TIMELINE  // debug build only (tools/timeline.py): per-CTA phase timestamps, [grid][32]:
+// [k] = globaltimer ns (256 ns ticks on B200) and [16 + k] = SM clock at mark k (k < 15), [15] = smid
+__device__ unsigned long long* g_timeline = nullptr;
+__device__ __forceinline__ void tl_mark(const int k) {
+  if (threadIdx.x == 0 && g_timeline != nullptr) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    g_timeline[(size_t)blockIdx.x * 32 + k] = t;
+    g_timeline[(size_t)blockIdx.x * 32 + 16 + k] = (unsigned long long)clock64();
+    if (k == 0) {
+      unsigned sm;
+      asm volatile("mov.u32 %0, %%smid;" : "=r"(sm));
+      g_timeline[(size_t)blockIdx.x * 32 + 15] = sm;
+    }
+  }
+}
+__device__ __forceinline__ void tl_mark_w1(const int k) {  // SM clock only, taken by warp 1 (first stage-out warp)
+  if (threadIdx.x == 32 && g_timeline != nullptr) g_timeline[(size_t)blockIdx.x * 32 + 16 + k] = (unsigned long long)clock64();
+}
+#define TL_MARK(k) tl_mark(k)
+#define TL_MARK_W1(k) tl_mark_w1(k)
+#else
+#define TL_MARK(k)
+#define TL_MARK_W1(k)
+#endif
 // ------------------------------------------------------------------------------------------------
 // phase 0: stage-in.  Plain LDG -> STS batches (all loads of a batch issued before the first store), no
 // cp.async: on sm_100a every 4-byte LDGSTS costs four issue slots, and this kernel is issue-bound.
@@ -662,7 +687,7 @@ __device__ __forceinline__ void post_items(const PostArgs& A, float* smem, const
 // ------------------------------------------------------------------------------------------------
 template <bool BG>
 __device__ __forceinline__ bool post_scalar(const PostArgs& A, float* smem, const int e0, const int ne,
-                                            unsigned& ticket_old, unsigned* s_rbits) {
+                                            const unsigned stamp, unsigned* s_rbits) {
   const DexParams& P = A.p;
   const int lane = threadIdx.x & 31;
   const bool active = lane < ne;
@@ -750,6 +775,7 @@ __device__ __forceinline__ bool post_scalar(const PostArgs& A, float* smem, cons
       if (stage == 3) prog = 1.0f;
       E[C_STAGEF] = (float)stage;
       E[C_PROG] = prog;
+      TL_MARK(7);
       min_tip_box = E[C_TIPBOX];
 #pragma unroll
       for (int f = 1; f < DEX_NUM_FINGERS; ++f) min_tip_box = fminf(min_tip_box, E[C_TIPBOX + f]);
@@ -808,6 +834,7 @@ __device__ __forceinline__ bool post_scalar(const PostArgs& A, float* smem, cons
     }
   }
 
+  TL_MARK(8);
   if (full) {
     // reset ballot word + cross-env counters (termination_manager.py:164-185,259-266)
     const unsigned fullmask = 0xffffffffu;
@@ -821,26 +848,43 @@ __device__ __forceinline__ bool post_scalar(const PostArgs& A, float* smem, cons
     unsigned bc[DEX_NUM_CRITERIA];
 #pragma unroll
     for (int c = 0; c < DEX_NUM_CRITERIA; ++c) bc[c] = __ballot_sync(fullmask, crit[c]);
-    if (lane == 0) {
-      if (bs) atomicAdd(A.out.counters + DEX_CNT_SUCCESS, __popc(bs));
-      if (bf) atomicAdd(A.out.counters + DEX_CNT_FAILURE, __popc(bf));
-      if (bt) atomicAdd(A.out.counters + DEX_CNT_TIMEOUT, __popc(bt));
-      if (rbits) atomicAdd(A.out.counters + DEX_CNT_RESET, __popc(rbits));
-#pragma unroll
-      for (int c = 0; c < DEX_NUM_CRITERIA; ++c)
-        if (bc[c]) atomicAdd(A.out.counters + DEX_CNT_CRIT0 + c, __popc(bc[c]));
-    }
+    int len = 0;
     if (rbits) {  // sum of the finished episodes' lengths (warp-uniform branch)
-      int len = should_reset ? ep_len_done : 0;
+      len = should_reset ? ep_len_done : 0;
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) len += __shfl_xor_sync(fullmask, len, o);
-      if (lane == 0) atomicAdd(A.out.counters + DEX_CNT_EPISODE_LENGTH, len);
     }
-    // Last-CTA-done ticket for the fused epilogue.  Everything the epilogue reads from this CTA (its reset
-    // word, its counter contributions) was written by THIS thread, so a release RMW orders it; taken here,
-    // early, its round trip overlaps the stage-out instead of sitting behind a full memory fence at the end.
-    if (A.fused_epilogue && lane == 0)
-      asm volatile("atom.add.release.gpu.u32 %0, [%1], 1;" : "=r"(ticket_old) : "l"(A.ep.ticket) : "memory");
+    TL_MARK(9);
+    if (lane == 0) {
+      if (A.fused_epilogue) {
+        // Fused epilogue: the tile PUBLISHES its reset word and its counter contributions as three self-validating
+        // 8-byte records (aligned 8-byte stores are single-copy atomic; bits 48..63 = stamp of this step).  The
+        // CTA of the last tile polls the stamps: no fence, no atomic, no contention on shared counters here.
+        //   rec0: [0,32) reset word | [32,38) #success | [38,44) #failure     (#timeout = popc(word) - both)
+        //   rec1: [0,36) six 6-bit criterion hit counts
+        //   rec2: [0,48) sum of the finished episodes' lengths
+        const unsigned long long st = (unsigned long long)stamp << 48;
+        unsigned long long r1 = 0;
+#pragma unroll
+        for (int c = 0; c < DEX_NUM_CRITERIA; ++c) r1 |= (unsigned long long)__popc(bc[c]) << (6 * c);
+        unsigned long long* rec = reinterpret_cast<unsigned long long*>(A.ep.tile_records) + 4 * (size_t)(e0 >> 5);
+        __stcg(rec + 0, st | rbits | ((unsigned long long)__popc(bs) << 32) | ((unsigned long long)__popc(bf) << 38));
+        __stcg(rec + 1, st | r1);
+        __stcg(rec + 2, st | (unsigned long long)(unsigned)len);
+      } else {
+#ifndef EXP_NO_COUNTERS
+        if (bs) atomicAdd(A.out.counters + DEX_CNT_SUCCESS, __popc(bs));
+        if (bf) atomicAdd(A.out.counters + DEX_CNT_FAILURE, __popc(bf));
+        if (bt) atomicAdd(A.out.counters + DEX_CNT_TIMEOUT, __popc(bt));
+        if (rbits) atomicAdd(A.out.counters + DEX_CNT_RESET, __popc(rbits));
+#pragma unroll
+        for (int c = 0; c < DEX_NUM_CRITERIA; ++c)
+          if (bc[c]) atomicAdd(A.out.counters + DEX_CNT_CRIT0 + c, __popc(bc[c]));
+        if (rbits) atomicAdd(A.out.counters + DEX_CNT_EPISODE_LENGTH, len);
+#endif
+      }
+    }
+    TL_MARK(10);
   }
   return should_reset;
 }
@@ -851,7 +895,7 @@ __device__ __forceinline__ bool post_scalar(const PostArgs& A, float* smem, cons
 // Writes the raw term and the weighted term into the component rows of the slab.
 // ------------------------------------------------------------------------------------------------
 template <bool BG>
-__device__ __forceinline__ void post_reward_terms(const PostArgs& A, float* smem, const int ne) {
+__device__ __forceinline__ void post_reward_terms(const PostArgs& A, float* smem, const int ne, const int nw) {
   const DexParams& P = A.p;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (lane >= ne) return;
@@ -859,7 +903,7 @@ __device__ __forceinline__ void post_reward_terms(const PostArgs& A, float* smem
   const float* rb = E + I_RB;
   float* comp = E + C_COMP;
   const int nterms = BG ? DEX_NUM_REWARD_TERMS : DEX_NUM_COMMON_TERMS;
-  for (int i = warp; i < nterms; i += kPostWarps) {
+  for (int i = warp; i < nterms; i += nw) {  // nw warps share the terms
     const float w = P.reward_weight[i];
     if (w == 0.0f) continue;  // reward_calculator.py:247-251: zero-weight terms are not materialised
     float r = 0.0f;
@@ -1041,6 +1085,9 @@ __device__ __forceinline__ void gather_rows_out(float* __restrict__ dst, const i
       float* d = d0 + 32 * c;
 #pragma unroll
       for (int i = 0; i < R; ++i) {
+#ifdef EXP_NO_OBS
+        if (v[i] == 123.456f)
+#endif
         if (w + NW * i < ne) *d = v[i];
         d += dstep;
       }
@@ -1063,17 +1110,21 @@ __device__ __forceinline__ void post_rows_f32(const PostArgs& A, const float* sm
       if (r0 + NW * u < r_end) v[u] = lds_f32(Eb + (unsigned)A.out_meta[r0 + NW * u] * 4u);
 #pragma unroll
     for (int u = 0; u < kRowU; ++u)
+#ifdef EXP_NO_ROWS
+      if (v[u] == 123.456f)
+#endif
       if (r0 + NW * u < r_end) *reinterpret_cast<float*>(A.out_ptr[r0 + NW * u] + colb) = v[u];
   }
 }
 
 // int64 / bool rows of the OUT table (counters, stage, masks)
-__device__ __forceinline__ void post_rows_typed(const PostArgs& A, const float* smem, const int e0, const int ne) {
+__device__ __forceinline__ void post_rows_typed(const PostArgs& A, const float* smem, const int e0, const int ne,
+                                                const int nw) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (lane >= ne) return;
   const unsigned Eb = (unsigned)__cvta_generic_to_shared(smem) + (unsigned)(lane * A.stride) * 4u;
   const size_t col = (size_t)e0 + lane;
-  for (int r = A.n_out_f32 + warp; r < A.n_out; r += kPostWarps) {
+  for (int r = A.n_out_f32 + warp; r < A.n_out; r += nw) {
     const float v = lds_f32(Eb + (unsigned)A.out_meta[r] * 4u);
     if (r < A.n_out_i64)
       reinterpret_cast<long long*>(A.out_ptr[r])[col] = (long long)__float_as_int(v);
@@ -1258,26 +1309,135 @@ __device__ void epilogue_body(const DexEpilogueBuffers& ep, const int n, const i
 }
 
 // ------------------------------------------------------------------------------------------------
-// the kernel
+// fused step epilogue over the tile records (see post_scalar): T threads of the LAST tile's CTA (named barrier
+// BAR) wait until every tile has published this step's stamp - tiles with a lower block index were scheduled
+// before this CTA, so they are running or done - then do the work of epilogue_body() without any counter array.
 // ------------------------------------------------------------------------------------------------
-#ifdef DEXSTEP_TIMELINE  // debug build only (tools/timeline.py): per-CTA phase timestamps, [grid][8] ns + smid
-__device__ unsigned long long* g_timeline = nullptr;
-__device__ __forceinline__ void tl_mark(const int k) {
-  if (threadIdx.x == 0 && g_timeline != nullptr) {
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    g_timeline[(size_t)blockIdx.x * 8 + k] = t;
-    if (k == 0) {
-      unsigned sm;
-      asm volatile("mov.u32 %0, %%smid;" : "=r"(sm));
-      g_timeline[(size_t)blockIdx.x * 8 + 7] = sm;
+template <int T, int BAR>
+__device__ void epilogue_records(const DexEpilogueBuffers& ep, const int n, const int max_consecutive, const unsigned stamp,
+                                 int* s_warp, int* s_base, int* s_cnt, const int tid) {
+  const int lane = tid & 31, warp = tid >> 5;
+  constexpr int NW = T / 32;
+  const int tiles = (n + 31) >> 5;
+  const int K = (tiles + T - 1) / T;  // thread t owns the contiguous tile range [t*K, (t+1)*K)
+  const int w_begin = min(tid * K, tiles), w_end = min(w_begin + K, tiles);
+  const volatile unsigned long long* rec = reinterpret_cast<const volatile unsigned long long*>(ep.tile_records);
+  // loads that do not depend on the other tiles: issued first
+  const bool has_tot = warp == 0 && lane <= DEX_NUM_COUNTERS && ep.totals != nullptr;
+  const long long tot0 = has_tot ? __ldcg(reinterpret_cast<const long long*>(ep.totals) + lane) : 0;
+  const bool l0 = tid == 0;
+  const int cs0 = l0 ? __ldcg(ep.consecutive_successes) : 0;
+  const unsigned long long rs0 = l0 ? __ldcg(reinterpret_cast<const unsigned long long*>(ep.rng_step)) : 0ull;
+  if (tid < DEX_NUM_COUNTERS) s_cnt[tid] = 0;
+  constexpr int kCache = 4;
+  unsigned cache[kCache] = {0u, 0u, 0u, 0u};
+  int cnt = 0, n_s = 0, n_f = 0, crit[DEX_NUM_CRITERIA];
+  long long len = 0;
+#pragma unroll
+  for (int c = 0; c < DEX_NUM_CRITERIA; ++c) crit[c] = 0;
+  for (int w0 = w_begin; w0 < w_end; w0 += kCache) {  // kCache tiles per round trip (volatile loads: L2 every time)
+    unsigned long long r0[kCache], r1[kCache], r2[kCache];
+    bool ok;
+    do {
+#pragma unroll
+      for (int j = 0; j < kCache; ++j) {
+        const size_t w = (size_t)min(w0 + j, w_end - 1);
+        r0[j] = rec[4 * w + 0];
+        r1[j] = rec[4 * w + 1];
+        r2[j] = rec[4 * w + 2];
+      }
+      ok = true;
+#pragma unroll
+      for (int j = 0; j < kCache; ++j)
+        ok = ok && (unsigned)(r0[j] >> 48) == stamp && (unsigned)(r1[j] >> 48) == stamp && (unsigned)(r2[j] >> 48) == stamp;
+    } while (!ok);
+#pragma unroll
+    for (int j = 0; j < kCache; ++j) {
+      if (w0 + j < w_end) {
+        const unsigned bits = (unsigned)r0[j];
+        if (w0 == w_begin) cache[j] = bits;
+        cnt += __popc(bits);
+        n_s += (int)((r0[j] >> 32) & 63u);
+        n_f += (int)((r0[j] >> 38) & 63u);
+#pragma unroll
+        for (int c = 0; c < DEX_NUM_CRITERIA; ++c) crit[c] += (int)((r1[j] >> (6 * c)) & 63u);
+        len += (long long)(r2[j] & 0xffffffffffffull);
+      }
+    }
+  }
+  // block scan of the reset counts
+  int incl = cnt;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int v = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += v;
+  }
+  if (lane == 31) s_warp[warp] = incl;
+  // counter totals: warp reduce, then one shared atomic per warp and counter
+  int red[4 + DEX_NUM_CRITERIA] = {n_s, n_f, cnt, (int)len};
+#pragma unroll
+  for (int c = 0; c < DEX_NUM_CRITERIA; ++c) red[4 + c] = crit[c];
+#pragma unroll
+  for (int k = 0; k < 4 + DEX_NUM_CRITERIA; ++k) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) red[k] += __shfl_xor_sync(0xffffffffu, red[k], o);
+  }
+  epilogue_sync<T, BAR>();  // s_cnt zeroed, s_warp written
+  if (lane == 0) {
+    atomicAdd(s_cnt + DEX_CNT_SUCCESS, red[0]);
+    atomicAdd(s_cnt + DEX_CNT_FAILURE, red[1]);
+    atomicAdd(s_cnt + DEX_CNT_RESET, red[2]);
+    atomicAdd(s_cnt + DEX_CNT_EPISODE_LENGTH, red[3]);
+#pragma unroll
+    for (int c = 0; c < DEX_NUM_CRITERIA; ++c) atomicAdd(s_cnt + DEX_CNT_CRIT0 + c, red[4 + c]);
+  }
+  if (warp == 0) {
+    int v = (lane < NW) ? s_warp[lane] : 0;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int u = __shfl_up_sync(0xffffffffu, v, o);
+      if (lane >= o) v += u;
+    }
+    if (lane < NW) s_warp[lane] = v;
+    if (lane == NW - 1) *s_base = v;
+  }
+  epilogue_sync<T, BAR>();
+  int pos = (warp > 0 ? s_warp[warp - 1] : 0) + incl - cnt;
+  for (int w = w_begin; w < w_end; ++w) {
+    const int i = w - w_begin;
+    unsigned bits = (i < kCache) ? (i == 0 ? cache[0] : i == 1 ? cache[1] : i == 2 ? cache[2] : cache[3])
+                                 : (unsigned)rec[4 * (size_t)w];
+    while (bits) {
+      const int b = __ffs(bits) - 1;
+      ep.env_ids[pos++] = w * 32 + b;
+      bits &= bits - 1;
+    }
+  }
+  if (warp == 0) {  // counters -> rates (termination_manager.py:259-266); lane k owns counter k
+    int c = (lane < DEX_NUM_COUNTERS) ? s_cnt[lane] : 0;
+    const int n_reset = __shfl_sync(0xffffffffu, c, DEX_CNT_RESET);
+    const int n_success = __shfl_sync(0xffffffffu, c, DEX_CNT_SUCCESS);
+    const int n_failure = __shfl_sync(0xffffffffu, c, DEX_CNT_FAILURE);
+    if (lane == DEX_CNT_TIMEOUT) c = n_reset - n_success - n_failure;  // the three classes partition the resets
+    const float fn = (float)n;
+    if (lane == DEX_CNT_SUCCESS) ep.stats[DEX_STAT_SUCCESS_RATE] = (float)c / fn;
+    if (lane == DEX_CNT_FAILURE) ep.stats[DEX_STAT_FAILURE_RATE] = (float)c / fn;
+    if (lane == DEX_CNT_TIMEOUT) ep.stats[DEX_STAT_TIMEOUT_RATE] = (float)c / fn;
+    if (lane >= DEX_CNT_CRIT0 && lane < DEX_CNT_CRIT0 + DEX_NUM_CRITERIA)
+      ep.stats[DEX_STAT_CRIT0 + (lane - DEX_CNT_CRIT0)] = (float)c / fn;
+    if (has_tot) ep.totals[lane] = tot0 + (lane < DEX_NUM_COUNTERS ? c : 1);  // [DEX_NUM_COUNTERS] counts steps
+    if (lane == 0) {
+      *ep.num_reset = *s_base;
+      const int cs = (n_success > 0) ? cs0 + 1 : 0;  // termination_manager.py:323-339
+      *ep.consecutive_successes = min(cs, max_consecutive);
+      *ep.rng_step = rs0 + 1;
     }
   }
 }
-#define TL_MARK(k) tl_mark(k)
-#else
-#define TL_MARK(k)
-#endif
+
+// ------------------------------------------------------------------------------------------------
+// the kernel
+// ------------------------------------------------------------------------------------------------
 template <bool BG, bool DICT>
 __global__ void __launch_bounds__(kPostThreads, DICT ? 1 : 4) post_physics_kernel(const __grid_constant__ PostArgs A) {
   extern __shared__ __align__(16) float smem[];
@@ -1285,7 +1445,7 @@ __global__ void __launch_bounds__(kPostThreads, DICT ? 1 : 4) post_physics_kerne
   __shared__ short s_dict_map[DICT ? kMaxDict : 1];
   __shared__ int s_epi_warp[kPostWarps];
   __shared__ int s_epi_base;
-  __shared__ int s_last;
+  __shared__ int s_epi_cnt[DEX_NUM_COUNTERS];
   __shared__ float s_reset_u[32 * kPostWarps];
   __shared__ unsigned long long s_rng_step;
   __shared__ unsigned s_rbits;
@@ -1305,8 +1465,9 @@ __global__ void __launch_bounds__(kPostThreads, DICT ? 1 : 4) post_physics_kerne
     post_stage_in<BG, true>(A, smem, e0, ne);
   else
     post_stage_in<BG, false>(A, smem, e0, ne);
-  // Philox step counter: read before this CTA takes its ticket (scalar phase), i.e. before the fused epilogue can
-  // advance it - but by ONE thread and after the stage-in loads are in flight (it is an HBM miss of its own)
+  // Philox step counter (also the stamp of this step's tile records): read before this CTA publishes its record
+  // (scalar phase), i.e. before the fused epilogue can advance it - by ONE thread and after the stage-in loads
+  // are in flight (it is an HBM miss of its own)
   if (tid == 64) s_rng_step = A.st.rng_step ? *A.st.rng_step : A.step;
   __syncthreads();
   pdl_launch_dependents();
@@ -1315,46 +1476,56 @@ __global__ void __launch_bounds__(kPostThreads, DICT ? 1 : 4) post_physics_kerne
   __syncthreads();
   TL_MARK(2);
   bool sr = false;
-  unsigned ticket_old = 0;
   if (warp == 0) {
-    sr = post_scalar<BG>(A, smem, e0, ne, ticket_old, &s_rbits);
+    sr = post_scalar<BG>(A, smem, e0, ne, ((unsigned)s_rng_step + 1u) & 0xffffu, &s_rbits);
   } else {  // meanwhile everything that is final after the items phase leaves through warps 1..7
     constexpr int NW = kPostWarps - 1;
+    TL_MARK_W1(11);
     post_rows_f32<NW>(A, smem, e0, ne, 0, A.n_out_early, warp - 1);
+    TL_MARK_W1(12);
     gather_rows_out<NW>(A.out.obs_buf, A.p.obs_dim, s_obs_map, smem, A.stride, e0, ne, ~A.obs_late, warp - 1);
+    TL_MARK_W1(13);
     if (DICT) gather_rows_out<NW>(A.out.obs_dict, A.dict_dim, s_dict_map, smem, A.stride, e0, ne, ~A.dict_late, warp - 1);
   }
   const int any_reset = __syncthreads_or(sr ? 1 : 0);
   TL_MARK(3);
   const bool full_mode = A.mode == DEX_MODE_FULL;
-  if (full_mode) post_reward_terms<BG>(A, smem, ne);
-  gather_rows_out<kPostWarps>(A.out.obs_buf, A.p.obs_dim, s_obs_map, smem, A.stride, e0, ne, A.obs_late, warp);
-  if (DICT) gather_rows_out<kPostWarps>(A.out.obs_dict, A.dict_dim, s_dict_map, smem, A.stride, e0, ne, A.dict_late, warp);
-  post_rows_typed(A, smem, e0, ne);
-  bool epi_warp = false;  // this warp runs the fused step epilogue
-  if (full_mode) {
-    // the CTA that drew the last ticket (scalar phase; the value has long arrived): every other CTA has published
-    // its reset word and counters, so warps 4..7 of this CTA run the step epilogue NOW, next to the rest of the
-    // stage-out (warps 0..3), instead of after it
-    if (A.fused_epilogue && tid == 0) {
-      s_last = (ticket_old == gridDim.x - 1) ? 1 : 0;
-      if (s_last) __threadfence();  // acquire side of the release tickets of all other CTAs
-    }
-    __syncthreads();  // the reward-term rows of the slab are complete; s_last is visible
+  // Fused step epilogue: warps 4..7 of the LAST tile's CTA leave the tile here - every tile publishes its record at
+  // the end of its scalar phase, i.e. about now - and the other four warps finish the tile on their own.
+#ifdef EXP_NO_EPILOGUE
+  const bool epi_cta = false;
+#else
+  const bool epi_cta = A.fused_epilogue && full_mode && blockIdx.x == gridDim.x - 1;  // CTA-uniform
+#endif
+  if (epi_cta && warp >= kPostWarps / 2) {
+    epilogue_records<kPostThreads / 2, 1>(A.ep, A.n, A.p.max_consecutive_successes, ((unsigned)s_rng_step + 1u) & 0xffffu,
+                                          s_epi_warp, &s_epi_base, s_epi_cnt, tid - kPostThreads / 2);
+  } else if (epi_cta) {
+    constexpr int NW = kPostWarps / 2;
+    post_reward_terms<BG>(A, smem, ne, NW);
+    gather_rows_out<NW>(A.out.obs_buf, A.p.obs_dim, s_obs_map, smem, A.stride, e0, ne, A.obs_late, warp);
+    if (DICT) gather_rows_out<NW>(A.out.obs_dict, A.dict_dim, s_dict_map, smem, A.stride, e0, ne, A.dict_late, warp);
+    post_rows_typed(A, smem, e0, ne, NW);
+    asm volatile("bar.sync 2, %0;" ::"n"(kPostThreads / 2) : "memory");  // the reward-term rows of the slab are complete
     if (warp == 0) post_total<BG>(A, smem, e0, ne);
-    epi_warp = A.fused_epilogue && s_last && warp >= kPostWarps / 2;
-  }
-  if (epi_warp) {  // tid 0's fence + the barrier above order these (L2, ld.cg) reads
-    epilogue_body<kPostThreads / 2, 1>(A.ep, A.n, A.p.max_consecutive_successes, s_epi_warp, &s_epi_base,
-                                       tid - kPostThreads / 2);
-    if (tid == kPostThreads / 2) *A.ep.ticket = 0u;
-  } else if (full_mode && A.fused_epilogue && s_last) {
-    post_rows_f32<kPostWarps / 2>(A, smem, e0, ne, A.n_out_early, A.n_out_f32, warp);
+    post_rows_f32<NW>(A, smem, e0, ne, A.n_out_early, A.n_out_f32, warp);
   } else {
+    if (full_mode) post_reward_terms<BG>(A, smem, ne, kPostWarps);
+    gather_rows_out<kPostWarps>(A.out.obs_buf, A.p.obs_dim, s_obs_map, smem, A.stride, e0, ne, A.obs_late, warp);
+    if (DICT) gather_rows_out<kPostWarps>(A.out.obs_dict, A.dict_dim, s_dict_map, smem, A.stride, e0, ne, A.dict_late, warp);
+    post_rows_typed(A, smem, e0, ne, kPostWarps);
+    if (full_mode) {
+      __syncthreads();  // the reward-term rows of the slab are complete
+      if (warp == 0) post_total<BG>(A, smem, e0, ne);
+    }
     post_rows_f32<kPostWarps>(A, smem, e0, ne, A.n_out_early, A.n_out_f32, warp);
   }
   TL_MARK(4);
+#ifdef EXP_NO_RESET
+  if (false) {
+#else
   if (any_reset && !(A.flags & DEX_FLAG_NO_FUSED_RESET)) {  // fused reset (dexhand_base.py:743-756), CTA-uniform branch
+#endif
     __syncthreads();  // the OUT-table rows of the tile are written before the reset overwrites some of them
     unsigned mask = s_rbits;  // written by warp 0 before the vote barrier
     const uint64_t rng_step = s_rng_step;

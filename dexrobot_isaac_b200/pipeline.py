@@ -110,13 +110,13 @@ class StepPipeline:
             setattr(self._out, name, _ptr(o.get(name)))
         e = self.epi = {"env_ids": z(n, dtype=torch.int32), "num_reset": z(1, dtype=torch.int32),
                         "stats": z(C["DEX_NUM_STATS"]), "consecutive_successes": z(1, dtype=torch.int32),
-                        "totals": z(C["DEX_NUM_COUNTERS"] + 1, dtype=i64), "ticket": z(1, dtype=torch.int32)}
+                        "totals": z(C["DEX_NUM_COUNTERS"] + 1, dtype=i64), "tile_records": z((n + 31) // 32, 4, dtype=i64)}
         self._epi = L.DexEpilogueBuffers()
         self._epi.reset_bits, self._epi.counters = _ptr(o["reset_bits"]), _ptr(o["counters"])
         self._epi.env_ids, self._epi.num_reset = _ptr(e["env_ids"]), _ptr(e["num_reset"])
         self._epi.stats, self._epi.consecutive_successes = _ptr(e["stats"]), _ptr(e["consecutive_successes"])
         self._epi.rng_step, self._epi.totals = _ptr(s["rng_step"]), _ptr(e["totals"])
-        self._epi.ticket = _ptr(e["ticket"])
+        self._epi.tile_records = _ptr(e["tile_records"])
         self.uniforms: Optional[torch.Tensor] = None  # [N,29] injected reset randoms (None = in-kernel Philox)
         self.launches = 0  # kernels launched through the C ABI (bench.py's gpu_launches)
 

@@ -59,7 +59,7 @@
 extern "C" {
 #endif
 
-#define DEX_ABI_VERSION 6
+#define DEX_ABI_VERSION 7
 
 #define DEX_NUM_DOF 26          /* constants.py:8-10: 6 base + 20 finger DOFs */
 #define DEX_NUM_BASE 6
@@ -295,8 +295,11 @@ typedef struct DexEpilogueBuffers {
   int64_t* totals;                /* [DEX_NUM_COUNTERS + 1] optional running totals since the caller last zeroed them:
                                      totals[k] += counters[k], totals[DEX_NUM_COUNTERS] += 1 (steps).  Together with
                                      DexOutBuffers.stat_totals this is the payload of the NCCL all-reduce */
-  uint32_t* ticket;               /* [1] zero-initialised by the caller; required only when the epilogue is fused into
-                                     dex_post_physics (last-CTA-done ticket; the library leaves it at zero) */
+  uint64_t* tile_records;         /* [ceil(N/32)][4] zero-initialised once by the caller; required only when the epilogue is
+                                     fused into dex_post_physics (and then rng_step is required too).  Every 32-env tile
+                                     publishes its reset ballot word and its counter contributions as three self-validating
+                                     8-byte records (top 16 bits = step stamp derived from *rng_step); the thread block of
+                                     the last tile polls them - no fence, no atomic, no counter contention on the step path */
 } DexEpilogueBuffers;
 
 const char* dex_strerror(int code);

@@ -43,7 +43,7 @@ for i in range(6):
     e.reset()
     envs.append((e, synthetic.random_actions(n, e.num_actions, gen, dev).contiguous()))
 grid = (n + 31) // 32
-tl = torch.zeros(grid, 8, dtype=torch.int64, device=dev)
+tl = torch.zeros(grid, 32, dtype=torch.int64, device=dev)
 for _ in range(3):
     for e, a in envs:
         e.pipeline.step(a)
@@ -67,6 +67,15 @@ for k, nm in enumerate(names):
 for k, nm in enumerate(["stage-in", "items", "scalar", "stage-out", "reset", "epilogue"]):
     print(f"phase {nm:10s} median {med(lambda t: float(((t[:, k + 1] - t[:, k]) / 1e3).median())):6.2f}  "
           f"max {med(lambda t: float(((t[:, k + 1] - t[:, k]) / 1e3).max())):6.2f}")
+# SM-clock deltas inside the scalar phase (marks 2 -> 7 FSM done -> 8 termination done -> 9 counters -> 10 ticket -> 3)
+seq = [2, 7, 8, 9, 10, 3]
+lab = ["task obs + FSM", "termination + masks", "ballots + counters", "len-sum + ticket", "barrier (wait for warps 1-7)"]
+for (a_, b_), nm in zip(zip(seq[:-1], seq[1:]), lab):
+    print(f"scalar: {nm:30s} median {med(lambda t: float((t[:, 16 + b_] - t[:, 16 + a_]).median())):8.0f} clk  "
+          f"max {med(lambda t: float((t[:, 16 + b_] - t[:, 16 + a_]).max())):8.0f} clk")
+for (a_, b_), nm in (((11, 12), "warp 1: early f32 rows"), ((12, 13), "warp 1: early obs chunks")):
+    print(f"early:  {nm:30s} median {med(lambda t: float((t[:, 16 + b_] - t[:, 16 + a_]).median())):8.0f} clk  "
+          f"max {med(lambda t: float((t[:, 16 + b_] - t[:, 16 + a_]).max())):8.0f} clk")
 # event-timed average of the (instrumentation-free path of the) same library: ring over the replicas
 e0_, e1_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 reps = 40
