@@ -15,6 +15,7 @@ HBM layout:
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Dict, Optional, Sequence
 
 import torch
@@ -27,6 +28,8 @@ MODE_FULL, MODE_OBS_ONLY = C["DEX_MODE_FULL"], C["DEX_MODE_OBS_ONLY"]
 FLAG_FIRST_REWARD_CALL = C["DEX_FLAG_FIRST_REWARD_CALL"]
 FLAG_STALE_CONTACTS = C["DEX_FLAG_STALE_CONTACTS"]
 FLAG_NO_FUSED_RESET = C["DEX_FLAG_NO_FUSED_RESET"]
+FLAG_EARLY_SIM_LOADS = C["DEX_FLAG_EARLY_SIM_LOADS"]
+_EARLY_SIM = os.environ.get("DEXSTEP_EARLY_SIM_LOADS", "1") != "0"  # A/B switch for StepPipeline.step()
 NUM_UNIFORMS = C["DEX_NUM_UNIFORMS"]
 
 
@@ -211,14 +214,16 @@ class StepPipeline:
         self.pre_physics(actions)
         if physics is not None:
             physics()
-        self.post_step()
+        # without a physics launch in between, the kernel ahead of post-physics is pre-physics, which does not touch
+        # the sim tensors: their rows may be loaded before the programmatic-launch wait (DEX_FLAG_EARLY_SIM_LOADS)
+        self.post_step(flags=FLAG_EARLY_SIM_LOADS if (physics is None and _EARLY_SIM) else 0)
 
-    def post_step(self, uniforms: Optional[torch.Tensor] = None):
+    def post_step(self, uniforms: Optional[torch.Tensor] = None, flags: int = 0):
         """post-physics + step epilogue: one launch when fuse_epilogue, else two."""
         if self.fuse_epilogue:
-            self.post_physics(uniforms=uniforms, fused_epilogue=True)
+            self.post_physics(uniforms=uniforms, fused_epilogue=True, flags=flags)
         else:
-            self.post_physics(uniforms=uniforms)
+            self.post_physics(uniforms=uniforms, flags=flags)
             self.epilogue()
 
     def capture_step_graph(self, actions: torch.Tensor, physics=None):

@@ -90,6 +90,11 @@ extern "C" {
 #define DEX_FLAG_STALE_CONTACTS 2u     /* read monitored contact forces from state.contact_forces instead of gathering
                                           (reset() computes its first obs pass without refresh_tensors, dexhand_base.py:813) */
 #define DEX_FLAG_NO_FUSED_RESET 4u     /* compute reset_buf but leave the reset to a later dex_reset_idx call */
+#define DEX_FLAG_EARLY_SIM_LOADS 8u    /* the kernel directly ahead in the stream does not write the four sim tensors (it is
+                                          dex_pre_physics of the same step, or any kernel that has completed): their rows are
+                                          loaded before the programmatic-launch wait, overlapping that kernel.  Never set it when
+                                          the previous launch is a dex_post_physics of the same envs (its fused reset writes
+                                          dof_state / actor_root_state) or a physics kernel that signals early */
 
 /* observation keys (obs_dict entries of the reference, observation_encoder.py:613-756,
  * step_processor.py:73, blind_grasping_task.py:569-652,702-746,895-899) */

@@ -300,3 +300,50 @@ def test_fused_epilogue_records(n):
     for k in ("success", "failure", "timeout", "reset"):
         assert int(T[C[f"DEX_CNT_{k.upper()}"]]) - base[k] == tot[k], k
     assert int(T[C["DEX_NUM_COUNTERS"]]) - base["steps"] == 4
+
+
+@pytest.mark.parametrize("task", ["BaseTask", "BlindGrasping"])
+def test_early_sim_loads_equal_plain(task):
+    """StepPipeline.step() without a physics launch sets DEX_FLAG_EARLY_SIM_LOADS (the sim rows are loaded before the
+    programmatic-launch wait, overlapping dex_pre_physics): eager and graph-replayed it must give exactly what the
+    separately launched pre-/post-physics calls give, with the sim state rewritten before every step."""
+    n, steps = 5000, 9
+    lay = synth.BodyLayout(with_box=task == "BlindGrasping")
+    e1, e2 = _env(task, n, materialize=False), _env(task, n, materialize=False)
+    world = synth.ScriptedWorld(n, lay, seed=21, nact=e1.num_actions)
+    u = world.uniforms(0).to(DEV)
+    st0 = world.state(0, e1.episode_step_count, None)
+    for e in (e1, e2):
+        e.load_state(st0)
+        e.reset(u)
+        e.pipeline.uniforms = u
+    act = torch.zeros(n, e2.num_actions, device=DEV)
+    g = None
+    for t in range(1, steps + 1):
+        st = world.state(t, e1.episode_step_count, None)
+        a = world.actions(t).to(DEV)
+        e1.load_state(st)
+        e1.pre_physics_step(a)
+        e1.post_physics_step()
+        e2.load_state(st)
+        act.copy_(a)
+        if t < 4:
+            e2.pipeline.step(act)
+        else:
+            if g is None:
+                saved = [{k: v.clone() for k, v in d.items() if v is not None}
+                         for d in (e2.pipeline.state, e2.pipeline.sim_tensors, e2.pipeline.out, e2.pipeline.epi)]
+                g = e2.pipeline.capture_step_graph(act)
+                for d, sv in zip((e2.pipeline.state, e2.pipeline.sim_tensors, e2.pipeline.out, e2.pipeline.epi), saved):
+                    for k, v in sv.items():
+                        d[k].copy_(v)
+            e2.pipeline.replay()
+        torch.cuda.synchronize()
+        for k in ("obs_buf", "rew_buf", "reset_buf", "reward_components", "success", "failure", "timeout"):
+            assert torch.equal(e1.pipeline.out[k], e2.pipeline.out[k]), f"step {t} {k}"
+        for k, v in e1.pipeline.state.items():
+            if k != "rng_step":
+                assert torch.equal(v, e2.pipeline.state[k]), f"step {t} state {k}"
+        for k, v in e1.pipeline.sim_tensors.items():
+            assert torch.equal(v, e2.pipeline.sim_tensors[k]), f"step {t} sim {k}"
+        assert torch.equal(e1.pipeline.env_ids(), e2.pipeline.env_ids())
