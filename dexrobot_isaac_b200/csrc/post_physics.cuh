@@ -1143,6 +1143,26 @@ __device__ __forceinline__ void post_rows_typed(const PostArgs& A, const float* 
   }
 }
 
+// Optional policy-input stage: obs_norm[env, k] = clamp((obs[k] - mean[k]) / den[k], -clip, clip), the
+// frozen-statistics form of rl_games' RunningMeanStd.forward (normalize_input, cfg/train/BaseTaskPPO.yaml:44), read from
+// the slab through the same column map as obs_buf.  lane = column, nw warps share the env rows; same operation
+// order as the torch expression (fp32 subtract, IEEE divide, clamp that lets NaN through like torch.clamp).
+__device__ __noinline__ void gather_rows_norm(float* __restrict__ dst, const float* __restrict__ mean,
+                                              const float* __restrict__ den, const float clip, const int W,
+                                              const short* s_map, const float* smem, const int S, const int e0,
+                                              const int ne, const int w, const int nw) {
+  const int lane = threadIdx.x & 31;
+  for (int k = lane; k < W; k += 32) {
+    const float m = __ldg(mean + k), d = __ldg(den + k);
+    const float* src = smem + s_map[k];
+    float* out = dst + (size_t)e0 * W + k;
+    for (int i = w; i < ne; i += nw) {
+      const float y = div_rn(src[i * S] - m, d);
+      out[(size_t)i * W] = (y != y) ? y : fminf(fmaxf(y, -clip), clip);
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------------
 // phase 4: fused reset of ONE finished env by ONE warp (ResetManager.reset_idx reset_manager.py:92-190,
 // BlindGraspingTask.reset_task_state blind_grasping_task.py:433-547, ActionProcessor.reset_targets
@@ -1518,6 +1538,9 @@ __global__ void __launch_bounds__(kPostThreads, DICT ? 1 : 4) post_physics_kerne
     asm volatile("bar.sync 2, %0;" ::"n"(kPostThreads / 2) : "memory");  // the reward-term rows of the slab are complete
     if (warp == 0) post_total<BG>(A, smem, e0, ne);
     post_rows_f32<NW>(A, smem, e0, ne, A.n_out_early, A.n_out_f32, warp);
+    if (A.out.obs_norm != nullptr)
+      gather_rows_norm(A.out.obs_norm, A.out.norm_mean, A.out.norm_den, A.out.norm_clip, A.p.obs_dim, s_obs_map, smem,
+                       A.stride, e0, ne, warp, NW);
   } else {
     if (full_mode) post_reward_terms<BG>(A, smem, ne, kPostWarps);
     gather_rows_out<kPostWarps>(A.out.obs_buf, A.p.obs_dim, s_obs_map, smem, A.stride, e0, ne, A.obs_late, warp);
@@ -1528,6 +1551,9 @@ __global__ void __launch_bounds__(kPostThreads, DICT ? 1 : 4) post_physics_kerne
       if (warp == 0) post_total<BG>(A, smem, e0, ne);
     }
     post_rows_f32<kPostWarps>(A, smem, e0, ne, A.n_out_early, A.n_out_f32, warp);
+    if (A.out.obs_norm != nullptr)
+      gather_rows_norm(A.out.obs_norm, A.out.norm_mean, A.out.norm_den, A.out.norm_clip, A.p.obs_dim, s_obs_map, smem,
+                       A.stride, e0, ne, warp, kPostWarps);
   }
   TL_MARK(4);
 #ifdef EXP_NO_RESET

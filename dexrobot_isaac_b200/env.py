@@ -125,6 +125,17 @@ class DexStepEnv:
             self.physics()
         return self.post_physics_step()
 
+    # ------------------------------------------------------------------ policy-input stage
+    def set_obs_normalization(self, running_mean, running_var=None, epsilon: float = 1e-5, clip: float = 5.0):
+        """Fuse rl_games' input normalisation (normalize_input, cfg/train/BaseTaskPPO.yaml:44) into the post-physics
+        pass: ``self.obs_norm`` then holds clamp((obs_buf - mean) / sqrt(var + epsilon), -clip, clip) after every
+        step, computed from the same on-chip copy of the observation as obs_buf.  See StepPipeline.set_obs_normalization."""
+        self.pipeline.set_obs_normalization(running_mean, running_var, epsilon, clip)
+
+    @property
+    def obs_norm(self) -> Optional[torch.Tensor]:
+        return self.pipeline.out.get("obs_norm")
+
     # ------------------------------------------------------------------ host-buffer entry (end-to-end path)
     def alloc_host_buffers(self):
         """Pinned host mirrors of one step's inputs (sim tensors + actions) and results (obs, rew, reset)."""

@@ -109,8 +109,9 @@ class StepPipeline:
             "stat_totals": z(4, 2 + rows, dtype=torch.float64) if observer else None,
         }
         self._out = L.DexOutBuffers()
-        for name, _ in L.DexOutBuffers._fields_:
-            setattr(self._out, name, _ptr(o.get(name)))
+        for name, ctype in L.DexOutBuffers._fields_:
+            if ctype is ctypes.c_void_p:
+                setattr(self._out, name, _ptr(o.get(name)))
         e = self.epi = {"env_ids": z(n, dtype=torch.int32), "num_reset": z(1, dtype=torch.int32),
                         "stats": z(C["DEX_NUM_STATS"]), "consecutive_successes": z(1, dtype=torch.int32),
                         "totals": z(C["DEX_NUM_COUNTERS"] + 1, dtype=i64), "tile_records": z((n + 31) // 32, 4, dtype=i64)}
@@ -122,6 +123,38 @@ class StepPipeline:
         self._epi.tile_records = _ptr(e["tile_records"])
         self.uniforms: Optional[torch.Tensor] = None  # [N,29] injected reset randoms (None = in-kernel Philox)
         self.launches = 0  # kernels launched through the C ABI (bench.py's gpu_launches)
+
+    # ------------------------------------------------------------------ policy-input stage
+    def set_obs_normalization(self, running_mean: Optional[torch.Tensor], running_var: Optional[torch.Tensor] = None,
+                              epsilon: float = 1e-5, clip: float = 5.0):
+        """Have dex_post_physics also write ``out["obs_norm"]``: the network input rl_games derives from obs_buf when
+        ``normalize_input`` is on (cfg/train/BaseTaskPPO.yaml:44), i.e. RunningMeanStd.forward with frozen statistics:
+        ``clamp((obs - running_mean.float()) / sqrt(running_var.float() + epsilon), -clip, clip)``.
+        ``running_mean`` / ``running_var`` are rl_games' float64 buffers [obs_dim]; call again whenever they change
+        (the values are copied into pipeline-owned buffers, so a captured graph stays valid).  ``None`` switches the
+        stage off - only before a graph is captured."""
+        o = self.out
+        if running_mean is None:
+            o["obs_norm"] = None
+            self._out.obs_norm = None
+            return
+        d = self.spec.obs_dim
+        if running_mean.numel() != d or running_var is None or running_var.numel() != d:
+            raise ValueError(f"running_mean / running_var must have obs_dim = {d} elements")
+        mean = running_mean.detach().to(self.device).float().reshape(d)
+        den = torch.sqrt(running_var.detach().to(self.device).float().reshape(d) + epsilon)
+        if o.get("obs_norm") is None:
+            o["obs_norm"] = torch.zeros(self.n, d, dtype=torch.float32, device=self.device)
+            o["norm_mean"], o["norm_den"] = mean.clone(), den.clone()
+            self._out.obs_norm, self._out.norm_mean = _ptr(o["obs_norm"]), _ptr(o["norm_mean"])
+            self._out.norm_den = _ptr(o["norm_den"])
+        else:
+            o["norm_mean"].copy_(mean)
+            o["norm_den"].copy_(den)
+        if self._out.norm_clip != float(clip):
+            if getattr(self, "_graph", None) is not None:
+                raise RuntimeError("norm_clip is a launch parameter: set it before capture_step_graph()")
+            self._out.norm_clip = float(clip)
 
     # ------------------------------------------------------------------ sim binding (zero-copy)
     def bind_sim(self, sim: Dict[str, torch.Tensor]):

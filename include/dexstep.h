@@ -59,7 +59,7 @@
 extern "C" {
 #endif
 
-#define DEX_ABI_VERSION 7
+#define DEX_ABI_VERSION 8
 
 #define DEX_NUM_DOF 26          /* constants.py:8-10: 6 base + 20 finger DOFs */
 #define DEX_NUM_BASE 6
@@ -287,6 +287,15 @@ typedef struct DexOutBuffers {
   double* stat_totals;            /* [4][2 + num_component_rows], classes {all, success, failure, timeout}:
                                      n_episodes, sum(episode_length), sum of each component's episode sum.
                                      This vector is the payload of the single NCCL all-reduce. */
+  /* Optional policy-input stage: the input normalisation rl_games applies to obs_buf before the
+   * network (cfg/train/BaseTaskPPO.yaml:44 normalize_input -> rl_games RunningMeanStd.forward with frozen statistics:
+   * y = clamp((obs - running_mean.float()) / sqrt(running_var.float() + epsilon), -5, 5)), written from the same
+   * shared-memory slab as obs_buf so the policy never re-reads obs_buf.  obs_norm == NULL = off.
+   * The running statistics themselves stay with the caller (they change only in training, from the raw obs_buf). */
+  float* obs_norm;                /* [N,obs_dim] normalised + clipped observations */
+  const float* norm_mean;         /* [obs_dim] running_mean.float() */
+  const float* norm_den;          /* [obs_dim] sqrt(running_var.float() + epsilon), computed by the caller in fp32 */
+  float norm_clip;                /* 5.0 in rl_games; +inf = no clipping */
 } DexOutBuffers;
 
 typedef struct DexEpilogueBuffers {

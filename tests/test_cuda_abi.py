@@ -347,3 +347,66 @@ def test_early_sim_loads_equal_plain(task):
         for k, v in e1.pipeline.sim_tensors.items():
             assert torch.equal(v, e2.pipeline.sim_tensors[k]), f"step {t} sim {k}"
         assert torch.equal(e1.pipeline.env_ids(), e2.pipeline.env_ids())
+
+
+@pytest.mark.parametrize("task", ["BaseTask", "BlindGrasping"])
+def test_fused_obs_normalization(task):
+    """DexOutBuffers.obs_norm == rl_games' RunningMeanStd.forward (frozen statistics) of obs_buf,
+    bit for bit (fp32 subtract, IEEE divide, clamp), eager and graph-replayed, with the statistics replaced mid-run
+    and obs_buf itself unchanged by the extra output."""
+    from oracle.policy_input import RunningMeanStd
+
+    n, steps = 4097, 8
+    lay = synth.BodyLayout(with_box=task == "BlindGrasping")
+    e1, e2 = _env(task, n, materialize=False), _env(task, n, materialize=False)
+    world = synth.ScriptedWorld(n, lay, seed=5, nact=e1.num_actions)
+    d = e2.pipeline.spec.obs_dim
+    g = torch.Generator().manual_seed(11)
+    rms = RunningMeanStd(d)
+    rms.running_mean = torch.randn(d, generator=g, dtype=torch.float64) * 0.3
+    rms.running_var = torch.rand(d, generator=g, dtype=torch.float64) ** 4 * 2.0  # some columns far below 1: clamp hits
+    e2.set_obs_normalization(rms.running_mean, rms.running_var, rms.epsilon, rms.clip)
+    u = world.uniforms(0).to(DEV)
+    st0 = world.state(0, e1.episode_step_count, None)
+    for e in (e1, e2):
+        e.load_state(st0)
+        e.reset(u)
+        e.pipeline.uniforms = u
+    act = torch.zeros(n, e2.num_actions, device=DEV)
+    captured = False
+    clamped = 0
+    for t in range(1, steps + 1):
+        st = world.state(t, e1.episode_step_count, None)
+        a = world.actions(t).to(DEV)
+        e1.load_state(st)
+        e1.pre_physics_step(a)
+        e1.post_physics_step()
+        e2.load_state(st)
+        act.copy_(a)
+        if t == 4:  # new statistics (a training-time update on the host): same buffers, so the graph below sees them
+            rms.training = True
+            rms.forward(e2.obs_buf.cpu())
+            rms.training = False
+            e2.set_obs_normalization(rms.running_mean, rms.running_var, rms.epsilon, rms.clip)
+        if t < 6:
+            e2.pipeline.step(act)
+        else:
+            if not captured:
+                dicts = (e2.pipeline.state, e2.pipeline.sim_tensors, e2.pipeline.out, e2.pipeline.epi)
+                saved = [{k: v.clone() for k, v in dd.items() if v is not None} for dd in dicts]
+                e2.pipeline.capture_step_graph(act)
+                for dd, sv in zip(dicts, saved):
+                    for k, v in sv.items():
+                        dd[k].copy_(v)
+                captured = True
+            e2.pipeline.replay()
+        torch.cuda.synchronize()
+        assert torch.equal(e1.obs_buf, e2.obs_buf), f"step {t}: obs_buf changed by the fused stage"
+        assert torch.equal(e1.rew_buf, e2.rew_buf)
+        want = rms.forward(e2.obs_buf.cpu())
+        got = e2.obs_norm.cpu()
+        assert torch.equal(got, want), f"step {t}: max diff {(got - want).abs().max()}"
+        clamped += int((want.abs() == rms.clip).sum())
+    assert clamped > 0  # the clip branch was exercised
+    with pytest.raises(ValueError):
+        e2.set_obs_normalization(torch.zeros(d + 1), torch.ones(d + 1))
