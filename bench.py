@@ -57,6 +57,7 @@ def parse_args():
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument("--envs", type=int, default=0, help="override envs per GPU")
     ap.add_argument("--observer", type=int, default=0, help="1 = fused RewardComponentObserver on (SURVEY §8f N1)")
+    ap.add_argument("--obs-norm", type=int, default=0, help="1 = fused policy-input normalisation on (SURVEY §8f N3)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--sweep", action="store_true", help="also print the post-physics num_envs sweep (configs[4])")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the bounded CPU-baseline sample")
@@ -156,7 +157,7 @@ def _clocks_from_nvidia_smi(index):
 class Ring:
     """R independent replicas of the workload (own sim tensors, path state, outputs, actions)."""
 
-    def __init__(self, task, n, device, seed, observer, min_bytes=2 * L2_BYTES, max_replicas=64):
+    def __init__(self, task, n, device, seed, observer, min_bytes=2 * L2_BYTES, max_replicas=64, obs_norm=False):
         from dexrobot_isaac_b200 import synthetic
         from dexrobot_isaac_b200.config import load_task_config
         from dexrobot_isaac_b200.env import DexStepEnv
@@ -172,6 +173,9 @@ class Ring:
             env = DexStepEnv(self.cfg, n, self.layout, synthetic.dof_props(), device=device, observer=bool(observer),
                              seed=seed + len(self.envs), sim=synthetic.random_state(n, self.layout, gen, device))
             env.pipeline.uniforms = None  # resets draw from the in-kernel Philox stream
+            if obs_norm:
+                d = env.pipeline.spec.obs_dim
+                env.set_obs_normalization(torch.zeros(d, dtype=torch.float64), torch.ones(d, dtype=torch.float64))
             env.reset()
             a = synthetic.random_actions(n, env.num_actions, gen, device).contiguous()
             for _ in range(2):
@@ -394,7 +398,7 @@ def main():
     from dexrobot_isaac_b200 import stats as dex_stats
 
     _lib.load()  # fails loudly when the CUDA library is missing
-    ring = Ring(task, n_env, device, 1234 + rank, args.observer)
+    ring = Ring(task, n_env, device, 1234 + rank, args.observer, obs_norm=bool(args.obs_norm))
     R = len(ring)
     group = R * max(1, -(-32 // R))
     if args.warmup > 0:
@@ -475,7 +479,7 @@ def main():
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": args.workload, "task": task, "envs_per_gpu": n_env, "envs_total": n_env * world,
                        "obs_dim": ring.envs[0].num_observations, "num_bodies": ring.layout.num_bodies,
-                       "observer": bool(args.observer), "l2": ring.l2_note, "graph_steps": group,
+                       "observer": bool(args.observer), "obs_norm": bool(args.obs_norm), "l2": ring.l2_note, "graph_steps": group,
                        "parallelism": f"env-sharded x{world}, no step-path collective, 1 NCCL all-reduce of stats"},
             "roofline": roofline, "e2e": e2e, "gpu_launches": launches_per_step * args.steps, "clocks": clocks,
             "kernels_us": {"pre_physics": pre_us, "post_physics": post_us, "epilogue": epi_us},

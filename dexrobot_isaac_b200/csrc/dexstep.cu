@@ -312,7 +312,7 @@ int dex_post_physics(const DexParams* params, const DexSimViews* sim, const DexS
   rc = check_state(params, state);
   if (rc) return rc;
   if (out == nullptr || out->obs_buf == nullptr) return DEX_ERR_NULL;
-  if (out->obs_norm != nullptr && (out->norm_mean == nullptr || out->norm_den == nullptr)) return DEX_ERR_NULL;
+  if (out->obs_norm != nullptr && (out->norm_mean == nullptr || out->norm_scale == nullptr)) return DEX_ERR_NULL;
   if (mode != DEX_MODE_FULL && mode != DEX_MODE_OBS_ONLY) return DEX_ERR_PARAM;
   if (mode == DEX_MODE_FULL &&
       (!out->rew_buf || !out->reset_buf || !out->success || !out->failure || !out->timeout || !out->reward_components ||

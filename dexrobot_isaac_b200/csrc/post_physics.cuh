@@ -1070,15 +1070,27 @@ __device__ __forceinline__ void post_total(const PostArgs& A, float* smem, const
 // rows of a [N, W] row-major buffer gathered from the slab through a column map (shared copy of the map):
 // lane = column (mod 32), so every global store is a full coalesced 128 B request.  Only the 32-column chunks
 // whose bit is set in `chunks` are written; the env rows are spread over NW warps, this warp is number `w`.
-template <int NW>
+// NORM: the optional policy-input stage rides on the same registers:
+//   norm.dst[env, k] = clamp((obs[k] - mean[k]) * scale[k], -clip, clip),  scale = 1 / sqrt(var + eps)
+// i.e. the frozen-statistics form of rl_games' RunningMeanStd.forward (normalize_input, cfg/train/BaseTaskPPO.yaml:44)
+// (fp32 subtract, multiply by the caller's fp32 reciprocal - within 2 ulp of the torch division -, clamp that lets
+// NaN through like torch.clamp).
+struct NormOut {
+  float* dst;
+  const float* mean;  // shared-memory copies of DexOutBuffers.norm_mean / norm_scale
+  const float* scale;
+  float clip;
+};
+template <int NW, bool NORM = false>
 __device__ __forceinline__ void gather_rows_out(float* __restrict__ dst, const int W, const short* s_map,
                                                 const float* smem, const int S, const int e0, const int ne,
-                                                unsigned chunks, const int w) {
+                                                unsigned chunks, const int w, const NormOut norm = NormOut{}) {
   const int lane = threadIdx.x & 31;
   constexpr int R = (kTile + NW - 1) / NW;  // env rows per warp
   const unsigned s0 = (unsigned)__cvta_generic_to_shared(smem) + (unsigned)(w * S) * 4u;
   const unsigned sstep = (unsigned)(NW * S) * 4u;
-  float* d0 = dst + ((size_t)e0 + w) * W + lane;
+  const size_t off0 = ((size_t)e0 + w) * W + lane;
+  float* d0 = dst + off0;
   const size_t dstep = (size_t)NW * W;
   const int nchunk = (W + 31) >> 5;
   if (nchunk < 32) chunks &= (1u << nchunk) - 1u;
@@ -1090,8 +1102,10 @@ __device__ __forceinline__ void gather_rows_out(float* __restrict__ dst, const i
       const unsigned a = s0 + (unsigned)s_map[k] * 4u;
       float v[R];
 #pragma unroll
-      for (int i = 0; i < R; ++i)
+      for (int i = 0; i < R; ++i) {
+        if (NORM) v[i] = 0.0f;
         if (w + NW * i < ne) v[i] = lds_f32(a + i * sstep);
+      }
       float* d = d0 + 32 * c;
 #pragma unroll
       for (int i = 0; i < R; ++i) {
@@ -1100,6 +1114,16 @@ __device__ __forceinline__ void gather_rows_out(float* __restrict__ dst, const i
 #endif
         if (w + NW * i < ne) *d = v[i];
         d += dstep;
+      }
+      if (NORM) {
+        const float m = norm.mean[k], sc = norm.scale[k];  // shared copies
+        float* d2 = norm.dst + off0 + 32 * c;
+#pragma unroll
+        for (int i = 0; i < R; ++i) {
+          const float y = (v[i] - m) * sc;
+          if (w + NW * i < ne) *d2 = (y != y) ? y : fminf(fmaxf(y, -norm.clip), norm.clip);
+          d2 += dstep;
+        }
       }
     }
   }
@@ -1140,26 +1164,6 @@ __device__ __forceinline__ void post_rows_typed(const PostArgs& A, const float* 
       reinterpret_cast<long long*>(A.out_ptr[r])[col] = (long long)__float_as_int(v);
     else
       reinterpret_cast<unsigned char*>(A.out_ptr[r])[col] = (v != 0.0f) ? 1 : 0;
-  }
-}
-
-// Optional policy-input stage: obs_norm[env, k] = clamp((obs[k] - mean[k]) / den[k], -clip, clip), the
-// frozen-statistics form of rl_games' RunningMeanStd.forward (normalize_input, cfg/train/BaseTaskPPO.yaml:44), read from
-// the slab through the same column map as obs_buf.  lane = column, nw warps share the env rows; same operation
-// order as the torch expression (fp32 subtract, IEEE divide, clamp that lets NaN through like torch.clamp).
-__device__ __noinline__ void gather_rows_norm(float* __restrict__ dst, const float* __restrict__ mean,
-                                              const float* __restrict__ den, const float clip, const int W,
-                                              const short* s_map, const float* smem, const int S, const int e0,
-                                              const int ne, const int w, const int nw) {
-  const int lane = threadIdx.x & 31;
-  for (int k = lane; k < W; k += 32) {
-    const float m = __ldg(mean + k), d = __ldg(den + k);
-    const float* src = smem + s_map[k];
-    float* out = dst + (size_t)e0 * W + k;
-    for (int i = w; i < ne; i += nw) {
-      const float y = div_rn(src[i * S] - m, d);
-      out[(size_t)i * W] = (y != y) ? y : fminf(fmaxf(y, -clip), clip);
-    }
   }
 }
 
@@ -1468,10 +1472,11 @@ __device__ void epilogue_records(const DexEpilogueBuffers& ep, const int n, cons
 // ------------------------------------------------------------------------------------------------
 // the kernel
 // ------------------------------------------------------------------------------------------------
-template <bool BG, bool DICT>
+template <bool BG, bool DICT, bool NORM>
 __global__ void __launch_bounds__(kPostThreads, DICT ? 1 : 4) post_physics_kernel(const __grid_constant__ PostArgs A) {
   extern __shared__ __align__(16) float smem[];
   __shared__ short s_obs_map[kMaxObs];
+  __shared__ float s_norm[NORM ? 2 * kMaxObs : 2];  // mean | denominator of the policy-input stage
   __shared__ short s_dict_map[DICT ? kMaxDict : 1];
   __shared__ int s_epi_warp[kPostWarps];
   __shared__ int s_epi_base;
@@ -1485,15 +1490,25 @@ __global__ void __launch_bounds__(kPostThreads, DICT ? 1 : 4) post_physics_kerne
 
   TL_MARK(0);
   s_obs_map[tid] = A.obs_src[tid];  // kMaxObs == kPostThreads
+  float nm = 0.0f, ns = 1.0f;  // NORM: issued here, parked in shared memory after the stage-in loads are in flight
+  if (NORM && tid < A.p.obs_dim) {  // written by the caller's copies, which precede dex_pre_physics in the stream
+    nm = __ldg(A.out.norm_mean + tid);
+    ns = __ldg(A.out.norm_scale + tid);
+  }
   if (DICT) {
     s_dict_map[tid] = A.dict_src[tid];
     s_dict_map[tid + kPostThreads] = A.dict_src[tid + kPostThreads];
   }
   const bool full_tile = ne == kTile;  // CTA-uniform
+  const NormOut norm{A.out.obs_norm, s_norm, s_norm + (NORM ? kMaxObs : 1), A.out.norm_clip};  // NORM instances only
   if (full_tile)
     post_stage_in<BG, true>(A, smem, e0, ne);
   else
     post_stage_in<BG, false>(A, smem, e0, ne);
+  if (NORM) {
+    s_norm[tid] = nm;
+    s_norm[kMaxObs + tid] = ns;
+  }
   // Philox step counter (also the stamp of this step's tile records): read before this CTA publishes its record
   // (scalar phase), i.e. before the fused epilogue can advance it - by ONE thread and after the stage-in loads
   // are in flight (it is an HBM miss of its own)
@@ -1512,7 +1527,7 @@ __global__ void __launch_bounds__(kPostThreads, DICT ? 1 : 4) post_physics_kerne
     TL_MARK_W1(11);
     post_rows_f32<NW>(A, smem, e0, ne, 0, A.n_out_early, warp - 1);
     TL_MARK_W1(12);
-    gather_rows_out<NW>(A.out.obs_buf, A.p.obs_dim, s_obs_map, smem, A.stride, e0, ne, ~A.obs_late, warp - 1);
+    gather_rows_out<NW, NORM>(A.out.obs_buf, A.p.obs_dim, s_obs_map, smem, A.stride, e0, ne, ~A.obs_late, warp - 1, norm);
     TL_MARK_W1(13);
     if (DICT) gather_rows_out<NW>(A.out.obs_dict, A.dict_dim, s_dict_map, smem, A.stride, e0, ne, ~A.dict_late, warp - 1);
   }
@@ -1532,18 +1547,15 @@ __global__ void __launch_bounds__(kPostThreads, DICT ? 1 : 4) post_physics_kerne
   } else if (epi_cta) {
     constexpr int NW = kPostWarps / 2;
     post_reward_terms<BG>(A, smem, ne, NW);
-    gather_rows_out<NW>(A.out.obs_buf, A.p.obs_dim, s_obs_map, smem, A.stride, e0, ne, A.obs_late, warp);
+    gather_rows_out<NW, NORM>(A.out.obs_buf, A.p.obs_dim, s_obs_map, smem, A.stride, e0, ne, A.obs_late, warp, norm);
     if (DICT) gather_rows_out<NW>(A.out.obs_dict, A.dict_dim, s_dict_map, smem, A.stride, e0, ne, A.dict_late, warp);
     post_rows_typed(A, smem, e0, ne, NW);
     asm volatile("bar.sync 2, %0;" ::"n"(kPostThreads / 2) : "memory");  // the reward-term rows of the slab are complete
     if (warp == 0) post_total<BG>(A, smem, e0, ne);
     post_rows_f32<NW>(A, smem, e0, ne, A.n_out_early, A.n_out_f32, warp);
-    if (A.out.obs_norm != nullptr)
-      gather_rows_norm(A.out.obs_norm, A.out.norm_mean, A.out.norm_den, A.out.norm_clip, A.p.obs_dim, s_obs_map, smem,
-                       A.stride, e0, ne, warp, NW);
   } else {
     if (full_mode) post_reward_terms<BG>(A, smem, ne, kPostWarps);
-    gather_rows_out<kPostWarps>(A.out.obs_buf, A.p.obs_dim, s_obs_map, smem, A.stride, e0, ne, A.obs_late, warp);
+    gather_rows_out<kPostWarps, NORM>(A.out.obs_buf, A.p.obs_dim, s_obs_map, smem, A.stride, e0, ne, A.obs_late, warp, norm);
     if (DICT) gather_rows_out<kPostWarps>(A.out.obs_dict, A.dict_dim, s_dict_map, smem, A.stride, e0, ne, A.dict_late, warp);
     post_rows_typed(A, smem, e0, ne, kPostWarps);
     if (full_mode) {
@@ -1551,9 +1563,6 @@ __global__ void __launch_bounds__(kPostThreads, DICT ? 1 : 4) post_physics_kerne
       if (warp == 0) post_total<BG>(A, smem, e0, ne);
     }
     post_rows_f32<kPostWarps>(A, smem, e0, ne, A.n_out_early, A.n_out_f32, warp);
-    if (A.out.obs_norm != nullptr)
-      gather_rows_norm(A.out.obs_norm, A.out.norm_mean, A.out.norm_den, A.out.norm_clip, A.p.obs_dim, s_obs_map, smem,
-                       A.stride, e0, ne, warp, kPostWarps);
   }
   TL_MARK(4);
 #ifdef EXP_NO_RESET
@@ -1581,19 +1590,19 @@ __global__ void __launch_bounds__(1024) epilogue_kernel(const DexEpilogueBuffers
   epilogue_body<1024, 0>(ep, n, max_consecutive, s_warp, &s_base, threadIdx.x);
 }
 
-template <bool BG, bool DICT>
+template <bool BG, bool DICT, bool NORM>
 int launch_post_t(const PostArgs& a, cudaStream_t s) {
   const size_t smem = (size_t)a.stride * kTile * sizeof(float);
   if (smem > 200 * 1024) return DEX_ERR_SIZE;
   static bool configured = false;  // per template instance
   if (!configured) {
-    const cudaError_t e = cudaFuncSetAttribute(post_physics_kernel<BG, DICT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    const cudaError_t e = cudaFuncSetAttribute(post_physics_kernel<BG, DICT, NORM>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                200 * 1024);
     if (e != cudaSuccess) return (int)e;
     configured = true;
   }
   const int grid = (a.n + kTile - 1) / kTile;
-  const cudaError_t e = launch_step_kernel(post_physics_kernel<BG, DICT>, grid, kPostThreads, smem, s, a);
+  const cudaError_t e = launch_step_kernel(post_physics_kernel<BG, DICT, NORM>, grid, kPostThreads, smem, s, a);
   if (e != cudaSuccess) (void)cudaGetLastError();
   return e == cudaSuccess ? DEX_OK : (int)e;
 }
@@ -1602,8 +1611,13 @@ inline int launch_post(PostArgs& a, cudaStream_t s) {
   const int rc = build_post_tables(a);
   if (rc) return rc;
   const bool bg = a.p.task == DEX_TASK_BLIND_GRASPING, dict = a.out.obs_dict != nullptr;
-  if (bg) return dict ? launch_post_t<true, true>(a, s) : launch_post_t<true, false>(a, s);
-  return dict ? launch_post_t<false, true>(a, s) : launch_post_t<false, false>(a, s);
+  const bool norm = a.out.obs_norm != nullptr;
+  if (norm) {
+    if (bg) return dict ? launch_post_t<true, true, true>(a, s) : launch_post_t<true, false, true>(a, s);
+    return dict ? launch_post_t<false, true, true>(a, s) : launch_post_t<false, false, true>(a, s);
+  }
+  if (bg) return dict ? launch_post_t<true, true, false>(a, s) : launch_post_t<true, false, false>(a, s);
+  return dict ? launch_post_t<false, true, false>(a, s) : launch_post_t<false, false, false>(a, s);
 }
 
 }  // namespace

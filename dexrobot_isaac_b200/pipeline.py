@@ -141,16 +141,18 @@ class StepPipeline:
         d = self.spec.obs_dim
         if running_mean.numel() != d or running_var is None or running_var.numel() != d:
             raise ValueError(f"running_mean / running_var must have obs_dim = {d} elements")
-        mean = running_mean.detach().to(self.device).float().reshape(d)
-        den = torch.sqrt(running_var.detach().to(self.device).float().reshape(d) + epsilon)
+        # same expressions as RunningMeanStd.forward, evaluated on the device the statistics live on (torch's CPU and
+        # CUDA sqrt differ in the last bit for some inputs), then moved
+        mean = running_mean.detach().float().reshape(d).to(self.device)
+        scale = (1.0 / torch.sqrt(running_var.detach().float().reshape(d) + epsilon)).to(self.device)
         if o.get("obs_norm") is None:
             o["obs_norm"] = torch.zeros(self.n, d, dtype=torch.float32, device=self.device)
-            o["norm_mean"], o["norm_den"] = mean.clone(), den.clone()
+            o["norm_mean"], o["norm_scale"] = mean.clone(), scale.clone()
             self._out.obs_norm, self._out.norm_mean = _ptr(o["obs_norm"]), _ptr(o["norm_mean"])
-            self._out.norm_den = _ptr(o["norm_den"])
+            self._out.norm_scale = _ptr(o["norm_scale"])
         else:
             o["norm_mean"].copy_(mean)
-            o["norm_den"].copy_(den)
+            o["norm_scale"].copy_(scale)
         if self._out.norm_clip != float(clip):
             if getattr(self, "_graph", None) is not None:
                 raise RuntimeError("norm_clip is a launch parameter: set it before capture_step_graph()")

@@ -290,11 +290,12 @@ typedef struct DexOutBuffers {
   /* Optional policy-input stage: the input normalisation rl_games applies to obs_buf before the
    * network (cfg/train/BaseTaskPPO.yaml:44 normalize_input -> rl_games RunningMeanStd.forward with frozen statistics:
    * y = clamp((obs - running_mean.float()) / sqrt(running_var.float() + epsilon), -5, 5)), written from the same
-   * shared-memory slab as obs_buf so the policy never re-reads obs_buf.  obs_norm == NULL = off.
+   * shared-memory slab as obs_buf so the policy never re-reads obs_buf.  obs_norm == NULL = off.  The division is a
+   * multiplication by the caller's fp32 reciprocal: within 2 ulp of the torch expression (tests: rtol 1e-6).
    * The running statistics themselves stay with the caller (they change only in training, from the raw obs_buf). */
   float* obs_norm;                /* [N,obs_dim] normalised + clipped observations */
   const float* norm_mean;         /* [obs_dim] running_mean.float() */
-  const float* norm_den;          /* [obs_dim] sqrt(running_var.float() + epsilon), computed by the caller in fp32 */
+  const float* norm_scale;        /* [obs_dim] 1 / sqrt(running_var.float() + epsilon), computed by the caller in fp32 */
   float norm_clip;                /* 5.0 in rl_games; +inf = no clipping */
 } DexOutBuffers;
 

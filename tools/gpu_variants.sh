@@ -1,9 +1,9 @@
 #!/bin/bash
 # usage: tools/gpu_variants.sh "FLAGS1" "FLAGS2" ...   -> rebuilds libdexstep.so on the GPU box with each set of extra
-# nvcc flags (experiment macros) and prints the bench kernel times; the default build is restored locally afterwards.
+# nvcc flags (experiment macros; extra bench.py arguments in $BENCH_ARGS) and prints the bench kernel times; the default build is restored locally afterwards.
 CMD=""
 for F in "$@"; do
-CMD="$CMD echo \"== [$F]\"; DEXSTEP_NVCC_FLAGS=\"$F\" python -m dexrobot_isaac_b200.build --force > /dev/null && timeout 300 python bench.py --steps 1500 --warmup 100 --no-cpu-baseline 2>&1 | tail -1 | python -c \"
+CMD="$CMD echo \"== [$F]\"; DEXSTEP_NVCC_FLAGS=\"$F\" python -m dexrobot_isaac_b200.build --force > /dev/null && timeout 300 python bench.py --steps 1500 --warmup 100 --no-cpu-baseline $BENCH_ARGS 2>&1 | tail -1 | python -c \"
 import sys, json
 for l in sys.stdin:
     if l.startswith('{'):
