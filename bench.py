@@ -57,6 +57,7 @@ def parse_args():
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument("--envs", type=int, default=0, help="override envs per GPU")
     ap.add_argument("--observer", type=int, default=0, help="1 = fused RewardComponentObserver on (SURVEY §8f N1)")
+    ap.add_argument("--nb-hand", type=int, default=31, help="hand bodies per env (31 = survey layout; 37 = sensitivity line)")
     ap.add_argument("--obs-norm", type=int, default=0, help="1 = fused policy-input normalisation on (SURVEY §8f N3)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--sweep", action="store_true", help="also print the post-physics num_envs sweep (configs[4])")
@@ -157,14 +158,15 @@ def _clocks_from_nvidia_smi(index):
 class Ring:
     """R independent replicas of the workload (own sim tensors, path state, outputs, actions)."""
 
-    def __init__(self, task, n, device, seed, observer, min_bytes=2 * L2_BYTES, max_replicas=64, obs_norm=False):
+    def __init__(self, task, n, device, seed, observer, min_bytes=2 * L2_BYTES, max_replicas=64, obs_norm=False,
+                 nb_hand=31):
         from dexrobot_isaac_b200 import synthetic
         from dexrobot_isaac_b200.config import load_task_config
         from dexrobot_isaac_b200.env import DexStepEnv
         from dexrobot_isaac_b200.params import BodyLayout
 
         self.task, self.n, self.device = task, n, device
-        self.layout = BodyLayout.default(with_box=task == "BlindGrasping")
+        self.layout = BodyLayout.default(with_box=task == "BlindGrasping", nb_hand=nb_hand)
         self.cfg = load_task_config(task, num_envs=n)
         gen = torch.Generator(device=device).manual_seed(seed)
         self.envs, self.actions = [], []
@@ -398,7 +400,7 @@ def main():
     from dexrobot_isaac_b200 import stats as dex_stats
 
     _lib.load()  # fails loudly when the CUDA library is missing
-    ring = Ring(task, n_env, device, 1234 + rank, args.observer, obs_norm=bool(args.obs_norm))
+    ring = Ring(task, n_env, device, 1234 + rank, args.observer, obs_norm=bool(args.obs_norm), nb_hand=args.nb_hand)
     R = len(ring)
     group = R * max(1, -(-32 // R))
     if args.warmup > 0:
