@@ -1489,6 +1489,32 @@ __global__ void __launch_bounds__(kPostThreads, DICT ? 1 : 4) post_physics_kerne
   const int ne = min(kTile, A.n - e0);
 
   TL_MARK(0);
+  // Fused step epilogue: the launch carries ONE extra CTA behind the tiles (launch_post_t).  It owns no tile: it polls
+  // the tile records - every tile publishes its own at the end of its scalar phase - and finishes the step
+  // (env_ids, rates, running totals, stamp counter) while the tiles are still staging out.  Tiles have lower block
+  // indices, so they were scheduled before this CTA: the wait cannot deadlock.
+  if (ne <= 0) {
+    pdl_wait();
+    pdl_launch_dependents();
+    if (tid == 0) {
+      // one thread waits for the record of the LAST tile (scheduled last, so among the last to publish) before the
+      // CTA starts the full poll: 256 threads polling from the start of the launch would load the LSU of an SM
+      // that also runs tiles
+      const unsigned long long rs = *A.st.rng_step;
+      const unsigned stamp = ((unsigned)rs + 1u) & 0xffffu;
+      const volatile unsigned long long* last =
+          reinterpret_cast<const volatile unsigned long long*>(A.ep.tile_records) + 4 * (size_t)(blockIdx.x - 1);
+      while ((unsigned)(last[0] >> 48) != stamp) {
+      }
+      s_rng_step = rs;
+    }
+    __syncthreads();
+    epilogue_records<kPostThreads, 0>(A.ep, A.n, A.p.max_consecutive_successes, ((unsigned)s_rng_step + 1u) & 0xffffu,
+                                      s_epi_warp, &s_epi_base, s_epi_cnt, tid);
+    TL_MARK(5);
+    TL_MARK(6);
+    return;
+  }
   s_obs_map[tid] = A.obs_src[tid];  // kMaxObs == kPostThreads
   float nm = 0.0f, ns = 1.0f;  // NORM: issued here, parked in shared memory after the stage-in loads are in flight
   if (NORM && tid < A.p.obs_dim) {  // written by the caller's copies, which precede dex_pre_physics in the stream
@@ -1534,26 +1560,7 @@ __global__ void __launch_bounds__(kPostThreads, DICT ? 1 : 4) post_physics_kerne
   const int any_reset = __syncthreads_or(sr ? 1 : 0);
   TL_MARK(3);
   const bool full_mode = A.mode == DEX_MODE_FULL;
-  // Fused step epilogue: warps 4..7 of the LAST tile's CTA leave the tile here - every tile publishes its record at
-  // the end of its scalar phase, i.e. about now - and the other four warps finish the tile on their own.
-#ifdef EXP_NO_EPILOGUE
-  const bool epi_cta = false;
-#else
-  const bool epi_cta = A.fused_epilogue && full_mode && blockIdx.x == gridDim.x - 1;  // CTA-uniform
-#endif
-  if (epi_cta && warp >= kPostWarps / 2) {
-    epilogue_records<kPostThreads / 2, 1>(A.ep, A.n, A.p.max_consecutive_successes, ((unsigned)s_rng_step + 1u) & 0xffffu,
-                                          s_epi_warp, &s_epi_base, s_epi_cnt, tid - kPostThreads / 2);
-  } else if (epi_cta) {
-    constexpr int NW = kPostWarps / 2;
-    post_reward_terms<BG>(A, smem, ne, NW);
-    gather_rows_out<NW, NORM>(A.out.obs_buf, A.p.obs_dim, s_obs_map, smem, A.stride, e0, ne, A.obs_late, warp, norm);
-    if (DICT) gather_rows_out<NW>(A.out.obs_dict, A.dict_dim, s_dict_map, smem, A.stride, e0, ne, A.dict_late, warp);
-    post_rows_typed(A, smem, e0, ne, NW);
-    asm volatile("bar.sync 2, %0;" ::"n"(kPostThreads / 2) : "memory");  // the reward-term rows of the slab are complete
-    if (warp == 0) post_total<BG>(A, smem, e0, ne);
-    post_rows_f32<NW>(A, smem, e0, ne, A.n_out_early, A.n_out_f32, warp);
-  } else {
+  {
     if (full_mode) post_reward_terms<BG>(A, smem, ne, kPostWarps);
     gather_rows_out<kPostWarps, NORM>(A.out.obs_buf, A.p.obs_dim, s_obs_map, smem, A.stride, e0, ne, A.obs_late, warp, norm);
     if (DICT) gather_rows_out<kPostWarps>(A.out.obs_dict, A.dict_dim, s_dict_map, smem, A.stride, e0, ne, A.dict_late, warp);
@@ -1601,7 +1608,7 @@ int launch_post_t(const PostArgs& a, cudaStream_t s) {
     if (e != cudaSuccess) return (int)e;
     configured = true;
   }
-  const int grid = (a.n + kTile - 1) / kTile;
+  const int grid = (a.n + kTile - 1) / kTile + ((a.fused_epilogue && a.mode == DEX_MODE_FULL) ? 1 : 0);  // + epilogue CTA
   const cudaError_t e = launch_step_kernel(post_physics_kernel<BG, DICT, NORM>, grid, kPostThreads, smem, s, a);
   if (e != cudaSuccess) (void)cudaGetLastError();
   return e == cudaSuccess ? DEX_OK : (int)e;

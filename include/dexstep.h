@@ -313,8 +313,8 @@ typedef struct DexEpilogueBuffers {
   uint64_t* tile_records;         /* [ceil(N/32)][4] zero-initialised once by the caller; required only when the epilogue is
                                      fused into dex_post_physics (and then rng_step is required too).  Every 32-env tile
                                      publishes its reset ballot word and its counter contributions as three self-validating
-                                     8-byte records (top 16 bits = step stamp derived from *rng_step); the thread block of
-                                     the last tile polls them - no fence, no atomic, no counter contention on the step path */
+                                     8-byte records (top 16 bits = step stamp derived from *rng_step); one extra thread block
+                                     behind the tiles polls them - no fence, no atomic, no counter contention on the step path */
 } DexEpilogueBuffers;
 
 const char* dex_strerror(int code);
@@ -330,7 +330,7 @@ int dex_pre_physics(const DexParams* params, const DexStateBuffers* state, const
 /* Post-physics: one pass per env over the sim buffers; see header comment.  `uniforms` [N,29]
  * (row-major) are the reset randoms in [0,1); if NULL they are generated in-kernel (Philox4x32-10
  * keyed by (seed, step_index, env)).  `epilogue` (may be NULL): when given and mode == DEX_MODE_FULL,
- * the work of dex_step_epilogue is done by the last thread block of the same launch (no second
+ * the work of dex_step_epilogue is done by one extra thread block of the same launch (no second
  * kernel); the caller must then NOT call dex_step_epilogue for this step. */
 int dex_post_physics(const DexParams* params, const DexSimViews* sim, const DexStateBuffers* state,
                      const DexOutBuffers* out, const DexEpilogueBuffers* epilogue, int32_t n_envs, int32_t mode,

@@ -43,22 +43,25 @@ for i in range(6):
     e.reset()
     envs.append((e, synthetic.random_actions(n, e.num_actions, gen, dev).contiguous()))
 grid = (n + 31) // 32
-tl = torch.zeros(grid, 32, dtype=torch.int64, device=dev)
+tl = torch.zeros(grid + 1, 32, dtype=torch.int64, device=dev)  # + the epilogue CTA (marks 0 and 6 only)
 for _ in range(3):
     for e, a in envs:
         e.pipeline.step(a)
 torch.cuda.synchronize()
 assert lib.dex_debug_set_timeline(tl.data_ptr()) == 0
-runs = []
+runs, epi_end = [], []
 for e, a in envs:  # one L2-cold launch per replica (6 x ~63 MB > L2)
     tl.zero_()
     e.pipeline.post_step()
     torch.cuda.synchronize()
-    runs.append(tl.cpu().double())
+    full = tl.cpu().double()
+    epi_end.append(float(full[grid, 6] - full[:grid, 0].min()) / 1e3)
+    runs.append(full[:grid])
 assert lib.dex_debug_set_timeline(None) == 0
 names = ["start", "stage-in done", "items done", "scalar done", "stage-out done", "reset done", "end"]
 print(f"envs {n} task {task} grid {grid}; times in us relative to the first CTA start; median over {len(runs)} launches")
 import statistics as st_
+print(f"epilogue CTA end   median {st_.median(epi_end):7.2f}")
 def med(f):
     return st_.median(f(t) for t in runs)
 for k, nm in enumerate(names):
