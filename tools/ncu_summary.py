@@ -62,14 +62,16 @@ def launches(path):
         elif r["Metric Unit"] in ("ms", "msecond"):
             v *= 1e3
         name = r["Kernel Name"][:100]
-        a = agg.setdefault(name, [0, 0.0, r["Grid Size"], r["Block Size"]])
+        a = agg.setdefault(name, [0, 0.0, {}, r["Block Size"]])
         a[0] += 1
         a[1] += v
+        a[2][r["Grid Size"]] = a[2].get(r["Grid Size"], 0) + 1
     tot = sum(a[1] for a in agg.values())
     print(f"# {len(rows)} launches captured, total {tot:.1f} us (ncu: cold-cache, serialised -> compare shares)")
     print(f"{'launches':>8s} {'total_us':>10s} {'avg_us':>9s} {'share':>6s}  grid / block  kernel")
     for name, a in sorted(agg.items(), key=lambda kv: -kv[1][1]):
-        print(f"{a[0]:8d} {a[1]:10.1f} {a[1] / a[0]:9.2f} {100 * a[1] / tot:5.1f}%  {a[2]} / {a[3]}  {name}")
+        grid = max(a[2].items(), key=lambda kv: kv[1])[0]  # the most frequent grid of this kernel
+        print(f"{a[0]:8d} {a[1]:10.1f} {a[1] / a[0]:9.2f} {100 * a[1] / tot:5.1f}%  {grid} / {a[3]}  {name}")
 
 
 if __name__ == "__main__":
