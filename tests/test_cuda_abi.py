@@ -349,8 +349,8 @@ def test_early_sim_loads_equal_plain(task):
         assert torch.equal(e1.pipeline.env_ids(), e2.pipeline.env_ids())
 
 
-@pytest.mark.parametrize("task", ["BaseTask", "BlindGrasping"])
-def test_fused_obs_normalization(task):
+@pytest.mark.parametrize("task,materialize", [("BaseTask", False), ("BlindGrasping", False), ("BlindGrasping", True)])
+def test_fused_obs_normalization(task, materialize):
     """DexOutBuffers.obs_norm == rl_games' RunningMeanStd.forward (frozen statistics) of obs_buf,
     to rtol 1e-6 (fp32 subtract, reciprocal multiply, clamp), eager and graph-replayed, with the statistics replaced mid-run
     and obs_buf itself unchanged by the extra output."""
@@ -358,7 +358,7 @@ def test_fused_obs_normalization(task):
 
     n, steps = 4097, 8
     lay = synth.BodyLayout(with_box=task == "BlindGrasping")
-    e1, e2 = _env(task, n, materialize=False), _env(task, n, materialize=False)
+    e1, e2 = _env(task, n, materialize=materialize), _env(task, n, materialize=materialize)
     world = synth.ScriptedWorld(n, lay, seed=5, nact=e1.num_actions)
     d = e2.pipeline.spec.obs_dim
     g = torch.Generator().manual_seed(11)
@@ -403,6 +403,8 @@ def test_fused_obs_normalization(task):
         torch.cuda.synchronize()
         assert torch.equal(e1.obs_buf, e2.obs_buf), f"step {t}: obs_buf changed by the fused stage"
         assert torch.equal(e1.rew_buf, e2.rew_buf)
+        if materialize:  # the privileged-observation instance of the kernel carries the stage too
+            assert torch.equal(e1.pipeline.out["obs_dict"], e2.pipeline.out["obs_dict"])
         want = rms.forward(e2.obs_buf.cpu())
         got = e2.obs_norm.cpu()
         # fp32: the kernel multiplies by the reciprocal of sqrt(var + eps) instead of dividing (<= 2 ulp)
