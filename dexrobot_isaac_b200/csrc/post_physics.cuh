@@ -385,6 +385,45 @@ inline int build_post_tables(PostArgs& a) {
 #ifdef DEXSTEP_TIMELINE  // debug build only (tools/timeline.py): per-CTA phase timestamps, [grid][32]:
 // [k] = globaltimer ns (256 ns ticks on B200) and [16 + k] = SM clock at mark k (k < 15), [15] = smid
 __device__ unsigned long long* g_timeline = nullptr;
+#ifdef DEXSTEP_TIMELINE_LIGHT
+// light marks: one CS2R + one shared store per mark (the heavy marks below put an L2 round trip - the load of
+// g_timeline - and two global stores on the critical path of warp 0, ~0.3 us each); dumped once at the end:
+// [16 + k] = 32-bit SM clock at mark k, [0] / [6] = globaltimer at the start / end of the CTA, [15] = smid
+__device__ __forceinline__ unsigned* tl_buf() {
+  __shared__ unsigned s_tl[20];  // [0..14] clocks, [16..17] globaltimer at mark 0
+  return s_tl;
+}
+__device__ __forceinline__ void tl_mark(const int k) {
+  if (threadIdx.x == 0) {
+    unsigned* b = tl_buf();
+    b[k] = (unsigned)clock();
+    if (k == 0) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+      b[16] = (unsigned)t;
+      b[17] = (unsigned)(t >> 32);
+    }
+    if (k == 6) {
+      unsigned long long* g = g_timeline;
+      if (g != nullptr) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        unsigned sm;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(sm));
+        g += (size_t)blockIdx.x * 32;
+        g[0] = ((unsigned long long)b[17] << 32) | b[16];
+        g[6] = t;
+        g[15] = sm;
+#pragma unroll
+        for (int i = 0; i < 15; ++i) g[16 + i] = b[i];
+      }
+    }
+  }
+}
+__device__ __forceinline__ void tl_mark_w1(const int k) {
+  if (threadIdx.x == 32) tl_buf()[k] = (unsigned)clock();
+}
+#else
 __device__ __forceinline__ void tl_mark(const int k) {
   if (threadIdx.x == 0 && g_timeline != nullptr) {
     unsigned long long t;
@@ -401,6 +440,7 @@ __device__ __forceinline__ void tl_mark(const int k) {
 __device__ __forceinline__ void tl_mark_w1(const int k) {  // SM clock only, taken by warp 1 (first stage-out warp)
   if (threadIdx.x == 32 && g_timeline != nullptr) g_timeline[(size_t)blockIdx.x * 32 + 16 + k] = (unsigned long long)clock64();
 }
+#endif
 #define TL_MARK(k) tl_mark(k)
 #define TL_MARK_W1(k) tl_mark_w1(k)
 #else
@@ -877,10 +917,12 @@ __device__ __forceinline__ bool post_scalar(const PostArgs& A, float* smem, cons
         unsigned long long r1 = 0;
 #pragma unroll
         for (int c = 0; c < DEX_NUM_CRITERIA; ++c) r1 |= (unsigned long long)__popc(bc[c]) << (6 * c);
-        unsigned long long* rec = reinterpret_cast<unsigned long long*>(A.ep.tile_records) + 4 * (size_t)(e0 >> 5);
-        __stcg(rec + 0, st | rbits | ((unsigned long long)__popc(bs) << 32) | ((unsigned long long)__popc(bf) << 38));
-        __stcg(rec + 1, st | r1);
-        __stcg(rec + 2, st | (unsigned long long)(unsigned)len);
+        // three planes of [tiles] words (not [tiles][3]): the epilogue CTA reads them lane-contiguously
+        const size_t tiles = (size_t)((A.n + kTile - 1) / kTile);
+        unsigned long long* rec = reinterpret_cast<unsigned long long*>(A.ep.tile_records) + (size_t)(e0 >> 5);
+        __stcg(rec, st | rbits | ((unsigned long long)__popc(bs) << 32) | ((unsigned long long)__popc(bf) << 38));
+        __stcg(rec + tiles, st | r1);
+        __stcg(rec + 2 * tiles, st | (unsigned long long)(unsigned)len);
       } else {
 #ifndef EXP_NO_COUNTERS
         if (bs) atomicAdd(A.out.counters + DEX_CNT_SUCCESS, __popc(bs));
@@ -1349,13 +1391,13 @@ __device__ void epilogue_body(const DexEpilogueBuffers& ep, const int n, const i
 // ------------------------------------------------------------------------------------------------
 template <int T, int BAR>
 __device__ void epilogue_records(const DexEpilogueBuffers& ep, const int n, const int max_consecutive, const unsigned stamp,
-                                 int* s_warp, int* s_base, int* s_cnt, const int tid) {
+                                 int* s_warp, int* s_base, int* s_cnt, unsigned* s_words, const int cap, const int tid) {
   const int lane = tid & 31, warp = tid >> 5;
   constexpr int NW = T / 32;
   const int tiles = (n + 31) >> 5;
-  const int K = (tiles + T - 1) / T;  // thread t owns the contiguous tile range [t*K, (t+1)*K)
-  const int w_begin = min(tid * K, tiles), w_end = min(w_begin + K, tiles);
-  const volatile unsigned long long* rec = reinterpret_cast<const volatile unsigned long long*>(ep.tile_records);
+  const volatile unsigned long long* rec0 = reinterpret_cast<const volatile unsigned long long*>(ep.tile_records);
+  const volatile unsigned long long* rec1 = rec0 + tiles;
+  const volatile unsigned long long* rec2 = rec1 + tiles;
   // loads that do not depend on the other tiles: issued first
   const bool has_tot = warp == 0 && lane <= DEX_NUM_COUNTERS && ep.totals != nullptr;
   const long long tot0 = has_tot ? __ldcg(reinterpret_cast<const long long*>(ep.totals) + lane) : 0;
@@ -1363,34 +1405,45 @@ __device__ void epilogue_records(const DexEpilogueBuffers& ep, const int n, cons
   const int cs0 = l0 ? __ldcg(ep.consecutive_successes) : 0;
   const unsigned long long rs0 = l0 ? __ldcg(reinterpret_cast<const unsigned long long*>(ep.rng_step)) : 0ull;
   if (tid < DEX_NUM_COUNTERS) s_cnt[tid] = 0;
-  constexpr int kCache = 4;
-  unsigned cache[kCache] = {0u, 0u, 0u, 0u};
-  int cnt = 0, n_s = 0, n_f = 0, crit[DEX_NUM_CRITERIA];
+  // ---- pass 1, lane = tile (consecutive lanes read consecutive 8-byte records of a plane: 8 sectors per request
+  // instead of 32): wait for the stamps, sum the counters, park the reset words in shared memory (s_words[cap])
+  constexpr int kBatch = 2;
+  int n_s = 0, n_f = 0, crit[DEX_NUM_CRITERIA];
   long long len = 0;
 #pragma unroll
   for (int c = 0; c < DEX_NUM_CRITERIA; ++c) crit[c] = 0;
-  for (int w0 = w_begin; w0 < w_end; w0 += kCache) {  // kCache tiles per round trip (volatile loads: L2 every time)
-    unsigned long long r0[kCache], r1[kCache], r2[kCache];
+  // thread t owns the contiguous tile range [t*K, (t+1)*K) in pass 2.  Up to kBatch tiles per thread (<= 32 768 envs)
+  // it also reads exactly those in pass 1 - no barrier between the passes; beyond, pass 1 is lane-contiguous.
+  const int K = (tiles + T - 1) / T;
+  const int w_begin = min(tid * K, tiles), w_end = min(w_begin + K, tiles);
+  const bool direct = K <= kBatch;  // CTA-uniform
+  for (int i0 = tid; i0 < (direct ? T : tiles); i0 += T * kBatch) {  // kBatch tiles per round trip (volatile: L2 every time)
+    unsigned long long r0[kBatch], r1[kBatch], r2[kBatch];
+    int idx[kBatch];
+#pragma unroll
+    for (int j = 0; j < kBatch; ++j) {
+      idx[j] = direct ? w_begin + j : i0 + j * T;
+      if (direct && j >= K) idx[j] = tiles;  // nothing to do
+    }
     bool ok;
     do {
 #pragma unroll
-      for (int j = 0; j < kCache; ++j) {
-        const size_t w = (size_t)min(w0 + j, w_end - 1);
-        r0[j] = rec[4 * w + 0];
-        r1[j] = rec[4 * w + 1];
-        r2[j] = rec[4 * w + 2];
+      for (int j = 0; j < kBatch; ++j) {
+        const int i = min(idx[j], tiles - 1);
+        r0[j] = rec0[i];
+        r1[j] = rec1[i];
+        r2[j] = rec2[i];
       }
       ok = true;
 #pragma unroll
-      for (int j = 0; j < kCache; ++j)
+      for (int j = 0; j < kBatch; ++j)
         ok = ok && (unsigned)(r0[j] >> 48) == stamp && (unsigned)(r1[j] >> 48) == stamp && (unsigned)(r2[j] >> 48) == stamp;
     } while (!ok);
 #pragma unroll
-    for (int j = 0; j < kCache; ++j) {
-      if (w0 + j < w_end) {
-        const unsigned bits = (unsigned)r0[j];
-        if (w0 == w_begin) cache[j] = bits;
-        cnt += __popc(bits);
+    for (int j = 0; j < kBatch; ++j) {
+      const int i = idx[j];
+      if (i < tiles) {
+        if (i < cap) s_words[i] = (unsigned)r0[j];
         n_s += (int)((r0[j] >> 32) & 63u);
         n_f += (int)((r0[j] >> 38) & 63u);
 #pragma unroll
@@ -1399,6 +1452,10 @@ __device__ void epilogue_records(const DexEpilogueBuffers& ep, const int n, cons
       }
     }
   }
+  if (!direct) epilogue_sync<T, BAR>();  // s_words complete (direct: every thread reads back its own words only)
+  auto word = [&](const int w) { return w < cap ? s_words[w] : (unsigned)rec0[w]; };
+  int cnt = 0;
+  for (int w = w_begin; w < w_end; ++w) cnt += __popc(word(w));
   // block scan of the reset counts
   int incl = cnt;
 #pragma unroll
@@ -1438,9 +1495,7 @@ __device__ void epilogue_records(const DexEpilogueBuffers& ep, const int n, cons
   epilogue_sync<T, BAR>();
   int pos = (warp > 0 ? s_warp[warp - 1] : 0) + incl - cnt;
   for (int w = w_begin; w < w_end; ++w) {
-    const int i = w - w_begin;
-    unsigned bits = (i < kCache) ? (i == 0 ? cache[0] : i == 1 ? cache[1] : i == 2 ? cache[2] : cache[3])
-                                 : (unsigned)rec[4 * (size_t)w];
+    unsigned bits = word(w);
     while (bits) {
       const int b = __ffs(bits) - 1;
       ep.env_ids[pos++] = w * 32 + b;
@@ -1503,14 +1558,15 @@ __global__ void __launch_bounds__(kPostThreads, DICT ? 1 : 4) post_physics_kerne
       const unsigned long long rs = *A.st.rng_step;
       const unsigned stamp = ((unsigned)rs + 1u) & 0xffffu;
       const volatile unsigned long long* last =
-          reinterpret_cast<const volatile unsigned long long*>(A.ep.tile_records) + 4 * (size_t)(blockIdx.x - 1);
+          reinterpret_cast<const volatile unsigned long long*>(A.ep.tile_records) + (size_t)(blockIdx.x - 1);  // plane 0
       while ((unsigned)(last[0] >> 48) != stamp) {
       }
       s_rng_step = rs;
     }
     __syncthreads();
     epilogue_records<kPostThreads, 0>(A.ep, A.n, A.p.max_consecutive_successes, ((unsigned)s_rng_step + 1u) & 0xffffu,
-                                      s_epi_warp, &s_epi_base, s_epi_cnt, tid);
+                                      s_epi_warp, &s_epi_base, s_epi_cnt, reinterpret_cast<unsigned*>(smem),
+                                      A.stride * kTile, tid);  // the slab of this CTA is free: it holds the reset words
     TL_MARK(5);
     TL_MARK(6);
     return;

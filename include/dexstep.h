@@ -310,7 +310,7 @@ typedef struct DexEpilogueBuffers {
   int64_t* totals;                /* [DEX_NUM_COUNTERS + 1] optional running totals since the caller last zeroed them:
                                      totals[k] += counters[k], totals[DEX_NUM_COUNTERS] += 1 (steps).  Together with
                                      DexOutBuffers.stat_totals this is the payload of the NCCL all-reduce */
-  uint64_t* tile_records;         /* [ceil(N/32)][4] zero-initialised once by the caller; required only when the epilogue is
+  uint64_t* tile_records;         /* [4 * ceil(N/32)] (three planes of ceil(N/32) words are used) zero-initialised once by the caller; required only when the epilogue is
                                      fused into dex_post_physics (and then rng_step is required too).  Every 32-env tile
                                      publishes its reset ballot word and its counter contributions as three self-validating
                                      8-byte records (top 16 bits = step stamp derived from *rng_step); one extra thread block

@@ -58,12 +58,31 @@ for e, a in envs:  # one L2-cold launch per replica (6 x ~63 MB > L2)
     epi_end.append(float(full[grid, 6] - full[:grid, 0].min()) / 1e3)
     runs.append(full[:grid])
 assert lib.dex_debug_set_timeline(None) == 0
-names = ["start", "stage-in done", "items done", "scalar done", "stage-out done", "reset done", "end"]
-print(f"envs {n} task {task} grid {grid}; times in us relative to the first CTA start; median over {len(runs)} launches")
+LIGHT = "-DDEXSTEP_TIMELINE_LIGHT" in os.environ.get("TL_FLAGS", "")
 import statistics as st_
-print(f"epilogue CTA end   median {st_.median(epi_end):7.2f}")
 def med(f):
     return st_.median(f(t) for t in runs)
+print(f"envs {n} task {task} grid {grid}; median over {len(runs)} launches")
+print(f"epilogue CTA end   median {st_.median(epi_end):7.2f} us after the first CTA start")
+if LIGHT:
+    # light marks: 32-bit SM clocks per mark (differences mod 2^32), globaltimer only at CTA start / end
+    ghz = 1.965
+    def d(t, a_, b_):
+        return ((t[:, 16 + b_] - t[:, 16 + a_]) % 2 ** 32) / ghz / 1e3
+    print(f"CTA start skew     median {med(lambda t: float(((t[:, 0] - t[:, 0].min()) / 1e3).median())):6.2f}  "
+          f"max {med(lambda t: float(((t[:, 0] - t[:, 0].min()) / 1e3).max())):6.2f} us")
+    print(f"CTA end            median {med(lambda t: float(((t[:, 6] - t[:, 0].min()) / 1e3).median())):6.2f}  "
+          f"max {med(lambda t: float(((t[:, 6] - t[:, 0].min()) / 1e3).max())):6.2f} us")
+    for (a_, b_), nm in [((0, 1), "stage-in"), ((1, 2), "items"), ((2, 3), "scalar || early stage-out"),
+                         ((2, 7), "  scalar: task obs + FSM"), ((7, 8), "  scalar: termination"),
+                         ((8, 9), "  scalar: ballots"), ((9, 10), "  scalar: record"), ((10, 3), "  scalar: vote barrier"),
+                         ((11, 12), "  warp 1: early f32 rows"), ((12, 13), "  warp 1: early obs chunks"),
+                         ((3, 4), "terms + late stage-out"), ((4, 5), "reset"), ((0, 5), "whole CTA")]:
+        print(f"phase {nm:28s} median {med(lambda t: float(d(t, a_, b_).median())):6.2f}  "
+              f"max {med(lambda t: float(d(t, a_, b_).max())):6.2f} us")
+    sys.exit(0)
+names = ["start", "stage-in done", "items done", "scalar done", "stage-out done", "reset done", "end"]
+print(f"envs {n} task {task} grid {grid}; times in us relative to the first CTA start; median over {len(runs)} launches")
 for k, nm in enumerate(names):
     print(f"{nm:16s} median {med(lambda t: float(((t[:, k] - t[:, 0].min()) / 1e3).median())):7.2f}  "
           f"max {med(lambda t: float(((t[:, k] - t[:, 0].min()) / 1e3).max())):7.2f}")
