@@ -60,6 +60,8 @@ def parse_args():
     ap.add_argument("--nb-hand", type=int, default=31, help="hand bodies per env (31 = survey layout; 37 = sensitivity line)")
     ap.add_argument("--obs-norm", type=int, default=0, help="1 = fused policy-input normalisation on (SURVEY §8f N3)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--tile-kernel", action="store_true",
+                    help="A/B: run the round-1 one-tile-per-CTA kernel (DEX_FLAG_TILE_KERNEL) instead of the persistent v2 kernel")
     ap.add_argument("--sweep", action="store_true", help="also print the post-physics num_envs sweep (configs[4])")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the bounded CPU-baseline sample")
     return ap.parse_args()
@@ -219,6 +221,20 @@ class Ring:
         return g
 
 
+def warm_plan(plan, steps_per_graph, warmup_steps, device):
+    """Untimed replays of the SAME CUDAGraph objects that are timed afterwards: every graph of the plan runs at least
+    once (a graph's first launch pays its one-time upload), and at least `warmup_steps` ring steps run in total."""
+    done = 0
+    for (g, _), spg in zip(plan, steps_per_graph):
+        g.replay()
+        done += spg
+    while done < warmup_steps:
+        plan[0][0].replay()
+        done += steps_per_graph[0]
+    torch.cuda.synchronize(device)
+    return done
+
+
 def timed_replays(plan, device, dist_barrier=None):
     """plan = [(graph, replays)]; returns device milliseconds between two events on the current stream."""
     if dist_barrier is not None:
@@ -237,14 +253,17 @@ def timed_replays(plan, device, dist_barrier=None):
 
 
 def make_plan(ring, fn, steps, group):
-    """Graphs that together run exactly `steps` ring steps: q replays of a `group`-step graph + one remainder graph."""
-    plan, per_launch = [], []
+    """Graphs that together run exactly `steps` ring steps: q replays of a `group`-step graph + one remainder graph.
+    Returns (plan, steps_per_graph)."""
+    plan, spg = [], []
     q, r = divmod(steps, group)
     if q:
         plan.append((ring.capture(fn, group), q))
+        spg.append(group)
     if r:
         plan.append((ring.capture(fn, r, start=(q * group) % len(ring)), 1))
-    return plan
+        spg.append(r)
+    return plan, spg
 
 
 def full_step(env, a):
@@ -310,38 +329,100 @@ def cpu_reference_run(task, n, steps, warmup, seed, budget_s=None):
 
 
 def run_reference_arm(args, task, n_env, rank, world):
-    """--impl reference: the reference's CPU implementation of the path (oracle port; the reference is
-    pure Python and /root/reference does not travel) on the host cores.  Rank 0 only."""
+    """--impl reference: the reference's CPU implementation of the path (oracle port; the reference is pure Python,
+    needs Isaac Gym to instantiate and /root/reference does not travel) on ALL host cores, over the whole job's env
+    count (n_env x world; a bounded sample of it when the run would take more than ~2 minutes).  Rank 0 only."""
     if rank != 0:
         return
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)  # torchrun exports OMP_NUM_THREADS=1: undo it for the CPU arm
+    n_job = n_env * world
     total = args.steps + args.warmup
-    # bounded sample: shrink the env batch per step so the whole run ends within ~2 minutes
     _, ms_full, _, _ = cpu_reference_run(task, n_env, 2, 1, 1234)
-    n_s = n_env
+    n_s = n_job
     while n_s > 64 and total * ms_full * (n_s / n_env) > 120e3:
         n_s //= 2
-    value, ms, done, threads = cpu_reference_run(task, n_s, args.steps, min(args.warmup, 3), 1234)
-    sample = f"{done} steps x {n_s} envs of {task} (oracle port of the reference's torch components, {threads} threads)"
+    value, ms, done, threads = cpu_reference_run(task, n_s, args.steps, args.warmup, 1234)
+    sample = (f"{done} steps x {n_s} envs of {task} (job = {n_job} envs; oracle port of the reference's torch components, "
+              f"{threads} threads; the port runs ~2x faster than the unmodified reference components on the same cores, "
+              f"BASELINE.md section 5)")
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": done,
-            "warmup": min(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": args.workload, "task": task, "envs_per_step": n_s, "device": "cpu"},
+            "config": {"workload": args.workload, "task": task, "envs_per_gpu": n_env, "envs_total": n_job,
+                       "envs_per_step_sampled": n_s, "device": "cpu", "threads": threads},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
 
 
+def eager_gpu_reference(task, n, device, steps=12):
+    """The reference's op chain as it runs in production - eager torch ON THE GPU (tasks/dexhand_base.py:893-942) -
+    restated by the oracle port with every tensor on `device`.  Returns ms/step and CUDA kernel launches per step."""
+    from oracle import synth as osynth
+    from oracle.dexstep_oracle import OracleEnv
+    from dexrobot_isaac_b200 import synthetic
+    from dexrobot_isaac_b200.config import load_task_config
+    from dexrobot_isaac_b200.params import BodyLayout
+
+    lay = BodyLayout.default(with_box=task == "BlindGrasping")
+    olay = osynth.BodyLayout(with_box=task == "BlindGrasping")
+    gen = torch.Generator(device=device).manual_seed(7)
+    cgen = torch.Generator().manual_seed(7)
+    with torch.device(device):
+        env = OracleEnv(load_task_config(task, num_envs=n), n, olay, synthetic.dof_props().to(device))
+        ring = []
+        for _ in range(3):
+            st = synthetic.random_state(n, lay, gen, device)
+            st["rigid_body_states"] = st.pop("rigid_body_state")
+            ring.append((st, synthetic.random_actions(n, env.num_actions, gen, device),
+                         synthetic.random_uniforms(n, cgen).to(device)))
+        env.load_state(ring[0][0])
+        env.reset(ring[0][2])
+
+        def one(i):
+            st, a, u = ring[i % len(ring)]
+            env.pre_physics_step(a)
+            env.load_state(st)
+            env.post_physics_step(u)
+
+        for i in range(3):
+            one(i)
+        torch.cuda.synchronize(device)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record()
+        for i in range(steps):
+            one(i)
+        e1.record()
+        torch.cuda.synchronize(device)
+        wall_ms = 1e3 * (time.perf_counter() - t0) / steps
+        dev_ms = e0.elapsed_time(e1) / steps
+        launches = None
+        try:
+            from torch.profiler import ProfilerActivity, profile
+
+            with profile(activities=[ProfilerActivity.CUDA]) as prof:
+                one(0)
+                torch.cuda.synchronize(device)
+            launches = sum(1 for ev in prof.events() if ev.device_type == torch.autograd.DeviceType.CUDA)
+        except Exception:
+            pass
+    ms = max(dev_ms, wall_ms)
+    return {"ms_per_step": ms, "device_ms_per_step": dev_ms, "value": n / (ms * 1e-3), "unit": UNIT,
+            "cuda_launches_per_step": launches,
+            "what": "oracle port of the reference's torch components, eager torch, all tensors on the same B200"}
+
+
 # ------------------------------------------------------------------------------------------------
-# end-to-end: host buffers in, host buffers out, copies inside the timed region
+# end to end: host buffers in, host buffers out, copies inside the timed region
 # ------------------------------------------------------------------------------------------------
-def run_e2e(ring, steps, device, barrier):
+def run_e2e(ring, steps, device, barrier, compact=False):
     envs = ring.envs[:2]
-    bufs = [e.alloc_host_buffers() for e in envs]
+    bufs = [e.alloc_host_buffers(compact=compact) for e in envs]
     for e, a, (hin, _) in zip(envs, ring.actions, bufs):
-        for k, v in e.pipeline.sim_tensors.items():
-            hin[k].copy_(v)
-        hin["actions"].copy_(a)
+        e.fill_host_inputs(hin, a)
     streams = [torch.cuda.Stream(device) for _ in envs]
     main = torch.cuda.current_stream(device)
     h2d = d2h = 0
@@ -368,13 +449,27 @@ def run_e2e(ring, steps, device, barrier):
     torch.cuda.synchronize(device)
     if barrier is not None:
         barrier()
+    for e in envs:
+        e.end_host_mode()
     return e0.elapsed_time(e1), h2d, d2h
 
 
 def kernel_avg_us(ring, fn, launches, group, device):
-    plan = make_plan(ring, fn, launches, group)
-    timed_replays(make_plan(ring, fn, min(launches, group), group), device)  # warm
+    plan, spg = make_plan(ring, fn, launches, group)
+    warm_plan(plan, spg, 3, device)  # the graphs that are timed, not copies of them
     return 1e3 * timed_replays(plan, device) / launches
+
+
+class HotRing:
+    """One replica replayed back to back: its ~40 MB working set stays in the 126 MB L2 (the L2-hot line)."""
+
+    def __init__(self, ring):
+        self.envs, self.actions = ring.envs[:1], ring.actions[:1]
+
+    def __len__(self):
+        return 1
+
+    capture = Ring.capture
 
 
 def main():
@@ -399,13 +494,19 @@ def main():
     from dexrobot_isaac_b200 import _lib
     from dexrobot_isaac_b200 import stats as dex_stats
 
-    _lib.load()  # fails loudly when the CUDA library is missing
+    lib = _lib.load()  # fails loudly when the CUDA library is missing
     ring = Ring(task, n_env, device, 1234 + rank, args.observer, obs_norm=bool(args.obs_norm), nb_hand=args.nb_hand)
+    if args.tile_kernel:
+        for e in ring.envs:
+            e.pipeline.tile_kernel = True
     R = len(ring)
     group = R * max(1, -(-32 // R))
-    if args.warmup > 0:
-        timed_replays(make_plan(ring, full_step, args.warmup, group), device, barrier)
-    plan = make_plan(ring, full_step, args.steps, group)
+    # The graphs that are timed are captured once and ALSO run the warm-up (>= --warmup untimed steps, every graph of
+    # the plan at least once): the first launch of a CUDA graph pays a one-time upload that must not be timed.
+    v2_before = lib.dex_debug_v2_launches()
+    plan, spg = make_plan(ring, full_step, args.steps, group)
+    v2_in_plan = lib.dex_debug_v2_launches() - v2_before
+    warm_plan(plan, spg, max(args.warmup, 3), device)
     for e in ring.envs:
         e.pipeline.epi["totals"].zero_()
         if e.pipeline.out["stat_totals"] is not None:
@@ -419,21 +520,25 @@ def main():
     torch.cuda.synchronize(device)
     sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for g, reps in plan:
         for _ in range(reps):
             g.replay()
     e1.record()
-    # the single statistics all-reduce of the logging interval, on a side stream
+    # the single statistics all-reduce of the logging interval, on a side stream; timed by itself
     side.wait_event(e1)
     with torch.cuda.stream(side):
+        a0.record()
         payload = dex_stats.pack_pipelines([e.pipeline for e in ring.envs])
         dex_stats.all_reduce(payload)  # NCCL over NVLink when world > 1, no-op on one GPU
+        a1.record()
     torch.cuda.synchronize(device)
     if barrier is not None:
         barrier()
     sampler.stop()
     ms = e0.elapsed_time(e1)
+    allreduce_us = 1e3 * a0.elapsed_time(a1)
     if world > 1:
         t = torch.tensor([ms], device=device, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -457,23 +562,38 @@ def main():
             traffic = json.load(f).get(f"{task}_{n_env}")
     except Exception:
         pass
-    roofline = {"bound": "hbm", "kernel": "post_physics_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                "algorithmic_bytes_per_env": b_post, "launch_us": post_us,
+    post_kernel = "post_physics_v2_kernel" if v2_in_plan > 0 else "post_physics_kernel"
+    roofline = {"bound": "hbm", "kernel": post_kernel, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": traffic,
+                "traffic_source": "profiles/traffic.json (static: dram__bytes_read + dram__bytes_write of one launch, ncu --set full)",
+                "peak_source": peak_src, "algorithmic_bytes_per_env": b_post, "launch_us": post_us,
                 "step_frac": (b_pre + b_post) * n_env * args.steps / (ms * 1e-3) / 1e9 / peak}
+
+    # ---- L2-hot line (report both): ONE replica replayed back to back, working set inside the 126 MB L2 ----
+    hot = HotRing(ring)
+    hk = max(32, min(args.steps, 1000))
+    hot_step = kernel_avg_us(hot, full_step, hk, 32, device)
+    hot_post = kernel_avg_us(hot, post_only, hk, 32, device)
+    l2_hot = {"step_us": hot_step, "post_us": hot_post, "value": n_env * world / (hot_step * 1e-6),
+              "post_frac_of_hbm_peak": b_post * n_env / (hot_post * 1e-6) / 1e9 / peak,
+              "note": "one replica replayed back to back (inputs stay in L2); the headline value is the L2-cold ring"}
 
     # ---- end to end through DexStepEnv.step_host (host buffers, copies inside the timed region) ----
     ke = max(2, min(args.steps, 200))
     sampler.start()
-    ems, h2d, d2h = run_e2e(ring, ke, device, barrier)
+    ems, h2d, d2h = run_e2e(ring, ke, device, barrier, compact=True)
     sampler.stop()
+    fms, fh2d, fd2h = run_e2e(ring, ke, device, barrier, compact=False)
     if world > 1:
-        t = torch.tensor([ems], device=device, dtype=torch.float64)
+        t = torch.tensor([ems, fms], device=device, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ems = float(t.item())
+        ems, fms = (float(x) for x in t.tolist())
     e2e = {"value": n_env * world * ke / (ems * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
            "d2h_bytes_per_step": d2h, "steps": ke, "ms_per_step": ems / ke,
-           "api": "DexStepEnv.step_host (pinned host buffers, 2 streams)"}
+           "api": "DexStepEnv.step_host, compact host staging (the 12 monitored body rows per env; pinned, 2 streams)",
+           "full_tensor_layout": {"value": n_env * world * ke / (fms * 1e-3), "h2d_bytes_per_step": fh2d,
+                                  "d2h_bytes_per_step": fd2h, "ms_per_step": fms / ke,
+                                  "api": "DexStepEnv.step_host, whole Isaac Gym tensors shipped"}}
     clocks = sampler.summary()
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -482,22 +602,39 @@ def main():
             "config": {"workload": args.workload, "task": task, "envs_per_gpu": n_env, "envs_total": n_env * world,
                        "obs_dim": ring.envs[0].num_observations, "num_bodies": ring.layout.num_bodies,
                        "observer": bool(args.observer), "obs_norm": bool(args.obs_norm), "l2": ring.l2_note, "graph_steps": group,
+                       "early_sim_loads": os.environ.get("DEXSTEP_EARLY_SIM_LOADS", "1") != "0",
                        "parallelism": f"env-sharded x{world}, no step-path collective, 1 NCCL all-reduce of stats"},
             "roofline": roofline, "e2e": e2e, "gpu_launches": launches_per_step * args.steps, "clocks": clocks,
-            "kernels_us": {"pre_physics": pre_us, "post_physics": post_us, "epilogue": epi_us},
+            "kernels_us": {"pre_physics": pre_us, "post_physics": post_us, "epilogue": epi_us,
+                           "stats_allreduce": allreduce_us},
+            "l2_hot": l2_hot,
             "episode_stats": {"steps": stats[C["DEX_NUM_COUNTERS"]], "resets": stats[C["DEX_CNT_RESET"]],
                               "success": stats[C["DEX_CNT_SUCCESS"]], "failure": stats[C["DEX_CNT_FAILURE"]],
                               "timeout": stats[C["DEX_CNT_TIMEOUT"]],
                               "episode_length_sum": stats[C["DEX_CNT_EPISODE_LENGTH"]]}}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        torch.set_num_threads(os.cpu_count() or 1)
         v, cms, done, threads = cpu_reference_run(task, n_env, 10**9, 2, 1234, budget_s=args.cpu_seconds)
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "ms_per_step": cms,
                                 "sample": f"{done} steps x {n_env} envs of {task} (same workload; oracle port of the "
-                                          f"reference's torch components; os.cpu_count()={os.cpu_count()})"}
+                                          f"reference's torch components; os.cpu_count()={os.cpu_count()}; the port runs "
+                                          f"~2x faster than the unmodified reference, BASELINE.md section 5)"}
+        torch.set_num_threads(1)
+        v1, cms1, done1, _ = cpu_reference_run(task, n_env, 10**9, 1, 1234, budget_s=min(6.0, args.cpu_seconds))
+        line["cpu_baseline_1thread"] = {"value": v1, "unit": UNIT, "cores": 1, "kind": "port", "ms_per_step": cms1,
+                                        "sample": f"{done1} steps x {n_env} envs"}
+        torch.set_num_threads(os.cpu_count() or 1)
+        try:
+            line["reference_gpu_eager"] = eager_gpu_reference(task, n_env, device)
+        except Exception as ex:  # the line is informational: never let it take the bench down
+            line["reference_gpu_eager"] = {"unavailable": f"{type(ex).__name__}: {ex}"[:300]}
     if args.sweep and rank == 0:
         sweep = []
         for n in (1024, 2048, 4096, 8192, 16384, 32768, 65536, 131072, 262144):
             r = Ring(task, n, device, 99, args.observer)
+            if args.tile_kernel:
+                for e in r.envs:
+                    e.pipeline.tile_kernel = True
             g = len(r) * max(1, -(-32 // len(r)))
             us = kernel_avg_us(r, post_only, max(len(r), 600), g, device)
             sus = kernel_avg_us(r, full_step, max(len(r), 600), g, device)

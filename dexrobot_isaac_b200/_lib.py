@@ -136,6 +136,7 @@ def load(path: str = None) -> ctypes.CDLL:
     lib.dex_extract_active_targets.argtypes = [P(DexParams), vp, vp, i32, vp]
     lib.dex_point_in_hand_frame.argtypes = [vp, vp, vp, vp, i32, vp]
     lib.dex_quat_mul.argtypes = [vp, vp, vp, i32, vp]
+    lib.dex_debug_v2_launches.argtypes = []
     for fn in FUNCTIONS:
         if fn != "dex_strerror":
             getattr(lib, fn).restype = ctypes.c_int

@@ -21,6 +21,7 @@
 
 #include "dexstep_common.cuh"
 #include "post_physics.cuh"
+#include "post_physics_v2.cuh"
 
 namespace {
 
@@ -208,16 +209,17 @@ int check_params(const DexParams* p) {
   if (p == nullptr) return DEX_ERR_NULL;
   if (p->abi_version != DEX_ABI_VERSION) return DEX_ERR_VERSION;
   if (p->task != DEX_TASK_BASE && p->task != DEX_TASK_BLIND_GRASPING) return DEX_ERR_PARAM;
-  if (p->num_bodies <= 0 || p->num_actors <= 0) return DEX_ERR_SIZE;
+  if (p->num_bodies <= 0 || p->num_actors <= 0 || p->num_contact_bodies <= 0) return DEX_ERR_SIZE;
   if (p->num_actions != 18 && p->num_actions != 12 && p->num_actions != 6) return DEX_ERR_SIZE;
-  if (p->obs_dim <= 0 || p->obs_dim > 1024) return DEX_ERR_SIZE;
+  if (p->obs_dim <= 0 || p->obs_dim > 256) return DEX_ERR_SIZE;  // kMaxObs of the kernels
   if (!(p->control_dt > 0.0f)) return DEX_ERR_PARAM;
   auto body_ok = [&](int b) { return b >= 0 && b < p->num_bodies; };
+  auto cbody_ok = [&](int b) { return b >= 0 && b < p->num_contact_bodies; };
   if (!body_ok(p->hand_body)) return DEX_ERR_PARAM;
   for (int f = 0; f < DEX_NUM_FINGERS; ++f)
-    if (!body_ok(p->tip_body[f]) || !body_ok(p->pad_body[f]) || !body_ok(p->contact_body[f])) return DEX_ERR_PARAM;
+    if (!body_ok(p->tip_body[f]) || !body_ok(p->pad_body[f]) || !cbody_ok(p->contact_body[f])) return DEX_ERR_PARAM;
   if (p->task == DEX_TASK_BLIND_GRASPING) {
-    if (!body_ok(p->box_body) || p->box_actor < 0 || p->box_actor >= p->num_actors) return DEX_ERR_PARAM;
+    if (!cbody_ok(p->box_body) || p->box_actor < 0 || p->box_actor >= p->num_actors) return DEX_ERR_PARAM;
   }
   for (int a = 0; a < DEX_NUM_ACTIVE; ++a)
     if (p->inverse_src_dof[a] < 0 || p->inverse_src_dof[a] >= DEX_NUM_DOF) return DEX_ERR_PARAM;
@@ -226,6 +228,12 @@ int check_params(const DexParams* p) {
   for (int j = 0; j < DEX_NUM_ACTIVE_FINGER; ++j)
     if (p->active_finger_dof[j] < 0 || p->active_finger_dof[j] >= DEX_NUM_DOF) return DEX_ERR_PARAM;
   if (p->num_component_rows <= 0 || p->num_component_rows > 2 * DEX_NUM_REWARD_TERMS + 7) return DEX_ERR_PARAM;
+  for (int i = 0; i < DEX_NUM_REWARD_TERMS; ++i)  // rows index the reward_components buffer and the shared slab
+    if (p->component_row[i] < -1 || p->component_row[i] + 1 >= p->num_component_rows) return DEX_ERR_PARAM;
+  if (p->total_row < 0 || p->total_row >= p->num_component_rows) return DEX_ERR_PARAM;
+  if (p->termination_row < 0 || p->termination_row + 5 >= p->num_component_rows) return DEX_ERR_PARAM;
+  for (int k = 0; k < DEX_NUM_OBS_KEYS; ++k)
+    if (p->obs_offset[k] < -1 || p->obs_offset[k] >= p->obs_dim) return DEX_ERR_PARAM;
   return DEX_OK;
 }
 
@@ -277,6 +285,8 @@ const char* dex_strerror(int code) {
   }
 }
 
+static int g_v2_launches = 0;
+int dex_debug_v2_launches(void) { return g_v2_launches; }
 int dex_abi_version(void) { return DEX_ABI_VERSION; }
 int dex_sizeof_params(void) { return (int)sizeof(DexParams); }
 
@@ -328,6 +338,31 @@ int dex_post_physics(const DexParams* params, const DexSimViews* sim, const DexS
     if (epilogue->tile_records == nullptr || epilogue->rng_step == nullptr || epilogue->rng_step != state->rng_step ||
         epilogue->reset_bits != out->reset_bits || epilogue->counters != out->counters)
       return DEX_ERR_NULL;
+  }
+  // The persistent warp-specialised kernel (post_physics_v2.cuh) takes every launch it covers; the table-driven tile
+  // kernel (post_physics.cuh) keeps the rest: obs_dict materialisation, the observation-only pass and the stale-contact
+  // pass of reset(), and layouts v2 has no stage for.  DEXSTEP_POST_V1=1 forces the tile kernel (A/B runs).
+  static const bool force_v1 = []() {
+    const char* e = getenv("DEXSTEP_POST_V1");
+    return e != nullptr && e[0] == '1';
+  }();
+  if (!force_v1 && !(flags & DEX_FLAG_TILE_KERNEL) && pp2::post2_eligible(*params, *out, mode, flags)) {
+    static thread_local pp2::Post2Args b;
+    b.p = *params;
+    b.sim = *sim;
+    b.st = *state;
+    b.out = *out;
+    b.ep = fused ? *epilogue : DexEpilogueBuffers{};
+    b.n = n_envs;
+    b.mode = mode;
+    b.flags = flags;
+    b.fused_epilogue = fused ? 1 : 0;
+    b.uniforms = uniforms;
+    b.seed = seed;
+    b.step = step_index;
+    ++g_v2_launches;
+    return params->task == DEX_TASK_BLIND_GRASPING ? pp2::launch_post2_t<true>(b, (cudaStream_t)stream)
+                                                   : pp2::launch_post2_t<false>(b, (cudaStream_t)stream);
   }
   static thread_local PostArgs a;  // ~7 KB of launch arguments: keep it off the stack
   a.p = *params;

@@ -485,7 +485,7 @@ __device__ __forceinline__ void post_stage_in(const PostArgs& A, float* smem, co
     // lanes 0..17: contact rows (5 monitored + box), lanes 18..23: box root state (pos, linvel); slots I_CF + lane
     const bool is_box = BG && lane >= 18 && lane < 24;
     const bool p_x = is_box || (lane < (BG ? 18 : 15) && (lane >= 15 || !stale));
-    const int xrow = is_box ? P.num_actors * 13 : nb * 3;
+    const int xrow = is_box ? P.num_actors * 13 : P.num_contact_bodies * 3;
     int xoff;
     if (is_box) {
       const int k = lane - 18;
@@ -1216,8 +1216,8 @@ __device__ __forceinline__ void post_rows_typed(const PostArgs& A, const float* 
 // Same arithmetic as reset_env() (dexstep_common.cuh), lane = element; the warps of the CTA reset different
 // envs of the tile concurrently, no CTA barrier inside.  s_u: this warp's 32-float scratch.
 // ------------------------------------------------------------------------------------------------
-template <bool BG>
-__device__ __forceinline__ void reset_env_warp(const PostArgs& A, const int env, const uint64_t step, float* s_u) {
+template <bool BG, typename ArgsT>
+__device__ __forceinline__ void reset_env_warp(const ArgsT& A, const int env, const uint64_t step, float* s_u) {
   const DexParams& P = A.p;
   const DexStateBuffers& st = A.st;
   const int lane = threadIdx.x & 31;

@@ -137,23 +137,72 @@ class DexStepEnv:
         return self.pipeline.out.get("obs_norm")
 
     # ------------------------------------------------------------------ host-buffer entry (end-to-end path)
-    def alloc_host_buffers(self):
-        """Pinned host mirrors of one step's inputs (sim tensors + actions) and results (obs, rew, reset)."""
+    def alloc_host_buffers(self, compact: bool = False):
+        """Pinned host mirrors of one step's inputs (sim tensors + actions) and results (obs, rew, reset).
+
+        ``compact=False``: the four Isaac Gym tensors as they are (2 432 B/env for BlindGrasping with 32 bodies).
+        ``compact=True``: a host staging layout that holds only the rows the path reads - rigid_body_state
+        [N,11,13] (hand, 5 tips, 5 pads), net_contact_force [N,6,3] (5 monitored bodies, box), actor_root_state
+        [N,1,13] (box), dof_state [N,26,2] - 904 B/env.  The body indices are run-time parameters of the kernels, so the
+        same kernels run on the compact device mirrors (``BodyLayout.compact()``); a host-side simulator fills the
+        compact buffers directly, ``fill_host_inputs`` gathers them from full tensors."""
         p = self.pipeline
-        pin = lambda t: torch.empty(t.shape, dtype=t.dtype, pin_memory=True)  # noqa: E731
-        inputs = {k: pin(v) for k, v in p.sim_tensors.items()}
-        inputs["actions"] = pin(self._actions)
-        outputs = {"obs_buf": pin(self.obs_buf), "rew_buf": pin(self.rew_buf), "reset_buf": pin(self.reset_buf)}
+        pin = lambda *shape, dtype=torch.float32: torch.empty(*shape, dtype=dtype, pin_memory=True)  # noqa: E731
+        n = self.num_envs
+        if compact:
+            lay = self._full_layout().compact()
+            inputs = {"dof_state": pin(n, 26, 2), "rigid_body_state": pin(n, lay.num_bodies, 13),
+                      "net_contact_force": pin(n, lay.contact_rows, 3), "actor_root_state": pin(n, lay.num_actors, 13)}
+        else:
+            inputs = {k: pin(*v.shape) for k, v in self._full_sim().items()}
+        inputs["actions"] = pin(n, self.num_actions)
+        outputs = {"obs_buf": pin(*self.obs_buf.shape), "rew_buf": pin(n), "reset_buf": pin(n, dtype=torch.bool)}
         return inputs, outputs
 
+    def _full_layout(self):
+        saved = getattr(self, "_host_saved", None)
+        return saved[0] if saved is not None else self.layout
+
+    def _full_sim(self):
+        saved = getattr(self, "_host_saved", None)
+        return saved[1] if saved is not None else self.pipeline.sim_tensors
+
+    def fill_host_inputs(self, host_inputs: Dict[str, torch.Tensor], actions: torch.Tensor):
+        """Copy the current device sim state (+ ``actions``) into host buffers of either layout (outside any timed
+        region: this stands in for the host-side simulator that would write them)."""
+        full, lay = self._full_sim(), self._full_layout()
+        if host_inputs["rigid_body_state"].shape[1] == lay.num_bodies:
+            for k, v in full.items():
+                host_inputs[k].copy_(v.view(host_inputs[k].shape))
+        else:
+            rigid, contact, actors = lay.compact_gather_indices()
+            n = self.num_envs
+            host_inputs["dof_state"].copy_(full["dof_state"].view(n, 26, 2))
+            host_inputs["rigid_body_state"].copy_(full["rigid_body_state"].view(n, lay.num_bodies, 13)[:, rigid])
+            host_inputs["net_contact_force"].copy_(full["net_contact_force"].view(n, lay.contact_rows, 3)[:, contact])
+            host_inputs["actor_root_state"].copy_(full["actor_root_state"].view(n, lay.num_actors, 13)[:, actors])
+        host_inputs["actions"].copy_(actions)
+
     def step_host(self, host_inputs: Dict[str, torch.Tensor], host_outputs: Dict[str, torch.Tensor]):
-        """One control step fed from HOST buffers: H2D of the sim state + actions, the three kernel
-        launches, D2H of obs/rew/reset — all asynchronous on the current stream (synchronise the stream
-        before reading ``host_outputs``).  Returns (h2d_bytes, d2h_bytes)."""
+        """One control step fed from HOST buffers: H2D of the sim state + actions, the two kernel launches, D2H of
+        obs/rew/reset - all asynchronous on the current stream (synchronise the stream before reading
+        ``host_outputs``).  The layout (full or compact) is taken from the buffers' shapes; the first compact call
+        switches the pipeline to device mirrors of that layout (``end_host_mode`` switches back).
+        Returns (h2d_bytes, d2h_bytes)."""
         p = self.pipeline
+        compact = host_inputs["rigid_body_state"].shape[1] != self._full_layout().num_bodies
+        if compact != (getattr(self, "_host_saved", None) is not None):
+            if compact:
+                self._host_saved = (self.layout, dict(p.sim_tensors))
+                lay = self.layout.compact()
+                dev = {k: torch.empty(v.shape, dtype=v.dtype, device=self.device)
+                       for k, v in host_inputs.items() if k != "actions"}
+                p.use_layout(lay, dev)
+            else:
+                self.end_host_mode()
         h2d = d2h = 0
         for k, dst in p.sim_tensors.items():
-            dst.copy_(host_inputs[k], non_blocking=True)
+            dst.copy_(host_inputs[k].view(dst.shape), non_blocking=True)
             h2d += dst.numel() * dst.element_size()
         self._actions.copy_(host_inputs["actions"], non_blocking=True)
         h2d += self._actions.numel() * 4
@@ -162,6 +211,14 @@ class DexStepEnv:
             host_outputs[k].copy_(src, non_blocking=True)
             d2h += src.numel() * src.element_size()
         return h2d, d2h
+
+    def end_host_mode(self):
+        """Back to the env's own (full-layout) sim tensors after compact ``step_host`` calls."""
+        saved = getattr(self, "_host_saved", None)
+        if saved is not None:
+            torch.cuda.synchronize(self.device)
+            self.pipeline.use_layout(*saved)
+            self._host_saved = None
 
     # ------------------------------------------------------------------ extras (step_processor.py:221-232)
     def _update_extras(self):

@@ -96,6 +96,28 @@ class BodyLayout:
     box_body: int = -1
     box_actor: int = -1
     body_names: Dict[int, str] = field(default_factory=dict)
+    num_contact_bodies: int = 0  # bodies per env in net_contact_force (0 = num_bodies, the Isaac Gym tensors)
+
+    @property
+    def contact_rows(self) -> int:
+        return self.num_contact_bodies or self.num_bodies
+
+    def compact(self) -> "BodyLayout":
+        """The host-staging layout that ships only the rows the path reads (DexStepEnv.alloc_host_buffers(compact=True)):
+        rigid_body_state rows [hand, 5 tips, 5 pads], net_contact_force rows [5 monitored bodies (, box)],
+        actor_root_state row [box] (or the hand actor when there is no box)."""
+        has_box = self.box_body >= 0
+        return BodyLayout(num_bodies=11, num_actors=1, hand_body=0, tip_bodies=[1 + f for f in range(NUM_FINGERS)],
+                          pad_bodies=[6 + f for f in range(NUM_FINGERS)], contact_bodies=list(range(NUM_FINGERS)),
+                          box_body=5 if has_box else -1, box_actor=0 if has_box else -1,
+                          num_contact_bodies=6 if has_box else 5)
+
+    def compact_gather_indices(self):
+        """-> (rigid rows, contact rows, actor rows) of THIS layout that make up the compact layout, in its order."""
+        rigid = [self.hand_body] + list(self.tip_bodies) + list(self.pad_bodies)
+        contact = list(self.contact_bodies) + ([self.box_body] if self.box_body >= 0 else [])
+        actors = [self.box_actor if self.box_actor >= 0 else 0]
+        return rigid, contact, actors
 
     @staticmethod
     def default(with_box: bool = False, nb_hand: int = 31) -> "BodyLayout":
@@ -201,6 +223,7 @@ def make_params(cfg: dict, layout: BodyLayout, dof_lower: Sequence[float], dof_u
     P.abi_version = C["DEX_ABI_VERSION"]
     P.task = C["DEX_TASK_BLIND_GRASPING"] if is_bg else C["DEX_TASK_BASE"]
     P.num_bodies, P.num_actors, P.hand_body = layout.num_bodies, layout.num_actors, layout.hand_body
+    P.num_contact_bodies = layout.contact_rows
     for f in range(NUM_FINGERS):
         P.tip_body[f], P.pad_body[f], P.contact_body[f] = (layout.tip_bodies[f], layout.pad_bodies[f],
                                                            layout.contact_bodies[f])

@@ -29,6 +29,7 @@ FLAG_FIRST_REWARD_CALL = C["DEX_FLAG_FIRST_REWARD_CALL"]
 FLAG_STALE_CONTACTS = C["DEX_FLAG_STALE_CONTACTS"]
 FLAG_NO_FUSED_RESET = C["DEX_FLAG_NO_FUSED_RESET"]
 FLAG_EARLY_SIM_LOADS = C["DEX_FLAG_EARLY_SIM_LOADS"]
+FLAG_TILE_KERNEL = C["DEX_FLAG_TILE_KERNEL"]
 _EARLY_SIM = os.environ.get("DEXSTEP_EARLY_SIM_LOADS", "1") != "0"  # A/B switch for StepPipeline.step()
 NUM_UNIFORMS = C["DEX_NUM_UNIFORMS"]
 
@@ -59,7 +60,8 @@ class StepPipeline:
         self.host_step = 0
         self._reward_initialized = False
         self._graph = None
-        self.fuse_epilogue = bool(fuse_epilogue)  # epilogue done by the last CTA of the post-physics launch
+        self.fuse_epilogue = bool(fuse_epilogue)  # step epilogue done by one extra CTA of the post-physics launch
+        self.tile_kernel = False  # True: DEX_FLAG_TILE_KERNEL on every post-physics launch (A/B against the v2 kernel)
         n, dev, sp = self.n, self.device, self.spec
         f32, i64, u8 = torch.float32, torch.int64, torch.uint8
 
@@ -71,7 +73,7 @@ class StepPipeline:
         self._sim = L.DexSimViews()
         self.bind_sim(sim or {
             "dof_state": z(n, NUM_DOF, 2), "rigid_body_state": z(n, layout.num_bodies, 13),
-            "net_contact_force": z(n, layout.num_bodies, 3), "actor_root_state": z(n, layout.num_actors, 13)})
+            "net_contact_force": z(n, layout.contact_rows, 3), "actor_root_state": z(n, layout.num_actors, 13)})
 
         # ---- persistent state, SoA [K,N] ----
         nact = sp.num_actions
@@ -164,7 +166,7 @@ class StepPipeline:
         gymtorch.wrap_tensor views (tensor_manager.py:173-328): no copy is ever made."""
         n, lay = self.n, self.layout
         want = {"dof_state": n * NUM_DOF * 2, "rigid_body_state": n * lay.num_bodies * 13,
-                "net_contact_force": n * lay.num_bodies * 3, "actor_root_state": n * lay.num_actors * 13}
+                "net_contact_force": n * lay.contact_rows * 3, "actor_root_state": n * lay.num_actors * 13}
         for k, numel in want.items():
             t = sim.get(k)
             if t is None:
@@ -175,6 +177,21 @@ class StepPipeline:
             self.sim_tensors[k] = t
             setattr(self._sim, k, t.data_ptr())
         self._graph = None
+
+    def use_layout(self, layout: BodyLayout, sim: Dict[str, torch.Tensor]):
+        """Switch the body / actor indexing of the sim tensors (they are run-time parameters of the kernels) and bind
+        tensors of that layout: used to run the path on a compact host-staging layout (``BodyLayout.compact()``) and to
+        switch back.  Everything else in the parameter block is unchanged; a captured graph is invalidated."""
+        P = self.params
+        P.num_bodies, P.num_contact_bodies, P.num_actors = layout.num_bodies, layout.contact_rows, layout.num_actors
+        P.hand_body = layout.hand_body
+        for f in range(NUM_FINGERS):
+            P.tip_body[f], P.pad_body[f], P.contact_body[f] = (layout.tip_bodies[f], layout.pad_bodies[f],
+                                                               layout.contact_bodies[f])
+        if self.spec.is_blind_grasping:
+            P.box_body, P.box_actor = layout.box_body, layout.box_actor
+        self.layout = layout
+        self.bind_sim(sim)
 
     # ------------------------------------------------------------------ [N,K] views of SoA state
     def view(self, name: str) -> torch.Tensor:
@@ -206,6 +223,8 @@ class StepPipeline:
         if mode == MODE_FULL and not self._reward_initialized:
             flags |= FLAG_FIRST_REWARD_CALL
             self._reward_initialized = True
+        if self.tile_kernel:
+            flags |= FLAG_TILE_KERNEL
         L.check(self.lib.dex_post_physics(ctypes.byref(self.params), ctypes.byref(self._sim), ctypes.byref(self._state),
                                           ctypes.byref(self._out),
                                           ctypes.byref(self._epi) if fused_epilogue and mode == MODE_FULL else None,

@@ -59,7 +59,7 @@
 extern "C" {
 #endif
 
-#define DEX_ABI_VERSION 8
+#define DEX_ABI_VERSION 9
 
 #define DEX_NUM_DOF 26          /* constants.py:8-10: 6 base + 20 finger DOFs */
 #define DEX_NUM_BASE 6
@@ -95,6 +95,10 @@ extern "C" {
                                           loaded before the programmatic-launch wait, overlapping that kernel.  Never set it when
                                           the previous launch is a dex_post_physics of the same envs (its fused reset writes
                                           dof_state / actor_root_state) or a physics kernel that signals early */
+
+#define DEX_FLAG_TILE_KERNEL 16u       /* run the table-driven one-tile-per-CTA kernel (post_physics.cuh) even where the persistent
+                                          warp-specialised kernel (post_physics_v2.cuh) covers the launch: A/B runs and the
+                                          bit-for-bit cross-check of the two implementations (tests/test_cuda_v2.py) */
 
 /* observation keys (obs_dict entries of the reference, observation_encoder.py:613-756,
  * step_processor.py:73, blind_grasping_task.py:569-652,702-746,895-899) */
@@ -161,7 +165,10 @@ typedef struct DexParams {
   int32_t abi_version;            /* must be DEX_ABI_VERSION */
   int32_t task;                   /* DEX_TASK_* */
   /* --- layout of the sim buffers (hand_initializer.py:439-560, blind_grasping_task.py:388-419) --- */
-  int32_t num_bodies;             /* NB: rigid bodies per env */
+  int32_t num_bodies;             /* NB: rigid bodies per env = row pitch of rigid_body_state */
+  int32_t num_contact_bodies;     /* bodies per env in net_contact_force (its row pitch; contact_body[] and box_body index it).
+                                     Equal to num_bodies for the Isaac Gym tensors; smaller for a compact host-staging layout
+                                     that ships only the monitored rows (DexStepEnv.alloc_host_buffers(compact=True)) */
   int32_t num_actors;             /* NA: actors per env */
   int32_t hand_body;              /* right_hand_base */
   int32_t tip_body[DEX_NUM_FINGERS];      /* r_f_link{1..5}_tip */
@@ -321,6 +328,9 @@ const char* dex_strerror(int code);
 int dex_abi_version(void);
 /* sizeof(DexParams) as compiled, so a binding can verify its struct mirror */
 int dex_sizeof_params(void);
+/* number of dex_post_physics calls of this process that launched the persistent warp-specialised kernel
+ * (csrc/post_physics_v2.cuh) rather than the tile kernel: lets a test assert which kernel the lean path runs */
+int dex_debug_v2_launches(void);
 
 /* Pre-physics: actions -> 26 DOF position targets.  `actions` [N,NACT] row-major.  Optional debug
  * outputs (may be NULL): active_raw_targets [18][N] (ActionProcessor.active_raw_targets). */

@@ -1,0 +1,209 @@
+"""GPU tests of the persistent warp-specialised post-physics kernel (csrc/post_physics_v2.cuh), the kernel the bench
+times.  It runs whenever no obs_dict is materialised (the lean production configuration):
+  (1) lockstep against the CPU oracle, lean configuration, both tasks, all action variants, ragged N / second body
+      layout (the plain-load fallback of the producer warps) and N % 16 == 0 (the bulk-copy path);
+  (2) a 16 384-env (BASELINE.json configs[3]) oracle lockstep per task;
+  (3) bit-for-bit equality with the table-driven tile kernel (DEX_FLAG_TILE_KERNEL) on every output and state buffer,
+      at 16 384 / 4 096 envs (bulk path), 5 000 and 100 003 envs (fallback path, many tiles per CTA), eager and
+      graph-replayed, with in-kernel Philox resets.
+Tolerances as tests/test_cuda_parity.py (BASELINE.json north_star)."""
+import pytest
+import torch
+
+from oracle import synth
+from oracle.driver import compare_snapshots, run_lockstep
+from dexrobot_isaac_b200.config import load_task_config
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+RTOL, ATOL = 1e-5, 1e-6
+
+
+def lean_env(task, n, layout=None, observer=False, **kw):
+    from dexrobot_isaac_b200.env import DexStepEnv
+    from dexrobot_isaac_b200.params import BodyLayout
+
+    cfg = load_task_config(task, num_envs=n, **kw)
+    layout = layout or synth.BodyLayout(with_box=task == "BlindGrasping")
+    return DexStepEnv(cfg, n, BodyLayout.from_synth(layout), synth.dof_props_tensor(), device=DEV,
+                      materialize_obs_dict=False, observer=observer)
+
+
+def oracle_env(task, n, layout=None, **kw):
+    from oracle.dexstep_oracle import OracleEnv
+
+    cfg = load_task_config(task, num_envs=n, **kw)
+    layout = layout or synth.BodyLayout(with_box=task == "BlindGrasping")
+    return OracleEnv(cfg, n, layout, synth.dof_props_tensor())
+
+
+def _lockstep(task, n, steps, seed, layout=None, check_every=1, **kw):
+    layout = layout or synth.BodyLayout(with_box=task == "BlindGrasping")
+    ora, cud = oracle_env(task, n, layout, **kw), lean_env(task, n, layout, **kw)
+    world = synth.ScriptedWorld(n, layout, seed=seed, nact=ora.num_actions)
+    bad, seen = [], {"reset": 0, "success": 0, "failure": 0, "timeout": 0}
+
+    def on_step(t, envs):
+        if len(bad) > 20 or (t % check_every and t > 3):
+            return
+        a, b = envs[0].snapshot(), envs[1].snapshot()
+        seen["reset"] += int(a["reset_buf"].sum())
+        for k in ("success", "failure", "timeout"):
+            seen[k] += int(a[f"extras/{k}"].sum())
+        for m in compare_snapshots(a, b, RTOL, ATOL, skip_rows=a["reset_buf"].bool(), ignore=("obs/",)):
+            bad.append(f"step {t} {m}")
+        ids = envs[1].pipeline.env_ids().cpu()
+        if not torch.equal(ids, torch.nonzero(a["reset_buf"]).flatten()):
+            bad.append(f"step {t} env_ids differ")
+
+    run_lockstep([ora, cud], world, steps, on_step)
+    assert not bad, "\n".join(bad)
+    return seen
+
+
+def test_v2_lockstep_basetask_n64():
+    seen = _lockstep("BaseTask", 64, 330, seed=201)
+    assert seen["timeout"] > 0 and seen["failure"] > 0
+
+
+def test_v2_lockstep_blindgrasping_n64():
+    seen = _lockstep("BlindGrasping", 64, 520, seed=202)
+    assert seen["success"] > 0 and seen["failure"] > 0 and seen["timeout"] > 0
+
+
+@pytest.mark.parametrize("kw", [dict(control_mode="position"), dict(policy_controls_hand_base=False),
+                                dict(policy_controls_fingers=False)],
+                         ids=["position", "nobase", "nofingers"])
+def test_v2_lockstep_action_variants(kw):
+    _lockstep("BlindGrasping", 48, 120, seed=203, **kw)
+    _lockstep("BaseTask", 33, 40, seed=204, **kw)
+
+
+def test_v2_lockstep_ragged_and_other_body_layout():
+    _lockstep("BaseTask", 1, 12, seed=205)
+    _lockstep("BlindGrasping", 77, 215, seed=206, layout=synth.BodyLayout(nb_hand=37, with_box=True))
+    _lockstep("BaseTask", 77, 60, seed=207, layout=synth.BodyLayout(nb_hand=37, with_box=False))
+
+
+def test_v2_lockstep_n4096():
+    _lockstep("BaseTask", 4096, 40, seed=208, check_every=8)
+    seen = _lockstep("BlindGrasping", 4096, 240, seed=209, check_every=40)
+    assert seen["reset"] > 0
+
+
+@pytest.mark.parametrize("task", ["BaseTask", "BlindGrasping"])
+def test_v2_lockstep_headline_size(task):
+    """BASELINE.json configs[3] size (16 384 envs): 24 control steps against the oracle, every step compared."""
+    seen = _lockstep(task, 16384, 24, seed=210)
+    assert seen["reset"] > 0
+
+
+BUFS_OUT = ("obs_buf", "rew_buf", "reset_buf", "reward_components", "success", "failure", "timeout", "reset_bits")
+
+
+@pytest.mark.parametrize("task,n", [("BlindGrasping", 16384), ("BaseTask", 16384), ("BlindGrasping", 4096),
+                                    ("BaseTask", 5000), ("BlindGrasping", 100003), ("BlindGrasping", 33)])
+def test_v2_equals_tile_kernel_bitwise(task, n):
+    """Same seeded random-state trajectory through the persistent kernel and through the tile kernel: every output,
+    every state buffer, the sim tensors the fused reset rewrites, env_ids and the epilogue statistics are identical
+    bit for bit (in-kernel Philox resets included: both kernels key the stream by (seed, step, env))."""
+    lay = synth.BodyLayout(with_box=task == "BlindGrasping")
+    gen = torch.Generator().manual_seed(31)
+    e1, e2 = lean_env(task, n), lean_env(task, n)
+    e1.pipeline.tile_kernel = True
+    u = synth.random_uniforms(n, gen)
+    steps = 7
+    for t in range(steps):
+        st = synth.random_state(n, lay, gen, ground_frac=0.01)
+        a = synth.random_actions(n, e1.num_actions, gen)
+        for e in (e1, e2):
+            e.load_state(st)
+            if t == 0:
+                e.reset(u)
+                e.pipeline.uniforms = None  # from here on: in-kernel Philox
+            else:
+                if t == 3:  # force some timeouts
+                    cnt = torch.where(torch.arange(n) % 7 == 0, e.pipeline.params.max_episode_length - 2, 5)
+                    e.episode_step_count.copy_(cnt.to(DEV))
+                e.pipeline.pre_physics(a.to(DEV).contiguous())
+                e.pipeline.post_step()
+        torch.cuda.synchronize()
+        p1, p2 = e1.pipeline, e2.pipeline
+        for k in BUFS_OUT:
+            assert torch.equal(p1.out[k], p2.out[k]), f"step {t} out {k}"
+        for k, v in p1.state.items():
+            assert torch.equal(v, p2.state[k]), f"step {t} state {k}"
+        for k, v in p1.sim_tensors.items():
+            assert torch.equal(v, p2.sim_tensors[k]), f"step {t} sim {k}"
+        for k in ("env_ids", "num_reset", "stats", "consecutive_successes", "totals"):
+            if k == "env_ids":
+                assert torch.equal(p1.env_ids(), p2.env_ids()), f"step {t} env_ids"
+            else:
+                assert torch.equal(p1.epi[k], p2.epi[k]), f"step {t} epi {k}"
+        if t == 3:
+            assert int(p2.out["timeout"].sum()) > 0
+    assert int(e2.pipeline.epi["totals"][3]) > 0  # some envs did reset
+
+
+@pytest.mark.parametrize("task", ["BaseTask", "BlindGrasping"])
+def test_v2_graph_replay_equals_tile_kernel(task):
+    """The whole control step (dex_pre_physics + dex_post_physics with DEX_FLAG_EARLY_SIM_LOADS) captured in one CUDA
+    graph and replayed == the tile kernel launched eagerly, on a scripted world with resets."""
+    n, steps = 4096, 10
+    lay = synth.BodyLayout(with_box=task == "BlindGrasping")
+    e1, e2 = lean_env(task, n), lean_env(task, n)
+    e1.pipeline.tile_kernel = True
+    world = synth.ScriptedWorld(n, lay, seed=23, nact=e1.num_actions)
+    u = world.uniforms(0).to(DEV)
+    st0 = world.state(0, e1.episode_step_count, None)
+    for e in (e1, e2):
+        e.load_state(st0)
+        e.reset(u)
+        e.pipeline.uniforms = u
+    act = torch.zeros(n, e2.num_actions, device=DEV)
+    g = None
+    for t in range(1, steps + 1):
+        st = world.state(t, e1.episode_step_count, None)
+        a = world.actions(t).to(DEV)
+        e1.load_state(st)
+        e1.pre_physics_step(a)
+        e1.post_physics_step()
+        e2.load_state(st)
+        act.copy_(a)
+        if t < 4:
+            e2.pipeline.step(act)
+        else:
+            if g is None:
+                dicts = (e2.pipeline.state, e2.pipeline.sim_tensors, e2.pipeline.out, e2.pipeline.epi)
+                saved = [{k: v.clone() for k, v in d.items() if v is not None} for d in dicts]
+                g = e2.pipeline.capture_step_graph(act)
+                for d, sv in zip(dicts, saved):
+                    for k, v in sv.items():
+                        d[k].copy_(v)
+            e2.pipeline.replay()
+        torch.cuda.synchronize()
+        for k in BUFS_OUT:
+            assert torch.equal(e1.pipeline.out[k], e2.pipeline.out[k]), f"step {t} {k}"
+        for k, v in e1.pipeline.state.items():
+            if k != "rng_step":
+                assert torch.equal(v, e2.pipeline.state[k]), f"step {t} state {k}"
+        assert torch.equal(e1.pipeline.env_ids(), e2.pipeline.env_ids())
+
+
+def test_v2_is_the_kernel_that_runs():
+    """The lean configuration must launch post_physics_v2_kernel (not silently fall back to the tile kernel):
+    checked through the CUDA profiler-free route of counting tile records - the persistent kernel publishes its
+    records from <= SMs x 2 CTAs, which shows in `DexStepError`-free execution and in identical results; here we
+    assert the dispatch predicate itself through the library's debug counter."""
+    from dexrobot_isaac_b200 import _lib as L
+
+    lib = L.load()
+    env = lean_env("BlindGrasping", 256)
+    before = lib.dex_debug_v2_launches()
+    gen = torch.Generator().manual_seed(1)
+    env.load_state(synth.random_state(256, synth.BodyLayout(with_box=True), gen))
+    env.reset(synth.random_uniforms(256, gen))
+    a = synth.random_actions(256, env.num_actions, gen).to(DEV)
+    env.pipeline.step(a)
+    torch.cuda.synchronize()
+    assert lib.dex_debug_v2_launches() > before
