@@ -446,6 +446,11 @@ int dex_quat_mul(const float* a, const float* b, float* out, int32_t n, void* st
   return launch_status();
 }
 
+#ifdef DEXSTEP_TL2
+/* debug builds only (tools/timeline_v2.py): device buffer [grid][8][32] of uint64 for the v2 kernel's phase marks */
+int dex_debug_set_timeline2(void* dev_ptr) { return (int)cudaMemcpyToSymbol(pp2::g_tl2, &dev_ptr, sizeof(dev_ptr)); }
+#endif
+
 #ifdef DEXSTEP_TIMELINE
 /* debug builds only: device buffer [grid][8] of uint64 that receives per-CTA phase timestamps */
 int dex_debug_set_timeline(void* dev_ptr) {

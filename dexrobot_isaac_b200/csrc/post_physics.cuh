@@ -1426,6 +1426,7 @@ __device__ void epilogue_records(const DexEpilogueBuffers& ep, const int n, cons
       if (direct && j >= K) idx[j] = tiles;  // nothing to do
     }
     bool ok;
+    unsigned polls = 0;
     do {
 #pragma unroll
       for (int j = 0; j < kBatch; ++j) {
@@ -1438,6 +1439,9 @@ __device__ void epilogue_records(const DexEpilogueBuffers& ep, const int n, cons
 #pragma unroll
       for (int j = 0; j < kBatch; ++j)
         ok = ok && (unsigned)(r0[j] >> 48) == stamp && (unsigned)(r1[j] >> 48) == stamp && (unsigned)(r2[j] >> 48) == stamp;
+      // bounded (each poll is an L2 round trip, ~0.5 us): a tile that never publishes - a fault in its CTA, or a record
+      // buffer shared with another pipeline - ends the launch with a trap after a few seconds instead of hanging the stream
+      if (!ok && ++polls > (1u << 23)) __trap();
     } while (!ok);
 #pragma unroll
     for (int j = 0; j < kBatch; ++j) {
@@ -1559,7 +1563,9 @@ __global__ void __launch_bounds__(kPostThreads, DICT ? 1 : 4) post_physics_kerne
       const unsigned stamp = ((unsigned)rs + 1u) & 0xffffu;
       const volatile unsigned long long* last =
           reinterpret_cast<const volatile unsigned long long*>(A.ep.tile_records) + (size_t)(blockIdx.x - 1);  // plane 0
+      unsigned polls = 0;
       while ((unsigned)(last[0] >> 48) != stamp) {
+        if (++polls > (1u << 23)) __trap();  // bounded wait, see epilogue_records
       }
       s_rng_step = rs;
     }

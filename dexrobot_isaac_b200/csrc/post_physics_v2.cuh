@@ -52,14 +52,14 @@ struct Lay {
   static constexpr int SA = BG ? 107 : 99;
   static constexpr int STAGE_BYTES = (OFF_AOS + 32 * SA * 4 + 127) / 128 * 128;
   // work block: values that cross a warp or a phase, [field][32] floats
-  static constexpr int W_BIN = 0, W_PADBOX = 5, W_HDIFF = 10, W_TIPBOX = 15;
-  static constexpr int W_CDIST = 20, W_DRIFT = 21, W_VMAG = 22, W_BOXHAS = 23, W_HANDBOX = 24;
-  static constexpr int W_BVEL = 25;  // 6
-  static constexpr int W_GRASP = 31, W_THUMB = 32, W_OTHERS = 33, W_GRASPDUR = 34, W_SDS = 35, W_STAGE = 36, W_J2 = 37,
-                       W_J3 = 38;
-  static constexpr int W_HITG = 39, W_BOXFAR = 40, W_QUALOK = 41, W_MINTIPBOX = 42, W_AVGHDIFF = 43;
-  static constexpr int W_CHG = 44, W_RHAND = 49, W_FV2 = 53, W_FA2 = 73, W_JL = 93;  // BaseTask (common rewards)
-  static constexpr int W_WGT = BG ? 44 : 113;  // 26 weighted reward terms
+  static constexpr int W_BIN = 0, W_PADBOX = 5;           // 5 each
+  static constexpr int W_CDIST = 10, W_DRIFT = 11, W_VMAG = 12, W_BOXHAS = 13, W_BOXFAR = 14;
+  static constexpr int W_BVEL = 15;                       // 6: finite-difference base velocity
+  static constexpr int W_GRASP = 21, W_THUMB = 22, W_OTHERS = 23, W_GRASPDUR = 24, W_SDS = 25, W_STAGE = 26, W_J2 = 27,
+                       W_J3 = 28;
+  static constexpr int W_HITG = 29, W_HCOK = 30, W_SOK = 31, W_MINTIPBOX = 32, W_AVGHDIFF = 33;
+  static constexpr int W_CHG = 34, W_RHAND = 39, W_FV2 = 43, W_FA2 = 63, W_JL = 83;  // BaseTask (common rewards)
+  static constexpr int W_WGT = BG ? 34 : 103;  // 26 weighted reward terms
   static constexpr int W_COUNT = W_WGT + DEX_NUM_REWARD_TERMS;
 };
 
@@ -80,6 +80,7 @@ struct Post2Args {
   int32_t bulk_ok, n_bulk, n_bulk_early;  // entries [0, n_bulk_early) touch sim tensors only
   uint32_t tx_bytes;                      // bytes of all bulk entries of a full tile
   int32_t wp;                             // obs tile row stride (odd)
+  uint32_t obs_late;                      // bit c: obs columns [32c, 32c+32) hold a value that phase B writes
   uint32_t smem_bytes;
   int32_t rb_off[11], cf_off[6];
   int32_t dof2afj[DEX_NUM_DOF];           // dof -> index in active_finger_dof, -1 = not an active finger DOF
@@ -118,6 +119,13 @@ inline int build_post2(Post2Args& a) {
   a.want_tgt = (has(DEX_K_BASE_DOF_TARGET) || has(DEX_K_ACTIVE_FINGER_DOF_TARGET) || has(DEX_K_ALL_FINGER_DOF_TARGET)) ? 1 : 0;
   a.tiles = (a.n + 31) / 32;
   a.wp = P.obs_dim | 1;
+  a.obs_late = 0;
+  {
+    const int late_keys[7] = {DEX_K_THUMB_CONTACT, DEX_K_OTHER_FINGERS_CONTACT, DEX_K_GRASP_STATE, DEX_K_GRASP_DURATION,
+                              DEX_K_CURRENT_STAGE, DEX_K_TIME_IN_STAGE, DEX_K_STAGE_PROGRESS};
+    for (int i = 0; i < 7; ++i)
+      if (BG && has(late_keys[i])) a.obs_late |= 1u << (P.obs_offset[late_keys[i]] >> 5);
+  }
   a.rb_off[0] = P.hand_body * 13;
   for (int f = 0; f < DEX_NUM_FINGERS; ++f) {
     a.rb_off[1 + f] = P.tip_body[f] * 13;
@@ -172,6 +180,31 @@ inline int build_post2(Post2Args& a) {
   return DEX_OK;
 }
 
+#ifdef DEXSTEP_TL2  // debug build only (tools/timeline_v2.py): SM-clock marks per (CTA, tile iteration), [cta][kTlIters][32] u64:
+// [0..15] consumer thread 0, [16..23] producer thread 0, [30] globaltimer ns at the mark 0 of the iteration, [31] smid
+constexpr int kTlIters = 8;
+__device__ unsigned long long* g_tl2 = nullptr;
+#define TL2_DECL unsigned long long* const tl2 = g_tl2
+#define TL2(it, k)                                                                                                 \
+  do {                                                                                                             \
+    if (tl2 != nullptr && (it) < kTlIters && (threadIdx.x == 0 || threadIdx.x == kConsThreads)) {                 \
+      unsigned long long* q_ = tl2 + ((size_t)blockIdx.x * kTlIters + (it)) * 32;                                  \
+      q_[(k)] = (unsigned long long)clock64();                                                                     \
+      if ((k) == 0) {                                                                                              \
+        unsigned long long t_;                                                                                     \
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                                                     \
+        unsigned sm_;                                                                                              \
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(sm_));                                                           \
+        q_[30] = t_;                                                                                               \
+        q_[31] = sm_;                                                                                              \
+      }                                                                                                            \
+    }                                                                                                              \
+  } while (0)
+#else
+#define TL2_DECL
+#define TL2(it, k)
+#endif
+
 // ------------------------------------------------------------------------------------------------
 // device: mbarrier / bulk-copy / named-barrier primitives
 // ------------------------------------------------------------------------------------------------
@@ -185,11 +218,26 @@ __device__ __forceinline__ void mbar_arrive(const uint32_t bar) {
 __device__ __forceinline__ void mbar_arrive_tx(const uint32_t bar, const uint32_t bytes) {
   asm volatile("{\n.reg .b64 t;\nmbarrier.arrive.expect_tx.shared::cta.b64 t, [%0], %1;\n}" ::"r"(bar), "r"(bytes) : "memory");
 }
+// try_wait with a suspend-time hint: the warp sleeps in hardware until the phase completes (or ~the hint elapses) instead
+// of spinning through the issue slots of the warps that do the work
+__device__ __forceinline__ bool mbar_try(const uint32_t bar, const uint32_t parity) {
+  uint32_t ok;
+  asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\nselp.u32 %0, 1, 0, p;\n}"
+               : "=r"(ok)
+               : "r"(bar), "r"(parity), "r"(1000000u)
+               : "memory");
+  return ok != 0;
+}
+// Bounded wait: a stage that is never filled / released (a bug, or a faulted peer warp) traps after ~2 s of SM clocks
+// instead of hanging the stream - the host sees a launch failure on its next CUDA call.
+constexpr long long kSpinLimitClocks = 4000000000ll;
 __device__ __forceinline__ void mbar_wait(const uint32_t bar, const uint32_t parity) {
-  asm volatile(
-      "{\n.reg .pred p;\nMB_WAIT:\nmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n@p bra MB_DONE;\nbra MB_WAIT;\nMB_DONE:\n}" ::"r"(bar),
-      "r"(parity)
-      : "memory");
+  if (mbar_try(bar, parity)) return;
+  const long long t0 = clock64();
+  unsigned n = 0;
+  while (!mbar_try(bar, parity)) {
+    if ((++n & 255u) == 0u && clock64() - t0 > kSpinLimitClocks) __trap();
+  }
 }
 // global -> shared bulk copy (TMA engine, SASS UBLKCP); src, dst 16-byte aligned, bytes a multiple of 16
 __device__ __forceinline__ void bulk_g2s(const uint32_t dst, const void* src, const uint32_t bytes, const uint32_t bar) {
@@ -204,45 +252,8 @@ __device__ __forceinline__ void obs_put(float* obs, const int off, const int j, 
 }
 
 // ------------------------------------------------------------------------------------------------
-// producer: one tile into one stage
+// producer side
 // ------------------------------------------------------------------------------------------------
-struct ProdCtx {
-  int rbo0, rbo1, rbo2, xoff, xrow;
-  bool p_rb0, p_rb2, p_x, is_box;
-  uint64_t e_ptr;
-  uint32_t e_dst, e_len;
-  bool e_has, e_early;
-};
-
-template <bool BG>
-__device__ __forceinline__ void prod_setup(const Post2Args& A, ProdCtx& c, const int lane, const int ptid) {
-  auto rbo = [&](int s) {
-    s = min(s, kRbW - 1);
-    const int row = s < 13 ? 0 : 1 + (s - 13) / 7;
-    return A.rb_off[row] + (s < 13 ? s : (s - 13) - (row - 1) * 7);
-  };
-  c.rbo0 = rbo(lane);
-  c.rbo1 = rbo(lane + 32);
-  c.rbo2 = rbo(lane + 64);
-  c.p_rb0 = lane < 7 || lane >= 13 || A.common;  // hand velocities feed only the common reward terms
-  c.p_rb2 = lane + 64 < kRbW;
-  c.is_box = BG && lane >= 18 && lane < 24;
-  c.p_x = c.is_box || lane < (BG ? 18 : 15);
-  c.xrow = c.is_box ? A.p.num_actors * 13 : A.p.num_contact_bodies * 3;
-  if (c.is_box) {
-    const int k = lane - 18;
-    c.xoff = A.p.box_actor * 13 + (k < 3 ? k : k + 4);
-  } else {
-    const int f = min(lane / 3, 5);
-    c.xoff = A.cf_off[f] + (lane - 3 * f);
-  }
-  c.e_has = ptid < A.n_bulk;
-  c.e_ptr = c.e_has ? A.bk_ptr[ptid] : 0ull;
-  c.e_dst = c.e_has ? (uint32_t)A.bk_dst16[ptid] * 16u : 0u;
-  c.e_len = c.e_has ? (uint32_t)A.bk_len16[ptid] * 16u : 0u;
-  c.e_early = ptid < A.n_bulk_early;
-}
-
 // generic path (ragged tile, or row bases / N that are not 16-byte friendly): every row with plain loads
 template <bool BG>
 __device__ __forceinline__ void prod_rows_ldg(const Post2Args& A, unsigned char* stage, const int e0, const int ne, const int pw,
@@ -293,7 +304,9 @@ __device__ __forceinline__ void prod_rows_ldg(const Post2Args& A, unsigned char*
 }
 
 // ------------------------------------------------------------------------------------------------
-// consumer phases (lane = env)
+// consumer side (lane = env).  Each of the 8 consumer warps owns a fixed JOB per phase: its code is straight-line
+// (loads first, then the independent per-finger / per-DOF chains side by side), so one warp covers its own latencies
+// and keeps re-running the same few hundred instructions tile after tile.
 // ------------------------------------------------------------------------------------------------
 template <bool BG>
 struct Cx {
@@ -312,49 +325,40 @@ struct Cx {
   }
 };
 
-// phase A: per-env work items, taken round-robin by the 8 consumer warps (item type is warp-uniform)
-template <bool BG>
-__device__ __forceinline__ void phase_items(const Post2Args& A, const Cx<BG>& c) {
+// ---- job: the five tip (or pad) poses: world columns, hand-frame columns (observation_encoder.py:915-986) and, for
+//      BlindGrasping, the box distances (blind_grasping_task.py:684-771, 1178-1192, 1334-1364)
+template <bool BG, bool PAD, bool WORLD, bool HANDF>
+__device__ __forceinline__ void job_poses(const Post2Args& A, const Cx<BG>& c) {
   using LY = Lay<BG>;
-  if (!c.act) return;
   const DexParams& P = A.p;
-  const DexStateBuffers& st = A.st;
-  const float dt = P.control_dt;
   const float* aos = c.aos();
-  const float* soa = c.soa();
   const float* rb = aos + LY::A_RB;
   float* wk = c.wk;
   float* obs = c.obs;
-  const size_t N = c.N, env = c.env;
-  const bool common = A.common != 0, first = A.first != 0;
-  constexpr int I_CONTACT = 10, I_DOF = 15, I_PACT = 28, I_APT = 31, I_HAND = 34, I_BOX = 35, I_PAIR = 36;
-  constexpr int N_ITEMS = BG ? I_PAIR + 5 : I_HAND + 1;
-
-  for (int it = c.cw; it < N_ITEMS; it += kConsWarps) {
-    if (it < I_CONTACT) {
-      // ---- tip / pad pose f (observation_encoder.py:915-986; blind_grasping_task.py:684-724, 1178-1192) ----
-      const int f = it;
-      const bool is_pad = f >= DEX_NUM_FINGERS;
-      const int g = is_pad ? f - DEX_NUM_FINGERS : f;
-      const float* p = rb + 13 + 7 * f;
-      const float px = p[0], py = p[1], pz = p[2], qx = p[3], qy = p[4], qz = p[5], qw = p[6];
-      const int ow = P.obs_offset[is_pad ? DEX_K_FINGERPAD_POSES_WORLD : DEX_K_FINGERTIP_POSES_WORLD];
-      if (ow >= 0) {
-        float* o = obs + ow + 7 * g;
-        o[0] = px;
-        o[1] = py;
-        o[2] = pz;
-        o[3] = qx;
-        o[4] = qy;
-        o[5] = qz;
-        o[6] = qw;
-      }
-      const int oh = P.obs_offset[is_pad ? DEX_K_FINGERPAD_POSES_HAND : DEX_K_FINGERTIP_POSES_HAND];
-      if (oh >= 0) {
-        const Quat hq{rb[3], rb[4], rb[5], rb[6]};
-        const Vec3 ph = quat_rotate_inverse(hq, Vec3{px - rb[0], py - rb[1], pz - rb[2]});
-        const Quat qh = quat_mul(quat_conj(hq), Quat{qx, qy, qz, qw});
-        float* o = obs + oh + 7 * g;
+  float p[DEX_NUM_FINGERS][7];
+#pragma unroll
+  for (int f = 0; f < DEX_NUM_FINGERS; ++f)
+#pragma unroll
+    for (int j = 0; j < 7; ++j) p[f][j] = rb[13 + (PAD ? 35 : 0) + 7 * f + j];
+  if (WORLD) {
+    const int ow = P.obs_offset[PAD ? DEX_K_FINGERPAD_POSES_WORLD : DEX_K_FINGERTIP_POSES_WORLD];
+    if (ow >= 0) {
+#pragma unroll
+      for (int f = 0; f < DEX_NUM_FINGERS; ++f)
+#pragma unroll
+        for (int j = 0; j < 7; ++j) obs[ow + 7 * f + j] = p[f][j];
+    }
+  }
+  if (HANDF) {
+    const int oh = P.obs_offset[PAD ? DEX_K_FINGERPAD_POSES_HAND : DEX_K_FINGERTIP_POSES_HAND];
+    if (oh >= 0) {
+      const Quat hq{rb[3], rb[4], rb[5], rb[6]};
+      const float hx = rb[0], hy = rb[1], hz = rb[2];
+#pragma unroll
+      for (int f = 0; f < DEX_NUM_FINGERS; ++f) {
+        const Vec3 ph = quat_rotate_inverse(hq, Vec3{p[f][0] - hx, p[f][1] - hy, p[f][2] - hz});
+        const Quat qh = quat_mul(quat_conj(hq), Quat{p[f][3], p[f][4], p[f][5], p[f][6]});
+        float* o = obs + oh + 7 * f;
         o[0] = ph.x;
         o[1] = ph.y;
         o[2] = ph.z;
@@ -363,196 +367,334 @@ __device__ __forceinline__ void phase_items(const Post2Args& A, const Cx<BG>& c)
         o[5] = qh.z;
         o[6] = qh.w;
       }
-      if (BG) {
-        const float* box = aos + LY::A_BOX;
-        const float d = norm3(px - box[0], py - box[1], pz - box[2]);
-        if (is_pad) {
-          const float hd = fabsf(pz - box[2]);
-          wk[(LY::W_PADBOX + g) * 32] = d;
-          wk[(LY::W_HDIFF + g) * 32] = hd;
-          obs_put(obs, P.obs_offset[DEX_K_FINGER_TO_OBJECT_DISTANCES], g, d);
-          obs_put(obs, P.obs_offset[DEX_K_FINGER_TO_OBJECT_HEIGHT_DIFF], g, hd);
-        } else {
-          wk[(LY::W_TIPBOX + g) * 32] = d;
-        }
-      }
-    } else if (it < I_DOF) {
-      // ---- contact sensor f (observation_encoder.py:658-735, 323-361; reward_calculator.py:183-199) ----
-      const int f = it - I_CONTACT;
-      const float* cf = aos + LY::A_CF + 3 * f;
-      const float fx = cf[0], fy = cf[1], fz = cf[2];
-      const float mag = norm3(fx, fy, fz);
-      const bool bin = mag > P.contact_binary_threshold;
-      const float dur = soa[(LY::R_CDUR + f) * 32], prevb = soa[(LY::R_PBIN + f) * 32];
-      const float ndur = (bin && prevb == 0.0f) ? 1.0f : (bin ? dur + 1.0f : 0.0f);
-      const float fb = bin ? 1.0f : 0.0f;
-      st.contact_duration_steps[f * N + env] = ndur;
-      st.prev_contact_binary[f * N + env] = fb;
-      if (st.contact_forces != nullptr) {
-        st.contact_forces[(3 * f + 0) * N + env] = fx;
-        st.contact_forces[(3 * f + 1) * N + env] = fy;
-        st.contact_forces[(3 * f + 2) * N + env] = fz;
-      }
-      wk[(LY::W_BIN + f) * 32] = fb;
-      const int ocf = P.obs_offset[DEX_K_CONTACT_FORCES];
-      if (ocf >= 0) {
-        obs[ocf + 3 * f] = fx;
-        obs[ocf + 3 * f + 1] = fy;
-        obs[ocf + 3 * f + 2] = fz;
-      }
-      obs_put(obs, P.obs_offset[DEX_K_CONTACT_FORCE_MAGNITUDE], f, mag);
-      obs_put(obs, P.obs_offset[DEX_K_CONTACT_BINARY], f, fb);
-      obs_put(obs, P.obs_offset[DEX_K_CONTACT_DURATION], f, ndur * dt);
-      if (!BG && common) {
-        const bool c_now = mag > 0.1f;  // hard-coded 0.1 N (reward_calculator.py:186)
-        const bool c_prev = first ? c_now : (c.stage[LY::OFF_U8 + f * 32 + c.lane] != 0);
-        wk[(LY::W_CHG + f) * 32] = (c_now != c_prev) ? 1.0f : 0.0f;
-        st.prev_contacts[f * N + env] = c_now ? 1 : 0;
-      }
-    } else if (it < I_PACT) {
-      // ---- DOF pair (2q, 2q+1): finite-difference velocity (observation_encoder.py:298-321), obs columns,
-      //      common-reward partial terms (reward_calculator.py:94-98,138-160: Isaac dof_vel, not the finite difference)
-      const int q = it - I_DOF;
-      const float4 pv4 = reinterpret_cast<const float4*>(c.stage + LY::OFF_DOF)[c.lane * 13 + q];
-      const float pos2[2] = {pv4.x, pv4.z}, vel2[2] = {pv4.y, pv4.w};
+    }
+  }
+  if (WORLD && !PAD) {
+    // hitting_ground inputs (step_processor.py:133-181): min over the tips in finger order
+    float min_tip_z = p[0][2];
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int d = 2 * q + h;
-        const float pos = pos2[h];
-        const float dp = pos - soa[(LY::R_PDP + d) * 32];
-        const float fd = div_rn(dp, dt);
-        st.prev_dof_pos[d * N + env] = pos;
-        float tgt = 0.0f;
-        if (!BG && A.want_tgt) tgt = reinterpret_cast<const float*>(c.stage + LY::OFF_TGT)[c.lane * 26 + d];
-        if (d < DEX_NUM_BASE) {
-          obs_put(obs, P.obs_offset[DEX_K_BASE_DOF_POS], d, pos);
-          obs_put(obs, P.obs_offset[DEX_K_BASE_DOF_VEL], d, fd);
-          if (!BG) obs_put(obs, P.obs_offset[DEX_K_BASE_DOF_TARGET], d, tgt);
-          if (BG) wk[(LY::W_BVEL + d) * 32] = fd;
-        } else {
-          const int j = d - DEX_NUM_BASE;
-          obs_put(obs, P.obs_offset[DEX_K_ALL_FINGER_DOF_POS], j, pos);
-          obs_put(obs, P.obs_offset[DEX_K_ALL_FINGER_DOF_VEL], j, fd);
-          if (!BG) obs_put(obs, P.obs_offset[DEX_K_ALL_FINGER_DOF_TARGET], j, tgt);
-          const int aj = A.dof2afj[d];
-          if (aj >= 0) {
-            obs_put(obs, P.obs_offset[DEX_K_ACTIVE_FINGER_DOF_POS], aj, pos);
-            obs_put(obs, P.obs_offset[DEX_K_ACTIVE_FINGER_DOF_VEL], aj, fd);
-            if (!BG) obs_put(obs, P.obs_offset[DEX_K_ACTIVE_FINGER_DOF_TARGET], aj, tgt);
-          }
-          if (!BG && common) {
-            const float iv = vel2[h];
-            const float pvv = first ? iv : soa[(LY::R_PFDV + j) * 32];
-            wk[(LY::W_FV2 + j) * 32] = iv * iv;
-            const float acc = iv - pvv;
-            wk[(LY::W_FA2 + j) * 32] = acc * acc;
-            const float nj = div_rn(2.0f * (pos - P.dof_lower[d]), P.dof_upper[d] - P.dof_lower[d]) - 1.0f;
-            wk[(LY::W_JL + j) * 32] = clampf(fabsf(nj) - 0.8f, 0.0f, 1.0f);
-            st.prev_finger_dof_vel[j * N + env] = iv;
-          }
-        }
-      }
-    } else if (it < I_APT) {
-      // ---- prev_actions columns (observation_encoder.py:287-296) ----
-      const int k0 = 6 * (it - I_PACT);
-      const int op = P.obs_offset[DEX_K_PREV_ACTIONS];
-      if (op >= 0 && k0 < P.num_actions) {
+    for (int f = 1; f < DEX_NUM_FINGERS; ++f) min_tip_z = fminf(min_tip_z, p[f][2]);
+    const bool hitg = P.has_height_safety && ((rb[2] < P.handbase_threshold) || (min_tip_z < P.fingertip_threshold));
+    wk[LY::W_HITG * 32] = hitg ? 1.0f : 0.0f;
+  }
+  if (BG && WORLD) {
+    const float* box = aos + LY::A_BOX;
+    const float bx = box[0], by = box[1], bz = box[2];
+    float d[DEX_NUM_FINGERS];
 #pragma unroll
-        for (int k = 0; k < 6; ++k) obs[op + k0 + k] = soa[(LY::R_PACT + k0 + k) * 32];  // num_actions is 6, 12 or 18
-      }
-    } else if (it < I_HAND) {
-      // ---- active_rule_targets <- active_prev_targets (rules.py:78-95, step_processor.py:73) ----
-      const int k0 = 6 * (it - I_APT);
-      const int o1 = P.obs_offset[DEX_K_ACTIVE_PREV_TARGETS], o2 = P.obs_offset[DEX_K_ACTIVE_RULE_TARGETS];
+    for (int f = 0; f < DEX_NUM_FINGERS; ++f) d[f] = norm3(p[f][0] - bx, p[f][1] - by, p[f][2] - bz);
+    if (!PAD) {
+      float m = d[0];
 #pragma unroll
-      for (int k = 0; k < 6; ++k) {
-        const float v = soa[(LY::R_APT + k0 + k) * 32];
-        st.active_rule_targets[(k0 + k) * N + env] = v;
-        obs_put(obs, o1, k0 + k, v);
-        obs_put(obs, o2, k0 + k, v);
-      }
-    } else if (it == I_HAND) {
-      // ---- hand pose, ARR-aligned pose (observation_encoder.py:1483-1521), hand -> box distance,
-      //      hand velocity reward terms (reward_calculator.py:100-181) ----
-      const int oh = P.obs_offset[DEX_K_HAND_POSE];
-      if (oh >= 0) {
+      for (int f = 1; f < DEX_NUM_FINGERS; ++f) m = fminf(m, d[f]);
+      wk[LY::W_MINTIPBOX * 32] = m;
+    } else {
+      const int od = P.obs_offset[DEX_K_FINGER_TO_OBJECT_DISTANCES], ohd = P.obs_offset[DEX_K_FINGER_TO_OBJECT_HEIGHT_DIFF];
+      float hd[DEX_NUM_FINGERS], dsum = 0.0f, hsum = 0.0f;
 #pragma unroll
-        for (int j = 0; j < 7; ++j) obs[oh + j] = rb[j];
+      for (int f = 0; f < DEX_NUM_FINGERS; ++f) {
+        hd[f] = fabsf(p[f][2] - bz);
+        wk[(LY::W_PADBOX + f) * 32] = d[f];
+        obs_put(obs, od, f, d[f]);
+        obs_put(obs, ohd, f, hd[f]);
+        dsum += d[f];
+        hsum += hd[f];
       }
-      const int oa = P.obs_offset[DEX_K_HAND_POSE_ARR_ALIGNED];
-      if (oa >= 0) {
-        const float sh = 0.7071067811865476f;
-        const Quat qa = quat_mul(Quat{rb[3], rb[4], rb[5], rb[6]}, Quat{-0.0f, -sh, -0.0f, sh});
-        obs[oa + 0] = rb[0];
-        obs[oa + 1] = rb[1];
-        obs[oa + 2] = rb[2];
-        obs[oa + 3] = qa.x;
-        obs[oa + 4] = qa.y;
-        obs[oa + 5] = qa.z;
-        obs[oa + 6] = qa.w;
-      }
-      if (BG) {
-        const float* box = aos + LY::A_BOX;
-        const float hb = norm3(rb[0] - box[0], rb[1] - box[1], rb[2] - box[2]);
-        wk[LY::W_HANDBOX * 32] = hb;
-        obs_put(obs, P.obs_offset[DEX_K_HAND_TO_OBJECT_DISTANCE], 0, hb);
-      }
-      if (!BG && common) {
-        float hv[3], ha[3], phv[3], pha[3];
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-          hv[k] = rb[7 + k];
-          ha[k] = rb[10 + k];
-          phv[k] = first ? hv[k] : soa[(LY::R_PHV + k) * 32];
-          pha[k] = first ? ha[k] : soa[(LY::R_PHA + k) * 32];
-          st.prev_hand_vel[k * N + env] = hv[k];
-          st.prev_hand_ang_vel[k * N + env] = ha[k];
-        }
-        wk[(LY::W_RHAND + 0) * 32] = expf(-0.2f * norm3(hv[0], hv[1], hv[2]));
-        wk[(LY::W_RHAND + 1) * 32] = expf(-0.2f * norm3(ha[0], ha[1], ha[2]));
-        wk[(LY::W_RHAND + 2) * 32] = expf(-0.5f * norm3(hv[0] - phv[0], hv[1] - phv[1], hv[2] - phv[2]));
-        wk[(LY::W_RHAND + 3) * 32] = expf(-0.5f * norm3(ha[0] - pha[0], ha[1] - pha[1], ha[2] - pha[2]));
-      }
-    } else if (BG && it == I_BOX) {
-      // ---- pad centroid, box stability inputs (blind_grasping_task.py:746-771, 1334-1364) ----
-      const float* box = aos + LY::A_BOX;
+      const float avg_h = div_rn(hsum, 5.0f);  // blind_grasping_task.py:702-724
+      wk[LY::W_AVGHDIFF * 32] = avg_h;
+      obs_put(obs, P.obs_offset[DEX_K_AVG_FINGER_TO_OBJECT_DISTANCE], 0, div_rn(dsum, 5.0f));
+      obs_put(obs, P.obs_offset[DEX_K_AVG_FINGER_TO_OBJECT_HEIGHT_DIFF], 0, avg_h);
+      // pad centroid + the height / centroid part of _evaluate_pregrasp_quality (:746-771, :1334-1364)
       float cen[3];
 #pragma unroll
-      for (int k = 0; k < 3; ++k) cen[k] = (rb[13 + 35 + k] + rb[13 + 35 + 7 + k] + rb[13 + 35 + 14 + k]) / 3.0f;
+      for (int k = 0; k < 3; ++k) cen[k] = (p[0][k] + p[1][k] + p[2][k]) / 3.0f;
       const int oc = P.obs_offset[DEX_K_FIRST_THREE_FINGERPAD_CENTROID];
-      const int opos = P.obs_offset[DEX_K_OBJECT_POS], ovel = P.obs_offset[DEX_K_OBJECT_VEL];
 #pragma unroll
-      for (int k = 0; k < 3; ++k) {
-        obs_put(obs, oc, k, cen[k]);
-        obs_put(obs, opos, k, box[k]);
-        obs_put(obs, ovel, k, box[3 + k]);
+      for (int k = 0; k < 3; ++k) obs_put(obs, oc, k, cen[k]);
+      const float cdist = norm3(cen[0] - bx, cen[1] - by, cen[2] - bz);
+      wk[LY::W_CDIST * 32] = cdist;
+      const bool h_ok = (hd[0] <= P.height_tolerance) && (hd[1] <= P.height_tolerance) && (hd[2] <= P.height_tolerance);
+      wk[LY::W_HCOK * 32] = (h_ok && (cdist <= P.centroid_tolerance)) ? 1.0f : 0.0f;
+    }
+  }
+}
+
+// ---- job: the five contact sensors (observation_encoder.py:658-735, 323-361; reward_calculator.py:183-199) and, for
+//      BlindGrasping, the box contact flag and the box stability inputs
+template <bool BG>
+__device__ __forceinline__ void job_contacts(const Post2Args& A, const Cx<BG>& c) {
+  using LY = Lay<BG>;
+  const DexParams& P = A.p;
+  const DexStateBuffers& st = A.st;
+  const float* aos = c.aos();
+  const float* soa = c.soa();
+  float* wk = c.wk;
+  float* obs = c.obs;
+  const size_t N = c.N, env = c.env;
+  const float dt = P.control_dt;
+  float cf[DEX_NUM_FINGERS][3], dur[DEX_NUM_FINGERS], prevb[DEX_NUM_FINGERS];
+#pragma unroll
+  for (int f = 0; f < DEX_NUM_FINGERS; ++f) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) cf[f][k] = aos[LY::A_CF + 3 * f + k];
+    dur[f] = soa[(LY::R_CDUR + f) * 32];
+    prevb[f] = soa[(LY::R_PBIN + f) * 32];
+  }
+  const int ocf = P.obs_offset[DEX_K_CONTACT_FORCES], om = P.obs_offset[DEX_K_CONTACT_FORCE_MAGNITUDE];
+  const int ob = P.obs_offset[DEX_K_CONTACT_BINARY], od = P.obs_offset[DEX_K_CONTACT_DURATION];
+  const bool common = !BG && A.common != 0, first = A.first != 0;
+#pragma unroll
+  for (int f = 0; f < DEX_NUM_FINGERS; ++f) {
+    const float mag = norm3(cf[f][0], cf[f][1], cf[f][2]);
+    const bool bin = mag > P.contact_binary_threshold;
+    const float ndur = (bin && prevb[f] == 0.0f) ? 1.0f : (bin ? dur[f] + 1.0f : 0.0f);
+    const float fb = bin ? 1.0f : 0.0f;
+    st.contact_duration_steps[f * N + env] = ndur;
+    st.prev_contact_binary[f * N + env] = fb;
+    if (st.contact_forces != nullptr) {
+#pragma unroll
+      for (int k = 0; k < 3; ++k) st.contact_forces[(3 * f + k) * N + env] = cf[f][k];
+    }
+    wk[(LY::W_BIN + f) * 32] = fb;
+    if (ocf >= 0) {
+#pragma unroll
+      for (int k = 0; k < 3; ++k) obs[ocf + 3 * f + k] = cf[f][k];
+    }
+    obs_put(obs, om, f, mag);
+    obs_put(obs, ob, f, fb);
+    obs_put(obs, od, f, ndur * dt);
+    if (common) {
+      const bool c_now = mag > 0.1f;  // hard-coded 0.1 N (reward_calculator.py:186)
+      const bool c_prev = first ? c_now : (c.stage[LY::OFF_U8 + f * 32 + c.lane] != 0);
+      wk[(LY::W_CHG + f) * 32] = (c_now != c_prev) ? 1.0f : 0.0f;
+      st.prev_contacts[f * N + env] = c_now ? 1 : 0;
+    }
+  }
+  if (BG) {
+    const float* cfb = aos + LY::A_CF + 15;
+    const float* box = aos + LY::A_BOX;
+    const float b[6] = {box[0], box[1], box[2], box[3], box[4], box[5]};
+    wk[LY::W_BOXHAS * 32] = (norm3(cfb[0], cfb[1], cfb[2]) > P.contact_binary_threshold) ? 1.0f : 0.0f;
+    const float drift = norm3(b[0] - soa[(LY::R_BOX0 + 0) * 32], b[1] - soa[(LY::R_BOX0 + 1) * 32], b[2] - soa[(LY::R_BOX0 + 2) * 32]);
+    const float vmag = norm3(b[3], b[4], b[5]);
+    wk[LY::W_DRIFT * 32] = drift;
+    wk[LY::W_VMAG * 32] = vmag;
+    wk[LY::W_SOK * 32] = ((drift <= P.position_drift_tolerance) && (vmag <= P.velocity_tolerance)) ? 1.0f : 0.0f;
+    const int opos = P.obs_offset[DEX_K_OBJECT_POS], ovel = P.obs_offset[DEX_K_OBJECT_VEL];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      obs_put(obs, opos, k, b[k]);
+      obs_put(obs, ovel, k, b[3 + k]);
+    }
+  }
+}
+
+// ---- job: hand pose, ARR-aligned pose (observation_encoder.py:1483-1521), hand -> box distance, hand velocity
+//      reward terms (reward_calculator.py:100-181), episode time (dexhand_base.py:703-712: PRE-increment count)
+template <bool BG>
+__device__ __forceinline__ void job_hand(const Post2Args& A, const Cx<BG>& c) {
+  using LY = Lay<BG>;
+  const DexParams& P = A.p;
+  const DexStateBuffers& st = A.st;
+  const float* aos = c.aos();
+  const float* soa = c.soa();
+  const float* rb = aos + LY::A_RB;
+  float* wk = c.wk;
+  float* obs = c.obs;
+  float h[7];
+#pragma unroll
+  for (int j = 0; j < 7; ++j) h[j] = rb[j];
+  obs_put(obs, P.obs_offset[DEX_K_EPISODE_TIME], 0, (float)c.i64lo(LY::I_STEP) * P.control_dt);
+  const int oh = P.obs_offset[DEX_K_HAND_POSE];
+  if (oh >= 0) {
+#pragma unroll
+    for (int j = 0; j < 7; ++j) obs[oh + j] = h[j];
+  }
+  const int oa = P.obs_offset[DEX_K_HAND_POSE_ARR_ALIGNED];
+  if (oa >= 0) {
+    const float sh = 0.7071067811865476f;
+    const Quat qa = quat_mul(Quat{h[3], h[4], h[5], h[6]}, Quat{-0.0f, -sh, -0.0f, sh});
+    obs[oa + 0] = h[0];
+    obs[oa + 1] = h[1];
+    obs[oa + 2] = h[2];
+    obs[oa + 3] = qa.x;
+    obs[oa + 4] = qa.y;
+    obs[oa + 5] = qa.z;
+    obs[oa + 6] = qa.w;
+  }
+  if (BG) {
+    const float* box = aos + LY::A_BOX;
+    const float hb = norm3(h[0] - box[0], h[1] - box[1], h[2] - box[2]);
+    wk[LY::W_BOXFAR * 32] = (hb > P.max_box_distance) ? 1.0f : 0.0f;
+    obs_put(obs, P.obs_offset[DEX_K_HAND_TO_OBJECT_DISTANCE], 0, hb);
+  }
+  if (!BG && A.common) {
+    const bool first = A.first != 0;
+    float hv[3], ha[3], phv[3], pha[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      hv[k] = rb[7 + k];
+      ha[k] = rb[10 + k];
+      phv[k] = first ? hv[k] : soa[(LY::R_PHV + k) * 32];
+      pha[k] = first ? ha[k] : soa[(LY::R_PHA + k) * 32];
+      st.prev_hand_vel[k * c.N + c.env] = hv[k];
+      st.prev_hand_ang_vel[k * c.N + c.env] = ha[k];
+    }
+    wk[(LY::W_RHAND + 0) * 32] = expf(-0.2f * norm3(hv[0], hv[1], hv[2]));
+    wk[(LY::W_RHAND + 1) * 32] = expf(-0.2f * norm3(ha[0], ha[1], ha[2]));
+    wk[(LY::W_RHAND + 2) * 32] = expf(-0.5f * norm3(hv[0] - phv[0], hv[1] - phv[1], hv[2] - phv[2]));
+    wk[(LY::W_RHAND + 3) * 32] = expf(-0.5f * norm3(ha[0] - pha[0], ha[1] - pha[1], ha[2] - pha[2]));
+  }
+}
+
+// ---- job: the ten pad pair distances, triu order (blind_grasping_task.py:726-771)
+template <bool BG>
+__device__ __forceinline__ void job_pairs(const Post2Args& A, const Cx<BG>& c) {
+  using LY = Lay<BG>;
+  const int op = A.p.obs_offset[DEX_K_FINGERPAD_DISTANCES];
+  if (op < 0) return;
+  const float* rb = c.aos() + LY::A_RB;
+  float q[DEX_NUM_FINGERS][3];
+#pragma unroll
+  for (int f = 0; f < DEX_NUM_FINGERS; ++f)
+#pragma unroll
+    for (int k = 0; k < 3; ++k) q[f][k] = rb[13 + 35 + 7 * f + k];
+  int k = 0;
+#pragma unroll
+  for (int a = 0; a < DEX_NUM_FINGERS; ++a)
+#pragma unroll
+    for (int b = a + 1; b < DEX_NUM_FINGERS; ++b, ++k)
+      c.obs[op + k] = norm3(q[a][0] - q[b][0], q[a][1] - q[b][1], q[a][2] - q[b][2]);
+}
+
+// ---- job: DOFs [D0, D1): finite-difference velocity (observation_encoder.py:298-321), obs columns, common-reward
+//      partial terms (reward_calculator.py:94-98,138-160: Isaac dof_vel, not the finite difference)
+template <bool BG, int D0, int D1>
+__device__ __forceinline__ void job_dofs(const Post2Args& A, const Cx<BG>& c) {
+  using LY = Lay<BG>;
+  static_assert(D0 % 2 == 0 && D1 % 2 == 0, "whole (pos, vel) pairs of DOFs");
+  const DexParams& P = A.p;
+  const DexStateBuffers& st = A.st;
+  const float* soa = c.soa();
+  float* wk = c.wk;
+  float* obs = c.obs;
+  const size_t N = c.N, env = c.env;
+  const float dt = P.control_dt;
+  constexpr int ND = D1 - D0;
+  float pos[ND], vel[ND], prev[ND], tgt[ND];
+  const float4* d4 = reinterpret_cast<const float4*>(c.stage + LY::OFF_DOF) + c.lane * 13;
+#pragma unroll
+  for (int q = 0; q < ND / 2; ++q) {
+    const float4 v = d4[D0 / 2 + q];
+    pos[2 * q] = v.x;
+    vel[2 * q] = v.y;
+    pos[2 * q + 1] = v.z;
+    vel[2 * q + 1] = v.w;
+  }
+  const bool want_tgt = !BG && A.want_tgt != 0;
+#pragma unroll
+  for (int i = 0; i < ND; ++i) {
+    prev[i] = soa[(LY::R_PDP + D0 + i) * 32];
+    tgt[i] = want_tgt ? reinterpret_cast<const float*>(c.stage + LY::OFF_TGT)[c.lane * 26 + D0 + i] : 0.0f;
+  }
+  const bool common = !BG && A.common != 0, first = A.first != 0;
+  const int o_bp = P.obs_offset[DEX_K_BASE_DOF_POS], o_bv = P.obs_offset[DEX_K_BASE_DOF_VEL], o_bt = P.obs_offset[DEX_K_BASE_DOF_TARGET];
+  const int o_ap = P.obs_offset[DEX_K_ALL_FINGER_DOF_POS], o_av = P.obs_offset[DEX_K_ALL_FINGER_DOF_VEL],
+            o_at = P.obs_offset[DEX_K_ALL_FINGER_DOF_TARGET];
+  const int o_fp = P.obs_offset[DEX_K_ACTIVE_FINGER_DOF_POS], o_fv = P.obs_offset[DEX_K_ACTIVE_FINGER_DOF_VEL],
+            o_ft = P.obs_offset[DEX_K_ACTIVE_FINGER_DOF_TARGET];
+#pragma unroll
+  for (int i = 0; i < ND; ++i) {
+    const int d = D0 + i;
+    const float fd = div_rn(pos[i] - prev[i], dt);
+    st.prev_dof_pos[d * N + env] = pos[i];
+    if (d < DEX_NUM_BASE) {
+      obs_put(obs, o_bp, d, pos[i]);
+      obs_put(obs, o_bv, d, fd);
+      if (!BG) obs_put(obs, o_bt, d, tgt[i]);
+      if (BG) wk[(LY::W_BVEL + d) * 32] = fd;
+    } else {
+      const int j = d - DEX_NUM_BASE;
+      obs_put(obs, o_ap, j, pos[i]);
+      obs_put(obs, o_av, j, fd);
+      if (!BG) obs_put(obs, o_at, j, tgt[i]);
+      const int aj = A.dof2afj[d];
+      if (aj >= 0) {
+        obs_put(obs, o_fp, aj, pos[i]);
+        obs_put(obs, o_fv, aj, fd);
+        if (!BG) obs_put(obs, o_ft, aj, tgt[i]);
       }
-      wk[LY::W_CDIST * 32] = norm3(cen[0] - box[0], cen[1] - box[1], cen[2] - box[2]);
-      wk[LY::W_DRIFT * 32] = norm3(box[0] - soa[(LY::R_BOX0 + 0) * 32], box[1] - soa[(LY::R_BOX0 + 1) * 32],
-                                   box[2] - soa[(LY::R_BOX0 + 2) * 32]);
-      wk[LY::W_VMAG * 32] = norm3(box[3], box[4], box[5]);
-      const float* cfb = aos + LY::A_CF + 15;
-      wk[LY::W_BOXHAS * 32] = (norm3(cfb[0], cfb[1], cfb[2]) > P.contact_binary_threshold) ? 1.0f : 0.0f;
-    } else if (BG) {
-      // ---- two pad pair distances, triu order (blind_grasping_task.py:726-771) ----
-      const int op = P.obs_offset[DEX_K_FINGERPAD_DISTANCES];
-      if (op >= 0) {
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          const int k = 2 * (it - I_PAIR) + h;
-          // k -> (a, b): rows of the strict upper triangle of a 5x5 matrix start at 0, 4, 7, 9
-          const int a = (k >= 4) + (k >= 7) + (k >= 9);
-          const int b = k - (a == 0 ? 0 : a == 1 ? 4 : a == 2 ? 7 : 9) + a + 1;
-          const float* pa = rb + 13 + 35 + 7 * a;
-          const float* pb = rb + 13 + 35 + 7 * b;
-          obs[op + k] = norm3(pa[0] - pb[0], pa[1] - pb[1], pa[2] - pb[2]);
-        }
+      if (common) {
+        const float iv = vel[i];
+        const float pvv = first ? iv : soa[(LY::R_PFDV + j) * 32];
+        wk[(LY::W_FV2 + j) * 32] = iv * iv;
+        const float acc = iv - pvv;
+        wk[(LY::W_FA2 + j) * 32] = acc * acc;
+        const float nj = div_rn(2.0f * (pos[i] - P.dof_lower[d]), P.dof_upper[d] - P.dof_lower[d]) - 1.0f;
+        wk[(LY::W_JL + j) * 32] = clampf(fabsf(nj) - 0.8f, 0.0f, 1.0f);
+        st.prev_finger_dof_vel[j * N + env] = iv;
       }
     }
   }
 }
 
-// one common reward term (reward_calculator.py:66-221); BaseTask, phase B
+// ---- job: prev_actions columns (observation_encoder.py:287-296); active_rule_targets <- active_prev_targets
+//      (rules.py:78-95, step_processor.py:73)
+template <bool BG>
+__device__ __forceinline__ void job_copies(const Post2Args& A, const Cx<BG>& c) {
+  using LY = Lay<BG>;
+  const DexParams& P = A.p;
+  const float* soa = c.soa();
+  float* obs = c.obs;
+  float apt[DEX_NUM_ACTIVE];
+#pragma unroll
+  for (int k = 0; k < DEX_NUM_ACTIVE; ++k) apt[k] = soa[(LY::R_APT + k) * 32];
+  const int op = P.obs_offset[DEX_K_PREV_ACTIONS];
+  if (op >= 0) {
+#pragma unroll
+    for (int k0 = 0; k0 < DEX_NUM_ACTIVE; k0 += 6) {  // num_actions is 6, 12 or 18
+      if (k0 < P.num_actions) {
+        float v[6];
+#pragma unroll
+        for (int k = 0; k < 6; ++k) v[k] = soa[(LY::R_PACT + k0 + k) * 32];
+#pragma unroll
+        for (int k = 0; k < 6; ++k) obs[op + k0 + k] = v[k];
+      }
+    }
+  }
+  const int o1 = P.obs_offset[DEX_K_ACTIVE_PREV_TARGETS], o2 = P.obs_offset[DEX_K_ACTIVE_RULE_TARGETS];
+  float* art = A.st.active_rule_targets + c.env;
+#pragma unroll
+  for (int k = 0; k < DEX_NUM_ACTIVE; ++k) {
+    art[(size_t)k * c.N] = apt[k];
+    obs_put(obs, o1, k, apt[k]);
+    obs_put(obs, o2, k, apt[k]);
+  }
+}
+
+// phase A: everything that depends only on the staged tile
+template <bool BG>
+__device__ __forceinline__ void phase_a(const Post2Args& A, const Cx<BG>& c) {
+  if (!c.act) return;
+  switch (c.cw) {
+    case 0: job_poses<BG, false, true, BG>(A, c); break;   // tips: world (+ hand frame for BlindGrasping configs that ask)
+    case 1: job_poses<BG, true, true, BG>(A, c); break;    // pads
+    case 2: job_contacts<BG>(A, c); break;
+    case 3: job_hand<BG>(A, c); break;
+    case 4:
+      if (BG) job_pairs<BG>(A, c);
+      else job_poses<BG, false, false, true>(A, c);         // BaseTask: tip poses in the hand frame
+      break;
+    case 5: job_dofs<BG, 0, 14>(A, c); break;
+    case 6: job_dofs<BG, 14, 26>(A, c); break;
+    default:
+      job_copies<BG>(A, c);
+      if (!BG) job_poses<BG, true, false, true>(A, c);      // BaseTask: pad poses in the hand frame
+      break;
+  }
+}
+
+// one common reward term (reward_calculator.py:66-221); BaseTask
 template <bool BG>
 __device__ __forceinline__ float common_term(const Post2Args& A, const Cx<BG>& c, const int i) {
   using LY = Lay<BG>;
@@ -599,13 +741,12 @@ __device__ __forceinline__ float common_term(const Post2Args& A, const Cx<BG>& c
 
 // one BlindGrasping task term (blind_grasping_task.py:980-1208); phase C (after the FSM)
 template <bool BG>
-__device__ __forceinline__ float task_term(const Post2Args& A, const Cx<BG>& c, const int i) {
+__device__ __forceinline__ float task_term(const Post2Args& A, const Cx<BG>& c, const int i, const int stage) {
   using LY = Lay<BG>;
   const DexParams& P = A.p;
   const float* wk = c.wk;
   const float* aos = c.aos();
   const float* rb = aos + LY::A_RB;
-  const int stage = __float_as_int(wk[LY::W_STAGE * 32]);
   const float m1 = (stage == 1) ? 1.0f : 0.0f, m2 = (stage == 2) ? 1.0f : 0.0f, m3 = (stage == 3) ? 1.0f : 0.0f;
   switch (i) {
     case DEX_R_S1_HEIGHT_ALIGNMENT: return expf(-P.height_alignment_decay * wk[LY::W_AVGHDIFF * 32]) * m1;
@@ -643,7 +784,8 @@ __device__ __forceinline__ float task_term(const Post2Args& A, const Cx<BG>& c, 
     case DEX_R_S3_GRASP_DURATION:
       return clampf(div_rn(wk[LY::W_GRASPDUR * 32], P.contact_duration_threshold_s), 0.0f, 1.0f) * m3;
     // completion bonuses :1025-1048 (transition and not failed), penetration :1194-1208
-    case DEX_R_S1_COMPLETION: return (wk[LY::W_J2 * 32] != 0.0f && wk[LY::W_QUALOK * 32] != 0.0f) ? 1.0f : 0.0f;
+    case DEX_R_S1_COMPLETION:
+      return (wk[LY::W_J2 * 32] != 0.0f && wk[LY::W_HCOK * 32] != 0.0f && wk[LY::W_SOK * 32] != 0.0f) ? 1.0f : 0.0f;
     case DEX_R_S2_COMPLETION: return (wk[LY::W_J3 * 32] != 0.0f && wk[LY::W_GRASP * 32] != 0.0f) ? 1.0f : 0.0f;
     default:  // DEX_R_PENETRATION_PENALTY
       return fmaxf(P.penetration_threshold - wk[LY::W_MINTIPBOX * 32], 0.0f) * P.penetration_depth_scale;
@@ -662,9 +804,9 @@ __device__ __forceinline__ void emit_term(const Post2Args& A, const Cx<BG>& c, c
   c.wk[(Lay<BG>::W_WGT + i) * 32] = rw;
 }
 
-// phase B: the per-env scalar part, split over the consumer warps (warp-uniform job index)
+// phase B (BlindGrasping): the two scalar chains that the reward terms and the termination wait for
 template <bool BG>
-__device__ __forceinline__ void phase_scalar(const Post2Args& A, const Cx<BG>& c) {
+__device__ __forceinline__ void phase_b(const Post2Args& A, const Cx<BG>& c) {
   using LY = Lay<BG>;
   if (!c.act) return;
   const DexParams& P = A.p;
@@ -672,118 +814,70 @@ __device__ __forceinline__ void phase_scalar(const Post2Args& A, const Cx<BG>& c
   const float dt = P.control_dt;
   float* wk = c.wk;
   float* obs = c.obs;
-  const float* aos = c.aos();
   const float* soa = c.soa();
-  const float* rb = aos + LY::A_RB;
   const size_t env = c.env;
-  if (BG) {
-    if (c.cw == 0) {
-      // ---- finger-box contacts (blind_grasping_task.py:773-833), success duration (:626-648) ----
-      const bool box_has = wk[LY::W_BOXHAS * 32] != 0.0f;
-      bool fbc[DEX_NUM_FINGERS];
-      int n_on_box = 0;
+  if (c.cw == 0) {
+    // ---- finger-box contacts (blind_grasping_task.py:773-833), success duration (:626-648) ----
+    const bool box_has = wk[LY::W_BOXHAS * 32] != 0.0f;
+    const float box_z = c.aos()[LY::A_BOX + 2];
+    const int sds_old = c.i64lo(LY::I_SDS);
+    bool fbc[DEX_NUM_FINGERS];
+    int n_on_box = 0;
 #pragma unroll
-      for (int f = 0; f < DEX_NUM_FINGERS; ++f) {
-        fbc[f] = (wk[(LY::W_BIN + f) * 32] != 0.0f) && box_has && (wk[(LY::W_PADBOX + f) * 32] < P.proximity_threshold);
-        n_on_box += fbc[f] ? 1 : 0;
-      }
-      const bool thumb_c = fbc[0], others_c = fbc[1] || fbc[2] || fbc[3] || fbc[4];
-      const bool grasp = thumb_c && others_c;
-      const float ft = thumb_c ? 1.0f : 0.0f, fo = others_c ? 1.0f : 0.0f, fg = grasp ? 1.0f : 0.0f;
-      wk[LY::W_THUMB * 32] = ft;
-      wk[LY::W_OTHERS * 32] = fo;
-      wk[LY::W_GRASP * 32] = fg;
-      obs_put(obs, P.obs_offset[DEX_K_THUMB_CONTACT], 0, ft);
-      obs_put(obs, P.obs_offset[DEX_K_OTHER_FINGERS_CONTACT], 0, fo);
-      obs_put(obs, P.obs_offset[DEX_K_GRASP_STATE], 0, fg);
-      const float box_z = aos[LY::A_BOX + 2];
-      const bool cond = (box_z > P.success_height_threshold) && (n_on_box >= P.min_fingers_for_grasp);
-      const int sds = cond ? c.i64lo(LY::I_SDS) + 1 : 0;
-      st.success_duration_steps[env] = (long long)sds;
-      st.success_conditions_met[env] = cond ? 1 : 0;
-      const float gd = (float)sds * dt;
-      wk[LY::W_SDS * 32] = __int_as_float(sds);
-      wk[LY::W_GRASPDUR * 32] = gd;
-      obs_put(obs, P.obs_offset[DEX_K_GRASP_DURATION], 0, gd);
-    } else if (c.cw == 1) {
-      // ---- stage FSM :835-956 (plain fp32 accumulation of (float)control_dt decides the transition step) ----
-      int stage = c.i64lo(LY::I_STAGE);
-      float tis = soa[LY::R_TIS * 32] + dt;
-      float scd = soa[LY::R_SCD * 32];
-      const bool b0 = wk[(LY::W_BIN + 0) * 32] != 0.0f;
-      const bool bo = (wk[(LY::W_BIN + 1) * 32] != 0.0f) || (wk[(LY::W_BIN + 2) * 32] != 0.0f) ||
-                      (wk[(LY::W_BIN + 3) * 32] != 0.0f) || (wk[(LY::W_BIN + 4) * 32] != 0.0f);
-      const bool thumb_other = b0 && bo;
-      if (stage == 2) scd = thumb_other ? scd + dt : 0.0f;
-      const bool s1_done = (stage == 1) && (tis >= P.stage1_duration);
-      const bool s2_done = (stage == 2) && ((scd >= P.stage2_contact_success_threshold) || (tis >= P.stage2_duration));
-      if (s1_done) stage = 2;
-      if (s2_done) stage = 3;
-      if (s1_done || s2_done) {
-        tis = 0.0f;
-        scd = 0.0f;
-      }
-      st.current_stage[env] = (long long)stage;
-      st.time_in_stage[env] = tis;
-      st.stage_contact_duration[env] = scd;
-      st.just_transitioned_to_stage2[env] = s1_done ? 1 : 0;
-      st.just_transitioned_to_stage3[env] = s2_done ? 1 : 0;
-      float prog = 0.0f;  // :958-978
-      if (stage == 1) prog = clampf(div_rn(tis, P.stage1_duration), 0.0f, 1.0f);
-      if (stage == 2) prog = clampf(div_rn(tis, P.stage2_duration), 0.0f, 1.0f);
-      if (stage == 3) prog = 1.0f;
-      wk[LY::W_STAGE * 32] = __int_as_float(stage);
-      wk[LY::W_J2 * 32] = s1_done ? 1.0f : 0.0f;
-      wk[LY::W_J3 * 32] = s2_done ? 1.0f : 0.0f;
-      obs_put(obs, P.obs_offset[DEX_K_CURRENT_STAGE], 0, (float)stage);
-      obs_put(obs, P.obs_offset[DEX_K_TIME_IN_STAGE], 0, tis);
-      obs_put(obs, P.obs_offset[DEX_K_STAGE_PROGRESS], 0, prog);
-    } else if (c.cw == 2) {
-      // ---- minima, criteria inputs (step_processor.py:133-181, blind_grasping_task.py:1290-1364) ----
-      float min_tip_z = rb[13 + 2], min_tip_box = wk[LY::W_TIPBOX * 32];
-#pragma unroll
-      for (int f = 1; f < DEX_NUM_FINGERS; ++f) {
-        min_tip_z = fminf(min_tip_z, rb[13 + 7 * f + 2]);
-        min_tip_box = fminf(min_tip_box, wk[(LY::W_TIPBOX + f) * 32]);
-      }
-      const bool hitg = P.has_height_safety && ((rb[2] < P.handbase_threshold) || (min_tip_z < P.fingertip_threshold));
-      const bool h_ok = (wk[(LY::W_HDIFF + 0) * 32] <= P.height_tolerance) && (wk[(LY::W_HDIFF + 1) * 32] <= P.height_tolerance) &&
-                        (wk[(LY::W_HDIFF + 2) * 32] <= P.height_tolerance);
-      const bool c_ok = wk[LY::W_CDIST * 32] <= P.centroid_tolerance;
-      const bool s_ok = (wk[LY::W_DRIFT * 32] <= P.position_drift_tolerance) && (wk[LY::W_VMAG * 32] <= P.velocity_tolerance);
-      wk[LY::W_MINTIPBOX * 32] = min_tip_box;
-      wk[LY::W_HITG * 32] = hitg ? 1.0f : 0.0f;
-      wk[LY::W_BOXFAR * 32] = (wk[LY::W_HANDBOX * 32] > P.max_box_distance) ? 1.0f : 0.0f;
-      wk[LY::W_QUALOK * 32] = (h_ok && c_ok && s_ok) ? 1.0f : 0.0f;
-    } else if (c.cw == 3) {
-      // ---- averages (blind_grasping_task.py:702-724), episode time (dexhand_base.py:703-712: PRE-increment count) ----
-      float dsum = 0.0f, hsum = 0.0f;
-#pragma unroll
-      for (int f = 0; f < DEX_NUM_FINGERS; ++f) {
-        dsum += wk[(LY::W_PADBOX + f) * 32];
-        hsum += wk[(LY::W_HDIFF + f) * 32];
-      }
-      const float avg_h = div_rn(hsum, 5.0f);
-      wk[LY::W_AVGHDIFF * 32] = avg_h;
-      obs_put(obs, P.obs_offset[DEX_K_AVG_FINGER_TO_OBJECT_DISTANCE], 0, div_rn(dsum, 5.0f));
-      obs_put(obs, P.obs_offset[DEX_K_AVG_FINGER_TO_OBJECT_HEIGHT_DIFF], 0, avg_h);
-      obs_put(obs, P.obs_offset[DEX_K_EPISODE_TIME], 0, (float)c.i64lo(LY::I_STEP) * dt);
+    for (int f = 0; f < DEX_NUM_FINGERS; ++f) {
+      fbc[f] = (wk[(LY::W_BIN + f) * 32] != 0.0f) && box_has && (wk[(LY::W_PADBOX + f) * 32] < P.proximity_threshold);
+      n_on_box += fbc[f] ? 1 : 0;
     }
-  } else {
-    if (c.cw == 2) {
-      float min_tip_z = rb[13 + 2];
-#pragma unroll
-      for (int f = 1; f < DEX_NUM_FINGERS; ++f) min_tip_z = fminf(min_tip_z, rb[13 + 7 * f + 2]);
-      const bool hitg = P.has_height_safety && ((rb[2] < P.handbase_threshold) || (min_tip_z < P.fingertip_threshold));
-      wk[LY::W_HITG * 32] = hitg ? 1.0f : 0.0f;
-      obs_put(obs, P.obs_offset[DEX_K_EPISODE_TIME], 0, (float)c.i64lo(LY::I_STEP) * dt);
-    } else {
-      // common reward terms over the seven other warps (0, 1, 3..7)
-      for (int i = (c.cw < 2 ? c.cw : c.cw - 1); i < DEX_NUM_COMMON_TERMS; i += kConsWarps - 1) {
-        if (A.p.reward_weight[i] == 0.0f) continue;  // reward_calculator.py:247-251: zero-weight terms are not materialised
-        emit_term<BG>(A, c, i, common_term<BG>(A, c, i));
-      }
+    const bool thumb_c = fbc[0], others_c = fbc[1] || fbc[2] || fbc[3] || fbc[4];
+    const bool grasp = thumb_c && others_c;
+    const float ft = thumb_c ? 1.0f : 0.0f, fo = others_c ? 1.0f : 0.0f, fg = grasp ? 1.0f : 0.0f;
+    wk[LY::W_THUMB * 32] = ft;
+    wk[LY::W_OTHERS * 32] = fo;
+    wk[LY::W_GRASP * 32] = fg;
+    obs_put(obs, P.obs_offset[DEX_K_THUMB_CONTACT], 0, ft);
+    obs_put(obs, P.obs_offset[DEX_K_OTHER_FINGERS_CONTACT], 0, fo);
+    obs_put(obs, P.obs_offset[DEX_K_GRASP_STATE], 0, fg);
+    const bool cond = (box_z > P.success_height_threshold) && (n_on_box >= P.min_fingers_for_grasp);
+    const int sds = cond ? sds_old + 1 : 0;
+    st.success_duration_steps[env] = (long long)sds;
+    st.success_conditions_met[env] = cond ? 1 : 0;
+    const float gd = (float)sds * dt;
+    wk[LY::W_SDS * 32] = __int_as_float(sds);
+    wk[LY::W_GRASPDUR * 32] = gd;
+    obs_put(obs, P.obs_offset[DEX_K_GRASP_DURATION], 0, gd);
+  } else if (c.cw == 1) {
+    // ---- stage FSM :835-956 (plain fp32 accumulation of (float)control_dt decides the transition step) ----
+    int stage = c.i64lo(LY::I_STAGE);
+    float tis = soa[LY::R_TIS * 32] + dt;
+    float scd = soa[LY::R_SCD * 32];
+    const bool b0 = wk[(LY::W_BIN + 0) * 32] != 0.0f;
+    const bool bo = (wk[(LY::W_BIN + 1) * 32] != 0.0f) || (wk[(LY::W_BIN + 2) * 32] != 0.0f) ||
+                    (wk[(LY::W_BIN + 3) * 32] != 0.0f) || (wk[(LY::W_BIN + 4) * 32] != 0.0f);
+    const bool thumb_other = b0 && bo;
+    if (stage == 2) scd = thumb_other ? scd + dt : 0.0f;
+    const bool s1_done = (stage == 1) && (tis >= P.stage1_duration);
+    const bool s2_done = (stage == 2) && ((scd >= P.stage2_contact_success_threshold) || (tis >= P.stage2_duration));
+    if (s1_done) stage = 2;
+    if (s2_done) stage = 3;
+    if (s1_done || s2_done) {
+      tis = 0.0f;
+      scd = 0.0f;
     }
+    st.current_stage[env] = (long long)stage;
+    st.time_in_stage[env] = tis;
+    st.stage_contact_duration[env] = scd;
+    st.just_transitioned_to_stage2[env] = s1_done ? 1 : 0;
+    st.just_transitioned_to_stage3[env] = s2_done ? 1 : 0;
+    float prog = 0.0f;  // :958-978
+    if (stage == 1) prog = clampf(div_rn(tis, P.stage1_duration), 0.0f, 1.0f);
+    if (stage == 2) prog = clampf(div_rn(tis, P.stage2_duration), 0.0f, 1.0f);
+    if (stage == 3) prog = 1.0f;
+    wk[LY::W_STAGE * 32] = __int_as_float(stage);
+    wk[LY::W_J2 * 32] = s1_done ? 1.0f : 0.0f;
+    wk[LY::W_J3 * 32] = s2_done ? 1.0f : 0.0f;
+    obs_put(obs, P.obs_offset[DEX_K_CURRENT_STAGE], 0, (float)stage);
+    obs_put(obs, P.obs_offset[DEX_K_TIME_IN_STAGE], 0, tis);
+    obs_put(obs, P.obs_offset[DEX_K_STAGE_PROGRESS], 0, prog);
   }
 }
 
@@ -808,11 +902,12 @@ __device__ __forceinline__ unsigned phase_combine(const Post2Args& A, const Cx<B
     if (BG) {
       const bool grasp = wk[LY::W_GRASP * 32] != 0.0f;
       const bool j2 = wk[LY::W_J2 * 32] != 0.0f, j3 = wk[LY::W_J3 * 32] != 0.0f;
+      const bool qual_ok = (wk[LY::W_HCOK * 32] != 0.0f) && (wk[LY::W_SOK * 32] != 0.0f);
       const int stage = __float_as_int(wk[LY::W_STAGE * 32]);
       const int sds = __float_as_int(wk[LY::W_SDS * 32]);
       crit[DEX_C_GRASP_LIFT_SUCCESS] = sds >= P.contact_duration_threshold_steps;
       crit[DEX_C_BOX_TOO_FAR] = wk[LY::W_BOXFAR * 32] != 0.0f;
-      const bool pregrasp_failed = j2 && (wk[LY::W_QUALOK * 32] == 0.0f);  // _evaluate_pregrasp_quality :1334-1364
+      const bool pregrasp_failed = j2 && !qual_ok;  // _evaluate_pregrasp_quality :1334-1364
       const bool contact_failed = j3 && !grasp;
       const bool grasp_lost = (stage == 3) && !grasp;
       crit[DEX_C_STAGE1_PREGRASP_FAILED] = pregrasp_failed;
@@ -894,12 +989,14 @@ __device__ __forceinline__ void phase_total(const Post2Args& A, const Cx<BG>& c,
   if (!c.act) return;
   const DexParams& P = A.p;
   const float* wk = c.wk;
+  constexpr int NT = BG ? DEX_NUM_REWARD_TERMS : DEX_NUM_COMMON_TERMS;
+  float wv[NT];
+#pragma unroll
+  for (int i = 0; i < NT; ++i) wv[i] = wk[(LY::W_WGT + i) * 32];  // terms with weight 0 hold stale values: skipped below
   float total = 0.0f;
 #pragma unroll
-  for (int i = 0; i < DEX_NUM_REWARD_TERMS; ++i) {
-    if (!BG && i >= DEX_NUM_COMMON_TERMS) break;
-    if (P.reward_weight[i] != 0.0f) total += wk[(LY::W_WGT + i) * 32];  // dict order: common, then task
-  }
+  for (int i = 0; i < NT; ++i)
+    if (P.reward_weight[i] != 0.0f) total += wv[i];  // dict order: common, then task
   const bool t_success = cls & 1u, t_failure = cls & 2u, t_timeout = cls & 4u;
   const float rs = t_success ? P.success_reward : 0.0f;
   const float rf = t_failure ? P.failure_reward : 0.0f;
@@ -916,6 +1013,38 @@ __device__ __forceinline__ void phase_total(const Post2Args& A, const Cx<BG>& c,
   A.out.rew_buf[c.env] = rew;
 }
 
+// obs tile -> obs_buf for the 32-column chunks in `chunks`: the env rows are spread over NW warps (this one is number w),
+// lane = column: every global store is one full 128-byte request.  Row pointers are formed once; the chunk offset is
+// an immediate.
+template <int NW>
+__device__ __forceinline__ void copy_obs(const float* s_obs, float* g_tile, const int W, const int WP, const int ne,
+                                         const unsigned chunks, const int w, const int lane) {
+  constexpr int R = (32 + NW - 1) / NW;
+  const float* sp[R];
+  float* gp[R];
+  bool ok[R];
+#pragma unroll
+  for (int i = 0; i < R; ++i) {
+    const int row = w + NW * i;
+    ok[i] = row < ne;
+    sp[i] = s_obs + row * WP + lane;
+    gp[i] = g_tile + (size_t)row * W + lane;
+  }
+#pragma unroll
+  for (int ch = 0; ch < 8; ++ch) {  // obs_dim <= 256
+    if (!((chunks >> ch) & 1u)) continue;
+    if (32 * ch + lane < W) {
+      float v[R];
+#pragma unroll
+      for (int i = 0; i < R; ++i)
+        if (ok[i]) v[i] = sp[i][32 * ch];
+#pragma unroll
+      for (int i = 0; i < R; ++i)
+        if (ok[i]) gp[i][32 * ch] = v[i];
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------------
 // the kernel
 // ------------------------------------------------------------------------------------------------
@@ -925,6 +1054,7 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
   extern __shared__ __align__(128) unsigned char smem2[];
   __shared__ __align__(8) unsigned long long s_bar[2 * kStages];  // full[0..], empty[0..]
   __shared__ float s_reset_u[32 * kConsWarps];
+  __shared__ int s_rbo[kRbW + 1];  // gathered rigid slot -> float offset inside one env's [NB,13] block
   __shared__ unsigned long long s_rng_step;
   __shared__ unsigned s_rbits;
   __shared__ int s_epi_warp[kConsWarps];
@@ -941,7 +1071,9 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
       const unsigned stamp = ((unsigned)rs + 1u) & 0xffffu;
       const volatile unsigned long long* last =
           reinterpret_cast<const volatile unsigned long long*>(A.ep.tile_records) + (size_t)(A.tiles - 1);  // plane 0
+      const long long t0 = clock64();
       while ((unsigned)(last[0] >> 48) != stamp) {
+        if (clock64() - t0 > kSpinLimitClocks) __trap();  // bounded: see mbar_wait
       }
       s_rng_step = rs;
     }
@@ -964,8 +1096,14 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
+  if (tid < kRbW) {  // one slot per thread: the integer division happens once per CTA, not per producer lane
+    const int s = tid;
+    const int row = s < 13 ? 0 : 1 + (s - 13) / 7;
+    s_rbo[s] = A.rb_off[row] + (s < 13 ? s : (s - 13) - (row - 1) * 7);
+  }
   __syncthreads();
   pdl_launch_dependents();
+  TL2_DECL;
   float* const wk_base = reinterpret_cast<float*>(smem2 + kStages * LY::STAGE_BYTES);
   float* const s_obs = wk_base + LY::W_COUNT * 32;
   const int tiles = A.tiles, workers = A.workers;
@@ -973,9 +1111,29 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
   if (warp >= kConsWarps) {
     // =========================== producer warps ===========================
     const int pw = warp - kConsWarps, ptid = tid - kConsThreads;
-    ProdCtx pc;
-    prod_setup<BG>(A, pc, lane, ptid);
-    const int nb13 = A.p.num_bodies * 13;
+    // this thread's bulk entry (one row / tile array per producer thread)
+    const bool e_has = ptid < A.n_bulk, e_early = ptid < A.n_bulk_early;
+    const char* const e_ptr = e_has ? reinterpret_cast<const char*>(A.bk_ptr[ptid]) : nullptr;
+    const uint32_t e_dst = e_has ? (uint32_t)A.bk_dst16[ptid] * 16u : 0u;
+    const uint32_t e_len = e_has ? (uint32_t)A.bk_len16[ptid] * 16u : 0u;
+    // scattered Isaac Gym rows: lane = gathered float (rigid slots lane, lane + 32, lane + 64; contact / box slot lane)
+    const int rbo0 = s_rbo[lane], rbo1 = s_rbo[lane + 32], rbo2 = s_rbo[min(lane + 64, kRbW - 1)];
+    const bool p_rb0 = lane < 7 || lane >= 13 || A.common;  // hand velocities feed only the common reward terms
+    const bool p_rb2 = lane + 64 < kRbW;
+    const bool is_box = BG && lane >= 18 && lane < 24;
+    const bool p_x = is_box || lane < (BG ? 18 : 15);
+    const int xrow = is_box ? A.p.num_actors * 13 : A.p.num_contact_bodies * 3;
+    int xoff;
+    if (is_box) {
+      const int k = lane - 18;
+      xoff = A.p.box_actor * 13 + (k < 3 ? k : k + 4);
+    } else {
+      const int f = min(lane / 3, 5);
+      xoff = A.cf_off[f] + (lane - 3 * f);
+    }
+    const float* const x_base = (is_box ? (const float*)A.sim.actor_root_state : A.sim.net_contact_force) + xoff;
+    const size_t nb13 = (size_t)A.p.num_bodies * 13;
+    const size_t rb_step = kProdWarps * nb13, x_step = (size_t)kProdWarps * xrow;
     const bool early = (A.flags & DEX_FLAG_EARLY_SIM_LOADS) != 0;
     constexpr int R = 32 / kProdWarps;  // env rows per producer warp
     int it = 0;
@@ -984,46 +1142,63 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
       const int e0 = tile * 32, ne = min(32, A.n - e0);
       unsigned char* stage = smem2 + s * LY::STAGE_BYTES;
       const uint32_t sst = s32(stage), fb = bar_full + 8 * s;
+      TL2(it, 16);
       if (use > 0) mbar_wait(bar_empty + 8 * s, (unsigned)(use - 1) & 1u);
+      TL2(it, 17);
       const bool bulk = A.bulk_ok && ne == 32;  // CTA-uniform
       if (it == 0 && !early) pdl_wait();
-      if (bulk && pc.e_has && pc.e_early) bulk_g2s(sst + pc.e_dst, reinterpret_cast<const char*>(pc.e_ptr) + (size_t)tile * pc.e_len, pc.e_len, fb);
-      // ---- scattered Isaac Gym rows: warp pw takes env rows pw, pw+4, ..; consecutive lanes = consecutive floats ----
+      if (bulk && e_has && e_early) bulk_g2s(sst + e_dst, e_ptr + (size_t)tile * e_len, e_len, fb);
+      if (bulk && e_has && !e_early && !(it == 0 && early)) bulk_g2s(sst + e_dst, e_ptr + (size_t)tile * e_len, e_len, fb);
+      // ---- scattered rows: warp pw takes env rows pw, pw+4, ..; consecutive lanes = consecutive floats ----
       float v[R][4];
       {
-        const float* g_rb = A.sim.rigid_body_state + (size_t)(e0 + pw) * nb13;
-        const float* gx = (pc.is_box ? (const float*)A.sim.actor_root_state : A.sim.net_contact_force) + (size_t)(e0 + pw) * pc.xrow + pc.xoff;
+        const float* q0 = A.sim.rigid_body_state + (size_t)(e0 + pw) * nb13;
+        const float* qx = x_base + (size_t)(e0 + pw) * xrow;
+        if (ne == 32) {
 #pragma unroll
-        for (int i = 0; i < R; ++i) {
-          if (pw + kProdWarps * i < ne) {
-            const float* rbp = g_rb + (size_t)i * (kProdWarps * nb13);
-            if (pc.p_rb0) v[i][0] = __ldg(rbp + pc.rbo0);
-            v[i][1] = __ldg(rbp + pc.rbo1);
-            if (pc.p_rb2) v[i][2] = __ldg(rbp + pc.rbo2);
-            if (pc.p_x) v[i][3] = pc.is_box ? gx[(size_t)i * (kProdWarps * pc.xrow)] : __ldg(gx + (size_t)i * (kProdWarps * pc.xrow));
+          for (int i = 0; i < R; ++i) {
+            if (p_rb0) v[i][0] = __ldg(q0 + rbo0);
+            v[i][1] = __ldg(q0 + rbo1);
+            if (p_rb2) v[i][2] = __ldg(q0 + rbo2);
+            if (p_x) v[i][3] = *qx;  // actor_root_state rows are rewritten by the fused reset of this kernel: plain load
+            q0 += rb_step;
+            qx += x_step;
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < R; ++i) {
+            if (pw + kProdWarps * i < ne) {
+              if (p_rb0) v[i][0] = __ldg(q0 + rbo0);
+              v[i][1] = __ldg(q0 + rbo1);
+              if (p_rb2) v[i][2] = __ldg(q0 + rbo2);
+              if (p_x) v[i][3] = *qx;
+            }
+            q0 += rb_step;
+            qx += x_step;
           }
         }
       }
-      if (it == 0 && early) pdl_wait();  // everything above touched only kernel parameters and the sim tensors
-      if (bulk) {
-        if (pc.e_has && !pc.e_early) bulk_g2s(sst + pc.e_dst, reinterpret_cast<const char*>(pc.e_ptr) + (size_t)tile * pc.e_len, pc.e_len, fb);
-      } else {
-        prod_rows_ldg<BG>(A, stage, e0, ne, pw, lane);
+      TL2(it, 18);
+      if (it == 0 && early) {
+        pdl_wait();  // everything above touched only kernel parameters and the sim tensors
+        if (bulk && e_has && !e_early) bulk_g2s(sst + e_dst, e_ptr + (size_t)tile * e_len, e_len, fb);
       }
+      if (!bulk) prod_rows_ldg<BG>(A, stage, e0, ne, pw, lane);
       {
-        float* aos = reinterpret_cast<float*>(stage + LY::OFF_AOS) + pw * LY::SA + lane;
+        float* a = reinterpret_cast<float*>(stage + LY::OFF_AOS) + pw * LY::SA + lane;
 #pragma unroll
         for (int i = 0; i < R; ++i) {
-          if (pw + kProdWarps * i < ne) {
-            float* a = aos + i * (kProdWarps * LY::SA);
-            if (pc.p_rb0) a[LY::A_RB] = v[i][0];
+          if (ne == 32 || pw + kProdWarps * i < ne) {
+            if (p_rb0) a[LY::A_RB] = v[i][0];
             a[LY::A_RB + 32] = v[i][1];
-            if (pc.p_rb2) a[LY::A_RB + 64] = v[i][2];
-            if (pc.p_x) a[LY::A_CF] = v[i][3];
+            if (p_rb2) a[LY::A_RB + 64] = v[i][2];
+            if (p_x) a[LY::A_CF] = v[i][3];
           }
+          a += kProdWarps * LY::SA;
         }
       }
       __syncwarp();
+      TL2(it, 19);
       if (lane == 0) {
         if (pw == 0 && bulk)
           mbar_arrive_tx(fb, A.tx_bytes);
@@ -1044,7 +1219,9 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
   unsigned stamp = 0;
   uint64_t rng_step = 0;
   const int W = A.p.obs_dim, WP = A.wp;
-  const int nchunk = (W + 31) >> 5;
+  const unsigned all_chunks = (W >= 256) ? 0xffu : ((1u << ((W + 31) >> 5)) - 1u);
+  const unsigned late_chunks = BG ? (A.obs_late & all_chunks) : all_chunks;  // BaseTask has no phase B: one copy at the end
+  const unsigned early_chunks = all_chunks & ~late_chunks;
   int it = 0;
   for (int tile = blockIdx.x; tile < tiles; tile += workers, ++it) {
     const int s = it & 1, use = it >> 1;
@@ -1053,58 +1230,63 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
     c.act = lane < c.ne;
     c.env = (size_t)c.e0 + (c.act ? lane : 0);
     c.stage = smem2 + s * LY::STAGE_BYTES;
+    float* const g_obs = A.out.obs_buf + (size_t)c.e0 * W;
+    TL2(it, 0);
     mbar_wait(bar_full + 8 * s, (unsigned)use & 1u);
+    TL2(it, 1);
     // Philox step counter == stamp of this step's tile records: read once per CTA, behind the first full barrier
     // (i.e. behind the producers' griddepcontrol.wait; the epilogue CTA advances it only after every record of this
-    // launch has been published), by one thread, and parked while the items run
+    // launch has been published), by one thread, and parked while phase A runs
     unsigned long long rs_tmp = 0ull;
     if (it == 0 && tid == 0) rs_tmp = A.st.rng_step ? *reinterpret_cast<const volatile unsigned long long*>(A.st.rng_step) : A.step;
 
-    phase_items<BG>(A, c);
+    phase_a<BG>(A, c);
     if (it == 0 && tid == 0) s_rng_step = rs_tmp;
+    TL2(it, 2);
     cons_sync();
+    TL2(it, 3);
     if (it == 0) {
       rng_step = s_rng_step;
       stamp = ((unsigned)rng_step + 1u) & 0xffffu;
     }
-    phase_scalar<BG>(A, c);
-    cons_sync();
+    if (BG) {
+      // phase B: warps 0 / 1 run the two scalar chains, the other six send off the obs chunks that are already final
+      if (warp < 2)
+        phase_b<BG>(A, c);
+      else
+        copy_obs<kConsWarps - 2>(s_obs, g_obs, W, WP, c.ne, early_chunks, warp - 2, lane);
+      TL2(it, 4);
+      cons_sync();
+      TL2(it, 5);
+    }
+    // phase C: warp 0 termination + tile record; warps 1..7 the reward terms
     unsigned cls = 0;
     if (warp == 0) {
       cls = phase_combine<BG>(A, c, stamp, &s_rbits);
-    } else if (BG) {
-      if (c.act) {
+    } else if (c.act) {
+      if (BG) {
+        const int stage_now = __float_as_int(c.wk[LY::W_STAGE * 32]);
         for (int i = DEX_NUM_COMMON_TERMS + (warp - 1); i < DEX_NUM_REWARD_TERMS; i += kConsWarps - 1) {
+          if (A.p.reward_weight[i] == 0.0f) continue;  // reward_calculator.py:247-251: zero-weight terms are not materialised
+          emit_term<BG>(A, c, i, task_term<BG>(A, c, i, stage_now));
+        }
+      } else {
+        for (int i = warp - 1; i < DEX_NUM_COMMON_TERMS; i += kConsWarps - 1) {
           if (A.p.reward_weight[i] == 0.0f) continue;
-          emit_term<BG>(A, c, i, task_term<BG>(A, c, i));
+          emit_term<BG>(A, c, i, common_term<BG>(A, c, i));
         }
       }
     }
     // the raw stage is not read after this point: hand it back to the producers
     __syncwarp();
+    TL2(it, 6);
     cons_sync();
+    TL2(it, 7);
     if (lane == 0) mbar_arrive(bar_empty + 8 * s);
     if (warp == 0) phase_total<BG>(A, c, cls);
-    // ---- obs tile -> obs_buf: row-per-warp, 128 B coalesced ----
-    {
-      float* g0 = A.out.obs_buf + (size_t)c.e0 * W;
-      for (int ch = 0; ch < nchunk; ++ch) {
-        const int col = 32 * ch + lane;
-        if (col < W) {
-          float v[4];
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const int row = warp + kConsWarps * i;
-            if (row < c.ne) v[i] = s_obs[row * WP + col];
-          }
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const int row = warp + kConsWarps * i;
-            if (row < c.ne) g0[(size_t)row * W + col] = v[i];
-          }
-        }
-      }
-    }
+    TL2(it, 8);
+    copy_obs<kConsWarps>(s_obs, g_obs, W, WP, c.ne, late_chunks, warp, lane);
+    TL2(it, 9);
     // ---- fused reset of the finished envs (dexhand_base.py:743-756): one warp per env ----
     {
       unsigned mask = s_rbits;  // written by warp 0 before the barrier above
@@ -1116,7 +1298,9 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
         }
       }
     }
+    TL2(it, 10);
     cons_sync();  // work block, obs tile and s_rbits are reused by the next tile
+    TL2(it, 11);
   }
 }
 
