@@ -23,11 +23,9 @@
 namespace {
 namespace pp2 {
 
-constexpr int kConsWarps = 8, kProdWarps = 4;
-constexpr int kConsThreads = kConsWarps * 32, kProdThreads = kProdWarps * 32;
-constexpr int kThreads = kConsThreads + kProdThreads;
-constexpr int kStages = 2;
-constexpr int kMaxBulk = kProdThreads;  // one bulk entry per producer thread
+constexpr int kMaxPairs = 4;   // (compute warp, producer warp) pairs per CTA; each pair owns one tile slot
+constexpr int kMaxBulk = 128;  // bulk entries of one tile (<= 4 per producer lane)
+constexpr int kEpiThreads = 256;
 
 enum : int { BK_F32 = 0, BK_I64 = 1, BK_U8 = 2, BK_DOF = 3, BK_TGT = 4 };
 
@@ -51,16 +49,6 @@ struct Lay {
   static constexpr int A_RB = 0, A_CF = 83, A_BOX = 101;     // hand row 13 | 5 tips x 7 | 5 pads x 7 ; contacts ; box
   static constexpr int SA = BG ? 107 : 99;
   static constexpr int STAGE_BYTES = (OFF_AOS + 32 * SA * 4 + 127) / 128 * 128;
-  // work block: values that cross a warp or a phase, [field][32] floats
-  static constexpr int W_BIN = 0, W_PADBOX = 5;           // 5 each
-  static constexpr int W_CDIST = 10, W_DRIFT = 11, W_VMAG = 12, W_BOXHAS = 13, W_BOXFAR = 14;
-  static constexpr int W_BVEL = 15;                       // 6: finite-difference base velocity
-  static constexpr int W_GRASP = 21, W_THUMB = 22, W_OTHERS = 23, W_GRASPDUR = 24, W_SDS = 25, W_STAGE = 26, W_J2 = 27,
-                       W_J3 = 28;
-  static constexpr int W_HITG = 29, W_HCOK = 30, W_SOK = 31, W_MINTIPBOX = 32, W_AVGHDIFF = 33;
-  static constexpr int W_CHG = 34, W_RHAND = 39, W_FV2 = 43, W_FA2 = 63, W_JL = 83;  // BaseTask (common rewards)
-  static constexpr int W_WGT = BG ? 34 : 103;  // 26 weighted reward terms
-  static constexpr int W_COUNT = W_WGT + DEX_NUM_REWARD_TERMS;
 };
 
 struct Post2Args {
@@ -75,7 +63,7 @@ struct Post2Args {
   const float* uniforms;
   uint64_t seed, step;
   // ---- derived on the host (build_post2) ----
-  int32_t tiles, workers;
+  int32_t tiles, workers, nc;             // nc = compute warps (= producer warps = tile slots) per CTA
   int32_t common, first, want_tgt;
   int32_t bulk_ok, n_bulk, n_bulk_early;  // entries [0, n_bulk_early) touch sim tensors only
   uint32_t tx_bytes;                      // bytes of all bulk entries of a full tile
@@ -176,7 +164,7 @@ inline int build_post2(Post2Args& a) {
   a.n_bulk = k;
   a.tx_bytes = tx;
   a.bulk_ok = aligned ? 1 : 0;
-  a.smem_bytes = (uint32_t)(kStages * LY::STAGE_BYTES + LY::W_COUNT * 128 + 32 * a.wp * 4);
+  a.smem_bytes = 0;  // set by the launcher: nc x (stage + obs tile)
   return DEX_OK;
 }
 
@@ -187,7 +175,7 @@ __device__ unsigned long long* g_tl2 = nullptr;
 #define TL2_DECL unsigned long long* const tl2 = g_tl2
 #define TL2(it, k)                                                                                                 \
   do {                                                                                                             \
-    if (tl2 != nullptr && (it) < kTlIters && (threadIdx.x == 0 || threadIdx.x == kConsThreads)) {                 \
+    if (tl2 != nullptr && (it) < kTlIters && (threadIdx.x == 0 || threadIdx.x == 32 * A.nc)) {                 \
       unsigned long long* q_ = tl2 + ((size_t)blockIdx.x * kTlIters + (it)) * 32;                                  \
       q_[(k)] = (unsigned long long)clock64();                                                                     \
       if ((k) == 0) {                                                                                              \
@@ -245,25 +233,21 @@ __device__ __forceinline__ void bulk_g2s(const uint32_t dst, const void* src, co
                "r"(bytes), "r"(bar)
                : "memory");
 }
-__device__ __forceinline__ void cons_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kConsThreads) : "memory"); }
-
 __device__ __forceinline__ void obs_put(float* obs, const int off, const int j, const float v) {
   if (off >= 0) obs[off + j] = v;
 }
 
 // ------------------------------------------------------------------------------------------------
-// producer side
+// producer side: one producer warp fills the slot of its compute warp
 // ------------------------------------------------------------------------------------------------
 // generic path (ragged tile, or row bases / N that are not 16-byte friendly): every row with plain loads
-template <bool BG>
-__device__ __forceinline__ void prod_rows_ldg(const Post2Args& A, unsigned char* stage, const int e0, const int ne, const int pw,
-                                              const int lane) {
+__device__ __forceinline__ void prod_rows_ldg(const Post2Args& A, unsigned char* stage, const int e0, const int ne, const int lane) {
   const bool act = lane < ne;
-  for (int k0 = pw; k0 < A.n_bulk; k0 += kProdWarps * 4) {
-    unsigned long long v[4];
+  for (int k0 = 0; k0 < A.n_bulk; k0 += 8) {
+    unsigned long long v[8];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int k = k0 + kProdWarps * u;
+    for (int u = 0; u < 8; ++u) {
+      const int k = k0 + u;
       v[u] = 0ull;
       if (k < A.n_bulk) {
         const int kind = A.bk_kind[k];
@@ -278,8 +262,8 @@ __device__ __forceinline__ void prod_rows_ldg(const Post2Args& A, unsigned char*
       }
     }
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int k = k0 + kProdWarps * u;
+    for (int u = 0; u < 8; ++u) {
+      const int k = k0 + u;
       if (k < A.n_bulk && act) {
         const int kind = A.bk_kind[k];
         unsigned char* dst = stage + (size_t)A.bk_dst16[k] * 16;
@@ -299,21 +283,21 @@ __device__ __forceinline__ void prod_rows_ldg(const Post2Args& A, unsigned char*
     const int per = kind == BK_DOF ? 52 : 26;
     const float* src = reinterpret_cast<const float*>(A.bk_ptr[k]) + (size_t)e0 * per;
     float* dst = reinterpret_cast<float*>(stage + (size_t)A.bk_dst16[k] * 16);
-    for (int i = pw * 32 + lane; i < ne * per; i += kProdThreads) dst[i] = src[i];
+    for (int i = lane; i < ne * per; i += 32) dst[i] = src[i];
   }
 }
 
 // ------------------------------------------------------------------------------------------------
-// consumer side (lane = env).  Each of the 8 consumer warps owns a fixed JOB per phase: its code is straight-line
-// (loads first, then the independent per-finger / per-DOF chains side by side), so one warp covers its own latencies
-// and keeps re-running the same few hundred instructions tile after tile.
+// compute side: ONE warp runs the whole per-env program for its tile, lane = env.  Every compute warp of the SM
+// executes the same straight-line instruction stream (instruction fetch is shared, no intra-tile barrier exists),
+// intermediates stay in registers, and the compiler schedules the independent chains (5 fingers, 26 DOFs, 10 pad
+// pairs, 16 reward terms) of one env side by side.
 // ------------------------------------------------------------------------------------------------
 template <bool BG>
 struct Cx {
   const unsigned char* stage;
-  float* wk;   // work block + lane
   float* obs;  // obs tile row of this lane's env
-  int lane, cw, e0, ne;
+  int lane, e0, ne;
   bool act;
   size_t N, env;
   __device__ __forceinline__ const float* soa() const { return reinterpret_cast<const float*>(stage) + lane; }
@@ -325,85 +309,90 @@ struct Cx {
   }
 };
 
-// ---- job: the five tip (or pad) poses: world columns, hand-frame columns (observation_encoder.py:915-986) and, for
+// values that flow between the parts of the per-env program (registers)
+struct Mid {
+  float bin[DEX_NUM_FINGERS], padbox[DEX_NUM_FINGERS];
+  float cdist, drift, vmag, min_tip_box, avg_hdiff, graspdur;
+  float bvel[DEX_NUM_BASE];
+  bool boxhas, boxfar, hitg, hcok, sok, grasp, thumb, others, j2, j3;
+  int sds, stage;
+  float fv2, fa2, jl, chg, rhand[4], min_tip_z;  // BaseTask: ordered partial sums of the common reward terms
+  float wgt[DEX_NUM_REWARD_TERMS];
+};
+
+// ---- the five tip (or pad) poses: world columns, hand-frame columns (observation_encoder.py:915-986) and, for
 //      BlindGrasping, the box distances (blind_grasping_task.py:684-771, 1178-1192, 1334-1364)
-template <bool BG, bool PAD, bool WORLD, bool HANDF>
-__device__ __forceinline__ void job_poses(const Post2Args& A, const Cx<BG>& c) {
+template <bool BG, bool PAD>
+__device__ __forceinline__ void part_poses(const Post2Args& A, const Cx<BG>& c, Mid& m) {
   using LY = Lay<BG>;
   const DexParams& P = A.p;
   const float* aos = c.aos();
   const float* rb = aos + LY::A_RB;
-  float* wk = c.wk;
   float* obs = c.obs;
   float p[DEX_NUM_FINGERS][7];
 #pragma unroll
   for (int f = 0; f < DEX_NUM_FINGERS; ++f)
 #pragma unroll
     for (int j = 0; j < 7; ++j) p[f][j] = rb[13 + (PAD ? 35 : 0) + 7 * f + j];
-  if (WORLD) {
-    const int ow = P.obs_offset[PAD ? DEX_K_FINGERPAD_POSES_WORLD : DEX_K_FINGERTIP_POSES_WORLD];
-    if (ow >= 0) {
+  const int ow = P.obs_offset[PAD ? DEX_K_FINGERPAD_POSES_WORLD : DEX_K_FINGERTIP_POSES_WORLD];
+  if (ow >= 0) {
 #pragma unroll
-      for (int f = 0; f < DEX_NUM_FINGERS; ++f)
+    for (int f = 0; f < DEX_NUM_FINGERS; ++f)
 #pragma unroll
-        for (int j = 0; j < 7; ++j) obs[ow + 7 * f + j] = p[f][j];
+      for (int j = 0; j < 7; ++j) obs[ow + 7 * f + j] = p[f][j];
+  }
+  const int oh = P.obs_offset[PAD ? DEX_K_FINGERPAD_POSES_HAND : DEX_K_FINGERTIP_POSES_HAND];
+  if (oh >= 0) {
+    const Quat hq{rb[3], rb[4], rb[5], rb[6]};
+    const float hx = rb[0], hy = rb[1], hz = rb[2];
+#pragma unroll
+    for (int f = 0; f < DEX_NUM_FINGERS; ++f) {
+      const Vec3 ph = quat_rotate_inverse(hq, Vec3{p[f][0] - hx, p[f][1] - hy, p[f][2] - hz});
+      const Quat qh = quat_mul(quat_conj(hq), Quat{p[f][3], p[f][4], p[f][5], p[f][6]});
+      float* o = obs + oh + 7 * f;
+      o[0] = ph.x;
+      o[1] = ph.y;
+      o[2] = ph.z;
+      o[3] = qh.x;
+      o[4] = qh.y;
+      o[5] = qh.z;
+      o[6] = qh.w;
     }
   }
-  if (HANDF) {
-    const int oh = P.obs_offset[PAD ? DEX_K_FINGERPAD_POSES_HAND : DEX_K_FINGERTIP_POSES_HAND];
-    if (oh >= 0) {
-      const Quat hq{rb[3], rb[4], rb[5], rb[6]};
-      const float hx = rb[0], hy = rb[1], hz = rb[2];
-#pragma unroll
-      for (int f = 0; f < DEX_NUM_FINGERS; ++f) {
-        const Vec3 ph = quat_rotate_inverse(hq, Vec3{p[f][0] - hx, p[f][1] - hy, p[f][2] - hz});
-        const Quat qh = quat_mul(quat_conj(hq), Quat{p[f][3], p[f][4], p[f][5], p[f][6]});
-        float* o = obs + oh + 7 * f;
-        o[0] = ph.x;
-        o[1] = ph.y;
-        o[2] = ph.z;
-        o[3] = qh.x;
-        o[4] = qh.y;
-        o[5] = qh.z;
-        o[6] = qh.w;
-      }
-    }
-  }
-  if (WORLD && !PAD) {
+  if (!PAD) {
     // hitting_ground inputs (step_processor.py:133-181): min over the tips in finger order
-    float min_tip_z = p[0][2];
+    float mz = p[0][2];
 #pragma unroll
-    for (int f = 1; f < DEX_NUM_FINGERS; ++f) min_tip_z = fminf(min_tip_z, p[f][2]);
-    const bool hitg = P.has_height_safety && ((rb[2] < P.handbase_threshold) || (min_tip_z < P.fingertip_threshold));
-    wk[LY::W_HITG * 32] = hitg ? 1.0f : 0.0f;
+    for (int f = 1; f < DEX_NUM_FINGERS; ++f) mz = fminf(mz, p[f][2]);
+    m.min_tip_z = mz;
+    m.hitg = P.has_height_safety && ((rb[2] < P.handbase_threshold) || (mz < P.fingertip_threshold));
   }
-  if (BG && WORLD) {
+  if (BG) {
     const float* box = aos + LY::A_BOX;
     const float bx = box[0], by = box[1], bz = box[2];
     float d[DEX_NUM_FINGERS];
 #pragma unroll
     for (int f = 0; f < DEX_NUM_FINGERS; ++f) d[f] = norm3(p[f][0] - bx, p[f][1] - by, p[f][2] - bz);
     if (!PAD) {
-      float m = d[0];
+      float mb = d[0];
 #pragma unroll
-      for (int f = 1; f < DEX_NUM_FINGERS; ++f) m = fminf(m, d[f]);
-      wk[LY::W_MINTIPBOX * 32] = m;
+      for (int f = 1; f < DEX_NUM_FINGERS; ++f) mb = fminf(mb, d[f]);
+      m.min_tip_box = mb;
     } else {
       const int od = P.obs_offset[DEX_K_FINGER_TO_OBJECT_DISTANCES], ohd = P.obs_offset[DEX_K_FINGER_TO_OBJECT_HEIGHT_DIFF];
       float hd[DEX_NUM_FINGERS], dsum = 0.0f, hsum = 0.0f;
 #pragma unroll
       for (int f = 0; f < DEX_NUM_FINGERS; ++f) {
         hd[f] = fabsf(p[f][2] - bz);
-        wk[(LY::W_PADBOX + f) * 32] = d[f];
+        m.padbox[f] = d[f];
         obs_put(obs, od, f, d[f]);
         obs_put(obs, ohd, f, hd[f]);
         dsum += d[f];
         hsum += hd[f];
       }
-      const float avg_h = div_rn(hsum, 5.0f);  // blind_grasping_task.py:702-724
-      wk[LY::W_AVGHDIFF * 32] = avg_h;
+      m.avg_hdiff = div_rn(hsum, 5.0f);  // blind_grasping_task.py:702-724
       obs_put(obs, P.obs_offset[DEX_K_AVG_FINGER_TO_OBJECT_DISTANCE], 0, div_rn(dsum, 5.0f));
-      obs_put(obs, P.obs_offset[DEX_K_AVG_FINGER_TO_OBJECT_HEIGHT_DIFF], 0, avg_h);
+      obs_put(obs, P.obs_offset[DEX_K_AVG_FINGER_TO_OBJECT_HEIGHT_DIFF], 0, m.avg_hdiff);
       // pad centroid + the height / centroid part of _evaluate_pregrasp_quality (:746-771, :1334-1364)
       float cen[3];
 #pragma unroll
@@ -411,24 +400,32 @@ __device__ __forceinline__ void job_poses(const Post2Args& A, const Cx<BG>& c) {
       const int oc = P.obs_offset[DEX_K_FIRST_THREE_FINGERPAD_CENTROID];
 #pragma unroll
       for (int k = 0; k < 3; ++k) obs_put(obs, oc, k, cen[k]);
-      const float cdist = norm3(cen[0] - bx, cen[1] - by, cen[2] - bz);
-      wk[LY::W_CDIST * 32] = cdist;
+      m.cdist = norm3(cen[0] - bx, cen[1] - by, cen[2] - bz);
       const bool h_ok = (hd[0] <= P.height_tolerance) && (hd[1] <= P.height_tolerance) && (hd[2] <= P.height_tolerance);
-      wk[LY::W_HCOK * 32] = (h_ok && (cdist <= P.centroid_tolerance)) ? 1.0f : 0.0f;
+      m.hcok = h_ok && (m.cdist <= P.centroid_tolerance);
+      // the ten pad pair distances, triu order (:726-771)
+      const int op = P.obs_offset[DEX_K_FINGERPAD_DISTANCES];
+      if (op >= 0) {
+        int k = 0;
+#pragma unroll
+        for (int a = 0; a < DEX_NUM_FINGERS; ++a)
+#pragma unroll
+          for (int b = a + 1; b < DEX_NUM_FINGERS; ++b, ++k)
+            obs[op + k] = norm3(p[a][0] - p[b][0], p[a][1] - p[b][1], p[a][2] - p[b][2]);
+      }
     }
   }
 }
 
-// ---- job: the five contact sensors (observation_encoder.py:658-735, 323-361; reward_calculator.py:183-199) and, for
+// ---- the five contact sensors (observation_encoder.py:658-735, 323-361; reward_calculator.py:183-199) and, for
 //      BlindGrasping, the box contact flag and the box stability inputs
 template <bool BG>
-__device__ __forceinline__ void job_contacts(const Post2Args& A, const Cx<BG>& c) {
+__device__ __forceinline__ void part_contacts(const Post2Args& A, const Cx<BG>& c, Mid& m) {
   using LY = Lay<BG>;
   const DexParams& P = A.p;
   const DexStateBuffers& st = A.st;
   const float* aos = c.aos();
   const float* soa = c.soa();
-  float* wk = c.wk;
   float* obs = c.obs;
   const size_t N = c.N, env = c.env;
   const float dt = P.control_dt;
@@ -443,6 +440,7 @@ __device__ __forceinline__ void job_contacts(const Post2Args& A, const Cx<BG>& c
   const int ocf = P.obs_offset[DEX_K_CONTACT_FORCES], om = P.obs_offset[DEX_K_CONTACT_FORCE_MAGNITUDE];
   const int ob = P.obs_offset[DEX_K_CONTACT_BINARY], od = P.obs_offset[DEX_K_CONTACT_DURATION];
   const bool common = !BG && A.common != 0, first = A.first != 0;
+  float chg = 0.0f;
 #pragma unroll
   for (int f = 0; f < DEX_NUM_FINGERS; ++f) {
     const float mag = norm3(cf[f][0], cf[f][1], cf[f][2]);
@@ -455,7 +453,7 @@ __device__ __forceinline__ void job_contacts(const Post2Args& A, const Cx<BG>& c
 #pragma unroll
       for (int k = 0; k < 3; ++k) st.contact_forces[(3 * f + k) * N + env] = cf[f][k];
     }
-    wk[(LY::W_BIN + f) * 32] = fb;
+    m.bin[f] = fb;
     if (ocf >= 0) {
 #pragma unroll
       for (int k = 0; k < 3; ++k) obs[ocf + 3 * f + k] = cf[f][k];
@@ -466,20 +464,19 @@ __device__ __forceinline__ void job_contacts(const Post2Args& A, const Cx<BG>& c
     if (common) {
       const bool c_now = mag > 0.1f;  // hard-coded 0.1 N (reward_calculator.py:186)
       const bool c_prev = first ? c_now : (c.stage[LY::OFF_U8 + f * 32 + c.lane] != 0);
-      wk[(LY::W_CHG + f) * 32] = (c_now != c_prev) ? 1.0f : 0.0f;
+      chg += (c_now != c_prev) ? 1.0f : 0.0f;  // summed in finger order as the term does (reward_calculator.py:183-199)
       st.prev_contacts[f * N + env] = c_now ? 1 : 0;
     }
   }
+  m.chg = chg;
   if (BG) {
     const float* cfb = aos + LY::A_CF + 15;
     const float* box = aos + LY::A_BOX;
     const float b[6] = {box[0], box[1], box[2], box[3], box[4], box[5]};
-    wk[LY::W_BOXHAS * 32] = (norm3(cfb[0], cfb[1], cfb[2]) > P.contact_binary_threshold) ? 1.0f : 0.0f;
-    const float drift = norm3(b[0] - soa[(LY::R_BOX0 + 0) * 32], b[1] - soa[(LY::R_BOX0 + 1) * 32], b[2] - soa[(LY::R_BOX0 + 2) * 32]);
-    const float vmag = norm3(b[3], b[4], b[5]);
-    wk[LY::W_DRIFT * 32] = drift;
-    wk[LY::W_VMAG * 32] = vmag;
-    wk[LY::W_SOK * 32] = ((drift <= P.position_drift_tolerance) && (vmag <= P.velocity_tolerance)) ? 1.0f : 0.0f;
+    m.boxhas = norm3(cfb[0], cfb[1], cfb[2]) > P.contact_binary_threshold;
+    m.drift = norm3(b[0] - soa[(LY::R_BOX0 + 0) * 32], b[1] - soa[(LY::R_BOX0 + 1) * 32], b[2] - soa[(LY::R_BOX0 + 2) * 32]);
+    m.vmag = norm3(b[3], b[4], b[5]);
+    m.sok = (m.drift <= P.position_drift_tolerance) && (m.vmag <= P.velocity_tolerance);
     const int opos = P.obs_offset[DEX_K_OBJECT_POS], ovel = P.obs_offset[DEX_K_OBJECT_VEL];
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
@@ -489,17 +486,16 @@ __device__ __forceinline__ void job_contacts(const Post2Args& A, const Cx<BG>& c
   }
 }
 
-// ---- job: hand pose, ARR-aligned pose (observation_encoder.py:1483-1521), hand -> box distance, hand velocity
-//      reward terms (reward_calculator.py:100-181), episode time (dexhand_base.py:703-712: PRE-increment count)
+// ---- hand pose, ARR-aligned pose (observation_encoder.py:1483-1521), hand -> box distance, hand velocity reward
+//      terms (reward_calculator.py:100-181), episode time (dexhand_base.py:703-712: PRE-increment count)
 template <bool BG>
-__device__ __forceinline__ void job_hand(const Post2Args& A, const Cx<BG>& c) {
+__device__ __forceinline__ void part_hand(const Post2Args& A, const Cx<BG>& c, Mid& m) {
   using LY = Lay<BG>;
   const DexParams& P = A.p;
   const DexStateBuffers& st = A.st;
   const float* aos = c.aos();
   const float* soa = c.soa();
   const float* rb = aos + LY::A_RB;
-  float* wk = c.wk;
   float* obs = c.obs;
   float h[7];
 #pragma unroll
@@ -525,7 +521,7 @@ __device__ __forceinline__ void job_hand(const Post2Args& A, const Cx<BG>& c) {
   if (BG) {
     const float* box = aos + LY::A_BOX;
     const float hb = norm3(h[0] - box[0], h[1] - box[1], h[2] - box[2]);
-    wk[LY::W_BOXFAR * 32] = (hb > P.max_box_distance) ? 1.0f : 0.0f;
+    m.boxfar = hb > P.max_box_distance;
     obs_put(obs, P.obs_offset[DEX_K_HAND_TO_OBJECT_DISTANCE], 0, hb);
   }
   if (!BG && A.common) {
@@ -540,108 +536,82 @@ __device__ __forceinline__ void job_hand(const Post2Args& A, const Cx<BG>& c) {
       st.prev_hand_vel[k * c.N + c.env] = hv[k];
       st.prev_hand_ang_vel[k * c.N + c.env] = ha[k];
     }
-    wk[(LY::W_RHAND + 0) * 32] = expf(-0.2f * norm3(hv[0], hv[1], hv[2]));
-    wk[(LY::W_RHAND + 1) * 32] = expf(-0.2f * norm3(ha[0], ha[1], ha[2]));
-    wk[(LY::W_RHAND + 2) * 32] = expf(-0.5f * norm3(hv[0] - phv[0], hv[1] - phv[1], hv[2] - phv[2]));
-    wk[(LY::W_RHAND + 3) * 32] = expf(-0.5f * norm3(ha[0] - pha[0], ha[1] - pha[1], ha[2] - pha[2]));
+    m.rhand[0] = expf(-0.2f * norm3(hv[0], hv[1], hv[2]));
+    m.rhand[1] = expf(-0.2f * norm3(ha[0], ha[1], ha[2]));
+    m.rhand[2] = expf(-0.5f * norm3(hv[0] - phv[0], hv[1] - phv[1], hv[2] - phv[2]));
+    m.rhand[3] = expf(-0.5f * norm3(ha[0] - pha[0], ha[1] - pha[1], ha[2] - pha[2]));
   }
 }
 
-// ---- job: the ten pad pair distances, triu order (blind_grasping_task.py:726-771)
+// ---- the 26 DOFs: finite-difference velocity (observation_encoder.py:298-321), obs columns, common-reward partial
+//      sums (reward_calculator.py:94-98,138-160: Isaac dof_vel, not the finite difference; summed in DOF order)
 template <bool BG>
-__device__ __forceinline__ void job_pairs(const Post2Args& A, const Cx<BG>& c) {
+__device__ __forceinline__ void part_dofs(const Post2Args& A, const Cx<BG>& c, Mid& m) {
   using LY = Lay<BG>;
-  const int op = A.p.obs_offset[DEX_K_FINGERPAD_DISTANCES];
-  if (op < 0) return;
-  const float* rb = c.aos() + LY::A_RB;
-  float q[DEX_NUM_FINGERS][3];
-#pragma unroll
-  for (int f = 0; f < DEX_NUM_FINGERS; ++f)
-#pragma unroll
-    for (int k = 0; k < 3; ++k) q[f][k] = rb[13 + 35 + 7 * f + k];
-  int k = 0;
-#pragma unroll
-  for (int a = 0; a < DEX_NUM_FINGERS; ++a)
-#pragma unroll
-    for (int b = a + 1; b < DEX_NUM_FINGERS; ++b, ++k)
-      c.obs[op + k] = norm3(q[a][0] - q[b][0], q[a][1] - q[b][1], q[a][2] - q[b][2]);
-}
-
-// ---- job: DOFs [D0, D1): finite-difference velocity (observation_encoder.py:298-321), obs columns, common-reward
-//      partial terms (reward_calculator.py:94-98,138-160: Isaac dof_vel, not the finite difference)
-template <bool BG, int D0, int D1>
-__device__ __forceinline__ void job_dofs(const Post2Args& A, const Cx<BG>& c) {
-  using LY = Lay<BG>;
-  static_assert(D0 % 2 == 0 && D1 % 2 == 0, "whole (pos, vel) pairs of DOFs");
   const DexParams& P = A.p;
   const DexStateBuffers& st = A.st;
   const float* soa = c.soa();
-  float* wk = c.wk;
   float* obs = c.obs;
   const size_t N = c.N, env = c.env;
   const float dt = P.control_dt;
-  constexpr int ND = D1 - D0;
-  float pos[ND], vel[ND], prev[ND], tgt[ND];
   const float4* d4 = reinterpret_cast<const float4*>(c.stage + LY::OFF_DOF) + c.lane * 13;
-#pragma unroll
-  for (int q = 0; q < ND / 2; ++q) {
-    const float4 v = d4[D0 / 2 + q];
-    pos[2 * q] = v.x;
-    vel[2 * q] = v.y;
-    pos[2 * q + 1] = v.z;
-    vel[2 * q + 1] = v.w;
-  }
   const bool want_tgt = !BG && A.want_tgt != 0;
-#pragma unroll
-  for (int i = 0; i < ND; ++i) {
-    prev[i] = soa[(LY::R_PDP + D0 + i) * 32];
-    tgt[i] = want_tgt ? reinterpret_cast<const float*>(c.stage + LY::OFF_TGT)[c.lane * 26 + D0 + i] : 0.0f;
-  }
   const bool common = !BG && A.common != 0, first = A.first != 0;
   const int o_bp = P.obs_offset[DEX_K_BASE_DOF_POS], o_bv = P.obs_offset[DEX_K_BASE_DOF_VEL], o_bt = P.obs_offset[DEX_K_BASE_DOF_TARGET];
   const int o_ap = P.obs_offset[DEX_K_ALL_FINGER_DOF_POS], o_av = P.obs_offset[DEX_K_ALL_FINGER_DOF_VEL],
             o_at = P.obs_offset[DEX_K_ALL_FINGER_DOF_TARGET];
   const int o_fp = P.obs_offset[DEX_K_ACTIVE_FINGER_DOF_POS], o_fv = P.obs_offset[DEX_K_ACTIVE_FINGER_DOF_VEL],
             o_ft = P.obs_offset[DEX_K_ACTIVE_FINGER_DOF_TARGET];
+  float fv2 = 0.0f, fa2 = 0.0f, jl = 0.0f;
 #pragma unroll
-  for (int i = 0; i < ND; ++i) {
-    const int d = D0 + i;
-    const float fd = div_rn(pos[i] - prev[i], dt);
-    st.prev_dof_pos[d * N + env] = pos[i];
-    if (d < DEX_NUM_BASE) {
-      obs_put(obs, o_bp, d, pos[i]);
-      obs_put(obs, o_bv, d, fd);
-      if (!BG) obs_put(obs, o_bt, d, tgt[i]);
-      if (BG) wk[(LY::W_BVEL + d) * 32] = fd;
-    } else {
-      const int j = d - DEX_NUM_BASE;
-      obs_put(obs, o_ap, j, pos[i]);
-      obs_put(obs, o_av, j, fd);
-      if (!BG) obs_put(obs, o_at, j, tgt[i]);
-      const int aj = A.dof2afj[d];
-      if (aj >= 0) {
-        obs_put(obs, o_fp, aj, pos[i]);
-        obs_put(obs, o_fv, aj, fd);
-        if (!BG) obs_put(obs, o_ft, aj, tgt[i]);
-      }
-      if (common) {
-        const float iv = vel[i];
-        const float pvv = first ? iv : soa[(LY::R_PFDV + j) * 32];
-        wk[(LY::W_FV2 + j) * 32] = iv * iv;
-        const float acc = iv - pvv;
-        wk[(LY::W_FA2 + j) * 32] = acc * acc;
-        const float nj = div_rn(2.0f * (pos[i] - P.dof_lower[d]), P.dof_upper[d] - P.dof_lower[d]) - 1.0f;
-        wk[(LY::W_JL + j) * 32] = clampf(fabsf(nj) - 0.8f, 0.0f, 1.0f);
-        st.prev_finger_dof_vel[j * N + env] = iv;
+  for (int q = 0; q < DEX_NUM_DOF / 2; ++q) {
+    const float4 v4 = d4[q];
+    const float pos2[2] = {v4.x, v4.z}, vel2[2] = {v4.y, v4.w};
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int d = 2 * q + h;
+      const float pos = pos2[h];
+      const float fd = div_rn(pos - soa[(LY::R_PDP + d) * 32], dt);
+      st.prev_dof_pos[d * N + env] = pos;
+      const float tgt = want_tgt ? reinterpret_cast<const float*>(c.stage + LY::OFF_TGT)[c.lane * 26 + d] : 0.0f;
+      if (d < DEX_NUM_BASE) {
+        obs_put(obs, o_bp, d, pos);
+        obs_put(obs, o_bv, d, fd);
+        if (!BG) obs_put(obs, o_bt, d, tgt);
+        m.bvel[d < DEX_NUM_BASE ? d : 0] = fd;
+      } else {
+        const int j = d - DEX_NUM_BASE;
+        obs_put(obs, o_ap, j, pos);
+        obs_put(obs, o_av, j, fd);
+        if (!BG) obs_put(obs, o_at, j, tgt);
+        const int aj = A.dof2afj[d];
+        if (aj >= 0) {
+          obs_put(obs, o_fp, aj, pos);
+          obs_put(obs, o_fv, aj, fd);
+          if (!BG) obs_put(obs, o_ft, aj, tgt);
+        }
+        if (common) {
+          const float iv = vel2[h];
+          const float pvv = first ? iv : soa[(LY::R_PFDV + j) * 32];
+          fv2 += iv * iv;
+          const float acc = iv - pvv;
+          fa2 += acc * acc;
+          const float nj = div_rn(2.0f * (pos - P.dof_lower[d]), P.dof_upper[d] - P.dof_lower[d]) - 1.0f;
+          jl += clampf(fabsf(nj) - 0.8f, 0.0f, 1.0f);
+          st.prev_finger_dof_vel[j * N + env] = iv;
+        }
       }
     }
   }
+  m.fv2 = fv2;
+  m.fa2 = fa2;
+  m.jl = jl;
 }
 
-// ---- job: prev_actions columns (observation_encoder.py:287-296); active_rule_targets <- active_prev_targets
+// ---- prev_actions columns (observation_encoder.py:287-296); active_rule_targets <- active_prev_targets
 //      (rules.py:78-95, step_processor.py:73)
 template <bool BG>
-__device__ __forceinline__ void job_copies(const Post2Args& A, const Cx<BG>& c) {
+__device__ __forceinline__ void part_copies(const Post2Args& A, const Cx<BG>& c) {
   using LY = Lay<BG>;
   const DexParams& P = A.p;
   const float* soa = c.soa();
@@ -672,223 +642,145 @@ __device__ __forceinline__ void job_copies(const Post2Args& A, const Cx<BG>& c) 
   }
 }
 
-// phase A: everything that depends only on the staged tile
-template <bool BG>
-__device__ __forceinline__ void phase_a(const Post2Args& A, const Cx<BG>& c) {
-  if (!c.act) return;
-  switch (c.cw) {
-    case 0: job_poses<BG, false, true, BG>(A, c); break;   // tips: world (+ hand frame for BlindGrasping configs that ask)
-    case 1: job_poses<BG, true, true, BG>(A, c); break;    // pads
-    case 2: job_contacts<BG>(A, c); break;
-    case 3: job_hand<BG>(A, c); break;
-    case 4:
-      if (BG) job_pairs<BG>(A, c);
-      else job_poses<BG, false, false, true>(A, c);         // BaseTask: tip poses in the hand frame
-      break;
-    case 5: job_dofs<BG, 0, 14>(A, c); break;
-    case 6: job_dofs<BG, 14, 26>(A, c); break;
-    default:
-      job_copies<BG>(A, c);
-      if (!BG) job_poses<BG, true, false, true>(A, c);      // BaseTask: pad poses in the hand frame
-      break;
-  }
-}
-
-// one common reward term (reward_calculator.py:66-221); BaseTask
-template <bool BG>
-__device__ __forceinline__ float common_term(const Post2Args& A, const Cx<BG>& c, const int i) {
-  using LY = Lay<BG>;
-  const float* wk = c.wk;
-  const float* rb = c.aos() + LY::A_RB;
-  switch (i) {
-    case DEX_R_ALIVE: return 1.0f;
-    case DEX_R_HEIGHT_SAFETY: {
-      float mz = rb[13 + 2];
-#pragma unroll
-      for (int f = 1; f < DEX_NUM_FINGERS; ++f) mz = fminf(mz, rb[13 + 7 * f + 2]);
-      return clampf(1.0f - expf(-(mz - 0.02f) * 20.0f), 0.0f, 1.0f);
-    }
-    case DEX_R_FINGER_VELOCITY: {
-      float a = 0.0f;
-#pragma unroll
-      for (int j = 0; j < DEX_NUM_FINGER_DOF; ++j) a += wk[(LY::W_FV2 + j) * 32];
-      return expf(-0.1f * sqrtf(a));
-    }
-    case DEX_R_HAND_VELOCITY: return wk[(LY::W_RHAND + 0) * 32];
-    case DEX_R_HAND_ANGULAR_VELOCITY: return wk[(LY::W_RHAND + 1) * 32];
-    case DEX_R_JOINT_LIMIT: {
-      float a = 0.0f;
-#pragma unroll
-      for (int j = 0; j < DEX_NUM_FINGER_DOF; ++j) a += wk[(LY::W_JL + j) * 32];
-      return 1.0f - div_rn(a, 20.0f);
-    }
-    case DEX_R_FINGER_ACCELERATION: {
-      float a = 0.0f;
-#pragma unroll
-      for (int j = 0; j < DEX_NUM_FINGER_DOF; ++j) a += wk[(LY::W_FA2 + j) * 32];
-      return expf(-2.0f * sqrtf(a));
-    }
-    case DEX_R_HAND_ACCELERATION: return wk[(LY::W_RHAND + 2) * 32];
-    case DEX_R_HAND_ANGULAR_ACCELERATION: return wk[(LY::W_RHAND + 3) * 32];
-    default: {  // DEX_R_CONTACT_STABILITY
-      float a = 0.0f;
-#pragma unroll
-      for (int f = 0; f < DEX_NUM_FINGERS; ++f) a += wk[(LY::W_CHG + f) * 32];
-      return expf(-a);
-    }
-  }
-}
-
-// one BlindGrasping task term (blind_grasping_task.py:980-1208); phase C (after the FSM)
-template <bool BG>
-__device__ __forceinline__ float task_term(const Post2Args& A, const Cx<BG>& c, const int i, const int stage) {
-  using LY = Lay<BG>;
+// ---- BlindGrasping: finger-box contacts (blind_grasping_task.py:773-833), success duration (:626-648), stage FSM
+//      (:835-978; plain fp32 accumulation of (float)control_dt decides the transition step)
+__device__ __forceinline__ void part_task_state(const Post2Args& A, const Cx<true>& c, Mid& m) {
+  using LY = Lay<true>;
   const DexParams& P = A.p;
-  const float* wk = c.wk;
-  const float* aos = c.aos();
-  const float* rb = aos + LY::A_RB;
-  const float m1 = (stage == 1) ? 1.0f : 0.0f, m2 = (stage == 2) ? 1.0f : 0.0f, m3 = (stage == 3) ? 1.0f : 0.0f;
-  switch (i) {
-    case DEX_R_S1_HEIGHT_ALIGNMENT: return expf(-P.height_alignment_decay * wk[LY::W_AVGHDIFF * 32]) * m1;
-    case DEX_R_S1_CENTROID_POSITIONING: return expf(-P.centroid_positioning_decay * wk[LY::W_CDIST * 32]) * m1;
-    case DEX_R_S1_OBJECT_STABILITY:
-      return expf(-P.object_stability_decay * (wk[LY::W_DRIFT * 32] + wk[LY::W_VMAG * 32])) * m1;
-    case DEX_R_S1_FINGER_HEIGHT_CONSISTENCY: {  // torch.var(dim=1), unbiased, z of the first three pads
-      const float z0 = rb[13 + 35 + 2], z1 = rb[13 + 35 + 7 + 2], z2 = rb[13 + 35 + 14 + 2];
-      const float mean = (z0 + z1 + z2) / 3.0f;
-      const float d0 = z0 - mean, d1 = z1 - mean, d2 = z2 - mean;
-      const float var = (d0 * d0 + d1 * d1 + d2 * d2) / 2.0f;
-      return expf(-P.height_consistency_decay * var) * m1;
-    }
-    case DEX_R_S1_THUMB_ROTATION: {
-      const float th = reinterpret_cast<const float*>(c.stage + LY::OFF_DOF)[c.lane * 52 + 2 * DEX_NUM_BASE];
-      return expf(-5.0f * fabsf(th - P.half_pi)) * m1;
-    }
-    case DEX_R_S2_THUMB_CONTACT: return wk[LY::W_THUMB * 32] * m2;
-    case DEX_R_S2_OTHER_FINGERS_CONTACT: return wk[LY::W_OTHERS * 32] * m2;
-    case DEX_R_S2_GRASP_ACHIEVEMENT: return wk[LY::W_GRASP * 32] * m2;
-    case DEX_R_S2_FINGERPAD_PROXIMITY:
-      return expf(-P.fingerpad_proximity_decay * fmaxf(wk[LY::W_MINTIPBOX * 32], P.min_reward_distance)) * m2;
-    case DEX_R_S2_BASE_STABILITY: {
-      float bv2 = 0.0f;
+  const DexStateBuffers& st = A.st;
+  const float dt = P.control_dt;
+  float* obs = c.obs;
+  const float* soa = c.soa();
+  const size_t env = c.env;
+  const float box_z = c.aos()[LY::A_BOX + 2];
+  const int sds_old = c.i64lo(LY::I_SDS);
+  int stage = c.i64lo(LY::I_STAGE);
+  float tis = soa[LY::R_TIS * 32] + dt;
+  float scd = soa[LY::R_SCD * 32];
+  bool fbc[DEX_NUM_FINGERS];
+  int n_on_box = 0;
 #pragma unroll
-      for (int d = 0; d < DEX_NUM_BASE; ++d) {
-        const float v = wk[(LY::W_BVEL + d) * 32];  // finite-difference base velocity
-        bv2 += v * v;
-      }
-      return expf(-P.base_stability_decay * sqrtf(bv2)) * m2;
-    }
-    case DEX_R_S3_OBJECT_HEIGHT:
-      return clampf(div_rn(aos[LY::A_BOX + 2] - P.box_z, P.lift_height_range), 0.0f, 1.0f) * m3;
-    case DEX_R_S3_GRASP_MAINTENANCE: return wk[LY::W_GRASP * 32] * m3;
-    case DEX_R_S3_GRASP_DURATION:
-      return clampf(div_rn(wk[LY::W_GRASPDUR * 32], P.contact_duration_threshold_s), 0.0f, 1.0f) * m3;
-    // completion bonuses :1025-1048 (transition and not failed), penetration :1194-1208
-    case DEX_R_S1_COMPLETION:
-      return (wk[LY::W_J2 * 32] != 0.0f && wk[LY::W_HCOK * 32] != 0.0f && wk[LY::W_SOK * 32] != 0.0f) ? 1.0f : 0.0f;
-    case DEX_R_S2_COMPLETION: return (wk[LY::W_J3 * 32] != 0.0f && wk[LY::W_GRASP * 32] != 0.0f) ? 1.0f : 0.0f;
-    default:  // DEX_R_PENETRATION_PENALTY
-      return fmaxf(P.penetration_threshold - wk[LY::W_MINTIPBOX * 32], 0.0f) * P.penetration_depth_scale;
+  for (int f = 0; f < DEX_NUM_FINGERS; ++f) {
+    fbc[f] = (m.bin[f] != 0.0f) && m.boxhas && (m.padbox[f] < P.proximity_threshold);
+    n_on_box += fbc[f] ? 1 : 0;
   }
+  m.thumb = fbc[0];
+  m.others = fbc[1] || fbc[2] || fbc[3] || fbc[4];
+  m.grasp = m.thumb && m.others;
+  obs_put(obs, P.obs_offset[DEX_K_THUMB_CONTACT], 0, m.thumb ? 1.0f : 0.0f);
+  obs_put(obs, P.obs_offset[DEX_K_OTHER_FINGERS_CONTACT], 0, m.others ? 1.0f : 0.0f);
+  obs_put(obs, P.obs_offset[DEX_K_GRASP_STATE], 0, m.grasp ? 1.0f : 0.0f);
+  const bool cond = (box_z > P.success_height_threshold) && (n_on_box >= P.min_fingers_for_grasp);
+  m.sds = cond ? sds_old + 1 : 0;
+  st.success_duration_steps[env] = (long long)m.sds;
+  st.success_conditions_met[env] = cond ? 1 : 0;
+  m.graspdur = (float)m.sds * dt;
+  obs_put(obs, P.obs_offset[DEX_K_GRASP_DURATION], 0, m.graspdur);
+  // FSM
+  const bool thumb_other = (m.bin[0] != 0.0f) && ((m.bin[1] != 0.0f) || (m.bin[2] != 0.0f) || (m.bin[3] != 0.0f) || (m.bin[4] != 0.0f));
+  if (stage == 2) scd = thumb_other ? scd + dt : 0.0f;
+  const bool s1_done = (stage == 1) && (tis >= P.stage1_duration);
+  const bool s2_done = (stage == 2) && ((scd >= P.stage2_contact_success_threshold) || (tis >= P.stage2_duration));
+  if (s1_done) stage = 2;
+  if (s2_done) stage = 3;
+  if (s1_done || s2_done) {
+    tis = 0.0f;
+    scd = 0.0f;
+  }
+  st.current_stage[env] = (long long)stage;
+  st.time_in_stage[env] = tis;
+  st.stage_contact_duration[env] = scd;
+  st.just_transitioned_to_stage2[env] = s1_done ? 1 : 0;
+  st.just_transitioned_to_stage3[env] = s2_done ? 1 : 0;
+  float prog = 0.0f;  // :958-978
+  if (stage == 1) prog = clampf(div_rn(tis, P.stage1_duration), 0.0f, 1.0f);
+  if (stage == 2) prog = clampf(div_rn(tis, P.stage2_duration), 0.0f, 1.0f);
+  if (stage == 3) prog = 1.0f;
+  m.stage = stage;
+  m.j2 = s1_done;
+  m.j3 = s2_done;
+  obs_put(obs, P.obs_offset[DEX_K_CURRENT_STAGE], 0, (float)stage);
+  obs_put(obs, P.obs_offset[DEX_K_TIME_IN_STAGE], 0, tis);
+  obs_put(obs, P.obs_offset[DEX_K_STAGE_PROGRESS], 0, prog);
 }
 
-// raw + weighted rows of term i leave from registers; the weighted value is parked for the ordered total
+// raw + weighted rows of term i leave from registers; the weighted value is kept for the ordered total
 template <bool BG>
-__device__ __forceinline__ void emit_term(const Post2Args& A, const Cx<BG>& c, const int i, const float r) {
+__device__ __forceinline__ void emit_term(const Post2Args& A, const Cx<BG>& c, Mid& m, const int i, const float r) {
   const float w = A.p.reward_weight[i];
+  if (w == 0.0f) return;  // reward_calculator.py:247-251: zero-weight terms are not materialised
   const int row = A.p.component_row[i];
   const float rw = r * w;
   float* g = A.out.reward_components + c.env;
   g[(size_t)row * c.N] = r;
   g[(size_t)(row + 1) * c.N] = rw;
-  c.wk[(Lay<BG>::W_WGT + i) * 32] = rw;
+  m.wgt[i] = rw;
 }
 
-// phase B (BlindGrasping): the two scalar chains that the reward terms and the termination wait for
-template <bool BG>
-__device__ __forceinline__ void phase_b(const Post2Args& A, const Cx<BG>& c) {
-  using LY = Lay<BG>;
-  if (!c.act) return;
+// ---- common reward terms (reward_calculator.py:66-221); BaseTask
+__device__ __forceinline__ void part_common_terms(const Post2Args& A, const Cx<false>& c, Mid& m) {
+  emit_term<false>(A, c, m, DEX_R_ALIVE, 1.0f);
+  emit_term<false>(A, c, m, DEX_R_HEIGHT_SAFETY, clampf(1.0f - expf(-(m.min_tip_z - 0.02f) * 20.0f), 0.0f, 1.0f));
+  emit_term<false>(A, c, m, DEX_R_FINGER_VELOCITY, expf(-0.1f * sqrtf(m.fv2)));
+  emit_term<false>(A, c, m, DEX_R_HAND_VELOCITY, m.rhand[0]);
+  emit_term<false>(A, c, m, DEX_R_HAND_ANGULAR_VELOCITY, m.rhand[1]);
+  emit_term<false>(A, c, m, DEX_R_JOINT_LIMIT, 1.0f - div_rn(m.jl, 20.0f));
+  emit_term<false>(A, c, m, DEX_R_FINGER_ACCELERATION, expf(-2.0f * sqrtf(m.fa2)));
+  emit_term<false>(A, c, m, DEX_R_HAND_ACCELERATION, m.rhand[2]);
+  emit_term<false>(A, c, m, DEX_R_HAND_ANGULAR_ACCELERATION, m.rhand[3]);
+  emit_term<false>(A, c, m, DEX_R_CONTACT_STABILITY, expf(-m.chg));
+}
+
+// ---- BlindGrasping task terms (blind_grasping_task.py:980-1208), after the FSM
+__device__ __forceinline__ void part_task_terms(const Post2Args& A, const Cx<true>& c, Mid& m) {
+  using LY = Lay<true>;
   const DexParams& P = A.p;
-  const DexStateBuffers& st = A.st;
-  const float dt = P.control_dt;
-  float* wk = c.wk;
-  float* obs = c.obs;
-  const float* soa = c.soa();
-  const size_t env = c.env;
-  if (c.cw == 0) {
-    // ---- finger-box contacts (blind_grasping_task.py:773-833), success duration (:626-648) ----
-    const bool box_has = wk[LY::W_BOXHAS * 32] != 0.0f;
-    const float box_z = c.aos()[LY::A_BOX + 2];
-    const int sds_old = c.i64lo(LY::I_SDS);
-    bool fbc[DEX_NUM_FINGERS];
-    int n_on_box = 0;
-#pragma unroll
-    for (int f = 0; f < DEX_NUM_FINGERS; ++f) {
-      fbc[f] = (wk[(LY::W_BIN + f) * 32] != 0.0f) && box_has && (wk[(LY::W_PADBOX + f) * 32] < P.proximity_threshold);
-      n_on_box += fbc[f] ? 1 : 0;
-    }
-    const bool thumb_c = fbc[0], others_c = fbc[1] || fbc[2] || fbc[3] || fbc[4];
-    const bool grasp = thumb_c && others_c;
-    const float ft = thumb_c ? 1.0f : 0.0f, fo = others_c ? 1.0f : 0.0f, fg = grasp ? 1.0f : 0.0f;
-    wk[LY::W_THUMB * 32] = ft;
-    wk[LY::W_OTHERS * 32] = fo;
-    wk[LY::W_GRASP * 32] = fg;
-    obs_put(obs, P.obs_offset[DEX_K_THUMB_CONTACT], 0, ft);
-    obs_put(obs, P.obs_offset[DEX_K_OTHER_FINGERS_CONTACT], 0, fo);
-    obs_put(obs, P.obs_offset[DEX_K_GRASP_STATE], 0, fg);
-    const bool cond = (box_z > P.success_height_threshold) && (n_on_box >= P.min_fingers_for_grasp);
-    const int sds = cond ? sds_old + 1 : 0;
-    st.success_duration_steps[env] = (long long)sds;
-    st.success_conditions_met[env] = cond ? 1 : 0;
-    const float gd = (float)sds * dt;
-    wk[LY::W_SDS * 32] = __int_as_float(sds);
-    wk[LY::W_GRASPDUR * 32] = gd;
-    obs_put(obs, P.obs_offset[DEX_K_GRASP_DURATION], 0, gd);
-  } else if (c.cw == 1) {
-    // ---- stage FSM :835-956 (plain fp32 accumulation of (float)control_dt decides the transition step) ----
-    int stage = c.i64lo(LY::I_STAGE);
-    float tis = soa[LY::R_TIS * 32] + dt;
-    float scd = soa[LY::R_SCD * 32];
-    const bool b0 = wk[(LY::W_BIN + 0) * 32] != 0.0f;
-    const bool bo = (wk[(LY::W_BIN + 1) * 32] != 0.0f) || (wk[(LY::W_BIN + 2) * 32] != 0.0f) ||
-                    (wk[(LY::W_BIN + 3) * 32] != 0.0f) || (wk[(LY::W_BIN + 4) * 32] != 0.0f);
-    const bool thumb_other = b0 && bo;
-    if (stage == 2) scd = thumb_other ? scd + dt : 0.0f;
-    const bool s1_done = (stage == 1) && (tis >= P.stage1_duration);
-    const bool s2_done = (stage == 2) && ((scd >= P.stage2_contact_success_threshold) || (tis >= P.stage2_duration));
-    if (s1_done) stage = 2;
-    if (s2_done) stage = 3;
-    if (s1_done || s2_done) {
-      tis = 0.0f;
-      scd = 0.0f;
-    }
-    st.current_stage[env] = (long long)stage;
-    st.time_in_stage[env] = tis;
-    st.stage_contact_duration[env] = scd;
-    st.just_transitioned_to_stage2[env] = s1_done ? 1 : 0;
-    st.just_transitioned_to_stage3[env] = s2_done ? 1 : 0;
-    float prog = 0.0f;  // :958-978
-    if (stage == 1) prog = clampf(div_rn(tis, P.stage1_duration), 0.0f, 1.0f);
-    if (stage == 2) prog = clampf(div_rn(tis, P.stage2_duration), 0.0f, 1.0f);
-    if (stage == 3) prog = 1.0f;
-    wk[LY::W_STAGE * 32] = __int_as_float(stage);
-    wk[LY::W_J2 * 32] = s1_done ? 1.0f : 0.0f;
-    wk[LY::W_J3 * 32] = s2_done ? 1.0f : 0.0f;
-    obs_put(obs, P.obs_offset[DEX_K_CURRENT_STAGE], 0, (float)stage);
-    obs_put(obs, P.obs_offset[DEX_K_TIME_IN_STAGE], 0, tis);
-    obs_put(obs, P.obs_offset[DEX_K_STAGE_PROGRESS], 0, prog);
+  const float* aos = c.aos();
+  const float* rb = aos + LY::A_RB;
+  const float m1 = (m.stage == 1) ? 1.0f : 0.0f, m2 = (m.stage == 2) ? 1.0f : 0.0f, m3 = (m.stage == 3) ? 1.0f : 0.0f;
+  const float fg = m.grasp ? 1.0f : 0.0f;
+  emit_term<true>(A, c, m, DEX_R_S1_HEIGHT_ALIGNMENT, expf(-P.height_alignment_decay * m.avg_hdiff) * m1);
+  emit_term<true>(A, c, m, DEX_R_S1_CENTROID_POSITIONING, expf(-P.centroid_positioning_decay * m.cdist) * m1);
+  emit_term<true>(A, c, m, DEX_R_S1_OBJECT_STABILITY, expf(-P.object_stability_decay * (m.drift + m.vmag)) * m1);
+  {  // torch.var(dim=1), unbiased, z of the first three pads
+    const float z0 = rb[13 + 35 + 2], z1 = rb[13 + 35 + 7 + 2], z2 = rb[13 + 35 + 14 + 2];
+    const float mean = (z0 + z1 + z2) / 3.0f;
+    const float d0 = z0 - mean, d1 = z1 - mean, d2 = z2 - mean;
+    const float var = (d0 * d0 + d1 * d1 + d2 * d2) / 2.0f;
+    emit_term<true>(A, c, m, DEX_R_S1_FINGER_HEIGHT_CONSISTENCY, expf(-P.height_consistency_decay * var) * m1);
   }
+  {
+    const float th = reinterpret_cast<const float*>(c.stage + LY::OFF_DOF)[c.lane * 52 + 2 * DEX_NUM_BASE];
+    emit_term<true>(A, c, m, DEX_R_S1_THUMB_ROTATION, expf(-5.0f * fabsf(th - P.half_pi)) * m1);
+  }
+  emit_term<true>(A, c, m, DEX_R_S2_THUMB_CONTACT, (m.thumb ? 1.0f : 0.0f) * m2);
+  emit_term<true>(A, c, m, DEX_R_S2_OTHER_FINGERS_CONTACT, (m.others ? 1.0f : 0.0f) * m2);
+  emit_term<true>(A, c, m, DEX_R_S2_GRASP_ACHIEVEMENT, fg * m2);
+  emit_term<true>(A, c, m, DEX_R_S2_FINGERPAD_PROXIMITY,
+                  expf(-P.fingerpad_proximity_decay * fmaxf(m.min_tip_box, P.min_reward_distance)) * m2);
+  {
+    float bv2 = 0.0f;
+#pragma unroll
+    for (int d = 0; d < DEX_NUM_BASE; ++d) bv2 += m.bvel[d] * m.bvel[d];  // finite-difference base velocity
+    emit_term<true>(A, c, m, DEX_R_S2_BASE_STABILITY, expf(-P.base_stability_decay * sqrtf(bv2)) * m2);
+  }
+  emit_term<true>(A, c, m, DEX_R_S3_OBJECT_HEIGHT, clampf(div_rn(aos[LY::A_BOX + 2] - P.box_z, P.lift_height_range), 0.0f, 1.0f) * m3);
+  emit_term<true>(A, c, m, DEX_R_S3_GRASP_MAINTENANCE, fg * m3);
+  emit_term<true>(A, c, m, DEX_R_S3_GRASP_DURATION, clampf(div_rn(m.graspdur, P.contact_duration_threshold_s), 0.0f, 1.0f) * m3);
+  // completion bonuses :1025-1048 (transition and not failed), penetration :1194-1208
+  emit_term<true>(A, c, m, DEX_R_S1_COMPLETION, (m.j2 && m.hcok && m.sok) ? 1.0f : 0.0f);
+  emit_term<true>(A, c, m, DEX_R_S2_COMPLETION, (m.j3 && m.grasp) ? 1.0f : 0.0f);
+  emit_term<true>(A, c, m, DEX_R_PENETRATION_PENALTY, fmaxf(P.penetration_threshold - m.min_tip_box, 0.0f) * P.penetration_depth_scale);
 }
 
-// phase C, warp 0: termination (step_processor.py:133-181, termination_manager.py:120-278), masks, tile record.
-// Returns the exclusive termination class of this lane's env: bit 0 success, 1 failure, 2 timeout.
+// ---- termination (step_processor.py:133-181, termination_manager.py:120-278), masks, tile record.
+// Returns the exclusive termination class of this lane's env (bit 0 success, 1 failure, 2 timeout) and the reset ballot.
 template <bool BG>
-__device__ __forceinline__ unsigned phase_combine(const Post2Args& A, const Cx<BG>& c, const unsigned stamp, unsigned* s_rbits) {
+__device__ __forceinline__ unsigned part_terminate(const Post2Args& A, const Cx<BG>& c, const Mid& m, const unsigned stamp,
+                                                   unsigned& rbits_out) {
   using LY = Lay<BG>;
   const DexParams& P = A.p;
   const DexStateBuffers& st = A.st;
-  const float* wk = c.wk;
   bool should_reset = false, t_success = false, t_failure = false, t_timeout = false;
   int ep_len_done = 0;
   bool crit[DEX_NUM_CRITERIA];
@@ -898,18 +790,13 @@ __device__ __forceinline__ unsigned phase_combine(const Post2Args& A, const Cx<B
     const int step_now = c.i64lo(LY::I_STEP) + 1;  // step_processor.py:80
     st.episode_step_count[c.env] = (long long)step_now;
     ep_len_done = step_now;
-    crit[DEX_C_HITTING_GROUND] = wk[LY::W_HITG * 32] != 0.0f;
+    crit[DEX_C_HITTING_GROUND] = m.hitg;
     if (BG) {
-      const bool grasp = wk[LY::W_GRASP * 32] != 0.0f;
-      const bool j2 = wk[LY::W_J2 * 32] != 0.0f, j3 = wk[LY::W_J3 * 32] != 0.0f;
-      const bool qual_ok = (wk[LY::W_HCOK * 32] != 0.0f) && (wk[LY::W_SOK * 32] != 0.0f);
-      const int stage = __float_as_int(wk[LY::W_STAGE * 32]);
-      const int sds = __float_as_int(wk[LY::W_SDS * 32]);
-      crit[DEX_C_GRASP_LIFT_SUCCESS] = sds >= P.contact_duration_threshold_steps;
-      crit[DEX_C_BOX_TOO_FAR] = wk[LY::W_BOXFAR * 32] != 0.0f;
-      const bool pregrasp_failed = j2 && !qual_ok;  // _evaluate_pregrasp_quality :1334-1364
-      const bool contact_failed = j3 && !grasp;
-      const bool grasp_lost = (stage == 3) && !grasp;
+      crit[DEX_C_GRASP_LIFT_SUCCESS] = m.sds >= P.contact_duration_threshold_steps;
+      crit[DEX_C_BOX_TOO_FAR] = m.boxfar;
+      const bool pregrasp_failed = m.j2 && !(m.hcok && m.sok);  // _evaluate_pregrasp_quality :1334-1364
+      const bool contact_failed = m.j3 && !m.grasp;
+      const bool grasp_lost = (m.stage == 3) && !m.grasp;
       crit[DEX_C_STAGE1_PREGRASP_FAILED] = pregrasp_failed;
       crit[DEX_C_STAGE2_CONTACT_FAILED] = contact_failed;
       crit[DEX_C_STAGE3_GRASP_LOST] = grasp_lost;
@@ -939,11 +826,9 @@ __device__ __forceinline__ unsigned phase_combine(const Post2Args& A, const Cx<B
   // reset ballot word + cross-env counters (termination_manager.py:164-185,259-266)
   const unsigned fullmask = 0xffffffffu;
   const unsigned rbits = __ballot_sync(fullmask, should_reset);
+  rbits_out = rbits;
   const int lane = c.lane;
-  if (lane == 0) {
-    A.out.reset_bits[c.e0 >> 5] = rbits;
-    *s_rbits = rbits;
-  }
+  if (lane == 0) A.out.reset_bits[c.e0 >> 5] = rbits;
   const unsigned bs = __ballot_sync(fullmask, t_success), bf = __ballot_sync(fullmask, t_failure),
                  bt = __ballot_sync(fullmask, t_timeout);
   unsigned bc[DEX_NUM_CRITERIA];
@@ -981,22 +866,16 @@ __device__ __forceinline__ unsigned phase_combine(const Post2Args& A, const Cx<B
   return (t_success ? 1u : 0u) | (t_failure ? 2u : 0u) | (t_timeout ? 4u : 0u);
 }
 
-// phase D, warp 0: ordered weighted sum (reward_calculator.py:223-275) + termination rewards
-// (termination_manager.py:280-321, step_processor.py:204-219)
+// ---- ordered weighted sum (reward_calculator.py:223-275) + termination rewards
+//      (termination_manager.py:280-321, step_processor.py:204-219)
 template <bool BG>
-__device__ __forceinline__ void phase_total(const Post2Args& A, const Cx<BG>& c, const unsigned cls) {
-  using LY = Lay<BG>;
-  if (!c.act) return;
+__device__ __forceinline__ void part_total(const Post2Args& A, const Cx<BG>& c, const Mid& m, const unsigned cls) {
   const DexParams& P = A.p;
-  const float* wk = c.wk;
-  constexpr int NT = BG ? DEX_NUM_REWARD_TERMS : DEX_NUM_COMMON_TERMS;
-  float wv[NT];
-#pragma unroll
-  for (int i = 0; i < NT; ++i) wv[i] = wk[(LY::W_WGT + i) * 32];  // terms with weight 0 hold stale values: skipped below
+  constexpr int I0 = BG ? DEX_NUM_COMMON_TERMS : 0, I1 = BG ? DEX_NUM_REWARD_TERMS : DEX_NUM_COMMON_TERMS;
   float total = 0.0f;
 #pragma unroll
-  for (int i = 0; i < NT; ++i)
-    if (P.reward_weight[i] != 0.0f) total += wv[i];  // dict order: common, then task
+  for (int i = I0; i < I1; ++i)
+    if (P.reward_weight[i] != 0.0f) total += m.wgt[i];  // dict order: common, then task
   const bool t_success = cls & 1u, t_failure = cls & 2u, t_timeout = cls & 4u;
   const float rs = t_success ? P.success_reward : 0.0f;
   const float rf = t_failure ? P.failure_reward : 0.0f;
@@ -1013,54 +892,48 @@ __device__ __forceinline__ void phase_total(const Post2Args& A, const Cx<BG>& c,
   A.out.rew_buf[c.env] = rew;
 }
 
-// obs tile -> obs_buf for the 32-column chunks in `chunks`: the env rows are spread over NW warps (this one is number w),
-// lane = column: every global store is one full 128-byte request.  Row pointers are formed once; the chunk offset is
-// an immediate.
-template <int NW>
-__device__ __forceinline__ void copy_obs(const float* s_obs, float* g_tile, const int W, const int WP, const int ne,
-                                         const unsigned chunks, const int w, const int lane) {
-  constexpr int R = (32 + NW - 1) / NW;
-  const float* sp[R];
-  float* gp[R];
-  bool ok[R];
+// obs tile -> obs_buf by the tile's own warp: lane = column, every global store is one full 128-byte request;
+// eight rows per batch keep eight loads in flight
+__device__ __forceinline__ void copy_obs(const float* s_obs, float* g_tile, const int W, const int WP, const int ne, const int lane) {
+  const int nchunk = (W + 31) >> 5;
+  for (int ch = 0; ch < nchunk; ++ch) {
+    const int col = 32 * ch + lane;
+    if (col < W) {
+      const float* sp = s_obs + col;
+      float* gp = g_tile + col;
+      if (ne == 32) {
 #pragma unroll
-  for (int i = 0; i < R; ++i) {
-    const int row = w + NW * i;
-    ok[i] = row < ne;
-    sp[i] = s_obs + row * WP + lane;
-    gp[i] = g_tile + (size_t)row * W + lane;
-  }
+        for (int r0 = 0; r0 < 32; r0 += 8) {
+          float v[8];
 #pragma unroll
-  for (int ch = 0; ch < 8; ++ch) {  // obs_dim <= 256
-    if (!((chunks >> ch) & 1u)) continue;
-    if (32 * ch + lane < W) {
-      float v[R];
+          for (int i = 0; i < 8; ++i) v[i] = sp[(r0 + i) * WP];
 #pragma unroll
-      for (int i = 0; i < R; ++i)
-        if (ok[i]) v[i] = sp[i][32 * ch];
-#pragma unroll
-      for (int i = 0; i < R; ++i)
-        if (ok[i]) gp[i][32 * ch] = v[i];
+          for (int i = 0; i < 8; ++i) gp[(size_t)(r0 + i) * W] = v[i];
+        }
+      } else {
+        for (int r = 0; r < ne; ++r) gp[(size_t)r * W] = sp[r * WP];
+      }
     }
   }
 }
 
 // ------------------------------------------------------------------------------------------------
-// the kernel
+// the kernel: NC (compute warp, producer warp) pairs per CTA, one CTA per SM, persistent
 // ------------------------------------------------------------------------------------------------
-template <bool BG>
-__global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(const __grid_constant__ Post2Args A) {
+template <bool BG, int NC>
+__global__ void __launch_bounds__(64 * NC, 1) post_physics_v2_kernel(const __grid_constant__ Post2Args A) {
   using LY = Lay<BG>;
+  constexpr int kThreads = 64 * NC;
   extern __shared__ __align__(128) unsigned char smem2[];
-  __shared__ __align__(8) unsigned long long s_bar[2 * kStages];  // full[0..], empty[0..]
-  __shared__ float s_reset_u[32 * kConsWarps];
+  __shared__ __align__(8) unsigned long long s_bar[2 * kMaxPairs];  // full[pair], empty[pair]
+  __shared__ float s_reset_u[32 * kMaxPairs];
   __shared__ int s_rbo[kRbW + 1];  // gathered rigid slot -> float offset inside one env's [NB,13] block
   __shared__ unsigned long long s_rng_step;
-  __shared__ unsigned s_rbits;
-  __shared__ int s_epi_warp[kConsWarps];
+  __shared__ int s_epi_warp[8];
   __shared__ int s_epi_base;
   __shared__ int s_epi_cnt[DEX_NUM_COUNTERS];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int slot_bytes = LY::STAGE_BYTES + 32 * A.wp * 4;
 
   // ---- the epilogue CTA (last block): polls the tile records of the workers, all of which are co-resident ----
   if (A.fused_epilogue && (int)blockIdx.x == A.workers) {
@@ -1078,20 +951,18 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
       s_rng_step = rs;
     }
     __syncthreads();
-    if (tid < kConsThreads)
-      epilogue_records<kConsThreads, 2>(A.ep, A.n, A.p.max_consecutive_successes, ((unsigned)s_rng_step + 1u) & 0xffffu,
-                                        s_epi_warp, &s_epi_base, s_epi_cnt, reinterpret_cast<unsigned*>(smem2),
-                                        (int)(A.smem_bytes / 4), tid);
+    epilogue_records<kThreads, 0>(A.ep, A.n, A.p.max_consecutive_successes, ((unsigned)s_rng_step + 1u) & 0xffffu, s_epi_warp,
+                                  &s_epi_base, s_epi_cnt, reinterpret_cast<unsigned*>(smem2), (NC * slot_bytes) / 4, tid);
     return;
   }
 
   // ---- setup ----
-  const uint32_t bar_full = s32(&s_bar[0]), bar_empty = s32(&s_bar[kStages]);
+  const uint32_t bar_full = s32(&s_bar[0]), bar_empty = s32(&s_bar[kMaxPairs]);
   if (tid == 0) {
 #pragma unroll
-    for (int s = 0; s < kStages; ++s) {
-      mbar_init(bar_full + 8 * s, kProdWarps);
-      mbar_init(bar_empty + 8 * s, kConsWarps);
+    for (int p = 0; p < NC; ++p) {
+      mbar_init(bar_full + 8 * p, 1);
+      mbar_init(bar_empty + 8 * p, 1);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -1104,19 +975,16 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
   __syncthreads();
   pdl_launch_dependents();
   TL2_DECL;
-  float* const wk_base = reinterpret_cast<float*>(smem2 + kStages * LY::STAGE_BYTES);
-  float* const s_obs = wk_base + LY::W_COUNT * 32;
   const int tiles = A.tiles, workers = A.workers;
+  const int pair = warp < NC ? warp : warp - NC;
+  unsigned char* const stage = smem2 + pair * slot_bytes;
+  float* const s_obs = reinterpret_cast<float*>(stage + LY::STAGE_BYTES);
+  const uint32_t fb = bar_full + 8 * pair, eb = bar_empty + 8 * pair;
+  // tile of (iteration it, CTA b, pair p) = b + workers * (p + NC * it): consecutive tiles go to different SMs
+  const int tile0 = blockIdx.x + workers * pair, tstep = workers * NC;
 
-  if (warp >= kConsWarps) {
-    // =========================== producer warps ===========================
-    const int pw = warp - kConsWarps, ptid = tid - kConsThreads;
-    // this thread's bulk entry (one row / tile array per producer thread)
-    const bool e_has = ptid < A.n_bulk, e_early = ptid < A.n_bulk_early;
-    const char* const e_ptr = e_has ? reinterpret_cast<const char*>(A.bk_ptr[ptid]) : nullptr;
-    const uint32_t e_dst = e_has ? (uint32_t)A.bk_dst16[ptid] * 16u : 0u;
-    const uint32_t e_len = e_has ? (uint32_t)A.bk_len16[ptid] * 16u : 0u;
-    // scattered Isaac Gym rows: lane = gathered float (rigid slots lane, lane + 32, lane + 64; contact / box slot lane)
+  if (warp >= NC) {
+    // =========================== producer warp of this pair ===========================
     const int rbo0 = s_rbo[lane], rbo1 = s_rbo[lane + 32], rbo2 = s_rbo[min(lane + 64, kRbW - 1)];
     const bool p_rb0 = lane < 7 || lane >= 13 || A.common;  // hand velocities feed only the common reward terms
     const bool p_rb2 = lane + 64 < kRbW;
@@ -1133,74 +1001,68 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
     }
     const float* const x_base = (is_box ? (const float*)A.sim.actor_root_state : A.sim.net_contact_force) + xoff;
     const size_t nb13 = (size_t)A.p.num_bodies * 13;
-    const size_t rb_step = kProdWarps * nb13, x_step = (size_t)kProdWarps * xrow;
     const bool early = (A.flags & DEX_FLAG_EARLY_SIM_LOADS) != 0;
-    constexpr int R = 32 / kProdWarps;  // env rows per producer warp
+    const uint32_t sst = s32(stage);
     int it = 0;
-    for (int tile = blockIdx.x; tile < tiles; tile += workers, ++it) {
-      const int s = it & 1, use = it >> 1;
+    for (int tile = tile0; tile < tiles; tile += tstep, ++it) {
       const int e0 = tile * 32, ne = min(32, A.n - e0);
-      unsigned char* stage = smem2 + s * LY::STAGE_BYTES;
-      const uint32_t sst = s32(stage), fb = bar_full + 8 * s;
       TL2(it, 16);
-      if (use > 0) mbar_wait(bar_empty + 8 * s, (unsigned)(use - 1) & 1u);
+      if (it > 0) mbar_wait(eb, (unsigned)(it - 1) & 1u);
       TL2(it, 17);
-      const bool bulk = A.bulk_ok && ne == 32;  // CTA-uniform
+      const bool bulk = A.bulk_ok && ne == 32;  // warp-uniform
       if (it == 0 && !early) pdl_wait();
-      if (bulk && e_has && e_early) bulk_g2s(sst + e_dst, e_ptr + (size_t)tile * e_len, e_len, fb);
-      if (bulk && e_has && !e_early && !(it == 0 && early)) bulk_g2s(sst + e_dst, e_ptr + (size_t)tile * e_len, e_len, fb);
-      // ---- scattered rows: warp pw takes env rows pw, pw+4, ..; consecutive lanes = consecutive floats ----
-      float v[R][4];
-      {
-        const float* q0 = A.sim.rigid_body_state + (size_t)(e0 + pw) * nb13;
-        const float* qx = x_base + (size_t)(e0 + pw) * xrow;
-        if (ne == 32) {
+      // bulk entries: lane l issues entries l, l + 32, ..; the sim-tensor entries come first in the table
+      if (bulk) {
+        for (int k = lane; k < A.n_bulk; k += 32) {
+          if (it == 0 && early && k >= A.n_bulk_early) break;
+          const uint32_t len = (uint32_t)A.bk_len16[k] * 16u;
+          bulk_g2s(sst + (uint32_t)A.bk_dst16[k] * 16u, reinterpret_cast<const char*>(A.bk_ptr[k]) + (size_t)tile * len, len, fb);
+        }
+      }
+      // ---- scattered Isaac Gym rows, 16 env rows per batch: consecutive lanes = consecutive floats of a row ----
+      float* aos = reinterpret_cast<float*>(stage + LY::OFF_AOS) + lane;
+      const float* q0 = A.sim.rigid_body_state + (size_t)e0 * nb13;
+      const float* qx = x_base + (size_t)e0 * xrow;
+#pragma unroll 1
+      for (int half = 0; half < 2; ++half) {
+        float v[16][4];
 #pragma unroll
-          for (int i = 0; i < R; ++i) {
+        for (int i = 0; i < 16; ++i) {
+          if (ne == 32 || 16 * half + i < ne) {
             if (p_rb0) v[i][0] = __ldg(q0 + rbo0);
             v[i][1] = __ldg(q0 + rbo1);
             if (p_rb2) v[i][2] = __ldg(q0 + rbo2);
             if (p_x) v[i][3] = *qx;  // actor_root_state rows are rewritten by the fused reset of this kernel: plain load
-            q0 += rb_step;
-            qx += x_step;
           }
-        } else {
-#pragma unroll
-          for (int i = 0; i < R; ++i) {
-            if (pw + kProdWarps * i < ne) {
-              if (p_rb0) v[i][0] = __ldg(q0 + rbo0);
-              v[i][1] = __ldg(q0 + rbo1);
-              if (p_rb2) v[i][2] = __ldg(q0 + rbo2);
-              if (p_x) v[i][3] = *qx;
+          q0 += nb13;
+          qx += xrow;
+        }
+        if (half == 1 && it == 0 && early) {
+          TL2(it, 18);
+          pdl_wait();  // everything above touched only kernel parameters and the sim tensors
+          if (bulk) {
+            for (int k = A.n_bulk_early + lane; k < A.n_bulk; k += 32) {
+              const uint32_t len = (uint32_t)A.bk_len16[k] * 16u;
+              bulk_g2s(sst + (uint32_t)A.bk_dst16[k] * 16u, reinterpret_cast<const char*>(A.bk_ptr[k]) + (size_t)tile * len, len, fb);
             }
-            q0 += rb_step;
-            qx += x_step;
           }
         }
-      }
-      TL2(it, 18);
-      if (it == 0 && early) {
-        pdl_wait();  // everything above touched only kernel parameters and the sim tensors
-        if (bulk && e_has && !e_early) bulk_g2s(sst + e_dst, e_ptr + (size_t)tile * e_len, e_len, fb);
-      }
-      if (!bulk) prod_rows_ldg<BG>(A, stage, e0, ne, pw, lane);
-      {
-        float* a = reinterpret_cast<float*>(stage + LY::OFF_AOS) + pw * LY::SA + lane;
 #pragma unroll
-        for (int i = 0; i < R; ++i) {
-          if (ne == 32 || pw + kProdWarps * i < ne) {
-            if (p_rb0) a[LY::A_RB] = v[i][0];
-            a[LY::A_RB + 32] = v[i][1];
-            if (p_rb2) a[LY::A_RB + 64] = v[i][2];
-            if (p_x) a[LY::A_CF] = v[i][3];
+        for (int i = 0; i < 16; ++i) {
+          if (ne == 32 || 16 * half + i < ne) {
+            if (p_rb0) aos[LY::A_RB] = v[i][0];
+            aos[LY::A_RB + 32] = v[i][1];
+            if (p_rb2) aos[LY::A_RB + 64] = v[i][2];
+            if (p_x) aos[LY::A_CF] = v[i][3];
           }
-          a += kProdWarps * LY::SA;
+          aos += LY::SA;
         }
       }
+      if (!bulk) prod_rows_ldg(A, stage, e0, ne, lane);
       __syncwarp();
       TL2(it, 19);
       if (lane == 0) {
-        if (pw == 0 && bulk)
+        if (bulk)
           mbar_arrive_tx(fb, A.tx_bytes);
         else
           mbar_arrive(fb);
@@ -1209,130 +1071,97 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
     return;
   }
 
-  // =========================== consumer warps ===========================
+  // =========================== compute warp of this pair ===========================
   Cx<BG> c;
   c.lane = lane;
-  c.cw = warp;
   c.N = (size_t)A.n;
-  c.wk = wk_base + lane;
   c.obs = s_obs + lane * A.wp;
+  c.stage = stage;
   unsigned stamp = 0;
   uint64_t rng_step = 0;
   const int W = A.p.obs_dim, WP = A.wp;
-  const unsigned all_chunks = (W >= 256) ? 0xffu : ((1u << ((W + 31) >> 5)) - 1u);
-  const unsigned late_chunks = BG ? (A.obs_late & all_chunks) : all_chunks;  // BaseTask has no phase B: one copy at the end
-  const unsigned early_chunks = all_chunks & ~late_chunks;
   int it = 0;
-  for (int tile = blockIdx.x; tile < tiles; tile += workers, ++it) {
-    const int s = it & 1, use = it >> 1;
+  for (int tile = tile0; tile < tiles; tile += tstep, ++it) {
     c.e0 = tile * 32;
     c.ne = min(32, A.n - c.e0);
     c.act = lane < c.ne;
     c.env = (size_t)c.e0 + (c.act ? lane : 0);
-    c.stage = smem2 + s * LY::STAGE_BYTES;
-    float* const g_obs = A.out.obs_buf + (size_t)c.e0 * W;
     TL2(it, 0);
-    mbar_wait(bar_full + 8 * s, (unsigned)use & 1u);
+    mbar_wait(fb, (unsigned)it & 1u);
     TL2(it, 1);
-    // Philox step counter == stamp of this step's tile records: read once per CTA, behind the first full barrier
-    // (i.e. behind the producers' griddepcontrol.wait; the epilogue CTA advances it only after every record of this
-    // launch has been published), by one thread, and parked while phase A runs
-    unsigned long long rs_tmp = 0ull;
-    if (it == 0 && tid == 0) rs_tmp = A.st.rng_step ? *reinterpret_cast<const volatile unsigned long long*>(A.st.rng_step) : A.step;
-
-    phase_a<BG>(A, c);
-    if (it == 0 && tid == 0) s_rng_step = rs_tmp;
-    TL2(it, 2);
-    cons_sync();
-    TL2(it, 3);
     if (it == 0) {
-      rng_step = s_rng_step;
+      // Philox step counter == stamp of this step's tile records: read behind the first full barrier (i.e. behind the
+      // producer's griddepcontrol.wait; the epilogue CTA advances it only after every record of this launch is out)
+      unsigned long long rs = 0ull;
+      if (lane == 0) rs = A.st.rng_step ? *reinterpret_cast<const volatile unsigned long long*>(A.st.rng_step) : A.step;
+      rng_step = __shfl_sync(0xffffffffu, rs, 0);
       stamp = ((unsigned)rng_step + 1u) & 0xffffu;
     }
-    if (BG) {
-      // phase B: warps 0 / 1 run the two scalar chains, the other six send off the obs chunks that are already final
-      if (warp < 2)
-        phase_b<BG>(A, c);
+    Mid m;
+    unsigned cls = 0, rbits = 0;
+    if (c.act) {
+      part_poses<BG, false>(A, c, m);
+      part_poses<BG, true>(A, c, m);
+      part_contacts<BG>(A, c, m);
+      part_hand<BG>(A, c, m);
+      part_dofs<BG>(A, c, m);
+      part_copies<BG>(A, c);
+      if constexpr (BG) part_task_state(A, c, m);
+    }
+    TL2(it, 2);
+    cls = part_terminate<BG>(A, c, m, stamp, rbits);
+    TL2(it, 3);
+    if (c.act) {
+      if constexpr (BG)
+        part_task_terms(A, c, m);
       else
-        copy_obs<kConsWarps - 2>(s_obs, g_obs, W, WP, c.ne, early_chunks, warp - 2, lane);
-      TL2(it, 4);
-      cons_sync();
-      TL2(it, 5);
+        part_common_terms(A, c, m);
+      part_total<BG>(A, c, m, cls);
     }
-    // phase C: warp 0 termination + tile record; warps 1..7 the reward terms
-    unsigned cls = 0;
-    if (warp == 0) {
-      cls = phase_combine<BG>(A, c, stamp, &s_rbits);
-    } else if (c.act) {
-      if (BG) {
-        const int stage_now = __float_as_int(c.wk[LY::W_STAGE * 32]);
-        for (int i = DEX_NUM_COMMON_TERMS + (warp - 1); i < DEX_NUM_REWARD_TERMS; i += kConsWarps - 1) {
-          if (A.p.reward_weight[i] == 0.0f) continue;  // reward_calculator.py:247-251: zero-weight terms are not materialised
-          emit_term<BG>(A, c, i, task_term<BG>(A, c, i, stage_now));
-        }
-      } else {
-        for (int i = warp - 1; i < DEX_NUM_COMMON_TERMS; i += kConsWarps - 1) {
-          if (A.p.reward_weight[i] == 0.0f) continue;
-          emit_term<BG>(A, c, i, common_term<BG>(A, c, i));
-        }
-      }
-    }
-    // the raw stage is not read after this point: hand it back to the producers
+    TL2(it, 4);
+    // the raw stage is not read after this point: hand it back to the producer
     __syncwarp();
-    TL2(it, 6);
-    cons_sync();
-    TL2(it, 7);
-    if (lane == 0) mbar_arrive(bar_empty + 8 * s);
-    if (warp == 0) phase_total<BG>(A, c, cls);
-    TL2(it, 8);
-    copy_obs<kConsWarps>(s_obs, g_obs, W, WP, c.ne, late_chunks, warp, lane);
-    TL2(it, 9);
-    // ---- fused reset of the finished envs (dexhand_base.py:743-756): one warp per env ----
-    {
-      unsigned mask = s_rbits;  // written by warp 0 before the barrier above
-      if (mask && !(A.flags & DEX_FLAG_NO_FUSED_RESET)) {
-        for (int k = 0; mask; ++k) {
-          const int e = __ffs(mask) - 1;
-          mask &= mask - 1;
-          if ((k & (kConsWarps - 1)) == warp) reset_env_warp<BG>(A, c.e0 + e, rng_step, s_reset_u + 32 * warp);
-        }
+    if (lane == 0) mbar_arrive(eb);
+    copy_obs(s_obs, A.out.obs_buf + (size_t)c.e0 * W, W, WP, c.ne, lane);
+    TL2(it, 5);
+    // ---- fused reset of the finished envs (dexhand_base.py:743-756) ----
+    if (rbits && !(A.flags & DEX_FLAG_NO_FUSED_RESET)) {
+      unsigned mask = rbits;
+      while (mask) {
+        const int e = __ffs(mask) - 1;
+        mask &= mask - 1;
+        reset_env_warp<BG>(A, c.e0 + e, rng_step, s_reset_u + 32 * pair);
       }
     }
-    TL2(it, 10);
-    cons_sync();  // work block, obs tile and s_rbits are reused by the next tile
-    TL2(it, 11);
+    __syncwarp();  // the obs tile is rewritten by the next tile
+    TL2(it, 6);
   }
 }
 
-template <bool BG>
+template <bool BG, int NC>
 int launch_post2_t(Post2Args& a, cudaStream_t s) {
+  using LY = Lay<BG>;
   const int rc = build_post2<BG>(a);
   if (rc) return rc;
-  static int ctas_per_sm = -1, num_sms = 0;
+  a.nc = NC;
+  a.smem_bytes = (uint32_t)(NC * (LY::STAGE_BYTES + 32 * a.wp * 4));
+  if (a.smem_bytes > 227 * 1024 - 2048) return DEX_ERR_SIZE;
+  static int num_sms = 0;
   static size_t smem_cfg = 0;
   if (a.smem_bytes > smem_cfg) {
-    const size_t want = a.smem_bytes > 120 * 1024 ? a.smem_bytes : 120 * 1024;
-    const cudaError_t e = cudaFuncSetAttribute(post_physics_v2_kernel<BG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)want);
+    const cudaError_t e = cudaFuncSetAttribute(post_physics_v2_kernel<BG, NC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a.smem_bytes);
     if (e != cudaSuccess) return (int)e;
-    smem_cfg = want;
-    ctas_per_sm = -1;
-  }
-  static size_t smem_occ = 0;
-  if (ctas_per_sm < 0 || smem_occ != a.smem_bytes) {
-    int dev = 0, occ = 0;
+    smem_cfg = a.smem_bytes;
+    int dev = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
-    const cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, post_physics_v2_kernel<BG>, kThreads, a.smem_bytes);
-    if (e != cudaSuccess) return (int)e;
-    if (occ < 1) return DEX_ERR_SIZE;
-    ctas_per_sm = occ;
-    smem_occ = a.smem_bytes;
   }
   const int fused = a.fused_epilogue ? 1 : 0;
-  int cap = num_sms * ctas_per_sm - fused;  // every CTA of the launch (workers + epilogue) is resident at once
-  if (cap < 1) cap = 1;
-  a.workers = a.tiles < cap ? a.tiles : cap;
-  const cudaError_t e = launch_step_kernel(post_physics_v2_kernel<BG>, a.workers + fused, kThreads, a.smem_bytes, s, a);
+  // one CTA per SM; every CTA of the launch (workers + epilogue) is resident at once
+  const int cap = num_sms - fused > 1 ? num_sms - fused : 1;
+  const int want = (a.tiles + NC - 1) / NC;  // CTAs needed to give every tile its own slot
+  a.workers = want < cap ? want : cap;
+  const cudaError_t e = launch_step_kernel(post_physics_v2_kernel<BG, NC>, a.workers + fused, 64 * NC, a.smem_bytes, s, a);
   if (e != cudaSuccess) (void)cudaGetLastError();
   return e == cudaSuccess ? DEX_OK : (int)e;
 }

@@ -71,11 +71,10 @@ t = runs[0]
 used = (t[:, 0, 0] > 0)
 print(f"envs {n} task {task}: {int(used.sum())} worker CTAs; tiles per CTA: "
       f"{ {k: int(((t[:, :, 1] > 0).sum(dim=1) == k).sum()) for k in range(1, ITERS + 1) if int(((t[:, :, 1] > 0).sum(dim=1) == k).sum())} }")
-cons = [((0, 1), "wait full (load latency seen by consumers)"), ((1, 2), "items (thread 0's warp)"), ((2, 3), "  barrier A"),
-        ((3, 4), "scalar jobs (warp 0)"), ((4, 5), "  barrier B"), ((5, 6), "combine + record (warp 0)"), ((6, 7), "  barrier C"),
-        ((7, 8), "total (warp 0)"), ((8, 9), "obs tile -> obs_buf"), ((9, 10), "reset"), ((10, 11), "  barrier D"),
-        ((0, 11), "whole tile (consumer)")]
-prod = [((16, 17), "producer: wait empty"), ((17, 18), "producer: issue bulk + gathers"), ((18, 19), "producer: rows + STS + arrive")]
+cons = [((0, 1), "wait full (load latency seen by the compute warp)"), ((1, 2), "per-env parts (poses, contacts, hand, DOFs, FSM)"),
+        ((2, 3), "termination + ballots + record"), ((3, 4), "reward terms + total"), ((4, 5), "obs tile -> obs_buf"),
+        ((5, 6), "reset"), ((0, 6), "whole tile (compute warp)")]
+prod = [((16, 17), "producer: wait empty"), ((17, 19), "producer: bulk issue + gather + STS + arrive")]
 for it in range(ITERS):
     if not any(bool((r[:, it, 1] > 0).any()) for r in runs):
         break
@@ -90,7 +89,7 @@ for it in range(ITERS):
     for (a_, b_), nm in cons + prod:
         d_med = med(lambda r: None if dur(r, a_, b_) is None else float(dur(r, a_, b_).median()))
         d_max = med(lambda r: None if dur(r, a_, b_) is None else float(dur(r, a_, b_).max()))
-        print(f"  {nm:44s} median {d_med:7.2f}  max {d_max:7.2f} us")
+        print(f"  {nm:52s} median {d_med:7.2f}  max {d_max:7.2f} us")
 # absolute: when does each CTA finish its last tile, relative to the earliest CTA start (globaltimer, 32 ns ticks or coarser)
 
 
@@ -103,7 +102,7 @@ def ends(r):
     out = []
     for cta in torch.nonzero(m).flatten().tolist():
         li = int(last_it[cta])
-        out.append(float(r[cta, li, 30] - t0) / 1e3 + float(r[cta, li, 11] - r[cta, li, 0]) / GHZ)
+        out.append(float(r[cta, li, 30] - t0) / 1e3 + float(r[cta, li, 6] - r[cta, li, 0]) / GHZ)
     return out
 
 
