@@ -51,6 +51,65 @@ struct Lay {
   static constexpr int STAGE_BYTES = (OFF_AOS + 32 * SA * 4 + 127) / 128 * 128;
 };
 
+
+// ------------------------------------------------------------------------------------------------
+// The reference's two shipped observation layouts (cfg/task/BaseTask.yaml:103-116, BlindGrasping.yaml:50-66; SURVEY
+// App. B) as compile-time constants.  A launch whose parameter block matches them (std_layout_matches) runs the STD
+// instance of the kernel: every obs column offset is an immediate, no key test and no zero-weight test survives, so
+// the per-env program is (almost) free of taken branches - with one compute warp per scheduler a taken branch costs a
+// front-end refetch that nothing hides (profiles/r02c_*).  Any other layout runs the generic instance.
+// ------------------------------------------------------------------------------------------------
+template <bool BG>
+__host__ __device__ constexpr int std_obs_off(const int k) {
+  if (BG) {
+    switch (k) {
+      case DEX_K_BASE_DOF_POS: return 0;
+      case DEX_K_ACTIVE_FINGER_DOF_POS: return 6;
+      case DEX_K_BASE_DOF_VEL: return 18;
+      case DEX_K_ACTIVE_FINGER_DOF_VEL: return 24;
+      case DEX_K_CONTACT_BINARY: return 36;
+      case DEX_K_CONTACT_DURATION: return 41;
+      case DEX_K_HAND_POSE: return 46;
+      case DEX_K_PREV_ACTIONS: return 53;
+      case DEX_K_FINGERTIP_POSES_WORLD: return 71;
+      case DEX_K_FINGERPAD_POSES_WORLD: return 106;
+      case DEX_K_FIRST_THREE_FINGERPAD_CENTROID: return 141;
+      case DEX_K_EPISODE_TIME: return 144;
+      case DEX_K_FINGERPAD_DISTANCES: return 145;
+      case DEX_K_CURRENT_STAGE: return 155;
+      case DEX_K_TIME_IN_STAGE: return 156;
+      case DEX_K_STAGE_PROGRESS: return 157;
+      default: return -1;
+    }
+  } else {
+    switch (k) {
+      case DEX_K_BASE_DOF_POS: return 0;
+      case DEX_K_BASE_DOF_VEL: return 6;
+      case DEX_K_ACTIVE_FINGER_DOF_POS: return 12;
+      case DEX_K_ACTIVE_FINGER_DOF_VEL: return 24;
+      case DEX_K_HAND_POSE: return 36;
+      case DEX_K_CONTACT_BINARY: return 43;
+      case DEX_K_PREV_ACTIONS: return 48;
+      case DEX_K_BASE_DOF_TARGET: return 66;
+      case DEX_K_ACTIVE_FINGER_DOF_TARGET: return 72;
+      case DEX_K_FINGERTIP_POSES_WORLD: return 84;
+      case DEX_K_FINGERTIP_POSES_HAND: return 119;
+      case DEX_K_FINGERPAD_POSES_WORLD: return 154;
+      case DEX_K_FINGERPAD_POSES_HAND: return 189;
+      default: return -1;
+    }
+  }
+}
+constexpr int kStdObsDim[2] = {224, 158};
+// HardwareMapping order of the 12 active finger DOFs (hand_initializer.py:20-34): dof -> column, -1 = not active
+__host__ __device__ constexpr int std_dof2afj(const int d) {
+  switch (d) {
+    case 8: return 0; case 7: return 1; case 6: return 2; case 10: return 3; case 12: return 4; case 11: return 5;
+    case 16: return 6; case 15: return 7; case 20: return 8; case 19: return 9; case 24: return 10; case 23: return 11;
+    default: return -1;
+  }
+}
+
 struct Post2Args {
   DexParams p;
   DexSimViews sim;
@@ -72,6 +131,12 @@ struct Post2Args {
   uint32_t smem_bytes;
   int32_t rb_off[11], cf_off[6];
   int32_t dof2afj[DEX_NUM_DOF];           // dof -> index in active_finger_dof, -1 = not an active finger DOF
+  // the same rows as GROUPS (one per state buffer): lane r of the producer warp copies row r of the group, every
+  // table read is warp-uniform (a lane-indexed read of the parameter bank would serialise 32-way)
+  int32_t n_grp, n_grp_early;
+  uint64_t grp_ptr[16];                   // global base of the buffer
+  uint32_t grp_rowb[16];                  // bytes between consecutive rows of the buffer (N * elem)
+  uint16_t grp_rows[16], grp_dst16[16], grp_len16[16];  // rows (<= 32), stage offset of row 0 / 16, bytes per row and tile / 16
   uint64_t bk_ptr[kMaxBulk];              // global base of the row / tile array
   uint16_t bk_dst16[kMaxBulk];            // byte offset inside the stage / 16
   uint16_t bk_len16[kMaxBulk];            // bytes per full tile / 16 (== source stride per tile)
@@ -124,9 +189,19 @@ inline int build_post2(Post2Args& a) {
   for (int d = 0; d < DEX_NUM_DOF; ++d) a.dof2afj[d] = -1;
   for (int j = 0; j < DEX_NUM_ACTIVE_FINGER; ++j) a.dof2afj[P.active_finger_dof[j]] = j;
 
-  int k = 0;
+  int k = 0, g = 0;
   bool aligned = (a.n % 16) == 0;
   uint32_t tx = 0;
+  auto grp = [&](const void* base, int rows, int elem, int dst, int kind) {  // rows of one buffer = one group
+    if (g >= 16 || rows > 32) return;
+    const int len = kind == BK_DOF ? 32 * 52 * 4 : kind == BK_TGT ? 32 * 26 * 4 : 32 * elem;
+    a.grp_ptr[g] = (uint64_t)(uintptr_t)base;
+    a.grp_rowb[g] = (uint32_t)(N * elem);
+    a.grp_rows[g] = (uint16_t)rows;
+    a.grp_dst16[g] = (uint16_t)(dst / 16);
+    a.grp_len16[g] = (uint16_t)(len / 16);
+    ++g;
+  };
   auto add = [&](const void* base, size_t row, int elem, int dst, int kind) {
     if (k >= kMaxBulk) return;
     const uintptr_t ptr = (uintptr_t)((const char*)base + row * N * elem);
@@ -140,8 +215,32 @@ inline int build_post2(Post2Args& a) {
     ++k;
   };
   add(a.sim.dof_state, 0, 4, LY::OFF_DOF, BK_DOF);
+  grp(a.sim.dof_state, 1, 4, LY::OFF_DOF, BK_DOF);
   a.n_bulk_early = k;
-  if (!BG && a.want_tgt) add(st.full_dof_targets, 0, 4, LY::OFF_TGT, BK_TGT);
+  a.n_grp_early = g;
+  if (!BG && a.want_tgt) {
+    add(st.full_dof_targets, 0, 4, LY::OFF_TGT, BK_TGT);
+    grp(st.full_dof_targets, 1, 4, LY::OFF_TGT, BK_TGT);
+  }
+  grp(st.prev_dof_pos, DEX_NUM_DOF, 4, LY::R_PDP * 128, BK_F32);
+  grp(st.active_prev_targets, DEX_NUM_ACTIVE, 4, LY::R_APT * 128, BK_F32);
+  grp(st.prev_actions, P.num_actions, 4, LY::R_PACT * 128, BK_F32);
+  grp(st.contact_duration_steps, DEX_NUM_FINGERS, 4, LY::R_CDUR * 128, BK_F32);
+  grp(st.prev_contact_binary, DEX_NUM_FINGERS, 4, LY::R_PBIN * 128, BK_F32);
+  grp(st.episode_step_count, 1, 8, LY::OFF_I64 + LY::I_STEP * 256, BK_I64);
+  if (BG) {
+    grp(st.initial_box_positions, 3, 4, LY::R_BOX0 * 128, BK_F32);
+    grp(st.time_in_stage, 1, 4, LY::R_TIS * 128, BK_F32);
+    grp(st.stage_contact_duration, 1, 4, LY::R_SCD * 128, BK_F32);
+    grp(st.success_duration_steps, 1, 8, LY::OFF_I64 + LY::I_SDS * 256, BK_I64);
+    grp(st.current_stage, 1, 8, LY::OFF_I64 + LY::I_STAGE * 256, BK_I64);
+  } else if (a.common && !a.first) {
+    grp(st.prev_finger_dof_vel, DEX_NUM_FINGER_DOF, 4, LY::R_PFDV * 128, BK_F32);
+    grp(st.prev_hand_vel, 3, 4, LY::R_PHV * 128, BK_F32);
+    grp(st.prev_hand_ang_vel, 3, 4, LY::R_PHA * 128, BK_F32);
+    grp(st.prev_contacts, DEX_NUM_FINGERS, 1, LY::OFF_U8, BK_U8);
+  }
+  a.n_grp = g;
   for (int d = 0; d < DEX_NUM_DOF; ++d) add(st.prev_dof_pos, d, 4, (LY::R_PDP + d) * 128, BK_F32);
   for (int i = 0; i < DEX_NUM_ACTIVE; ++i) add(st.active_prev_targets, i, 4, (LY::R_APT + i) * 128, BK_F32);
   for (int i = 0; i < P.num_actions; ++i) add(st.prev_actions, i, 4, (LY::R_PACT + i) * 128, BK_F32);
@@ -160,12 +259,31 @@ inline int build_post2(Post2Args& a) {
     for (int c = 0; c < 3; ++c) add(st.prev_hand_ang_vel, c, 4, (LY::R_PHA + c) * 128, BK_F32);
     for (int f = 0; f < DEX_NUM_FINGERS; ++f) add(st.prev_contacts, f, 1, LY::OFF_U8 + f * 32, BK_U8);
   }
-  if (k >= kMaxBulk) return DEX_ERR_SIZE;
+  if (k >= kMaxBulk || g >= 16) return DEX_ERR_SIZE;
   a.n_bulk = k;
   a.tx_bytes = tx;
   a.bulk_ok = aligned ? 1 : 0;
   a.smem_bytes = 0;  // set by the launcher: nc x (stage + obs tile)
   return DEX_OK;
+}
+
+
+// does the launch match the compile-time layout of the STD kernel instance?
+template <bool BG>
+inline bool std_layout_matches(const Post2Args& a) {
+  const DexParams& P = a.p;
+  if (P.obs_dim != kStdObsDim[BG ? 1 : 0] || P.num_actions != DEX_NUM_ACTIVE) return false;
+  for (int k = 0; k < DEX_NUM_OBS_KEYS; ++k)
+    if (P.obs_offset[k] != std_obs_off<BG>(k)) return false;
+  for (int d = 0; d < DEX_NUM_DOF; ++d)
+    if (a.dof2afj[d] != std_dof2afj(d)) return false;
+  for (int i = 0; i < DEX_NUM_REWARD_TERMS; ++i) {  // every term of the task is materialised, no other one
+    const bool want = BG ? i >= DEX_NUM_COMMON_TERMS : i < DEX_NUM_COMMON_TERMS;
+    if ((P.reward_weight[i] != 0.0f) != want) return false;
+  }
+  if (a.st.contact_forces == nullptr || a.first) return false;
+  if (!BG && (!a.common || !a.want_tgt)) return false;
+  return true;
 }
 
 #ifdef DEXSTEP_TL2  // debug build only (tools/timeline_v2.py): SM-clock marks per (CTA, tile iteration), [cta][kTlIters][32] u64:
@@ -293,13 +411,23 @@ __device__ __forceinline__ void prod_rows_ldg(const Post2Args& A, unsigned char*
 // intermediates stay in registers, and the compiler schedules the independent chains (5 fingers, 26 DOFs, 10 pad
 // pairs, 16 reward terms) of one env side by side.
 // ------------------------------------------------------------------------------------------------
-template <bool BG>
+template <bool BG, bool STD>
 struct Cx {
   const unsigned char* stage;
   float* obs;  // obs tile row of this lane's env
+  const int32_t* obs_offset;  // generic instance: DexParams.obs_offset
+  const int32_t* dof2afj;
   int lane, e0, ne;
   bool act;
   size_t N, env;
+  __device__ __forceinline__ int off(const int k) const {
+    if constexpr (STD) return std_obs_off<BG>(k);
+    else return obs_offset[k];
+  }
+  __device__ __forceinline__ int afj(const int d) const {
+    if constexpr (STD) return std_dof2afj(d);
+    else return dof2afj[d];
+  }
   __device__ __forceinline__ const float* soa() const { return reinterpret_cast<const float*>(stage) + lane; }
   __device__ __forceinline__ const float* aos() const {
     return reinterpret_cast<const float*>(stage + Lay<BG>::OFF_AOS) + lane * Lay<BG>::SA;
@@ -322,8 +450,8 @@ struct Mid {
 
 // ---- the five tip (or pad) poses: world columns, hand-frame columns (observation_encoder.py:915-986) and, for
 //      BlindGrasping, the box distances (blind_grasping_task.py:684-771, 1178-1192, 1334-1364)
-template <bool BG, bool PAD>
-__device__ __forceinline__ void part_poses(const Post2Args& A, const Cx<BG>& c, Mid& m) {
+template <bool BG, bool STD, bool PAD>
+__device__ __forceinline__ void part_poses(const Post2Args& A, const Cx<BG, STD>& c, Mid& m) {
   using LY = Lay<BG>;
   const DexParams& P = A.p;
   const float* aos = c.aos();
@@ -334,14 +462,14 @@ __device__ __forceinline__ void part_poses(const Post2Args& A, const Cx<BG>& c, 
   for (int f = 0; f < DEX_NUM_FINGERS; ++f)
 #pragma unroll
     for (int j = 0; j < 7; ++j) p[f][j] = rb[13 + (PAD ? 35 : 0) + 7 * f + j];
-  const int ow = P.obs_offset[PAD ? DEX_K_FINGERPAD_POSES_WORLD : DEX_K_FINGERTIP_POSES_WORLD];
+  const int ow = c.off(PAD ? DEX_K_FINGERPAD_POSES_WORLD : DEX_K_FINGERTIP_POSES_WORLD);
   if (ow >= 0) {
 #pragma unroll
     for (int f = 0; f < DEX_NUM_FINGERS; ++f)
 #pragma unroll
       for (int j = 0; j < 7; ++j) obs[ow + 7 * f + j] = p[f][j];
   }
-  const int oh = P.obs_offset[PAD ? DEX_K_FINGERPAD_POSES_HAND : DEX_K_FINGERTIP_POSES_HAND];
+  const int oh = c.off(PAD ? DEX_K_FINGERPAD_POSES_HAND : DEX_K_FINGERTIP_POSES_HAND);
   if (oh >= 0) {
     const Quat hq{rb[3], rb[4], rb[5], rb[6]};
     const float hx = rb[0], hy = rb[1], hz = rb[2];
@@ -379,7 +507,7 @@ __device__ __forceinline__ void part_poses(const Post2Args& A, const Cx<BG>& c, 
       for (int f = 1; f < DEX_NUM_FINGERS; ++f) mb = fminf(mb, d[f]);
       m.min_tip_box = mb;
     } else {
-      const int od = P.obs_offset[DEX_K_FINGER_TO_OBJECT_DISTANCES], ohd = P.obs_offset[DEX_K_FINGER_TO_OBJECT_HEIGHT_DIFF];
+      const int od = c.off(DEX_K_FINGER_TO_OBJECT_DISTANCES), ohd = c.off(DEX_K_FINGER_TO_OBJECT_HEIGHT_DIFF);
       float hd[DEX_NUM_FINGERS], dsum = 0.0f, hsum = 0.0f;
 #pragma unroll
       for (int f = 0; f < DEX_NUM_FINGERS; ++f) {
@@ -391,20 +519,20 @@ __device__ __forceinline__ void part_poses(const Post2Args& A, const Cx<BG>& c, 
         hsum += hd[f];
       }
       m.avg_hdiff = div_rn(hsum, 5.0f);  // blind_grasping_task.py:702-724
-      obs_put(obs, P.obs_offset[DEX_K_AVG_FINGER_TO_OBJECT_DISTANCE], 0, div_rn(dsum, 5.0f));
-      obs_put(obs, P.obs_offset[DEX_K_AVG_FINGER_TO_OBJECT_HEIGHT_DIFF], 0, m.avg_hdiff);
+      obs_put(obs, c.off(DEX_K_AVG_FINGER_TO_OBJECT_DISTANCE), 0, div_rn(dsum, 5.0f));
+      obs_put(obs, c.off(DEX_K_AVG_FINGER_TO_OBJECT_HEIGHT_DIFF), 0, m.avg_hdiff);
       // pad centroid + the height / centroid part of _evaluate_pregrasp_quality (:746-771, :1334-1364)
       float cen[3];
 #pragma unroll
       for (int k = 0; k < 3; ++k) cen[k] = (p[0][k] + p[1][k] + p[2][k]) / 3.0f;
-      const int oc = P.obs_offset[DEX_K_FIRST_THREE_FINGERPAD_CENTROID];
+      const int oc = c.off(DEX_K_FIRST_THREE_FINGERPAD_CENTROID);
 #pragma unroll
       for (int k = 0; k < 3; ++k) obs_put(obs, oc, k, cen[k]);
       m.cdist = norm3(cen[0] - bx, cen[1] - by, cen[2] - bz);
       const bool h_ok = (hd[0] <= P.height_tolerance) && (hd[1] <= P.height_tolerance) && (hd[2] <= P.height_tolerance);
       m.hcok = h_ok && (m.cdist <= P.centroid_tolerance);
       // the ten pad pair distances, triu order (:726-771)
-      const int op = P.obs_offset[DEX_K_FINGERPAD_DISTANCES];
+      const int op = c.off(DEX_K_FINGERPAD_DISTANCES);
       if (op >= 0) {
         int k = 0;
 #pragma unroll
@@ -419,8 +547,8 @@ __device__ __forceinline__ void part_poses(const Post2Args& A, const Cx<BG>& c, 
 
 // ---- the five contact sensors (observation_encoder.py:658-735, 323-361; reward_calculator.py:183-199) and, for
 //      BlindGrasping, the box contact flag and the box stability inputs
-template <bool BG>
-__device__ __forceinline__ void part_contacts(const Post2Args& A, const Cx<BG>& c, Mid& m) {
+template <bool BG, bool STD>
+__device__ __forceinline__ void part_contacts(const Post2Args& A, const Cx<BG, STD>& c, Mid& m) {
   using LY = Lay<BG>;
   const DexParams& P = A.p;
   const DexStateBuffers& st = A.st;
@@ -437,9 +565,9 @@ __device__ __forceinline__ void part_contacts(const Post2Args& A, const Cx<BG>& 
     dur[f] = soa[(LY::R_CDUR + f) * 32];
     prevb[f] = soa[(LY::R_PBIN + f) * 32];
   }
-  const int ocf = P.obs_offset[DEX_K_CONTACT_FORCES], om = P.obs_offset[DEX_K_CONTACT_FORCE_MAGNITUDE];
-  const int ob = P.obs_offset[DEX_K_CONTACT_BINARY], od = P.obs_offset[DEX_K_CONTACT_DURATION];
-  const bool common = !BG && A.common != 0, first = A.first != 0;
+  const int ocf = c.off(DEX_K_CONTACT_FORCES), om = c.off(DEX_K_CONTACT_FORCE_MAGNITUDE);
+  const int ob = c.off(DEX_K_CONTACT_BINARY), od = c.off(DEX_K_CONTACT_DURATION);
+  const bool common = !BG && (STD || A.common != 0), first = !STD && A.first != 0;
   float chg = 0.0f;
 #pragma unroll
   for (int f = 0; f < DEX_NUM_FINGERS; ++f) {
@@ -449,7 +577,7 @@ __device__ __forceinline__ void part_contacts(const Post2Args& A, const Cx<BG>& 
     const float fb = bin ? 1.0f : 0.0f;
     st.contact_duration_steps[f * N + env] = ndur;
     st.prev_contact_binary[f * N + env] = fb;
-    if (st.contact_forces != nullptr) {
+    if (STD || st.contact_forces != nullptr) {
 #pragma unroll
       for (int k = 0; k < 3; ++k) st.contact_forces[(3 * f + k) * N + env] = cf[f][k];
     }
@@ -477,7 +605,7 @@ __device__ __forceinline__ void part_contacts(const Post2Args& A, const Cx<BG>& 
     m.drift = norm3(b[0] - soa[(LY::R_BOX0 + 0) * 32], b[1] - soa[(LY::R_BOX0 + 1) * 32], b[2] - soa[(LY::R_BOX0 + 2) * 32]);
     m.vmag = norm3(b[3], b[4], b[5]);
     m.sok = (m.drift <= P.position_drift_tolerance) && (m.vmag <= P.velocity_tolerance);
-    const int opos = P.obs_offset[DEX_K_OBJECT_POS], ovel = P.obs_offset[DEX_K_OBJECT_VEL];
+    const int opos = c.off(DEX_K_OBJECT_POS), ovel = c.off(DEX_K_OBJECT_VEL);
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
       obs_put(obs, opos, k, b[k]);
@@ -488,8 +616,8 @@ __device__ __forceinline__ void part_contacts(const Post2Args& A, const Cx<BG>& 
 
 // ---- hand pose, ARR-aligned pose (observation_encoder.py:1483-1521), hand -> box distance, hand velocity reward
 //      terms (reward_calculator.py:100-181), episode time (dexhand_base.py:703-712: PRE-increment count)
-template <bool BG>
-__device__ __forceinline__ void part_hand(const Post2Args& A, const Cx<BG>& c, Mid& m) {
+template <bool BG, bool STD>
+__device__ __forceinline__ void part_hand(const Post2Args& A, const Cx<BG, STD>& c, Mid& m) {
   using LY = Lay<BG>;
   const DexParams& P = A.p;
   const DexStateBuffers& st = A.st;
@@ -500,13 +628,13 @@ __device__ __forceinline__ void part_hand(const Post2Args& A, const Cx<BG>& c, M
   float h[7];
 #pragma unroll
   for (int j = 0; j < 7; ++j) h[j] = rb[j];
-  obs_put(obs, P.obs_offset[DEX_K_EPISODE_TIME], 0, (float)c.i64lo(LY::I_STEP) * P.control_dt);
-  const int oh = P.obs_offset[DEX_K_HAND_POSE];
+  obs_put(obs, c.off(DEX_K_EPISODE_TIME), 0, (float)c.i64lo(LY::I_STEP) * P.control_dt);
+  const int oh = c.off(DEX_K_HAND_POSE);
   if (oh >= 0) {
 #pragma unroll
     for (int j = 0; j < 7; ++j) obs[oh + j] = h[j];
   }
-  const int oa = P.obs_offset[DEX_K_HAND_POSE_ARR_ALIGNED];
+  const int oa = c.off(DEX_K_HAND_POSE_ARR_ALIGNED);
   if (oa >= 0) {
     const float sh = 0.7071067811865476f;
     const Quat qa = quat_mul(Quat{h[3], h[4], h[5], h[6]}, Quat{-0.0f, -sh, -0.0f, sh});
@@ -522,10 +650,10 @@ __device__ __forceinline__ void part_hand(const Post2Args& A, const Cx<BG>& c, M
     const float* box = aos + LY::A_BOX;
     const float hb = norm3(h[0] - box[0], h[1] - box[1], h[2] - box[2]);
     m.boxfar = hb > P.max_box_distance;
-    obs_put(obs, P.obs_offset[DEX_K_HAND_TO_OBJECT_DISTANCE], 0, hb);
+    obs_put(obs, c.off(DEX_K_HAND_TO_OBJECT_DISTANCE), 0, hb);
   }
-  if (!BG && A.common) {
-    const bool first = A.first != 0;
+  if (!BG && (STD || A.common)) {
+    const bool first = !STD && A.first != 0;
     float hv[3], ha[3], phv[3], pha[3];
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
@@ -545,8 +673,8 @@ __device__ __forceinline__ void part_hand(const Post2Args& A, const Cx<BG>& c, M
 
 // ---- the 26 DOFs: finite-difference velocity (observation_encoder.py:298-321), obs columns, common-reward partial
 //      sums (reward_calculator.py:94-98,138-160: Isaac dof_vel, not the finite difference; summed in DOF order)
-template <bool BG>
-__device__ __forceinline__ void part_dofs(const Post2Args& A, const Cx<BG>& c, Mid& m) {
+template <bool BG, bool STD>
+__device__ __forceinline__ void part_dofs(const Post2Args& A, const Cx<BG, STD>& c, Mid& m) {
   using LY = Lay<BG>;
   const DexParams& P = A.p;
   const DexStateBuffers& st = A.st;
@@ -555,13 +683,13 @@ __device__ __forceinline__ void part_dofs(const Post2Args& A, const Cx<BG>& c, M
   const size_t N = c.N, env = c.env;
   const float dt = P.control_dt;
   const float4* d4 = reinterpret_cast<const float4*>(c.stage + LY::OFF_DOF) + c.lane * 13;
-  const bool want_tgt = !BG && A.want_tgt != 0;
-  const bool common = !BG && A.common != 0, first = A.first != 0;
-  const int o_bp = P.obs_offset[DEX_K_BASE_DOF_POS], o_bv = P.obs_offset[DEX_K_BASE_DOF_VEL], o_bt = P.obs_offset[DEX_K_BASE_DOF_TARGET];
-  const int o_ap = P.obs_offset[DEX_K_ALL_FINGER_DOF_POS], o_av = P.obs_offset[DEX_K_ALL_FINGER_DOF_VEL],
-            o_at = P.obs_offset[DEX_K_ALL_FINGER_DOF_TARGET];
-  const int o_fp = P.obs_offset[DEX_K_ACTIVE_FINGER_DOF_POS], o_fv = P.obs_offset[DEX_K_ACTIVE_FINGER_DOF_VEL],
-            o_ft = P.obs_offset[DEX_K_ACTIVE_FINGER_DOF_TARGET];
+  const bool want_tgt = !BG && (STD || A.want_tgt != 0);
+  const bool common = !BG && (STD || A.common != 0), first = !STD && A.first != 0;
+  const int o_bp = c.off(DEX_K_BASE_DOF_POS), o_bv = c.off(DEX_K_BASE_DOF_VEL), o_bt = c.off(DEX_K_BASE_DOF_TARGET);
+  const int o_ap = c.off(DEX_K_ALL_FINGER_DOF_POS), o_av = c.off(DEX_K_ALL_FINGER_DOF_VEL),
+            o_at = c.off(DEX_K_ALL_FINGER_DOF_TARGET);
+  const int o_fp = c.off(DEX_K_ACTIVE_FINGER_DOF_POS), o_fv = c.off(DEX_K_ACTIVE_FINGER_DOF_VEL),
+            o_ft = c.off(DEX_K_ACTIVE_FINGER_DOF_TARGET);
   float fv2 = 0.0f, fa2 = 0.0f, jl = 0.0f;
 #pragma unroll
   for (int q = 0; q < DEX_NUM_DOF / 2; ++q) {
@@ -584,7 +712,7 @@ __device__ __forceinline__ void part_dofs(const Post2Args& A, const Cx<BG>& c, M
         obs_put(obs, o_ap, j, pos);
         obs_put(obs, o_av, j, fd);
         if (!BG) obs_put(obs, o_at, j, tgt);
-        const int aj = A.dof2afj[d];
+        const int aj = c.afj(d);
         if (aj >= 0) {
           obs_put(obs, o_fp, aj, pos);
           obs_put(obs, o_fv, aj, fd);
@@ -610,8 +738,8 @@ __device__ __forceinline__ void part_dofs(const Post2Args& A, const Cx<BG>& c, M
 
 // ---- prev_actions columns (observation_encoder.py:287-296); active_rule_targets <- active_prev_targets
 //      (rules.py:78-95, step_processor.py:73)
-template <bool BG>
-__device__ __forceinline__ void part_copies(const Post2Args& A, const Cx<BG>& c) {
+template <bool BG, bool STD>
+__device__ __forceinline__ void part_copies(const Post2Args& A, const Cx<BG, STD>& c) {
   using LY = Lay<BG>;
   const DexParams& P = A.p;
   const float* soa = c.soa();
@@ -619,7 +747,7 @@ __device__ __forceinline__ void part_copies(const Post2Args& A, const Cx<BG>& c)
   float apt[DEX_NUM_ACTIVE];
 #pragma unroll
   for (int k = 0; k < DEX_NUM_ACTIVE; ++k) apt[k] = soa[(LY::R_APT + k) * 32];
-  const int op = P.obs_offset[DEX_K_PREV_ACTIONS];
+  const int op = c.off(DEX_K_PREV_ACTIONS);
   if (op >= 0) {
 #pragma unroll
     for (int k0 = 0; k0 < DEX_NUM_ACTIVE; k0 += 6) {  // num_actions is 6, 12 or 18
@@ -632,7 +760,7 @@ __device__ __forceinline__ void part_copies(const Post2Args& A, const Cx<BG>& c)
       }
     }
   }
-  const int o1 = P.obs_offset[DEX_K_ACTIVE_PREV_TARGETS], o2 = P.obs_offset[DEX_K_ACTIVE_RULE_TARGETS];
+  const int o1 = c.off(DEX_K_ACTIVE_PREV_TARGETS), o2 = c.off(DEX_K_ACTIVE_RULE_TARGETS);
   float* art = A.st.active_rule_targets + c.env;
 #pragma unroll
   for (int k = 0; k < DEX_NUM_ACTIVE; ++k) {
@@ -644,7 +772,8 @@ __device__ __forceinline__ void part_copies(const Post2Args& A, const Cx<BG>& c)
 
 // ---- BlindGrasping: finger-box contacts (blind_grasping_task.py:773-833), success duration (:626-648), stage FSM
 //      (:835-978; plain fp32 accumulation of (float)control_dt decides the transition step)
-__device__ __forceinline__ void part_task_state(const Post2Args& A, const Cx<true>& c, Mid& m) {
+template <bool STD>
+__device__ __forceinline__ void part_task_state(const Post2Args& A, const Cx<true, STD>& c, Mid& m) {
   using LY = Lay<true>;
   const DexParams& P = A.p;
   const DexStateBuffers& st = A.st;
@@ -667,15 +796,15 @@ __device__ __forceinline__ void part_task_state(const Post2Args& A, const Cx<tru
   m.thumb = fbc[0];
   m.others = fbc[1] || fbc[2] || fbc[3] || fbc[4];
   m.grasp = m.thumb && m.others;
-  obs_put(obs, P.obs_offset[DEX_K_THUMB_CONTACT], 0, m.thumb ? 1.0f : 0.0f);
-  obs_put(obs, P.obs_offset[DEX_K_OTHER_FINGERS_CONTACT], 0, m.others ? 1.0f : 0.0f);
-  obs_put(obs, P.obs_offset[DEX_K_GRASP_STATE], 0, m.grasp ? 1.0f : 0.0f);
+  obs_put(obs, c.off(DEX_K_THUMB_CONTACT), 0, m.thumb ? 1.0f : 0.0f);
+  obs_put(obs, c.off(DEX_K_OTHER_FINGERS_CONTACT), 0, m.others ? 1.0f : 0.0f);
+  obs_put(obs, c.off(DEX_K_GRASP_STATE), 0, m.grasp ? 1.0f : 0.0f);
   const bool cond = (box_z > P.success_height_threshold) && (n_on_box >= P.min_fingers_for_grasp);
   m.sds = cond ? sds_old + 1 : 0;
   st.success_duration_steps[env] = (long long)m.sds;
   st.success_conditions_met[env] = cond ? 1 : 0;
   m.graspdur = (float)m.sds * dt;
-  obs_put(obs, P.obs_offset[DEX_K_GRASP_DURATION], 0, m.graspdur);
+  obs_put(obs, c.off(DEX_K_GRASP_DURATION), 0, m.graspdur);
   // FSM
   const bool thumb_other = (m.bin[0] != 0.0f) && ((m.bin[1] != 0.0f) || (m.bin[2] != 0.0f) || (m.bin[3] != 0.0f) || (m.bin[4] != 0.0f));
   if (stage == 2) scd = thumb_other ? scd + dt : 0.0f;
@@ -699,16 +828,16 @@ __device__ __forceinline__ void part_task_state(const Post2Args& A, const Cx<tru
   m.stage = stage;
   m.j2 = s1_done;
   m.j3 = s2_done;
-  obs_put(obs, P.obs_offset[DEX_K_CURRENT_STAGE], 0, (float)stage);
-  obs_put(obs, P.obs_offset[DEX_K_TIME_IN_STAGE], 0, tis);
-  obs_put(obs, P.obs_offset[DEX_K_STAGE_PROGRESS], 0, prog);
+  obs_put(obs, c.off(DEX_K_CURRENT_STAGE), 0, (float)stage);
+  obs_put(obs, c.off(DEX_K_TIME_IN_STAGE), 0, tis);
+  obs_put(obs, c.off(DEX_K_STAGE_PROGRESS), 0, prog);
 }
 
 // raw + weighted rows of term i leave from registers; the weighted value is kept for the ordered total
-template <bool BG>
-__device__ __forceinline__ void emit_term(const Post2Args& A, const Cx<BG>& c, Mid& m, const int i, const float r) {
+template <bool BG, bool STD>
+__device__ __forceinline__ void emit_term(const Post2Args& A, const Cx<BG, STD>& c, Mid& m, const int i, const float r) {
   const float w = A.p.reward_weight[i];
-  if (w == 0.0f) return;  // reward_calculator.py:247-251: zero-weight terms are not materialised
+  if (!STD && w == 0.0f) return;  // reward_calculator.py:247-251: zero-weight terms are not materialised (STD: none is)
   const int row = A.p.component_row[i];
   const float rw = r * w;
   float* g = A.out.reward_components + c.env;
@@ -718,65 +847,67 @@ __device__ __forceinline__ void emit_term(const Post2Args& A, const Cx<BG>& c, M
 }
 
 // ---- common reward terms (reward_calculator.py:66-221); BaseTask
-__device__ __forceinline__ void part_common_terms(const Post2Args& A, const Cx<false>& c, Mid& m) {
-  emit_term<false>(A, c, m, DEX_R_ALIVE, 1.0f);
-  emit_term<false>(A, c, m, DEX_R_HEIGHT_SAFETY, clampf(1.0f - expf(-(m.min_tip_z - 0.02f) * 20.0f), 0.0f, 1.0f));
-  emit_term<false>(A, c, m, DEX_R_FINGER_VELOCITY, expf(-0.1f * sqrtf(m.fv2)));
-  emit_term<false>(A, c, m, DEX_R_HAND_VELOCITY, m.rhand[0]);
-  emit_term<false>(A, c, m, DEX_R_HAND_ANGULAR_VELOCITY, m.rhand[1]);
-  emit_term<false>(A, c, m, DEX_R_JOINT_LIMIT, 1.0f - div_rn(m.jl, 20.0f));
-  emit_term<false>(A, c, m, DEX_R_FINGER_ACCELERATION, expf(-2.0f * sqrtf(m.fa2)));
-  emit_term<false>(A, c, m, DEX_R_HAND_ACCELERATION, m.rhand[2]);
-  emit_term<false>(A, c, m, DEX_R_HAND_ANGULAR_ACCELERATION, m.rhand[3]);
-  emit_term<false>(A, c, m, DEX_R_CONTACT_STABILITY, expf(-m.chg));
+template <bool STD>
+__device__ __forceinline__ void part_common_terms(const Post2Args& A, const Cx<false, STD>& c, Mid& m) {
+  emit_term<false, STD>(A, c, m, DEX_R_ALIVE, 1.0f);
+  emit_term<false, STD>(A, c, m, DEX_R_HEIGHT_SAFETY, clampf(1.0f - expf(-(m.min_tip_z - 0.02f) * 20.0f), 0.0f, 1.0f));
+  emit_term<false, STD>(A, c, m, DEX_R_FINGER_VELOCITY, expf(-0.1f * sqrtf(m.fv2)));
+  emit_term<false, STD>(A, c, m, DEX_R_HAND_VELOCITY, m.rhand[0]);
+  emit_term<false, STD>(A, c, m, DEX_R_HAND_ANGULAR_VELOCITY, m.rhand[1]);
+  emit_term<false, STD>(A, c, m, DEX_R_JOINT_LIMIT, 1.0f - div_rn(m.jl, 20.0f));
+  emit_term<false, STD>(A, c, m, DEX_R_FINGER_ACCELERATION, expf(-2.0f * sqrtf(m.fa2)));
+  emit_term<false, STD>(A, c, m, DEX_R_HAND_ACCELERATION, m.rhand[2]);
+  emit_term<false, STD>(A, c, m, DEX_R_HAND_ANGULAR_ACCELERATION, m.rhand[3]);
+  emit_term<false, STD>(A, c, m, DEX_R_CONTACT_STABILITY, expf(-m.chg));
 }
 
 // ---- BlindGrasping task terms (blind_grasping_task.py:980-1208), after the FSM
-__device__ __forceinline__ void part_task_terms(const Post2Args& A, const Cx<true>& c, Mid& m) {
+template <bool STD>
+__device__ __forceinline__ void part_task_terms(const Post2Args& A, const Cx<true, STD>& c, Mid& m) {
   using LY = Lay<true>;
   const DexParams& P = A.p;
   const float* aos = c.aos();
   const float* rb = aos + LY::A_RB;
   const float m1 = (m.stage == 1) ? 1.0f : 0.0f, m2 = (m.stage == 2) ? 1.0f : 0.0f, m3 = (m.stage == 3) ? 1.0f : 0.0f;
   const float fg = m.grasp ? 1.0f : 0.0f;
-  emit_term<true>(A, c, m, DEX_R_S1_HEIGHT_ALIGNMENT, expf(-P.height_alignment_decay * m.avg_hdiff) * m1);
-  emit_term<true>(A, c, m, DEX_R_S1_CENTROID_POSITIONING, expf(-P.centroid_positioning_decay * m.cdist) * m1);
-  emit_term<true>(A, c, m, DEX_R_S1_OBJECT_STABILITY, expf(-P.object_stability_decay * (m.drift + m.vmag)) * m1);
+  emit_term<true, STD>(A, c, m, DEX_R_S1_HEIGHT_ALIGNMENT, expf(-P.height_alignment_decay * m.avg_hdiff) * m1);
+  emit_term<true, STD>(A, c, m, DEX_R_S1_CENTROID_POSITIONING, expf(-P.centroid_positioning_decay * m.cdist) * m1);
+  emit_term<true, STD>(A, c, m, DEX_R_S1_OBJECT_STABILITY, expf(-P.object_stability_decay * (m.drift + m.vmag)) * m1);
   {  // torch.var(dim=1), unbiased, z of the first three pads
     const float z0 = rb[13 + 35 + 2], z1 = rb[13 + 35 + 7 + 2], z2 = rb[13 + 35 + 14 + 2];
     const float mean = (z0 + z1 + z2) / 3.0f;
     const float d0 = z0 - mean, d1 = z1 - mean, d2 = z2 - mean;
     const float var = (d0 * d0 + d1 * d1 + d2 * d2) / 2.0f;
-    emit_term<true>(A, c, m, DEX_R_S1_FINGER_HEIGHT_CONSISTENCY, expf(-P.height_consistency_decay * var) * m1);
+    emit_term<true, STD>(A, c, m, DEX_R_S1_FINGER_HEIGHT_CONSISTENCY, expf(-P.height_consistency_decay * var) * m1);
   }
   {
     const float th = reinterpret_cast<const float*>(c.stage + LY::OFF_DOF)[c.lane * 52 + 2 * DEX_NUM_BASE];
-    emit_term<true>(A, c, m, DEX_R_S1_THUMB_ROTATION, expf(-5.0f * fabsf(th - P.half_pi)) * m1);
+    emit_term<true, STD>(A, c, m, DEX_R_S1_THUMB_ROTATION, expf(-5.0f * fabsf(th - P.half_pi)) * m1);
   }
-  emit_term<true>(A, c, m, DEX_R_S2_THUMB_CONTACT, (m.thumb ? 1.0f : 0.0f) * m2);
-  emit_term<true>(A, c, m, DEX_R_S2_OTHER_FINGERS_CONTACT, (m.others ? 1.0f : 0.0f) * m2);
-  emit_term<true>(A, c, m, DEX_R_S2_GRASP_ACHIEVEMENT, fg * m2);
-  emit_term<true>(A, c, m, DEX_R_S2_FINGERPAD_PROXIMITY,
+  emit_term<true, STD>(A, c, m, DEX_R_S2_THUMB_CONTACT, (m.thumb ? 1.0f : 0.0f) * m2);
+  emit_term<true, STD>(A, c, m, DEX_R_S2_OTHER_FINGERS_CONTACT, (m.others ? 1.0f : 0.0f) * m2);
+  emit_term<true, STD>(A, c, m, DEX_R_S2_GRASP_ACHIEVEMENT, fg * m2);
+  emit_term<true, STD>(A, c, m, DEX_R_S2_FINGERPAD_PROXIMITY,
                   expf(-P.fingerpad_proximity_decay * fmaxf(m.min_tip_box, P.min_reward_distance)) * m2);
   {
     float bv2 = 0.0f;
 #pragma unroll
     for (int d = 0; d < DEX_NUM_BASE; ++d) bv2 += m.bvel[d] * m.bvel[d];  // finite-difference base velocity
-    emit_term<true>(A, c, m, DEX_R_S2_BASE_STABILITY, expf(-P.base_stability_decay * sqrtf(bv2)) * m2);
+    emit_term<true, STD>(A, c, m, DEX_R_S2_BASE_STABILITY, expf(-P.base_stability_decay * sqrtf(bv2)) * m2);
   }
-  emit_term<true>(A, c, m, DEX_R_S3_OBJECT_HEIGHT, clampf(div_rn(aos[LY::A_BOX + 2] - P.box_z, P.lift_height_range), 0.0f, 1.0f) * m3);
-  emit_term<true>(A, c, m, DEX_R_S3_GRASP_MAINTENANCE, fg * m3);
-  emit_term<true>(A, c, m, DEX_R_S3_GRASP_DURATION, clampf(div_rn(m.graspdur, P.contact_duration_threshold_s), 0.0f, 1.0f) * m3);
+  emit_term<true, STD>(A, c, m, DEX_R_S3_OBJECT_HEIGHT, clampf(div_rn(aos[LY::A_BOX + 2] - P.box_z, P.lift_height_range), 0.0f, 1.0f) * m3);
+  emit_term<true, STD>(A, c, m, DEX_R_S3_GRASP_MAINTENANCE, fg * m3);
+  emit_term<true, STD>(A, c, m, DEX_R_S3_GRASP_DURATION, clampf(div_rn(m.graspdur, P.contact_duration_threshold_s), 0.0f, 1.0f) * m3);
   // completion bonuses :1025-1048 (transition and not failed), penetration :1194-1208
-  emit_term<true>(A, c, m, DEX_R_S1_COMPLETION, (m.j2 && m.hcok && m.sok) ? 1.0f : 0.0f);
-  emit_term<true>(A, c, m, DEX_R_S2_COMPLETION, (m.j3 && m.grasp) ? 1.0f : 0.0f);
-  emit_term<true>(A, c, m, DEX_R_PENETRATION_PENALTY, fmaxf(P.penetration_threshold - m.min_tip_box, 0.0f) * P.penetration_depth_scale);
+  emit_term<true, STD>(A, c, m, DEX_R_S1_COMPLETION, (m.j2 && m.hcok && m.sok) ? 1.0f : 0.0f);
+  emit_term<true, STD>(A, c, m, DEX_R_S2_COMPLETION, (m.j3 && m.grasp) ? 1.0f : 0.0f);
+  emit_term<true, STD>(A, c, m, DEX_R_PENETRATION_PENALTY, fmaxf(P.penetration_threshold - m.min_tip_box, 0.0f) * P.penetration_depth_scale);
 }
 
 // ---- termination (step_processor.py:133-181, termination_manager.py:120-278), masks, tile record.
 // Returns the exclusive termination class of this lane's env (bit 0 success, 1 failure, 2 timeout) and the reset ballot.
-template <bool BG>
-__device__ __forceinline__ unsigned part_terminate(const Post2Args& A, const Cx<BG>& c, const Mid& m, const unsigned stamp,
+template <bool BG, bool STD, bool FULL>
+__device__ __forceinline__ unsigned part_terminate(const Post2Args& A, const Cx<BG, STD>& c, const Mid& m, const unsigned stamp,
                                                    unsigned& rbits_out) {
   using LY = Lay<BG>;
   const DexParams& P = A.p;
@@ -868,14 +999,14 @@ __device__ __forceinline__ unsigned part_terminate(const Post2Args& A, const Cx<
 
 // ---- ordered weighted sum (reward_calculator.py:223-275) + termination rewards
 //      (termination_manager.py:280-321, step_processor.py:204-219)
-template <bool BG>
-__device__ __forceinline__ void part_total(const Post2Args& A, const Cx<BG>& c, const Mid& m, const unsigned cls) {
+template <bool BG, bool STD>
+__device__ __forceinline__ void part_total(const Post2Args& A, const Cx<BG, STD>& c, const Mid& m, const unsigned cls) {
   const DexParams& P = A.p;
   constexpr int I0 = BG ? DEX_NUM_COMMON_TERMS : 0, I1 = BG ? DEX_NUM_REWARD_TERMS : DEX_NUM_COMMON_TERMS;
   float total = 0.0f;
 #pragma unroll
   for (int i = I0; i < I1; ++i)
-    if (P.reward_weight[i] != 0.0f) total += m.wgt[i];  // dict order: common, then task
+    if (STD || P.reward_weight[i] != 0.0f) total += m.wgt[i];  // dict order: common, then task
   const bool t_success = cls & 1u, t_failure = cls & 2u, t_timeout = cls & 4u;
   const float rs = t_success ? P.success_reward : 0.0f;
   const float rf = t_failure ? P.failure_reward : 0.0f;
@@ -894,15 +1025,17 @@ __device__ __forceinline__ void part_total(const Post2Args& A, const Cx<BG>& c, 
 
 // obs tile -> obs_buf by the tile's own warp: lane = column, every global store is one full 128-byte request;
 // eight rows per batch keep eight loads in flight
+template <bool FULL>
 __device__ __forceinline__ void copy_obs(const float* s_obs, float* g_tile, const int W, const int WP, const int ne, const int lane) {
   const int nchunk = (W + 31) >> 5;
+#pragma unroll 1
   for (int ch = 0; ch < nchunk; ++ch) {
     const int col = 32 * ch + lane;
     if (col < W) {
       const float* sp = s_obs + col;
       float* gp = g_tile + col;
-      if (ne == 32) {
-#pragma unroll
+      if (FULL) {
+#pragma unroll 1
         for (int r0 = 0; r0 < 32; r0 += 8) {
           float v[8];
 #pragma unroll
@@ -917,10 +1050,35 @@ __device__ __forceinline__ void copy_obs(const float* s_obs, float* g_tile, cons
   }
 }
 
+// the whole per-env program of one tile, run by the tile's compute warp
+template <bool BG, bool STD, bool FULL>
+__device__ __forceinline__ unsigned tile_program(const Post2Args& A, Cx<BG, STD>& c, const unsigned stamp) {
+  Mid m;
+  unsigned rbits = 0;
+  if (FULL || c.act) {
+    part_poses<BG, STD, false>(A, c, m);
+    part_poses<BG, STD, true>(A, c, m);
+    part_contacts<BG, STD>(A, c, m);
+    part_hand<BG, STD>(A, c, m);
+    part_dofs<BG, STD>(A, c, m);
+    part_copies<BG, STD>(A, c);
+    if constexpr (BG) part_task_state<STD>(A, c, m);
+  }
+  const unsigned cls = part_terminate<BG, STD, FULL>(A, c, m, stamp, rbits);
+  if (FULL || c.act) {
+    if constexpr (BG)
+      part_task_terms<STD>(A, c, m);
+    else
+      part_common_terms<STD>(A, c, m);
+    part_total<BG, STD>(A, c, m, cls);
+  }
+  return rbits;
+}
+
 // ------------------------------------------------------------------------------------------------
 // the kernel: NC (compute warp, producer warp) pairs per CTA, one CTA per SM, persistent
 // ------------------------------------------------------------------------------------------------
-template <bool BG, int NC>
+template <bool BG, int NC, bool STD>
 __global__ void __launch_bounds__(64 * NC, 1) post_physics_v2_kernel(const __grid_constant__ Post2Args A) {
   using LY = Lay<BG>;
   constexpr int kThreads = 64 * NC;
@@ -1003,6 +1161,16 @@ __global__ void __launch_bounds__(64 * NC, 1) post_physics_v2_kernel(const __gri
     const size_t nb13 = (size_t)A.p.num_bodies * 13;
     const bool early = (A.flags & DEX_FLAG_EARLY_SIM_LOADS) != 0;
     const uint32_t sst = s32(stage);
+    const int n_grp = A.n_grp, n_grp_early = A.n_grp_early;
+    // bulk copies of the groups [g0, g1): lane r copies row r of each group (group tables are read warp-uniformly)
+    auto issue_groups = [&](const int g0, const int g1, const int tile) {
+      for (int g = g0; g < g1; ++g) {
+        const uint32_t len = (uint32_t)A.grp_len16[g] * 16u;
+        if (lane < (int)A.grp_rows[g])
+          bulk_g2s(sst + (uint32_t)A.grp_dst16[g] * 16u + (uint32_t)lane * len,
+                   reinterpret_cast<const char*>(A.grp_ptr[g]) + (size_t)lane * A.grp_rowb[g] + (size_t)tile * len, len, fb);
+      }
+    };
     int it = 0;
     for (int tile = tile0; tile < tiles; tile += tstep, ++it) {
       const int e0 = tile * 32, ne = min(32, A.n - e0);
@@ -1010,15 +1178,9 @@ __global__ void __launch_bounds__(64 * NC, 1) post_physics_v2_kernel(const __gri
       if (it > 0) mbar_wait(eb, (unsigned)(it - 1) & 1u);
       TL2(it, 17);
       const bool bulk = A.bulk_ok && ne == 32;  // warp-uniform
+      const bool split = it == 0 && early;      // first tile: the state rows wait for griddepcontrol.wait, the sim rows do not
       if (it == 0 && !early) pdl_wait();
-      // bulk entries: lane l issues entries l, l + 32, ..; the sim-tensor entries come first in the table
-      if (bulk) {
-        for (int k = lane; k < A.n_bulk; k += 32) {
-          if (it == 0 && early && k >= A.n_bulk_early) break;
-          const uint32_t len = (uint32_t)A.bk_len16[k] * 16u;
-          bulk_g2s(sst + (uint32_t)A.bk_dst16[k] * 16u, reinterpret_cast<const char*>(A.bk_ptr[k]) + (size_t)tile * len, len, fb);
-        }
-      }
+      if (bulk) issue_groups(0, split ? n_grp_early : n_grp, tile);
       // ---- scattered Isaac Gym rows, 16 env rows per batch: consecutive lanes = consecutive floats of a row ----
       float* aos = reinterpret_cast<float*>(stage + LY::OFF_AOS) + lane;
       const float* q0 = A.sim.rigid_body_state + (size_t)e0 * nb13;
@@ -1037,15 +1199,10 @@ __global__ void __launch_bounds__(64 * NC, 1) post_physics_v2_kernel(const __gri
           q0 += nb13;
           qx += xrow;
         }
-        if (half == 1 && it == 0 && early) {
+        if (half == 1 && split) {
           TL2(it, 18);
           pdl_wait();  // everything above touched only kernel parameters and the sim tensors
-          if (bulk) {
-            for (int k = A.n_bulk_early + lane; k < A.n_bulk; k += 32) {
-              const uint32_t len = (uint32_t)A.bk_len16[k] * 16u;
-              bulk_g2s(sst + (uint32_t)A.bk_dst16[k] * 16u, reinterpret_cast<const char*>(A.bk_ptr[k]) + (size_t)tile * len, len, fb);
-            }
-          }
+          if (bulk) issue_groups(n_grp_early, n_grp, tile);
         }
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
@@ -1072,11 +1229,13 @@ __global__ void __launch_bounds__(64 * NC, 1) post_physics_v2_kernel(const __gri
   }
 
   // =========================== compute warp of this pair ===========================
-  Cx<BG> c;
+  Cx<BG, STD> c;
   c.lane = lane;
   c.N = (size_t)A.n;
   c.obs = s_obs + lane * A.wp;
   c.stage = stage;
+  c.obs_offset = A.p.obs_offset;
+  c.dof2afj = A.dof2afj;
   unsigned stamp = 0;
   uint64_t rng_step = 0;
   const int W = A.p.obs_dim, WP = A.wp;
@@ -1097,32 +1256,21 @@ __global__ void __launch_bounds__(64 * NC, 1) post_physics_v2_kernel(const __gri
       rng_step = __shfl_sync(0xffffffffu, rs, 0);
       stamp = ((unsigned)rng_step + 1u) & 0xffffu;
     }
-    Mid m;
-    unsigned cls = 0, rbits = 0;
-    if (c.act) {
-      part_poses<BG, false>(A, c, m);
-      part_poses<BG, true>(A, c, m);
-      part_contacts<BG>(A, c, m);
-      part_hand<BG>(A, c, m);
-      part_dofs<BG>(A, c, m);
-      part_copies<BG>(A, c);
-      if constexpr (BG) part_task_state(A, c, m);
+    unsigned rbits;
+    float* const g_obs = A.out.obs_buf + (size_t)c.e0 * W;
+    if (c.ne == 32) {  // warp-uniform
+      rbits = tile_program<BG, STD, true>(A, c, stamp);
+      TL2(it, 4);
+      __syncwarp();  // the raw stage is not read after this point: hand it back to the producer
+      if (lane == 0) mbar_arrive(eb);
+      copy_obs<true>(s_obs, g_obs, W, WP, 32, lane);
+    } else {
+      rbits = tile_program<BG, false, false>(A, reinterpret_cast<Cx<BG, false>&>(c), stamp);
+      TL2(it, 4);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(eb);
+      copy_obs<false>(s_obs, g_obs, W, WP, c.ne, lane);
     }
-    TL2(it, 2);
-    cls = part_terminate<BG>(A, c, m, stamp, rbits);
-    TL2(it, 3);
-    if (c.act) {
-      if constexpr (BG)
-        part_task_terms(A, c, m);
-      else
-        part_common_terms(A, c, m);
-      part_total<BG>(A, c, m, cls);
-    }
-    TL2(it, 4);
-    // the raw stage is not read after this point: hand it back to the producer
-    __syncwarp();
-    if (lane == 0) mbar_arrive(eb);
-    copy_obs(s_obs, A.out.obs_buf + (size_t)c.e0 * W, W, WP, c.ne, lane);
     TL2(it, 5);
     // ---- fused reset of the finished envs (dexhand_base.py:743-756) ----
     if (rbits && !(A.flags & DEX_FLAG_NO_FUSED_RESET)) {
@@ -1138,6 +1286,28 @@ __global__ void __launch_bounds__(64 * NC, 1) post_physics_v2_kernel(const __gri
   }
 }
 
+template <bool BG, int NC, bool STD>
+int launch_post2_k(Post2Args& a, cudaStream_t s) {
+  static int num_sms = 0;
+  static size_t smem_cfg = 0;
+  if (a.smem_bytes > smem_cfg) {
+    const cudaError_t e =
+        cudaFuncSetAttribute(post_physics_v2_kernel<BG, NC, STD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a.smem_bytes);
+    if (e != cudaSuccess) return (int)e;
+    smem_cfg = a.smem_bytes;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
+  }
+  const int fused = a.fused_epilogue ? 1 : 0;
+  // one CTA per SM; every CTA of the launch (workers + epilogue) is resident at once; tiles spread over all of them
+  const int cap = num_sms - fused > 1 ? num_sms - fused : 1;
+  a.workers = a.tiles < cap ? a.tiles : cap;
+  const cudaError_t e = launch_step_kernel(post_physics_v2_kernel<BG, NC, STD>, a.workers + fused, 64 * NC, a.smem_bytes, s, a);
+  if (e != cudaSuccess) (void)cudaGetLastError();
+  return e == cudaSuccess ? DEX_OK : (int)e;
+}
+
 template <bool BG, int NC>
 int launch_post2_t(Post2Args& a, cudaStream_t s) {
   using LY = Lay<BG>;
@@ -1146,24 +1316,7 @@ int launch_post2_t(Post2Args& a, cudaStream_t s) {
   a.nc = NC;
   a.smem_bytes = (uint32_t)(NC * (LY::STAGE_BYTES + 32 * a.wp * 4));
   if (a.smem_bytes > 227 * 1024 - 2048) return DEX_ERR_SIZE;
-  static int num_sms = 0;
-  static size_t smem_cfg = 0;
-  if (a.smem_bytes > smem_cfg) {
-    const cudaError_t e = cudaFuncSetAttribute(post_physics_v2_kernel<BG, NC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a.smem_bytes);
-    if (e != cudaSuccess) return (int)e;
-    smem_cfg = a.smem_bytes;
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
-  }
-  const int fused = a.fused_epilogue ? 1 : 0;
-  // one CTA per SM; every CTA of the launch (workers + epilogue) is resident at once
-  const int cap = num_sms - fused > 1 ? num_sms - fused : 1;
-  const int want = (a.tiles + NC - 1) / NC;  // CTAs needed to give every tile its own slot
-  a.workers = want < cap ? want : cap;
-  const cudaError_t e = launch_step_kernel(post_physics_v2_kernel<BG, NC>, a.workers + fused, 64 * NC, a.smem_bytes, s, a);
-  if (e != cudaSuccess) (void)cudaGetLastError();
-  return e == cudaSuccess ? DEX_OK : (int)e;
+  return std_layout_matches<BG>(a) ? launch_post2_k<BG, NC, true>(a, s) : launch_post2_k<BG, NC, false>(a, s);
 }
 
 }  // namespace pp2
