@@ -361,8 +361,8 @@ int dex_post_physics(const DexParams* params, const DexSimViews* sim, const DexS
     b.seed = seed;
     b.step = step_index;
     ++g_v2_launches;
-    return params->task == DEX_TASK_BLIND_GRASPING ? pp2::launch_post2_t<true, 4>(b, (cudaStream_t)stream)
-                                                   : pp2::launch_post2_t<false, 3>(b, (cudaStream_t)stream);
+    return params->task == DEX_TASK_BLIND_GRASPING ? pp2::launch_post2_t<true>(b, (cudaStream_t)stream)
+                                                   : pp2::launch_post2_t<false>(b, (cudaStream_t)stream);
   }
   static thread_local PostArgs a;  // ~7 KB of launch arguments: keep it off the stack
   a.p = *params;

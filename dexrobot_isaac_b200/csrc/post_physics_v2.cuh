@@ -23,9 +23,11 @@
 namespace {
 namespace pp2 {
 
-constexpr int kMaxPairs = 4;   // (compute warp, producer warp) pairs per CTA; each pair owns one tile slot
-constexpr int kMaxBulk = 128;  // bulk entries of one tile (<= 4 per producer lane)
-constexpr int kEpiThreads = 256;
+constexpr int kConsWarps = 8, kProdWarps = 4;
+constexpr int kConsThreads = kConsWarps * 32, kProdThreads = kProdWarps * 32;
+constexpr int kThreads = kConsThreads + kProdThreads;
+constexpr int kStages = 2;
+constexpr int kMaxBulk = 128;  // rows / tile arrays of one tile (the plain-load fallback walks this table)
 
 enum : int { BK_F32 = 0, BK_I64 = 1, BK_U8 = 2, BK_DOF = 3, BK_TGT = 4 };
 
@@ -49,6 +51,14 @@ struct Lay {
   static constexpr int A_RB = 0, A_CF = 83, A_BOX = 101;     // hand row 13 | 5 tips x 7 | 5 pads x 7 ; contacts ; box
   static constexpr int SA = BG ? 107 : 99;
   static constexpr int STAGE_BYTES = (OFF_AOS + 32 * SA * 4 + 127) / 128 * 128;
+  // work block: values that cross a warp, [field][32] floats (lane = env: conflict-free)
+  static constexpr int W_BIN = 0, W_PADBOX = 5;  // 5 each
+  static constexpr int W_CDIST = 10, W_DRIFT = 11, W_VMAG = 12, W_AVGHDIFF = 13, W_MINTIPBOX = 14, W_MINTIPZ = 15;
+  static constexpr int W_BVEL = 16;              // 6: finite-difference base velocity
+  static constexpr int W_BOXHAS = 22, W_SOK = 23, W_BOXFAR = 24, W_HITG = 25, W_HCOK = 26;
+  static constexpr int W_WGT = 27;               // 26 weighted reward terms
+  static constexpr int W_CHG = 53, W_RHAND = 54, W_FV2 = 58, W_FA2 = 78, W_JL = 98;  // BaseTask (common rewards)
+  static constexpr int W_COUNT = BG ? 53 : 118;
 };
 
 
@@ -122,11 +132,12 @@ struct Post2Args {
   const float* uniforms;
   uint64_t seed, step;
   // ---- derived on the host (build_post2) ----
-  int32_t tiles, workers, nc;             // nc = compute warps (= producer warps = tile slots) per CTA
+  int32_t tiles, workers;
   int32_t common, first, want_tgt;
   int32_t bulk_ok, n_bulk, n_bulk_early;  // entries [0, n_bulk_early) touch sim tensors only
   uint32_t tx_bytes;                      // bytes of all bulk entries of a full tile
-  int32_t wp;                             // obs tile row stride (odd)
+  int32_t wp;                             // obs tile row stride in floats
+  int32_t obs_bulk;                       // 1: the obs tile of a full tile is flat ([32][obs_dim]) and leaves with ONE bulk store
   uint32_t obs_late;                      // bit c: obs columns [32c, 32c+32) hold a value that phase B writes
   uint32_t smem_bytes;
   int32_t rb_off[11], cf_off[6];
@@ -171,7 +182,10 @@ inline int build_post2(Post2Args& a) {
   a.first = (a.flags & DEX_FLAG_FIRST_REWARD_CALL) ? 1 : 0;
   a.want_tgt = (has(DEX_K_BASE_DOF_TARGET) || has(DEX_K_ACTIVE_FINGER_DOF_TARGET) || has(DEX_K_ALL_FINGER_DOF_TARGET)) ? 1 : 0;
   a.tiles = (a.n + 31) / 32;
-  a.wp = P.obs_dim | 1;
+  // obs tile: flat rows (stride obs_dim) whenever lane = env stores stay <= 4-way bank conflicted, so that a full tile is
+  // one contiguous 16-byte-aligned block and leaves with a single cp.async.bulk store; else odd stride + row copies
+  a.obs_bulk = (P.obs_dim % 8 != 0 && ((uintptr_t)a.out.obs_buf & 15u) == 0) ? 1 : 0;
+  a.wp = a.obs_bulk ? P.obs_dim : (P.obs_dim | 1);
   a.obs_late = 0;
   {
     const int late_keys[7] = {DEX_K_THUMB_CONTACT, DEX_K_OTHER_FINGERS_CONTACT, DEX_K_GRASP_STATE, DEX_K_GRASP_DURATION,
@@ -263,7 +277,7 @@ inline int build_post2(Post2Args& a) {
   a.n_bulk = k;
   a.tx_bytes = tx;
   a.bulk_ok = aligned ? 1 : 0;
-  a.smem_bytes = 0;  // set by the launcher: nc x (stage + obs tile)
+  a.smem_bytes = (uint32_t)(kStages * LY::STAGE_BYTES + LY::W_COUNT * 128 + (32 * a.wp * 4 + 127) / 128 * 128);
   return DEX_OK;
 }
 
@@ -291,9 +305,11 @@ inline bool std_layout_matches(const Post2Args& a) {
 constexpr int kTlIters = 8;
 __device__ unsigned long long* g_tl2 = nullptr;
 #define TL2_DECL unsigned long long* const tl2 = g_tl2
+#define TL2_PARAM , unsigned long long* const tl2
+#define TL2_ARG , tl2
 #define TL2(it, k)                                                                                                 \
   do {                                                                                                             \
-    if (tl2 != nullptr && (it) < kTlIters && (threadIdx.x == 0 || threadIdx.x == 32 * A.nc)) {                 \
+    if (tl2 != nullptr && (it) < kTlIters && (threadIdx.x == 0 || threadIdx.x == kConsThreads)) {                 \
       unsigned long long* q_ = tl2 + ((size_t)blockIdx.x * kTlIters + (it)) * 32;                                  \
       q_[(k)] = (unsigned long long)clock64();                                                                     \
       if ((k) == 0) {                                                                                              \
@@ -308,6 +324,8 @@ __device__ unsigned long long* g_tl2 = nullptr;
   } while (0)
 #else
 #define TL2_DECL
+#define TL2_PARAM
+#define TL2_ARG
 #define TL2(it, k)
 #endif
 
@@ -359,13 +377,14 @@ __device__ __forceinline__ void obs_put(float* obs, const int off, const int j, 
 // producer side: one producer warp fills the slot of its compute warp
 // ------------------------------------------------------------------------------------------------
 // generic path (ragged tile, or row bases / N that are not 16-byte friendly): every row with plain loads
-__device__ __forceinline__ void prod_rows_ldg(const Post2Args& A, unsigned char* stage, const int e0, const int ne, const int lane) {
+__device__ __forceinline__ void prod_rows_ldg(const Post2Args& A, unsigned char* stage, const int e0, const int ne, const int pw,
+                                              const int lane) {
   const bool act = lane < ne;
-  for (int k0 = 0; k0 < A.n_bulk; k0 += 8) {
+  for (int k0 = pw; k0 < A.n_bulk; k0 += 8 * kProdWarps) {
     unsigned long long v[8];
 #pragma unroll
     for (int u = 0; u < 8; ++u) {
-      const int k = k0 + u;
+      const int k = k0 + kProdWarps * u;
       v[u] = 0ull;
       if (k < A.n_bulk) {
         const int kind = A.bk_kind[k];
@@ -381,7 +400,7 @@ __device__ __forceinline__ void prod_rows_ldg(const Post2Args& A, unsigned char*
     }
 #pragma unroll
     for (int u = 0; u < 8; ++u) {
-      const int k = k0 + u;
+      const int k = k0 + kProdWarps * u;
       if (k < A.n_bulk && act) {
         const int kind = A.bk_kind[k];
         unsigned char* dst = stage + (size_t)A.bk_dst16[k] * 16;
@@ -401,7 +420,7 @@ __device__ __forceinline__ void prod_rows_ldg(const Post2Args& A, unsigned char*
     const int per = kind == BK_DOF ? 52 : 26;
     const float* src = reinterpret_cast<const float*>(A.bk_ptr[k]) + (size_t)e0 * per;
     float* dst = reinterpret_cast<float*>(stage + (size_t)A.bk_dst16[k] * 16);
-    for (int i = lane; i < ne * per; i += 32) dst[i] = src[i];
+    for (int i = pw * 32 + lane; i < ne * per; i += kProdThreads) dst[i] = src[i];
   }
 }
 
@@ -415,6 +434,7 @@ template <bool BG, bool STD>
 struct Cx {
   const unsigned char* stage;
   float* obs;  // obs tile row of this lane's env
+  float* wk;   // work block + lane
   const int32_t* obs_offset;  // generic instance: DexParams.obs_offset
   const int32_t* dof2afj;
   int lane, e0, ne;
@@ -673,7 +693,7 @@ __device__ __forceinline__ void part_hand(const Post2Args& A, const Cx<BG, STD>&
 
 // ---- the 26 DOFs: finite-difference velocity (observation_encoder.py:298-321), obs columns, common-reward partial
 //      sums (reward_calculator.py:94-98,138-160: Isaac dof_vel, not the finite difference; summed in DOF order)
-template <bool BG, bool STD>
+template <bool BG, bool STD, int Q0, int Q1>  // DOF pairs [Q0, Q1)
 __device__ __forceinline__ void part_dofs(const Post2Args& A, const Cx<BG, STD>& c, Mid& m) {
   using LY = Lay<BG>;
   const DexParams& P = A.p;
@@ -690,9 +710,8 @@ __device__ __forceinline__ void part_dofs(const Post2Args& A, const Cx<BG, STD>&
             o_at = c.off(DEX_K_ALL_FINGER_DOF_TARGET);
   const int o_fp = c.off(DEX_K_ACTIVE_FINGER_DOF_POS), o_fv = c.off(DEX_K_ACTIVE_FINGER_DOF_VEL),
             o_ft = c.off(DEX_K_ACTIVE_FINGER_DOF_TARGET);
-  float fv2 = 0.0f, fa2 = 0.0f, jl = 0.0f;
 #pragma unroll
-  for (int q = 0; q < DEX_NUM_DOF / 2; ++q) {
+  for (int q = Q0; q < Q1; ++q) {
     const float4 v4 = d4[q];
     const float pos2[2] = {v4.x, v4.z}, vel2[2] = {v4.y, v4.w};
 #pragma unroll
@@ -706,7 +725,7 @@ __device__ __forceinline__ void part_dofs(const Post2Args& A, const Cx<BG, STD>&
         obs_put(obs, o_bp, d, pos);
         obs_put(obs, o_bv, d, fd);
         if (!BG) obs_put(obs, o_bt, d, tgt);
-        m.bvel[d < DEX_NUM_BASE ? d : 0] = fd;
+        if (BG) c.wk[(LY::W_BVEL + (d < DEX_NUM_BASE ? d : 0)) * 32] = fd;
       } else {
         const int j = d - DEX_NUM_BASE;
         obs_put(obs, o_ap, j, pos);
@@ -721,19 +740,17 @@ __device__ __forceinline__ void part_dofs(const Post2Args& A, const Cx<BG, STD>&
         if (common) {
           const float iv = vel2[h];
           const float pvv = first ? iv : soa[(LY::R_PFDV + j) * 32];
-          fv2 += iv * iv;
+          // partial terms: summed in DOF order by the term itself (reward_calculator.py:138-160)
+          c.wk[(LY::W_FV2 + j) * 32] = iv * iv;
           const float acc = iv - pvv;
-          fa2 += acc * acc;
+          c.wk[(LY::W_FA2 + j) * 32] = acc * acc;
           const float nj = div_rn(2.0f * (pos - P.dof_lower[d]), P.dof_upper[d] - P.dof_lower[d]) - 1.0f;
-          jl += clampf(fabsf(nj) - 0.8f, 0.0f, 1.0f);
+          c.wk[(LY::W_JL + j) * 32] = clampf(fabsf(nj) - 0.8f, 0.0f, 1.0f);
           st.prev_finger_dof_vel[j * N + env] = iv;
         }
       }
     }
   }
-  m.fv2 = fv2;
-  m.fa2 = fa2;
-  m.jl = jl;
 }
 
 // ---- prev_actions columns (observation_encoder.py:287-296); active_rule_targets <- active_prev_targets
@@ -772,7 +789,8 @@ __device__ __forceinline__ void part_copies(const Post2Args& A, const Cx<BG, STD
 
 // ---- BlindGrasping: finger-box contacts (blind_grasping_task.py:773-833), success duration (:626-648), stage FSM
 //      (:835-978; plain fp32 accumulation of (float)control_dt decides the transition step)
-template <bool STD>
+// WRITE = false: the reward-term warps recompute the (cheap) chain for themselves instead of waiting for warp 0
+template <bool STD, bool WRITE>
 __device__ __forceinline__ void part_task_state(const Post2Args& A, const Cx<true, STD>& c, Mid& m) {
   using LY = Lay<true>;
   const DexParams& P = A.p;
@@ -796,15 +814,15 @@ __device__ __forceinline__ void part_task_state(const Post2Args& A, const Cx<tru
   m.thumb = fbc[0];
   m.others = fbc[1] || fbc[2] || fbc[3] || fbc[4];
   m.grasp = m.thumb && m.others;
-  obs_put(obs, c.off(DEX_K_THUMB_CONTACT), 0, m.thumb ? 1.0f : 0.0f);
-  obs_put(obs, c.off(DEX_K_OTHER_FINGERS_CONTACT), 0, m.others ? 1.0f : 0.0f);
-  obs_put(obs, c.off(DEX_K_GRASP_STATE), 0, m.grasp ? 1.0f : 0.0f);
+  if (WRITE) obs_put(obs, c.off(DEX_K_THUMB_CONTACT), 0, m.thumb ? 1.0f : 0.0f);
+  if (WRITE) obs_put(obs, c.off(DEX_K_OTHER_FINGERS_CONTACT), 0, m.others ? 1.0f : 0.0f);
+  if (WRITE) obs_put(obs, c.off(DEX_K_GRASP_STATE), 0, m.grasp ? 1.0f : 0.0f);
   const bool cond = (box_z > P.success_height_threshold) && (n_on_box >= P.min_fingers_for_grasp);
   m.sds = cond ? sds_old + 1 : 0;
-  st.success_duration_steps[env] = (long long)m.sds;
-  st.success_conditions_met[env] = cond ? 1 : 0;
+  if (WRITE) st.success_duration_steps[env] = (long long)m.sds;
+  if (WRITE) st.success_conditions_met[env] = cond ? 1 : 0;
   m.graspdur = (float)m.sds * dt;
-  obs_put(obs, c.off(DEX_K_GRASP_DURATION), 0, m.graspdur);
+  if (WRITE) obs_put(obs, c.off(DEX_K_GRASP_DURATION), 0, m.graspdur);
   // FSM
   const bool thumb_other = (m.bin[0] != 0.0f) && ((m.bin[1] != 0.0f) || (m.bin[2] != 0.0f) || (m.bin[3] != 0.0f) || (m.bin[4] != 0.0f));
   if (stage == 2) scd = thumb_other ? scd + dt : 0.0f;
@@ -816,11 +834,11 @@ __device__ __forceinline__ void part_task_state(const Post2Args& A, const Cx<tru
     tis = 0.0f;
     scd = 0.0f;
   }
-  st.current_stage[env] = (long long)stage;
-  st.time_in_stage[env] = tis;
-  st.stage_contact_duration[env] = scd;
-  st.just_transitioned_to_stage2[env] = s1_done ? 1 : 0;
-  st.just_transitioned_to_stage3[env] = s2_done ? 1 : 0;
+  if (WRITE) st.current_stage[env] = (long long)stage;
+  if (WRITE) st.time_in_stage[env] = tis;
+  if (WRITE) st.stage_contact_duration[env] = scd;
+  if (WRITE) st.just_transitioned_to_stage2[env] = s1_done ? 1 : 0;
+  if (WRITE) st.just_transitioned_to_stage3[env] = s2_done ? 1 : 0;
   float prog = 0.0f;  // :958-978
   if (stage == 1) prog = clampf(div_rn(tis, P.stage1_duration), 0.0f, 1.0f);
   if (stage == 2) prog = clampf(div_rn(tis, P.stage2_duration), 0.0f, 1.0f);
@@ -828,14 +846,14 @@ __device__ __forceinline__ void part_task_state(const Post2Args& A, const Cx<tru
   m.stage = stage;
   m.j2 = s1_done;
   m.j3 = s2_done;
-  obs_put(obs, c.off(DEX_K_CURRENT_STAGE), 0, (float)stage);
-  obs_put(obs, c.off(DEX_K_TIME_IN_STAGE), 0, tis);
-  obs_put(obs, c.off(DEX_K_STAGE_PROGRESS), 0, prog);
+  if (WRITE) obs_put(obs, c.off(DEX_K_CURRENT_STAGE), 0, (float)stage);
+  if (WRITE) obs_put(obs, c.off(DEX_K_TIME_IN_STAGE), 0, tis);
+  if (WRITE) obs_put(obs, c.off(DEX_K_STAGE_PROGRESS), 0, prog);
 }
 
-// raw + weighted rows of term i leave from registers; the weighted value is kept for the ordered total
+// raw + weighted rows of term i leave from registers; the weighted value is parked in the work block for the ordered total
 template <bool BG, bool STD>
-__device__ __forceinline__ void emit_term(const Post2Args& A, const Cx<BG, STD>& c, Mid& m, const int i, const float r) {
+__device__ __forceinline__ void emit_term(const Post2Args& A, const Cx<BG, STD>& c, const int i, const float r) {
   const float w = A.p.reward_weight[i];
   if (!STD && w == 0.0f) return;  // reward_calculator.py:247-251: zero-weight terms are not materialised (STD: none is)
   const int row = A.p.component_row[i];
@@ -843,65 +861,80 @@ __device__ __forceinline__ void emit_term(const Post2Args& A, const Cx<BG, STD>&
   float* g = A.out.reward_components + c.env;
   g[(size_t)row * c.N] = r;
   g[(size_t)(row + 1) * c.N] = rw;
-  m.wgt[i] = rw;
+  c.wk[(Lay<BG>::W_WGT + i) * 32] = rw;
 }
 
-// ---- common reward terms (reward_calculator.py:66-221); BaseTask
-template <bool STD>
-__device__ __forceinline__ void part_common_terms(const Post2Args& A, const Cx<false, STD>& c, Mid& m) {
-  emit_term<false, STD>(A, c, m, DEX_R_ALIVE, 1.0f);
-  emit_term<false, STD>(A, c, m, DEX_R_HEIGHT_SAFETY, clampf(1.0f - expf(-(m.min_tip_z - 0.02f) * 20.0f), 0.0f, 1.0f));
-  emit_term<false, STD>(A, c, m, DEX_R_FINGER_VELOCITY, expf(-0.1f * sqrtf(m.fv2)));
-  emit_term<false, STD>(A, c, m, DEX_R_HAND_VELOCITY, m.rhand[0]);
-  emit_term<false, STD>(A, c, m, DEX_R_HAND_ANGULAR_VELOCITY, m.rhand[1]);
-  emit_term<false, STD>(A, c, m, DEX_R_JOINT_LIMIT, 1.0f - div_rn(m.jl, 20.0f));
-  emit_term<false, STD>(A, c, m, DEX_R_FINGER_ACCELERATION, expf(-2.0f * sqrtf(m.fa2)));
-  emit_term<false, STD>(A, c, m, DEX_R_HAND_ACCELERATION, m.rhand[2]);
-  emit_term<false, STD>(A, c, m, DEX_R_HAND_ANGULAR_ACCELERATION, m.rhand[3]);
-  emit_term<false, STD>(A, c, m, DEX_R_CONTACT_STABILITY, expf(-m.chg));
+// the reward terms are dealt round-robin to the consumer warps 1..7; warp CW runs the terms with (term % 7) == CW - 1 as
+// one straight-line block (TERM's value expression is only instantiated for the owner)
+#define DEX_TERM(BGF, i, expr)                                   \
+  if constexpr (((i) % (kConsWarps - 1)) == CW - 1) emit_term<BGF, STD>(A, c, (i), (expr))
+
+// ---- common reward terms (reward_calculator.py:66-221); BaseTask.  The ordered partial sums are formed here.
+template <bool STD, int CW>
+__device__ __forceinline__ void part_common_terms(const Post2Args& A, const Cx<false, STD>& c) {
+  using LY = Lay<false>;
+  const float* wk = c.wk;
+  auto sum20 = [&](const int f0) {
+    float a = 0.0f;
+#pragma unroll
+    for (int j = 0; j < DEX_NUM_FINGER_DOF; ++j) a += wk[(f0 + j) * 32];
+    return a;
+  };
+  DEX_TERM(false, DEX_R_ALIVE, 1.0f);
+  DEX_TERM(false, DEX_R_HEIGHT_SAFETY, clampf(1.0f - expf(-(wk[LY::W_MINTIPZ * 32] - 0.02f) * 20.0f), 0.0f, 1.0f));
+  DEX_TERM(false, DEX_R_FINGER_VELOCITY, expf(-0.1f * sqrtf(sum20(LY::W_FV2))));
+  DEX_TERM(false, DEX_R_HAND_VELOCITY, wk[(LY::W_RHAND + 0) * 32]);
+  DEX_TERM(false, DEX_R_HAND_ANGULAR_VELOCITY, wk[(LY::W_RHAND + 1) * 32]);
+  DEX_TERM(false, DEX_R_JOINT_LIMIT, 1.0f - div_rn(sum20(LY::W_JL), 20.0f));
+  DEX_TERM(false, DEX_R_FINGER_ACCELERATION, expf(-2.0f * sqrtf(sum20(LY::W_FA2))));
+  DEX_TERM(false, DEX_R_HAND_ACCELERATION, wk[(LY::W_RHAND + 2) * 32]);
+  DEX_TERM(false, DEX_R_HAND_ANGULAR_ACCELERATION, wk[(LY::W_RHAND + 3) * 32]);
+  DEX_TERM(false, DEX_R_CONTACT_STABILITY, expf(-wk[LY::W_CHG * 32]));  // summed in finger order by part_contacts
 }
 
-// ---- BlindGrasping task terms (blind_grasping_task.py:980-1208), after the FSM
-template <bool STD>
-__device__ __forceinline__ void part_task_terms(const Post2Args& A, const Cx<true, STD>& c, Mid& m) {
+// ---- BlindGrasping task terms (blind_grasping_task.py:980-1208), after the FSM (m: part_task_state of this warp)
+template <bool STD, int CW>
+__device__ __forceinline__ void part_task_terms(const Post2Args& A, const Cx<true, STD>& c, const Mid& m) {
   using LY = Lay<true>;
   const DexParams& P = A.p;
+  const float* wk = c.wk;
   const float* aos = c.aos();
   const float* rb = aos + LY::A_RB;
   const float m1 = (m.stage == 1) ? 1.0f : 0.0f, m2 = (m.stage == 2) ? 1.0f : 0.0f, m3 = (m.stage == 3) ? 1.0f : 0.0f;
   const float fg = m.grasp ? 1.0f : 0.0f;
-  emit_term<true, STD>(A, c, m, DEX_R_S1_HEIGHT_ALIGNMENT, expf(-P.height_alignment_decay * m.avg_hdiff) * m1);
-  emit_term<true, STD>(A, c, m, DEX_R_S1_CENTROID_POSITIONING, expf(-P.centroid_positioning_decay * m.cdist) * m1);
-  emit_term<true, STD>(A, c, m, DEX_R_S1_OBJECT_STABILITY, expf(-P.object_stability_decay * (m.drift + m.vmag)) * m1);
-  {  // torch.var(dim=1), unbiased, z of the first three pads
+  DEX_TERM(true, DEX_R_S1_HEIGHT_ALIGNMENT, expf(-P.height_alignment_decay * wk[LY::W_AVGHDIFF * 32]) * m1);
+  DEX_TERM(true, DEX_R_S1_CENTROID_POSITIONING, expf(-P.centroid_positioning_decay * wk[LY::W_CDIST * 32]) * m1);
+  DEX_TERM(true, DEX_R_S1_OBJECT_STABILITY, expf(-P.object_stability_decay * (wk[LY::W_DRIFT * 32] + wk[LY::W_VMAG * 32])) * m1);
+  if constexpr ((DEX_R_S1_FINGER_HEIGHT_CONSISTENCY % (kConsWarps - 1)) == CW - 1) {  // torch.var(dim=1), unbiased, z of the first three pads
     const float z0 = rb[13 + 35 + 2], z1 = rb[13 + 35 + 7 + 2], z2 = rb[13 + 35 + 14 + 2];
     const float mean = (z0 + z1 + z2) / 3.0f;
     const float d0 = z0 - mean, d1 = z1 - mean, d2 = z2 - mean;
     const float var = (d0 * d0 + d1 * d1 + d2 * d2) / 2.0f;
-    emit_term<true, STD>(A, c, m, DEX_R_S1_FINGER_HEIGHT_CONSISTENCY, expf(-P.height_consistency_decay * var) * m1);
+    emit_term<true, STD>(A, c, DEX_R_S1_FINGER_HEIGHT_CONSISTENCY, expf(-P.height_consistency_decay * var) * m1);
   }
-  {
-    const float th = reinterpret_cast<const float*>(c.stage + LY::OFF_DOF)[c.lane * 52 + 2 * DEX_NUM_BASE];
-    emit_term<true, STD>(A, c, m, DEX_R_S1_THUMB_ROTATION, expf(-5.0f * fabsf(th - P.half_pi)) * m1);
-  }
-  emit_term<true, STD>(A, c, m, DEX_R_S2_THUMB_CONTACT, (m.thumb ? 1.0f : 0.0f) * m2);
-  emit_term<true, STD>(A, c, m, DEX_R_S2_OTHER_FINGERS_CONTACT, (m.others ? 1.0f : 0.0f) * m2);
-  emit_term<true, STD>(A, c, m, DEX_R_S2_GRASP_ACHIEVEMENT, fg * m2);
-  emit_term<true, STD>(A, c, m, DEX_R_S2_FINGERPAD_PROXIMITY,
-                  expf(-P.fingerpad_proximity_decay * fmaxf(m.min_tip_box, P.min_reward_distance)) * m2);
-  {
+  DEX_TERM(true, DEX_R_S1_THUMB_ROTATION,
+           expf(-5.0f * fabsf(reinterpret_cast<const float*>(c.stage + LY::OFF_DOF)[c.lane * 52 + 2 * DEX_NUM_BASE] - P.half_pi)) * m1);
+  DEX_TERM(true, DEX_R_S2_THUMB_CONTACT, (m.thumb ? 1.0f : 0.0f) * m2);
+  DEX_TERM(true, DEX_R_S2_OTHER_FINGERS_CONTACT, (m.others ? 1.0f : 0.0f) * m2);
+  DEX_TERM(true, DEX_R_S2_GRASP_ACHIEVEMENT, fg * m2);
+  DEX_TERM(true, DEX_R_S2_FINGERPAD_PROXIMITY,
+           expf(-P.fingerpad_proximity_decay * fmaxf(wk[LY::W_MINTIPBOX * 32], P.min_reward_distance)) * m2);
+  if constexpr ((DEX_R_S2_BASE_STABILITY % (kConsWarps - 1)) == CW - 1) {
     float bv2 = 0.0f;
 #pragma unroll
-    for (int d = 0; d < DEX_NUM_BASE; ++d) bv2 += m.bvel[d] * m.bvel[d];  // finite-difference base velocity
-    emit_term<true, STD>(A, c, m, DEX_R_S2_BASE_STABILITY, expf(-P.base_stability_decay * sqrtf(bv2)) * m2);
+    for (int d = 0; d < DEX_NUM_BASE; ++d) {
+      const float v = wk[(LY::W_BVEL + d) * 32];  // finite-difference base velocity
+      bv2 += v * v;
+    }
+    emit_term<true, STD>(A, c, DEX_R_S2_BASE_STABILITY, expf(-P.base_stability_decay * sqrtf(bv2)) * m2);
   }
-  emit_term<true, STD>(A, c, m, DEX_R_S3_OBJECT_HEIGHT, clampf(div_rn(aos[LY::A_BOX + 2] - P.box_z, P.lift_height_range), 0.0f, 1.0f) * m3);
-  emit_term<true, STD>(A, c, m, DEX_R_S3_GRASP_MAINTENANCE, fg * m3);
-  emit_term<true, STD>(A, c, m, DEX_R_S3_GRASP_DURATION, clampf(div_rn(m.graspdur, P.contact_duration_threshold_s), 0.0f, 1.0f) * m3);
+  DEX_TERM(true, DEX_R_S3_OBJECT_HEIGHT, clampf(div_rn(aos[LY::A_BOX + 2] - P.box_z, P.lift_height_range), 0.0f, 1.0f) * m3);
+  DEX_TERM(true, DEX_R_S3_GRASP_MAINTENANCE, fg * m3);
+  DEX_TERM(true, DEX_R_S3_GRASP_DURATION, clampf(div_rn(m.graspdur, P.contact_duration_threshold_s), 0.0f, 1.0f) * m3);
   // completion bonuses :1025-1048 (transition and not failed), penetration :1194-1208
-  emit_term<true, STD>(A, c, m, DEX_R_S1_COMPLETION, (m.j2 && m.hcok && m.sok) ? 1.0f : 0.0f);
-  emit_term<true, STD>(A, c, m, DEX_R_S2_COMPLETION, (m.j3 && m.grasp) ? 1.0f : 0.0f);
-  emit_term<true, STD>(A, c, m, DEX_R_PENETRATION_PENALTY, fmaxf(P.penetration_threshold - m.min_tip_box, 0.0f) * P.penetration_depth_scale);
+  DEX_TERM(true, DEX_R_S1_COMPLETION, (m.j2 && m.hcok && m.sok) ? 1.0f : 0.0f);
+  DEX_TERM(true, DEX_R_S2_COMPLETION, (m.j3 && m.grasp) ? 1.0f : 0.0f);
+  DEX_TERM(true, DEX_R_PENETRATION_PENALTY, fmaxf(P.penetration_threshold - wk[LY::W_MINTIPBOX * 32], 0.0f) * P.penetration_depth_scale);
 }
 
 // ---- termination (step_processor.py:133-181, termination_manager.py:120-278), masks, tile record.
@@ -1000,13 +1033,16 @@ __device__ __forceinline__ unsigned part_terminate(const Post2Args& A, const Cx<
 // ---- ordered weighted sum (reward_calculator.py:223-275) + termination rewards
 //      (termination_manager.py:280-321, step_processor.py:204-219)
 template <bool BG, bool STD>
-__device__ __forceinline__ void part_total(const Post2Args& A, const Cx<BG, STD>& c, const Mid& m, const unsigned cls) {
+__device__ __forceinline__ void part_total(const Post2Args& A, const Cx<BG, STD>& c, const unsigned cls) {
   const DexParams& P = A.p;
   constexpr int I0 = BG ? DEX_NUM_COMMON_TERMS : 0, I1 = BG ? DEX_NUM_REWARD_TERMS : DEX_NUM_COMMON_TERMS;
+  float wv[I1 - I0];
+#pragma unroll
+  for (int i = I0; i < I1; ++i) wv[i - I0] = c.wk[(Lay<BG>::W_WGT + i) * 32];  // zero-weight terms hold stale values: skipped below
   float total = 0.0f;
 #pragma unroll
   for (int i = I0; i < I1; ++i)
-    if (STD || P.reward_weight[i] != 0.0f) total += m.wgt[i];  // dict order: common, then task
+    if (STD || P.reward_weight[i] != 0.0f) total += wv[i - I0];  // dict order: common, then task
   const bool t_success = cls & 1u, t_failure = cls & 2u, t_timeout = cls & 4u;
   const float rs = t_success ? P.success_reward : 0.0f;
   const float rf = t_failure ? P.failure_reward : 0.0f;
@@ -1023,75 +1059,216 @@ __device__ __forceinline__ void part_total(const Post2Args& A, const Cx<BG, STD>
   A.out.rew_buf[c.env] = rew;
 }
 
-// obs tile -> obs_buf by the tile's own warp: lane = column, every global store is one full 128-byte request;
-// eight rows per batch keep eight loads in flight
-template <bool FULL>
-__device__ __forceinline__ void copy_obs(const float* s_obs, float* g_tile, const int W, const int WP, const int ne, const int lane) {
+// obs tile -> obs_buf with row copies (ragged tiles, layouts whose flat tile would bank-conflict): the env rows are spread
+// over the 8 consumer warps, lane = column: every global store is one full 128-byte request
+__device__ __forceinline__ void copy_obs_rows(const float* s_obs, float* g_tile, const int W, const int WP, const int ne,
+                                              const int w, const int lane) {
   const int nchunk = (W + 31) >> 5;
 #pragma unroll 1
   for (int ch = 0; ch < nchunk; ++ch) {
     const int col = 32 * ch + lane;
     if (col < W) {
-      const float* sp = s_obs + col;
-      float* gp = g_tile + col;
-      if (FULL) {
-#pragma unroll 1
-        for (int r0 = 0; r0 < 32; r0 += 8) {
-          float v[8];
+      float v[4];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) v[i] = sp[(r0 + i) * WP];
+      for (int i = 0; i < 4; ++i) {
+        const int row = w + kConsWarps * i;
+        if (row < ne) v[i] = s_obs[row * WP + col];
+      }
 #pragma unroll
-          for (int i = 0; i < 8; ++i) gp[(size_t)(r0 + i) * W] = v[i];
-        }
-      } else {
-        for (int r = 0; r < ne; ++r) gp[(size_t)r * W] = sp[r * WP];
+      for (int i = 0; i < 4; ++i) {
+        const int row = w + kConsWarps * i;
+        if (row < ne) g_tile[(size_t)row * W + col] = v[i];
       }
     }
   }
 }
 
-// the whole per-env program of one tile, run by the tile's compute warp
-template <bool BG, bool STD, bool FULL>
-__device__ __forceinline__ unsigned tile_program(const Post2Args& A, Cx<BG, STD>& c, const unsigned stamp) {
+// phase A: everything that depends only on the staged tile.  One fixed job per consumer warp, straight-line code; the
+// values another warp needs later go to the work block.
+template <bool BG, bool STD>
+__device__ __forceinline__ void phase_a(const Post2Args& A, const Cx<BG, STD>& c, const int cw) {
+  using LY = Lay<BG>;
+  float* wk = c.wk;
   Mid m;
-  unsigned rbits = 0;
-  if (FULL || c.act) {
-    part_poses<BG, STD, false>(A, c, m);
-    part_poses<BG, STD, true>(A, c, m);
-    part_contacts<BG, STD>(A, c, m);
-    part_hand<BG, STD>(A, c, m);
-    part_dofs<BG, STD>(A, c, m);
-    part_copies<BG, STD>(A, c);
-    if constexpr (BG) part_task_state<STD>(A, c, m);
+  switch (cw) {
+    case 0:  // tips
+      part_poses<BG, STD, false>(A, c, m);
+      wk[LY::W_HITG * 32] = m.hitg ? 1.0f : 0.0f;
+      if (BG) wk[LY::W_MINTIPBOX * 32] = m.min_tip_box;
+      else wk[LY::W_MINTIPZ * 32] = m.min_tip_z;
+      break;
+    case 1:  // pads
+      part_poses<BG, STD, true>(A, c, m);
+      if (BG) {
+#pragma unroll
+        for (int f = 0; f < DEX_NUM_FINGERS; ++f) wk[(LY::W_PADBOX + f) * 32] = m.padbox[f];
+        wk[LY::W_AVGHDIFF * 32] = m.avg_hdiff;
+        wk[LY::W_CDIST * 32] = m.cdist;
+        wk[LY::W_HCOK * 32] = m.hcok ? 1.0f : 0.0f;
+      }
+      break;
+    case 2:  // contact sensors, box stability
+      part_contacts<BG, STD>(A, c, m);
+      if (BG) {
+#pragma unroll
+        for (int f = 0; f < DEX_NUM_FINGERS; ++f) wk[(LY::W_BIN + f) * 32] = m.bin[f];
+        wk[LY::W_BOXHAS * 32] = m.boxhas ? 1.0f : 0.0f;
+        wk[LY::W_DRIFT * 32] = m.drift;
+        wk[LY::W_VMAG * 32] = m.vmag;
+        wk[LY::W_SOK * 32] = m.sok ? 1.0f : 0.0f;
+      } else {
+        wk[LY::W_CHG * 32] = m.chg;
+      }
+      break;
+    case 3:  // hand, copies
+      part_hand<BG, STD>(A, c, m);
+      if (BG) {
+        wk[LY::W_BOXFAR * 32] = m.boxfar ? 1.0f : 0.0f;
+      } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) wk[(LY::W_RHAND + k) * 32] = m.rhand[k];
+      }
+      part_copies<BG, STD>(A, c);
+      break;
+    case 4: part_dofs<BG, STD, 0, 4>(A, c, m); break;
+    case 5: part_dofs<BG, STD, 4, 7>(A, c, m); break;
+    case 6: part_dofs<BG, STD, 7, 10>(A, c, m); break;
+    default: part_dofs<BG, STD, 10, 13>(A, c, m); break;
   }
-  const unsigned cls = part_terminate<BG, STD, FULL>(A, c, m, stamp, rbits);
-  if (FULL || c.act) {
-    if constexpr (BG)
-      part_task_terms<STD>(A, c, m);
-    else
-      part_common_terms<STD>(A, c, m);
-    part_total<BG, STD>(A, c, m, cls);
+}
+
+// work block -> the inputs of part_task_state / part_task_terms / part_terminate
+template <bool BG>
+__device__ __forceinline__ void import_mid(const float* wk, Mid& m) {
+  using LY = Lay<BG>;
+  m.hitg = wk[LY::W_HITG * 32] != 0.0f;
+  if (BG) {
+#pragma unroll
+    for (int f = 0; f < DEX_NUM_FINGERS; ++f) {
+      m.bin[f] = wk[(LY::W_BIN + f) * 32];
+      m.padbox[f] = wk[(LY::W_PADBOX + f) * 32];
+    }
+    m.boxhas = wk[LY::W_BOXHAS * 32] != 0.0f;
+    m.boxfar = wk[LY::W_BOXFAR * 32] != 0.0f;
+    m.hcok = wk[LY::W_HCOK * 32] != 0.0f;
+    m.sok = wk[LY::W_SOK * 32] != 0.0f;
   }
-  return rbits;
+}
+
+// phase C, warps 1..7: the reward terms (BlindGrasping: behind a private copy of the task-state chain)
+template <bool BG, bool STD, int CW>
+__device__ __forceinline__ void phase_c_terms(const Post2Args& A, const Cx<BG, STD>& c) {
+  if constexpr (BG) {
+    Mid m;
+    import_mid<true>(c.wk, m);
+    part_task_state<STD, false>(A, c, m);
+    part_task_terms<STD, CW>(A, c, m);
+  } else {
+    part_common_terms<STD, CW>(A, c);
+  }
+}
+
+__device__ __forceinline__ void cons_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kConsThreads) : "memory"); }
+
+// shared -> global bulk store of the flat obs tile (TMA engine): one instruction for 20 KB
+__device__ __forceinline__ void bulk_s2g(void* dst, const uint32_t src, const uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+
+// one tile on the 8 consumer warps: phase A | barrier | phase C | barrier | phase D | barrier
+template <bool BG, bool STD, bool FULL>
+__device__ __forceinline__ void consume_tile(const Post2Args& A, Cx<BG, STD>& c, const int warp, const int it, const unsigned stamp_in,
+                                             unsigned long long* s_rng_step, unsigned* s_rbits, unsigned& stamp, uint64_t& rng_step,
+                                             const uint32_t bar_empty_s, float* s_obs, float* s_reset_u, bool& store_pending TL2_PARAM) {
+  const int lane = c.lane, tid = warp * 32 + lane;
+  // Philox step counter == stamp of this step's tile records: read once per CTA, behind the first full barrier (i.e.
+  // behind the producers' griddepcontrol.wait; the epilogue CTA advances it only after every record of this launch is out)
+  unsigned long long rs_tmp = 0ull;
+  if (it == 0 && tid == 0) rs_tmp = A.st.rng_step ? *reinterpret_cast<const volatile unsigned long long*>(A.st.rng_step) : A.step;
+  if (FULL || c.act) phase_a<BG, STD>(A, c, warp);
+  if (it == 0 && tid == 0) *s_rng_step = rs_tmp;
+  TL2(it, 2);
+  cons_sync();
+  TL2(it, 3);
+  if (it == 0) {
+    rng_step = *s_rng_step;
+    stamp = ((unsigned)rng_step + 1u) & 0xffffu;
+  }
+  (void)stamp_in;
+  // ---- phase C: warp 0 = task state + termination + tile record; warps 1..7 = reward terms ----
+  unsigned cls = 0;
+  if (warp == 0) {
+    Mid m;
+    if (FULL || c.act) {
+      import_mid<BG>(c.wk, m);
+      if constexpr (BG) part_task_state<STD, true>(A, c, m);
+    }
+    unsigned rbits;
+    cls = part_terminate<BG, STD, FULL>(A, c, m, stamp, rbits);
+    if (lane == 0) *s_rbits = rbits;
+  } else if (FULL || c.act) {
+    switch (warp) {
+      case 1: phase_c_terms<BG, STD, 1>(A, c); break;
+      case 2: phase_c_terms<BG, STD, 2>(A, c); break;
+      case 3: phase_c_terms<BG, STD, 3>(A, c); break;
+      case 4: phase_c_terms<BG, STD, 4>(A, c); break;
+      case 5: phase_c_terms<BG, STD, 5>(A, c); break;
+      case 6: phase_c_terms<BG, STD, 6>(A, c); break;
+      default: phase_c_terms<BG, STD, 7>(A, c); break;
+    }
+  }
+  const bool bulk_out = FULL && A.obs_bulk;
+  if (bulk_out) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // obs tile writes -> visible to the bulk store
+  __syncwarp();
+  TL2(it, 4);
+  cons_sync();
+  TL2(it, 5);
+  // the raw stage is not read after this point: hand it back to the producers
+  if (lane == 0) mbar_arrive(bar_empty_s);
+  // ---- phase D: total, obs tile out, fused reset ----
+  if (warp == 0 && (FULL || c.act)) part_total<BG, STD>(A, c, cls);
+  const int W = A.p.obs_dim;
+  float* const g_obs = A.out.obs_buf + (size_t)c.e0 * W;
+  if (bulk_out) {
+    if (tid == 32) {
+      bulk_s2g(g_obs, s32(s_obs), (uint32_t)(32 * W * 4));
+      store_pending = true;
+    }
+  } else {
+    copy_obs_rows(s_obs, g_obs, W, A.wp, c.ne, warp, lane);
+  }
+  {
+    unsigned mask = *s_rbits;  // written by warp 0 before the barrier above
+    if (mask && !(A.flags & DEX_FLAG_NO_FUSED_RESET)) {  // fused reset (dexhand_base.py:743-756): one warp per env
+      for (int k = 0; mask; ++k) {
+        const int e = __ffs(mask) - 1;
+        mask &= mask - 1;
+        if ((k & (kConsWarps - 1)) == warp) reset_env_warp<BG>(A, c.e0 + e, rng_step, s_reset_u + 32 * warp);
+      }
+    }
+  }
+  if (bulk_out && tid == 32) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // obs tile may be rewritten
+  TL2(it, 7);
+  cons_sync();  // work block, obs tile and s_rbits are reused by the next tile
 }
 
 // ------------------------------------------------------------------------------------------------
-// the kernel: NC (compute warp, producer warp) pairs per CTA, one CTA per SM, persistent
+// the kernel: persistent, 8 consumer + 4 producer warps per CTA, 2-stage ring, two CTAs per SM (BlindGrasping)
 // ------------------------------------------------------------------------------------------------
-template <bool BG, int NC, bool STD>
-__global__ void __launch_bounds__(64 * NC, 1) post_physics_v2_kernel(const __grid_constant__ Post2Args A) {
+template <bool BG, bool STD>
+__global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(const __grid_constant__ Post2Args A) {
   using LY = Lay<BG>;
-  constexpr int kThreads = 64 * NC;
   extern __shared__ __align__(128) unsigned char smem2[];
-  __shared__ __align__(8) unsigned long long s_bar[2 * kMaxPairs];  // full[pair], empty[pair]
-  __shared__ float s_reset_u[32 * kMaxPairs];
+  __shared__ __align__(8) unsigned long long s_bar[2 * kStages];  // full[0..], empty[0..]
+  __shared__ float s_reset_u[32 * kConsWarps];
   __shared__ int s_rbo[kRbW + 1];  // gathered rigid slot -> float offset inside one env's [NB,13] block
   __shared__ unsigned long long s_rng_step;
-  __shared__ int s_epi_warp[8];
+  __shared__ unsigned s_rbits;
+  __shared__ int s_epi_warp[kConsWarps];
   __shared__ int s_epi_base;
   __shared__ int s_epi_cnt[DEX_NUM_COUNTERS];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int slot_bytes = LY::STAGE_BYTES + 32 * A.wp * 4;
 
   // ---- the epilogue CTA (last block): polls the tile records of the workers, all of which are co-resident ----
   if (A.fused_epilogue && (int)blockIdx.x == A.workers) {
@@ -1109,18 +1286,20 @@ __global__ void __launch_bounds__(64 * NC, 1) post_physics_v2_kernel(const __gri
       s_rng_step = rs;
     }
     __syncthreads();
-    epilogue_records<kThreads, 0>(A.ep, A.n, A.p.max_consecutive_successes, ((unsigned)s_rng_step + 1u) & 0xffffu, s_epi_warp,
-                                  &s_epi_base, s_epi_cnt, reinterpret_cast<unsigned*>(smem2), (NC * slot_bytes) / 4, tid);
+    if (tid < kConsThreads)
+      epilogue_records<kConsThreads, 2>(A.ep, A.n, A.p.max_consecutive_successes, ((unsigned)s_rng_step + 1u) & 0xffffu,
+                                        s_epi_warp, &s_epi_base, s_epi_cnt, reinterpret_cast<unsigned*>(smem2),
+                                        (int)(A.smem_bytes / 4), tid);
     return;
   }
 
   // ---- setup ----
-  const uint32_t bar_full = s32(&s_bar[0]), bar_empty = s32(&s_bar[kMaxPairs]);
+  const uint32_t bar_full = s32(&s_bar[0]), bar_empty = s32(&s_bar[kStages]);
   if (tid == 0) {
 #pragma unroll
-    for (int p = 0; p < NC; ++p) {
-      mbar_init(bar_full + 8 * p, 1);
-      mbar_init(bar_empty + 8 * p, 1);
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(bar_full + 8 * s, kProdWarps);
+      mbar_init(bar_empty + 8 * s, kConsWarps);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -1133,16 +1312,13 @@ __global__ void __launch_bounds__(64 * NC, 1) post_physics_v2_kernel(const __gri
   __syncthreads();
   pdl_launch_dependents();
   TL2_DECL;
+  float* const wk_base = reinterpret_cast<float*>(smem2 + kStages * LY::STAGE_BYTES);
+  float* const s_obs = wk_base + LY::W_COUNT * 32;
   const int tiles = A.tiles, workers = A.workers;
-  const int pair = warp < NC ? warp : warp - NC;
-  unsigned char* const stage = smem2 + pair * slot_bytes;
-  float* const s_obs = reinterpret_cast<float*>(stage + LY::STAGE_BYTES);
-  const uint32_t fb = bar_full + 8 * pair, eb = bar_empty + 8 * pair;
-  // tile of (iteration it, CTA b, pair p) = b + workers * (p + NC * it): consecutive tiles go to different SMs
-  const int tile0 = blockIdx.x + workers * pair, tstep = workers * NC;
 
-  if (warp >= NC) {
-    // =========================== producer warp of this pair ===========================
+  if (warp >= kConsWarps) {
+    // =========================== producer warps ===========================
+    const int pw = warp - kConsWarps;
     const int rbo0 = s_rbo[lane], rbo1 = s_rbo[lane + 32], rbo2 = s_rbo[min(lane + 64, kRbW - 1)];
     const bool p_rb0 = lane < 7 || lane >= 13 || A.common;  // hand velocities feed only the common reward terms
     const bool p_rb2 = lane + 64 < kRbW;
@@ -1159,67 +1335,72 @@ __global__ void __launch_bounds__(64 * NC, 1) post_physics_v2_kernel(const __gri
     }
     const float* const x_base = (is_box ? (const float*)A.sim.actor_root_state : A.sim.net_contact_force) + xoff;
     const size_t nb13 = (size_t)A.p.num_bodies * 13;
+    const size_t rb_step = kProdWarps * nb13, x_step = (size_t)kProdWarps * xrow;
     const bool early = (A.flags & DEX_FLAG_EARLY_SIM_LOADS) != 0;
-    const uint32_t sst = s32(stage);
     const int n_grp = A.n_grp, n_grp_early = A.n_grp_early;
-    // bulk copies of the groups [g0, g1): lane r copies row r of each group (group tables are read warp-uniformly)
-    auto issue_groups = [&](const int g0, const int g1, const int tile) {
-      for (int g = g0; g < g1; ++g) {
-        const uint32_t len = (uint32_t)A.grp_len16[g] * 16u;
-        if (lane < (int)A.grp_rows[g])
-          bulk_g2s(sst + (uint32_t)A.grp_dst16[g] * 16u + (uint32_t)lane * len,
-                   reinterpret_cast<const char*>(A.grp_ptr[g]) + (size_t)lane * A.grp_rowb[g] + (size_t)tile * len, len, fb);
-      }
-    };
+    constexpr int R = 32 / kProdWarps;  // env rows per producer warp
     int it = 0;
-    for (int tile = tile0; tile < tiles; tile += tstep, ++it) {
+    for (int tile = blockIdx.x; tile < tiles; tile += workers, ++it) {
+      const int s = it & 1, use = it >> 1;
       const int e0 = tile * 32, ne = min(32, A.n - e0);
+      unsigned char* stage = smem2 + s * LY::STAGE_BYTES;
+      const uint32_t sst = s32(stage), fb = bar_full + 8 * s;
+      // bulk copies of the groups [g0, g1): lane r copies row r of each group (group tables are read warp-uniformly)
+      auto issue_groups = [&](const int g0, const int g1) {
+        for (int g = g0; g < g1; ++g) {
+          const uint32_t len = (uint32_t)A.grp_len16[g] * 16u;
+          if (lane < (int)A.grp_rows[g])
+            bulk_g2s(sst + (uint32_t)A.grp_dst16[g] * 16u + (uint32_t)lane * len,
+                     reinterpret_cast<const char*>(A.grp_ptr[g]) + (size_t)lane * A.grp_rowb[g] + (size_t)tile * len, len, fb);
+        }
+      };
       TL2(it, 16);
-      if (it > 0) mbar_wait(eb, (unsigned)(it - 1) & 1u);
+      if (use > 0) mbar_wait(bar_empty + 8 * s, (unsigned)(use - 1) & 1u);
       TL2(it, 17);
-      const bool bulk = A.bulk_ok && ne == 32;  // warp-uniform
+      const bool bulk = A.bulk_ok && ne == 32;  // CTA-uniform
       const bool split = it == 0 && early;      // first tile: the state rows wait for griddepcontrol.wait, the sim rows do not
       if (it == 0 && !early) pdl_wait();
-      if (bulk) issue_groups(0, split ? n_grp_early : n_grp, tile);
-      // ---- scattered Isaac Gym rows, 16 env rows per batch: consecutive lanes = consecutive floats of a row ----
-      float* aos = reinterpret_cast<float*>(stage + LY::OFF_AOS) + lane;
-      const float* q0 = A.sim.rigid_body_state + (size_t)e0 * nb13;
-      const float* qx = x_base + (size_t)e0 * xrow;
-#pragma unroll 1
-      for (int half = 0; half < 2; ++half) {
-        float v[16][4];
+      if (bulk && pw == 0) issue_groups(0, split ? n_grp_early : n_grp);
+      // ---- scattered Isaac Gym rows: warp pw takes env rows pw, pw+4, ..; consecutive lanes = consecutive floats ----
+      float v[R][4];
+      {
+        const float* q0 = A.sim.rigid_body_state + (size_t)(e0 + pw) * nb13;
+        const float* qx = x_base + (size_t)(e0 + pw) * xrow;
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          if (ne == 32 || 16 * half + i < ne) {
+        for (int i = 0; i < R; ++i) {
+          if (ne == 32 || pw + kProdWarps * i < ne) {
             if (p_rb0) v[i][0] = __ldg(q0 + rbo0);
             v[i][1] = __ldg(q0 + rbo1);
             if (p_rb2) v[i][2] = __ldg(q0 + rbo2);
             if (p_x) v[i][3] = *qx;  // actor_root_state rows are rewritten by the fused reset of this kernel: plain load
           }
-          q0 += nb13;
-          qx += xrow;
-        }
-        if (half == 1 && split) {
-          TL2(it, 18);
-          pdl_wait();  // everything above touched only kernel parameters and the sim tensors
-          if (bulk) issue_groups(n_grp_early, n_grp, tile);
-        }
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          if (ne == 32 || 16 * half + i < ne) {
-            if (p_rb0) aos[LY::A_RB] = v[i][0];
-            aos[LY::A_RB + 32] = v[i][1];
-            if (p_rb2) aos[LY::A_RB + 64] = v[i][2];
-            if (p_x) aos[LY::A_CF] = v[i][3];
-          }
-          aos += LY::SA;
+          q0 += rb_step;
+          qx += x_step;
         }
       }
-      if (!bulk) prod_rows_ldg(A, stage, e0, ne, lane);
+      TL2(it, 18);
+      if (split) {
+        pdl_wait();  // everything above touched only kernel parameters and the sim tensors
+        if (bulk && pw == 0) issue_groups(n_grp_early, n_grp);
+      }
+      if (!bulk) prod_rows_ldg(A, stage, e0, ne, pw, lane);
+      {
+        float* a = reinterpret_cast<float*>(stage + LY::OFF_AOS) + pw * LY::SA + lane;
+#pragma unroll
+        for (int i = 0; i < R; ++i) {
+          if (ne == 32 || pw + kProdWarps * i < ne) {
+            if (p_rb0) a[LY::A_RB] = v[i][0];
+            a[LY::A_RB + 32] = v[i][1];
+            if (p_rb2) a[LY::A_RB + 64] = v[i][2];
+            if (p_x) a[LY::A_CF] = v[i][3];
+          }
+          a += kProdWarps * LY::SA;
+        }
+      }
       __syncwarp();
       TL2(it, 19);
       if (lane == 0) {
-        if (bulk)
+        if (pw == 0 && bulk)
           mbar_arrive_tx(fb, A.tx_bytes);
         else
           mbar_arrive(fb);
@@ -1228,95 +1409,75 @@ __global__ void __launch_bounds__(64 * NC, 1) post_physics_v2_kernel(const __gri
     return;
   }
 
-  // =========================== compute warp of this pair ===========================
+  // =========================== consumer warps ===========================
   Cx<BG, STD> c;
   c.lane = lane;
   c.N = (size_t)A.n;
+  c.wk = wk_base + lane;
   c.obs = s_obs + lane * A.wp;
-  c.stage = stage;
   c.obs_offset = A.p.obs_offset;
   c.dof2afj = A.dof2afj;
   unsigned stamp = 0;
   uint64_t rng_step = 0;
-  const int W = A.p.obs_dim, WP = A.wp;
+  bool store_pending = false;
   int it = 0;
-  for (int tile = tile0; tile < tiles; tile += tstep, ++it) {
+  for (int tile = blockIdx.x; tile < tiles; tile += workers, ++it) {
+    const int s = it & 1, use = it >> 1;
     c.e0 = tile * 32;
     c.ne = min(32, A.n - c.e0);
     c.act = lane < c.ne;
     c.env = (size_t)c.e0 + (c.act ? lane : 0);
+    c.stage = smem2 + s * LY::STAGE_BYTES;
     TL2(it, 0);
-    mbar_wait(fb, (unsigned)it & 1u);
+    mbar_wait(bar_full + 8 * s, (unsigned)use & 1u);
     TL2(it, 1);
-    if (it == 0) {
-      // Philox step counter == stamp of this step's tile records: read behind the first full barrier (i.e. behind the
-      // producer's griddepcontrol.wait; the epilogue CTA advances it only after every record of this launch is out)
-      unsigned long long rs = 0ull;
-      if (lane == 0) rs = A.st.rng_step ? *reinterpret_cast<const volatile unsigned long long*>(A.st.rng_step) : A.step;
-      rng_step = __shfl_sync(0xffffffffu, rs, 0);
-      stamp = ((unsigned)rng_step + 1u) & 0xffffu;
-    }
-    unsigned rbits;
-    float* const g_obs = A.out.obs_buf + (size_t)c.e0 * W;
-    if (c.ne == 32) {  // warp-uniform
-      rbits = tile_program<BG, STD, true>(A, c, stamp);
-      TL2(it, 4);
-      __syncwarp();  // the raw stage is not read after this point: hand it back to the producer
-      if (lane == 0) mbar_arrive(eb);
-      copy_obs<true>(s_obs, g_obs, W, WP, 32, lane);
-    } else {
-      rbits = tile_program<BG, false, false>(A, reinterpret_cast<Cx<BG, false>&>(c), stamp);
-      TL2(it, 4);
-      __syncwarp();
-      if (lane == 0) mbar_arrive(eb);
-      copy_obs<false>(s_obs, g_obs, W, WP, c.ne, lane);
-    }
-    TL2(it, 5);
-    // ---- fused reset of the finished envs (dexhand_base.py:743-756) ----
-    if (rbits && !(A.flags & DEX_FLAG_NO_FUSED_RESET)) {
-      unsigned mask = rbits;
-      while (mask) {
-        const int e = __ffs(mask) - 1;
-        mask &= mask - 1;
-        reset_env_warp<BG>(A, c.e0 + e, rng_step, s_reset_u + 32 * pair);
-      }
-    }
-    __syncwarp();  // the obs tile is rewritten by the next tile
+    if (c.ne == 32)  // CTA-uniform
+      consume_tile<BG, STD, true>(A, c, warp, it, 0u, &s_rng_step, &s_rbits, stamp, rng_step, bar_empty + 8 * s, s_obs, s_reset_u,
+                                  store_pending TL2_ARG);
+    else
+      consume_tile<BG, false, false>(A, reinterpret_cast<Cx<BG, false>&>(c), warp, it, 0u, &s_rng_step, &s_rbits, stamp, rng_step,
+                                     bar_empty + 8 * s, s_obs, s_reset_u, store_pending TL2_ARG);
     TL2(it, 6);
   }
+  if (store_pending) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // the last obs tile has left shared memory
 }
 
-template <bool BG, int NC, bool STD>
+template <bool BG, bool STD>
 int launch_post2_k(Post2Args& a, cudaStream_t s) {
-  static int num_sms = 0;
-  static size_t smem_cfg = 0;
+  static int ctas_per_sm = -1, num_sms = 0;
+  static size_t smem_cfg = 0, smem_occ = 0;
   if (a.smem_bytes > smem_cfg) {
-    const cudaError_t e =
-        cudaFuncSetAttribute(post_physics_v2_kernel<BG, NC, STD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a.smem_bytes);
+    const size_t want = a.smem_bytes > 100 * 1024 ? a.smem_bytes : 100 * 1024;
+    const cudaError_t e = cudaFuncSetAttribute(post_physics_v2_kernel<BG, STD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)want);
     if (e != cudaSuccess) return (int)e;
-    smem_cfg = a.smem_bytes;
-    int dev = 0;
+    smem_cfg = want;
+    ctas_per_sm = -1;
+  }
+  if (ctas_per_sm < 0 || smem_occ != a.smem_bytes) {
+    int dev = 0, occ = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
+    const cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, post_physics_v2_kernel<BG, STD>, kThreads, a.smem_bytes);
+    if (e != cudaSuccess) return (int)e;
+    if (occ < 1) return DEX_ERR_SIZE;
+    ctas_per_sm = occ;
+    smem_occ = a.smem_bytes;
   }
   const int fused = a.fused_epilogue ? 1 : 0;
-  // one CTA per SM; every CTA of the launch (workers + epilogue) is resident at once; tiles spread over all of them
-  const int cap = num_sms - fused > 1 ? num_sms - fused : 1;
+  int cap = num_sms * ctas_per_sm - fused;  // every CTA of the launch (workers + epilogue) is resident at once
+  if (cap < 1) cap = 1;
   a.workers = a.tiles < cap ? a.tiles : cap;
-  const cudaError_t e = launch_step_kernel(post_physics_v2_kernel<BG, NC, STD>, a.workers + fused, 64 * NC, a.smem_bytes, s, a);
+  const cudaError_t e = launch_step_kernel(post_physics_v2_kernel<BG, STD>, a.workers + fused, kThreads, a.smem_bytes, s, a);
   if (e != cudaSuccess) (void)cudaGetLastError();
   return e == cudaSuccess ? DEX_OK : (int)e;
 }
 
-template <bool BG, int NC>
+template <bool BG>
 int launch_post2_t(Post2Args& a, cudaStream_t s) {
-  using LY = Lay<BG>;
   const int rc = build_post2<BG>(a);
   if (rc) return rc;
-  a.nc = NC;
-  a.smem_bytes = (uint32_t)(NC * (LY::STAGE_BYTES + 32 * a.wp * 4));
   if (a.smem_bytes > 227 * 1024 - 2048) return DEX_ERR_SIZE;
-  return std_layout_matches<BG>(a) ? launch_post2_k<BG, NC, true>(a, s) : launch_post2_k<BG, NC, false>(a, s);
+  return std_layout_matches<BG>(a) ? launch_post2_k<BG, true>(a, s) : launch_post2_k<BG, false>(a, s);
 }
 
 }  // namespace pp2

@@ -71,10 +71,10 @@ t = runs[0]
 used = (t[:, 0, 0] > 0)
 print(f"envs {n} task {task}: {int(used.sum())} worker CTAs; tiles per CTA: "
       f"{ {k: int(((t[:, :, 1] > 0).sum(dim=1) == k).sum()) for k in range(1, ITERS + 1) if int(((t[:, :, 1] > 0).sum(dim=1) == k).sum())} }")
-cons = [((0, 1), "wait full (load latency seen by the compute warp)"), ((1, 2), "per-env parts (poses, contacts, hand, DOFs, FSM)"),
-        ((2, 3), "termination + ballots + record"), ((3, 4), "reward terms + total"), ((4, 5), "obs tile -> obs_buf"),
-        ((5, 6), "reset"), ((0, 6), "whole tile (compute warp)")]
-prod = [((16, 17), "producer: wait empty"), ((17, 19), "producer: bulk issue + gather + STS + arrive")]
+cons = [((0, 1), "wait full (load latency seen by the consumers)"), ((1, 2), "phase A: per-warp jobs (warp 0: tips)"),
+        ((2, 3), "  barrier A"), ((3, 4), "phase C: warp 0 task state + termination + record"), ((4, 5), "  barrier C"),
+        ((5, 7), "phase D: total, obs store issue, reset (warp 0)"), ((7, 6), "  barrier D"), ((0, 6), "whole tile (consumer)")]
+prod = [((16, 17), "producer: wait empty"), ((17, 18), "producer: bulk issue + gather issue"), ((18, 19), "producer: data wait + STS + arrive")]
 for it in range(ITERS):
     if not any(bool((r[:, it, 1] > 0).any()) for r in runs):
         break
