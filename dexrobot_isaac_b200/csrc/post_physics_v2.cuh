@@ -135,19 +135,14 @@ struct Post2Args {
   int32_t tiles, workers;
   int32_t common, first, want_tgt;
   int32_t bulk_ok, n_bulk, n_bulk_early;  // entries [0, n_bulk_early) touch sim tensors only
-  uint32_t tx_bytes;                      // bytes of all bulk entries of a full tile
+  int32_t n_tile_entries;                 // entries [0, n_tile_entries) are whole AoS tiles (bulk copies), the rest SoA rows
+  uint32_t tx_bytes;                      // bytes of the bulk-copied AoS tiles of a full tile
   int32_t wp;                             // obs tile row stride in floats
   int32_t obs_bulk;                       // 1: the obs tile of a full tile is flat ([32][obs_dim]) and leaves with ONE bulk store
   uint32_t obs_late;                      // bit c: obs columns [32c, 32c+32) hold a value that phase B writes
   uint32_t smem_bytes;
   int32_t rb_off[11], cf_off[6];
   int32_t dof2afj[DEX_NUM_DOF];           // dof -> index in active_finger_dof, -1 = not an active finger DOF
-  // the same rows as GROUPS (one per state buffer): lane r of the producer warp copies row r of the group, every
-  // table read is warp-uniform (a lane-indexed read of the parameter bank would serialise 32-way)
-  int32_t n_grp, n_grp_early;
-  uint64_t grp_ptr[16];                   // global base of the buffer
-  uint32_t grp_rowb[16];                  // bytes between consecutive rows of the buffer (N * elem)
-  uint16_t grp_rows[16], grp_dst16[16], grp_len16[16];  // rows (<= 32), stage offset of row 0 / 16, bytes per row and tile / 16
   uint64_t bk_ptr[kMaxBulk];              // global base of the row / tile array
   uint16_t bk_dst16[kMaxBulk];            // byte offset inside the stage / 16
   uint16_t bk_len16[kMaxBulk];            // bytes per full tile / 16 (== source stride per tile)
@@ -203,58 +198,28 @@ inline int build_post2(Post2Args& a) {
   for (int d = 0; d < DEX_NUM_DOF; ++d) a.dof2afj[d] = -1;
   for (int j = 0; j < DEX_NUM_ACTIVE_FINGER; ++j) a.dof2afj[P.active_finger_dof[j]] = j;
 
-  int k = 0, g = 0;
-  bool aligned = (a.n % 16) == 0;
+  int k = 0;
+  bool aligned = true;  // the AoS tiles: base 16-byte aligned (tile offsets are multiples of 16 for any N)
   uint32_t tx = 0;
-  auto grp = [&](const void* base, int rows, int elem, int dst, int kind) {  // rows of one buffer = one group
-    if (g >= 16 || rows > 32) return;
-    const int len = kind == BK_DOF ? 32 * 52 * 4 : kind == BK_TGT ? 32 * 26 * 4 : 32 * elem;
-    a.grp_ptr[g] = (uint64_t)(uintptr_t)base;
-    a.grp_rowb[g] = (uint32_t)(N * elem);
-    a.grp_rows[g] = (uint16_t)rows;
-    a.grp_dst16[g] = (uint16_t)(dst / 16);
-    a.grp_len16[g] = (uint16_t)(len / 16);
-    ++g;
-  };
   auto add = [&](const void* base, size_t row, int elem, int dst, int kind) {
     if (k >= kMaxBulk) return;
     const uintptr_t ptr = (uintptr_t)((const char*)base + row * N * elem);
     const int len = kind == BK_DOF ? 32 * 52 * 4 : kind == BK_TGT ? 32 * 26 * 4 : 32 * elem;
-    if (ptr & 15u) aligned = false;
+    if ((kind == BK_DOF || kind == BK_TGT) && (ptr & 15u)) aligned = false;
     a.bk_ptr[k] = (uint64_t)ptr;
     a.bk_dst16[k] = (uint16_t)(dst / 16);
     a.bk_len16[k] = (uint16_t)(len / 16);
     a.bk_kind[k] = (uint8_t)kind;
-    tx += (uint32_t)len;
+    if (kind == BK_DOF || kind == BK_TGT) tx += (uint32_t)len;
     ++k;
   };
   add(a.sim.dof_state, 0, 4, LY::OFF_DOF, BK_DOF);
-  grp(a.sim.dof_state, 1, 4, LY::OFF_DOF, BK_DOF);
   a.n_bulk_early = k;
-  a.n_grp_early = g;
-  if (!BG && a.want_tgt) {
-    add(st.full_dof_targets, 0, 4, LY::OFF_TGT, BK_TGT);
-    grp(st.full_dof_targets, 1, 4, LY::OFF_TGT, BK_TGT);
-  }
-  grp(st.prev_dof_pos, DEX_NUM_DOF, 4, LY::R_PDP * 128, BK_F32);
-  grp(st.active_prev_targets, DEX_NUM_ACTIVE, 4, LY::R_APT * 128, BK_F32);
-  grp(st.prev_actions, P.num_actions, 4, LY::R_PACT * 128, BK_F32);
-  grp(st.contact_duration_steps, DEX_NUM_FINGERS, 4, LY::R_CDUR * 128, BK_F32);
-  grp(st.prev_contact_binary, DEX_NUM_FINGERS, 4, LY::R_PBIN * 128, BK_F32);
-  grp(st.episode_step_count, 1, 8, LY::OFF_I64 + LY::I_STEP * 256, BK_I64);
+  if (!BG && a.want_tgt) add(st.full_dof_targets, 0, 4, LY::OFF_TGT, BK_TGT);
+  a.n_tile_entries = k;
   if (BG) {
-    grp(st.initial_box_positions, 3, 4, LY::R_BOX0 * 128, BK_F32);
-    grp(st.time_in_stage, 1, 4, LY::R_TIS * 128, BK_F32);
-    grp(st.stage_contact_duration, 1, 4, LY::R_SCD * 128, BK_F32);
-    grp(st.success_duration_steps, 1, 8, LY::OFF_I64 + LY::I_SDS * 256, BK_I64);
-    grp(st.current_stage, 1, 8, LY::OFF_I64 + LY::I_STAGE * 256, BK_I64);
   } else if (a.common && !a.first) {
-    grp(st.prev_finger_dof_vel, DEX_NUM_FINGER_DOF, 4, LY::R_PFDV * 128, BK_F32);
-    grp(st.prev_hand_vel, 3, 4, LY::R_PHV * 128, BK_F32);
-    grp(st.prev_hand_ang_vel, 3, 4, LY::R_PHA * 128, BK_F32);
-    grp(st.prev_contacts, DEX_NUM_FINGERS, 1, LY::OFF_U8, BK_U8);
   }
-  a.n_grp = g;
   for (int d = 0; d < DEX_NUM_DOF; ++d) add(st.prev_dof_pos, d, 4, (LY::R_PDP + d) * 128, BK_F32);
   for (int i = 0; i < DEX_NUM_ACTIVE; ++i) add(st.active_prev_targets, i, 4, (LY::R_APT + i) * 128, BK_F32);
   for (int i = 0; i < P.num_actions; ++i) add(st.prev_actions, i, 4, (LY::R_PACT + i) * 128, BK_F32);
@@ -273,7 +238,7 @@ inline int build_post2(Post2Args& a) {
     for (int c = 0; c < 3; ++c) add(st.prev_hand_ang_vel, c, 4, (LY::R_PHA + c) * 128, BK_F32);
     for (int f = 0; f < DEX_NUM_FINGERS; ++f) add(st.prev_contacts, f, 1, LY::OFF_U8 + f * 32, BK_U8);
   }
-  if (k >= kMaxBulk || g >= 16) return DEX_ERR_SIZE;
+  if (k >= kMaxBulk) return DEX_ERR_SIZE;
   a.n_bulk = k;
   a.tx_bytes = tx;
   a.bulk_ok = aligned ? 1 : 0;
@@ -369,6 +334,18 @@ __device__ __forceinline__ void bulk_g2s(const uint32_t dst, const void* src, co
                "r"(bytes), "r"(bar)
                : "memory");
 }
+// Ampere-style asynchronous copies (SASS LDGSTS): global -> shared without a register in between; their completion is
+// tied to the stage's mbarrier by cp.async.mbarrier.arrive.noinc (one counted arrival per producer thread and tile)
+__device__ __forceinline__ void cpa4(const uint32_t dst, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cpa8(const uint32_t dst, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cpa_arrive(const uint32_t bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+}
+
 __device__ __forceinline__ void obs_put(float* obs, const int off, const int j, const float v) {
   if (off >= 0) obs[off + j] = v;
 }
@@ -376,54 +353,6 @@ __device__ __forceinline__ void obs_put(float* obs, const int off, const int j, 
 // ------------------------------------------------------------------------------------------------
 // producer side: one producer warp fills the slot of its compute warp
 // ------------------------------------------------------------------------------------------------
-// generic path (ragged tile, or row bases / N that are not 16-byte friendly): every row with plain loads
-__device__ __forceinline__ void prod_rows_ldg(const Post2Args& A, unsigned char* stage, const int e0, const int ne, const int pw,
-                                              const int lane) {
-  const bool act = lane < ne;
-  for (int k0 = pw; k0 < A.n_bulk; k0 += 8 * kProdWarps) {
-    unsigned long long v[8];
-#pragma unroll
-    for (int u = 0; u < 8; ++u) {
-      const int k = k0 + kProdWarps * u;
-      v[u] = 0ull;
-      if (k < A.n_bulk) {
-        const int kind = A.bk_kind[k];
-        const char* src = reinterpret_cast<const char*>(A.bk_ptr[k]);
-        if (kind == BK_F32) {
-          if (act) v[u] = __float_as_uint(*reinterpret_cast<const float*>(src + ((size_t)e0 + lane) * 4));
-        } else if (kind == BK_I64) {
-          if (act) v[u] = *reinterpret_cast<const unsigned long long*>(src + ((size_t)e0 + lane) * 8);
-        } else if (kind == BK_U8) {
-          if (act) v[u] = *reinterpret_cast<const unsigned char*>(src + ((size_t)e0 + lane));
-        }
-      }
-    }
-#pragma unroll
-    for (int u = 0; u < 8; ++u) {
-      const int k = k0 + kProdWarps * u;
-      if (k < A.n_bulk && act) {
-        const int kind = A.bk_kind[k];
-        unsigned char* dst = stage + (size_t)A.bk_dst16[k] * 16;
-        if (kind == BK_F32)
-          reinterpret_cast<unsigned*>(dst)[lane] = (unsigned)v[u];
-        else if (kind == BK_I64)
-          reinterpret_cast<unsigned long long*>(dst)[lane] = v[u];
-        else if (kind == BK_U8)
-          dst[lane] = (unsigned char)v[u];
-      }
-    }
-  }
-  // the two AoS tiles are contiguous: flat copies
-  for (int k = 0; k < A.n_bulk; ++k) {
-    const int kind = A.bk_kind[k];
-    if (kind != BK_DOF && kind != BK_TGT) continue;
-    const int per = kind == BK_DOF ? 52 : 26;
-    const float* src = reinterpret_cast<const float*>(A.bk_ptr[k]) + (size_t)e0 * per;
-    float* dst = reinterpret_cast<float*>(stage + (size_t)A.bk_dst16[k] * 16);
-    for (int i = pw * 32 + lane; i < ne * per; i += kProdThreads) dst[i] = src[i];
-  }
-}
-
 // ------------------------------------------------------------------------------------------------
 // compute side: ONE warp runs the whole per-env program for its tile, lane = env.  Every compute warp of the SM
 // executes the same straight-line instruction stream (instruction fetch is shared, no intra-tile barrier exists),
@@ -1298,7 +1227,7 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
   if (tid == 0) {
 #pragma unroll
     for (int s = 0; s < kStages; ++s) {
-      mbar_init(bar_full + 8 * s, kProdWarps);
+      mbar_init(bar_full + 8 * s, kProdThreads + kProdWarps);  // one cp.async-completion arrival per producer thread + one per warp
       mbar_init(bar_empty + 8 * s, kConsWarps);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -1337,7 +1266,7 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
     const size_t nb13 = (size_t)A.p.num_bodies * 13;
     const size_t rb_step = kProdWarps * nb13, x_step = (size_t)kProdWarps * xrow;
     const bool early = (A.flags & DEX_FLAG_EARLY_SIM_LOADS) != 0;
-    const int n_grp = A.n_grp, n_grp_early = A.n_grp_early;
+    const int n_rows = A.n_bulk;
     constexpr int R = 32 / kProdWarps;  // env rows per producer warp
     int it = 0;
     for (int tile = blockIdx.x; tile < tiles; tile += workers, ++it) {
@@ -1345,58 +1274,70 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
       const int e0 = tile * 32, ne = min(32, A.n - e0);
       unsigned char* stage = smem2 + s * LY::STAGE_BYTES;
       const uint32_t sst = s32(stage), fb = bar_full + 8 * s;
-      // bulk copies of the groups [g0, g1): lane r copies row r of each group (group tables are read warp-uniformly)
-      auto issue_groups = [&](const int g0, const int g1) {
-        for (int g = g0; g < g1; ++g) {
-          const uint32_t len = (uint32_t)A.grp_len16[g] * 16u;
-          if (lane < (int)A.grp_rows[g])
-            bulk_g2s(sst + (uint32_t)A.grp_dst16[g] * 16u + (uint32_t)lane * len,
-                     reinterpret_cast<const char*>(A.grp_ptr[g]) + (size_t)lane * A.grp_rowb[g] + (size_t)tile * len, len, fb);
-        }
-      };
       TL2(it, 16);
       if (use > 0) mbar_wait(bar_empty + 8 * s, (unsigned)(use - 1) & 1u);
       TL2(it, 17);
-      const bool bulk = A.bulk_ok && ne == 32;  // CTA-uniform
+      const bool full = ne == 32;               // CTA-uniform
+      const bool bulk = A.bulk_ok && full;      // the two AoS tiles (dof_state, full_dof_targets) as bulk copies
       const bool split = it == 0 && early;      // first tile: the state rows wait for griddepcontrol.wait, the sim rows do not
+      const bool act = lane < ne;
       if (it == 0 && !early) pdl_wait();
-      if (bulk && pw == 0) issue_groups(0, split ? n_grp_early : n_grp);
+      // table entry k: [0, n_bulk_early) sim-tensor tiles (dof_state) | state tiles (full_dof_targets) | state rows
+      auto issue_tiles = [&](const int k0, const int k1) {
+        for (int k = k0; k < k1; ++k) {
+          const int kind = A.bk_kind[k];
+          if (kind != BK_DOF && kind != BK_TGT) break;
+          const uint32_t len = (uint32_t)A.bk_len16[k] * 16u;
+          const char* src = reinterpret_cast<const char*>(A.bk_ptr[k]) + (size_t)tile * len;
+          const uint32_t dst = sst + (uint32_t)A.bk_dst16[k] * 16u;
+          if (bulk) {
+            if (pw == 0 && lane == 0) bulk_g2s(dst, src, len, fb);
+          } else {  // ragged tile / unaligned base: 4-byte asynchronous copies of the contiguous block
+            const int nfl = ne * (kind == BK_DOF ? 52 : 26);
+            for (int i = pw * 32 + lane; i < nfl; i += kProdThreads) cpa4(dst + 4u * i, src + 4 * i);
+          }
+        }
+      };
+      issue_tiles(0, A.n_bulk_early);
       // ---- scattered Isaac Gym rows: warp pw takes env rows pw, pw+4, ..; consecutive lanes = consecutive floats ----
-      float v[R][4];
       {
         const float* q0 = A.sim.rigid_body_state + (size_t)(e0 + pw) * nb13;
         const float* qx = x_base + (size_t)(e0 + pw) * xrow;
+        uint32_t a = sst + LY::OFF_AOS + (uint32_t)(pw * LY::SA + lane) * 4u;
 #pragma unroll
         for (int i = 0; i < R; ++i) {
-          if (ne == 32 || pw + kProdWarps * i < ne) {
-            if (p_rb0) v[i][0] = __ldg(q0 + rbo0);
-            v[i][1] = __ldg(q0 + rbo1);
-            if (p_rb2) v[i][2] = __ldg(q0 + rbo2);
-            if (p_x) v[i][3] = *qx;  // actor_root_state rows are rewritten by the fused reset of this kernel: plain load
+          if (full || pw + kProdWarps * i < ne) {
+            if (p_rb0) cpa4(a + LY::A_RB * 4, q0 + rbo0);
+            cpa4(a + (LY::A_RB + 32) * 4, q0 + rbo1);
+            if (p_rb2) cpa4(a + (LY::A_RB + 64) * 4, q0 + rbo2);
+            if (p_x) cpa4(a + LY::A_CF * 4, qx);
           }
           q0 += rb_step;
           qx += x_step;
+          a += kProdWarps * LY::SA * 4;
         }
       }
       TL2(it, 18);
-      if (split) {
-        pdl_wait();  // everything above touched only kernel parameters and the sim tensors
-        if (bulk && pw == 0) issue_groups(n_grp_early, n_grp);
-      }
-      if (!bulk) prod_rows_ldg(A, stage, e0, ne, pw, lane);
-      {
-        float* a = reinterpret_cast<float*>(stage + LY::OFF_AOS) + pw * LY::SA + lane;
-#pragma unroll
-        for (int i = 0; i < R; ++i) {
-          if (ne == 32 || pw + kProdWarps * i < ne) {
-            if (p_rb0) a[LY::A_RB] = v[i][0];
-            a[LY::A_RB + 32] = v[i][1];
-            if (p_rb2) a[LY::A_RB + 64] = v[i][2];
-            if (p_x) a[LY::A_CF] = v[i][3];
+      if (split) pdl_wait();  // everything above touched only kernel parameters and the sim tensors
+      issue_tiles(A.n_bulk_early, n_rows);
+      // ---- SoA state rows: lane = env, one 128-byte line per row; row k of the table goes to warp k % 4 ----
+      for (int k = A.n_tile_entries + pw; k < n_rows; k += kProdWarps) {
+        const int kind = A.bk_kind[k];
+        const char* src = reinterpret_cast<const char*>(A.bk_ptr[k]);
+        const uint32_t dst = sst + (uint32_t)A.bk_dst16[k] * 16u;
+        if (kind == BK_F32) {
+          if (act) cpa4(dst + 4u * lane, src + ((size_t)e0 + lane) * 4);
+        } else if (kind == BK_I64) {
+          if (act) cpa8(dst + 8u * lane, src + ((size_t)e0 + lane) * 8);
+        } else {  // BK_U8: 32 bytes of a bool row
+          if (full && (A.n & 3) == 0) {
+            if (lane < 8) cpa4(dst + 4u * lane, src + (size_t)e0 + 4 * lane);
+          } else if (act) {
+            stage[(size_t)A.bk_dst16[k] * 16 + lane] = *reinterpret_cast<const unsigned char*>(src + (size_t)e0 + lane);
           }
-          a += kProdWarps * LY::SA;
         }
       }
+      cpa_arrive(fb);  // counted arrival when every asynchronous copy of this thread has landed
       __syncwarp();
       TL2(it, 19);
       if (lane == 0) {
