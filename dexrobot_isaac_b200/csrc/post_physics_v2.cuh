@@ -51,14 +51,16 @@ struct Lay {
   static constexpr int A_RB = 0, A_CF = 83, A_BOX = 101;     // hand row 13 | 5 tips x 7 | 5 pads x 7 ; contacts ; box
   static constexpr int SA = BG ? 107 : 99;
   static constexpr int STAGE_BYTES = (OFF_AOS + 32 * SA * 4 + 127) / 128 * 128;
-  // work block: values that cross a warp, [field][32] floats (lane = env: conflict-free)
-  static constexpr int W_BIN = 0, W_PADBOX = 5;  // 5 each
-  static constexpr int W_CDIST = 10, W_DRIFT = 11, W_VMAG = 12, W_AVGHDIFF = 13, W_MINTIPBOX = 14, W_MINTIPZ = 15;
-  static constexpr int W_BVEL = 16;              // 6: finite-difference base velocity
-  static constexpr int W_BOXHAS = 22, W_SOK = 23, W_BOXFAR = 24, W_HITG = 25, W_HCOK = 26;
-  static constexpr int W_WGT = 27;               // 26 weighted reward terms
-  static constexpr int W_CHG = 53, W_RHAND = 54, W_FV2 = 58, W_FA2 = 78, W_JL = 98;  // BaseTask (common rewards)
-  static constexpr int W_COUNT = BG ? 53 : 118;
+  // work block: values that cross a warp or a phase, [field][32] floats (lane = env: conflict-free)
+  static constexpr int W_BIN = 0, W_PADBOX = 5, W_HDIFF = 10, W_TIPBOX = 15;
+  static constexpr int W_CDIST = 20, W_DRIFT = 21, W_VMAG = 22, W_BOXHAS = 23, W_HANDBOX = 24;
+  static constexpr int W_BVEL = 25;  // 6
+  static constexpr int W_GRASP = 31, W_THUMB = 32, W_OTHERS = 33, W_GRASPDUR = 34, W_SDS = 35, W_STAGE = 36, W_J2 = 37,
+                       W_J3 = 38;
+  static constexpr int W_HITG = 39, W_BOXFAR = 40, W_QUALOK = 41, W_MINTIPBOX = 42, W_AVGHDIFF = 43;
+  static constexpr int W_CHG = 44, W_RHAND = 49, W_FV2 = 53, W_FA2 = 73, W_JL = 93;  // BaseTask (common rewards)
+  static constexpr int W_WGT = BG ? 44 : 113;  // 26 weighted reward terms
+  static constexpr int W_COUNT = W_WGT + DEX_NUM_REWARD_TERMS;
 };
 
 
@@ -183,9 +185,10 @@ inline int build_post2(Post2Args& a) {
   a.wp = a.obs_bulk ? P.obs_dim : (P.obs_dim | 1);
   a.obs_late = 0;
   {
-    const int late_keys[7] = {DEX_K_THUMB_CONTACT, DEX_K_OTHER_FINGERS_CONTACT, DEX_K_GRASP_STATE, DEX_K_GRASP_DURATION,
-                              DEX_K_CURRENT_STAGE, DEX_K_TIME_IN_STAGE, DEX_K_STAGE_PROGRESS};
-    for (int i = 0; i < 7; ++i)
+    const int late_keys[10] = {DEX_K_THUMB_CONTACT, DEX_K_OTHER_FINGERS_CONTACT, DEX_K_GRASP_STATE, DEX_K_GRASP_DURATION,
+                               DEX_K_CURRENT_STAGE, DEX_K_TIME_IN_STAGE, DEX_K_STAGE_PROGRESS, DEX_K_AVG_FINGER_TO_OBJECT_DISTANCE,
+                               DEX_K_AVG_FINGER_TO_OBJECT_HEIGHT_DIFF, DEX_K_EPISODE_TIME};
+    for (int i = 0; i < 10; ++i)
       if (BG && has(late_keys[i])) a.obs_late |= 1u << (P.obs_offset[late_keys[i]] >> 5);
   }
   a.rb_off[0] = P.hand_body * 13;
@@ -354,19 +357,16 @@ __device__ __forceinline__ void obs_put(float* obs, const int off, const int j, 
 // producer side: one producer warp fills the slot of its compute warp
 // ------------------------------------------------------------------------------------------------
 // ------------------------------------------------------------------------------------------------
-// compute side: ONE warp runs the whole per-env program for its tile, lane = env.  Every compute warp of the SM
-// executes the same straight-line instruction stream (instruction fetch is shared, no intra-tile barrier exists),
-// intermediates stay in registers, and the compiler schedules the independent chains (5 fingers, 26 DOFs, 10 pad
-// pairs, 16 reward terms) of one env side by side.
+// consumer phases (lane = env)
 // ------------------------------------------------------------------------------------------------
 template <bool BG, bool STD>
 struct Cx {
   const unsigned char* stage;
-  float* obs;  // obs tile row of this lane's env
   float* wk;   // work block + lane
+  float* obs;  // obs tile row of this lane's env
   const int32_t* obs_offset;  // generic instance: DexParams.obs_offset
   const int32_t* dof2afj;
-  int lane, e0, ne;
+  int lane, cw, e0, ne;
   bool act;
   size_t N, env;
   __device__ __forceinline__ int off(const int k) const {
@@ -386,401 +386,345 @@ struct Cx {
   }
 };
 
-// values that flow between the parts of the per-env program (registers)
-struct Mid {
-  float bin[DEX_NUM_FINGERS], padbox[DEX_NUM_FINGERS];
-  float cdist, drift, vmag, min_tip_box, avg_hdiff, graspdur;
-  float bvel[DEX_NUM_BASE];
-  bool boxhas, boxfar, hitg, hcok, sok, grasp, thumb, others, j2, j3;
-  int sds, stage;
-  float fv2, fa2, jl, chg, rhand[4], min_tip_z;  // BaseTask: ordered partial sums of the common reward terms
-  float wgt[DEX_NUM_REWARD_TERMS];
-};
-
-// ---- the five tip (or pad) poses: world columns, hand-frame columns (observation_encoder.py:915-986) and, for
-//      BlindGrasping, the box distances (blind_grasping_task.py:684-771, 1178-1192, 1334-1364)
-template <bool BG, bool STD, bool PAD>
-__device__ __forceinline__ void part_poses(const Post2Args& A, const Cx<BG, STD>& c, Mid& m) {
+// phase A: per-env work items, taken round-robin by the 8 consumer warps (item type is warp-uniform)
+template <bool BG, bool STD>
+__device__ __forceinline__ void phase_items(const Post2Args& A, const Cx<BG, STD>& c) {
   using LY = Lay<BG>;
+  if (!c.act) return;
   const DexParams& P = A.p;
+  const DexStateBuffers& st = A.st;
+  const float dt = P.control_dt;
   const float* aos = c.aos();
+  const float* soa = c.soa();
   const float* rb = aos + LY::A_RB;
+  float* wk = c.wk;
   float* obs = c.obs;
-  float p[DEX_NUM_FINGERS][7];
-#pragma unroll
-  for (int f = 0; f < DEX_NUM_FINGERS; ++f)
-#pragma unroll
-    for (int j = 0; j < 7; ++j) p[f][j] = rb[13 + (PAD ? 35 : 0) + 7 * f + j];
-  const int ow = c.off(PAD ? DEX_K_FINGERPAD_POSES_WORLD : DEX_K_FINGERTIP_POSES_WORLD);
-  if (ow >= 0) {
-#pragma unroll
-    for (int f = 0; f < DEX_NUM_FINGERS; ++f)
-#pragma unroll
-      for (int j = 0; j < 7; ++j) obs[ow + 7 * f + j] = p[f][j];
-  }
-  const int oh = c.off(PAD ? DEX_K_FINGERPAD_POSES_HAND : DEX_K_FINGERTIP_POSES_HAND);
-  if (oh >= 0) {
-    const Quat hq{rb[3], rb[4], rb[5], rb[6]};
-    const float hx = rb[0], hy = rb[1], hz = rb[2];
-#pragma unroll
-    for (int f = 0; f < DEX_NUM_FINGERS; ++f) {
-      const Vec3 ph = quat_rotate_inverse(hq, Vec3{p[f][0] - hx, p[f][1] - hy, p[f][2] - hz});
-      const Quat qh = quat_mul(quat_conj(hq), Quat{p[f][3], p[f][4], p[f][5], p[f][6]});
-      float* o = obs + oh + 7 * f;
-      o[0] = ph.x;
-      o[1] = ph.y;
-      o[2] = ph.z;
-      o[3] = qh.x;
-      o[4] = qh.y;
-      o[5] = qh.z;
-      o[6] = qh.w;
-    }
-  }
-  if (!PAD) {
-    // hitting_ground inputs (step_processor.py:133-181): min over the tips in finger order
-    float mz = p[0][2];
-#pragma unroll
-    for (int f = 1; f < DEX_NUM_FINGERS; ++f) mz = fminf(mz, p[f][2]);
-    m.min_tip_z = mz;
-    m.hitg = P.has_height_safety && ((rb[2] < P.handbase_threshold) || (mz < P.fingertip_threshold));
-  }
-  if (BG) {
-    const float* box = aos + LY::A_BOX;
-    const float bx = box[0], by = box[1], bz = box[2];
-    float d[DEX_NUM_FINGERS];
-#pragma unroll
-    for (int f = 0; f < DEX_NUM_FINGERS; ++f) d[f] = norm3(p[f][0] - bx, p[f][1] - by, p[f][2] - bz);
-    if (!PAD) {
-      float mb = d[0];
-#pragma unroll
-      for (int f = 1; f < DEX_NUM_FINGERS; ++f) mb = fminf(mb, d[f]);
-      m.min_tip_box = mb;
-    } else {
-      const int od = c.off(DEX_K_FINGER_TO_OBJECT_DISTANCES), ohd = c.off(DEX_K_FINGER_TO_OBJECT_HEIGHT_DIFF);
-      float hd[DEX_NUM_FINGERS], dsum = 0.0f, hsum = 0.0f;
-#pragma unroll
-      for (int f = 0; f < DEX_NUM_FINGERS; ++f) {
-        hd[f] = fabsf(p[f][2] - bz);
-        m.padbox[f] = d[f];
-        obs_put(obs, od, f, d[f]);
-        obs_put(obs, ohd, f, hd[f]);
-        dsum += d[f];
-        hsum += hd[f];
+  const size_t N = c.N, env = c.env;
+  const bool common = !BG && (STD || A.common != 0), first = !STD && A.first != 0;
+  constexpr int I_CONTACT = 10, I_DOF = 15, I_PACT = 28, I_APT = 31, I_HAND = 34, I_BOX = 35, I_PAIR = 36;
+  constexpr int N_ITEMS = BG ? I_PAIR + 5 : I_HAND + 1;
+
+  for (int it = c.cw; it < N_ITEMS; it += kConsWarps) {
+    if (it < I_CONTACT) {
+      // ---- tip / pad pose f (observation_encoder.py:915-986; blind_grasping_task.py:684-724, 1178-1192) ----
+      const int f = it;
+      const bool is_pad = f >= DEX_NUM_FINGERS;
+      const int g = is_pad ? f - DEX_NUM_FINGERS : f;
+      const float* p = rb + 13 + 7 * f;
+      const float px = p[0], py = p[1], pz = p[2], qx = p[3], qy = p[4], qz = p[5], qw = p[6];
+      const int ow = c.off(is_pad ? DEX_K_FINGERPAD_POSES_WORLD : DEX_K_FINGERTIP_POSES_WORLD);
+      if (ow >= 0) {
+        float* o = obs + ow + 7 * g;
+        o[0] = px;
+        o[1] = py;
+        o[2] = pz;
+        o[3] = qx;
+        o[4] = qy;
+        o[5] = qz;
+        o[6] = qw;
       }
-      m.avg_hdiff = div_rn(hsum, 5.0f);  // blind_grasping_task.py:702-724
-      obs_put(obs, c.off(DEX_K_AVG_FINGER_TO_OBJECT_DISTANCE), 0, div_rn(dsum, 5.0f));
-      obs_put(obs, c.off(DEX_K_AVG_FINGER_TO_OBJECT_HEIGHT_DIFF), 0, m.avg_hdiff);
-      // pad centroid + the height / centroid part of _evaluate_pregrasp_quality (:746-771, :1334-1364)
+      const int oh = c.off(is_pad ? DEX_K_FINGERPAD_POSES_HAND : DEX_K_FINGERTIP_POSES_HAND);
+      if (oh >= 0) {
+        const Quat hq{rb[3], rb[4], rb[5], rb[6]};
+        const Vec3 ph = quat_rotate_inverse(hq, Vec3{px - rb[0], py - rb[1], pz - rb[2]});
+        const Quat qh = quat_mul(quat_conj(hq), Quat{qx, qy, qz, qw});
+        float* o = obs + oh + 7 * g;
+        o[0] = ph.x;
+        o[1] = ph.y;
+        o[2] = ph.z;
+        o[3] = qh.x;
+        o[4] = qh.y;
+        o[5] = qh.z;
+        o[6] = qh.w;
+      }
+      if (BG) {
+        const float* box = aos + LY::A_BOX;
+        const float d = norm3(px - box[0], py - box[1], pz - box[2]);
+        if (is_pad) {
+          const float hd = fabsf(pz - box[2]);
+          wk[(LY::W_PADBOX + g) * 32] = d;
+          wk[(LY::W_HDIFF + g) * 32] = hd;
+          obs_put(obs, c.off(DEX_K_FINGER_TO_OBJECT_DISTANCES), g, d);
+          obs_put(obs, c.off(DEX_K_FINGER_TO_OBJECT_HEIGHT_DIFF), g, hd);
+        } else {
+          wk[(LY::W_TIPBOX + g) * 32] = d;
+        }
+      }
+    } else if (it < I_DOF) {
+      // ---- contact sensor f (observation_encoder.py:658-735, 323-361; reward_calculator.py:183-199) ----
+      const int f = it - I_CONTACT;
+      const float* cf = aos + LY::A_CF + 3 * f;
+      const float fx = cf[0], fy = cf[1], fz = cf[2];
+      const float mag = norm3(fx, fy, fz);
+      const bool bin = mag > P.contact_binary_threshold;
+      const float dur = soa[(LY::R_CDUR + f) * 32], prevb = soa[(LY::R_PBIN + f) * 32];
+      const float ndur = (bin && prevb == 0.0f) ? 1.0f : (bin ? dur + 1.0f : 0.0f);
+      const float fb = bin ? 1.0f : 0.0f;
+      st.contact_duration_steps[f * N + env] = ndur;
+      st.prev_contact_binary[f * N + env] = fb;
+      if (STD || st.contact_forces != nullptr) {
+        st.contact_forces[(3 * f + 0) * N + env] = fx;
+        st.contact_forces[(3 * f + 1) * N + env] = fy;
+        st.contact_forces[(3 * f + 2) * N + env] = fz;
+      }
+      wk[(LY::W_BIN + f) * 32] = fb;
+      const int ocf = c.off(DEX_K_CONTACT_FORCES);
+      if (ocf >= 0) {
+        obs[ocf + 3 * f] = fx;
+        obs[ocf + 3 * f + 1] = fy;
+        obs[ocf + 3 * f + 2] = fz;
+      }
+      obs_put(obs, c.off(DEX_K_CONTACT_FORCE_MAGNITUDE), f, mag);
+      obs_put(obs, c.off(DEX_K_CONTACT_BINARY), f, fb);
+      obs_put(obs, c.off(DEX_K_CONTACT_DURATION), f, ndur * dt);
+      if (!BG && common) {
+        const bool c_now = mag > 0.1f;  // hard-coded 0.1 N (reward_calculator.py:186)
+        const bool c_prev = first ? c_now : (c.stage[LY::OFF_U8 + f * 32 + c.lane] != 0);
+        wk[(LY::W_CHG + f) * 32] = (c_now != c_prev) ? 1.0f : 0.0f;
+        st.prev_contacts[f * N + env] = c_now ? 1 : 0;
+      }
+    } else if (it < I_PACT) {
+      // ---- DOF pair (2q, 2q+1): finite-difference velocity (observation_encoder.py:298-321), obs columns,
+      //      common-reward partial terms (reward_calculator.py:94-98,138-160: Isaac dof_vel, not the finite difference)
+      const int q = it - I_DOF;
+      const float4 pv4 = reinterpret_cast<const float4*>(c.stage + LY::OFF_DOF)[c.lane * 13 + q];
+      const float pos2[2] = {pv4.x, pv4.z}, vel2[2] = {pv4.y, pv4.w};
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int d = 2 * q + h;
+        const float pos = pos2[h];
+        const float dp = pos - soa[(LY::R_PDP + d) * 32];
+        const float fd = div_rn(dp, dt);
+        st.prev_dof_pos[d * N + env] = pos;
+        float tgt = 0.0f;
+        if (!BG && (STD || A.want_tgt)) tgt = reinterpret_cast<const float*>(c.stage + LY::OFF_TGT)[c.lane * 26 + d];
+        if (d < DEX_NUM_BASE) {
+          obs_put(obs, c.off(DEX_K_BASE_DOF_POS), d, pos);
+          obs_put(obs, c.off(DEX_K_BASE_DOF_VEL), d, fd);
+          if (!BG) obs_put(obs, c.off(DEX_K_BASE_DOF_TARGET), d, tgt);
+          if (BG) wk[(LY::W_BVEL + d) * 32] = fd;
+        } else {
+          const int j = d - DEX_NUM_BASE;
+          obs_put(obs, c.off(DEX_K_ALL_FINGER_DOF_POS), j, pos);
+          obs_put(obs, c.off(DEX_K_ALL_FINGER_DOF_VEL), j, fd);
+          if (!BG) obs_put(obs, c.off(DEX_K_ALL_FINGER_DOF_TARGET), j, tgt);
+          const int aj = c.afj(d);
+          if (aj >= 0) {
+            obs_put(obs, c.off(DEX_K_ACTIVE_FINGER_DOF_POS), aj, pos);
+            obs_put(obs, c.off(DEX_K_ACTIVE_FINGER_DOF_VEL), aj, fd);
+            if (!BG) obs_put(obs, c.off(DEX_K_ACTIVE_FINGER_DOF_TARGET), aj, tgt);
+          }
+          if (!BG && common) {
+            const float iv = vel2[h];
+            const float pvv = first ? iv : soa[(LY::R_PFDV + j) * 32];
+            wk[(LY::W_FV2 + j) * 32] = iv * iv;
+            const float acc = iv - pvv;
+            wk[(LY::W_FA2 + j) * 32] = acc * acc;
+            const float nj = div_rn(2.0f * (pos - P.dof_lower[d]), P.dof_upper[d] - P.dof_lower[d]) - 1.0f;
+            wk[(LY::W_JL + j) * 32] = clampf(fabsf(nj) - 0.8f, 0.0f, 1.0f);
+            st.prev_finger_dof_vel[j * N + env] = iv;
+          }
+        }
+      }
+    } else if (it < I_APT) {
+      // ---- prev_actions columns (observation_encoder.py:287-296) ----
+      const int k0 = 6 * (it - I_PACT);
+      const int op = c.off(DEX_K_PREV_ACTIONS);
+      if (op >= 0 && k0 < P.num_actions) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) obs[op + k0 + k] = soa[(LY::R_PACT + k0 + k) * 32];  // num_actions is 6, 12 or 18
+      }
+    } else if (it < I_HAND) {
+      // ---- active_rule_targets <- active_prev_targets (rules.py:78-95, step_processor.py:73) ----
+      const int k0 = 6 * (it - I_APT);
+      const int o1 = c.off(DEX_K_ACTIVE_PREV_TARGETS), o2 = c.off(DEX_K_ACTIVE_RULE_TARGETS);
+#pragma unroll
+      for (int k = 0; k < 6; ++k) {
+        const float v = soa[(LY::R_APT + k0 + k) * 32];
+        st.active_rule_targets[(k0 + k) * N + env] = v;
+        obs_put(obs, o1, k0 + k, v);
+        obs_put(obs, o2, k0 + k, v);
+      }
+    } else if (it == I_HAND) {
+      // ---- hand pose, ARR-aligned pose (observation_encoder.py:1483-1521), hand -> box distance,
+      //      hand velocity reward terms (reward_calculator.py:100-181) ----
+      const int oh = c.off(DEX_K_HAND_POSE);
+      if (oh >= 0) {
+#pragma unroll
+        for (int j = 0; j < 7; ++j) obs[oh + j] = rb[j];
+      }
+      const int oa = c.off(DEX_K_HAND_POSE_ARR_ALIGNED);
+      if (oa >= 0) {
+        const float sh = 0.7071067811865476f;
+        const Quat qa = quat_mul(Quat{rb[3], rb[4], rb[5], rb[6]}, Quat{-0.0f, -sh, -0.0f, sh});
+        obs[oa + 0] = rb[0];
+        obs[oa + 1] = rb[1];
+        obs[oa + 2] = rb[2];
+        obs[oa + 3] = qa.x;
+        obs[oa + 4] = qa.y;
+        obs[oa + 5] = qa.z;
+        obs[oa + 6] = qa.w;
+      }
+      if (BG) {
+        const float* box = aos + LY::A_BOX;
+        const float hb = norm3(rb[0] - box[0], rb[1] - box[1], rb[2] - box[2]);
+        wk[LY::W_HANDBOX * 32] = hb;
+        obs_put(obs, c.off(DEX_K_HAND_TO_OBJECT_DISTANCE), 0, hb);
+      }
+      if (!BG && common) {
+        float hv[3], ha[3], phv[3], pha[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          hv[k] = rb[7 + k];
+          ha[k] = rb[10 + k];
+          phv[k] = first ? hv[k] : soa[(LY::R_PHV + k) * 32];
+          pha[k] = first ? ha[k] : soa[(LY::R_PHA + k) * 32];
+          st.prev_hand_vel[k * N + env] = hv[k];
+          st.prev_hand_ang_vel[k * N + env] = ha[k];
+        }
+        wk[(LY::W_RHAND + 0) * 32] = expf(-0.2f * norm3(hv[0], hv[1], hv[2]));
+        wk[(LY::W_RHAND + 1) * 32] = expf(-0.2f * norm3(ha[0], ha[1], ha[2]));
+        wk[(LY::W_RHAND + 2) * 32] = expf(-0.5f * norm3(hv[0] - phv[0], hv[1] - phv[1], hv[2] - phv[2]));
+        wk[(LY::W_RHAND + 3) * 32] = expf(-0.5f * norm3(ha[0] - pha[0], ha[1] - pha[1], ha[2] - pha[2]));
+      }
+    } else if (BG && it == I_BOX) {
+      // ---- pad centroid, box stability inputs (blind_grasping_task.py:746-771, 1334-1364) ----
+      const float* box = aos + LY::A_BOX;
       float cen[3];
 #pragma unroll
-      for (int k = 0; k < 3; ++k) cen[k] = (p[0][k] + p[1][k] + p[2][k]) / 3.0f;
+      for (int k = 0; k < 3; ++k) cen[k] = (rb[13 + 35 + k] + rb[13 + 35 + 7 + k] + rb[13 + 35 + 14 + k]) / 3.0f;
       const int oc = c.off(DEX_K_FIRST_THREE_FINGERPAD_CENTROID);
+      const int opos = c.off(DEX_K_OBJECT_POS), ovel = c.off(DEX_K_OBJECT_VEL);
 #pragma unroll
-      for (int k = 0; k < 3; ++k) obs_put(obs, oc, k, cen[k]);
-      m.cdist = norm3(cen[0] - bx, cen[1] - by, cen[2] - bz);
-      const bool h_ok = (hd[0] <= P.height_tolerance) && (hd[1] <= P.height_tolerance) && (hd[2] <= P.height_tolerance);
-      m.hcok = h_ok && (m.cdist <= P.centroid_tolerance);
-      // the ten pad pair distances, triu order (:726-771)
+      for (int k = 0; k < 3; ++k) {
+        obs_put(obs, oc, k, cen[k]);
+        obs_put(obs, opos, k, box[k]);
+        obs_put(obs, ovel, k, box[3 + k]);
+      }
+      wk[LY::W_CDIST * 32] = norm3(cen[0] - box[0], cen[1] - box[1], cen[2] - box[2]);
+      wk[LY::W_DRIFT * 32] = norm3(box[0] - soa[(LY::R_BOX0 + 0) * 32], box[1] - soa[(LY::R_BOX0 + 1) * 32],
+                                   box[2] - soa[(LY::R_BOX0 + 2) * 32]);
+      wk[LY::W_VMAG * 32] = norm3(box[3], box[4], box[5]);
+      const float* cfb = aos + LY::A_CF + 15;
+      wk[LY::W_BOXHAS * 32] = (norm3(cfb[0], cfb[1], cfb[2]) > P.contact_binary_threshold) ? 1.0f : 0.0f;
+    } else if (BG) {
+      // ---- two pad pair distances, triu order (blind_grasping_task.py:726-771) ----
       const int op = c.off(DEX_K_FINGERPAD_DISTANCES);
       if (op >= 0) {
-        int k = 0;
 #pragma unroll
-        for (int a = 0; a < DEX_NUM_FINGERS; ++a)
-#pragma unroll
-          for (int b = a + 1; b < DEX_NUM_FINGERS; ++b, ++k)
-            obs[op + k] = norm3(p[a][0] - p[b][0], p[a][1] - p[b][1], p[a][2] - p[b][2]);
+        for (int h = 0; h < 2; ++h) {
+          const int k = 2 * (it - I_PAIR) + h;
+          // k -> (a, b): rows of the strict upper triangle of a 5x5 matrix start at 0, 4, 7, 9
+          const int a = (k >= 4) + (k >= 7) + (k >= 9);
+          const int b = k - (a == 0 ? 0 : a == 1 ? 4 : a == 2 ? 7 : 9) + a + 1;
+          const float* pa = rb + 13 + 35 + 7 * a;
+          const float* pb = rb + 13 + 35 + 7 * b;
+          obs[op + k] = norm3(pa[0] - pb[0], pa[1] - pb[1], pa[2] - pb[2]);
+        }
       }
     }
   }
 }
 
-// ---- the five contact sensors (observation_encoder.py:658-735, 323-361; reward_calculator.py:183-199) and, for
-//      BlindGrasping, the box contact flag and the box stability inputs
+// one common reward term (reward_calculator.py:66-221); BaseTask, phase B
 template <bool BG, bool STD>
-__device__ __forceinline__ void part_contacts(const Post2Args& A, const Cx<BG, STD>& c, Mid& m) {
+__device__ __forceinline__ float common_term(const Post2Args& A, const Cx<BG, STD>& c, const int i) {
   using LY = Lay<BG>;
-  const DexParams& P = A.p;
-  const DexStateBuffers& st = A.st;
-  const float* aos = c.aos();
-  const float* soa = c.soa();
-  float* obs = c.obs;
-  const size_t N = c.N, env = c.env;
-  const float dt = P.control_dt;
-  float cf[DEX_NUM_FINGERS][3], dur[DEX_NUM_FINGERS], prevb[DEX_NUM_FINGERS];
+  const float* wk = c.wk;
+  const float* rb = c.aos() + LY::A_RB;
+  switch (i) {
+    case DEX_R_ALIVE: return 1.0f;
+    case DEX_R_HEIGHT_SAFETY: {
+      float mz = rb[13 + 2];
 #pragma unroll
-  for (int f = 0; f < DEX_NUM_FINGERS; ++f) {
-#pragma unroll
-    for (int k = 0; k < 3; ++k) cf[f][k] = aos[LY::A_CF + 3 * f + k];
-    dur[f] = soa[(LY::R_CDUR + f) * 32];
-    prevb[f] = soa[(LY::R_PBIN + f) * 32];
-  }
-  const int ocf = c.off(DEX_K_CONTACT_FORCES), om = c.off(DEX_K_CONTACT_FORCE_MAGNITUDE);
-  const int ob = c.off(DEX_K_CONTACT_BINARY), od = c.off(DEX_K_CONTACT_DURATION);
-  const bool common = !BG && (STD || A.common != 0), first = !STD && A.first != 0;
-  float chg = 0.0f;
-#pragma unroll
-  for (int f = 0; f < DEX_NUM_FINGERS; ++f) {
-    const float mag = norm3(cf[f][0], cf[f][1], cf[f][2]);
-    const bool bin = mag > P.contact_binary_threshold;
-    const float ndur = (bin && prevb[f] == 0.0f) ? 1.0f : (bin ? dur[f] + 1.0f : 0.0f);
-    const float fb = bin ? 1.0f : 0.0f;
-    st.contact_duration_steps[f * N + env] = ndur;
-    st.prev_contact_binary[f * N + env] = fb;
-    if (STD || st.contact_forces != nullptr) {
-#pragma unroll
-      for (int k = 0; k < 3; ++k) st.contact_forces[(3 * f + k) * N + env] = cf[f][k];
+      for (int f = 1; f < DEX_NUM_FINGERS; ++f) mz = fminf(mz, rb[13 + 7 * f + 2]);
+      return clampf(1.0f - expf(-(mz - 0.02f) * 20.0f), 0.0f, 1.0f);
     }
-    m.bin[f] = fb;
-    if (ocf >= 0) {
+    case DEX_R_FINGER_VELOCITY: {
+      float a = 0.0f;
 #pragma unroll
-      for (int k = 0; k < 3; ++k) obs[ocf + 3 * f + k] = cf[f][k];
+      for (int j = 0; j < DEX_NUM_FINGER_DOF; ++j) a += wk[(LY::W_FV2 + j) * 32];
+      return expf(-0.1f * sqrtf(a));
     }
-    obs_put(obs, om, f, mag);
-    obs_put(obs, ob, f, fb);
-    obs_put(obs, od, f, ndur * dt);
-    if (common) {
-      const bool c_now = mag > 0.1f;  // hard-coded 0.1 N (reward_calculator.py:186)
-      const bool c_prev = first ? c_now : (c.stage[LY::OFF_U8 + f * 32 + c.lane] != 0);
-      chg += (c_now != c_prev) ? 1.0f : 0.0f;  // summed in finger order as the term does (reward_calculator.py:183-199)
-      st.prev_contacts[f * N + env] = c_now ? 1 : 0;
-    }
-  }
-  m.chg = chg;
-  if (BG) {
-    const float* cfb = aos + LY::A_CF + 15;
-    const float* box = aos + LY::A_BOX;
-    const float b[6] = {box[0], box[1], box[2], box[3], box[4], box[5]};
-    m.boxhas = norm3(cfb[0], cfb[1], cfb[2]) > P.contact_binary_threshold;
-    m.drift = norm3(b[0] - soa[(LY::R_BOX0 + 0) * 32], b[1] - soa[(LY::R_BOX0 + 1) * 32], b[2] - soa[(LY::R_BOX0 + 2) * 32]);
-    m.vmag = norm3(b[3], b[4], b[5]);
-    m.sok = (m.drift <= P.position_drift_tolerance) && (m.vmag <= P.velocity_tolerance);
-    const int opos = c.off(DEX_K_OBJECT_POS), ovel = c.off(DEX_K_OBJECT_VEL);
+    case DEX_R_HAND_VELOCITY: return wk[(LY::W_RHAND + 0) * 32];
+    case DEX_R_HAND_ANGULAR_VELOCITY: return wk[(LY::W_RHAND + 1) * 32];
+    case DEX_R_JOINT_LIMIT: {
+      float a = 0.0f;
 #pragma unroll
-    for (int k = 0; k < 3; ++k) {
-      obs_put(obs, opos, k, b[k]);
-      obs_put(obs, ovel, k, b[3 + k]);
+      for (int j = 0; j < DEX_NUM_FINGER_DOF; ++j) a += wk[(LY::W_JL + j) * 32];
+      return 1.0f - div_rn(a, 20.0f);
+    }
+    case DEX_R_FINGER_ACCELERATION: {
+      float a = 0.0f;
+#pragma unroll
+      for (int j = 0; j < DEX_NUM_FINGER_DOF; ++j) a += wk[(LY::W_FA2 + j) * 32];
+      return expf(-2.0f * sqrtf(a));
+    }
+    case DEX_R_HAND_ACCELERATION: return wk[(LY::W_RHAND + 2) * 32];
+    case DEX_R_HAND_ANGULAR_ACCELERATION: return wk[(LY::W_RHAND + 3) * 32];
+    default: {  // DEX_R_CONTACT_STABILITY
+      float a = 0.0f;
+#pragma unroll
+      for (int f = 0; f < DEX_NUM_FINGERS; ++f) a += wk[(LY::W_CHG + f) * 32];
+      return expf(-a);
     }
   }
 }
 
-// ---- hand pose, ARR-aligned pose (observation_encoder.py:1483-1521), hand -> box distance, hand velocity reward
-//      terms (reward_calculator.py:100-181), episode time (dexhand_base.py:703-712: PRE-increment count)
+// one BlindGrasping task term (blind_grasping_task.py:980-1208); phase C (after the FSM)
 template <bool BG, bool STD>
-__device__ __forceinline__ void part_hand(const Post2Args& A, const Cx<BG, STD>& c, Mid& m) {
+__device__ __forceinline__ float task_term(const Post2Args& A, const Cx<BG, STD>& c, const int i) {
   using LY = Lay<BG>;
   const DexParams& P = A.p;
-  const DexStateBuffers& st = A.st;
+  const float* wk = c.wk;
   const float* aos = c.aos();
-  const float* soa = c.soa();
   const float* rb = aos + LY::A_RB;
-  float* obs = c.obs;
-  float h[7];
-#pragma unroll
-  for (int j = 0; j < 7; ++j) h[j] = rb[j];
-  obs_put(obs, c.off(DEX_K_EPISODE_TIME), 0, (float)c.i64lo(LY::I_STEP) * P.control_dt);
-  const int oh = c.off(DEX_K_HAND_POSE);
-  if (oh >= 0) {
-#pragma unroll
-    for (int j = 0; j < 7; ++j) obs[oh + j] = h[j];
-  }
-  const int oa = c.off(DEX_K_HAND_POSE_ARR_ALIGNED);
-  if (oa >= 0) {
-    const float sh = 0.7071067811865476f;
-    const Quat qa = quat_mul(Quat{h[3], h[4], h[5], h[6]}, Quat{-0.0f, -sh, -0.0f, sh});
-    obs[oa + 0] = h[0];
-    obs[oa + 1] = h[1];
-    obs[oa + 2] = h[2];
-    obs[oa + 3] = qa.x;
-    obs[oa + 4] = qa.y;
-    obs[oa + 5] = qa.z;
-    obs[oa + 6] = qa.w;
-  }
-  if (BG) {
-    const float* box = aos + LY::A_BOX;
-    const float hb = norm3(h[0] - box[0], h[1] - box[1], h[2] - box[2]);
-    m.boxfar = hb > P.max_box_distance;
-    obs_put(obs, c.off(DEX_K_HAND_TO_OBJECT_DISTANCE), 0, hb);
-  }
-  if (!BG && (STD || A.common)) {
-    const bool first = !STD && A.first != 0;
-    float hv[3], ha[3], phv[3], pha[3];
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-      hv[k] = rb[7 + k];
-      ha[k] = rb[10 + k];
-      phv[k] = first ? hv[k] : soa[(LY::R_PHV + k) * 32];
-      pha[k] = first ? ha[k] : soa[(LY::R_PHA + k) * 32];
-      st.prev_hand_vel[k * c.N + c.env] = hv[k];
-      st.prev_hand_ang_vel[k * c.N + c.env] = ha[k];
+  const int stage = __float_as_int(wk[LY::W_STAGE * 32]);
+  const float m1 = (stage == 1) ? 1.0f : 0.0f, m2 = (stage == 2) ? 1.0f : 0.0f, m3 = (stage == 3) ? 1.0f : 0.0f;
+  switch (i) {
+    case DEX_R_S1_HEIGHT_ALIGNMENT: return expf(-P.height_alignment_decay * wk[LY::W_AVGHDIFF * 32]) * m1;
+    case DEX_R_S1_CENTROID_POSITIONING: return expf(-P.centroid_positioning_decay * wk[LY::W_CDIST * 32]) * m1;
+    case DEX_R_S1_OBJECT_STABILITY:
+      return expf(-P.object_stability_decay * (wk[LY::W_DRIFT * 32] + wk[LY::W_VMAG * 32])) * m1;
+    case DEX_R_S1_FINGER_HEIGHT_CONSISTENCY: {  // torch.var(dim=1), unbiased, z of the first three pads
+      const float z0 = rb[13 + 35 + 2], z1 = rb[13 + 35 + 7 + 2], z2 = rb[13 + 35 + 14 + 2];
+      const float mean = (z0 + z1 + z2) / 3.0f;
+      const float d0 = z0 - mean, d1 = z1 - mean, d2 = z2 - mean;
+      const float var = (d0 * d0 + d1 * d1 + d2 * d2) / 2.0f;
+      return expf(-P.height_consistency_decay * var) * m1;
     }
-    m.rhand[0] = expf(-0.2f * norm3(hv[0], hv[1], hv[2]));
-    m.rhand[1] = expf(-0.2f * norm3(ha[0], ha[1], ha[2]));
-    m.rhand[2] = expf(-0.5f * norm3(hv[0] - phv[0], hv[1] - phv[1], hv[2] - phv[2]));
-    m.rhand[3] = expf(-0.5f * norm3(ha[0] - pha[0], ha[1] - pha[1], ha[2] - pha[2]));
-  }
-}
-
-// ---- the 26 DOFs: finite-difference velocity (observation_encoder.py:298-321), obs columns, common-reward partial
-//      sums (reward_calculator.py:94-98,138-160: Isaac dof_vel, not the finite difference; summed in DOF order)
-template <bool BG, bool STD, int Q0, int Q1>  // DOF pairs [Q0, Q1)
-__device__ __forceinline__ void part_dofs(const Post2Args& A, const Cx<BG, STD>& c, Mid& m) {
-  using LY = Lay<BG>;
-  const DexParams& P = A.p;
-  const DexStateBuffers& st = A.st;
-  const float* soa = c.soa();
-  float* obs = c.obs;
-  const size_t N = c.N, env = c.env;
-  const float dt = P.control_dt;
-  const float4* d4 = reinterpret_cast<const float4*>(c.stage + LY::OFF_DOF) + c.lane * 13;
-  const bool want_tgt = !BG && (STD || A.want_tgt != 0);
-  const bool common = !BG && (STD || A.common != 0), first = !STD && A.first != 0;
-  const int o_bp = c.off(DEX_K_BASE_DOF_POS), o_bv = c.off(DEX_K_BASE_DOF_VEL), o_bt = c.off(DEX_K_BASE_DOF_TARGET);
-  const int o_ap = c.off(DEX_K_ALL_FINGER_DOF_POS), o_av = c.off(DEX_K_ALL_FINGER_DOF_VEL),
-            o_at = c.off(DEX_K_ALL_FINGER_DOF_TARGET);
-  const int o_fp = c.off(DEX_K_ACTIVE_FINGER_DOF_POS), o_fv = c.off(DEX_K_ACTIVE_FINGER_DOF_VEL),
-            o_ft = c.off(DEX_K_ACTIVE_FINGER_DOF_TARGET);
+    case DEX_R_S1_THUMB_ROTATION: {
+      const float th = reinterpret_cast<const float*>(c.stage + LY::OFF_DOF)[c.lane * 52 + 2 * DEX_NUM_BASE];
+      return expf(-5.0f * fabsf(th - P.half_pi)) * m1;
+    }
+    case DEX_R_S2_THUMB_CONTACT: return wk[LY::W_THUMB * 32] * m2;
+    case DEX_R_S2_OTHER_FINGERS_CONTACT: return wk[LY::W_OTHERS * 32] * m2;
+    case DEX_R_S2_GRASP_ACHIEVEMENT: return wk[LY::W_GRASP * 32] * m2;
+    case DEX_R_S2_FINGERPAD_PROXIMITY:
+      return expf(-P.fingerpad_proximity_decay * fmaxf(wk[LY::W_MINTIPBOX * 32], P.min_reward_distance)) * m2;
+    case DEX_R_S2_BASE_STABILITY: {
+      float bv2 = 0.0f;
 #pragma unroll
-  for (int q = Q0; q < Q1; ++q) {
-    const float4 v4 = d4[q];
-    const float pos2[2] = {v4.x, v4.z}, vel2[2] = {v4.y, v4.w};
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      const int d = 2 * q + h;
-      const float pos = pos2[h];
-      const float fd = div_rn(pos - soa[(LY::R_PDP + d) * 32], dt);
-      st.prev_dof_pos[d * N + env] = pos;
-      const float tgt = want_tgt ? reinterpret_cast<const float*>(c.stage + LY::OFF_TGT)[c.lane * 26 + d] : 0.0f;
-      if (d < DEX_NUM_BASE) {
-        obs_put(obs, o_bp, d, pos);
-        obs_put(obs, o_bv, d, fd);
-        if (!BG) obs_put(obs, o_bt, d, tgt);
-        if (BG) c.wk[(LY::W_BVEL + (d < DEX_NUM_BASE ? d : 0)) * 32] = fd;
-      } else {
-        const int j = d - DEX_NUM_BASE;
-        obs_put(obs, o_ap, j, pos);
-        obs_put(obs, o_av, j, fd);
-        if (!BG) obs_put(obs, o_at, j, tgt);
-        const int aj = c.afj(d);
-        if (aj >= 0) {
-          obs_put(obs, o_fp, aj, pos);
-          obs_put(obs, o_fv, aj, fd);
-          if (!BG) obs_put(obs, o_ft, aj, tgt);
-        }
-        if (common) {
-          const float iv = vel2[h];
-          const float pvv = first ? iv : soa[(LY::R_PFDV + j) * 32];
-          // partial terms: summed in DOF order by the term itself (reward_calculator.py:138-160)
-          c.wk[(LY::W_FV2 + j) * 32] = iv * iv;
-          const float acc = iv - pvv;
-          c.wk[(LY::W_FA2 + j) * 32] = acc * acc;
-          const float nj = div_rn(2.0f * (pos - P.dof_lower[d]), P.dof_upper[d] - P.dof_lower[d]) - 1.0f;
-          c.wk[(LY::W_JL + j) * 32] = clampf(fabsf(nj) - 0.8f, 0.0f, 1.0f);
-          st.prev_finger_dof_vel[j * N + env] = iv;
-        }
+      for (int d = 0; d < DEX_NUM_BASE; ++d) {
+        const float v = wk[(LY::W_BVEL + d) * 32];  // finite-difference base velocity
+        bv2 += v * v;
       }
+      return expf(-P.base_stability_decay * sqrtf(bv2)) * m2;
     }
+    case DEX_R_S3_OBJECT_HEIGHT:
+      return clampf(div_rn(aos[LY::A_BOX + 2] - P.box_z, P.lift_height_range), 0.0f, 1.0f) * m3;
+    case DEX_R_S3_GRASP_MAINTENANCE: return wk[LY::W_GRASP * 32] * m3;
+    case DEX_R_S3_GRASP_DURATION:
+      return clampf(div_rn(wk[LY::W_GRASPDUR * 32], P.contact_duration_threshold_s), 0.0f, 1.0f) * m3;
+    // completion bonuses :1025-1048 (transition and not failed), penetration :1194-1208
+    case DEX_R_S1_COMPLETION: return (wk[LY::W_J2 * 32] != 0.0f && wk[LY::W_QUALOK * 32] != 0.0f) ? 1.0f : 0.0f;
+    case DEX_R_S2_COMPLETION: return (wk[LY::W_J3 * 32] != 0.0f && wk[LY::W_GRASP * 32] != 0.0f) ? 1.0f : 0.0f;
+    default:  // DEX_R_PENETRATION_PENALTY
+      return fmaxf(P.penetration_threshold - wk[LY::W_MINTIPBOX * 32], 0.0f) * P.penetration_depth_scale;
   }
 }
 
-// ---- prev_actions columns (observation_encoder.py:287-296); active_rule_targets <- active_prev_targets
-//      (rules.py:78-95, step_processor.py:73)
-template <bool BG, bool STD>
-__device__ __forceinline__ void part_copies(const Post2Args& A, const Cx<BG, STD>& c) {
-  using LY = Lay<BG>;
-  const DexParams& P = A.p;
-  const float* soa = c.soa();
-  float* obs = c.obs;
-  float apt[DEX_NUM_ACTIVE];
-#pragma unroll
-  for (int k = 0; k < DEX_NUM_ACTIVE; ++k) apt[k] = soa[(LY::R_APT + k) * 32];
-  const int op = c.off(DEX_K_PREV_ACTIONS);
-  if (op >= 0) {
-#pragma unroll
-    for (int k0 = 0; k0 < DEX_NUM_ACTIVE; k0 += 6) {  // num_actions is 6, 12 or 18
-      if (k0 < P.num_actions) {
-        float v[6];
-#pragma unroll
-        for (int k = 0; k < 6; ++k) v[k] = soa[(LY::R_PACT + k0 + k) * 32];
-#pragma unroll
-        for (int k = 0; k < 6; ++k) obs[op + k0 + k] = v[k];
-      }
-    }
-  }
-  const int o1 = c.off(DEX_K_ACTIVE_PREV_TARGETS), o2 = c.off(DEX_K_ACTIVE_RULE_TARGETS);
-  float* art = A.st.active_rule_targets + c.env;
-#pragma unroll
-  for (int k = 0; k < DEX_NUM_ACTIVE; ++k) {
-    art[(size_t)k * c.N] = apt[k];
-    obs_put(obs, o1, k, apt[k]);
-    obs_put(obs, o2, k, apt[k]);
-  }
-}
-
-// ---- BlindGrasping: finger-box contacts (blind_grasping_task.py:773-833), success duration (:626-648), stage FSM
-//      (:835-978; plain fp32 accumulation of (float)control_dt decides the transition step)
-// WRITE = false: the reward-term warps recompute the (cheap) chain for themselves instead of waiting for warp 0
-template <bool STD, bool WRITE>
-__device__ __forceinline__ void part_task_state(const Post2Args& A, const Cx<true, STD>& c, Mid& m) {
-  using LY = Lay<true>;
-  const DexParams& P = A.p;
-  const DexStateBuffers& st = A.st;
-  const float dt = P.control_dt;
-  float* obs = c.obs;
-  const float* soa = c.soa();
-  const size_t env = c.env;
-  const float box_z = c.aos()[LY::A_BOX + 2];
-  const int sds_old = c.i64lo(LY::I_SDS);
-  int stage = c.i64lo(LY::I_STAGE);
-  float tis = soa[LY::R_TIS * 32] + dt;
-  float scd = soa[LY::R_SCD * 32];
-  bool fbc[DEX_NUM_FINGERS];
-  int n_on_box = 0;
-#pragma unroll
-  for (int f = 0; f < DEX_NUM_FINGERS; ++f) {
-    fbc[f] = (m.bin[f] != 0.0f) && m.boxhas && (m.padbox[f] < P.proximity_threshold);
-    n_on_box += fbc[f] ? 1 : 0;
-  }
-  m.thumb = fbc[0];
-  m.others = fbc[1] || fbc[2] || fbc[3] || fbc[4];
-  m.grasp = m.thumb && m.others;
-  if (WRITE) obs_put(obs, c.off(DEX_K_THUMB_CONTACT), 0, m.thumb ? 1.0f : 0.0f);
-  if (WRITE) obs_put(obs, c.off(DEX_K_OTHER_FINGERS_CONTACT), 0, m.others ? 1.0f : 0.0f);
-  if (WRITE) obs_put(obs, c.off(DEX_K_GRASP_STATE), 0, m.grasp ? 1.0f : 0.0f);
-  const bool cond = (box_z > P.success_height_threshold) && (n_on_box >= P.min_fingers_for_grasp);
-  m.sds = cond ? sds_old + 1 : 0;
-  if (WRITE) st.success_duration_steps[env] = (long long)m.sds;
-  if (WRITE) st.success_conditions_met[env] = cond ? 1 : 0;
-  m.graspdur = (float)m.sds * dt;
-  if (WRITE) obs_put(obs, c.off(DEX_K_GRASP_DURATION), 0, m.graspdur);
-  // FSM
-  const bool thumb_other = (m.bin[0] != 0.0f) && ((m.bin[1] != 0.0f) || (m.bin[2] != 0.0f) || (m.bin[3] != 0.0f) || (m.bin[4] != 0.0f));
-  if (stage == 2) scd = thumb_other ? scd + dt : 0.0f;
-  const bool s1_done = (stage == 1) && (tis >= P.stage1_duration);
-  const bool s2_done = (stage == 2) && ((scd >= P.stage2_contact_success_threshold) || (tis >= P.stage2_duration));
-  if (s1_done) stage = 2;
-  if (s2_done) stage = 3;
-  if (s1_done || s2_done) {
-    tis = 0.0f;
-    scd = 0.0f;
-  }
-  if (WRITE) st.current_stage[env] = (long long)stage;
-  if (WRITE) st.time_in_stage[env] = tis;
-  if (WRITE) st.stage_contact_duration[env] = scd;
-  if (WRITE) st.just_transitioned_to_stage2[env] = s1_done ? 1 : 0;
-  if (WRITE) st.just_transitioned_to_stage3[env] = s2_done ? 1 : 0;
-  float prog = 0.0f;  // :958-978
-  if (stage == 1) prog = clampf(div_rn(tis, P.stage1_duration), 0.0f, 1.0f);
-  if (stage == 2) prog = clampf(div_rn(tis, P.stage2_duration), 0.0f, 1.0f);
-  if (stage == 3) prog = 1.0f;
-  m.stage = stage;
-  m.j2 = s1_done;
-  m.j3 = s2_done;
-  if (WRITE) obs_put(obs, c.off(DEX_K_CURRENT_STAGE), 0, (float)stage);
-  if (WRITE) obs_put(obs, c.off(DEX_K_TIME_IN_STAGE), 0, tis);
-  if (WRITE) obs_put(obs, c.off(DEX_K_STAGE_PROGRESS), 0, prog);
-}
-
-// raw + weighted rows of term i leave from registers; the weighted value is parked in the work block for the ordered total
+// raw + weighted rows of term i leave from registers; the weighted value is parked for the ordered total
 template <bool BG, bool STD>
 __device__ __forceinline__ void emit_term(const Post2Args& A, const Cx<BG, STD>& c, const int i, const float r) {
   const float w = A.p.reward_weight[i];
@@ -793,87 +737,138 @@ __device__ __forceinline__ void emit_term(const Post2Args& A, const Cx<BG, STD>&
   c.wk[(Lay<BG>::W_WGT + i) * 32] = rw;
 }
 
-// the reward terms are dealt round-robin to the consumer warps 1..7; warp CW runs the terms with (term % 7) == CW - 1 as
-// one straight-line block (TERM's value expression is only instantiated for the owner)
-#define DEX_TERM(BGF, i, expr)                                   \
-  if constexpr (((i) % (kConsWarps - 1)) == CW - 1) emit_term<BGF, STD>(A, c, (i), (expr))
-
-// ---- common reward terms (reward_calculator.py:66-221); BaseTask.  The ordered partial sums are formed here.
-template <bool STD, int CW>
-__device__ __forceinline__ void part_common_terms(const Post2Args& A, const Cx<false, STD>& c) {
-  using LY = Lay<false>;
-  const float* wk = c.wk;
-  auto sum20 = [&](const int f0) {
-    float a = 0.0f;
-#pragma unroll
-    for (int j = 0; j < DEX_NUM_FINGER_DOF; ++j) a += wk[(f0 + j) * 32];
-    return a;
-  };
-  DEX_TERM(false, DEX_R_ALIVE, 1.0f);
-  DEX_TERM(false, DEX_R_HEIGHT_SAFETY, clampf(1.0f - expf(-(wk[LY::W_MINTIPZ * 32] - 0.02f) * 20.0f), 0.0f, 1.0f));
-  DEX_TERM(false, DEX_R_FINGER_VELOCITY, expf(-0.1f * sqrtf(sum20(LY::W_FV2))));
-  DEX_TERM(false, DEX_R_HAND_VELOCITY, wk[(LY::W_RHAND + 0) * 32]);
-  DEX_TERM(false, DEX_R_HAND_ANGULAR_VELOCITY, wk[(LY::W_RHAND + 1) * 32]);
-  DEX_TERM(false, DEX_R_JOINT_LIMIT, 1.0f - div_rn(sum20(LY::W_JL), 20.0f));
-  DEX_TERM(false, DEX_R_FINGER_ACCELERATION, expf(-2.0f * sqrtf(sum20(LY::W_FA2))));
-  DEX_TERM(false, DEX_R_HAND_ACCELERATION, wk[(LY::W_RHAND + 2) * 32]);
-  DEX_TERM(false, DEX_R_HAND_ANGULAR_ACCELERATION, wk[(LY::W_RHAND + 3) * 32]);
-  DEX_TERM(false, DEX_R_CONTACT_STABILITY, expf(-wk[LY::W_CHG * 32]));  // summed in finger order by part_contacts
-}
-
-// ---- BlindGrasping task terms (blind_grasping_task.py:980-1208), after the FSM (m: part_task_state of this warp)
-template <bool STD, int CW>
-__device__ __forceinline__ void part_task_terms(const Post2Args& A, const Cx<true, STD>& c, const Mid& m) {
-  using LY = Lay<true>;
+// phase B: the per-env scalar part, split over the consumer warps (warp-uniform job index)
+template <bool BG, bool STD>
+__device__ __forceinline__ void phase_scalar(const Post2Args& A, const Cx<BG, STD>& c) {
+  using LY = Lay<BG>;
+  if (!c.act) return;
   const DexParams& P = A.p;
-  const float* wk = c.wk;
+  const DexStateBuffers& st = A.st;
+  const float dt = P.control_dt;
+  float* wk = c.wk;
+  float* obs = c.obs;
   const float* aos = c.aos();
+  const float* soa = c.soa();
   const float* rb = aos + LY::A_RB;
-  const float m1 = (m.stage == 1) ? 1.0f : 0.0f, m2 = (m.stage == 2) ? 1.0f : 0.0f, m3 = (m.stage == 3) ? 1.0f : 0.0f;
-  const float fg = m.grasp ? 1.0f : 0.0f;
-  DEX_TERM(true, DEX_R_S1_HEIGHT_ALIGNMENT, expf(-P.height_alignment_decay * wk[LY::W_AVGHDIFF * 32]) * m1);
-  DEX_TERM(true, DEX_R_S1_CENTROID_POSITIONING, expf(-P.centroid_positioning_decay * wk[LY::W_CDIST * 32]) * m1);
-  DEX_TERM(true, DEX_R_S1_OBJECT_STABILITY, expf(-P.object_stability_decay * (wk[LY::W_DRIFT * 32] + wk[LY::W_VMAG * 32])) * m1);
-  if constexpr ((DEX_R_S1_FINGER_HEIGHT_CONSISTENCY % (kConsWarps - 1)) == CW - 1) {  // torch.var(dim=1), unbiased, z of the first three pads
-    const float z0 = rb[13 + 35 + 2], z1 = rb[13 + 35 + 7 + 2], z2 = rb[13 + 35 + 14 + 2];
-    const float mean = (z0 + z1 + z2) / 3.0f;
-    const float d0 = z0 - mean, d1 = z1 - mean, d2 = z2 - mean;
-    const float var = (d0 * d0 + d1 * d1 + d2 * d2) / 2.0f;
-    emit_term<true, STD>(A, c, DEX_R_S1_FINGER_HEIGHT_CONSISTENCY, expf(-P.height_consistency_decay * var) * m1);
-  }
-  DEX_TERM(true, DEX_R_S1_THUMB_ROTATION,
-           expf(-5.0f * fabsf(reinterpret_cast<const float*>(c.stage + LY::OFF_DOF)[c.lane * 52 + 2 * DEX_NUM_BASE] - P.half_pi)) * m1);
-  DEX_TERM(true, DEX_R_S2_THUMB_CONTACT, (m.thumb ? 1.0f : 0.0f) * m2);
-  DEX_TERM(true, DEX_R_S2_OTHER_FINGERS_CONTACT, (m.others ? 1.0f : 0.0f) * m2);
-  DEX_TERM(true, DEX_R_S2_GRASP_ACHIEVEMENT, fg * m2);
-  DEX_TERM(true, DEX_R_S2_FINGERPAD_PROXIMITY,
-           expf(-P.fingerpad_proximity_decay * fmaxf(wk[LY::W_MINTIPBOX * 32], P.min_reward_distance)) * m2);
-  if constexpr ((DEX_R_S2_BASE_STABILITY % (kConsWarps - 1)) == CW - 1) {
-    float bv2 = 0.0f;
+  const size_t env = c.env;
+  if (BG) {
+    if (c.cw == 0) {
+      // ---- finger-box contacts (blind_grasping_task.py:773-833), success duration (:626-648) ----
+      const bool box_has = wk[LY::W_BOXHAS * 32] != 0.0f;
+      bool fbc[DEX_NUM_FINGERS];
+      int n_on_box = 0;
 #pragma unroll
-    for (int d = 0; d < DEX_NUM_BASE; ++d) {
-      const float v = wk[(LY::W_BVEL + d) * 32];  // finite-difference base velocity
-      bv2 += v * v;
+      for (int f = 0; f < DEX_NUM_FINGERS; ++f) {
+        fbc[f] = (wk[(LY::W_BIN + f) * 32] != 0.0f) && box_has && (wk[(LY::W_PADBOX + f) * 32] < P.proximity_threshold);
+        n_on_box += fbc[f] ? 1 : 0;
+      }
+      const bool thumb_c = fbc[0], others_c = fbc[1] || fbc[2] || fbc[3] || fbc[4];
+      const bool grasp = thumb_c && others_c;
+      const float ft = thumb_c ? 1.0f : 0.0f, fo = others_c ? 1.0f : 0.0f, fg = grasp ? 1.0f : 0.0f;
+      wk[LY::W_THUMB * 32] = ft;
+      wk[LY::W_OTHERS * 32] = fo;
+      wk[LY::W_GRASP * 32] = fg;
+      obs_put(obs, c.off(DEX_K_THUMB_CONTACT), 0, ft);
+      obs_put(obs, c.off(DEX_K_OTHER_FINGERS_CONTACT), 0, fo);
+      obs_put(obs, c.off(DEX_K_GRASP_STATE), 0, fg);
+      const float box_z = aos[LY::A_BOX + 2];
+      const bool cond = (box_z > P.success_height_threshold) && (n_on_box >= P.min_fingers_for_grasp);
+      const int sds = cond ? c.i64lo(LY::I_SDS) + 1 : 0;
+      st.success_duration_steps[env] = (long long)sds;
+      st.success_conditions_met[env] = cond ? 1 : 0;
+      const float gd = (float)sds * dt;
+      wk[LY::W_SDS * 32] = __int_as_float(sds);
+      wk[LY::W_GRASPDUR * 32] = gd;
+      obs_put(obs, c.off(DEX_K_GRASP_DURATION), 0, gd);
+    } else if (c.cw == 1) {
+      // ---- stage FSM :835-956 (plain fp32 accumulation of (float)control_dt decides the transition step) ----
+      int stage = c.i64lo(LY::I_STAGE);
+      float tis = soa[LY::R_TIS * 32] + dt;
+      float scd = soa[LY::R_SCD * 32];
+      const bool b0 = wk[(LY::W_BIN + 0) * 32] != 0.0f;
+      const bool bo = (wk[(LY::W_BIN + 1) * 32] != 0.0f) || (wk[(LY::W_BIN + 2) * 32] != 0.0f) ||
+                      (wk[(LY::W_BIN + 3) * 32] != 0.0f) || (wk[(LY::W_BIN + 4) * 32] != 0.0f);
+      const bool thumb_other = b0 && bo;
+      if (stage == 2) scd = thumb_other ? scd + dt : 0.0f;
+      const bool s1_done = (stage == 1) && (tis >= P.stage1_duration);
+      const bool s2_done = (stage == 2) && ((scd >= P.stage2_contact_success_threshold) || (tis >= P.stage2_duration));
+      if (s1_done) stage = 2;
+      if (s2_done) stage = 3;
+      if (s1_done || s2_done) {
+        tis = 0.0f;
+        scd = 0.0f;
+      }
+      st.current_stage[env] = (long long)stage;
+      st.time_in_stage[env] = tis;
+      st.stage_contact_duration[env] = scd;
+      st.just_transitioned_to_stage2[env] = s1_done ? 1 : 0;
+      st.just_transitioned_to_stage3[env] = s2_done ? 1 : 0;
+      float prog = 0.0f;  // :958-978
+      if (stage == 1) prog = clampf(div_rn(tis, P.stage1_duration), 0.0f, 1.0f);
+      if (stage == 2) prog = clampf(div_rn(tis, P.stage2_duration), 0.0f, 1.0f);
+      if (stage == 3) prog = 1.0f;
+      wk[LY::W_STAGE * 32] = __int_as_float(stage);
+      wk[LY::W_J2 * 32] = s1_done ? 1.0f : 0.0f;
+      wk[LY::W_J3 * 32] = s2_done ? 1.0f : 0.0f;
+      obs_put(obs, c.off(DEX_K_CURRENT_STAGE), 0, (float)stage);
+      obs_put(obs, c.off(DEX_K_TIME_IN_STAGE), 0, tis);
+      obs_put(obs, c.off(DEX_K_STAGE_PROGRESS), 0, prog);
+    } else if (c.cw == 2) {
+      // ---- minima, criteria inputs (step_processor.py:133-181, blind_grasping_task.py:1290-1364) ----
+      float min_tip_z = rb[13 + 2], min_tip_box = wk[LY::W_TIPBOX * 32];
+#pragma unroll
+      for (int f = 1; f < DEX_NUM_FINGERS; ++f) {
+        min_tip_z = fminf(min_tip_z, rb[13 + 7 * f + 2]);
+        min_tip_box = fminf(min_tip_box, wk[(LY::W_TIPBOX + f) * 32]);
+      }
+      const bool hitg = P.has_height_safety && ((rb[2] < P.handbase_threshold) || (min_tip_z < P.fingertip_threshold));
+      const bool h_ok = (wk[(LY::W_HDIFF + 0) * 32] <= P.height_tolerance) && (wk[(LY::W_HDIFF + 1) * 32] <= P.height_tolerance) &&
+                        (wk[(LY::W_HDIFF + 2) * 32] <= P.height_tolerance);
+      const bool c_ok = wk[LY::W_CDIST * 32] <= P.centroid_tolerance;
+      const bool s_ok = (wk[LY::W_DRIFT * 32] <= P.position_drift_tolerance) && (wk[LY::W_VMAG * 32] <= P.velocity_tolerance);
+      wk[LY::W_MINTIPBOX * 32] = min_tip_box;
+      wk[LY::W_HITG * 32] = hitg ? 1.0f : 0.0f;
+      wk[LY::W_BOXFAR * 32] = (wk[LY::W_HANDBOX * 32] > P.max_box_distance) ? 1.0f : 0.0f;
+      wk[LY::W_QUALOK * 32] = (h_ok && c_ok && s_ok) ? 1.0f : 0.0f;
+    } else if (c.cw == 3) {
+      // ---- averages (blind_grasping_task.py:702-724), episode time (dexhand_base.py:703-712: PRE-increment count) ----
+      float dsum = 0.0f, hsum = 0.0f;
+#pragma unroll
+      for (int f = 0; f < DEX_NUM_FINGERS; ++f) {
+        dsum += wk[(LY::W_PADBOX + f) * 32];
+        hsum += wk[(LY::W_HDIFF + f) * 32];
+      }
+      const float avg_h = div_rn(hsum, 5.0f);
+      wk[LY::W_AVGHDIFF * 32] = avg_h;
+      obs_put(obs, c.off(DEX_K_AVG_FINGER_TO_OBJECT_DISTANCE), 0, div_rn(dsum, 5.0f));
+      obs_put(obs, c.off(DEX_K_AVG_FINGER_TO_OBJECT_HEIGHT_DIFF), 0, avg_h);
+      obs_put(obs, c.off(DEX_K_EPISODE_TIME), 0, (float)c.i64lo(LY::I_STEP) * dt);
     }
-    emit_term<true, STD>(A, c, DEX_R_S2_BASE_STABILITY, expf(-P.base_stability_decay * sqrtf(bv2)) * m2);
+  } else {
+    if (c.cw == 2) {
+      float min_tip_z = rb[13 + 2];
+#pragma unroll
+      for (int f = 1; f < DEX_NUM_FINGERS; ++f) min_tip_z = fminf(min_tip_z, rb[13 + 7 * f + 2]);
+      const bool hitg = P.has_height_safety && ((rb[2] < P.handbase_threshold) || (min_tip_z < P.fingertip_threshold));
+      wk[LY::W_HITG * 32] = hitg ? 1.0f : 0.0f;
+      obs_put(obs, c.off(DEX_K_EPISODE_TIME), 0, (float)c.i64lo(LY::I_STEP) * dt);
+    } else {
+      // common reward terms over the seven other warps (0, 1, 3..7)
+      for (int i = (c.cw < 2 ? c.cw : c.cw - 1); i < DEX_NUM_COMMON_TERMS; i += kConsWarps - 1) {
+        emit_term<BG, STD>(A, c, i, common_term<BG, STD>(A, c, i));
+      }
+    }
   }
-  DEX_TERM(true, DEX_R_S3_OBJECT_HEIGHT, clampf(div_rn(aos[LY::A_BOX + 2] - P.box_z, P.lift_height_range), 0.0f, 1.0f) * m3);
-  DEX_TERM(true, DEX_R_S3_GRASP_MAINTENANCE, fg * m3);
-  DEX_TERM(true, DEX_R_S3_GRASP_DURATION, clampf(div_rn(m.graspdur, P.contact_duration_threshold_s), 0.0f, 1.0f) * m3);
-  // completion bonuses :1025-1048 (transition and not failed), penetration :1194-1208
-  DEX_TERM(true, DEX_R_S1_COMPLETION, (m.j2 && m.hcok && m.sok) ? 1.0f : 0.0f);
-  DEX_TERM(true, DEX_R_S2_COMPLETION, (m.j3 && m.grasp) ? 1.0f : 0.0f);
-  DEX_TERM(true, DEX_R_PENETRATION_PENALTY, fmaxf(P.penetration_threshold - wk[LY::W_MINTIPBOX * 32], 0.0f) * P.penetration_depth_scale);
 }
 
-// ---- termination (step_processor.py:133-181, termination_manager.py:120-278), masks, tile record.
-// Returns the exclusive termination class of this lane's env (bit 0 success, 1 failure, 2 timeout) and the reset ballot.
-template <bool BG, bool STD, bool FULL>
-__device__ __forceinline__ unsigned part_terminate(const Post2Args& A, const Cx<BG, STD>& c, const Mid& m, const unsigned stamp,
-                                                   unsigned& rbits_out) {
+// phase C, warp 0: termination (step_processor.py:133-181, termination_manager.py:120-278), masks, tile record.
+// Returns the exclusive termination class of this lane's env: bit 0 success, 1 failure, 2 timeout.
+template <bool BG, bool STD>
+__device__ __forceinline__ unsigned phase_combine(const Post2Args& A, const Cx<BG, STD>& c, const unsigned stamp, unsigned* s_rbits) {
   using LY = Lay<BG>;
   const DexParams& P = A.p;
   const DexStateBuffers& st = A.st;
+  const float* wk = c.wk;
   bool should_reset = false, t_success = false, t_failure = false, t_timeout = false;
   int ep_len_done = 0;
   bool crit[DEX_NUM_CRITERIA];
@@ -883,13 +878,17 @@ __device__ __forceinline__ unsigned part_terminate(const Post2Args& A, const Cx<
     const int step_now = c.i64lo(LY::I_STEP) + 1;  // step_processor.py:80
     st.episode_step_count[c.env] = (long long)step_now;
     ep_len_done = step_now;
-    crit[DEX_C_HITTING_GROUND] = m.hitg;
+    crit[DEX_C_HITTING_GROUND] = wk[LY::W_HITG * 32] != 0.0f;
     if (BG) {
-      crit[DEX_C_GRASP_LIFT_SUCCESS] = m.sds >= P.contact_duration_threshold_steps;
-      crit[DEX_C_BOX_TOO_FAR] = m.boxfar;
-      const bool pregrasp_failed = m.j2 && !(m.hcok && m.sok);  // _evaluate_pregrasp_quality :1334-1364
-      const bool contact_failed = m.j3 && !m.grasp;
-      const bool grasp_lost = (m.stage == 3) && !m.grasp;
+      const bool grasp = wk[LY::W_GRASP * 32] != 0.0f;
+      const bool j2 = wk[LY::W_J2 * 32] != 0.0f, j3 = wk[LY::W_J3 * 32] != 0.0f;
+      const int stage = __float_as_int(wk[LY::W_STAGE * 32]);
+      const int sds = __float_as_int(wk[LY::W_SDS * 32]);
+      crit[DEX_C_GRASP_LIFT_SUCCESS] = sds >= P.contact_duration_threshold_steps;
+      crit[DEX_C_BOX_TOO_FAR] = wk[LY::W_BOXFAR * 32] != 0.0f;
+      const bool pregrasp_failed = j2 && (wk[LY::W_QUALOK * 32] == 0.0f);  // _evaluate_pregrasp_quality :1334-1364
+      const bool contact_failed = j3 && !grasp;
+      const bool grasp_lost = (stage == 3) && !grasp;
       crit[DEX_C_STAGE1_PREGRASP_FAILED] = pregrasp_failed;
       crit[DEX_C_STAGE2_CONTACT_FAILED] = contact_failed;
       crit[DEX_C_STAGE3_GRASP_LOST] = grasp_lost;
@@ -919,9 +918,11 @@ __device__ __forceinline__ unsigned part_terminate(const Post2Args& A, const Cx<
   // reset ballot word + cross-env counters (termination_manager.py:164-185,259-266)
   const unsigned fullmask = 0xffffffffu;
   const unsigned rbits = __ballot_sync(fullmask, should_reset);
-  rbits_out = rbits;
   const int lane = c.lane;
-  if (lane == 0) A.out.reset_bits[c.e0 >> 5] = rbits;
+  if (lane == 0) {
+    A.out.reset_bits[c.e0 >> 5] = rbits;
+    *s_rbits = rbits;
+  }
   const unsigned bs = __ballot_sync(fullmask, t_success), bf = __ballot_sync(fullmask, t_failure),
                  bt = __ballot_sync(fullmask, t_timeout);
   unsigned bc[DEX_NUM_CRITERIA];
@@ -959,19 +960,20 @@ __device__ __forceinline__ unsigned part_terminate(const Post2Args& A, const Cx<
   return (t_success ? 1u : 0u) | (t_failure ? 2u : 0u) | (t_timeout ? 4u : 0u);
 }
 
-// ---- ordered weighted sum (reward_calculator.py:223-275) + termination rewards
-//      (termination_manager.py:280-321, step_processor.py:204-219)
+// phase D, warp 0: ordered weighted sum (reward_calculator.py:223-275) + termination rewards
+// (termination_manager.py:280-321, step_processor.py:204-219)
 template <bool BG, bool STD>
-__device__ __forceinline__ void part_total(const Post2Args& A, const Cx<BG, STD>& c, const unsigned cls) {
+__device__ __forceinline__ void phase_total(const Post2Args& A, const Cx<BG, STD>& c, const unsigned cls) {
+  using LY = Lay<BG>;
+  if (!c.act) return;
   const DexParams& P = A.p;
-  constexpr int I0 = BG ? DEX_NUM_COMMON_TERMS : 0, I1 = BG ? DEX_NUM_REWARD_TERMS : DEX_NUM_COMMON_TERMS;
-  float wv[I1 - I0];
-#pragma unroll
-  for (int i = I0; i < I1; ++i) wv[i - I0] = c.wk[(Lay<BG>::W_WGT + i) * 32];  // zero-weight terms hold stale values: skipped below
+  const float* wk = c.wk;
   float total = 0.0f;
 #pragma unroll
-  for (int i = I0; i < I1; ++i)
-    if (STD || P.reward_weight[i] != 0.0f) total += wv[i - I0];  // dict order: common, then task
+  for (int i = 0; i < DEX_NUM_REWARD_TERMS; ++i) {
+    if (!BG && i >= DEX_NUM_COMMON_TERMS) break;
+    if (STD || P.reward_weight[i] != 0.0f) total += wk[(LY::W_WGT + i) * 32];  // dict order: common, then task
+  }
   const bool t_success = cls & 1u, t_failure = cls & 2u, t_timeout = cls & 4u;
   const float rs = t_success ? P.success_reward : 0.0f;
   const float rf = t_failure ? P.failure_reward : 0.0f;
@@ -986,6 +988,15 @@ __device__ __forceinline__ void part_total(const Post2Args& A, const Cx<BG, STD>
 #pragma unroll
   for (int k = 0; k < 6; ++k) g[(size_t)(P.termination_row + k) * c.N] = tv[1 + k];
   A.out.rew_buf[c.env] = rew;
+}
+
+
+__device__ __forceinline__ void cons_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kConsThreads) : "memory"); }
+
+// shared -> global bulk store of the flat obs tile (TMA engine): one instruction for 20 KB
+__device__ __forceinline__ void bulk_s2g(void* dst, const uint32_t src, const uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
 }
 
 // obs tile -> obs_buf with row copies (ragged tiles, layouts whose flat tile would bank-conflict): the env rows are spread
@@ -1012,178 +1023,11 @@ __device__ __forceinline__ void copy_obs_rows(const float* s_obs, float* g_tile,
   }
 }
 
-// phase A: everything that depends only on the staged tile.  One fixed job per consumer warp, straight-line code; the
-// values another warp needs later go to the work block.
-template <bool BG, bool STD>
-__device__ __forceinline__ void phase_a(const Post2Args& A, const Cx<BG, STD>& c, const int cw) {
-  using LY = Lay<BG>;
-  float* wk = c.wk;
-  Mid m;
-  switch (cw) {
-    case 0:  // tips
-      part_poses<BG, STD, false>(A, c, m);
-      wk[LY::W_HITG * 32] = m.hitg ? 1.0f : 0.0f;
-      if (BG) wk[LY::W_MINTIPBOX * 32] = m.min_tip_box;
-      else wk[LY::W_MINTIPZ * 32] = m.min_tip_z;
-      break;
-    case 1:  // pads
-      part_poses<BG, STD, true>(A, c, m);
-      if (BG) {
-#pragma unroll
-        for (int f = 0; f < DEX_NUM_FINGERS; ++f) wk[(LY::W_PADBOX + f) * 32] = m.padbox[f];
-        wk[LY::W_AVGHDIFF * 32] = m.avg_hdiff;
-        wk[LY::W_CDIST * 32] = m.cdist;
-        wk[LY::W_HCOK * 32] = m.hcok ? 1.0f : 0.0f;
-      }
-      break;
-    case 2:  // contact sensors, box stability
-      part_contacts<BG, STD>(A, c, m);
-      if (BG) {
-#pragma unroll
-        for (int f = 0; f < DEX_NUM_FINGERS; ++f) wk[(LY::W_BIN + f) * 32] = m.bin[f];
-        wk[LY::W_BOXHAS * 32] = m.boxhas ? 1.0f : 0.0f;
-        wk[LY::W_DRIFT * 32] = m.drift;
-        wk[LY::W_VMAG * 32] = m.vmag;
-        wk[LY::W_SOK * 32] = m.sok ? 1.0f : 0.0f;
-      } else {
-        wk[LY::W_CHG * 32] = m.chg;
-      }
-      break;
-    case 3:  // hand, copies
-      part_hand<BG, STD>(A, c, m);
-      if (BG) {
-        wk[LY::W_BOXFAR * 32] = m.boxfar ? 1.0f : 0.0f;
-      } else {
-#pragma unroll
-        for (int k = 0; k < 4; ++k) wk[(LY::W_RHAND + k) * 32] = m.rhand[k];
-      }
-      part_copies<BG, STD>(A, c);
-      break;
-    case 4: part_dofs<BG, STD, 0, 4>(A, c, m); break;
-    case 5: part_dofs<BG, STD, 4, 7>(A, c, m); break;
-    case 6: part_dofs<BG, STD, 7, 10>(A, c, m); break;
-    default: part_dofs<BG, STD, 10, 13>(A, c, m); break;
-  }
-}
-
-// work block -> the inputs of part_task_state / part_task_terms / part_terminate
-template <bool BG>
-__device__ __forceinline__ void import_mid(const float* wk, Mid& m) {
-  using LY = Lay<BG>;
-  m.hitg = wk[LY::W_HITG * 32] != 0.0f;
-  if (BG) {
-#pragma unroll
-    for (int f = 0; f < DEX_NUM_FINGERS; ++f) {
-      m.bin[f] = wk[(LY::W_BIN + f) * 32];
-      m.padbox[f] = wk[(LY::W_PADBOX + f) * 32];
-    }
-    m.boxhas = wk[LY::W_BOXHAS * 32] != 0.0f;
-    m.boxfar = wk[LY::W_BOXFAR * 32] != 0.0f;
-    m.hcok = wk[LY::W_HCOK * 32] != 0.0f;
-    m.sok = wk[LY::W_SOK * 32] != 0.0f;
-  }
-}
-
-// phase C, warps 1..7: the reward terms (BlindGrasping: behind a private copy of the task-state chain)
-template <bool BG, bool STD, int CW>
-__device__ __forceinline__ void phase_c_terms(const Post2Args& A, const Cx<BG, STD>& c) {
-  if constexpr (BG) {
-    Mid m;
-    import_mid<true>(c.wk, m);
-    part_task_state<STD, false>(A, c, m);
-    part_task_terms<STD, CW>(A, c, m);
-  } else {
-    part_common_terms<STD, CW>(A, c);
-  }
-}
-
-__device__ __forceinline__ void cons_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kConsThreads) : "memory"); }
-
-// shared -> global bulk store of the flat obs tile (TMA engine): one instruction for 20 KB
-__device__ __forceinline__ void bulk_s2g(void* dst, const uint32_t src, const uint32_t bytes) {
-  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src), "r"(bytes) : "memory");
-  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-}
-
-// one tile on the 8 consumer warps: phase A | barrier | phase C | barrier | phase D | barrier
-template <bool BG, bool STD, bool FULL>
-__device__ __forceinline__ void consume_tile(const Post2Args& A, Cx<BG, STD>& c, const int warp, const int it, const unsigned stamp_in,
-                                             unsigned long long* s_rng_step, unsigned* s_rbits, unsigned& stamp, uint64_t& rng_step,
-                                             const uint32_t bar_empty_s, float* s_obs, float* s_reset_u, bool& store_pending TL2_PARAM) {
-  const int lane = c.lane, tid = warp * 32 + lane;
-  // Philox step counter == stamp of this step's tile records: read once per CTA, behind the first full barrier (i.e.
-  // behind the producers' griddepcontrol.wait; the epilogue CTA advances it only after every record of this launch is out)
-  unsigned long long rs_tmp = 0ull;
-  if (it == 0 && tid == 0) rs_tmp = A.st.rng_step ? *reinterpret_cast<const volatile unsigned long long*>(A.st.rng_step) : A.step;
-  if (FULL || c.act) phase_a<BG, STD>(A, c, warp);
-  if (it == 0 && tid == 0) *s_rng_step = rs_tmp;
-  TL2(it, 2);
-  cons_sync();
-  TL2(it, 3);
-  if (it == 0) {
-    rng_step = *s_rng_step;
-    stamp = ((unsigned)rng_step + 1u) & 0xffffu;
-  }
-  (void)stamp_in;
-  // ---- phase C: warp 0 = task state + termination + tile record; warps 1..7 = reward terms ----
-  unsigned cls = 0;
-  if (warp == 0) {
-    Mid m;
-    if (FULL || c.act) {
-      import_mid<BG>(c.wk, m);
-      if constexpr (BG) part_task_state<STD, true>(A, c, m);
-    }
-    unsigned rbits;
-    cls = part_terminate<BG, STD, FULL>(A, c, m, stamp, rbits);
-    if (lane == 0) *s_rbits = rbits;
-  } else if (FULL || c.act) {
-    switch (warp) {
-      case 1: phase_c_terms<BG, STD, 1>(A, c); break;
-      case 2: phase_c_terms<BG, STD, 2>(A, c); break;
-      case 3: phase_c_terms<BG, STD, 3>(A, c); break;
-      case 4: phase_c_terms<BG, STD, 4>(A, c); break;
-      case 5: phase_c_terms<BG, STD, 5>(A, c); break;
-      case 6: phase_c_terms<BG, STD, 6>(A, c); break;
-      default: phase_c_terms<BG, STD, 7>(A, c); break;
-    }
-  }
-  const bool bulk_out = FULL && A.obs_bulk;
-  if (bulk_out) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // obs tile writes -> visible to the bulk store
-  __syncwarp();
-  TL2(it, 4);
-  cons_sync();
-  TL2(it, 5);
-  // the raw stage is not read after this point: hand it back to the producers
-  if (lane == 0) mbar_arrive(bar_empty_s);
-  // ---- phase D: total, obs tile out, fused reset ----
-  if (warp == 0 && (FULL || c.act)) part_total<BG, STD>(A, c, cls);
-  const int W = A.p.obs_dim;
-  float* const g_obs = A.out.obs_buf + (size_t)c.e0 * W;
-  if (bulk_out) {
-    if (tid == 32) {
-      bulk_s2g(g_obs, s32(s_obs), (uint32_t)(32 * W * 4));
-      store_pending = true;
-    }
-  } else {
-    copy_obs_rows(s_obs, g_obs, W, A.wp, c.ne, warp, lane);
-  }
-  {
-    unsigned mask = *s_rbits;  // written by warp 0 before the barrier above
-    if (mask && !(A.flags & DEX_FLAG_NO_FUSED_RESET)) {  // fused reset (dexhand_base.py:743-756): one warp per env
-      for (int k = 0; mask; ++k) {
-        const int e = __ffs(mask) - 1;
-        mask &= mask - 1;
-        if ((k & (kConsWarps - 1)) == warp) reset_env_warp<BG>(A, c.e0 + e, rng_step, s_reset_u + 32 * warp);
-      }
-    }
-  }
-  if (bulk_out && tid == 32) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // obs tile may be rewritten
-  TL2(it, 7);
-  cons_sync();  // work block, obs tile and s_rbits are reused by the next tile
-}
-
 // ------------------------------------------------------------------------------------------------
-// the kernel: persistent, 8 consumer + 4 producer warps per CTA, 2-stage ring, two CTAs per SM (BlindGrasping)
+// the kernel: persistent, 8 consumer + 4 producer warps per CTA, 2-stage ring, two CTAs per SM (BlindGrasping).
+// Instruction supply is the scarce resource of this path (profiles/r02_variants.md): the consumer warps run the SAME
+// item code on different items at the same time (one fetched line serves all), loops are not unrolled, and a warp that
+// waits blocks in hardware (bar.sync behind one polling warp) instead of spinning through fetch slots.
 // ------------------------------------------------------------------------------------------------
 template <bool BG, bool STD>
 __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(const __grid_constant__ Post2Args A) {
@@ -1210,6 +1054,7 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
           reinterpret_cast<const volatile unsigned long long*>(A.ep.tile_records) + (size_t)(A.tiles - 1);  // plane 0
       const long long t0 = clock64();
       while ((unsigned)(last[0] >> 48) != stamp) {
+        __nanosleep(100);
         if (clock64() - t0 > kSpinLimitClocks) __trap();  // bounded: see mbar_wait
       }
       s_rng_step = rs;
@@ -1265,10 +1110,13 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
     const float* const x_base = (is_box ? (const float*)A.sim.actor_root_state : A.sim.net_contact_force) + xoff;
     const size_t nb13 = (size_t)A.p.num_bodies * 13;
     const size_t rb_step = kProdWarps * nb13, x_step = (size_t)kProdWarps * xrow;
+    const size_t N = (size_t)A.n;
     const bool early = (A.flags & DEX_FLAG_EARLY_SIM_LOADS) != 0;
-    const int n_rows = A.n_bulk;
+    const bool prev_state = !BG && A.common && !A.first;
+    const DexStateBuffers& st = A.st;
     constexpr int R = 32 / kProdWarps;  // env rows per producer warp
     int it = 0;
+#pragma unroll 1
     for (int tile = blockIdx.x; tile < tiles; tile += workers, ++it) {
       const int s = it & 1, use = it >> 1;
       const int e0 = tile * 32, ne = min(32, A.n - e0);
@@ -1277,34 +1125,28 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
       TL2(it, 16);
       if (use > 0) mbar_wait(bar_empty + 8 * s, (unsigned)(use - 1) & 1u);
       TL2(it, 17);
-      const bool full = ne == 32;               // CTA-uniform
-      const bool bulk = A.bulk_ok && full;      // the two AoS tiles (dof_state, full_dof_targets) as bulk copies
-      const bool split = it == 0 && early;      // first tile: the state rows wait for griddepcontrol.wait, the sim rows do not
+      const bool full = ne == 32;           // CTA-uniform
+      const bool bulk = A.bulk_ok && full;  // the AoS tiles (dof_state, full_dof_targets) as ONE bulk copy each
+      const bool split = it == 0 && early;  // first tile: the state rows wait for griddepcontrol.wait, the sim rows do not
       const bool act = lane < ne;
       if (it == 0 && !early) pdl_wait();
-      // table entry k: [0, n_bulk_early) sim-tensor tiles (dof_state) | state tiles (full_dof_targets) | state rows
-      auto issue_tiles = [&](const int k0, const int k1) {
-        for (int k = k0; k < k1; ++k) {
-          const int kind = A.bk_kind[k];
-          if (kind != BK_DOF && kind != BK_TGT) break;
-          const uint32_t len = (uint32_t)A.bk_len16[k] * 16u;
-          const char* src = reinterpret_cast<const char*>(A.bk_ptr[k]) + (size_t)tile * len;
-          const uint32_t dst = sst + (uint32_t)A.bk_dst16[k] * 16u;
-          if (bulk) {
-            if (pw == 0 && lane == 0) bulk_g2s(dst, src, len, fb);
-          } else {  // ragged tile / unaligned base: 4-byte asynchronous copies of the contiguous block
-            const int nfl = ne * (kind == BK_DOF ? 52 : 26);
-            for (int i = pw * 32 + lane; i < nfl; i += kProdThreads) cpa4(dst + 4u * i, src + 4 * i);
-          }
+      // a contiguous AoS tile: one bulk copy, or (ragged tile / unaligned base) 4-byte asynchronous copies
+      auto aos_tile = [&](const float* base, const int per, const int off) {
+        const float* src = base + (size_t)e0 * per;
+        if (bulk) {
+          if (pw == 0 && lane == 0) bulk_g2s(sst + off, src, (uint32_t)(32 * per * 4), fb);
+        } else {
+#pragma unroll 1
+          for (int i = pw * 32 + lane; i < ne * per; i += kProdThreads) cpa4(sst + off + 4u * i, src + i);
         }
       };
-      issue_tiles(0, A.n_bulk_early);
+      aos_tile(A.sim.dof_state, 52, LY::OFF_DOF);
       // ---- scattered Isaac Gym rows: warp pw takes env rows pw, pw+4, ..; consecutive lanes = consecutive floats ----
       {
         const float* q0 = A.sim.rigid_body_state + (size_t)(e0 + pw) * nb13;
         const float* qx = x_base + (size_t)(e0 + pw) * xrow;
         uint32_t a = sst + LY::OFF_AOS + (uint32_t)(pw * LY::SA + lane) * 4u;
-#pragma unroll
+#pragma unroll 1
         for (int i = 0; i < R; ++i) {
           if (full || pw + kProdWarps * i < ne) {
             if (p_rb0) cpa4(a + LY::A_RB * 4, q0 + rbo0);
@@ -1319,24 +1161,47 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
       }
       TL2(it, 18);
       if (split) pdl_wait();  // everything above touched only kernel parameters and the sim tensors
-      issue_tiles(A.n_bulk_early, n_rows);
-      // ---- SoA state rows: lane = env, one 128-byte line per row; row k of the table goes to warp k % 4 ----
-      for (int k = A.n_tile_entries + pw; k < n_rows; k += kProdWarps) {
-        const int kind = A.bk_kind[k];
-        const char* src = reinterpret_cast<const char*>(A.bk_ptr[k]);
-        const uint32_t dst = sst + (uint32_t)A.bk_dst16[k] * 16u;
-        if (kind == BK_F32) {
-          if (act) cpa4(dst + 4u * lane, src + ((size_t)e0 + lane) * 4);
-        } else if (kind == BK_I64) {
-          if (act) cpa8(dst + 8u * lane, src + ((size_t)e0 + lane) * 8);
-        } else {  // BK_U8: 32 bytes of a bool row
+      if (!BG && A.want_tgt) aos_tile(st.full_dof_targets, 26, LY::OFF_TGT);
+      // ---- SoA state rows: lane = env, one 128-byte line per row; row r of a buffer goes to warp r % 4 ----
+      auto rows = [&](const float* base, const int nrows, const int r0) {
+        const float* src = base + (size_t)pw * N + e0 + lane;
+        uint32_t dst = sst + (uint32_t)(r0 + pw) * 128u + 4u * lane;
+#pragma unroll 1
+        for (int r = pw; r < nrows; r += kProdWarps) {
+          if (act) cpa4(dst, src);
+          src += kProdWarps * N;
+          dst += kProdWarps * 128u;
+        }
+      };
+      auto row64 = [&](const int64_t* base, const int slot) {
+        if (act) cpa8(sst + LY::OFF_I64 + slot * 256 + 8u * lane, base + e0 + lane);
+      };
+      rows(st.prev_dof_pos, DEX_NUM_DOF, LY::R_PDP);
+      rows(st.active_prev_targets, DEX_NUM_ACTIVE, LY::R_APT);
+      rows(st.prev_actions, A.p.num_actions, LY::R_PACT);
+      rows(st.contact_duration_steps, DEX_NUM_FINGERS, LY::R_CDUR);
+      rows(st.prev_contact_binary, DEX_NUM_FINGERS, LY::R_PBIN);
+      if (BG) {
+        rows(st.initial_box_positions, 3, LY::R_BOX0);
+        if (pw == 3 && act) cpa4(sst + LY::R_TIS * 128u + 4u * lane, st.time_in_stage + e0 + lane);  // single rows
+        if (pw == 0 && act) cpa4(sst + LY::R_SCD * 128u + 4u * lane, st.stage_contact_duration + e0 + lane);
+        if (pw == 1) row64(st.success_duration_steps, LY::I_SDS);
+        if (pw == 2) row64(st.current_stage, LY::I_STAGE);
+      } else if (prev_state) {
+        rows(st.prev_finger_dof_vel, DEX_NUM_FINGER_DOF, LY::R_PFDV);
+        rows(st.prev_hand_vel, 3, LY::R_PHV);
+        rows(st.prev_hand_ang_vel, 3, LY::R_PHA);
+        // prev_contacts: 5 bool rows of 32 bytes
+        for (int f = pw; f < DEX_NUM_FINGERS; f += kProdWarps) {
+          const unsigned char* src = st.prev_contacts + (size_t)f * N + e0;
           if (full && (A.n & 3) == 0) {
-            if (lane < 8) cpa4(dst + 4u * lane, src + (size_t)e0 + 4 * lane);
+            if (lane < 8) cpa4(sst + LY::OFF_U8 + f * 32 + 4u * lane, src + 4 * lane);
           } else if (act) {
-            stage[(size_t)A.bk_dst16[k] * 16 + lane] = *reinterpret_cast<const unsigned char*>(src + (size_t)e0 + lane);
+            stage[LY::OFF_U8 + f * 32 + lane] = src[lane];
           }
         }
       }
+      if (pw == 3) row64(st.episode_step_count, LY::I_STEP);
       cpa_arrive(fb);  // counted arrival when every asynchronous copy of this thread has landed
       __syncwarp();
       TL2(it, 19);
@@ -1353,6 +1218,7 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
   // =========================== consumer warps ===========================
   Cx<BG, STD> c;
   c.lane = lane;
+  c.cw = warp;
   c.N = (size_t)A.n;
   c.wk = wk_base + lane;
   c.obs = s_obs + lane * A.wp;
@@ -1361,7 +1227,9 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
   unsigned stamp = 0;
   uint64_t rng_step = 0;
   bool store_pending = false;
+  const int W = A.p.obs_dim;
   int it = 0;
+#pragma unroll 1
   for (int tile = blockIdx.x; tile < tiles; tile += workers, ++it) {
     const int s = it & 1, use = it >> 1;
     c.e0 = tile * 32;
@@ -1369,16 +1237,70 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
     c.act = lane < c.ne;
     c.env = (size_t)c.e0 + (c.act ? lane : 0);
     c.stage = smem2 + s * LY::STAGE_BYTES;
+    float* const g_obs = A.out.obs_buf + (size_t)c.e0 * W;
+    const bool bulk_out = A.obs_bulk && c.ne == 32;  // CTA-uniform
     TL2(it, 0);
-    mbar_wait(bar_full + 8 * s, (unsigned)use & 1u);
+    // ONE warp polls the stage's mbarrier, the other seven block in hardware behind it
+    if (warp == 0) mbar_wait(bar_full + 8 * s, (unsigned)use & 1u);
+    // Philox step counter == stamp of this step's tile records: read once per CTA, behind the first full barrier (i.e.
+    // behind the producers' griddepcontrol.wait; the epilogue CTA advances it only after every record of this launch is out)
+    if (it == 0 && tid == 0) s_rng_step = A.st.rng_step ? *reinterpret_cast<const volatile unsigned long long*>(A.st.rng_step) : A.step;
+    cons_sync();
     TL2(it, 1);
-    if (c.ne == 32)  // CTA-uniform
-      consume_tile<BG, STD, true>(A, c, warp, it, 0u, &s_rng_step, &s_rbits, stamp, rng_step, bar_empty + 8 * s, s_obs, s_reset_u,
-                                  store_pending TL2_ARG);
-    else
-      consume_tile<BG, false, false>(A, reinterpret_cast<Cx<BG, false>&>(c), warp, it, 0u, &s_rng_step, &s_rbits, stamp, rng_step,
-                                     bar_empty + 8 * s, s_obs, s_reset_u, store_pending TL2_ARG);
+    if (it == 0) {
+      rng_step = s_rng_step;
+      stamp = ((unsigned)rng_step + 1u) & 0xffffu;
+    }
+    phase_items<BG, STD>(A, c);
+    TL2(it, 2);
+    cons_sync();
+    TL2(it, 3);
+    phase_scalar<BG, STD>(A, c);
+    TL2(it, 4);
+    cons_sync();
+    TL2(it, 5);
+    unsigned cls = 0;
+    if (warp == 0) {
+      cls = phase_combine<BG, STD>(A, c, stamp, &s_rbits);
+    } else if (BG) {
+      if (c.act) {
+#pragma unroll 1
+        for (int i = DEX_NUM_COMMON_TERMS + (warp - 1); i < DEX_NUM_REWARD_TERMS; i += kConsWarps - 1)
+          emit_term<BG, STD>(A, c, i, task_term<BG, STD>(A, c, i));
+      }
+    }
+    if (bulk_out) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // obs tile writes -> visible to the bulk store
+    __syncwarp();
     TL2(it, 6);
+    cons_sync();
+    TL2(it, 7);
+    // the raw stage is not read after this point: hand it back to the producers
+    if (lane == 0) mbar_arrive(bar_empty + 8 * s);
+    if (warp == 0) phase_total<BG, STD>(A, c, cls);
+    TL2(it, 8);
+    if (bulk_out) {
+      if (tid == 32) {
+        bulk_s2g(g_obs, s32(s_obs), (uint32_t)(32 * W * 4));
+        store_pending = true;
+      }
+    } else {
+      copy_obs_rows(s_obs, g_obs, W, A.wp, c.ne, warp, lane);
+    }
+    TL2(it, 9);
+    {
+      unsigned mask = s_rbits;  // written by warp 0 before the barrier above
+      if (mask && !(A.flags & DEX_FLAG_NO_FUSED_RESET)) {  // fused reset (dexhand_base.py:743-756): one warp per env
+        for (int k = 0; mask; ++k) {
+          const int e = __ffs(mask) - 1;
+          mask &= mask - 1;
+          if ((k & (kConsWarps - 1)) == warp) reset_env_warp<BG>(A, c.e0 + e, rng_step, s_reset_u + 32 * warp);
+        }
+      }
+    }
+    if (bulk_out && tid == 32) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // obs tile may be rewritten
+    TL2(it, 10);
+    cons_sync();  // work block, obs tile and s_rbits are reused by the next tile
+    TL2(it, 11);
   }
   if (store_pending) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // the last obs tile has left shared memory
 }

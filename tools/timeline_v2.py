@@ -71,10 +71,11 @@ t = runs[0]
 used = (t[:, 0, 0] > 0)
 print(f"envs {n} task {task}: {int(used.sum())} worker CTAs; tiles per CTA: "
       f"{ {k: int(((t[:, :, 1] > 0).sum(dim=1) == k).sum()) for k in range(1, ITERS + 1) if int(((t[:, :, 1] > 0).sum(dim=1) == k).sum())} }")
-cons = [((0, 1), "wait full (load latency seen by the consumers)"), ((1, 2), "phase A: per-warp jobs (warp 0: tips)"),
-        ((2, 3), "  barrier A"), ((3, 4), "phase C: warp 0 task state + termination + record"), ((4, 5), "  barrier C"),
-        ((5, 7), "phase D: total, obs store issue, reset (warp 0)"), ((7, 6), "  barrier D"), ((0, 6), "whole tile (consumer)")]
-prod = [((16, 17), "producer: wait empty"), ((17, 18), "producer: bulk issue + gather issue"), ((18, 19), "producer: data wait + STS + arrive")]
+cons = [((0, 1), "wait full (load latency seen by consumers)"), ((1, 2), "items (thread 0's warp)"), ((2, 3), "  barrier A"),
+        ((3, 4), "scalar jobs (warp 0)"), ((4, 5), "  barrier B"), ((5, 6), "combine + record (warp 0)"), ((6, 7), "  barrier C"),
+        ((7, 8), "total (warp 0)"), ((8, 9), "obs tile out"), ((9, 10), "reset + store read wait"), ((10, 11), "  barrier D"),
+        ((0, 11), "whole tile (consumer)")]
+prod = [((16, 17), "producer: wait empty"), ((17, 18), "producer: dof tile + gather issue"), ((18, 19), "producer: state rows issue")]
 for it in range(ITERS):
     if not any(bool((r[:, it, 1] > 0).any()) for r in runs):
         break
@@ -102,7 +103,7 @@ def ends(r):
     out = []
     for cta in torch.nonzero(m).flatten().tolist():
         li = int(last_it[cta])
-        out.append(float(r[cta, li, 30] - t0) / 1e3 + float(r[cta, li, 6] - r[cta, li, 0]) / GHZ)
+        out.append(float(r[cta, li, 30] - t0) / 1e3 + float(r[cta, li, 11] - r[cta, li, 0]) / GHZ)
     return out
 
 
