@@ -968,10 +968,11 @@ __device__ __forceinline__ void phase_total(const Post2Args& A, const Cx<BG, STD
   if (!c.act) return;
   const DexParams& P = A.p;
   const float* wk = c.wk;
+  // STD: exactly the task's own terms are materialised (BlindGrasping: the 16 task terms, BaseTask: the 10 common ones)
+  constexpr int I0 = (STD && BG) ? DEX_NUM_COMMON_TERMS : 0, I1 = BG ? DEX_NUM_REWARD_TERMS : DEX_NUM_COMMON_TERMS;
   float total = 0.0f;
 #pragma unroll
-  for (int i = 0; i < DEX_NUM_REWARD_TERMS; ++i) {
-    if (!BG && i >= DEX_NUM_COMMON_TERMS) break;
+  for (int i = I0; i < I1; ++i) {
     if (STD || P.reward_weight[i] != 0.0f) total += wk[(LY::W_WGT + i) * 32];  // dict order: common, then task
   }
   const bool t_success = cls & 1u, t_failure = cls & 2u, t_timeout = cls & 4u;
