@@ -32,7 +32,9 @@ constexpr int kMaxBulk = 128;  // rows / tile arrays of one tile (the plain-load
 enum : int { BK_F32 = 0, BK_I64 = 1, BK_U8 = 2, BK_DOF = 3, BK_TGT = 4 };
 
 // ---- shared-memory layout of one stage (bytes) and of the work block (fields of 32 floats) ----
-template <bool BG>
+// AL: the single-pass geometry (one tile per CTA, four CTAs per SM) folds the work block into the stage: fields that are
+// written after phase A alias state rows that are dead by then, the phase-A fields sit right behind the stage
+template <bool BG, bool AL = false>
 struct Lay {
   // SoA state rows, [row][32] floats
   static constexpr int R_PDP = 0, R_APT = 26, R_PACT = 44, R_CDUR = 62, R_PBIN = 67;
@@ -51,16 +53,22 @@ struct Lay {
   static constexpr int A_RB = 0, A_CF = 83, A_BOX = 101;     // hand row 13 | 5 tips x 7 | 5 pads x 7 ; contacts ; box
   static constexpr int SA = BG ? 107 : 99;
   static constexpr int STAGE_BYTES = (OFF_AOS + 32 * SA * 4 + 127) / 128 * 128;
-  // work block: values that cross a warp or a phase, [field][32] floats (lane = env: conflict-free)
-  static constexpr int W_BIN = 0, W_PADBOX = 5, W_HDIFF = 10, W_TIPBOX = 15;
-  static constexpr int W_CDIST = 20, W_DRIFT = 21, W_VMAG = 22, W_BOXHAS = 23, W_HANDBOX = 24;
-  static constexpr int W_BVEL = 25;  // 6
-  static constexpr int W_GRASP = 31, W_THUMB = 32, W_OTHERS = 33, W_GRASPDUR = 34, W_SDS = 35, W_STAGE = 36, W_J2 = 37,
-                       W_J3 = 38;
-  static constexpr int W_HITG = 39, W_BOXFAR = 40, W_QUALOK = 41, W_MINTIPBOX = 42, W_AVGHDIFF = 43;
-  static constexpr int W_CHG = 44, W_RHAND = 49, W_FV2 = 53, W_FA2 = 73, W_JL = 93;  // BaseTask (common rewards)
-  static constexpr int W_WGT = BG ? 44 : 113;  // 26 weighted reward terms
-  static constexpr int W_COUNT = W_WGT + DEX_NUM_REWARD_TERMS;
+  // work block: values that cross a warp or a phase, [field][32] floats (lane = env: conflict-free), indexed from WK0:
+  // !AL: a block of its own (WK0 = 0).  AL: indexed from the stage base in 128-byte rows - the phase-A fields behind the stage
+  // (row STAGE_BYTES / 128 on), the phase-B fields over the active_prev_targets rows and the weighted terms over the
+  // prev_dof_pos rows (both only read in phase A)
+  static constexpr int WKA = AL ? STAGE_BYTES / 128 : 0;        // phase-A fields
+  static constexpr int W_BIN = WKA + 0, W_PADBOX = WKA + 5, W_HDIFF = WKA + 10, W_TIPBOX = WKA + 15;
+  static constexpr int W_CDIST = WKA + 20, W_DRIFT = WKA + 21, W_VMAG = WKA + 22, W_BOXHAS = WKA + 23, W_HANDBOX = WKA + 24;
+  static constexpr int W_BVEL = WKA + 25;  // 6
+  static constexpr int NWKA = 31;
+  static constexpr int WKB = AL ? R_APT : 31;                   // phase-B fields (13)
+  static constexpr int W_GRASP = WKB + 0, W_THUMB = WKB + 1, W_OTHERS = WKB + 2, W_GRASPDUR = WKB + 3, W_SDS = WKB + 4,
+                       W_STAGE = WKB + 5, W_J2 = WKB + 6, W_J3 = WKB + 7;
+  static constexpr int W_HITG = WKB + 8, W_BOXFAR = WKB + 9, W_QUALOK = WKB + 10, W_MINTIPBOX = WKB + 11, W_AVGHDIFF = WKB + 12;
+  static constexpr int W_CHG = 44, W_RHAND = 49, W_FV2 = 53, W_FA2 = 73, W_JL = 93;  // BaseTask (common rewards; !AL only)
+  static constexpr int W_WGT = AL ? R_PDP : (BG ? 44 : 113);    // 26 weighted reward terms
+  static constexpr int W_COUNT = AL ? NWKA : W_WGT + DEX_NUM_REWARD_TERMS;  // rows of the separate block
 };
 
 
@@ -387,9 +395,9 @@ struct Cx {
 };
 
 // phase A: per-env work items, taken round-robin by the 8 consumer warps (item type is warp-uniform)
-template <bool BG, bool STD>
+template <bool BG, bool STD, bool AL>
 __device__ __forceinline__ void phase_items(const Post2Args& A, const Cx<BG, STD>& c) {
-  using LY = Lay<BG>;
+  using LY = Lay<BG, AL>;
   if (!c.act) return;
   const DexParams& P = A.p;
   const DexStateBuffers& st = A.st;
@@ -627,9 +635,9 @@ __device__ __forceinline__ void phase_items(const Post2Args& A, const Cx<BG, STD
 }
 
 // one common reward term (reward_calculator.py:66-221); BaseTask, phase B
-template <bool BG, bool STD>
+template <bool BG, bool STD, bool AL>
 __device__ __forceinline__ float common_term(const Post2Args& A, const Cx<BG, STD>& c, const int i) {
-  using LY = Lay<BG>;
+  using LY = Lay<BG, AL>;
   const float* wk = c.wk;
   const float* rb = c.aos() + LY::A_RB;
   switch (i) {
@@ -672,9 +680,9 @@ __device__ __forceinline__ float common_term(const Post2Args& A, const Cx<BG, ST
 }
 
 // one BlindGrasping task term (blind_grasping_task.py:980-1208); phase C (after the FSM)
-template <bool BG, bool STD>
+template <bool BG, bool STD, bool AL>
 __device__ __forceinline__ float task_term(const Post2Args& A, const Cx<BG, STD>& c, const int i) {
-  using LY = Lay<BG>;
+  using LY = Lay<BG, AL>;
   const DexParams& P = A.p;
   const float* wk = c.wk;
   const float* aos = c.aos();
@@ -725,7 +733,7 @@ __device__ __forceinline__ float task_term(const Post2Args& A, const Cx<BG, STD>
 }
 
 // raw + weighted rows of term i leave from registers; the weighted value is parked for the ordered total
-template <bool BG, bool STD>
+template <bool BG, bool STD, bool AL>
 __device__ __forceinline__ void emit_term(const Post2Args& A, const Cx<BG, STD>& c, const int i, const float r) {
   const float w = A.p.reward_weight[i];
   if (!STD && w == 0.0f) return;  // reward_calculator.py:247-251: zero-weight terms are not materialised (STD: none is)
@@ -734,13 +742,13 @@ __device__ __forceinline__ void emit_term(const Post2Args& A, const Cx<BG, STD>&
   float* g = A.out.reward_components + c.env;
   g[(size_t)row * c.N] = r;
   g[(size_t)(row + 1) * c.N] = rw;
-  c.wk[(Lay<BG>::W_WGT + i) * 32] = rw;
+  c.wk[(Lay<BG, AL>::W_WGT + i) * 32] = rw;
 }
 
 // phase B: the per-env scalar part, split over the consumer warps (warp-uniform job index)
-template <bool BG, bool STD>
+template <bool BG, bool STD, bool AL>
 __device__ __forceinline__ void phase_scalar(const Post2Args& A, const Cx<BG, STD>& c) {
-  using LY = Lay<BG>;
+  using LY = Lay<BG, AL>;
   if (!c.act) return;
   const DexParams& P = A.p;
   const DexStateBuffers& st = A.st;
@@ -855,7 +863,7 @@ __device__ __forceinline__ void phase_scalar(const Post2Args& A, const Cx<BG, ST
     } else {
       // common reward terms over the seven other warps (0, 1, 3..7)
       for (int i = (c.cw < 2 ? c.cw : c.cw - 1); i < DEX_NUM_COMMON_TERMS; i += kConsWarps - 1) {
-        emit_term<BG, STD>(A, c, i, common_term<BG, STD>(A, c, i));
+        emit_term<BG, STD, AL>(A, c, i, common_term<BG, STD, AL>(A, c, i));
       }
     }
   }
@@ -863,9 +871,9 @@ __device__ __forceinline__ void phase_scalar(const Post2Args& A, const Cx<BG, ST
 
 // phase C, warp 0: termination (step_processor.py:133-181, termination_manager.py:120-278), masks, tile record.
 // Returns the exclusive termination class of this lane's env: bit 0 success, 1 failure, 2 timeout.
-template <bool BG, bool STD>
+template <bool BG, bool STD, bool AL>
 __device__ __forceinline__ unsigned phase_combine(const Post2Args& A, const Cx<BG, STD>& c, const unsigned stamp, unsigned* s_rbits) {
-  using LY = Lay<BG>;
+  using LY = Lay<BG, AL>;
   const DexParams& P = A.p;
   const DexStateBuffers& st = A.st;
   const float* wk = c.wk;
@@ -962,9 +970,9 @@ __device__ __forceinline__ unsigned phase_combine(const Post2Args& A, const Cx<B
 
 // phase D, warp 0: ordered weighted sum (reward_calculator.py:223-275) + termination rewards
 // (termination_manager.py:280-321, step_processor.py:204-219)
-template <bool BG, bool STD>
+template <bool BG, bool STD, bool AL>
 __device__ __forceinline__ void phase_total(const Post2Args& A, const Cx<BG, STD>& c, const unsigned cls) {
-  using LY = Lay<BG>;
+  using LY = Lay<BG, AL>;
   if (!c.act) return;
   const DexParams& P = A.p;
   const float* wk = c.wk;
@@ -991,6 +999,132 @@ __device__ __forceinline__ void phase_total(const Post2Args& A, const Cx<BG, STD
   A.out.rew_buf[c.env] = rew;
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// tile loads, shared by both geometries: NW warps issue asynchronous copies of one tile into `stage`; every thread
+// ends with one counted cp.async arrival on the stage's mbarrier, every warp with one plain arrival, and warp 0 / lane 0
+// carries the byte count of the bulk copies.
+// ------------------------------------------------------------------------------------------------
+template <bool BG>
+struct LoadCtx {
+  int rbo0, rbo1, rbo2, xrow;
+  bool p_rb0, p_rb2, p_x;
+  const float* x_base;
+  __device__ __forceinline__ void setup(const Post2Args& A, const int* s_rbo, const int lane) {
+    rbo0 = s_rbo[lane];
+    rbo1 = s_rbo[lane + 32];
+    rbo2 = s_rbo[min(lane + 64, kRbW - 1)];
+    p_rb0 = lane < 7 || lane >= 13 || A.common;  // hand velocities feed only the common reward terms
+    p_rb2 = lane + 64 < kRbW;
+    const bool is_box = BG && lane >= 18 && lane < 24;
+    p_x = is_box || lane < (BG ? 18 : 15);
+    xrow = is_box ? A.p.num_actors * 13 : A.p.num_contact_bodies * 3;
+    int xoff;
+    if (is_box) {
+      const int k = lane - 18;
+      xoff = A.p.box_actor * 13 + (k < 3 ? k : k + 4);
+    } else {
+      const int f = min(lane / 3, 5);
+      xoff = A.cf_off[f] + (lane - 3 * f);
+    }
+    x_base = (is_box ? (const float*)A.sim.actor_root_state : A.sim.net_contact_force) + xoff;
+  }
+};
+
+template <bool BG, int NW>
+__device__ __forceinline__ void issue_tile_loads(const Post2Args& A, const LoadCtx<BG>& lc, unsigned char* stage, const uint32_t fb,
+                                                 const int tile, const int pw, const int lane, const bool first) {
+  using LY = Lay<BG>;
+  const DexStateBuffers& st = A.st;
+  const size_t N = (size_t)A.n;
+  const int e0 = tile * 32, ne = min(32, A.n - e0);
+  const uint32_t sst = s32(stage);
+  const bool full = ne == 32;           // CTA-uniform
+  const bool bulk = A.bulk_ok && full;  // the AoS tiles (dof_state, full_dof_targets) as ONE bulk copy each
+  const bool early = (A.flags & DEX_FLAG_EARLY_SIM_LOADS) != 0;
+  const bool split = first && early;    // first tile: the state rows wait for griddepcontrol.wait, the sim rows do not
+  const bool act = lane < ne;
+  if (first && !early) pdl_wait();
+  // a contiguous AoS tile: one bulk copy, or (ragged tile / unaligned base) 4-byte asynchronous copies
+  auto aos_tile = [&](const float* base, const int per, const int off) {
+    const float* src = base + (size_t)e0 * per;
+    if (bulk) {
+      if (pw == 0 && lane == 0) bulk_g2s(sst + off, src, (uint32_t)(32 * per * 4), fb);
+    } else {
+#pragma unroll 1
+      for (int i = pw * 32 + lane; i < ne * per; i += NW * 32) cpa4(sst + off + 4u * i, src + i);
+    }
+  };
+  aos_tile(A.sim.dof_state, 52, LY::OFF_DOF);
+  // ---- scattered Isaac Gym rows: warp pw takes env rows pw, pw+NW, ..; consecutive lanes = consecutive floats ----
+  {
+    const size_t nb13 = (size_t)A.p.num_bodies * 13;
+    const float* q0 = A.sim.rigid_body_state + (size_t)(e0 + pw) * nb13;
+    const float* qx = lc.x_base + (size_t)(e0 + pw) * lc.xrow;
+    uint32_t a = sst + LY::OFF_AOS + (uint32_t)(pw * LY::SA + lane) * 4u;
+#pragma unroll 1
+    for (int i = 0; i < 32 / NW; ++i) {
+      if (full || pw + NW * i < ne) {
+        if (lc.p_rb0) cpa4(a + LY::A_RB * 4, q0 + lc.rbo0);
+        cpa4(a + (LY::A_RB + 32) * 4, q0 + lc.rbo1);
+        if (lc.p_rb2) cpa4(a + (LY::A_RB + 64) * 4, q0 + lc.rbo2);
+        if (lc.p_x) cpa4(a + LY::A_CF * 4, qx);
+      }
+      q0 += NW * nb13;
+      qx += (size_t)NW * lc.xrow;
+      a += NW * LY::SA * 4;
+    }
+  }
+  if (split) pdl_wait();  // everything above touched only kernel parameters and the sim tensors
+  if (!BG && A.want_tgt) aos_tile(st.full_dof_targets, 26, LY::OFF_TGT);
+  // ---- SoA state rows: lane = env, one 128-byte line per row; row r of a buffer goes to warp r % NW ----
+  auto rows = [&](const float* base, const int nrows, const int r0) {
+    const float* src = base + (size_t)pw * N + e0 + lane;
+    uint32_t dst = sst + (uint32_t)(r0 + pw) * 128u + 4u * lane;
+#pragma unroll 1
+    for (int r = pw; r < nrows; r += NW) {
+      if (act) cpa4(dst, src);
+      src += NW * N;
+      dst += NW * 128u;
+    }
+  };
+  auto row64 = [&](const int64_t* base, const int slot) {
+    if (act) cpa8(sst + LY::OFF_I64 + slot * 256 + 8u * lane, base + e0 + lane);
+  };
+  rows(st.prev_dof_pos, DEX_NUM_DOF, LY::R_PDP);
+  rows(st.active_prev_targets, DEX_NUM_ACTIVE, LY::R_APT);
+  rows(st.prev_actions, A.p.num_actions, LY::R_PACT);
+  rows(st.contact_duration_steps, DEX_NUM_FINGERS, LY::R_CDUR);
+  rows(st.prev_contact_binary, DEX_NUM_FINGERS, LY::R_PBIN);
+  if (BG) {
+    rows(st.initial_box_positions, 3, LY::R_BOX0);
+    if (pw == 3 && act) cpa4(sst + LY::R_TIS * 128u + 4u * lane, st.time_in_stage + e0 + lane);  // single rows
+    if (pw == 0 && act) cpa4(sst + LY::R_SCD * 128u + 4u * lane, st.stage_contact_duration + e0 + lane);
+    if (pw == 1) row64(st.success_duration_steps, LY::I_SDS);
+    if (pw == 2) row64(st.current_stage, LY::I_STAGE);
+  } else if (A.common && !A.first) {
+    rows(st.prev_finger_dof_vel, DEX_NUM_FINGER_DOF, LY::R_PFDV);
+    rows(st.prev_hand_vel, 3, LY::R_PHV);
+    rows(st.prev_hand_ang_vel, 3, LY::R_PHA);
+    for (int f = pw; f < DEX_NUM_FINGERS; f += NW) {  // prev_contacts: 5 bool rows of 32 bytes
+      const unsigned char* src = st.prev_contacts + (size_t)f * N + e0;
+      if (full && (A.n & 3) == 0) {
+        if (lane < 8) cpa4(sst + LY::OFF_U8 + f * 32 + 4u * lane, src + 4 * lane);
+      } else if (act) {
+        stage[LY::OFF_U8 + f * 32 + lane] = src[lane];
+      }
+    }
+  }
+  if (pw == 3) row64(st.episode_step_count, LY::I_STEP);
+  cpa_arrive(fb);  // counted arrival when every asynchronous copy of this thread has landed
+  __syncwarp();
+  if (lane == 0) {
+    if (pw == 0 && bulk)
+      mbar_arrive_tx(fb, A.tx_bytes);
+    else
+      mbar_arrive(fb);
+  }
+}
 
 __device__ __forceinline__ void cons_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kConsThreads) : "memory"); }
 
@@ -1094,124 +1228,19 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
   if (warp >= kConsWarps) {
     // =========================== producer warps ===========================
     const int pw = warp - kConsWarps;
-    const int rbo0 = s_rbo[lane], rbo1 = s_rbo[lane + 32], rbo2 = s_rbo[min(lane + 64, kRbW - 1)];
-    const bool p_rb0 = lane < 7 || lane >= 13 || A.common;  // hand velocities feed only the common reward terms
-    const bool p_rb2 = lane + 64 < kRbW;
-    const bool is_box = BG && lane >= 18 && lane < 24;
-    const bool p_x = is_box || lane < (BG ? 18 : 15);
-    const int xrow = is_box ? A.p.num_actors * 13 : A.p.num_contact_bodies * 3;
-    int xoff;
-    if (is_box) {
-      const int k = lane - 18;
-      xoff = A.p.box_actor * 13 + (k < 3 ? k : k + 4);
-    } else {
-      const int f = min(lane / 3, 5);
-      xoff = A.cf_off[f] + (lane - 3 * f);
-    }
-    const float* const x_base = (is_box ? (const float*)A.sim.actor_root_state : A.sim.net_contact_force) + xoff;
-    const size_t nb13 = (size_t)A.p.num_bodies * 13;
-    const size_t rb_step = kProdWarps * nb13, x_step = (size_t)kProdWarps * xrow;
-    const size_t N = (size_t)A.n;
-    const bool early = (A.flags & DEX_FLAG_EARLY_SIM_LOADS) != 0;
-    const bool prev_state = !BG && A.common && !A.first;
-    const DexStateBuffers& st = A.st;
-    constexpr int R = 32 / kProdWarps;  // env rows per producer warp
+    LoadCtx<BG> lc;
+    lc.setup(A, s_rbo, lane);
     int it = 0;
 #pragma unroll 1
     for (int tile = blockIdx.x; tile < tiles; tile += workers, ++it) {
       const int s = it & 1, use = it >> 1;
-      const int e0 = tile * 32, ne = min(32, A.n - e0);
       unsigned char* stage = smem2 + s * LY::STAGE_BYTES;
-      const uint32_t sst = s32(stage), fb = bar_full + 8 * s;
+      const uint32_t fb = bar_full + 8 * s;
       TL2(it, 16);
       if (use > 0) mbar_wait(bar_empty + 8 * s, (unsigned)(use - 1) & 1u);
       TL2(it, 17);
-      const bool full = ne == 32;           // CTA-uniform
-      const bool bulk = A.bulk_ok && full;  // the AoS tiles (dof_state, full_dof_targets) as ONE bulk copy each
-      const bool split = it == 0 && early;  // first tile: the state rows wait for griddepcontrol.wait, the sim rows do not
-      const bool act = lane < ne;
-      if (it == 0 && !early) pdl_wait();
-      // a contiguous AoS tile: one bulk copy, or (ragged tile / unaligned base) 4-byte asynchronous copies
-      auto aos_tile = [&](const float* base, const int per, const int off) {
-        const float* src = base + (size_t)e0 * per;
-        if (bulk) {
-          if (pw == 0 && lane == 0) bulk_g2s(sst + off, src, (uint32_t)(32 * per * 4), fb);
-        } else {
-#pragma unroll 1
-          for (int i = pw * 32 + lane; i < ne * per; i += kProdThreads) cpa4(sst + off + 4u * i, src + i);
-        }
-      };
-      aos_tile(A.sim.dof_state, 52, LY::OFF_DOF);
-      // ---- scattered Isaac Gym rows: warp pw takes env rows pw, pw+4, ..; consecutive lanes = consecutive floats ----
-      {
-        const float* q0 = A.sim.rigid_body_state + (size_t)(e0 + pw) * nb13;
-        const float* qx = x_base + (size_t)(e0 + pw) * xrow;
-        uint32_t a = sst + LY::OFF_AOS + (uint32_t)(pw * LY::SA + lane) * 4u;
-#pragma unroll 1
-        for (int i = 0; i < R; ++i) {
-          if (full || pw + kProdWarps * i < ne) {
-            if (p_rb0) cpa4(a + LY::A_RB * 4, q0 + rbo0);
-            cpa4(a + (LY::A_RB + 32) * 4, q0 + rbo1);
-            if (p_rb2) cpa4(a + (LY::A_RB + 64) * 4, q0 + rbo2);
-            if (p_x) cpa4(a + LY::A_CF * 4, qx);
-          }
-          q0 += rb_step;
-          qx += x_step;
-          a += kProdWarps * LY::SA * 4;
-        }
-      }
-      TL2(it, 18);
-      if (split) pdl_wait();  // everything above touched only kernel parameters and the sim tensors
-      if (!BG && A.want_tgt) aos_tile(st.full_dof_targets, 26, LY::OFF_TGT);
-      // ---- SoA state rows: lane = env, one 128-byte line per row; row r of a buffer goes to warp r % 4 ----
-      auto rows = [&](const float* base, const int nrows, const int r0) {
-        const float* src = base + (size_t)pw * N + e0 + lane;
-        uint32_t dst = sst + (uint32_t)(r0 + pw) * 128u + 4u * lane;
-#pragma unroll 1
-        for (int r = pw; r < nrows; r += kProdWarps) {
-          if (act) cpa4(dst, src);
-          src += kProdWarps * N;
-          dst += kProdWarps * 128u;
-        }
-      };
-      auto row64 = [&](const int64_t* base, const int slot) {
-        if (act) cpa8(sst + LY::OFF_I64 + slot * 256 + 8u * lane, base + e0 + lane);
-      };
-      rows(st.prev_dof_pos, DEX_NUM_DOF, LY::R_PDP);
-      rows(st.active_prev_targets, DEX_NUM_ACTIVE, LY::R_APT);
-      rows(st.prev_actions, A.p.num_actions, LY::R_PACT);
-      rows(st.contact_duration_steps, DEX_NUM_FINGERS, LY::R_CDUR);
-      rows(st.prev_contact_binary, DEX_NUM_FINGERS, LY::R_PBIN);
-      if (BG) {
-        rows(st.initial_box_positions, 3, LY::R_BOX0);
-        if (pw == 3 && act) cpa4(sst + LY::R_TIS * 128u + 4u * lane, st.time_in_stage + e0 + lane);  // single rows
-        if (pw == 0 && act) cpa4(sst + LY::R_SCD * 128u + 4u * lane, st.stage_contact_duration + e0 + lane);
-        if (pw == 1) row64(st.success_duration_steps, LY::I_SDS);
-        if (pw == 2) row64(st.current_stage, LY::I_STAGE);
-      } else if (prev_state) {
-        rows(st.prev_finger_dof_vel, DEX_NUM_FINGER_DOF, LY::R_PFDV);
-        rows(st.prev_hand_vel, 3, LY::R_PHV);
-        rows(st.prev_hand_ang_vel, 3, LY::R_PHA);
-        // prev_contacts: 5 bool rows of 32 bytes
-        for (int f = pw; f < DEX_NUM_FINGERS; f += kProdWarps) {
-          const unsigned char* src = st.prev_contacts + (size_t)f * N + e0;
-          if (full && (A.n & 3) == 0) {
-            if (lane < 8) cpa4(sst + LY::OFF_U8 + f * 32 + 4u * lane, src + 4 * lane);
-          } else if (act) {
-            stage[LY::OFF_U8 + f * 32 + lane] = src[lane];
-          }
-        }
-      }
-      if (pw == 3) row64(st.episode_step_count, LY::I_STEP);
-      cpa_arrive(fb);  // counted arrival when every asynchronous copy of this thread has landed
-      __syncwarp();
+      issue_tile_loads<BG, kProdWarps>(A, lc, stage, fb, tile, pw, lane, it == 0);
       TL2(it, 19);
-      if (lane == 0) {
-        if (pw == 0 && bulk)
-          mbar_arrive_tx(fb, A.tx_bytes);
-        else
-          mbar_arrive(fb);
-      }
     }
     return;
   }
@@ -1252,22 +1281,22 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
       rng_step = s_rng_step;
       stamp = ((unsigned)rng_step + 1u) & 0xffffu;
     }
-    phase_items<BG, STD>(A, c);
+    phase_items<BG, STD, false>(A, c);
     TL2(it, 2);
     cons_sync();
     TL2(it, 3);
-    phase_scalar<BG, STD>(A, c);
+    phase_scalar<BG, STD, false>(A, c);
     TL2(it, 4);
     cons_sync();
     TL2(it, 5);
     unsigned cls = 0;
     if (warp == 0) {
-      cls = phase_combine<BG, STD>(A, c, stamp, &s_rbits);
+      cls = phase_combine<BG, STD, false>(A, c, stamp, &s_rbits);
     } else if (BG) {
       if (c.act) {
 #pragma unroll 1
         for (int i = DEX_NUM_COMMON_TERMS + (warp - 1); i < DEX_NUM_REWARD_TERMS; i += kConsWarps - 1)
-          emit_term<BG, STD>(A, c, i, task_term<BG, STD>(A, c, i));
+          emit_term<BG, STD, false>(A, c, i, task_term<BG, STD, false>(A, c, i));
       }
     }
     if (bulk_out) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // obs tile writes -> visible to the bulk store
@@ -1277,7 +1306,7 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
     TL2(it, 7);
     // the raw stage is not read after this point: hand it back to the producers
     if (lane == 0) mbar_arrive(bar_empty + 8 * s);
-    if (warp == 0) phase_total<BG, STD>(A, c, cls);
+    if (warp == 0) phase_total<BG, STD, false>(A, c, cls);
     TL2(it, 8);
     if (bulk_out) {
       if (tid == 32) {
@@ -1304,6 +1333,155 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
     TL2(it, 11);
   }
   if (store_pending) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // the last obs tile has left shared memory
+}
+
+// ------------------------------------------------------------------------------------------------
+// single-pass geometry: ONE tile per CTA of 8 warps, four CTAs per SM (64 registers), no producer warps and no ring - every
+// warp issues its share of the tile's asynchronous copies, then all run the same four phases.  Chosen when the launch
+// has more tiles than the persistent grid has CTAs but no more than 4 x SMs (e.g. 16 384 envs = 512 tiles on 148 SMs):
+// there the persistent kernel would run two full tile rounds on most CTAs, this one runs a single round.
+// The work block is folded into the stage (Lay<BG, true>) to fit four CTAs into the SM's shared memory.
+// ------------------------------------------------------------------------------------------------
+constexpr int kOneThreads = kConsThreads;
+
+template <bool BG, bool STD>
+__global__ void __launch_bounds__(kOneThreads, 4) post_physics_v2s_kernel(const __grid_constant__ Post2Args A) {
+  using LY = Lay<BG, true>;
+  static_assert(BG, "the aliased work block covers the BlindGrasping fields only");
+  extern __shared__ __align__(128) unsigned char smem2[];
+  __shared__ __align__(8) unsigned long long s_bar[1];
+  __shared__ float s_reset_u[32 * kConsWarps];
+  __shared__ int s_rbo[kRbW + 1];
+  __shared__ unsigned long long s_rng_step;
+  __shared__ unsigned s_rbits;
+  __shared__ int s_epi_warp[kConsWarps];
+  __shared__ int s_epi_base;
+  __shared__ int s_epi_cnt[DEX_NUM_COUNTERS];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tile = blockIdx.x;
+
+  if (tile >= A.tiles) {  // the epilogue CTA (fused launches carry one extra block)
+    pdl_wait();
+    pdl_launch_dependents();
+    if (tid == 0) {
+      const unsigned long long rs = *A.st.rng_step;
+      const unsigned stamp = ((unsigned)rs + 1u) & 0xffffu;
+      const volatile unsigned long long* last =
+          reinterpret_cast<const volatile unsigned long long*>(A.ep.tile_records) + (size_t)(A.tiles - 1);  // plane 0
+      const long long t0 = clock64();
+      while ((unsigned)(last[0] >> 48) != stamp) {
+        __nanosleep(100);
+        if (clock64() - t0 > kSpinLimitClocks) __trap();
+      }
+      s_rng_step = rs;
+    }
+    __syncthreads();
+    epilogue_records<kOneThreads, 0>(A.ep, A.n, A.p.max_consecutive_successes, ((unsigned)s_rng_step + 1u) & 0xffffu, s_epi_warp,
+                                     &s_epi_base, s_epi_cnt, reinterpret_cast<unsigned*>(smem2), (int)(A.smem_bytes / 4), tid);
+    return;
+  }
+
+  const uint32_t fb = s32(&s_bar[0]);
+  if (tid == 0) {
+    mbar_init(fb, kOneThreads + kConsWarps);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (tid < kRbW) {
+    const int s = tid;
+    const int row = s < 13 ? 0 : 1 + (s - 13) / 7;
+    s_rbo[s] = A.rb_off[row] + (s < 13 ? s : (s - 13) - (row - 1) * 7);
+  }
+  __syncthreads();
+  pdl_launch_dependents();
+  unsigned char* const stage = smem2;
+  float* const s_obs = reinterpret_cast<float*>(smem2 + LY::STAGE_BYTES + LY::NWKA * 128);
+  {
+    LoadCtx<BG> lc;
+    lc.setup(A, s_rbo, lane);
+    issue_tile_loads<BG, kConsWarps>(A, lc, stage, fb, tile, warp, lane, true);
+  }
+  Cx<BG, STD> c;
+  c.lane = lane;
+  c.cw = warp;
+  c.N = (size_t)A.n;
+  c.wk = reinterpret_cast<float*>(stage) + lane;  // aliased work block: indexed from the stage base
+  c.obs = s_obs + lane * A.wp;
+  c.obs_offset = A.p.obs_offset;
+  c.dof2afj = A.dof2afj;
+  c.e0 = tile * 32;
+  c.ne = min(32, A.n - c.e0);
+  c.act = lane < c.ne;
+  c.env = (size_t)c.e0 + (c.act ? lane : 0);
+  c.stage = stage;
+  const int W = A.p.obs_dim;
+  float* const g_obs = A.out.obs_buf + (size_t)c.e0 * W;
+  const bool bulk_out = A.obs_bulk && c.ne == 32;
+  if (warp == 0) mbar_wait(fb, 0u);  // one polling warp, seven blocked in hardware behind it
+  if (tid == 0) s_rng_step = A.st.rng_step ? *reinterpret_cast<const volatile unsigned long long*>(A.st.rng_step) : A.step;
+  cons_sync();
+  const uint64_t rng_step = s_rng_step;
+  const unsigned stamp = ((unsigned)rng_step + 1u) & 0xffffu;
+  phase_items<BG, STD, true>(A, c);
+  cons_sync();
+  phase_scalar<BG, STD, true>(A, c);
+  cons_sync();
+  unsigned cls = 0;
+  if (warp == 0) {
+    cls = phase_combine<BG, STD, true>(A, c, stamp, &s_rbits);
+  } else if (c.act) {
+#pragma unroll 1
+    for (int i = DEX_NUM_COMMON_TERMS + (warp - 1); i < DEX_NUM_REWARD_TERMS; i += kConsWarps - 1)
+      emit_term<BG, STD, true>(A, c, i, task_term<BG, STD, true>(A, c, i));
+  }
+  if (bulk_out) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  __syncwarp();
+  cons_sync();
+  if (warp == 0) phase_total<BG, STD, true>(A, c, cls);
+  if (bulk_out) {
+    if (tid == 32) bulk_s2g(g_obs, s32(s_obs), (uint32_t)(32 * W * 4));
+  } else {
+    copy_obs_rows(s_obs, g_obs, W, A.wp, c.ne, warp, lane);
+  }
+  {
+    unsigned mask = s_rbits;
+    if (mask && !(A.flags & DEX_FLAG_NO_FUSED_RESET)) {
+      for (int k = 0; mask; ++k) {
+        const int e = __ffs(mask) - 1;
+        mask &= mask - 1;
+        if ((k & (kConsWarps - 1)) == warp) reset_env_warp<BG>(A, c.e0 + e, rng_step, s_reset_u + 32 * warp);
+      }
+    }
+  }
+  if (bulk_out && tid == 32) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // the obs tile has left shared memory
+}
+
+template <bool STD>
+int launch_post2_single(Post2Args& a, cudaStream_t s, int& ok) {
+  using LY = Lay<true, true>;
+  static int ctas_per_sm = -1, num_sms = 0;
+  const uint32_t smem = (uint32_t)(LY::STAGE_BYTES + LY::NWKA * 128 + (32 * a.wp * 4 + 127) / 128 * 128);
+  static uint32_t smem_cfg = 0;
+  if (smem != smem_cfg) {
+    cudaError_t e = cudaFuncSetAttribute(post_physics_v2s_kernel<true, STD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    int dev = 0, occ = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, post_physics_v2s_kernel<true, STD>, kOneThreads, smem);
+    if (e != cudaSuccess) return (int)e;
+    ctas_per_sm = occ;
+    smem_cfg = smem;
+  }
+  const int fused = a.fused_epilogue ? 1 : 0;
+  // every CTA (tiles + epilogue) must be resident at once: the epilogue CTA polls the tiles' records
+  ok = a.tiles + fused <= num_sms * ctas_per_sm && a.tiles + fused > num_sms * 2;
+  if (!ok) return DEX_OK;
+  a.smem_bytes = smem;
+  a.workers = a.tiles;
+  const cudaError_t e = launch_step_kernel(post_physics_v2s_kernel<true, STD>, a.tiles + fused, kOneThreads, smem, s, a);
+  if (e != cudaSuccess) (void)cudaGetLastError();
+  return e == cudaSuccess ? DEX_OK : (int)e;
 }
 
 template <bool BG, bool STD>
@@ -1341,7 +1519,21 @@ int launch_post2_t(Post2Args& a, cudaStream_t s) {
   const int rc = build_post2<BG>(a);
   if (rc) return rc;
   if (a.smem_bytes > 227 * 1024 - 2048) return DEX_ERR_SIZE;
-  return std_layout_matches<BG>(a) ? launch_post2_k<BG, true>(a, s) : launch_post2_k<BG, false>(a, s);
+  const bool std_layout = std_layout_matches<BG>(a);
+  if constexpr (BG) {
+    // geometry by grid size: between 2 x SMs and 4 x SMs tiles the single-pass kernel runs one round where the persistent
+    // one would run two (DEXSTEP_POST_GEOMETRY=persistent keeps the persistent kernel for A/B runs)
+    static const bool allow_single = []() {
+      const char* e = getenv("DEXSTEP_POST_GEOMETRY");
+      return !(e != nullptr && e[0] == 'p');
+    }();
+    if (allow_single) {
+      int ok = 0;
+      const int rc1 = std_layout ? launch_post2_single<true>(a, s, ok) : launch_post2_single<false>(a, s, ok);
+      if (ok || rc1) return rc1;
+    }
+  }
+  return std_layout ? launch_post2_k<BG, true>(a, s) : launch_post2_k<BG, false>(a, s);
 }
 
 }  // namespace pp2
