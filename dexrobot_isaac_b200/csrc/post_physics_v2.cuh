@@ -1126,6 +1126,112 @@ __device__ __forceinline__ void issue_tile_loads(const Post2Args& A, const LoadC
   }
 }
 
+// Register-staged tile load for the single-pass geometry (8 warps, nothing to overlap with: plain LDG costs the LSU a
+// quarter of an LDGSTS).  Every load of the tile is in flight before the first shared store; the dof_state tile still
+// comes as one bulk copy on `fb` (thread 0 carries its byte count).  Ends with the stores issued, not yet synchronised.
+template <bool BG>
+__device__ __forceinline__ void load_tile_regs(const Post2Args& A, const LoadCtx<BG>& lc, unsigned char* stage, const uint32_t fb,
+                                               const int tile, const int w, const int lane) {
+  using LY = Lay<BG>;
+  static_assert(BG, "single-pass geometry: BlindGrasping stage layout");
+  constexpr int NW = kConsWarps;
+  const DexStateBuffers& st = A.st;
+  const size_t N = (size_t)A.n;
+  const int e0 = tile * 32, ne = min(32, A.n - e0);
+  const uint32_t sst = s32(stage);
+  const bool full = ne == 32;
+  const bool bulk = A.bulk_ok && full;
+  const bool early = (A.flags & DEX_FLAG_EARLY_SIM_LOADS) != 0;
+  const bool act = lane < ne;
+  if (!early) pdl_wait();
+  if (bulk) {
+    if (w == 0 && lane == 0) {
+      bulk_g2s(sst + LY::OFF_DOF, A.sim.dof_state + (size_t)e0 * 52, 32 * 52 * 4, fb);
+      mbar_arrive_tx(fb, 32 * 52 * 4);
+    }
+  } else {
+    float* dst = reinterpret_cast<float*>(stage + LY::OFF_DOF);
+    const float* src = A.sim.dof_state + (size_t)e0 * 52;
+    for (int i = w * 32 + lane; i < ne * 52; i += NW * 32) dst[i] = src[i];
+    if (w == 0 && lane == 0) mbar_arrive(fb);
+  }
+  // scattered Isaac Gym rows: warp w takes env rows w, w+8, w+16, w+24
+  float g[4][4];
+  {
+    const size_t nb13 = (size_t)A.p.num_bodies * 13;
+    const float* q0 = A.sim.rigid_body_state + (size_t)(e0 + w) * nb13;
+    const float* qx = lc.x_base + (size_t)(e0 + w) * lc.xrow;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      if (full || w + NW * i < ne) {
+        if (lc.p_rb0) g[i][0] = __ldg(q0 + lc.rbo0);
+        g[i][1] = __ldg(q0 + lc.rbo1);
+        if (lc.p_rb2) g[i][2] = __ldg(q0 + lc.rbo2);
+        if (lc.p_x) g[i][3] = *qx;
+      }
+      q0 += NW * nb13;
+      qx += (size_t)NW * lc.xrow;
+    }
+  }
+  if (early) pdl_wait();  // everything above touched only kernel parameters and the sim tensors
+  // SoA state rows: lane = env; row r of a buffer goes to warp r % 8
+  const size_t col = (size_t)e0 + (act ? lane : 0);
+  float r_pdp[4], r_apt[3], r_pact[3], r_one[4];
+  long long r_i64 = 0;
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+    if (w + NW * j < DEX_NUM_DOF) r_pdp[j] = st.prev_dof_pos[(size_t)(w + NW * j) * N + col];
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    if (w + NW * j < DEX_NUM_ACTIVE) r_apt[j] = st.active_prev_targets[(size_t)(w + NW * j) * N + col];
+    if (w + NW * j < A.p.num_actions) r_pact[j] = st.prev_actions[(size_t)(w + NW * j) * N + col];
+  }
+  if (w < DEX_NUM_FINGERS) {
+    r_one[0] = st.contact_duration_steps[(size_t)w * N + col];
+    r_one[1] = st.prev_contact_binary[(size_t)w * N + col];
+  }
+  if (w < 3) r_one[2] = st.initial_box_positions[(size_t)w * N + col];
+  if (w == 3) r_one[3] = st.time_in_stage[col];
+  if (w == 4) r_one[3] = st.stage_contact_duration[col];
+  if (w == 5) r_i64 = st.success_duration_steps[col];
+  if (w == 6) r_i64 = st.current_stage[col];
+  if (w == 7) r_i64 = st.episode_step_count[col];
+  // ---- stores ----
+  {
+    float* a = reinterpret_cast<float*>(stage + LY::OFF_AOS) + w * LY::SA + lane;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      if (full || w + NW * i < ne) {
+        if (lc.p_rb0) a[LY::A_RB] = g[i][0];
+        a[LY::A_RB + 32] = g[i][1];
+        if (lc.p_rb2) a[LY::A_RB + 64] = g[i][2];
+        if (lc.p_x) a[LY::A_CF] = g[i][3];
+      }
+      a += NW * LY::SA;
+    }
+  }
+  float* rows = reinterpret_cast<float*>(stage) + lane;
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+    if (w + NW * j < DEX_NUM_DOF) rows[(LY::R_PDP + w + NW * j) * 32] = r_pdp[j];
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    if (w + NW * j < DEX_NUM_ACTIVE) rows[(LY::R_APT + w + NW * j) * 32] = r_apt[j];
+    if (w + NW * j < A.p.num_actions) rows[(LY::R_PACT + w + NW * j) * 32] = r_pact[j];
+  }
+  if (w < DEX_NUM_FINGERS) {
+    rows[(LY::R_CDUR + w) * 32] = r_one[0];
+    rows[(LY::R_PBIN + w) * 32] = r_one[1];
+  }
+  if (w < 3) rows[(LY::R_BOX0 + w) * 32] = r_one[2];
+  if (w == 3) rows[LY::R_TIS * 32] = r_one[3];
+  if (w == 4) rows[LY::R_SCD * 32] = r_one[3];
+  long long* i64 = reinterpret_cast<long long*>(stage + LY::OFF_I64) + lane;
+  if (w == 5) i64[LY::I_SDS * 32] = r_i64;
+  if (w == 6) i64[LY::I_STAGE * 32] = r_i64;
+  if (w == 7) i64[LY::I_STEP * 32] = r_i64;
+}
+
 __device__ __forceinline__ void cons_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kConsThreads) : "memory"); }
 
 // shared -> global bulk store of the flat obs tile (TMA engine): one instruction for 20 KB
@@ -1383,7 +1489,7 @@ __global__ void __launch_bounds__(kOneThreads, 4) post_physics_v2s_kernel(const 
 
   const uint32_t fb = s32(&s_bar[0]);
   if (tid == 0) {
-    mbar_init(fb, kOneThreads + kConsWarps);
+    mbar_init(fb, 1);  // tracks the bulk copy of the dof_state tile only; everything else is register-staged
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
@@ -1399,7 +1505,7 @@ __global__ void __launch_bounds__(kOneThreads, 4) post_physics_v2s_kernel(const 
   {
     LoadCtx<BG> lc;
     lc.setup(A, s_rbo, lane);
-    issue_tile_loads<BG, kConsWarps>(A, lc, stage, fb, tile, warp, lane, true);
+    load_tile_regs<BG>(A, lc, stage, fb, tile, warp, lane);
   }
   Cx<BG, STD> c;
   c.lane = lane;
