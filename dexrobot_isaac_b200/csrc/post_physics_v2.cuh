@@ -381,10 +381,7 @@ struct Cx {
     if constexpr (STD) return std_obs_off<BG>(k);
     else return obs_offset[k];
   }
-  __device__ __forceinline__ int afj(const int d) const {
-    if constexpr (STD) return std_dof2afj(d);
-    else return dof2afj[d];
-  }
+  __device__ __forceinline__ int afj(const int d) const { return dof2afj[d]; }  // run-time d: one constant-bank load
   __device__ __forceinline__ const float* soa() const { return reinterpret_cast<const float*>(stage) + lane; }
   __device__ __forceinline__ const float* aos() const {
     return reinterpret_cast<const float*>(stage + Lay<BG>::OFF_AOS) + lane * Lay<BG>::SA;
@@ -1144,17 +1141,16 @@ __device__ __forceinline__ void load_tile_regs(const Post2Args& A, const LoadCtx
   const bool early = (A.flags & DEX_FLAG_EARLY_SIM_LOADS) != 0;
   const bool act = lane < ne;
   if (!early) pdl_wait();
-  if (bulk) {
-    if (w == 0 && lane == 0) {
-      bulk_g2s(sst + LY::OFF_DOF, A.sim.dof_state + (size_t)e0 * 52, 32 * 52 * 4, fb);
-      mbar_arrive_tx(fb, 32 * 52 * 4);
-    }
-  } else {
-    float* dst = reinterpret_cast<float*>(stage + LY::OFF_DOF);
-    const float* src = A.sim.dof_state + (size_t)e0 * 52;
-    for (int i = w * 32 + lane; i < ne * 52; i += NW * 32) dst[i] = src[i];
-    if (w == 0 && lane == 0) mbar_arrive(fb);
-  }
+  // dof_state tile: contiguous 32 x 208 B -> 416 float4, two coalesced 128-bit loads per thread (16-byte aligned: check_sim)
+  float4 d4[2];
+  const float4* dsrc = reinterpret_cast<const float4*>(A.sim.dof_state + (size_t)e0 * 52);
+  const int tq = w * 32 + lane, nq = ne * 13;
+#pragma unroll
+  for (int j = 0; j < 2; ++j)
+    if (tq + 256 * j < nq) d4[j] = dsrc[tq + 256 * j];
+  (void)bulk;
+  (void)sst;
+  (void)fb;
   // scattered Isaac Gym rows: warp w takes env rows w, w+8, w+16, w+24
   float g[4][4];
   {
@@ -1197,6 +1193,12 @@ __device__ __forceinline__ void load_tile_regs(const Post2Args& A, const LoadCtx
   if (w == 6) r_i64 = st.current_stage[col];
   if (w == 7) r_i64 = st.episode_step_count[col];
   // ---- stores ----
+  {
+    float4* ddst = reinterpret_cast<float4*>(stage + LY::OFF_DOF);
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+      if (tq + 256 * j < nq) ddst[tq + 256 * j] = d4[j];
+  }
   {
     float* a = reinterpret_cast<float*>(stage + LY::OFF_AOS) + w * LY::SA + lane;
 #pragma unroll
@@ -1523,7 +1525,6 @@ __global__ void __launch_bounds__(kOneThreads, 4) post_physics_v2s_kernel(const 
   const int W = A.p.obs_dim;
   float* const g_obs = A.out.obs_buf + (size_t)c.e0 * W;
   const bool bulk_out = A.obs_bulk && c.ne == 32;
-  if (warp == 0) mbar_wait(fb, 0u);  // one polling warp, seven blocked in hardware behind it
   if (tid == 0) s_rng_step = A.st.rng_step ? *reinterpret_cast<const volatile unsigned long long*>(A.st.rng_step) : A.step;
   cons_sync();
   const uint64_t rng_step = s_rng_step;
