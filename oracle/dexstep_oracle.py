@@ -268,14 +268,19 @@ class OracleEnv:
         return full
 
     def extract_active_targets(self, full):
-        """action_processor.py:616-666 (inverse coupling; duplicate scatter indices -> the last
-        DOF in index order wins on CPU)."""
+        """action_processor.py:616-666 (inverse coupling).  The reference scatters with DUPLICATE column indices
+        (`active[:, 6 + finger_indices] = scaled`, :657-659: three spread DOFs map to one control, two DOFs to each
+        dip control), which torch documents as undefined order: single-threaded (small batches) the last DOF in index
+        order wins, but a large reset batch is split over threads and other DOFs of the group can win for some rows
+        (seen at 4096 envs when ~100 envs time out in one step).  The oracle states the deterministic rule - the LAST
+        DOF in index order wins - which is what the reference does whenever its scatter runs sequentially and what
+        tests/test_oracle_vs_reference.py pins; the CUDA kernels implement the same rule (DexParams.inverse_src_dof)."""
         out = torch.zeros(full.shape[0], N_ACTIVE)
         out[:, :NB_BASE] = full[:, :NB_BASE]
         fi, sc = self.inv_finger[NB_BASE:], self.inv_scale[NB_BASE:]
-        valid = fi >= 0
-        if valid.any():
-            out[:, NB_BASE + fi[valid]] = full[:, NB_BASE:][:, valid] / sc[valid].unsqueeze(0)
+        for j in range(fi.numel()):  # ascending DOF order: later DOFs overwrite earlier ones
+            if int(fi[j]) >= 0:
+                out[:, NB_BASE + int(fi[j])] = full[:, NB_BASE + j] / sc[j]
         return out
 
     def _action_rule(self, prev, rule, actions):
