@@ -361,3 +361,54 @@ class RefEnv:
         for k, v in self.obs_dict.items():
             out[f"obs/{k}"] = v.clone()
         return out
+
+
+class RefObserver:
+    """Runs the UNMODIFIED reference RewardComponentObserver (dexhand_env/rl/reward_observer.py) on a RefEnv, behind
+    the rl_games stubs of oracle/stubs/rl_games.  `step()` is called once per control step, after
+    RefEnv.post_physics_step: after_steps() then process_infos(extras, done ids) - the order the observer's own
+    docstrings describe."""
+
+    def __init__(self, env: "RefEnv"):
+        _ensure_paths()
+        # the module file itself, not the dexhand_env.rl package (whose __init__ pulls in the rl_games training stack)
+        import importlib.util
+
+        spec = importlib.util.spec_from_file_location(
+            "_ref_reward_observer", os.path.join(REFERENCE_ROOT, "dexhand_env", "rl", "reward_observer.py"))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        RewardComponentObserver = mod.RewardComponentObserver
+
+        class _Vec:
+            pass
+
+        class _Algo:
+            pass
+
+        self.env = env
+        algo = _Algo()
+        algo.vec_env = _Vec()
+        algo.vec_env.env = env          # needs .num_envs and .extras
+        algo.device = "cpu"
+        self.obs = RewardComponentObserver(log_interval=10 ** 9)
+        self.obs.after_init(algo)
+
+    def step(self):
+        self.obs.after_steps()
+        done = torch.nonzero(self.env.reset_buf).flatten()
+        self.obs.process_infos(self.env.extras, done)
+
+    def totals(self, names):
+        """-> [4][2 + len(names)] float64 in the layout of DexOutBuffers.stat_totals ('total' stays 0: the reference skips it)."""
+        o = self.obs
+        out = torch.zeros(4, 2 + len(names), dtype=torch.float64)
+        out[0, 0] = o.total_episodes
+        for c, t in enumerate(("success", "failure", "timeout"), start=1):
+            out[c, 0] = o.episodes_by_type[t]
+        for c, t in enumerate(("all", "success", "failure", "timeout")):
+            for r, k in enumerate(names):
+                if k in o.cumulative_sums[t]:
+                    out[c, 2 + r] = o.cumulative_sums[t][k]["rewards"]
+                    out[c, 1] = o.cumulative_sums[t][k]["steps"]
+        return out
