@@ -163,7 +163,7 @@ struct Post2Args {
 // host: eligibility + derived arguments
 // ------------------------------------------------------------------------------------------------
 inline bool post2_eligible(const DexParams& P, const DexOutBuffers& out, const int mode, const uint32_t flags) {
-  if (mode != DEX_MODE_FULL || out.obs_dict != nullptr || out.obs_norm != nullptr || out.episode_sums != nullptr) return false;
+  if (mode != DEX_MODE_FULL || out.obs_dict != nullptr || out.obs_norm != nullptr) return false;
   if (flags & DEX_FLAG_STALE_CONTACTS) return false;
   if (P.obs_dim > 256) return false;
   const bool bg = P.task == DEX_TASK_BLIND_GRASPING;
@@ -740,6 +740,11 @@ __device__ __forceinline__ void emit_term(const Post2Args& A, const Cx<BG, STD>&
   g[(size_t)row * c.N] = r;
   g[(size_t)(row + 1) * c.N] = rw;
   c.wk[(Lay<BG, AL>::W_WGT + i) * 32] = rw;
+  if (A.out.episode_sums != nullptr) {  // fused RewardComponentObserver (rl/reward_observer.py:176-188): sums += component
+    float* es = A.out.episode_sums + c.env;
+    es[(size_t)row * c.N] += r;
+    es[(size_t)(row + 1) * c.N] += rw;
+  }
 }
 
 // phase B: the per-env scalar part, split over the consumer warps (warp-uniform job index)
@@ -926,10 +931,14 @@ __device__ __forceinline__ unsigned phase_combine(const Post2Args& A, const Cx<B
   const int lane = c.lane;
   if (lane == 0) {
     A.out.reset_bits[c.e0 >> 5] = rbits;
-    *s_rbits = rbits;
+    s_rbits[0] = rbits;
   }
   const unsigned bs = __ballot_sync(fullmask, t_success), bf = __ballot_sync(fullmask, t_failure),
                  bt = __ballot_sync(fullmask, t_timeout);
+  if (lane == 0) {  // termination class of every env of the tile, for the observer flush of the warps that reset them
+    s_rbits[1] = bs;
+    s_rbits[2] = bf;
+  }
   unsigned bc[DEX_NUM_CRITERIA];
 #pragma unroll
   for (int k = 0; k < DEX_NUM_CRITERIA; ++k) bc[k] = __ballot_sync(fullmask, crit[k]);
@@ -994,6 +1003,51 @@ __device__ __forceinline__ void phase_total(const Post2Args& A, const Cx<BG, STD
 #pragma unroll
   for (int k = 0; k < 6; ++k) g[(size_t)(P.termination_row + k) * c.N] = tv[1 + k];
   A.out.rew_buf[c.env] = rew;
+  // ---- fused RewardComponentObserver (rl/reward_observer.py:160-293): the rows this warp produces (total + the six
+  //      termination rows), the episode length and the episode counters; the term rows of a finished env are flushed
+  //      by the warp that resets it (observer_flush_terms)
+  if (A.out.episode_sums != nullptr) {
+    const bool done = cls != 0u;
+    const int stride = 2 + P.num_component_rows;
+    const int kc = t_success ? 1 : (t_failure ? 2 : 3);
+    double* tot = A.out.stat_totals;
+    const int len = A.out.episode_lengths[c.env] + 1;
+    A.out.episode_lengths[c.env] = done ? 0 : len;
+    if (done) {
+      atomicAdd(tot + 0, 1.0);
+      atomicAdd(tot + 1, (double)len);
+      atomicAdd(tot + kc * stride + 0, 1.0);
+      atomicAdd(tot + kc * stride + 1, (double)len);
+    }
+    float* es = A.out.episode_sums + c.env;
+#pragma unroll
+    for (int k = 0; k < 7; ++k) {
+      const int row = k == 0 ? P.total_row : P.termination_row + (k - 1);
+      const float sum = es[(size_t)row * c.N] + tv[k];
+      if (done) {
+        atomicAdd(tot + 2 + row, (double)sum);
+        atomicAdd(tot + kc * stride + 2 + row, (double)sum);
+      }
+      es[(size_t)row * c.N] = done ? 0.0f : sum;
+    }
+  }
+}
+
+// observer flush of the TERM rows (rows below total_row) of one finished env, by one warp: lane = row, so the 2 x terms
+// running sums are read, added to the class totals and zeroed with one strided access each
+__device__ __forceinline__ void observer_flush_terms(const Post2Args& A, const int env, const unsigned* s_rbits, const int e_local) {
+  const DexParams& P = A.p;
+  const int lane = threadIdx.x & 31;
+  const int kc = ((s_rbits[1] >> e_local) & 1u) ? 1 : (((s_rbits[2] >> e_local) & 1u) ? 2 : 3);
+  const int stride = 2 + P.num_component_rows;
+  double* tot = A.out.stat_totals;
+  for (int row = lane; row < P.total_row; row += 32) {
+    float* p = A.out.episode_sums + (size_t)row * A.n + env;
+    const float sum = *p;
+    atomicAdd(tot + 2 + row, (double)sum);
+    atomicAdd(tot + kc * stride + 2 + row, (double)sum);
+    *p = 0.0f;
+  }
 }
 
 
@@ -1280,7 +1334,7 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
   __shared__ float s_reset_u[32 * kConsWarps];
   __shared__ int s_rbo[kRbW + 1];  // gathered rigid slot -> float offset inside one env's [NB,13] block
   __shared__ unsigned long long s_rng_step;
-  __shared__ unsigned s_rbits;
+  __shared__ unsigned s_rbits[4];  // ballots of this tile: reset | success | failure
   __shared__ int s_epi_warp[kConsWarps];
   __shared__ int s_epi_base;
   __shared__ int s_epi_cnt[DEX_NUM_COUNTERS];
@@ -1399,7 +1453,7 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
     TL2(it, 5);
     unsigned cls = 0;
     if (warp == 0) {
-      cls = phase_combine<BG, STD, false>(A, c, stamp, &s_rbits);
+      cls = phase_combine<BG, STD, false>(A, c, stamp, s_rbits);
     } else if (BG) {
       if (c.act) {
 #pragma unroll 1
@@ -1426,12 +1480,17 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
     }
     TL2(it, 9);
     {
-      unsigned mask = s_rbits;  // written by warp 0 before the barrier above
-      if (mask && !(A.flags & DEX_FLAG_NO_FUSED_RESET)) {  // fused reset (dexhand_base.py:743-756): one warp per env
+      unsigned mask = s_rbits[0];  // written by warp 0 before the barrier above
+      // finished envs: one warp per env flushes the observer's term rows and applies the fused reset (dexhand_base.py:743-756)
+      const bool do_reset = !(A.flags & DEX_FLAG_NO_FUSED_RESET), do_flush = A.out.episode_sums != nullptr;
+      if (mask && (do_reset || do_flush)) {
         for (int k = 0; mask; ++k) {
           const int e = __ffs(mask) - 1;
           mask &= mask - 1;
-          if ((k & (kConsWarps - 1)) == warp) reset_env_warp<BG>(A, c.e0 + e, rng_step, s_reset_u + 32 * warp);
+          if ((k & (kConsWarps - 1)) == warp) {
+            if (do_flush) observer_flush_terms(A, c.e0 + e, s_rbits, e);
+            if (do_reset) reset_env_warp<BG>(A, c.e0 + e, rng_step, s_reset_u + 32 * warp);
+          }
         }
       }
     }
@@ -1461,7 +1520,7 @@ __global__ void __launch_bounds__(kOneThreads, 4) post_physics_v2s_kernel(const 
   __shared__ float s_reset_u[32 * kConsWarps];
   __shared__ int s_rbo[kRbW + 1];
   __shared__ unsigned long long s_rng_step;
-  __shared__ unsigned s_rbits;
+  __shared__ unsigned s_rbits[4];  // ballots of this tile: reset | success | failure
   __shared__ int s_epi_warp[kConsWarps];
   __shared__ int s_epi_base;
   __shared__ int s_epi_cnt[DEX_NUM_COUNTERS];
@@ -1535,7 +1594,7 @@ __global__ void __launch_bounds__(kOneThreads, 4) post_physics_v2s_kernel(const 
   cons_sync();
   unsigned cls = 0;
   if (warp == 0) {
-    cls = phase_combine<BG, STD, true>(A, c, stamp, &s_rbits);
+    cls = phase_combine<BG, STD, true>(A, c, stamp, s_rbits);
   } else if (c.act) {
 #pragma unroll 1
     for (int i = DEX_NUM_COMMON_TERMS + (warp - 1); i < DEX_NUM_REWARD_TERMS; i += kConsWarps - 1)
@@ -1551,12 +1610,16 @@ __global__ void __launch_bounds__(kOneThreads, 4) post_physics_v2s_kernel(const 
     copy_obs_rows(s_obs, g_obs, W, A.wp, c.ne, warp, lane);
   }
   {
-    unsigned mask = s_rbits;
-    if (mask && !(A.flags & DEX_FLAG_NO_FUSED_RESET)) {
+    unsigned mask = s_rbits[0];
+    const bool do_reset = !(A.flags & DEX_FLAG_NO_FUSED_RESET), do_flush = A.out.episode_sums != nullptr;
+    if (mask && (do_reset || do_flush)) {
       for (int k = 0; mask; ++k) {
         const int e = __ffs(mask) - 1;
         mask &= mask - 1;
-        if ((k & (kConsWarps - 1)) == warp) reset_env_warp<BG>(A, c.e0 + e, rng_step, s_reset_u + 32 * warp);
+        if ((k & (kConsWarps - 1)) == warp) {
+          if (do_flush) observer_flush_terms(A, c.e0 + e, s_rbits, e);
+          if (do_reset) reset_env_warp<BG>(A, c.e0 + e, rng_step, s_reset_u + 32 * warp);
+        }
       }
     }
   }

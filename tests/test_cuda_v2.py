@@ -207,3 +207,49 @@ def test_v2_is_the_kernel_that_runs():
     env.pipeline.step(a)
     torch.cuda.synchronize()
     assert lib.dex_debug_v2_launches() > before
+
+
+@pytest.mark.parametrize("task,n,steps", [("BlindGrasping", 64, 330), ("BaseTask", 96, 320), ("BlindGrasping", 4096, 60)])
+def test_v2_fused_observer_matches_oracle_observer(task, n, steps):
+    """the device-side RewardComponentObserver fused into the v2 kernels (per-env running sums of every
+    reward component, episode lengths, per-class totals) against oracle/reward_observer.py - the restatement that
+    tests/test_observer_oracle.py pins to the UNMODIFIED reference observer - in lockstep on a scripted world."""
+    from oracle.reward_observer import OracleObserver
+
+    lay = synth.BodyLayout(with_box=task == "BlindGrasping")
+    ora, cud = oracle_env(task, n, lay), lean_env(task, n, lay, observer=True)
+    names = cud.spec.component_names
+    obs = OracleObserver(n, names)
+    world = synth.ScriptedWorld(n, lay, seed=311, nact=ora.num_actions)
+    bad = []
+    launches0 = [0]
+
+    def on_step(t, envs):
+        p = envs[1].pipeline
+        if t == 0:  # reset() ran one full pass: the reference observer only sees training steps
+            for k in ("episode_sums", "episode_lengths", "stat_totals"):
+                p.out[k].zero_()
+            from dexrobot_isaac_b200 import _lib as L
+            launches0[0] = L.load().dex_debug_v2_launches()
+            return
+        a = envs[0].snapshot()
+        obs.after_steps({k: a["rc/" + k] for k in names})
+        obs.process_infos({k: a["extras/" + k] for k in ("success", "failure", "timeout")}, torch.nonzero(a["reset_buf"]).flatten())
+        if len(bad) > 10 or (t % 7 and t > 5):
+            return
+        got_s, got_l, got_t = p.out["episode_sums"].cpu(), p.out["episode_lengths"].cpu(), p.out["stat_totals"].cpu()
+        for r, k in enumerate(names):
+            if not torch.allclose(got_s[r], obs.episode_sums[k], rtol=1e-5, atol=1e-5):
+                bad.append(f"step {t} episode_sums[{k}] max err {float((got_s[r] - obs.episode_sums[k]).abs().max()):.3e}")
+        if not torch.equal(got_l.long(), obs.episode_lengths):
+            bad.append(f"step {t} episode_lengths")
+        if not torch.equal(got_t[:, :2], obs.totals[:, :2]):
+            bad.append(f"step {t} episode counts / length sums")
+        if not torch.allclose(got_t[:, 2:], obs.totals[:, 2:], rtol=1e-5, atol=1e-4):
+            bad.append(f"step {t} stat_totals max err {float((got_t[:, 2:] - obs.totals[:, 2:]).abs().max()):.3e}")
+
+    run_lockstep([ora, cud], world, steps, on_step)
+    assert not bad, "\n".join(bad)
+    assert float(obs.totals[0, 0]) > 0
+    from dexrobot_isaac_b200 import _lib as L
+    assert L.load().dex_debug_v2_launches() - launches0[0] >= steps  # the observer runs inside the v2 kernels
