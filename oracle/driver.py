@@ -56,9 +56,23 @@ def run_lockstep(envs: List, world: synth.ScriptedWorld, steps: int,
         on_step(t, envs)
 
 
+def penetration_floors(cfg: dict) -> Dict[str, float]:
+    """Magnitude floors for the one reward term that is a scaled DIFFERENCE of nearly equal numbers:
+    penetration_penalty = max(threshold - min_tip_distance, 0) * depth_scale (blind_grasping_task.py:1194-1208), weighted by
+    -100.  A 1-ulp difference in the distance (torch's CPU norm vs sqrtf of a plain sum of squares) is amplified by
+    distance / (threshold - distance); the 1e-5 relative bound is therefore taken relative to threshold * scale (* |w|)."""
+    try:
+        box, pp = cfg["env"]["box"], cfg["task"]["penetration_prevention"]
+        w = abs(float(cfg["task"]["reward_weights"].get("penetration_penalty", 0.0)))
+        raw = float(box["size"]) / 2.0 * float(pp["geometricPenetrationFactor"]) * float(pp["penetrationDepthScale"])
+        return {"rc/penetration_penalty": raw, "rc/penetration_penalty_weighted": raw * w}
+    except (KeyError, TypeError):
+        return {}
+
+
 def compare_snapshots(ref: Dict[str, torch.Tensor], got: Dict[str, torch.Tensor], rtol: float,
                       atol: float, skip_rows: Optional[torch.Tensor] = None,
-                      ignore: Iterable[str] = ()) -> List[str]:
+                      ignore: Iterable[str] = (), floors: Optional[Dict[str, float]] = None) -> List[str]:
     """Return a list of human-readable mismatches (empty = parity).  Integer/bool tensors must be
     bit-exact; float tensors must satisfy |a-b| <= atol + rtol*|ref|.  ``skip_rows`` masks out envs
     (used for obs_dict entries that alias live buffers mutated by the in-step reset)."""
@@ -67,9 +81,11 @@ def compare_snapshots(ref: Dict[str, torch.Tensor], got: Dict[str, torch.Tensor]
     # 1e-5 relative bound of the north star holds per term; for the sums it is taken relative to the sum of the terms'
     # magnitudes (cancellation otherwise turns a 1-ulp expf difference in one term into > 1e-5 of a small total)
     mag = None
+    floors = floors or {}
     for k, x in ref.items():
         if k.startswith("rc/") and k.endswith("_weighted") and x is not None:
-            mag = x.detach().cpu().abs().double() if mag is None else mag + x.detach().cpu().abs().double()
+            m = torch.clamp(x.detach().cpu().abs().double(), min=float(floors.get(k, 0.0)))
+            mag = m if mag is None else mag + m
     for k, x in ref.items():
         if x is None or any(k.startswith(p) for p in ignore):
             continue
@@ -98,6 +114,8 @@ def compare_snapshots(ref: Dict[str, torch.Tensor], got: Dict[str, torch.Tensor]
             tol = atol + rtol * x.abs()
             if k in ("rew_buf", "rc/total") and mag is not None and mag.shape == x.shape:
                 tol = atol + rtol * torch.maximum(x.abs().double(), mag).to(x.dtype)
+            elif k in floors:
+                tol = atol + rtol * torch.clamp(x.abs(), min=float(floors[k]))
             if not bool((err <= tol).all()):
                 i = int(torch.argmax(err - tol))
                 bad.append(f"{k}: max err {float(err.max()):.3e} (ref {float(x.flatten()[i]):.6e} "

@@ -12,7 +12,7 @@ import pytest
 import torch
 
 from oracle import synth
-from oracle.driver import check_against_golden, compare_snapshots, run_lockstep
+from oracle.driver import check_against_golden, compare_snapshots, penetration_floors, run_lockstep
 from dexrobot_isaac_b200.config import load_task_config
 
 pytestmark = pytest.mark.gpu
@@ -56,6 +56,7 @@ def _lockstep(task, n, steps, seed, layout=None, check_every=1, **kw):
     cud = make_cuda_env(task, n, layout, **kw)
     world = synth.ScriptedWorld(n, layout, seed=seed, nact=ora.num_actions)
     bad, seen = [], {"reset": 0, "success": 0, "failure": 0, "timeout": 0}
+    floors = penetration_floors(load_task_config(task, num_envs=n, **kw))
 
     def on_step(t, envs):
         if len(bad) > 20 or (t % check_every and t > 3):
@@ -64,7 +65,7 @@ def _lockstep(task, n, steps, seed, layout=None, check_every=1, **kw):
         seen["reset"] += int(a["reset_buf"].sum())
         for k in ("success", "failure", "timeout"):
             seen[k] += int(a[f"extras/{k}"].sum())
-        for m in compare_snapshots(a, b, RTOL, ATOL, skip_rows=a["reset_buf"].bool()):
+        for m in compare_snapshots(a, b, RTOL, ATOL, skip_rows=a["reset_buf"].bool(), floors=floors):
             bad.append(f"step {t} {m}")
         # the ordered id list of the envs that reset == torch.nonzero(reset_buf)
         ids = envs[1].pipeline.env_ids().cpu()
