@@ -243,7 +243,8 @@ def test_v2_fused_observer_matches_oracle_observer(task, n, steps):
             return
         got_s, got_l, got_t = p.out["episode_sums"].cpu(), p.out["episode_lengths"].cpu(), p.out["stat_totals"].cpu()
         for r, k in enumerate(names):
-            if not torch.allclose(got_s[r], obs.episode_sums[k], rtol=1e-5, atol=1e-5):
+            # running sums of up to episodeLength per-step values, each within 1e-5 relative / 1e-6 absolute
+            if not torch.allclose(got_s[r], obs.episode_sums[k], rtol=1e-5, atol=2e-4):
                 bad.append(f"step {t} episode_sums[{k}] max err {float((got_s[r] - obs.episode_sums[k]).abs().max()):.3e}")
         if not torch.equal(got_l.long(), obs.episode_lengths):
             bad.append(f"step {t} episode_lengths")
