@@ -163,7 +163,7 @@ struct Post2Args {
 // host: eligibility + derived arguments
 // ------------------------------------------------------------------------------------------------
 inline bool post2_eligible(const DexParams& P, const DexOutBuffers& out, const int mode, const uint32_t flags) {
-  if (mode != DEX_MODE_FULL || out.obs_dict != nullptr || out.obs_norm != nullptr) return false;
+  if (mode != DEX_MODE_FULL || out.obs_dict != nullptr) return false;
   if (flags & DEX_FLAG_STALE_CONTACTS) return false;
   if (P.obs_dim > 256) return false;
   const bool bg = P.task == DEX_TASK_BLIND_GRASPING;
@@ -1320,6 +1320,38 @@ __device__ __forceinline__ void copy_obs_rows(const float* s_obs, float* g_tile,
   }
 }
 
+// optional policy-input stage, from the same shared obs tile: obs_norm = clamp((obs - mean) * scale, +-clip),
+// the frozen-statistics form of rl_games' RunningMeanStd.forward (normalize_input, cfg/train/BaseTaskPPO.yaml:44); fp32
+// subtract, multiply by the caller's fp32 reciprocal, clamp that lets NaN through like torch.clamp.  Row-per-warp,
+// lane = column, 128-byte stores.
+__device__ __forceinline__ void copy_obs_norm_rows(const float* s_obs, const DexOutBuffers& out, const int e0, const int W, const int WP,
+                                                   const int ne, const int w, const int lane) {
+  const int nchunk = (W + 31) >> 5;
+  const float clip = out.norm_clip;
+  float* g_tile = out.obs_norm + (size_t)e0 * W;
+#pragma unroll 1
+  for (int ch = 0; ch < nchunk; ++ch) {
+    const int col = 32 * ch + lane;
+    if (col < W) {
+      const float m = __ldg(out.norm_mean + col), sc = __ldg(out.norm_scale + col);
+      float v[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int row = w + kConsWarps * i;
+        if (row < ne) v[i] = s_obs[row * WP + col];
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int row = w + kConsWarps * i;
+        if (row < ne) {
+          const float y = (v[i] - m) * sc;
+          g_tile[(size_t)row * W + col] = (y != y) ? y : fminf(fmaxf(y, -clip), clip);
+        }
+      }
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------------
 // the kernel: persistent, 8 consumer + 4 producer warps per CTA, 2-stage ring, two CTAs per SM (BlindGrasping).
 // Instruction supply is the scarce resource of this path (profiles/r02_variants.md): the consumer warps run the SAME
@@ -1478,6 +1510,7 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
     } else {
       copy_obs_rows(s_obs, g_obs, W, A.wp, c.ne, warp, lane);
     }
+    if (A.out.obs_norm != nullptr) copy_obs_norm_rows(s_obs, A.out, c.e0, W, A.wp, c.ne, warp, lane);
     TL2(it, 9);
     {
       unsigned mask = s_rbits[0];  // written by warp 0 before the barrier above
@@ -1609,6 +1642,7 @@ __global__ void __launch_bounds__(kOneThreads, 4) post_physics_v2s_kernel(const 
   } else {
     copy_obs_rows(s_obs, g_obs, W, A.wp, c.ne, warp, lane);
   }
+  if (A.out.obs_norm != nullptr) copy_obs_norm_rows(s_obs, A.out, c.e0, W, A.wp, c.ne, warp, lane);
   {
     unsigned mask = s_rbits[0];
     const bool do_reset = !(A.flags & DEX_FLAG_NO_FUSED_RESET), do_flush = A.out.episode_sums != nullptr;
