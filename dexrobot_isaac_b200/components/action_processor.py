@@ -5,9 +5,11 @@ post-action filters (rules.py:113-190), coupling 18 -> 26 (action_processor.py:5
 ``active_prev_targets <- next`` (:342) and ``ObservationEncoder.update_prev_actions``
 (observation_encoder.py:287-296) are fused.  The open extension points of the reference
 (``set_action_rule`` / ``set_pre_action_rule`` / ``set_coupling_rule`` / custom post filters) take
-arbitrary Python callables; the fused kernel covers the default rules of the two shipped tasks, so
-registering anything else raises ``NotImplementedError`` at registration time instead
-of silently running something different.
+arbitrary Python callables.  The fused kernel covers the default rules; as soon as a callable is
+registered the processor switches to the GENERIC route: the registered rule / filters
+run as torch ops on the pipeline's device tensors (same call signatures as rules.py:113-190), the
+built-in filters are the two clamps of rules.py:141-190, and the 18 -> 26 coupling is
+``dex_apply_coupling``.  Still no host round trip and no CPU fallback - just un-fused.
 """
 from __future__ import annotations
 
@@ -29,6 +31,7 @@ class ActionProcessor:
         self.action_rule = None
         self.coupling_rule = None
         self._enabled_post_action_filters = []
+        self._custom_filters = {}
 
     # ------------------------------------------------------------------ properties of the reference
     @property
@@ -147,12 +150,78 @@ class ActionProcessor:
                 if active_rule_targets.shape != own.shape:
                     raise RuntimeError(f"active_rule_targets shape {tuple(active_rule_targets.shape)} != {tuple(own.shape)}")
                 own.copy_(active_rule_targets)
-        buf = self.parent._actions
+        buf = self.action_buffer
         if a.data_ptr() != buf.data_ptr():
             buf.copy_(a)
         self.actions = buf
-        p.pre_physics(buf, self._raw)
+        if self.uses_generic_route:
+            self._process_actions_generic(buf)
+        else:
+            p.pre_physics(buf, self._raw)
         return True
+
+    @property
+    def action_buffer(self) -> torch.Tensor:
+        """The fixed-address [N, num_actions] device buffer dex_pre_physics reads (graph-capturable).  The parent may
+        own it (``parent._actions``, DexStepEnv does, to copy host actions straight into it); any other parent - e.g. the
+        reference's DexHandBase - gets one allocated here."""
+        buf = getattr(self.parent, "_actions", None)
+        if buf is None:
+            buf = getattr(self, "_own_actions", None)
+            if buf is None:
+                buf = self._own_actions = torch.zeros(self.num_envs, self._p.spec.num_actions, device=self.device)
+        return buf
+
+    # ------------------------------------------------------------------ generic route (custom callables)
+    @property
+    def uses_generic_route(self) -> bool:
+        return self.action_rule is not None or self.coupling_rule is not None or bool(self._custom_filters) or \
+            any(f not in ("velocity_clamp", "position_clamp") for f in self._enabled_post_action_filters)
+
+    def _default_action_rule(self, prev, rule, actions, config):
+        """default_rules.py:33-112 as torch ops (only used when a custom filter / coupling rule forces the generic
+        route while the action rule itself is the default)."""
+        t = rule.clone()
+        lo, hi, md = self.active_lower_limits, self.active_upper_limits, self.max_deltas
+        fs = NUM_BASE if config["policy_controls_base"] else 0
+        if config["control_mode"] == "position":
+            if config["policy_controls_base"]:
+                t[:, :NUM_BASE] = (actions[:, :NUM_BASE] + 1.0) * 0.5 * (hi[:NUM_BASE] - lo[:NUM_BASE]) + lo[:NUM_BASE]
+            if config["policy_controls_fingers"]:
+                a = actions[:, fs:fs + NUM_ACTIVE_FINGER]
+                t[:, NUM_BASE:] = (a + 1.0) * 0.5 * (hi[NUM_BASE:] - lo[NUM_BASE:]) + lo[NUM_BASE:]
+            return t
+        if config["policy_controls_base"]:
+            t[:, :NUM_BASE] = prev[:, :NUM_BASE] + actions[:, :NUM_BASE] * md[:NUM_BASE]
+        if config["policy_controls_fingers"]:
+            t[:, NUM_BASE:] = prev[:, NUM_BASE:] + actions[:, fs:fs + NUM_ACTIVE_FINGER] * md[NUM_BASE:]
+        return torch.clamp(t, lo, hi)  # default_rules.py:107-110
+
+    def _process_actions_generic(self, actions: torch.Tensor):
+        """action_processor.py:320-343 with the registered callables, on device tensors."""
+        p = self._p
+        prev, rule = self.active_prev_targets, self.active_rule_targets  # [N,18] views of the SoA state
+        config = {"control_mode": self.action_control_mode, "policy_controls_base": self.policy_controls_hand_base,
+                  "policy_controls_fingers": self.policy_controls_fingers}
+        fn = self.action_rule if self.action_rule is not None else self._default_action_rule
+        raw = fn(prev, rule, actions, config)
+        if self._raw is not None:
+            self._raw.copy_(raw.t())
+        nxt = raw
+        for name in self._enabled_post_action_filters:  # rules.py:113-139
+            if name == "velocity_clamp":
+                nxt = prev + torch.clamp(nxt - prev, -self.max_deltas, self.max_deltas)
+            elif name == "position_clamp":
+                nxt = torch.clamp(nxt, self.active_lower_limits, self.active_upper_limits)
+            elif name in self._custom_filters:
+                nxt = self._custom_filters[name](prev, rule, nxt)
+        nxt_soa = nxt.t().contiguous()
+        if self.coupling_rule is not None:
+            p.state["full_dof_targets"].copy_(self.coupling_rule(nxt))
+        else:
+            p.apply_coupling(nxt_soa, p.state["full_dof_targets"])
+        p.state["active_prev_targets"].copy_(nxt_soa)                       # :342
+        p.state["prev_actions"].copy_(actions.t())                          # observation_encoder.py:287-296
 
     def enable_raw_targets(self, on: bool = True):
         """Materialise ``active_raw_targets`` (debug attribute of the reference) on the next calls."""
@@ -203,21 +272,17 @@ class ActionProcessor:
             return (a + 1.0) * 0.5 * (hi[idx] - lo[idx]) + lo[idx]
         return a * md[idx]
 
-    # ------------------------------------------------------------------ extension points
-    def _fused_only(self, what):
-        raise NotImplementedError(
-            f"{what}: the fused pre-physics kernel implements the reference's default rules "
-            "(DefaultActionRules + velocity/position clamp + finger coupling); custom Python callables are "
-            "not part of this path (SURVEY.md §8f N4)")
-
+    # ------------------------------------------------------------------ extension points (rules.py:196-244)
     def set_pre_action_rule(self, rule):
-        self._fused_only("set_pre_action_rule")
+        """rule(active_prev_targets, state) -> active_rule_targets; None restores the identity rule.  Applied by
+        StepProcessor after the post-physics launch (step_processor.py:66-73), on device tensors."""
+        self.pre_action_rule = rule
 
     def set_action_rule(self, rule):
-        self._fused_only("set_action_rule")
+        self.action_rule = rule
 
     def set_coupling_rule(self, rule):
-        self._fused_only("set_coupling_rule")
+        self.coupling_rule = rule
 
     def register_post_action_filter(self, name, filter_fn):
-        self._fused_only("register_post_action_filter")
+        self._custom_filters[name] = filter_fn

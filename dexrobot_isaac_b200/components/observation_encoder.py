@@ -29,6 +29,7 @@ class ObservationEncoder:
         self.task_states: Dict[str, torch.Tensor] = {}
         self.observation_keys: List[str] = []
         self.component_slice_indices: Dict[str, Tuple[int, int]] = {}
+        self.action_processor = None
         self._initialized = False
 
     @property
@@ -104,14 +105,13 @@ class ObservationEncoder:
     def update_prev_actions(self, actions: torch.Tensor):
         """observation_encoder.py:287-296.  ``ActionProcessor.process_actions`` (dex_pre_physics) already stored
         the actions it processed; only a different tensor needs a copy."""
-        buf = self.parent._actions
-        if actions.data_ptr() == buf.data_ptr():
+        buf = self.action_processor.action_buffer if self.action_processor is not None else None
+        if buf is not None and actions.data_ptr() == buf.data_ptr():
             return
         a = actions.to(self.device, torch.float32)
-        if a.shape != buf.shape:
-            raise RuntimeError(f"actions shape {tuple(a.shape)} != {tuple(buf.shape)}")
-        if not torch.equal(a, buf):
-            self.prev_actions.copy_(a)
+        if a.shape != self.prev_actions.shape:
+            raise RuntimeError(f"actions shape {tuple(a.shape)} != {tuple(self.prev_actions.shape)}")
+        self.prev_actions.copy_(a)  # a strided device copy; no comparison (that would be a host sync per step)
 
     def reset_observer_state(self, env_ids: torch.Tensor):
         """observation_encoder.py:363-383: contact duration / previous contacts / previous DOF positions (zero,

@@ -60,6 +60,15 @@ class ResetManager:
             tm.reset_tracking(ids)
         return True
 
+    def reset_mask(self, mask: torch.Tensor) -> bool:
+        """reset_idx for a boolean mask that lives on the device (no nonzero(), no host sync)."""
+        self.parent.pipeline.reset_idx(mask)
+        tm = getattr(self.parent, "termination_manager", None)
+        if tm is not None:
+            for t in [tm.episode_success, tm.episode_failure, *tm.success_reasons.values(), *tm.failure_reasons.values()]:
+                t.logical_and_(~mask.bool())
+        return True
+
     def reset_all(self) -> bool:
         """reset_manager.py:192-200."""
         self.parent.pipeline.reset_idx(None)

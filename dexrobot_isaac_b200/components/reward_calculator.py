@@ -74,5 +74,14 @@ class RewardCalculator:
                              success_failure_rewards: Optional[dict] = None) -> Tuple[torch.Tensor, Dict[str, torch.Tensor]]:
         """:223-275 -> (total reward WITHOUT termination rewards, components {name, name_weighted, total})."""
         comps = self._p.reward_components()
+        # terms the kernel does not know (a custom task's extra reward) or values that are not the kernel's own rows
+        # cannot be folded into the fused total: refuse instead of returning something else than the caller asked for
+        for d in (common_rewards, task_rewards):
+            for name, v in (d or {}).items():
+                if name not in comps:
+                    raise NotImplementedError(f"reward term '{name}' is not computed by the fused kernel (SURVEY 8f N4)")
+                if isinstance(v, torch.Tensor) and v.data_ptr() != comps[name].data_ptr() and v.shape == comps[name].shape \
+                        and not torch.equal(v, comps[name]):
+                    raise NotImplementedError(f"reward term '{name}': the values handed in differ from the kernel's")
         out = {k: v for k, v in comps.items() if not k.startswith("termination_")}
         return comps["total"], out

@@ -72,6 +72,19 @@ class TerminationManager:
             self.validate_criteria(builtin_success or {}, task_success or {}, self.active_success_criteria, "Success")
             self.validate_criteria(builtin_failure or {}, task_failure or {}, self.active_failure_criteria, "Failure")
         p = self.parent.pipeline
+        # The criteria were evaluated inside the kernel: dictionaries that carry anything else than the kernel's own
+        # criteria (a custom task's extra criterion, or a mask the caller computed differently) cannot be honoured here
+        # and must not be ignored silently - such tasks belong on the generic-task route (DexStepEnv(task=...)).
+        known = set(SUCCESS_CRITERIA) | set(FAILURE_CRITERIA)
+        for d in (builtin_success, task_success, builtin_failure, task_failure):
+            for name, mask in (d or {}).items():
+                if name not in known:
+                    raise NotImplementedError(f"criterion '{name}' is not evaluated by the fused kernel (SURVEY 8f N4)")
+                own = self._own_mask(name)
+                if own is not None and isinstance(mask, torch.Tensor) and mask.data_ptr() != own.data_ptr() and \
+                        mask.shape == own.shape and not torch.equal(mask.to(own.dtype), own):
+                    raise NotImplementedError(f"criterion '{name}': the mask handed in differs from the one the fused "
+                                              "kernel evaluated for this step")
         stats, out = p.epi["stats"], p.out
         info = {"success": out["success"], "failure": out["failure"], "timeout": out["timeout"],
                 "success_rate": stats[C["DEX_STAT_SUCCESS_RATE"]], "failure_rate": stats[C["DEX_STAT_FAILURE_RATE"]],
@@ -88,6 +101,14 @@ class TerminationManager:
         raw = {"success": comps["termination_success"], "failure_penalty": comps["termination_failure_penalty"],
                "timeout_penalty": comps["termination_timeout_penalty"]}
         return out["reset_buf"], info, rewards, raw
+
+    def _own_mask(self, name):
+        """The kernel's per-env mask of a criterion, where it is materialised."""
+        p = self.parent.pipeline
+        ft = ("stage1_pregrasp_failed", "stage2_contact_failed", "stage3_grasp_lost")
+        if name in ft and "failure_tensors" in p.state:
+            return p.state["failure_tensors"][ft.index(name)]
+        return None
 
     def update_consecutive_successes(self, success_tensor=None):
         """:323-339.  Done by the step epilogue on the device (``min(c + 1, max)`` if any env succeeded, else

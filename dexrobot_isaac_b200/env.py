@@ -20,7 +20,7 @@ from typing import Callable, Dict, Optional, Sequence
 import torch
 
 from . import _lib as L
-from .params import FAILURE_CRITERIA, SUCCESS_CRITERIA, BodyLayout
+from .params import BodyLayout
 from .pipeline import (FLAG_STALE_CONTACTS, MODE_FULL, MODE_OBS_ONLY, NUM_UNIFORMS, StepPipeline)
 
 C = L.CONSTS
@@ -31,7 +31,7 @@ class DexStepEnv:
                  dof_props: Optional[torch.Tensor] = None, device="cuda:0",
                  sim: Optional[Dict[str, torch.Tensor]] = None, materialize_obs_dict: bool = False,
                  observer: bool = True, seed: int = 1234, init_uniforms: Optional[torch.Tensor] = None,
-                 physics: Optional[Callable[[], None]] = None):
+                 physics: Optional[Callable[[], None]] = None, task=None, physics_steps_per_control_step: int = 2):
         self.cfg, self.env_cfg, self.task_cfg, self.sim_cfg = cfg, cfg["env"], cfg["task"], cfg["sim"]
         self.task_name = self.task_cfg.get("name", "BaseTask")
         self.num_envs = int(num_envs)
@@ -44,9 +44,20 @@ class DexStepEnv:
             raise ValueError("dof_props [26,6] (lower/upper limits in columns 4,5; tensor_manager.py:242) is required")
         self.dof_props = dof_props.detach().to("cpu", torch.float32)
         self.physics = physics
+        # ---- the task (dexhand_base.py:430-452).  The two shipped tasks are facades over the fused kernels; any other
+        # DexTask is a GENERIC task: its Python hooks run un-fused on the device tensors, which needs the
+        # obs_dict materialised by the kernel and the reset applied after the hooks have seen the step
+        from .tasks import BaseTask as _BaseTask, BlindGraspingTask as _BGTask
+        if task is None:
+            task = (_BGTask if self.task_name == "BlindGrasping" else _BaseTask)(None, None, dev, self.num_envs, cfg)
+        self.task = task
+        self.generic_task = type(task) not in (_BaseTask, _BGTask)
+        if self.generic_task:
+            materialize_obs_dict = True
         self.pipeline = StepPipeline(cfg, num_envs, self.layout, self.dof_props[:, 4].tolist(),
                                      self.dof_props[:, 5].tolist(), device=dev, sim=sim,
-                                     materialize_obs_dict=materialize_obs_dict, observer=observer, seed=seed)
+                                     materialize_obs_dict=materialize_obs_dict, observer=observer, seed=seed,
+                                     physics_steps_per_control_step=physics_steps_per_control_step)
         p = self.pipeline
         self.spec = p.spec
         self.num_actions = p.spec.num_actions
@@ -87,9 +98,23 @@ class DexStepEnv:
         self.termination_manager = TerminationManager(self, self.task_cfg)
         self.reward_calculator = RewardCalculator(self, self.task_cfg)
         self.reset_manager = ResetManager(self, self.dof_state, self.actor_root_state_tensor, 0,
-                                          torch.zeros(26, device=dev), task=None)
+                                          torch.zeros(26, device=dev), task=self.task)
         self.step_processor = StepProcessor(self)
+        # task wiring, in the reference's order (dexhand_base.py:238-262, 430-452, 322-340)
+        self.task.parent_env = self
+        self.task.device = dev
+        self.task.initialize_task_states()
+        self.task.set_tensor_references(self.actor_root_state_tensor)
+        ap = self.action_processor
+        if self.task.pre_action_rule is not None:
+            ap.set_pre_action_rule(self.task.pre_action_rule)
+        if self.task.action_rule is not None:
+            ap.set_action_rule(self.task.action_rule)
+        self.task.register_custom_filters(ap)
+        if self.task.post_action_filters:
+            ap._enabled_post_action_filters = list(ap._enabled_post_action_filters) + list(self.task.post_action_filters)
         self.action_processor.finalize_setup()
+        self.task.finalize_setup()
 
     # ------------------------------------------------------------------ reference call sequence
     def reset_idx(self, env_ids):
@@ -222,27 +247,7 @@ class DexStepEnv:
 
     # ------------------------------------------------------------------ extras (step_processor.py:221-232)
     def _update_extras(self):
-        """Lazy: tensors are views/slices of device buffers, no host sync happens here."""
-        p, sp = self.pipeline, self.spec
-        stats = p.epi["stats"]
-        ex = {"consecutive_successes": p.epi["consecutive_successes"][0],
-              "episode_length": p.state["episode_step_count"],
-              "success": p.out["success"], "failure": p.out["failure"], "timeout": p.out["timeout"],
-              "success_rate": stats[C["DEX_STAT_SUCCESS_RATE"]], "failure_rate": stats[C["DEX_STAT_FAILURE_RATE"]],
-              "timeout_rate": stats[C["DEX_STAT_TIMEOUT_RATE"]]}
-        crit = SUCCESS_CRITERIA + FAILURE_CRITERIA
-        for c, name in enumerate(crit):
-            kind = "success" if name in SUCCESS_CRITERIA else "failure"
-            if name in (sp.active_success if kind == "success" else sp.active_failure):
-                ex[f"{kind}_{name}"] = stats[C["DEX_STAT_CRIT0"] + c]
-                # termination_manager.py:353-357 + step_processor.py:109-111: every env whose criterion
-                # fired was reset in the same step, which clears its sticky reason bit before extras are
-                # built -> the masks that reach extras are all-False (SURVEY App. B quirk).
-                tm = getattr(self, "termination_manager", None)
-                ex[f"{kind}_reason_{name}"] = self._zero_mask if tm is None else \
-                    (tm.success_reasons if kind == "success" else tm.failure_reasons)[name]
-        ex["reward_components"] = p.reward_components()
-        self.extras = ex
+        self.step_processor._update_extras()
 
     # ------------------------------------------------------------------ test driver API (oracle/driver.py)
     def load_state(self, state: Dict[str, torch.Tensor]):

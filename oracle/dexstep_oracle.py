@@ -303,14 +303,23 @@ class OracleEnv:
         return torch.clamp(t, self.active_lower, self.active_upper)
 
     def process_actions(self, actions, rule_targets):
-        """action_processor.py:284-352 (post-finalize branch) + rules.py:113-190."""
+        """action_processor.py:284-352 (post-finalize branch) + rules.py:113-190.  `self.hooks` (optional, tests of the
+        generic-task route) carries custom callables with the reference's hook signatures (rules.py:196-244)."""
+        hooks = getattr(self, "hooks", None) or {}
         self.actions = actions.clone()
         self.active_rule_targets = rule_targets
-        raw = self._action_rule(self.active_prev_targets, rule_targets, actions)
+        if hooks.get("action_rule") is not None:
+            config = {"control_mode": self.control_mode, "policy_controls_base": self.ctrl_base,
+                      "policy_controls_fingers": self.ctrl_fingers}                # action_processor.py:322-326
+            raw = hooks["action_rule"](self.active_prev_targets, rule_targets, actions, config)
+        else:
+            raw = self._action_rule(self.active_prev_targets, rule_targets, actions)
         self.active_raw_targets = raw
         delta = raw - self.active_prev_targets                                    # rules.py:141-166
         nxt = self.active_prev_targets + torch.clamp(delta, -self.max_deltas, self.max_deltas)
         nxt = torch.clamp(nxt, self.active_lower, self.active_upper)              # rules.py:168-190
+        for _, fn in hooks.get("filters", []):                                    # rules.py:113-139, task filters last
+            nxt = fn(self.active_prev_targets, rule_targets, nxt)
         self.active_next_targets = nxt
         self.full_dof_targets = self.apply_coupling(nxt)
         self.active_prev_targets = nxt.clone()
@@ -750,14 +759,21 @@ class OracleEnv:
         # O1 tensor_manager.py:441-446: gather of the monitored contact bodies
         self.contact_forces = self.contact_forces_all[:, torch.tensor(self.layout.contacts), :]
         od = self.compute_observations()
-        od["active_rule_targets"] = self.active_prev_targets.clone()   # rules.py:78-95 identity rule
+        hooks = getattr(self, "hooks", None) or {}
+        if hooks.get("pre_action_rule") is not None:                   # step_processor.py:66-73
+            od["active_rule_targets"] = hooks["pre_action_rule"](self.active_prev_targets, {"obs_dict": od, "env": self})
+        else:
+            od["active_rule_targets"] = self.active_prev_targets.clone()   # rules.py:78-95 identity rule
         self.obs_buf = self.concatenate(od)
         self.states_buf = self.obs_buf.clone()
         self.obs_dict = od
         self.episode_step_count += 1
         should_reset, info, term_rew, raw_rew = self._evaluate_termination()
         self.reset_buf = should_reset
-        self.rew_buf[:], comps = self._total_reward(self._common_rewards(), self._task_rewards())
+        task_rewards = dict(self._task_rewards())
+        if hooks.get("extra_reward_terms") is not None:                # a custom task's compute_task_reward_terms
+            task_rewards.update(hooks["extra_reward_terms"](od))
+        self.rew_buf[:], comps = self._total_reward(self._common_rewards(), task_rewards)
         # termination_manager.py:323-339
         if torch.any(info["success"]):
             self.consecutive_successes += 1

@@ -114,7 +114,7 @@ class RefEnv:
     def __init__(self, task_name: str, num_envs: int, layout: Optional[synth.BodyLayout] = None,
                  control_mode: Optional[str] = None, policy_controls_hand_base: bool = True,
                  policy_controls_fingers: bool = True, init_uniforms: Optional[torch.Tensor] = None,
-                 cfg: Optional[dict] = None):
+                 cfg: Optional[dict] = None, hooks: Optional[dict] = None):
         if not reference_available():
             raise RuntimeError(f"reference not found at {REFERENCE_ROOT}")
         _ensure_paths()
@@ -237,6 +237,19 @@ class RefEnv:
         self.initialization_manager.create_index_mappings()
         self.initialization_manager.setup_additional_tensors()
         DefaultActionRules.setup_default_action_rule(self.action_processor, self.task_cfg["controlMode"])
+        if hooks:  # a custom task's hooks, registered the way DexHandBase._setup_action_rules does (dexhand_base.py:238-262)
+            if hooks.get("pre_action_rule") is not None:
+                self.action_processor.set_pre_action_rule(hooks["pre_action_rule"])
+            if hooks.get("action_rule") is not None:
+                self.action_processor.set_action_rule(hooks["action_rule"])
+            names = [name for name, _ in hooks.get("filters", [])]
+            if names:
+                self.action_processor._enabled_post_action_filters = \
+                    list(self.action_processor._enabled_post_action_filters) + names
+            if hooks.get("extra_reward_terms") is not None:
+                base_terms, extra = self.task.compute_task_reward_terms, hooks["extra_reward_terms"]
+                self.task.compute_task_reward_terms = lambda od: {**base_terms(od), **extra(od)}
+                self.reward_calculator.reward_weights.update(hooks.get("extra_reward_weights", {}))
 
         # control-cycle measurement (dexhand_base.py:270-320)
         self._uniforms = init_uniforms if init_uniforms is not None else torch.full((n, synth.N_UNIFORMS), 0.5)
@@ -246,6 +259,14 @@ class RefEnv:
         self.reset_idx(torch.arange(n))
         self.physics_manager.finish_control_cycle_measurement()
         self.action_processor.finalize_setup()
+        if hooks:
+            # NOTE (reference quirk): DexHandBase registers the task's custom filters BEFORE finalize_setup()
+            # (dexhand_base.py:216/253 vs :307), and finalize_setup() re-creates the filter registry with the two built-ins
+            # only (action_processor.py:267 -> rules.py:58-62): a task filter registered through the documented hook is
+            # dropped with a "enabled but not registered" warning.  The harness registers it again here, so that the
+            # filter the task API documents actually runs; parity of the generic route is defined on that behaviour.
+            for name, fn in hooks.get("filters", []):
+                self.action_processor.register_post_action_filter(name, fn)
         if hasattr(self.task, "finalize_setup"):
             self.task.finalize_setup()
         self.control_dt = self.physics_manager.control_dt

@@ -84,3 +84,32 @@ def test_reference_dims_and_constants():
     ref, ora = make_pair("BlindGrasping", 4, {})
     assert ref.num_observations == 158 and abs(ref.control_dt - 0.02) < 1e-12
     assert ref.task.contact_duration_threshold_steps == 100 == ora.contact_duration_threshold_steps
+
+
+def test_oracle_with_custom_task_hooks_vs_reference():
+    """SURVEY 8f N4: the toy third task (custom action rule, pre-action rule, post-action filter, extra reward term;
+    oracle/toy_hooks.py) through the UNMODIFIED reference components (ActionRules / StepProcessor / RewardCalculator run
+    the callables) against the oracle port running the same callables - bit-exact over 220 steps."""
+    from oracle import toy_hooks
+    from oracle.dexstep_oracle import OracleEnv
+
+    n, steps = 24, 220
+    layout = synth.BodyLayout(with_box=False)
+    ref = RefEnv("BaseTask", n, layout=layout, hooks=toy_hooks.HOOKS)
+    cfg = load_reference_cfg("BaseTask", n)
+    cfg["task"]["reward_weights"][toy_hooks.EXTRA_REWARD_NAME] = toy_hooks.EXTRA_REWARD_WEIGHT
+    ora = OracleEnv(cfg, n, layout, synth.dof_props_tensor())
+    ora.hooks = toy_hooks.HOOKS
+    world = synth.ScriptedWorld(n, layout, seed=131, nact=ref.num_actions)
+    bad = []
+
+    def on_step(t, envs):
+        a, b = envs[0].snapshot(), envs[1].snapshot()
+        for m in compare_snapshots(a, b, rtol=0.0, atol=0.0):
+            if len(bad) < 10:
+                bad.append(f"step {t}: {m}")
+        if t > 2:
+            assert f"rc/{toy_hooks.EXTRA_REWARD_NAME}_weighted" in a
+
+    run_lockstep([ref, ora], world, steps, on_step)
+    assert not bad, "\n".join(bad)
