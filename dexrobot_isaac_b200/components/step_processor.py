@@ -83,11 +83,11 @@ class StepProcessor:
         # pre-action rule (step_processor.py:66-73): the kernel wrote the identity rule; a custom rule replaces it
         if ap.pre_action_rule is not None:
             art = ap.pre_action_rule(ap.active_prev_targets, {"obs_dict": obs_dict, "env": env})
-            ap.active_rule_targets.copy_(art)
-        obs_dict["active_rule_targets"] = ap.active_rule_targets
-        sl = p.spec.obs_slices.get("active_rule_targets")
-        if sl is not None and ap.pre_action_rule is not None:
-            env.obs_buf[:, sl[0]:sl[1]].copy_(ap.active_rule_targets)
+            ap.active_rule_targets.copy_(art)                        # the state the next process_actions reads
+            obs_dict["active_rule_targets"].copy_(art)               # the materialised obs_dict entry (a buffer view)
+            sl = p.spec.obs_slices.get("active_rule_targets")
+            if sl is not None:
+                env.obs_buf[:, sl[0]:sl[1]].copy_(art)
         env.obs_dict = obs_dict
         # task reward terms the kernel does not know (step_processor.py:183-202, reward_calculator.py:223-275)
         comps = dict(env.extras["reward_components"])

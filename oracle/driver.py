@@ -124,6 +124,16 @@ def compare_snapshots(ref: Dict[str, torch.Tensor], got: Dict[str, torch.Tensor]
 
 
 # ------------------------------------------------------------------ golden fixtures
+def golden_cfg(meta, loader):
+    """The task config a fixture was recorded with: ``loader`` is load_task_config (or load_reference_cfg-compatible)."""
+    cfg = loader(meta["task"], num_envs=meta["n"], control_mode=meta["control_mode"],
+                 policy_controls_hand_base=meta["ctrl_base"], policy_controls_fingers=meta["ctrl_fingers"])
+    if meta.get("ties"):
+        from .synth import tie_config
+        tie_config(cfg)
+    return cfg
+
+
 def load_golden(path):
     import numpy as np
 
@@ -143,10 +153,14 @@ def check_against_golden(path, make_env, rtol=1e-5, atol=1e-6, max_report=12, ig
 
     z, meta = load_golden(path)
     env = make_env(meta)
-    from .synth import BodyLayout, ScriptedWorld
+    from .synth import BodyLayout, ScriptedWorld, TieWorld
 
     layout = BodyLayout(with_box=meta["task"] == "BlindGrasping")
-    world = ScriptedWorld(meta["n"], layout, seed=meta["seed"], nact=env.num_actions)
+    if meta.get("ties"):
+        world = TieWorld(meta["n"], layout, env.cfg, seed=meta["seed"], nact=env.num_actions)
+    else:
+        world = ScriptedWorld(meta["n"], layout, seed=meta["seed"], nact=env.num_actions)
+    E = {k.split("/", 1)[1]: z[k] for k in z.files if k.startswith("elem/")}
     steps = meta["steps"]
     full_steps = sorted({int(k.split("/")[1]) for k in z.files if k.startswith("full/")})
     bad: List[str] = []
@@ -172,6 +186,10 @@ def check_against_golden(path, make_env, rtol=1e-5, atol=1e-6, max_report=12, ig
             scale = 1.0 if k == "rew_buf" else 64.0  # row sums accumulate per-element tolerance
             if not bool(((ref - v).abs() <= scale * atol + rtol * ref.abs() * (1.0 if k == "rew_buf" else 8.0)).all()):
                 bad.append(f"step {t} {k}: max err {float((ref - v).abs().max()):.3e}")
+        if E:  # element-wise, every step (same bound as the full snapshots)
+            ref_e = {k: torch.from_numpy(v[t]) for k, v in E.items()}
+            for m in compare_snapshots(ref_e, s, rtol, atol):
+                bad.append(f"step {t} {m}")
         if t in full_steps:
             ref_full = {k.split("/", 2)[2]: torch.from_numpy(z[k]) for k in z.files if k.startswith(f"full/{t}/")}
             for m in compare_snapshots(ref_full, s, rtol, atol, skip_rows=ref_full["reset_buf"].bool(),

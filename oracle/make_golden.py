@@ -19,7 +19,7 @@ import torch
 
 from . import synth
 from .driver import run_lockstep
-from .ref_harness import RefEnv
+from .ref_harness import RefEnv, load_reference_cfg
 
 FULL_STEPS = (0, 1, 2, 3, 150, 201, 202, 203, 228, 232, 300, 352, 400, 499, 500, 520)
 GOLDEN = {
@@ -28,7 +28,14 @@ GOLDEN = {
     "basetask_position_n32": dict(task="BaseTask", n=32, seed=13, steps=64, kw=dict(control_mode="position")),
     "blindgrasping_nobase_n32": dict(task="BlindGrasping", n=32, seed=14, steps=260,
                                      kw=dict(policy_controls_hand_base=False)),
+    # every element of obs_buf / full_dof_targets / active_prev_targets of EVERY step (not row sums)
+    "blindgrasping_elementwise_n12": dict(task="BlindGrasping", n=12, seed=15, steps=520, kw={}, elementwise=True),
+    "basetask_elementwise_n8": dict(task="BaseTask", n=8, seed=16, steps=310, kw={}, elementwise=True),
+    # thresholds hit exactly (synth.TieWorld + synth.tie_config), the reference's own answers at the ties
+    "blindgrasping_ties_n32": dict(task="BlindGrasping", n=32, seed=17, steps=520, kw={}, ties=True),
+    "basetask_ties_n32": dict(task="BaseTask", n=32, seed=18, steps=310, kw={}, ties=True),
 }
+ELEMENTWISE_KEYS = ("obs_buf", "full_dof_targets", "active_prev_targets")
 
 
 def input_checksum(world, t, ep_step, box0):
@@ -38,9 +45,16 @@ def input_checksum(world, t, ep_step, box0):
 
 
 def record(name, spec, out_dir):
-    env = RefEnv(spec["task"], spec["n"], **spec["kw"])
-    world = synth.ScriptedWorld(spec["n"], env.layout, seed=spec["seed"], nact=env.num_actions)
+    ties, elementwise = bool(spec.get("ties")), bool(spec.get("elementwise"))
+    if ties:
+        cfg = synth.tie_config(load_reference_cfg(spec["task"], spec["n"]))
+        env = RefEnv(spec["task"], spec["n"], cfg=cfg, **spec["kw"])
+        world = synth.TieWorld(spec["n"], env.layout, cfg, seed=spec["seed"], nact=env.num_actions)
+    else:
+        env = RefEnv(spec["task"], spec["n"], **spec["kw"])
+        world = synth.ScriptedWorld(spec["n"], env.layout, seed=spec["seed"], nact=env.num_actions)
     rec = {}
+    elem = {k: [] for k in ELEMENTWISE_KEYS} if elementwise else {}
     per_step = {k: [] for k in ("reset_buf", "episode_step_count", "rew_buf", "obs_rowsum", "tgt_rowsum",
                                 "success", "failure", "timeout", "stage", "success_duration_steps")}
 
@@ -56,6 +70,8 @@ def record(name, spec, out_dir):
         if "task/current_stage" in s:
             per_step["stage"].append(s["task/current_stage"].numpy().astype(np.int8))
             per_step["success_duration_steps"].append(s["task/success_duration_steps"].numpy().astype(np.int16))
+        for k in elem:
+            elem[k].append(s[k].numpy().copy())
         if t in FULL_STEPS and t <= spec["steps"]:
             for k, v in s.items():
                 if v is not None:
@@ -65,6 +81,9 @@ def record(name, spec, out_dir):
     for k, v in per_step.items():
         if v:
             rec[f"steps/{k}"] = np.stack(v)
+    for k, v in elem.items():
+        rec[f"elem/{k}"] = np.stack(v)
+    rec["meta/ties"] = np.array(ties)
     rec["meta/task"] = np.array(spec["task"])
     rec["meta/n"] = np.array(spec["n"])
     rec["meta/seed"] = np.array(spec["seed"])
@@ -80,9 +99,12 @@ def record(name, spec, out_dir):
 
 
 def main():
+    """python -m oracle.make_golden [name ...]   (no names = all fixtures)"""
     out_dir = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
     os.makedirs(out_dir, exist_ok=True)
     for name, spec in GOLDEN.items():
+        if len(sys.argv) > 1 and name not in sys.argv[1:]:
+            continue
         record(name, spec, out_dir)
 
 

@@ -351,3 +351,140 @@ class ScriptedWorld:
         cf[rows, lay.box_body] = boxf[rows]
         _guard_geometry(rb, root, lay, box0)
         return st
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# tie cases: quantities that feed a thresholded mask placed EXACTLY on the threshold
+def tie_config(cfg: dict) -> dict:
+    """In place: a dyadic control_dt (sim.dt = 2^-7 -> control_dt = 2^-6) and stage durations that are exact multiples of it
+    with the SAME step counts as the shipped config (200 / 150 / 25 / 100 control steps), so that ``time_in_stage``,
+    ``stage_contact_duration`` and the grasp duration land exactly on their thresholds (blind_grasping_task.py:835-978,
+    1210-1236).  Everything else is the shipped configuration."""
+    cfg["sim"]["dt"] = 2.0 ** -7
+    tc = cfg["task"]
+    if "stage1_duration" in tc:
+        tc["stage1_duration"] = 200 / 64
+        tc["stage2_duration"] = 150 / 64
+        tc["stage_evaluation"]["stage2_contact_success_threshold"] = 25 / 64
+        tc["contact_duration_threshold"] = 100 / 64
+    return cfg
+
+
+class TieWorld(ScriptedWorld):
+    """ScriptedWorld whose states are post-processed so that, in a random ~1/6 of the envs per step and quantity, a
+    quantity that feeds a strict / non-strict comparison of the path sits exactly on its float32 threshold:
+
+      * monitored contact forces of magnitude exactly f32(contact_binary_threshold) and exactly f32(0.1)
+        (observation_encoder.py:712 ``>``; reward_calculator.py:186 ``> 0.1``), box force likewise (blind_grasping_task.py:797),
+      * a fingerpad at exactly f32(proximity_threshold) from the box centre (:797-812 ``<``),
+      * box height exactly f32(success_height_threshold) (:885 ``>``),
+      * fingertip / hand-base height exactly the height-safety thresholds (step_processor.py:150-160 ``<``),
+      * hand at exactly f32(max_box_distance) from the box (:1290 ``>``),
+      * box speed exactly f32(velocity_tolerance) (:1305-1330 ``<=``).
+
+    The vectors are axis aligned and the other coordinate of the difference is zero, so squares, sums, differences and
+    IEEE sqrt are exact whatever the summation order or FMA contraction of an implementation.  ``hits`` counts the injected
+    ties per kind (tests assert they happened)."""
+
+    def __init__(self, n, layout, cfg: dict, seed: int = 1234, nact: int = 18, rate: float = 1.0 / 6.0,
+                 scripted_rate: float = 0.002, **kw):
+        kw.setdefault("scenario_weights", [8, 3, 2, 2, 1, 1, 1, 2, 1])
+        super().__init__(n, layout, seed=seed, nact=nact, **kw)
+        self.scripted_rate = scripted_rate
+        tc = cfg["task"]
+        f32 = lambda v: float(torch.tensor(float(v), dtype=torch.float32))  # noqa: E731
+        self.rate = rate
+        self.thr_contact = f32(tc["contact_binary_threshold"])
+        self.thr_stability = f32(0.1)
+        hs = (tc.get("termination", {}) or {}).get("height_safety")
+        self.thr_hand_z = f32(hs["handbase_threshold"]) if hs else None
+        self.thr_tip_z = f32(hs["fingertip_threshold"]) if hs else None
+        if layout.with_box:
+            self.thr_prox = f32(math.sqrt(3) * cfg["env"]["box"]["size"] / 2 * 1.2)
+            self.thr_box_z = f32(tc["success_height_threshold"])
+            self.thr_far = f32(tc["max_box_distance"])
+            self.thr_vel = f32(tc["quality_thresholds"]["velocity_tolerance"])
+        self.hits: Dict[str, int] = {}
+
+    def _pick(self, gen, kind: str) -> torch.Tensor:
+        # scripted envs (scenario != 0) need undisturbed streaks of 25 / 100 steps to walk the FSM (and so reach the
+        # timer ties), so they get ties rarely; the noise envs get them at the full rate
+        rate = torch.where(self.scenario == 0, self.rate, self.scripted_rate)
+        rows = torch.nonzero(torch.rand(self.n, generator=gen) < rate).flatten()
+        self.hits[kind] = self.hits.get(kind, 0) + int(rows.numel())
+        return rows
+
+    @staticmethod
+    def _axis(rows, gen):
+        """Per-row signed unit vector along a random axis."""
+        ax = torch.randint(0, 3, (rows.numel(),), generator=gen)
+        sg = torch.randint(0, 2, (rows.numel(),), generator=gen).float() * 2 - 1
+        v = torch.zeros(rows.numel(), 3)
+        v[torch.arange(rows.numel()), ax] = sg
+        return v, ax
+
+    def state(self, t, ep_step, box0=None):
+        st = super().state(t, ep_step, box0)
+        lay, n = self.layout, self.n
+        gen = self._gen(t, 9)
+        rb, cf, root = st["rigid_body_states"], st["net_contact_force"], st["actor_root_state"]
+        mon = torch.tensor(lay.contacts)
+        for kind, thr in (("force==contact_thr", self.thr_contact), ("force==0.1", self.thr_stability)):
+            rows = self._pick(gen, kind)
+            body = mon[torch.randint(0, len(lay.contacts), (rows.numel(),), generator=gen)]
+            cf[rows, body] = self._axis(rows, gen)[0] * thr
+        if self.thr_tip_z is not None:
+            rows = self._pick(gen, "tip_z==thr")
+            tip = torch.tensor(lay.tips)[torch.randint(0, NUM_FINGERS, (rows.numel(),), generator=gen)]
+            rb[rows, tip, 2] = self.thr_tip_z
+            rows = self._pick(gen, "hand_z==thr")
+            rb[rows, lay.hand, 2] = self.thr_hand_z
+            root[rows, 0, 2] = self.thr_hand_z
+        if not lay.with_box:
+            return st
+        ba, bb = lay.box_actor, lay.box_body
+
+        def zero_box_axis(rows, ax):
+            root[rows, ba, ax] = 0.0
+            rb[rows, bb, ax] = 0.0
+
+        rows = self._pick(gen, "box_force==contact_thr")
+        cf[rows, bb] = self._axis(rows, gen)[0] * self.thr_contact
+        rows = self._pick(gen, "box_z==height_thr")
+        root[rows, ba, 2] = self.thr_box_z
+        rb[rows, bb, 2] = self.thr_box_z
+        rows = self._pick(gen, "box_speed==tol")
+        root[rows, ba, 7:10] = self._axis(rows, gen)[0] * self.thr_vel
+        # geometry ties: zero the box coordinate along the chosen axis so that (box + d) - box == d exactly
+        rows = self._pick(gen, "pad_dist==prox")
+        v, ax = self._axis(rows, gen)
+        zero_box_axis(rows, ax)
+        pad = torch.tensor(lay.pads)[torch.randint(0, NUM_FINGERS, (rows.numel(),), generator=gen)]
+        rb[rows, pad, 0:3] = root[rows, ba, 0:3] + v * self.thr_prox
+        rows = self._pick(gen, "hand_dist==max")
+        v, ax = self._axis(rows, gen)
+        v[:, 2] = v[:, 2].abs()  # never below the ground plane (that would be a plain hitting_ground failure)
+        zero_box_axis(rows, ax)
+        # (a pad tie of the same env stays valid only if it used the same axis; re-place pads of these rows is not needed:
+        # every kind is counted on its own and the comparison is on whatever the state finally holds)
+        rb[rows, lay.hand, 0:3] = root[rows, ba, 0:3] + v * self.thr_far
+        root[rows, 0, 0:3] = rb[rows, lay.hand, 0:3]
+        return st
+
+    def count_exact(self, st: Dict[str, torch.Tensor]) -> Dict[str, int]:
+        """How many quantities of ``st`` sit exactly on a threshold (computed like the path computes them)."""
+        lay = self.layout
+        rb, cf, root = st["rigid_body_states"], st["net_contact_force"], st["actor_root_state"]
+        mag = torch.norm(cf[:, list(lay.contacts)], dim=2)
+        out = {"force==contact_thr": int((mag == self.thr_contact).sum()), "force==0.1": int((mag == self.thr_stability).sum())}
+        if self.thr_tip_z is not None:
+            out["tip_z==thr"] = int((rb[:, list(lay.tips), 2] == self.thr_tip_z).sum())
+            out["hand_z==thr"] = int((rb[:, lay.hand, 2] == self.thr_hand_z).sum())
+        if lay.with_box:
+            box = root[:, lay.box_actor, 0:3]
+            out["box_force==contact_thr"] = int((torch.norm(cf[:, lay.box_body], dim=1) == self.thr_contact).sum())
+            out["box_z==height_thr"] = int((box[:, 2] == self.thr_box_z).sum())
+            out["box_speed==tol"] = int((torch.norm(root[:, lay.box_actor, 7:10], dim=1) == self.thr_vel).sum())
+            out["pad_dist==prox"] = int((torch.norm(rb[:, list(lay.pads), 0:3] - box.unsqueeze(1), dim=2) == self.thr_prox).sum())
+            out["hand_dist==max"] = int((torch.norm(rb[:, lay.hand, 0:3] - box, dim=1) == self.thr_far).sum())
+        return out

@@ -18,7 +18,7 @@ from dexrobot_isaac_b200.config import load_task_config
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
-RTOL, ATOL = 1e-5, 1e-6
+RTOL, ATOL = 1e-5, 1e-7
 
 
 def _toy_task_class():
@@ -327,7 +327,8 @@ def test_blind_grasping_facade_hooks_hand_out_the_kernel_results():
         terms = task.compute_task_reward_terms(cud.obs_dict)
         for k, v in terms.items():
             seen["terms"].add(k)
-            a, b = snap[f"rc/{k}"], v.cpu()
+            # the reference (and the oracle) only materialise a stage's terms while some env is in that stage
+            a, b = snap.get(f"rc/{k}", torch.zeros(n)), v.cpu()
             tol = ATOL + RTOL * max(floors.get(f"rc/{k}", 0.0), 0.0)
             if not torch.allclose(a, b, rtol=RTOL, atol=tol):
                 bad.append(f"step {t} reward term {k}")

@@ -16,7 +16,7 @@ from dexrobot_isaac_b200.config import load_task_config
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
-RTOL, ATOL = 1e-5, 1e-6
+RTOL, ATOL = 1e-5, 1e-7
 
 
 def lean_env(task, n, layout=None, observer=False, **kw):

@@ -6,7 +6,7 @@ import os
 import pytest
 
 from oracle import synth
-from oracle.driver import check_against_golden
+from oracle.driver import check_against_golden, golden_cfg
 from dexrobot_isaac_b200.config import load_task_config
 
 GOLDEN = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.npz")))
@@ -15,9 +15,7 @@ GOLDEN = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.n
 def make_oracle(meta):
     from oracle.dexstep_oracle import OracleEnv
 
-    cfg = load_task_config(meta["task"], num_envs=meta["n"], control_mode=meta["control_mode"],
-                           policy_controls_hand_base=meta["ctrl_base"],
-                           policy_controls_fingers=meta["ctrl_fingers"])
+    cfg = golden_cfg(meta, load_task_config)
     layout = synth.BodyLayout(with_box=meta["task"] == "BlindGrasping")
     return OracleEnv(cfg, meta["n"], layout, synth.dof_props_tensor())
 
@@ -29,4 +27,4 @@ def test_oracle_matches_reference_golden(path):
 
 
 def test_golden_fixtures_present():
-    assert len(GOLDEN) >= 4
+    assert len(GOLDEN) >= 8

@@ -113,3 +113,41 @@ def test_oracle_with_custom_task_hooks_vs_reference():
 
     run_lockstep([ref, ora], world, steps, on_step)
     assert not bad, "\n".join(bad)
+
+
+@pytest.mark.parametrize("task,n,steps", [("BaseTask", 48, 300), ("BlindGrasping", 48, 520)])
+def test_oracle_bit_exact_vs_reference_on_threshold_ties(task, n, steps):
+    """thresholds hit EXACTLY (synth.TieWorld: forces of exactly f32(0.1) / f32(contact threshold),
+    a pad exactly at the proximity threshold, box_z == f32(0.2), tip / hand height on the height-safety thresholds, hand at
+    exactly max_box_distance, box speed == velocity tolerance; synth.tie_config: a dyadic control_dt so time_in_stage /
+    stage_contact_duration / grasp duration land exactly on 200 / 150 / 25 / 100 steps' worth of seconds).  The unmodified
+    reference components and the oracle port must agree bit for bit - strict vs non-strict comparisons and f32-vs-double
+    thresholds are exactly what this distinguishes."""
+    from oracle.dexstep_oracle import OracleEnv
+
+    layout = synth.BodyLayout(with_box=task == "BlindGrasping")
+    cfg_r, cfg_o = (synth.tie_config(load_reference_cfg(task, n)) for _ in range(2))
+    ref = RefEnv(task, n, layout=layout, cfg=cfg_r)
+    ora = OracleEnv(cfg_o, n, layout, synth.dof_props_tensor())
+    assert ref.control_dt == 2.0 ** -6 == ora.control_dt
+    world = synth.TieWorld(n, layout, cfg_o, seed=141, nact=ref.num_actions)
+    bad, seen = [], {"reset": 0, "success": 0, "failure": 0, "timeout": 0, "tis_tie": 0}
+
+    def on_step(t, envs):
+        a, b = envs[0].snapshot(), envs[1].snapshot()
+        for m in compare_snapshots(a, b, rtol=0.0, atol=0.0):
+            if len(bad) < 10:
+                bad.append(f"step {t}: {m}")
+        seen["reset"] += int(a["reset_buf"].sum())
+        for k in ("success", "failure", "timeout"):
+            seen[k] += int(a[f"extras/{k}"].sum())
+        if task == "BlindGrasping":  # a stage timer that sits exactly on its duration was seen (and acted upon)
+            tis = a["task/time_in_stage"]
+            seen["tis_tie"] += int(((tis == 200 / 64) | (tis == 150 / 64)).sum())
+
+    run_lockstep([ref, ora], world, steps, on_step)
+    assert not bad, "\n".join(bad)
+    assert all(v > 0 for v in world.hits.values()), world.hits
+    assert seen["reset"] > 0 and seen["failure"] > 0
+    if task == "BlindGrasping":
+        assert seen["timeout"] + seen["success"] > 0 and seen["tis_tie"] > 0, seen
