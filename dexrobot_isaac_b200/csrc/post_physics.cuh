@@ -510,13 +510,13 @@ __device__ __forceinline__ void post_stage_in(const PostArgs& A, float* smem, co
 #pragma unroll
     for (int i = 0; i < R; ++i) {
       if (FULL || warp + kPostWarps * i < ne) {
-        v[i][0] = __ldg(g_dof + i * (kPostWarps * 2 * DEX_NUM_DOF));
-        if (p_dof1) v[i][1] = __ldg(g_dof + i * (kPostWarps * 2 * DEX_NUM_DOF) + 32);
+        v[i][0] = __ldcg(g_dof + i * (kPostWarps * 2 * DEX_NUM_DOF));
+        if (p_dof1) v[i][1] = __ldcg(g_dof + i * (kPostWarps * 2 * DEX_NUM_DOF) + 32);
         const float* rb = g_rb + i * rb_step;
         if (p_rb0) v[i][2] = __ldg(rb + rbo0);
         v[i][3] = __ldg(rb + rbo1);
         if (p_rb2) v[i][4] = __ldg(rb + rbo2);
-        if (p_x) v[i][5] = __ldg(gx + i * x_step);
+        if (p_x) v[i][5] = __ldcg(gx + i * x_step);
       }
     }
     pdl_wait();  // everything above touched only kernel parameters and the sim tensors
@@ -533,7 +533,7 @@ __device__ __forceinline__ void post_stage_in(const PostArgs& A, float* smem, co
       if (b < nbatch && act) {
 #pragma unroll
         for (int u = 0; u < kRowU; ++u)
-          w[b][u] = __ldg(reinterpret_cast<const float*>(A.in_ptr[b * kRowBatch + warp + kPostWarps * u] + colb));
+          w[b][u] = __ldcg(reinterpret_cast<const float*>(A.in_ptr[b * kRowBatch + warp + kPostWarps * u] + colb));
       }
     }
     // typed rows (int64 counters, bool flags): at most a few per warp, loaded as 32-bit values
@@ -541,14 +541,14 @@ __device__ __forceinline__ void post_stage_in(const PostArgs& A, float* smem, co
     float wt = 0.0f;
     if (act && r_typed < A.n_in) {
       if (r_typed < A.n_in_i64)  // int64 state is small (counts, stage): keep the low word
-        wt = __int_as_float((int)__ldg(reinterpret_cast<const long long*>(A.in_ptr[r_typed]) + col));
+        wt = __int_as_float((int)__ldcg(reinterpret_cast<const long long*>(A.in_ptr[r_typed]) + col));
       else
-        wt = __ldg(reinterpret_cast<const unsigned char*>(A.in_ptr[r_typed]) + col) ? 1.0f : 0.0f;
+        wt = __ldcg(reinterpret_cast<const unsigned char*>(A.in_ptr[r_typed]) + col) ? 1.0f : 0.0f;
     }
     if (p_tgt) {  // full_dof_targets is written by dex_pre_physics: always after the wait
 #pragma unroll
       for (int i = 0; i < R; ++i)
-        if (FULL || warp + kPostWarps * i < ne) v[i][6] = __ldg(g_tgt + i * (kPostWarps * DEX_NUM_DOF));
+        if (FULL || warp + kPostWarps * i < ne) v[i][6] = __ldcg(g_tgt + i * (kPostWarps * DEX_NUM_DOF));
     }
     // ---- stores ----
     const unsigned Eb = sbase + (unsigned)(lane * S) * 4u;
@@ -581,9 +581,9 @@ __device__ __forceinline__ void post_stage_in(const PostArgs& A, float* smem, co
     for (int r = r_typed + kPostWarps; act && r < A.n_in; r += kPostWarps) {
       float t;
       if (r < A.n_in_i64)
-        t = __int_as_float((int)__ldg(reinterpret_cast<const long long*>(A.in_ptr[r]) + col));
+        t = __int_as_float((int)__ldcg(reinterpret_cast<const long long*>(A.in_ptr[r]) + col));
       else
-        t = __ldg(reinterpret_cast<const unsigned char*>(A.in_ptr[r]) + col) ? 1.0f : 0.0f;
+        t = __ldcg(reinterpret_cast<const unsigned char*>(A.in_ptr[r]) + col) ? 1.0f : 0.0f;
       sts_f32(Eb + (unsigned)A.in_meta[r] * 4u, t);
     }
   }

@@ -245,6 +245,14 @@ class StepPipeline:
                 "dex_reset_idx")
         self.launches += 1
 
+    def set_rng_step(self, step: int):
+        """Rewind / restore the device-resident Philox step counter (e.g. when resuming from a checkpoint).  The tile
+        records are stamped with it (include/dexstep.h, DexEpilogueBuffers.tile_records): they are re-zeroed so that no
+        stale record can pass as current."""
+        self.state["rng_step"].fill_(int(step))
+        self.epi["tile_records"].zero_()
+        self.host_step = int(step)
+
     def epilogue(self):
         """dex_step_epilogue: env_ids = nonzero(reset_buf), rates, consecutive_successes (1 launch)."""
         L.check(self.lib.dex_step_epilogue(ctypes.byref(self.params), ctypes.byref(self._epi), self.n, self._stream()),

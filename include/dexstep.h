@@ -321,7 +321,18 @@ typedef struct DexEpilogueBuffers {
                                      fused into dex_post_physics (and then rng_step is required too).  Every 32-env tile
                                      publishes its reset ballot word and its counter contributions as three self-validating
                                      8-byte records (top 16 bits = step stamp derived from *rng_step); one extra thread block
-                                     behind the tiles polls them - no fence, no atomic, no counter contention on the step path */
+                                     behind the tiles polls them - no fence, no atomic, no counter contention on the step path.
+                                     SCHEDULING: the polling block has the highest block index of the launch.  The persistent
+                                     and single-pass kernels launch at most (SMs x occupancy) blocks, polling block included,
+                                     so every tile's block is resident by construction; the tile kernel relies on blocks being
+                                     dispatched in index order (every tile's block has started before the polling block does),
+                                     which holds on every CUDA GPU to date but is not a documented guarantee.  All waits are
+                                     therefore BOUNDED: a record that does not appear within ~2 s traps the kernel and the call
+                                     that next synchronises the stream returns a CUDA error (never a hang); pass ep == NULL to
+                                     dex_post_physics and call dex_step_epilogue for a configuration without that dependence.
+                                     STAMPS: a record is current when its stamp == (*rng_step + 1) & 0xffff, so *rng_step must
+                                     only move forward by dex_step_epilogue / the fused epilogue; a caller that rewinds or
+                                     restores *rng_step, or shares tile_records between pipelines, must re-zero tile_records */
 } DexEpilogueBuffers;
 
 const char* dex_strerror(int code);

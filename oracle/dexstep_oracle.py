@@ -126,7 +126,7 @@ class OracleEnv:
     post_physics_step / snapshot."""
 
     def __init__(self, cfg: dict, num_envs: int, layout, dof_props: torch.Tensor,
-                 init_uniforms: Optional[torch.Tensor] = None):
+                 init_uniforms: Optional[torch.Tensor] = None, physics_steps_per_control_step: int = 2):
         self.cfg = cfg
         self.env_cfg, self.task_cfg, self.sim_cfg = cfg["env"], cfg["task"], cfg["sim"]
         self.task_name = self.task_cfg["name"]
@@ -238,7 +238,7 @@ class OracleEnv:
         # steps were taken -> control_dt = 2 * sim.dt (physics_manager.py:243-259)
         self.full_dof_targets.zero_()
         self.reset_idx(torch.arange(n))
-        self.control_dt = self.sim_cfg["dt"] * 2
+        self.control_dt = self.sim_cfg["dt"] * physics_steps_per_control_step
         # action_processor.py:416-434
         self.max_deltas = torch.zeros(N_ACTIVE)
         self.max_deltas[0:3] = self.control_dt * tc["max_base_linear_velocity"]

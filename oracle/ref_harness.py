@@ -114,7 +114,7 @@ class RefEnv:
     def __init__(self, task_name: str, num_envs: int, layout: Optional[synth.BodyLayout] = None,
                  control_mode: Optional[str] = None, policy_controls_hand_base: bool = True,
                  policy_controls_fingers: bool = True, init_uniforms: Optional[torch.Tensor] = None,
-                 cfg: Optional[dict] = None, hooks: Optional[dict] = None):
+                 cfg: Optional[dict] = None, hooks: Optional[dict] = None, physics_steps_per_control_step: int = 2):
         if not reference_available():
             raise RuntimeError(f"reference not found at {REFERENCE_ROOT}")
         _ensure_paths()
@@ -256,6 +256,11 @@ class RefEnv:
         self.physics_manager.start_control_cycle_measurement()
         self.action_processor.process_actions(torch.zeros(n, self.num_actions), torch.zeros(n, 18))
         self.physics_manager.step_physics(refresh_tensors=True)
+        # the reference MEASURES the number of physics steps per control step here (physics_manager.py:243-259): one
+        # step above + the one reset_idx takes = 2 with the stock integration; an integration whose reset needs more
+        # steps measures more - emulated by stepping the (fake) physics again
+        for _ in range(physics_steps_per_control_step - 2):
+            self.physics_manager.step_physics(refresh_tensors=True)
         self.reset_idx(torch.arange(n))
         self.physics_manager.finish_control_cycle_measurement()
         self.action_processor.finalize_setup()

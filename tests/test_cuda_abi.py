@@ -177,6 +177,17 @@ def test_philox_reset_ranges_and_freshness():
     assert torch.equal(apt[:, :6], draws[1][:, :6])
     assert torch.equal(apt[:, 6], draws[1][:, 6]) and torch.equal(apt[:, 8], draws[1][:, 9])
     assert torch.allclose(apt[:, 9], draws[1][:, 22] / 2.0)
+    # the stand-alone reset and the reset fused into dex_post_physics draw from different Philox streams: an env reset by
+    # both within one step (same step counter) gets two different poses
+    step_before = int(p.state["rng_step"])
+    p.reset_idx(None)
+    a = env.dof_pos.clone()
+    env.episode_step_count.fill_(int(p.params.max_episode_length) - 1)  # every env times out -> fused reset of all
+    p.pre_physics(torch.zeros(n, env.num_actions, device=DEV))
+    p.post_step()
+    torch.cuda.synchronize()
+    assert int(p.out["reset_buf"].sum()) == n and int(p.state["rng_step"]) == step_before + 1
+    assert not torch.equal(a[:, 0:6], env.dof_pos[:, 0:6])
 
 
 @pytest.mark.parametrize("task", ["BaseTask", "BlindGrasping"])

@@ -112,3 +112,34 @@ def test_lockstep_basetask_n4096():
 def test_lockstep_blindgrasping_n4096():
     seen = _lockstep("BlindGrasping", 4096, 240, seed=108, check_every=40)
     assert seen["reset"] > 0
+
+
+@pytest.mark.parametrize("materialize", [False, True], ids=["persistent", "tile+obs_dict"])
+def test_lockstep_other_physics_step_count(materialize):
+    """physics_steps_per_control_step (the reference measures it, physics_manager.py:243-259) is a constructor
+    argument of DexStepEnv; 3 instead of the stock 2 changes control_dt -> max_deltas, stage timers, the contact-duration
+    step threshold and every finite difference.  Oracle pinned for the same value by tests/test_oracle_vs_reference.py."""
+    from oracle.dexstep_oracle import OracleEnv
+    from dexrobot_isaac_b200.env import DexStepEnv
+    from dexrobot_isaac_b200.params import BodyLayout
+
+    n, layout = 96, synth.BodyLayout(with_box=True)
+    cfg = load_task_config("BlindGrasping", num_envs=n)
+    ora = OracleEnv(cfg, n, layout, synth.dof_props_tensor(), physics_steps_per_control_step=3)
+    cud = DexStepEnv(cfg, n, BodyLayout.from_synth(layout), synth.dof_props_tensor(), device="cuda:0",
+                     materialize_obs_dict=materialize, physics_steps_per_control_step=3)
+    assert abs(cud.control_dt - 0.03) < 1e-12
+    assert int(cud.pipeline.params.contact_duration_threshold_steps) == ora.contact_duration_threshold_steps == 66
+    world = synth.ScriptedWorld(n, layout, seed=171, nact=ora.num_actions)
+    floors = penetration_floors(cfg)
+    bad = []
+
+    def on_step(t, envs):
+        a, b = envs[0].snapshot(), envs[1].snapshot()
+        ign = () if materialize else ("obs/",)
+        for m in compare_snapshots(a, b, RTOL, ATOL, skip_rows=a["reset_buf"].bool(), ignore=ign, floors=floors):
+            if len(bad) < 20:
+                bad.append(f"step {t} {m}")
+
+    run_lockstep([ora, cud], world, 380, on_step)
+    assert not bad, "\n".join(bad)

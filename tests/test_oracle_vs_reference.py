@@ -151,3 +151,27 @@ def test_oracle_bit_exact_vs_reference_on_threshold_ties(task, n, steps):
     assert seen["reset"] > 0 and seen["failure"] > 0
     if task == "BlindGrasping":
         assert seen["timeout"] + seen["success"] > 0 and seen["tis_tie"] > 0, seen
+
+
+def test_oracle_vs_reference_other_physics_step_count():
+    """control_dt is MEASURED by the reference (physics steps per control step x sim.dt,
+    physics_manager.py:243-259) and feeds max_deltas, the stage timers, contact_duration_threshold_steps and the finite
+    differences.  A count of 3 instead of the stock 2: the port follows."""
+    from oracle.dexstep_oracle import OracleEnv
+
+    n, layout = 24, synth.BodyLayout(with_box=True)
+    ref = RefEnv("BlindGrasping", n, layout=layout, physics_steps_per_control_step=3)
+    ora = OracleEnv(load_reference_cfg("BlindGrasping", n), n, layout, synth.dof_props_tensor(),
+                    physics_steps_per_control_step=3)
+    assert abs(ref.control_dt - 0.03) < 1e-12 and ref.control_dt == ora.control_dt
+    assert ref.task.contact_duration_threshold_steps == ora.contact_duration_threshold_steps == 66
+    world = synth.ScriptedWorld(n, layout, seed=161, nact=ref.num_actions)
+    bad = []
+
+    def on_step(t, envs):
+        for m in compare_snapshots(envs[0].snapshot(), envs[1].snapshot(), rtol=0.0, atol=0.0):
+            if len(bad) < 10:
+                bad.append(f"step {t}: {m}")
+
+    run_lockstep([ref, ora], world, 380, on_step)
+    assert not bad, "\n".join(bad)
