@@ -7,13 +7,15 @@
 // so un-fused multiplies cost nothing measurable.  No --use_fast_math: sqrtf/expf/division are the IEEE
 // (<=1-2 ulp) versions.
 //
-// Layout / mapping (DESIGN.md §3):
-//   * one thread per env for all arithmetic (envs are independent; no cross-env term on the path);
-//   * path-internal state is SoA [K][N] -> thread-per-env loads/stores are naturally 128 B-coalesced;
-//   * buffers whose layout is dictated from outside (Isaac Gym AoS sim tensors, actions, obs_buf,
-//     full_dof_targets) are staged through shared memory per tile of envs: coalesced 128-bit / sector
-//     gathers global->smem, conflict-free odd-stride rows for the thread-per-env side, coalesced
-//     smem->global copy-out.
+// Layout / mapping (DESIGN.md 3-4):
+//   * lane = env for all arithmetic (envs are independent; no cross-env term on the path except the step statistics);
+//   * path-internal state is SoA [K][N]: a warp's access to one row is one 128 B request;
+//   * buffers whose layout is dictated from outside (Isaac Gym AoS sim tensors, actions, obs_buf, full_dof_targets)
+//     are staged through shared memory per tile of 32 envs;
+//   * dex_post_physics dispatches between three kernels over the same arithmetic: the persistent warp-specialised kernel
+//     and the single-pass kernel of post_physics_v2.cuh (lean production path, chosen by tiles per SM) and the
+//     table-driven tile kernel of post_physics.cuh (obs_dict materialisation, OBS_ONLY, stale contacts, A/B runs);
+//   * dex_pre_physics: one kernel, 8 warps x 32 envs per CTA (this file).
 #include <cuda_runtime.h>
 #include <stdint.h>
 

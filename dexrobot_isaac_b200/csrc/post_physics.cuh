@@ -1,26 +1,36 @@
-// post_physics.cuh — the fused post-physics kernel (StepProcessor.process_physics_step, step_processor.py:37-131).
+// post_physics.cuh — the table-driven TILE kernel of the post-physics pass (StepProcessor.process_physics_step,
+// step_processor.py:37-131).  Round 1's production kernel; since round 2 the lean path runs the kernels of
+// post_physics_v2.cuh and this one serves the instances those have no stage for - obs_dict materialisation
+// (DexOutBuffers.obs_dict != NULL), DEX_MODE_OBS_ONLY, DEX_FLAG_STALE_CONTACTS, non-standard layouts - and A/B runs
+// (DEX_FLAG_TILE_KERNEL / DEXSTEP_POST_V1=1).  It is the kernel pinned first against the oracle; the v2 kernels are
+// compared with it bit for bit (tests/test_cuda_v2.py).
 //
-// Design (DESIGN.md §4): "gather table -> compute on a shared-memory slab -> scatter table".
+// Design (DESIGN.md 4.3): "gather table -> compute on a shared-memory slab -> scatter table".
 //   One CTA of 256 threads (8 warps) owns a tile of 32 consecutive envs.  Every env of the tile has a SLAB of
 //   floats in shared memory (odd stride, so `slab[lane * stride + const]` never bank-conflicts when lane = env).
-//   phase 0  stage-in    cp.async (LDGSTS) copies, all in flight at once, one wait:
+//   phase 0  stage-in    plain global loads staged through registers, ALL issued before the first shared store (one
+//                        DRAM round trip per tile):
 //                        * the Isaac Gym AoS rows (dof_state row, 11 rigid-body rows, 5(+1) contact rows, box root
-//                          row, full_dof_targets row) row-per-warp: consecutive lanes = consecutive floats of a row;
+//                          row, full_dof_targets row) row-per-warp: consecutive lanes = consecutive floats of a row
+//                          (with DEX_FLAG_EARLY_SIM_LOADS they are issued before griddepcontrol.wait);
 //                        * the path's SoA state rows through a host-built IN TABLE (row pointer, slab slot, type):
 //                          lane = env, one 128 B line per request.
+//                        Buffers the fused reset writes (dof_state, actor_root_state, full_dof_targets, state rows)
+//                        are read with coherent loads (ld.global.cg), only rigid bodies / contact forces with .nc.
 //   phase 1  items       the per-env arithmetic is cut into independent work items (one fingertip/pad pose, one
 //                        contact sensor, one pad pair, one DOF velocity, hand, box).  Warps take items round-robin,
 //                        lane = env: item-type branches are warp-uniform, all shared accesses conflict-free.
 //                        Items read slab slots and write slab slots - no global memory, no layout logic.
 //   phase 2  scalar      warp 0, lane = env: contact logic, stage FSM, termination, reward terms, masks -> slab;
-//                        cross-env counters via warp ballots.
+//                        cross-env counters via warp ballots, published as the tile's three 8-byte records.
 //   phase 3  stage-out   * obs_buf rows (and the optional obs_dict rows) are GATHERED from the slab through a
 //                          host-built column map (obs column -> slab slot), row-per-warp, coalesced;
 //                        * every updated state / output row leaves through the OUT TABLE (f32 / u8 / i64 rows),
 //                          lane = env, 128 B per request.
 //   phase 4  reset       tiles that contain finished envs (CTA-uniform vote) apply the fused reset.
-//   phase 5  epilogue    optional: the last CTA to finish (atomic ticket) compacts the reset mask into the ordered
-//                        env-id list and finalises the termination statistics (no extra launch).
+//   epilogue             optional (ep != NULL): ONE extra CTA behind the tiles polls the tile records (bounded wait,
+//                        include/dexstep.h DexEpilogueBuffers.tile_records), compacts the reset words into the ordered
+//                        env-id list and finalises the statistics - no extra launch, no atomics on the step path.
 #pragma once
 #include "dexstep_common.cuh"
 

@@ -1,22 +1,35 @@
-// post_physics_v2.cuh — the persistent, warp-specialised post-physics kernel (round 2).
+// post_physics_v2.cuh — the post-physics kernels the lean production path runs (round 2).
 //
-// Same arithmetic as post_physics.cuh (StepProcessor.process_physics_step, step_processor.py:37-131), different
-// machine mapping:
-//   * PERSISTENT grid: <= SMs x CTAs/SM worker CTAs (+ one epilogue CTA), each looping over 32-env tiles, so all
-//     CTAs are co-resident (the epilogue CTA's poll of the tile records needs no scheduling-order assumption) and
-//     every per-CTA setup cost is paid once per launch instead of once per tile.
-//   * WARP SPECIALISATION: 4 producer warps stream tile t+1 into a 2-stage shared-memory ring while 8 consumer
-//     warps compute tile t (mbarrier full/empty pairs).  Memory time and compute latency overlap instead of adding.
-//   * BULK ASYNC COPIES (cp.async.bulk -> SASS UBLKCP, completion on the stage's mbarrier) for everything that is
-//     contiguous in HBM at tile granularity: the dof_state tile (32 x 208 B), the full_dof_targets tile and every
-//     128-byte row segment of the SoA path state; only the scattered Isaac Gym rows (rigid bodies, contact forces,
-//     box root) are gathered with LDG by the producer warps (row-per-warp, sector-exact).
-//   * NO TABLES on the way out: every state row / reward row leaves straight from the registers of the lane (= env)
-//     that computed it (one 128 B request per row), observation values are written into an obs-shaped shared tile
-//     by the work item that produces them and the tile leaves with coalesced row stores.
-//   * The one-warp scalar phase of v1 is split over four warps (finger-box contacts + success counter | stage FSM |
-//     minima + criteria inputs | averages), the ordered reductions stay single-lane per env (parity).
-// Numerics are op-for-op those of v1 (which is pinned to the oracle); lane = env for all arithmetic.
+// Same arithmetic as post_physics.cuh (StepProcessor.process_physics_step, step_processor.py:37-131), op for op (that
+// file is pinned to the oracle and kept for the obs_dict / OBS_ONLY / stale-contact instances); different machine
+// mapping.  Two geometries, chosen per launch by the number of 32-env tiles (launch_post2_t):
+//
+//   post_physics_v2_kernel  PERSISTENT, warp-specialised: <= SMs x CTAs/SM worker CTAs (+ one epilogue CTA) loop over
+//     tiles; 4 producer warps stream tile t+1 into a 2-stage shared-memory ring (mbarrier full/empty pairs) while 8
+//     consumer warps compute tile t.  All CTAs are co-resident, so the epilogue CTA's poll of the tile records needs no
+//     scheduling-order assumption.  Used for <= 2 and > 4 tiles per SM.
+//   post_physics_v2s_kernel SINGLE PASS: one tile per CTA, 8 warps, 4 CTAs per SM, loads staged through registers, the
+//     work block aliased into the stage (Lay<BG, true>) so that four CTAs fit.  Used for 2 < tiles/SM <= 4 (16 384 envs
+//     on 148 SMs = 3.46 tiles per SM), where a persistent grid would leave half of the SMs a third round.
+//
+// What shaped them (profiles/r02_variants.md has the measurements of the variants that did NOT work):
+//   * The path is bound by INSTRUCTION SUPPLY for cold code, not by bytes or issue slots: every CTA runs ~10 K distinct
+//     SASS instructions once per tile.  Cold straight-line code costs ~3 cycles/instruction/SM, code that is resident in
+//     the 32 KB L1.5 ~1.  Hence: all consumer warps run the SAME item code at the same time (round-robin work items,
+//     phase_items), loops are not unrolled, compile-time observation layouts (STD instances, std_obs_off) remove the
+//     table walks, and the scalar phase is split over 4 warps only where the code is short.
+//   * Producer warps gather the scattered Isaac Gym rows and the SoA state rows with 4/8-byte cp.async (LDGSTS, completion
+//     counted on the stage's mbarrier with cp.async.mbarrier.arrive.noinc); cp.async.bulk (UBLKCP) is used only for the
+//     two tile-contiguous arrays (dof_state 32 x 208 B, full_dof_targets) - a bulk copy costs ~50 issue cycles, one per
+//     128-byte row starved the SM sub-partition the producers share with consumers.
+//   * Waiting warps block in hardware: ONE consumer warp polls the stage mbarrier (try_wait.parity with a suspend hint),
+//     the other seven wait behind a named barrier (bar.sync 1, 256).  All polls are bounded (kSpinLimitClocks -> trap).
+//   * NO TABLES on the way out: every state / reward row leaves straight from the registers of the lane (= env) that
+//     computed it (one 128 B request per row); observation values are written into an obs-shaped shared tile by the
+//     work item that produces them and the tile leaves as one bulk store (flat stride) or coalesced row copies.
+//   * Fused extras (all optional, all in the same pass): reset of finished envs, step epilogue (tile records + one
+//     polling CTA), RewardComponentObserver sums, rl_games input normalisation of obs_buf (obs_norm).
+// Numerics: lane = env for all arithmetic; ordered reductions stay single-lane per env (parity with torch's order).
 #pragma once
 #include "post_physics.cuh"
 
