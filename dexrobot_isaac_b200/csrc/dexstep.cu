@@ -273,6 +273,22 @@ int launch_status() {
 // ------------------------------------------------------------------------------------------------
 // C ABI
 // ------------------------------------------------------------------------------------------------
+// ------------------------------------------------------------------------------------------------
+// scratch of dex_post_physics_noalloc: tile records for up to DEX_NOALLOC_MAX_ENVS envs (4 words per 32-env tile, 256 KB).
+// Shared by every call on this GPU, keeps the last call's contents: each call invalidates the part it uses first.
+// ------------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned long long g_noalloc_tile_records[4 * (DEX_NOALLOC_MAX_ENVS / 32)];
+
+// A record is current when bits 48..63 == (*rng_step + 1) & 0xffff.  Writing that stamp with bit 15 flipped makes every
+// record of the coming step invalid whatever an earlier call (of any pipeline, at any step count) left there - a plain
+// clear to zero would pass as current once every 65 536 steps.
+__global__ void noalloc_invalidate_records_kernel(unsigned long long* rec, const int words, const uint64_t* rng_step) {
+  const unsigned stamp = ((unsigned)*rng_step + 1u) & 0xffffu;
+  const unsigned long long v = (unsigned long long)(stamp ^ 0x8000u) << 48;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < words) rec[i] = v;
+}
+
 extern "C" {
 
 const char* dex_strerror(int code) {
@@ -283,6 +299,7 @@ const char* dex_strerror(int code) {
     case DEX_ERR_ALIGN: return "dexstep: dof_state must be 16-byte aligned";
     case DEX_ERR_PARAM: return "dexstep: invalid parameter block (index out of range, bad enum or control_dt)";
     case DEX_ERR_VERSION: return "dexstep: DexParams.abi_version does not match the library";
+    case DEX_ERR_CAPACITY: return "dexstep: n_envs exceeds DEX_NOALLOC_MAX_ENVS (262144), the capacity of the built-in scratch of dex_post_physics_noalloc";
     default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "dexstep: unknown error";
   }
 }
@@ -380,6 +397,50 @@ int dex_post_physics(const DexParams* params, const DexSimViews* sim, const DexS
   a.seed = seed;
   a.step = step_index;
   return launch_post(a, (cudaStream_t)stream);
+}
+
+// ---- dex_post_physics_noalloc: the fused-epilogue launch with its tile-record scratch in a static device array ----
+// (no counterpart in the reference; see include/dexstep.h).  In HOST code the array's name is only a stand-in for the
+// symbol: its device address comes from cudaGetSymbolAddress, once per device, with that device current.
+int dex_post_physics_noalloc(const DexParams* params, const DexSimViews* sim, const DexStateBuffers* state,
+                             const DexOutBuffers* out, const DexEpilogueBuffers* epilogue, int32_t n_envs, int32_t mode,
+                             uint32_t flags, const float* uniforms, uint64_t seed, uint64_t step_index, void* stream) {
+  if (params == nullptr || sim == nullptr || state == nullptr || out == nullptr || epilogue == nullptr) return DEX_ERR_NULL;
+  if (mode != DEX_MODE_FULL) return DEX_ERR_PARAM;
+  if (n_envs <= 0) return DEX_ERR_SIZE;
+  if (n_envs > DEX_NOALLOC_MAX_ENVS) return DEX_ERR_CAPACITY;
+  if (state->rng_step == nullptr) return DEX_ERR_NULL;  // the records are stamped with the device-resident step counter
+  int rc = check_params(params);  // everything that can be rejected is rejected before the first launch
+  if (rc) return rc;
+  rc = check_sim(params, sim);
+  if (rc) return rc;
+  rc = check_state(params, state);
+  if (rc) return rc;
+  rc = check_epilogue(epilogue);
+  if (rc) return rc;
+  constexpr int kMaxDevices = 64;
+  static unsigned long long* s_records[kMaxDevices] = {};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= kMaxDevices) return DEX_ERR_SIZE;
+  if (s_records[dev] == nullptr) {
+    void* ptr = nullptr;
+    e = cudaGetSymbolAddress(&ptr, g_noalloc_tile_records);
+    if (e != cudaSuccess) {
+      (void)cudaGetLastError();
+      return (int)e;
+    }
+    s_records[dev] = static_cast<unsigned long long*>(ptr);
+  }
+  unsigned long long* const rec = s_records[dev];
+  const int words = 4 * ((n_envs + 31) / 32);
+  noalloc_invalidate_records_kernel<<<(words + 255) / 256, 256, 0, (cudaStream_t)stream>>>(rec, words, state->rng_step);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return (int)e;
+  DexEpilogueBuffers ep = *epilogue;
+  ep.tile_records = reinterpret_cast<uint64_t*>(rec);
+  return dex_post_physics(params, sim, state, out, &ep, n_envs, mode, flags, uniforms, seed, step_index, stream);
 }
 
 int dex_reset_idx(const DexParams* params, const DexSimViews* sim, const DexStateBuffers* state,

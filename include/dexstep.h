@@ -76,6 +76,7 @@ extern "C" {
 #define DEX_ERR_ALIGN -3
 #define DEX_ERR_PARAM -4
 #define DEX_ERR_VERSION -5
+#define DEX_ERR_CAPACITY -6   /* dex_post_physics_noalloc: n_envs exceeds DEX_NOALLOC_MAX_ENVS */
 
 /* task / mode enums */
 #define DEX_TASK_BASE 0
@@ -356,6 +357,25 @@ int dex_pre_physics(const DexParams* params, const DexStateBuffers* state, const
 int dex_post_physics(const DexParams* params, const DexSimViews* sim, const DexStateBuffers* state,
                      const DexOutBuffers* out, const DexEpilogueBuffers* epilogue, int32_t n_envs, int32_t mode,
                      uint32_t flags, const float* uniforms, uint64_t seed, uint64_t step_index, void* stream);
+
+/* dex_post_physics with the fused step epilogue, for callers that cannot allocate device memory (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments, same results and the same kernels as dex_post_physics called with
+ * `epilogue != NULL`, with one difference: the tile-record scratch the fused epilogue polls (DexEpilogueBuffers.tile_records,
+ * otherwise allocated and zero-initialised by the caller) is a file-scope `static __device__` array inside the library,
+ * 4 * DEX_NOALLOC_MAX_ENVS / 32 words = 256 KB, resident on every GPU that loads the library until the process exits.
+ * `epilogue->tile_records` is ignored (may be NULL); `epilogue` itself and mode == DEX_MODE_FULL are required.
+ *   - n_envs > DEX_NOALLOC_MAX_ENVS returns DEX_ERR_CAPACITY before anything is launched.
+ *   - The call allocates nothing: no cudaMalloc / cudaFree / allocating library routine, on the first call or later (the
+ *     array's device address is looked up once per device with cudaGetSymbolAddress).
+ *   - ALL calls of a process on one GPU share the array and it keeps the last call's contents.  Each call therefore first
+ *     launches a small kernel on `stream` that overwrites the records it will use with a stamp that cannot be this step's
+ *     (so records of an earlier call - of this or of any other pipeline - never pass as current); two launches are issued.
+ *   - Calls that OVERLAP on the GPU (different streams, or graphs replayed concurrently) race on the array: serialise them. */
+#define DEX_NOALLOC_MAX_ENVS 262144
+int dex_post_physics_noalloc(const DexParams* params, const DexSimViews* sim, const DexStateBuffers* state,
+                             const DexOutBuffers* out, const DexEpilogueBuffers* epilogue, int32_t n_envs, int32_t mode,
+                             uint32_t flags, const float* uniforms, uint64_t seed, uint64_t step_index, void* stream);
 
 /* Masked reset of envs with reset_mask[env] != 0 (NULL = all envs). */
 int dex_reset_idx(const DexParams* params, const DexSimViews* sim, const DexStateBuffers* state,
