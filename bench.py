@@ -282,6 +282,11 @@ def epi_only(env, a):
     env.pipeline.epilogue()
 
 
+def floor_only(env, a):
+    p = env.pipeline  # an empty kernel launched like dex_pre_physics: the per-launch floor in this stream of graphs
+    p.lib.dex_debug_launch_floor(p.n, p._stream())
+
+
 # ------------------------------------------------------------------------------------------------
 # CPU baseline: the oracle (CPU restatement of the reference's torch components) on the host cores.
 # The ONLY place bench.py touches oracle/.
@@ -562,7 +567,8 @@ def main():
             traffic = json.load(f).get(f"{task}_{n_env}")
     except Exception:
         pass
-    post_kernel = "post_physics_v2_kernel" if v2_in_plan > 0 else "post_physics_kernel"
+    post_kernel = ("post_physics_kernel", "post_physics_v2_kernel", "post_physics_v2s_kernel")[lib.dex_debug_last_post_kernel()]
+    floor_us = kernel_avg_us(ring, floor_only, kl, group, device)
     roofline = {"bound": "hbm", "kernel": post_kernel, "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic,
                 "traffic_source": "profiles/traffic.json (static: dram__bytes_read + dram__bytes_write of one launch, ncu --set full)",
@@ -605,7 +611,7 @@ def main():
                        "early_sim_loads": os.environ.get("DEXSTEP_EARLY_SIM_LOADS", "1") != "0",
                        "parallelism": f"env-sharded x{world}, no step-path collective, 1 NCCL all-reduce of stats"},
             "roofline": roofline, "e2e": e2e, "gpu_launches": launches_per_step * args.steps, "clocks": clocks,
-            "kernels_us": {"pre_physics": pre_us, "post_physics": post_us, "epilogue": epi_us,
+            "kernels_us": {"pre_physics": pre_us, "post_physics": post_us, "epilogue": epi_us, "empty_kernel_launch_floor": floor_us,
                            "stats_allreduce": allreduce_us},
             "l2_hot": l2_hot,
             "episode_stats": {"steps": stats[C["DEX_NUM_COUNTERS"]], "resets": stats[C["DEX_CNT_RESET"]],

@@ -138,6 +138,8 @@ def load(path: str = None) -> ctypes.CDLL:
     lib.dex_point_in_hand_frame.argtypes = [vp, vp, vp, vp, i32, vp]
     lib.dex_quat_mul.argtypes = [vp, vp, vp, i32, vp]
     lib.dex_debug_v2_launches.argtypes = []
+    lib.dex_debug_launch_floor.argtypes = [i32, vp]
+    lib.dex_debug_last_post_kernel.argtypes = []
     for fn in FUNCTIONS:
         if fn != "dex_strerror":
             getattr(lib, fn).restype = ctypes.c_int

@@ -150,6 +150,17 @@ __global__ void __launch_bounds__(kPreThreads) pre_physics_kernel(const __grid_c
   }
 }
 
+// The cost of A launch in a stream of step kernels, for bench.py: same grid / block / programmatic-launch attribute as
+// dex_pre_physics, no work.  What dex_pre_physics costs beyond this is what its loads, arithmetic and stores cost.
+struct NullArgs {
+  int32_t n;
+};
+__global__ void __launch_bounds__(kPreThreads) launch_floor_kernel(const __grid_constant__ NullArgs A) {
+  pdl_wait();
+  pdl_launch_dependents();
+  (void)A;
+}
+
 // ------------------------------------------------------------------------------------------------
 // small stand-alone helpers
 // ------------------------------------------------------------------------------------------------
@@ -306,6 +317,14 @@ const char* dex_strerror(int code) {
 
 static int g_v2_launches = 0;
 int dex_debug_v2_launches(void) { return g_v2_launches; }
+int dex_debug_last_post_kernel(void) { return pp2::g_last_geometry; }
+int dex_debug_launch_floor(int32_t n_envs, void* stream) {
+  if (n_envs <= 0) return DEX_ERR_SIZE;
+  const cudaError_t e = launch_step_kernel(launch_floor_kernel, (n_envs + kPreTile - 1) / kPreTile, kPreThreads, 0,
+                                           (cudaStream_t)stream, NullArgs{n_envs});
+  if (e != cudaSuccess) (void)cudaGetLastError();
+  return e == cudaSuccess ? DEX_OK : (int)e;
+}
 int dex_abi_version(void) { return DEX_ABI_VERSION; }
 int dex_sizeof_params(void) { return (int)sizeof(DexParams); }
 
@@ -349,6 +368,7 @@ int dex_post_physics(const DexParams* params, const DexSimViews* sim, const DexS
     return DEX_ERR_NULL;
   if ((flags & DEX_FLAG_STALE_CONTACTS) && state->contact_forces == nullptr) return DEX_ERR_NULL;
   if (out->episode_sums != nullptr && (out->episode_lengths == nullptr || out->stat_totals == nullptr)) return DEX_ERR_NULL;
+  if (out->stat_slices < 0 || out->stat_slices > 4096) return DEX_ERR_SIZE;
   if (n_envs <= 0) return DEX_ERR_SIZE;
   const bool fused = epilogue != nullptr && mode == DEX_MODE_FULL;
   if (fused) {
@@ -396,6 +416,7 @@ int dex_post_physics(const DexParams* params, const DexSimViews* sim, const DexS
   a.uniforms = uniforms;
   a.seed = seed;
   a.step = step_index;
+  pp2::g_last_geometry = 0;
   return launch_post(a, (cudaStream_t)stream);
 }
 

@@ -1096,7 +1096,7 @@ __device__ __forceinline__ void post_total(const PostArgs& A, float* smem, const
     const int rows = P.num_component_rows;
     const int len = A.out.episode_lengths[env] + 1;
     const int stride = 2 + rows;
-    double* tot = A.out.stat_totals;
+    double* tot = A.out.stat_totals + (size_t)((env >> 5) % max(1, A.out.stat_slices)) * 4 * stride;  // block of this tile
     const int cls = t_success ? 1 : (t_failure ? 2 : 3);
     if (should_reset) {
       atomicAdd(tot + 0, 1.0);

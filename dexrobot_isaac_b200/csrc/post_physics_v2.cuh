@@ -752,12 +752,7 @@ __device__ __forceinline__ void emit_term(const Post2Args& A, const Cx<BG, STD>&
   float* g = A.out.reward_components + c.env;
   g[(size_t)row * c.N] = r;
   g[(size_t)(row + 1) * c.N] = rw;
-  c.wk[(Lay<BG, AL>::W_WGT + i) * 32] = rw;
-  if (A.out.episode_sums != nullptr) {  // fused RewardComponentObserver (rl/reward_observer.py:176-188): sums += component
-    float* es = A.out.episode_sums + c.env;
-    es[(size_t)row * c.N] += r;
-    es[(size_t)(row + 1) * c.N] += rw;
-  }
+  c.wk[(Lay<BG, AL>::W_WGT + i) * 32] = rw;  // (the observer's running sums of these rows: observer_term_rows)
 }
 
 // phase B: the per-env scalar part, split over the consumer warps (warp-uniform job index)
@@ -995,6 +990,18 @@ __device__ __forceinline__ void phase_total(const Post2Args& A, const Cx<BG, STD
   if (!c.act) return;
   const DexParams& P = A.p;
   const float* wk = c.wk;
+  // observer on: the running sums of the seven rows this warp produces and the episode length are requested first, so
+  // that their (L2) latency runs under the ordered sum below instead of behind it, one round trip after the other
+  const bool observer = A.out.episode_sums != nullptr;
+  float es7[7];
+  int ep_len = 0;
+  if (observer) {
+    const float* es = A.out.episode_sums + c.env;
+    es7[0] = __ldcg(es + (size_t)P.total_row * c.N);
+#pragma unroll
+    for (int k = 0; k < 6; ++k) es7[1 + k] = __ldcg(es + (size_t)(P.termination_row + k) * c.N);
+    ep_len = __ldcg(A.out.episode_lengths + c.env);
+  }
   // STD: exactly the task's own terms are materialised (BlindGrasping: the 16 task terms, BaseTask: the 10 common ones)
   constexpr int I0 = (STD && BG) ? DEX_NUM_COMMON_TERMS : 0, I1 = BG ? DEX_NUM_REWARD_TERMS : DEX_NUM_COMMON_TERMS;
   float total = 0.0f;
@@ -1017,14 +1024,13 @@ __device__ __forceinline__ void phase_total(const Post2Args& A, const Cx<BG, STD
   for (int k = 0; k < 6; ++k) g[(size_t)(P.termination_row + k) * c.N] = tv[1 + k];
   A.out.rew_buf[c.env] = rew;
   // ---- fused RewardComponentObserver (rl/reward_observer.py:160-293): the rows this warp produces (total + the six
-  //      termination rows), the episode length and the episode counters; the term rows of a finished env are flushed
-  //      by the warp that resets it (observer_flush_terms)
-  if (A.out.episode_sums != nullptr) {
+  //      termination rows), the episode length and the episode counters; the term rows are warps 1-7's (observer_term_rows)
+  if (observer) {
     const bool done = cls != 0u;
     const int stride = 2 + P.num_component_rows;
     const int kc = t_success ? 1 : (t_failure ? 2 : 3);
-    double* tot = A.out.stat_totals;
-    const int len = A.out.episode_lengths[c.env] + 1;
+    double* tot = A.out.stat_totals + (size_t)((c.e0 >> 5) % max(1, A.out.stat_slices)) * 4 * stride;  // block of this tile
+    const int len = ep_len + 1;
     A.out.episode_lengths[c.env] = done ? 0 : len;
     if (done) {
       atomicAdd(tot + 0, 1.0);
@@ -1036,7 +1042,7 @@ __device__ __forceinline__ void phase_total(const Post2Args& A, const Cx<BG, STD
 #pragma unroll
     for (int k = 0; k < 7; ++k) {
       const int row = k == 0 ? P.total_row : P.termination_row + (k - 1);
-      const float sum = es[(size_t)row * c.N] + tv[k];
+      const float sum = es7[k] + tv[k];
       if (done) {
         atomicAdd(tot + 2 + row, (double)sum);
         atomicAdd(tot + kc * stride + 2 + row, (double)sum);
@@ -1046,20 +1052,57 @@ __device__ __forceinline__ void phase_total(const Post2Args& A, const Cx<BG, STD
   }
 }
 
-// observer flush of the TERM rows (rows below total_row) of one finished env, by one warp: lane = row, so the 2 x terms
-// running sums are read, added to the class totals and zeroed with one strided access each
-__device__ __forceinline__ void observer_flush_terms(const Post2Args& A, const int env, const unsigned* s_rbits, const int e_local) {
+// The observer's running sums (episode_sums [rows][N], one read-modify-write per row, env and step) are touched in the
+// middle of the per-tile program, where a DRAM miss cannot hide behind anything: one warp pulls the tile's 128-byte row
+// segments into L2 while the tile's inputs are still on their way (prefetch.global.L2 changes no state: always safe).
+__device__ __forceinline__ void observer_prefetch(const Post2Args& A, const int e0, const int lane) {
+  if (A.out.episode_sums == nullptr) return;
+  const int rows = A.p.num_component_rows;
+  for (int r = lane; r < rows; r += 32)
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(A.out.episode_sums + (size_t)r * A.n + e0));
+  if (lane == 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(A.out.episode_lengths + e0));
+}
+
+// The observer's running sums of the TERM rows (rows below total_row: raw / weighted value of every materialised reward
+// term; rl/reward_observer.py:176-188 `sums += component`, :190-230 flush at episode end), lane = env, rows dealt over
+// warps w = 0 .. nw-1.  Runs behind barrier C: every term row of the tile is in reward_components by then (read back
+// with coherent loads - other warps of this CTA wrote them) and the tile's reset / class ballots are in s_rbits.  All
+// loads of a batch of four rows are in flight together: one L2 round trip per batch instead of one per row.
+template <bool BG, bool STD>
+__device__ __forceinline__ void observer_term_rows(const Post2Args& A, const Cx<BG, STD>& c, const unsigned* s_rbits, const int w,
+                                                   const int nw) {
+  if (!c.act) return;
   const DexParams& P = A.p;
-  const int lane = threadIdx.x & 31;
-  const int kc = ((s_rbits[1] >> e_local) & 1u) ? 1 : (((s_rbits[2] >> e_local) & 1u) ? 2 : 3);
+  const int nrow = P.total_row;
+  const bool done = (s_rbits[0] >> c.lane) & 1u;
+  const int kc = ((s_rbits[1] >> c.lane) & 1u) ? 1 : (((s_rbits[2] >> c.lane) & 1u) ? 2 : 3);
   const int stride = 2 + P.num_component_rows;
-  double* tot = A.out.stat_totals;
-  for (int row = lane; row < P.total_row; row += 32) {
-    float* p = A.out.episode_sums + (size_t)row * A.n + env;
-    const float sum = *p;
-    atomicAdd(tot + 2 + row, (double)sum);
-    atomicAdd(tot + kc * stride + 2 + row, (double)sum);
-    *p = 0.0f;
+  double* tot = A.out.stat_totals + (size_t)((c.e0 >> 5) % max(1, A.out.stat_slices)) * 4 * stride;  // block of this tile
+  const float* rc = A.out.reward_components + c.env;
+  float* es = A.out.episode_sums + c.env;
+#pragma unroll 1
+  for (int r0 = w; r0 < nrow; r0 += 4 * nw) {
+    float a[4], b[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int r = r0 + j * nw;
+      if (r < nrow) {
+        a[j] = __ldcg(rc + (size_t)r * c.N);
+        b[j] = __ldcg(es + (size_t)r * c.N);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int r = r0 + j * nw;
+      if (r < nrow) {
+        const float sum = b[j] + a[j];
+        if (done) {
+          atomicAdd(tot + 2 + r, (double)sum);
+          atomicAdd(tot + kc * stride + 2 + r, (double)sum);
+        }
+        es[(size_t)r * c.N] = done ? 0.0f : sum;
+      }
+    }
   }
 }
 
@@ -1477,6 +1520,10 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
     float* const g_obs = A.out.obs_buf + (size_t)c.e0 * W;
     const bool bulk_out = A.obs_bulk && c.ne == 32;  // CTA-uniform
     TL2(it, 0);
+    if (warp == kConsWarps - 1) {  // observer rows of this tile (first iteration) and of the next one
+      if (it == 0) observer_prefetch(A, c.e0, lane);
+      if (tile + workers < tiles) observer_prefetch(A, (tile + workers) * 32, lane);
+    }
     // ONE warp polls the stage's mbarrier, the other seven block in hardware behind it
     if (warp == 0) mbar_wait(bar_full + 8 * s, (unsigned)use & 1u);
     // Philox step counter == stamp of this step's tile records: read once per CTA, behind the first full barrier (i.e.
@@ -1514,6 +1561,7 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
     // the raw stage is not read after this point: hand it back to the producers
     if (lane == 0) mbar_arrive(bar_empty + 8 * s);
     if (warp == 0) phase_total<BG, STD, false>(A, c, cls);
+    else if (A.out.episode_sums != nullptr) observer_term_rows<BG, STD>(A, c, s_rbits, warp - 1, kConsWarps - 1);
     TL2(it, 8);
     if (bulk_out) {
       if (tid == 32) {
@@ -1528,14 +1576,13 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
     {
       unsigned mask = s_rbits[0];  // written by warp 0 before the barrier above
       // finished envs: one warp per env flushes the observer's term rows and applies the fused reset (dexhand_base.py:743-756)
-      const bool do_reset = !(A.flags & DEX_FLAG_NO_FUSED_RESET), do_flush = A.out.episode_sums != nullptr;
-      if (mask && (do_reset || do_flush)) {
+      const bool do_reset = !(A.flags & DEX_FLAG_NO_FUSED_RESET);
+      if (mask && do_reset) {
         for (int k = 0; mask; ++k) {
           const int e = __ffs(mask) - 1;
           mask &= mask - 1;
           if ((k & (kConsWarps - 1)) == warp) {
-            if (do_flush) observer_flush_terms(A, c.e0 + e, s_rbits, e);
-            if (do_reset) reset_env_warp<BG>(A, c.e0 + e, rng_step, s_reset_u + 32 * warp);
+            reset_env_warp<BG>(A, c.e0 + e, rng_step, s_reset_u + 32 * warp);
           }
         }
       }
@@ -1609,6 +1656,7 @@ __global__ void __launch_bounds__(kOneThreads, 4) post_physics_v2s_kernel(const 
   pdl_launch_dependents();
   unsigned char* const stage = smem2;
   float* const s_obs = reinterpret_cast<float*>(smem2 + LY::STAGE_BYTES + LY::NWKA * 128);
+  if (warp == kConsWarps - 1) observer_prefetch(A, tile * 32, lane);
   {
     LoadCtx<BG> lc;
     lc.setup(A, s_rbo, lane);
@@ -1650,6 +1698,7 @@ __global__ void __launch_bounds__(kOneThreads, 4) post_physics_v2s_kernel(const 
   __syncwarp();
   cons_sync();
   if (warp == 0) phase_total<BG, STD, true>(A, c, cls);
+  else if (A.out.episode_sums != nullptr) observer_term_rows<BG, STD>(A, c, s_rbits, warp - 1, kConsWarps - 1);
   if (bulk_out) {
     if (tid == 32) bulk_s2g(g_obs, s32(s_obs), (uint32_t)(32 * W * 4));
   } else {
@@ -1658,20 +1707,21 @@ __global__ void __launch_bounds__(kOneThreads, 4) post_physics_v2s_kernel(const 
   if (A.out.obs_norm != nullptr) copy_obs_norm_rows(s_obs, A.out, c.e0, W, A.wp, c.ne, warp, lane);
   {
     unsigned mask = s_rbits[0];
-    const bool do_reset = !(A.flags & DEX_FLAG_NO_FUSED_RESET), do_flush = A.out.episode_sums != nullptr;
-    if (mask && (do_reset || do_flush)) {
+    const bool do_reset = !(A.flags & DEX_FLAG_NO_FUSED_RESET);
+    if (mask && do_reset) {
       for (int k = 0; mask; ++k) {
         const int e = __ffs(mask) - 1;
         mask &= mask - 1;
         if ((k & (kConsWarps - 1)) == warp) {
-          if (do_flush) observer_flush_terms(A, c.e0 + e, s_rbits, e);
-          if (do_reset) reset_env_warp<BG>(A, c.e0 + e, rng_step, s_reset_u + 32 * warp);
+          reset_env_warp<BG>(A, c.e0 + e, rng_step, s_reset_u + 32 * warp);
         }
       }
     }
   }
   if (bulk_out && tid == 32) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // the obs tile has left shared memory
 }
+
+static int g_last_geometry = 0;  // 0 tile kernel, 1 persistent, 2 single pass (dex_debug_last_post_kernel)
 
 template <bool STD>
 int launch_post2_single(Post2Args& a, cudaStream_t s, int& ok) {
@@ -1747,9 +1797,11 @@ int launch_post2_t(Post2Args& a, cudaStream_t s) {
     if (allow_single) {
       int ok = 0;
       const int rc1 = std_layout ? launch_post2_single<true>(a, s, ok) : launch_post2_single<false>(a, s, ok);
+      if (ok) g_last_geometry = 2;
       if (ok || rc1) return rc1;
     }
   }
+  g_last_geometry = 1;
   return std_layout ? launch_post2_k<BG, true>(a, s) : launch_post2_k<BG, false>(a, s);
 }
 

@@ -34,6 +34,9 @@ _EARLY_SIM = os.environ.get("DEXSTEP_EARLY_SIM_LOADS", "1") != "0"  # A/B switch
 NUM_UNIFORMS = C["DEX_NUM_UNIFORMS"]
 
 
+STAT_SLICES = 32  # blocks of DexOutBuffers.stat_totals
+
+
 def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
     return None if t is None else t.data_ptr()
 
@@ -108,12 +111,15 @@ class StepPipeline:
             "counters": z(C["DEX_NUM_COUNTERS"], dtype=torch.int32),
             "episode_sums": z(rows, n) if observer else None,
             "episode_lengths": z(n, dtype=torch.int32) if observer else None,
-            "stat_totals": z(4, 2 + rows, dtype=torch.float64) if observer else None,
+            # [S][4][2 + rows]: S blocks spread the fp64 atomics of finished episodes (include/dexstep.h, stat_slices);
+            # read through stat_totals(), which sums them
+            "stat_totals": z(STAT_SLICES, 4, 2 + rows, dtype=torch.float64) if observer else None,
         }
         self._out = L.DexOutBuffers()
         for name, ctype in L.DexOutBuffers._fields_:
             if ctype is ctypes.c_void_p:
                 setattr(self._out, name, _ptr(o.get(name)))
+        self._out.stat_slices = STAT_SLICES
         e = self.epi = {"env_ids": z(n, dtype=torch.int32), "num_reset": z(1, dtype=torch.int32),
                         "stats": z(C["DEX_NUM_STATS"]), "consecutive_successes": z(1, dtype=torch.int32),
                         "totals": z(C["DEX_NUM_COUNTERS"] + 1, dtype=i64), "tile_records": z((n + 31) // 32, 4, dtype=i64)}
@@ -321,6 +327,11 @@ class StepPipeline:
         """== torch.nonzero(reset_buf).flatten() of the last step (host sync: reads the count)."""
         k = int(self.epi["num_reset"].item())
         return self.epi["env_ids"][:k].to(torch.int64)
+
+    def stat_totals(self) -> Optional[torch.Tensor]:
+        """The observer's episode totals [4][2 + rows] (classes all / success / failure / timeout): sum of the blocks."""
+        t = self.out["stat_totals"]
+        return None if t is None else t.sum(dim=0)
 
     def reward_components(self) -> Dict[str, torch.Tensor]:
         rc = self.out["reward_components"]

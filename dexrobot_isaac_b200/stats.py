@@ -43,7 +43,7 @@ def pack_pipelines(pipelines: Sequence) -> torch.Tensor:
     tot = torch.stack([p.epi["totals"] for p in pipelines]).sum(dim=0)
     st = None
     if pipelines[0].out["stat_totals"] is not None:
-        st = torch.stack([p.out["stat_totals"] for p in pipelines]).sum(dim=0)
+        st = torch.stack([p.stat_totals() for p in pipelines]).sum(dim=0)
     return pack(tot, st)
 
 

@@ -59,7 +59,7 @@
 extern "C" {
 #endif
 
-#define DEX_ABI_VERSION 9
+#define DEX_ABI_VERSION 10
 
 #define DEX_NUM_DOF 26          /* constants.py:8-10: 6 base + 20 finger DOFs */
 #define DEX_NUM_BASE 6
@@ -292,9 +292,15 @@ typedef struct DexOutBuffers {
    * Fused into the post-physics pass so the per-step component arrays need not be re-read. */
   float* episode_sums;            /* [num_component_rows][N] running per-episode sum of each component */
   int32_t* episode_lengths;       /* [N] observer-side episode length (reward_observer.py:166) */
-  double* stat_totals;            /* [4][2 + num_component_rows], classes {all, success, failure, timeout}:
+  double* stat_totals;            /* [S][4][2 + num_component_rows], classes {all, success, failure, timeout}:
                                      n_episodes, sum(episode_length), sum of each component's episode sum.
-                                     This vector is the payload of the single NCCL all-reduce. */
+                                     S = stat_slices blocks; the totals are the SUM OVER THE S BLOCKS (the host adds them
+                                     when it reads).  Summed, this vector is the payload of the single NCCL all-reduce
+                                     (SURVEY 8e). */
+  int32_t stat_slices;            /* S >= 1 (0 is read as 1).  Every finished episode adds 2 x (2 + rows) fp64 atomics; with
+                                     one block they all land on the same ~80 addresses and serialise in L2 (measured:
+                                     +4.3 us per launch at 16 384 envs with 1.5 % of the envs finishing per step).  The
+                                     32-env tile t adds to block t % S, which divides the contention by S */
   /* Optional policy-input stage: the input normalisation rl_games applies to obs_buf before the
    * network (cfg/train/BaseTaskPPO.yaml:44 normalize_input -> rl_games RunningMeanStd.forward with frozen statistics:
    * y = clamp((obs - running_mean.float()) / sqrt(running_var.float() + epsilon), -5, 5)), written from the same
@@ -343,6 +349,12 @@ int dex_sizeof_params(void);
 /* number of dex_post_physics calls of this process that launched the persistent warp-specialised kernel
  * (csrc/post_physics_v2.cuh) rather than the tile kernel: lets a test assert which kernel the lean path runs */
 int dex_debug_v2_launches(void);
+/* which kernel the last dex_post_physics call of this process launched: 0 = table-driven tile kernel (post_physics_kernel),
+ * 1 = persistent warp-specialised kernel (post_physics_v2_kernel), 2 = single-pass kernel (post_physics_v2s_kernel) */
+int dex_debug_last_post_kernel(void);
+/* measurement aid (bench.py): launches an EMPTY kernel with dex_pre_physics' grid, block and programmatic-launch
+ * attribute for n_envs - the per-launch floor of a kernel in a stream / graph of step kernels on this GPU */
+int dex_debug_launch_floor(int32_t n_envs, void* stream);
 
 /* Pre-physics: actions -> 26 DOF position targets.  `actions` [N,NACT] row-major.  Optional debug
  * outputs (may be NULL): active_raw_targets [18][N] (ActionProcessor.active_raw_targets). */

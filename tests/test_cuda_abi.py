@@ -247,7 +247,7 @@ def test_full_size_properties(task):
             tot[c, 2:] += ep_sum[:, m].sum(dim=1)
         ep_sum[:, done] = 0
         ep_len[done] = 0
-        got = p1.out["stat_totals"].cpu()
+        got = p1.stat_totals().cpu()
         assert torch.allclose(got, tot, rtol=1e-6, atol=1e-4), f"step {t} stat_totals"
         if t == 3:
             assert int(p1.out["timeout"].sum()) > 0

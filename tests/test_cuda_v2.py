@@ -241,7 +241,7 @@ def test_v2_fused_observer_matches_oracle_observer(task, n, steps):
         obs.process_infos({k: a["extras/" + k] for k in ("success", "failure", "timeout")}, torch.nonzero(a["reset_buf"]).flatten())
         if len(bad) > 10 or (t % 7 and t > 5):
             return
-        got_s, got_l, got_t = p.out["episode_sums"].cpu(), p.out["episode_lengths"].cpu(), p.out["stat_totals"].cpu()
+        got_s, got_l, got_t = p.out["episode_sums"].cpu(), p.out["episode_lengths"].cpu(), p.stat_totals().cpu()
         for r, k in enumerate(names):
             # running sums of up to episodeLength per-step values, each within 1e-5 relative / 1e-6 absolute
             if not torch.allclose(got_s[r], obs.episode_sums[k], rtol=1e-5, atol=2e-4):
