@@ -162,6 +162,24 @@ __global__ void __launch_bounds__(kPreThreads) launch_floor_kernel(const __grid_
 }
 
 // ------------------------------------------------------------------------------------------------
+// fixed-capacity actor-index lists for Isaac Gym's indexed setters: see include/dexstep.h
+// ------------------------------------------------------------------------------------------------
+__global__ void reset_actor_indices_kernel(const int32_t* env_ids, const int32_t* num_reset, const int capacity,
+                                           const int num_actors, const int dof_actor, int32_t* root_ids, int32_t* dof_ids,
+                                           int32_t* overflow) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= capacity) return;
+  const int k = *num_reset;
+  // padding: the first reset env again (its rows hold the state just written, so applying them twice changes
+  // nothing); without any reset, env 0 - whose rows hold its current simulation state
+  const int pad = k > 0 ? env_ids[0] : 0;
+  const int e = i < k ? env_ids[i] : pad;
+  dof_ids[i] = e * num_actors + dof_actor;
+  for (int a = 0; a < num_actors; ++a) root_ids[i * num_actors + a] = e * num_actors + a;
+  if (i == 0 && overflow != nullptr) *overflow += max(k - capacity, 0);
+}
+
+// ------------------------------------------------------------------------------------------------
 // small stand-alone helpers
 // ------------------------------------------------------------------------------------------------
 struct CoupleArgs {
@@ -491,6 +509,17 @@ int dex_step_epilogue(const DexParams* params, const DexEpilogueBuffers* ep, int
   if (n_envs <= 0) return DEX_ERR_SIZE;
   epilogue_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(*ep, n_envs, params->max_consecutive_successes);
   return launch_status();
+}
+
+int dex_reset_actor_indices(const DexEpilogueBuffers* ep, int32_t capacity, int32_t num_actors, int32_t dof_actor,
+                            int32_t* root_actor_ids, int32_t* dof_actor_ids, int32_t* overflow, void* stream) {
+  if (ep == nullptr || ep->env_ids == nullptr || ep->num_reset == nullptr || root_actor_ids == nullptr || dof_actor_ids == nullptr)
+    return DEX_ERR_NULL;
+  if (capacity <= 0 || num_actors <= 0 || dof_actor < 0 || dof_actor >= num_actors) return DEX_ERR_SIZE;
+  reset_actor_indices_kernel<<<(capacity + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
+      ep->env_ids, ep->num_reset, capacity, num_actors, dof_actor, root_actor_ids, dof_actor_ids, overflow);
+  const cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? DEX_OK : (int)e;
 }
 
 int dex_apply_coupling(const DexParams* params, const float* active, float* full, int32_t n_envs, void* stream) {

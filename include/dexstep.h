@@ -389,6 +389,20 @@ int dex_post_physics_noalloc(const DexParams* params, const DexSimViews* sim, co
                              const DexOutBuffers* out, const DexEpilogueBuffers* epilogue, int32_t n_envs, int32_t mode,
                              uint32_t flags, const float* uniforms, uint64_t seed, uint64_t step_index, void* stream);
 
+/* Fixed-capacity actor-index lists for Isaac Gym's indexed setters (replaces the host-sized index tensors of
+ * components/reset/reset_manager.py:139-168 and components/physics/physics_manager.py:121-160).  From the epilogue's
+ * env_ids / num_reset (device resident) it writes, without any host read:
+ *   dof_actor_ids  [capacity]               global id (env * num_actors + dof_actor) of the hand actor of the i-th reset env
+ *   root_actor_ids [capacity * num_actors]  global ids of ALL actors of the i-th reset env (reset_manager.py:139-156)
+ * Entries past num_reset are PADDED with the first reset env (its rows hold the state the reset just wrote: applying them
+ * twice changes nothing) or, when no env was reset, with env 0 (whose rows hold its current simulation state).  The
+ * caller then always issues set_actor_root_state_tensor_indexed(..., capacity * num_actors) and
+ * set_dof_state_tensor_indexed(..., capacity): constant launch arguments, so the whole control step - setters included -
+ * can live in one CUDA graph.  capacity >= n_envs can never overflow; with a smaller capacity *overflow (optional, device,
+ * int32, accumulates) counts the resets that did not fit and were therefore NOT applied in that step. */
+int dex_reset_actor_indices(const DexEpilogueBuffers* epilogue, int32_t capacity, int32_t num_actors, int32_t dof_actor,
+                            int32_t* root_actor_ids, int32_t* dof_actor_ids, int32_t* overflow, void* stream);
+
 /* Masked reset of envs with reset_mask[env] != 0 (NULL = all envs). */
 int dex_reset_idx(const DexParams* params, const DexSimViews* sim, const DexStateBuffers* state,
                   const uint8_t* reset_mask, int32_t n_envs, const float* uniforms, uint64_t seed,
