@@ -31,6 +31,10 @@
 //     polling CTA), RewardComponentObserver sums, rl_games input normalisation of obs_buf (obs_norm).
 // Numerics: lane = env for all arithmetic; ordered reductions stay single-lane per env (parity with torch's order).
 #pragma once
+#include <string.h>
+
+#include <cuda.h>  // CUtensorMap (types only: the encoder is fetched with cudaGetDriverEntryPoint, libcuda is not linked)
+
 #include "post_physics.cuh"
 
 namespace {
@@ -166,6 +170,22 @@ struct Post2Args {
   uint32_t smem_bytes;
   int32_t rb_off[11], cf_off[6];
   int32_t dof2afj[DEX_NUM_DOF];           // dof -> index in active_finger_dof, -1 = not an active finger DOF
+  // ---- TMA staging of the persistent kernel (build_tma): one copy per lane of producer warp 0 and tile ----
+  int32_t tma;                            // 1: tensor copies instead of LDGSTS gathers
+  uint32_t stage_bytes;                   // bytes of one ring stage
+  uint32_t tma_tx;                        // bytes that land per tile (expect_tx)
+  int32_t t_ncopy;                        // copies per tile (<= 32)
+  int32_t t_root_g, t_root_sh;            // actor_root_state is viewed as [N / g][g * NA * 13] (16-byte pitch); sh = log2(g)
+  uint16_t t_hand, t_pose[10], t_cf[6], t_box[2];  // consumer view: float offset of element 0 of lane 0 inside the raw block
+  uint8_t t_pose_w[10], t_cf_w[6];                 //                box width in floats (lane stride)
+  uint8_t t_kind[32];                     // 0: sim box {c0, e0}   1: root box {c0, e0 / g}   2: state box {e0, 0}   3: plain bulk copy
+  uint8_t t_early[32];                    // 1: reads a sim tensor only (may be issued ahead of griddepcontrol.wait)
+  uint8_t t_map[32];                      // index into tmap
+  uint32_t t_dst[32];                     // byte offset inside the stage
+  int32_t t_c0[32];                       // inner coordinate (kinds 0, 1)
+  uint32_t t_bytes[32];                   // kind 3: bytes per tile (== source stride per tile)
+  uint64_t t_ptr[32];                     // kind 3: global base
+  alignas(64) CUtensorMap tmap[14];
   uint64_t bk_ptr[kMaxBulk];              // global base of the row / tile array
   uint16_t bk_dst16[kMaxBulk];            // byte offset inside the stage / 16
   uint16_t bk_len16[kMaxBulk];            // bytes per full tile / 16 (== source stride per tile)
@@ -289,6 +309,174 @@ inline bool std_layout_matches(const Post2Args& a) {
   return true;
 }
 
+// ------------------------------------------------------------------------------------------------
+// host: TMA staging of the persistent kernel (BlindGrasping).  Every gathered Isaac Gym row becomes one 2-D tensor copy
+// (box = [w floats] x [32 envs] out of rigid_body_state / net_contact_force viewed as [N][NB * 13 | NB * 3]); the TMA
+// unit wants 16-byte aligned box origins and row pitches, so a row that starts at float offset r inside an env's record is
+// fetched from (r & ~3) with the smallest box width that still covers it (hand: 16; pose: 8 or 12; contact: 4 or 8) and
+// the consumers read from element (r & 3) on.  actor_root_state (pitch NA * 52 B) is viewed as [N / g][g * NA * 13] with
+// g = 1 or 2 so that the pitch is a multiple of 16.  The [K][N] state rows are one box [32 envs] x [K rows] per buffer and
+// land exactly in the stage's row layout; the dof tile and the single 128 / 256-byte rows are plain bulk copies.  One copy
+// per lane of producer warp 0; all of them complete on the stage's mbarrier (expect_tx).  Needs: N % 32 == 0, NB % 4 == 0,
+// NA % 2 == 0 (or % 4), 16-byte aligned bases; anything else keeps the LDGSTS producers.
+// ------------------------------------------------------------------------------------------------
+typedef CUresult (*TmapEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                 const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+inline TmapEncodeFn tmap_encoder() {
+  static TmapEncodeFn fn = []() -> TmapEncodeFn {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) {
+      (void)cudaGetLastError();
+      return nullptr;
+    }
+    return (TmapEncodeFn)p;
+  }();
+  return fn;
+}
+
+inline bool tmap_2d(CUtensorMap* m, const void* base, const uint64_t inner, const uint64_t outer, const uint64_t pitch_bytes,
+                    const uint32_t box0, const uint32_t box1) {
+  TmapEncodeFn enc = tmap_encoder();
+  if (enc == nullptr) return false;
+  const cuuint64_t dims[2] = {inner, outer}, strides[1] = {pitch_bytes};
+  const cuuint32_t box[2] = {box0, box1}, es[2] = {1, 1};
+  return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+             CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+// fills a.tma / a.t_* / a.tmap / a.stage_bytes / a.smem_bytes; leaves a.tma = 0 when the launch does not qualify
+inline void build_tma(Post2Args& a) {
+  using LY = Lay<true>;
+  a.tma = 0;
+  a.stage_bytes = LY::STAGE_BYTES;
+  static const bool env_on = []() {  // DEXSTEP_POST_TMA=1: as if every call carried DEX_FLAG_TMA_STAGING
+    const char* e = getenv("DEXSTEP_POST_TMA");
+    return e != nullptr && e[0] == '1';
+  }();
+  const bool allow = env_on || (a.flags & DEX_FLAG_TMA_STAGING) != 0;
+  const DexParams& P = a.p;
+  const DexStateBuffers& st = a.st;
+  const int N = a.n, NB = P.num_bodies, NC = P.num_contact_bodies, NA = P.num_actors;
+  if (!allow || N % 32 != 0 || NB % 4 != 0 || NC % 4 != 0 || NA % 2 != 0 || !a.bulk_ok) return;
+  const void* bases[] = {a.sim.rigid_body_state, a.sim.net_contact_force, a.sim.actor_root_state, a.sim.dof_state,
+                         st.prev_dof_pos, st.active_prev_targets, st.prev_actions, st.contact_duration_steps,
+                         st.prev_contact_binary, st.initial_box_positions, st.time_in_stage, st.stage_contact_duration,
+                         st.success_duration_steps, st.current_stage, st.episode_step_count};
+  for (const void* b : bases)
+    if (b == nullptr || ((uintptr_t)b & 15u)) return;
+  const int g = (NA % 4 == 0) ? 1 : 2;
+  // ---- the maps are cached: a pipeline calls with the same buffers every step ----
+  struct Key {
+    const void* p[9];
+    int n, nb, nc, na, nact;
+  };
+  static thread_local Key key = {};
+  static thread_local CUtensorMap maps[14];
+  static thread_local bool maps_ok = false;
+  const Key now = {{a.sim.rigid_body_state, a.sim.net_contact_force, a.sim.actor_root_state, st.prev_dof_pos, st.active_prev_targets,
+                    st.prev_actions, st.contact_duration_steps, st.prev_contact_binary, st.initial_box_positions},
+                   N, NB, NC, NA, P.num_actions};
+  enum { M_RB16, M_RB12, M_RB8, M_CF8, M_CF4, M_ROOT, M_PDP, M_APT, M_PACT, M_CDUR, M_PBIN, M_BOX0 };
+  if (!maps_ok || memcmp(&key, &now, sizeof(Key)) != 0) {
+    maps_ok = false;
+    const uint64_t rbp = (uint64_t)NB * 52, cfp = (uint64_t)NC * 12, rtp = (uint64_t)g * NA * 52, sp = (uint64_t)N * 4;
+    bool ok = tmap_2d(&maps[M_RB16], a.sim.rigid_body_state, (uint64_t)NB * 13, N, rbp, 16, 32) &&
+              tmap_2d(&maps[M_RB12], a.sim.rigid_body_state, (uint64_t)NB * 13, N, rbp, 12, 32) &&
+              tmap_2d(&maps[M_RB8], a.sim.rigid_body_state, (uint64_t)NB * 13, N, rbp, 8, 32) &&
+              tmap_2d(&maps[M_CF8], a.sim.net_contact_force, (uint64_t)NC * 3, N, cfp, 8, 32) &&
+              tmap_2d(&maps[M_CF4], a.sim.net_contact_force, (uint64_t)NC * 3, N, cfp, 4, 32) &&
+              tmap_2d(&maps[M_ROOT], a.sim.actor_root_state, (uint64_t)g * NA * 13, N / g, rtp, 16, 32 / g) &&
+              tmap_2d(&maps[M_PDP], st.prev_dof_pos, N, DEX_NUM_DOF, sp, 32, DEX_NUM_DOF) &&
+              tmap_2d(&maps[M_APT], st.active_prev_targets, N, DEX_NUM_ACTIVE, sp, 32, DEX_NUM_ACTIVE) &&
+              tmap_2d(&maps[M_PACT], st.prev_actions, N, P.num_actions, sp, 32, P.num_actions) &&
+              tmap_2d(&maps[M_CDUR], st.contact_duration_steps, N, DEX_NUM_FINGERS, sp, 32, DEX_NUM_FINGERS) &&
+              tmap_2d(&maps[M_PBIN], st.prev_contact_binary, N, DEX_NUM_FINGERS, sp, 32, DEX_NUM_FINGERS) &&
+              tmap_2d(&maps[M_BOX0], st.initial_box_positions, N, 3, sp, 32, 3);
+    if (!ok) return;
+    key = now;
+    maps_ok = true;
+  }
+  memcpy(a.tmap, maps, sizeof(maps));
+  // ---- copy table + consumer view ----
+  int k = 0;
+  uint32_t raw = 0, tx = 0;  // raw: byte offset inside the raw block (behind OFF_AOS)
+  auto box_copy = [&](int kind, int map, uint32_t dst, int c0, uint32_t bytes) {
+    a.t_kind[k] = (uint8_t)kind;
+    a.t_early[k] = kind < 2 ? 1 : 0;
+    a.t_map[k] = (uint8_t)map;
+    a.t_dst[k] = dst;
+    a.t_c0[k] = c0;
+    a.t_bytes[k] = bytes;
+    a.t_ptr[k] = 0;
+    tx += bytes;
+    ++k;
+  };
+  auto bulk_copy = [&](const void* base, uint32_t dst, uint32_t bytes) {
+    a.t_kind[k] = 3;
+    a.t_early[k] = base == (const void*)a.sim.dof_state ? 1 : 0;
+    a.t_map[k] = 0;
+    a.t_dst[k] = dst;
+    a.t_c0[k] = 0;
+    a.t_bytes[k] = bytes;
+    a.t_ptr[k] = (uint64_t)(uintptr_t)base;
+    tx += bytes;
+    ++k;
+  };
+  bulk_copy(a.sim.dof_state, LY::OFF_DOF, 32 * 52 * 4);
+  {  // hand row: 13 floats
+    const int r = a.rb_off[0];
+    a.t_hand = (uint16_t)(raw / 4 + (r & 3));
+    box_copy(0, M_RB16, LY::OFF_AOS + raw, r & ~3, 32 * 16 * 4);
+    raw += 32 * 16 * 4;
+  }
+  for (int f = 0; f < 10; ++f) {  // tip / pad poses: 7 floats
+    const int r = a.rb_off[1 + f], w = ((r & 3) + 7 <= 8) ? 8 : 12;
+    a.t_pose[f] = (uint16_t)(raw / 4 + (r & 3));
+    a.t_pose_w[f] = (uint8_t)w;
+    box_copy(0, w == 8 ? M_RB8 : M_RB12, LY::OFF_AOS + raw, r & ~3, 32u * w * 4);
+    raw += (32u * w * 4 + 127) / 128 * 128;
+  }
+  for (int f = 0; f < 6; ++f) {  // contact forces (5 monitored bodies + the box): 3 floats
+    const int r = a.cf_off[f], w = ((r & 3) + 3 <= 4) ? 4 : 8;
+    a.t_cf[f] = (uint16_t)(raw / 4 + (r & 3));
+    a.t_cf_w[f] = (uint8_t)w;
+    box_copy(0, w == 4 ? M_CF4 : M_CF8, LY::OFF_AOS + raw, r & ~3, 32u * w * 4);
+    raw += (32u * w * 4 + 127) / 128 * 128;
+  }
+  a.t_root_g = g;
+  a.t_root_sh = g == 1 ? 0 : 1;
+  for (int j = 0; j < g; ++j) {  // box root row of the envs e = g * row + j: position [0..2], velocity [7..9]
+    const int r = (j * NA + P.box_actor) * 13;
+    a.t_box[j] = (uint16_t)(raw / 4 + (r & 3));
+    box_copy(1, M_ROOT, LY::OFF_AOS + raw, r & ~3, (32u / g) * 16 * 4);
+    raw += (32u / g) * 16 * 4;
+  }
+  if (g == 1) a.t_box[1] = a.t_box[0];
+  box_copy(2, M_PDP, LY::R_PDP * 128, 0, 32 * 4 * DEX_NUM_DOF);
+  box_copy(2, M_APT, LY::R_APT * 128, 0, 32 * 4 * DEX_NUM_ACTIVE);
+  box_copy(2, M_PACT, LY::R_PACT * 128, 0, 32u * 4 * P.num_actions);
+  box_copy(2, M_CDUR, LY::R_CDUR * 128, 0, 32 * 4 * DEX_NUM_FINGERS);
+  box_copy(2, M_PBIN, LY::R_PBIN * 128, 0, 32 * 4 * DEX_NUM_FINGERS);
+  box_copy(2, M_BOX0, LY::R_BOX0 * 128, 0, 32 * 4 * 3);
+  bulk_copy(st.time_in_stage, LY::R_TIS * 128, 128);
+  bulk_copy(st.stage_contact_duration, LY::R_SCD * 128, 128);
+  bulk_copy(st.episode_step_count, LY::OFF_I64 + LY::I_STEP * 256, 256);
+  bulk_copy(st.success_duration_steps, LY::OFF_I64 + LY::I_SDS * 256, 256);
+  bulk_copy(st.current_stage, LY::OFF_I64 + LY::I_STAGE * 256, 256);
+  if (k > 32) return;
+  const uint32_t stage_bytes = (LY::OFF_AOS + raw + 127) / 128 * 128;
+  const uint32_t smem = (uint32_t)(kStages * stage_bytes + LY::W_COUNT * 128 + (32 * a.wp * 4 + 127) / 128 * 128);
+  if (smem > 113 * 1024) return;  // two CTAs per SM must still fit
+  a.t_ncopy = k;
+  a.tma_tx = tx;
+  a.stage_bytes = stage_bytes;
+  a.smem_bytes = smem;
+  a.tma = 1;
+}
+
 #ifdef DEXSTEP_TL2  // debug build only (tools/timeline_v2.py): SM-clock marks per (CTA, tile iteration), [cta][kTlIters][32] u64:
 // [0..15] consumer thread 0, [16..23] producer thread 0, [30] globaltimer ns at the mark 0 of the iteration, [31] smid
 constexpr int kTlIters = 8;
@@ -380,6 +568,9 @@ __device__ __forceinline__ void obs_put(float* obs, const int off, const int j, 
 // ------------------------------------------------------------------------------------------------
 // consumer phases (lane = env)
 // ------------------------------------------------------------------------------------------------
+template <int LM>
+constexpr int kBoxVel = LM == 2 ? 7 : 3;  // where the box's linear velocity sits behind Cx::box()
+
 template <bool BG, bool STD>
 struct Cx {
   const unsigned char* stage;
@@ -399,22 +590,45 @@ struct Cx {
   __device__ __forceinline__ const float* aos() const {
     return reinterpret_cast<const float*>(stage + Lay<BG>::OFF_AOS) + lane * Lay<BG>::SA;
   }
+  // ---- the gathered Isaac Gym rows of this lane's env.  LM (layout mode of the stage): 0 = [32][SA] records filled by
+  // LDGSTS / register-staged loads, 1 = the same inside the aliased single-pass stage, 2 = the dense boxes the TMA unit
+  // wrote (one [32 envs][w floats] box per gathered row, w = 4 .. 16; element offsets from build_tma) ----
+  __device__ __forceinline__ const float* rawf() const { return reinterpret_cast<const float*>(stage + Lay<BG>::OFF_AOS); }
+  template <int LM>
+  __device__ __forceinline__ const float* hand(const Post2Args& A) const {  // 13 floats: pos, quat, lin vel, ang vel
+    if constexpr (LM == 2) return rawf() + A.t_hand + lane * 16;
+    else return aos() + Lay<BG>::A_RB;
+  }
+  template <int LM>
+  __device__ __forceinline__ const float* pose(const Post2Args& A, const int f) const {  // 7 floats; f: 5 tips, 5 pads
+    if constexpr (LM == 2) return rawf() + A.t_pose[f] + lane * (int)A.t_pose_w[f];
+    else return aos() + Lay<BG>::A_RB + 13 + 7 * f;
+  }
+  template <int LM>
+  __device__ __forceinline__ const float* contact(const Post2Args& A, const int f) const {  // 3 floats; f = 5: the box
+    if constexpr (LM == 2) return rawf() + A.t_cf[f] + lane * (int)A.t_cf_w[f];
+    else return aos() + Lay<BG>::A_CF + 3 * f;
+  }
+  template <int LM>
+  __device__ __forceinline__ const float* box(const Post2Args& A) const {  // position at [0..2], velocity at [kBoxVel<LM> ..]
+    if constexpr (LM == 2) return rawf() + ((lane & (A.t_root_g - 1)) ? A.t_box[1] : A.t_box[0]) + (lane >> A.t_root_sh) * 16;
+    else return aos() + Lay<BG>::A_BOX;
+  }
   __device__ __forceinline__ int i64lo(const int r) const {
     return reinterpret_cast<const int*>(stage + Lay<BG>::OFF_I64 + r * 256)[2 * lane];
   }
 };
 
 // phase A: per-env work items, taken round-robin by the 8 consumer warps (item type is warp-uniform)
-template <bool BG, bool STD, bool AL>
+template <bool BG, bool STD, int LM>
 __device__ __forceinline__ void phase_items(const Post2Args& A, const Cx<BG, STD>& c) {
-  using LY = Lay<BG, AL>;
+  using LY = Lay<BG, LM == 1>;
   if (!c.act) return;
   const DexParams& P = A.p;
   const DexStateBuffers& st = A.st;
   const float dt = P.control_dt;
-  const float* aos = c.aos();
   const float* soa = c.soa();
-  const float* rb = aos + LY::A_RB;
+  const float* rb = c.template hand<LM>(A);  // the hand row (13 floats)
   float* wk = c.wk;
   float* obs = c.obs;
   const size_t N = c.N, env = c.env;
@@ -428,7 +642,7 @@ __device__ __forceinline__ void phase_items(const Post2Args& A, const Cx<BG, STD
       const int f = it;
       const bool is_pad = f >= DEX_NUM_FINGERS;
       const int g = is_pad ? f - DEX_NUM_FINGERS : f;
-      const float* p = rb + 13 + 7 * f;
+      const float* p = c.template pose<LM>(A, f);
       const float px = p[0], py = p[1], pz = p[2], qx = p[3], qy = p[4], qz = p[5], qw = p[6];
       const int ow = c.off(is_pad ? DEX_K_FINGERPAD_POSES_WORLD : DEX_K_FINGERTIP_POSES_WORLD);
       if (ow >= 0) {
@@ -456,7 +670,7 @@ __device__ __forceinline__ void phase_items(const Post2Args& A, const Cx<BG, STD
         o[6] = qh.w;
       }
       if (BG) {
-        const float* box = aos + LY::A_BOX;
+        const float* box = c.template box<LM>(A);
         const float d = norm3(px - box[0], py - box[1], pz - box[2]);
         if (is_pad) {
           const float hd = fabsf(pz - box[2]);
@@ -471,7 +685,7 @@ __device__ __forceinline__ void phase_items(const Post2Args& A, const Cx<BG, STD
     } else if (it < I_DOF) {
       // ---- contact sensor f (observation_encoder.py:658-735, 323-361; reward_calculator.py:183-199) ----
       const int f = it - I_CONTACT;
-      const float* cf = aos + LY::A_CF + 3 * f;
+      const float* cf = c.template contact<LM>(A, f);
       const float fx = cf[0], fy = cf[1], fz = cf[2];
       const float mag = norm3(fx, fy, fz);
       const bool bin = mag > P.contact_binary_threshold;
@@ -584,7 +798,7 @@ __device__ __forceinline__ void phase_items(const Post2Args& A, const Cx<BG, STD
         obs[oa + 6] = qa.w;
       }
       if (BG) {
-        const float* box = aos + LY::A_BOX;
+        const float* box = c.template box<LM>(A);
         const float hb = norm3(rb[0] - box[0], rb[1] - box[1], rb[2] - box[2]);
         wk[LY::W_HANDBOX * 32] = hb;
         obs_put(obs, c.off(DEX_K_HAND_TO_OBJECT_DISTANCE), 0, hb);
@@ -607,23 +821,25 @@ __device__ __forceinline__ void phase_items(const Post2Args& A, const Cx<BG, STD
       }
     } else if (BG && it == I_BOX) {
       // ---- pad centroid, box stability inputs (blind_grasping_task.py:746-771, 1334-1364) ----
-      const float* box = aos + LY::A_BOX;
+      const float* box = c.template box<LM>(A);
+      constexpr int BV = kBoxVel<LM>;
       float cen[3];
 #pragma unroll
-      for (int k = 0; k < 3; ++k) cen[k] = (rb[13 + 35 + k] + rb[13 + 35 + 7 + k] + rb[13 + 35 + 14 + k]) / 3.0f;
+      for (int k = 0; k < 3; ++k)
+        cen[k] = (c.template pose<LM>(A, 5)[k] + c.template pose<LM>(A, 6)[k] + c.template pose<LM>(A, 7)[k]) / 3.0f;
       const int oc = c.off(DEX_K_FIRST_THREE_FINGERPAD_CENTROID);
       const int opos = c.off(DEX_K_OBJECT_POS), ovel = c.off(DEX_K_OBJECT_VEL);
 #pragma unroll
       for (int k = 0; k < 3; ++k) {
         obs_put(obs, oc, k, cen[k]);
         obs_put(obs, opos, k, box[k]);
-        obs_put(obs, ovel, k, box[3 + k]);
+        obs_put(obs, ovel, k, box[BV + k]);
       }
       wk[LY::W_CDIST * 32] = norm3(cen[0] - box[0], cen[1] - box[1], cen[2] - box[2]);
       wk[LY::W_DRIFT * 32] = norm3(box[0] - soa[(LY::R_BOX0 + 0) * 32], box[1] - soa[(LY::R_BOX0 + 1) * 32],
                                    box[2] - soa[(LY::R_BOX0 + 2) * 32]);
-      wk[LY::W_VMAG * 32] = norm3(box[3], box[4], box[5]);
-      const float* cfb = aos + LY::A_CF + 15;
+      wk[LY::W_VMAG * 32] = norm3(box[BV], box[BV + 1], box[BV + 2]);
+      const float* cfb = c.template contact<LM>(A, 5);
       wk[LY::W_BOXHAS * 32] = (norm3(cfb[0], cfb[1], cfb[2]) > P.contact_binary_threshold) ? 1.0f : 0.0f;
     } else if (BG) {
       // ---- two pad pair distances, triu order (blind_grasping_task.py:726-771) ----
@@ -635,8 +851,8 @@ __device__ __forceinline__ void phase_items(const Post2Args& A, const Cx<BG, STD
           // k -> (a, b): rows of the strict upper triangle of a 5x5 matrix start at 0, 4, 7, 9
           const int a = (k >= 4) + (k >= 7) + (k >= 9);
           const int b = k - (a == 0 ? 0 : a == 1 ? 4 : a == 2 ? 7 : 9) + a + 1;
-          const float* pa = rb + 13 + 35 + 7 * a;
-          const float* pb = rb + 13 + 35 + 7 * b;
+          const float* pa = c.template pose<LM>(A, 5 + a);
+          const float* pb = c.template pose<LM>(A, 5 + b);
           obs[op + k] = norm3(pa[0] - pb[0], pa[1] - pb[1], pa[2] - pb[2]);
         }
       }
@@ -645,17 +861,16 @@ __device__ __forceinline__ void phase_items(const Post2Args& A, const Cx<BG, STD
 }
 
 // one common reward term (reward_calculator.py:66-221); BaseTask, phase B
-template <bool BG, bool STD, bool AL>
+template <bool BG, bool STD, int LM>
 __device__ __forceinline__ float common_term(const Post2Args& A, const Cx<BG, STD>& c, const int i) {
-  using LY = Lay<BG, AL>;
+  using LY = Lay<BG, LM == 1>;
   const float* wk = c.wk;
-  const float* rb = c.aos() + LY::A_RB;
   switch (i) {
     case DEX_R_ALIVE: return 1.0f;
     case DEX_R_HEIGHT_SAFETY: {
-      float mz = rb[13 + 2];
+      float mz = c.template pose<LM>(A, 0)[2];
 #pragma unroll
-      for (int f = 1; f < DEX_NUM_FINGERS; ++f) mz = fminf(mz, rb[13 + 7 * f + 2]);
+      for (int f = 1; f < DEX_NUM_FINGERS; ++f) mz = fminf(mz, c.template pose<LM>(A, f)[2]);
       return clampf(1.0f - expf(-(mz - 0.02f) * 20.0f), 0.0f, 1.0f);
     }
     case DEX_R_FINGER_VELOCITY: {
@@ -690,13 +905,11 @@ __device__ __forceinline__ float common_term(const Post2Args& A, const Cx<BG, ST
 }
 
 // one BlindGrasping task term (blind_grasping_task.py:980-1208); phase C (after the FSM)
-template <bool BG, bool STD, bool AL>
+template <bool BG, bool STD, int LM>
 __device__ __forceinline__ float task_term(const Post2Args& A, const Cx<BG, STD>& c, const int i) {
-  using LY = Lay<BG, AL>;
+  using LY = Lay<BG, LM == 1>;
   const DexParams& P = A.p;
   const float* wk = c.wk;
-  const float* aos = c.aos();
-  const float* rb = aos + LY::A_RB;
   const int stage = __float_as_int(wk[LY::W_STAGE * 32]);
   const float m1 = (stage == 1) ? 1.0f : 0.0f, m2 = (stage == 2) ? 1.0f : 0.0f, m3 = (stage == 3) ? 1.0f : 0.0f;
   switch (i) {
@@ -705,7 +918,7 @@ __device__ __forceinline__ float task_term(const Post2Args& A, const Cx<BG, STD>
     case DEX_R_S1_OBJECT_STABILITY:
       return expf(-P.object_stability_decay * (wk[LY::W_DRIFT * 32] + wk[LY::W_VMAG * 32])) * m1;
     case DEX_R_S1_FINGER_HEIGHT_CONSISTENCY: {  // torch.var(dim=1), unbiased, z of the first three pads
-      const float z0 = rb[13 + 35 + 2], z1 = rb[13 + 35 + 7 + 2], z2 = rb[13 + 35 + 14 + 2];
+      const float z0 = c.template pose<LM>(A, 5)[2], z1 = c.template pose<LM>(A, 6)[2], z2 = c.template pose<LM>(A, 7)[2];
       const float mean = (z0 + z1 + z2) / 3.0f;
       const float d0 = z0 - mean, d1 = z1 - mean, d2 = z2 - mean;
       const float var = (d0 * d0 + d1 * d1 + d2 * d2) / 2.0f;
@@ -730,7 +943,7 @@ __device__ __forceinline__ float task_term(const Post2Args& A, const Cx<BG, STD>
       return expf(-P.base_stability_decay * sqrtf(bv2)) * m2;
     }
     case DEX_R_S3_OBJECT_HEIGHT:
-      return clampf(div_rn(aos[LY::A_BOX + 2] - P.box_z, P.lift_height_range), 0.0f, 1.0f) * m3;
+      return clampf(div_rn(c.template box<LM>(A)[2] - P.box_z, P.lift_height_range), 0.0f, 1.0f) * m3;
     case DEX_R_S3_GRASP_MAINTENANCE: return wk[LY::W_GRASP * 32] * m3;
     case DEX_R_S3_GRASP_DURATION:
       return clampf(div_rn(wk[LY::W_GRASPDUR * 32], P.contact_duration_threshold_s), 0.0f, 1.0f) * m3;
@@ -743,7 +956,7 @@ __device__ __forceinline__ float task_term(const Post2Args& A, const Cx<BG, STD>
 }
 
 // raw + weighted rows of term i leave from registers; the weighted value is parked for the ordered total
-template <bool BG, bool STD, bool AL>
+template <bool BG, bool STD, int LM>
 __device__ __forceinline__ void emit_term(const Post2Args& A, const Cx<BG, STD>& c, const int i, const float r) {
   const float w = A.p.reward_weight[i];
   if (!STD && w == 0.0f) return;  // reward_calculator.py:247-251: zero-weight terms are not materialised (STD: none is)
@@ -752,22 +965,21 @@ __device__ __forceinline__ void emit_term(const Post2Args& A, const Cx<BG, STD>&
   float* g = A.out.reward_components + c.env;
   g[(size_t)row * c.N] = r;
   g[(size_t)(row + 1) * c.N] = rw;
-  c.wk[(Lay<BG, AL>::W_WGT + i) * 32] = rw;  // (the observer's running sums of these rows: observer_term_rows)
+  c.wk[(Lay<BG, LM == 1>::W_WGT + i) * 32] = rw;  // (the observer's running sums of these rows: observer_term_rows)
 }
 
 // phase B: the per-env scalar part, split over the consumer warps (warp-uniform job index)
-template <bool BG, bool STD, bool AL>
+template <bool BG, bool STD, int LM>
 __device__ __forceinline__ void phase_scalar(const Post2Args& A, const Cx<BG, STD>& c) {
-  using LY = Lay<BG, AL>;
+  using LY = Lay<BG, LM == 1>;
   if (!c.act) return;
   const DexParams& P = A.p;
   const DexStateBuffers& st = A.st;
   const float dt = P.control_dt;
   float* wk = c.wk;
   float* obs = c.obs;
-  const float* aos = c.aos();
   const float* soa = c.soa();
-  const float* rb = aos + LY::A_RB;
+  const float* rb = c.template hand<LM>(A);
   const size_t env = c.env;
   if (BG) {
     if (c.cw == 0) {
@@ -789,7 +1001,7 @@ __device__ __forceinline__ void phase_scalar(const Post2Args& A, const Cx<BG, ST
       obs_put(obs, c.off(DEX_K_THUMB_CONTACT), 0, ft);
       obs_put(obs, c.off(DEX_K_OTHER_FINGERS_CONTACT), 0, fo);
       obs_put(obs, c.off(DEX_K_GRASP_STATE), 0, fg);
-      const float box_z = aos[LY::A_BOX + 2];
+      const float box_z = c.template box<LM>(A)[2];
       const bool cond = (box_z > P.success_height_threshold) && (n_on_box >= P.min_fingers_for_grasp);
       const int sds = cond ? c.i64lo(LY::I_SDS) + 1 : 0;
       st.success_duration_steps[env] = (long long)sds;
@@ -833,10 +1045,10 @@ __device__ __forceinline__ void phase_scalar(const Post2Args& A, const Cx<BG, ST
       obs_put(obs, c.off(DEX_K_STAGE_PROGRESS), 0, prog);
     } else if (c.cw == 2) {
       // ---- minima, criteria inputs (step_processor.py:133-181, blind_grasping_task.py:1290-1364) ----
-      float min_tip_z = rb[13 + 2], min_tip_box = wk[LY::W_TIPBOX * 32];
+      float min_tip_z = c.template pose<LM>(A, 0)[2], min_tip_box = wk[LY::W_TIPBOX * 32];
 #pragma unroll
       for (int f = 1; f < DEX_NUM_FINGERS; ++f) {
-        min_tip_z = fminf(min_tip_z, rb[13 + 7 * f + 2]);
+        min_tip_z = fminf(min_tip_z, c.template pose<LM>(A, f)[2]);
         min_tip_box = fminf(min_tip_box, wk[(LY::W_TIPBOX + f) * 32]);
       }
       const bool hitg = P.has_height_safety && ((rb[2] < P.handbase_threshold) || (min_tip_z < P.fingertip_threshold));
@@ -864,16 +1076,16 @@ __device__ __forceinline__ void phase_scalar(const Post2Args& A, const Cx<BG, ST
     }
   } else {
     if (c.cw == 2) {
-      float min_tip_z = rb[13 + 2];
+      float min_tip_z = c.template pose<LM>(A, 0)[2];
 #pragma unroll
-      for (int f = 1; f < DEX_NUM_FINGERS; ++f) min_tip_z = fminf(min_tip_z, rb[13 + 7 * f + 2]);
+      for (int f = 1; f < DEX_NUM_FINGERS; ++f) min_tip_z = fminf(min_tip_z, c.template pose<LM>(A, f)[2]);
       const bool hitg = P.has_height_safety && ((rb[2] < P.handbase_threshold) || (min_tip_z < P.fingertip_threshold));
       wk[LY::W_HITG * 32] = hitg ? 1.0f : 0.0f;
       obs_put(obs, c.off(DEX_K_EPISODE_TIME), 0, (float)c.i64lo(LY::I_STEP) * dt);
     } else {
       // common reward terms over the seven other warps (0, 1, 3..7)
       for (int i = (c.cw < 2 ? c.cw : c.cw - 1); i < DEX_NUM_COMMON_TERMS; i += kConsWarps - 1) {
-        emit_term<BG, STD, AL>(A, c, i, common_term<BG, STD, AL>(A, c, i));
+        emit_term<BG, STD, LM>(A, c, i, common_term<BG, STD, LM>(A, c, i));
       }
     }
   }
@@ -881,9 +1093,9 @@ __device__ __forceinline__ void phase_scalar(const Post2Args& A, const Cx<BG, ST
 
 // phase C, warp 0: termination (step_processor.py:133-181, termination_manager.py:120-278), masks, tile record.
 // Returns the exclusive termination class of this lane's env: bit 0 success, 1 failure, 2 timeout.
-template <bool BG, bool STD, bool AL>
+template <bool BG, bool STD, int LM>
 __device__ __forceinline__ unsigned phase_combine(const Post2Args& A, const Cx<BG, STD>& c, const unsigned stamp, unsigned* s_rbits) {
-  using LY = Lay<BG, AL>;
+  using LY = Lay<BG, LM == 1>;
   const DexParams& P = A.p;
   const DexStateBuffers& st = A.st;
   const float* wk = c.wk;
@@ -984,9 +1196,9 @@ __device__ __forceinline__ unsigned phase_combine(const Post2Args& A, const Cx<B
 
 // phase D, warp 0: ordered weighted sum (reward_calculator.py:223-275) + termination rewards
 // (termination_manager.py:280-321, step_processor.py:204-219)
-template <bool BG, bool STD, bool AL>
+template <bool BG, bool STD, int LM>
 __device__ __forceinline__ void phase_total(const Post2Args& A, const Cx<BG, STD>& c, const unsigned cls) {
-  using LY = Lay<BG, AL>;
+  using LY = Lay<BG, LM == 1>;
   if (!c.act) return;
   const DexParams& P = A.p;
   const float* wk = c.wk;
@@ -1414,9 +1626,12 @@ __device__ __forceinline__ void copy_obs_norm_rows(const float* s_obs, const Dex
 // item code on different items at the same time (one fetched line serves all), loops are not unrolled, and a warp that
 // waits blocks in hardware (bar.sync behind one polling warp) instead of spinning through fetch slots.
 // ------------------------------------------------------------------------------------------------
-template <bool BG, bool STD>
+template <bool BG, bool STD, bool TMA = false>
 __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(const __grid_constant__ Post2Args A) {
   using LY = Lay<BG>;
+  static_assert(BG || !TMA, "TMA staging: BlindGrasping stage layout");
+  constexpr int LM = TMA ? 2 : 0;
+  const uint32_t stage_bytes = TMA ? A.stage_bytes : (uint32_t)LY::STAGE_BYTES;
   extern __shared__ __align__(128) unsigned char smem2[];
   __shared__ __align__(8) unsigned long long s_bar[2 * kStages];  // full[0..], empty[0..]
   __shared__ float s_reset_u[32 * kConsWarps];
@@ -1457,7 +1672,8 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
   if (tid == 0) {
 #pragma unroll
     for (int s = 0; s < kStages; ++s) {
-      mbar_init(bar_full + 8 * s, kProdThreads + kProdWarps);  // one cp.async-completion arrival per producer thread + one per warp
+      // LDGSTS producers: one cp.async-completion arrival per producer thread + one per warp; TMA: one arrival (expect_tx)
+      mbar_init(bar_full + 8 * s, TMA ? 1 : kProdThreads + kProdWarps);
       mbar_init(bar_empty + 8 * s, kConsWarps);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -1471,20 +1687,65 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
   __syncthreads();
   pdl_launch_dependents();
   TL2_DECL;
-  float* const wk_base = reinterpret_cast<float*>(smem2 + kStages * LY::STAGE_BYTES);
+  float* const wk_base = reinterpret_cast<float*>(smem2 + kStages * stage_bytes);
   float* const s_obs = wk_base + LY::W_COUNT * 32;
   const int tiles = A.tiles, workers = A.workers;
 
   if (warp >= kConsWarps) {
     // =========================== producer warps ===========================
     const int pw = warp - kConsWarps;
+    if constexpr (TMA) {
+      // ONE warp, one copy per lane and tile (build_tma): 2-D tensor boxes for the gathered Isaac Gym rows and the [K][N]
+      // state rows, plain bulk copies for the dof tile and the single rows.  The TMA unit serves a CTA's copies in issue
+      // order, so the first tile lands while the second is still being fetched - and no load instruction competes with
+      // the consumers for issue slots.
+      if (pw != 0) return;
+      const bool mine = lane < A.t_ncopy;
+      const int kind = mine ? A.t_kind[lane] : 3;
+      const bool early_copy = mine && A.t_early[lane] != 0 && (A.flags & DEX_FLAG_EARLY_SIM_LOADS) != 0;
+      const uint32_t dst_off = mine ? A.t_dst[lane] : 0u, bytes = mine ? A.t_bytes[lane] : 0u;
+      const int c0 = mine ? A.t_c0[lane] : 0;
+      const CUtensorMap* map = &A.tmap[mine ? A.t_map[lane] : 0];
+      const char* gptr = reinterpret_cast<const char*>(mine ? A.t_ptr[lane] : 0ull);
+      auto issue = [&](const uint32_t sst, const uint32_t fb, const int e0) {
+        if (kind == 3) {
+          bulk_g2s(sst + dst_off, gptr + (size_t)(e0 >> 5) * bytes, bytes, fb);
+        } else {
+          const int x = kind == 2 ? e0 : c0, y = kind == 0 ? e0 : (kind == 1 ? (e0 >> A.t_root_sh) : 0);
+          asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+                           sst + dst_off),
+                       "l"(map), "r"(x), "r"(y), "r"(fb)
+                       : "memory");
+        }
+      };
+      int it = 0;
+#pragma unroll 1
+      for (int tile = blockIdx.x; tile < tiles; tile += workers, ++it) {
+        const int s = it & 1, use = it >> 1;
+        const uint32_t sst = s32(smem2 + s * stage_bytes), fb = bar_full + 8 * s;
+        TL2(it, 16);
+        if (use > 0) mbar_wait(bar_empty + 8 * s, (unsigned)(use - 1) & 1u);
+        TL2(it, 17);
+        if (lane == 0) mbar_arrive_tx(fb, A.tma_tx);
+        __syncwarp();
+        if (it == 0) {  // the kernel ahead in the stream may still be writing the path state (and, without the flag, the sim tensors)
+          if (early_copy) issue(sst, fb, tile * 32);
+          pdl_wait();
+          if (mine && !early_copy) issue(sst, fb, tile * 32);
+        } else if (mine) {
+          issue(sst, fb, tile * 32);
+        }
+        TL2(it, 19);
+      }
+      return;
+    }
     LoadCtx<BG> lc;
     lc.setup(A, s_rbo, lane);
     int it = 0;
 #pragma unroll 1
     for (int tile = blockIdx.x; tile < tiles; tile += workers, ++it) {
       const int s = it & 1, use = it >> 1;
-      unsigned char* stage = smem2 + s * LY::STAGE_BYTES;
+      unsigned char* stage = smem2 + s * stage_bytes;
       const uint32_t fb = bar_full + 8 * s;
       TL2(it, 16);
       if (use > 0) mbar_wait(bar_empty + 8 * s, (unsigned)(use - 1) & 1u);
@@ -1516,7 +1777,7 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
     c.ne = min(32, A.n - c.e0);
     c.act = lane < c.ne;
     c.env = (size_t)c.e0 + (c.act ? lane : 0);
-    c.stage = smem2 + s * LY::STAGE_BYTES;
+    c.stage = smem2 + s * stage_bytes;
     float* const g_obs = A.out.obs_buf + (size_t)c.e0 * W;
     const bool bulk_out = A.obs_bulk && c.ne == 32;  // CTA-uniform
     TL2(it, 0);
@@ -1535,22 +1796,22 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
       rng_step = s_rng_step;
       stamp = ((unsigned)rng_step + 1u) & 0xffffu;
     }
-    phase_items<BG, STD, false>(A, c);
+    phase_items<BG, STD, LM>(A, c);
     TL2(it, 2);
     cons_sync();
     TL2(it, 3);
-    phase_scalar<BG, STD, false>(A, c);
+    phase_scalar<BG, STD, LM>(A, c);
     TL2(it, 4);
     cons_sync();
     TL2(it, 5);
     unsigned cls = 0;
     if (warp == 0) {
-      cls = phase_combine<BG, STD, false>(A, c, stamp, s_rbits);
+      cls = phase_combine<BG, STD, LM>(A, c, stamp, s_rbits);
     } else if (BG) {
       if (c.act) {
 #pragma unroll 1
         for (int i = DEX_NUM_COMMON_TERMS + (warp - 1); i < DEX_NUM_REWARD_TERMS; i += kConsWarps - 1)
-          emit_term<BG, STD, false>(A, c, i, task_term<BG, STD, false>(A, c, i));
+          emit_term<BG, STD, LM>(A, c, i, task_term<BG, STD, LM>(A, c, i));
       }
     }
     if (bulk_out) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // obs tile writes -> visible to the bulk store
@@ -1560,7 +1821,7 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
     TL2(it, 7);
     // the raw stage is not read after this point: hand it back to the producers
     if (lane == 0) mbar_arrive(bar_empty + 8 * s);
-    if (warp == 0) phase_total<BG, STD, false>(A, c, cls);
+    if (warp == 0) phase_total<BG, STD, LM>(A, c, cls);
     else if (A.out.episode_sums != nullptr) observer_term_rows<BG, STD>(A, c, s_rbits, warp - 1, kConsWarps - 1);
     TL2(it, 8);
     if (bulk_out) {
@@ -1751,13 +2012,13 @@ int launch_post2_single(Post2Args& a, cudaStream_t s, int& ok) {
   return e == cudaSuccess ? DEX_OK : (int)e;
 }
 
-template <bool BG, bool STD>
+template <bool BG, bool STD, bool TMA = false>
 int launch_post2_k(Post2Args& a, cudaStream_t s) {
   static int ctas_per_sm = -1, num_sms = 0;
   static size_t smem_cfg = 0, smem_occ = 0;
   if (a.smem_bytes > smem_cfg) {
     const size_t want = a.smem_bytes > 100 * 1024 ? a.smem_bytes : 100 * 1024;
-    const cudaError_t e = cudaFuncSetAttribute(post_physics_v2_kernel<BG, STD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)want);
+    const cudaError_t e = cudaFuncSetAttribute(post_physics_v2_kernel<BG, STD, TMA>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)want);
     if (e != cudaSuccess) return (int)e;
     smem_cfg = want;
     ctas_per_sm = -1;
@@ -1766,7 +2027,7 @@ int launch_post2_k(Post2Args& a, cudaStream_t s) {
     int dev = 0, occ = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
-    const cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, post_physics_v2_kernel<BG, STD>, kThreads, a.smem_bytes);
+    const cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, post_physics_v2_kernel<BG, STD, TMA>, kThreads, a.smem_bytes);
     if (e != cudaSuccess) return (int)e;
     if (occ < 1) return DEX_ERR_SIZE;
     ctas_per_sm = occ;
@@ -1776,7 +2037,7 @@ int launch_post2_k(Post2Args& a, cudaStream_t s) {
   int cap = num_sms * ctas_per_sm - fused;  // every CTA of the launch (workers + epilogue) is resident at once
   if (cap < 1) cap = 1;
   a.workers = a.tiles < cap ? a.tiles : cap;
-  const cudaError_t e = launch_step_kernel(post_physics_v2_kernel<BG, STD>, a.workers + fused, kThreads, a.smem_bytes, s, a);
+  const cudaError_t e = launch_step_kernel(post_physics_v2_kernel<BG, STD, TMA>, a.workers + fused, kThreads, a.smem_bytes, s, a);
   if (e != cudaSuccess) (void)cudaGetLastError();
   return e == cudaSuccess ? DEX_OK : (int)e;
 }
@@ -1794,7 +2055,7 @@ int launch_post2_t(Post2Args& a, cudaStream_t s) {
       const char* e = getenv("DEXSTEP_POST_GEOMETRY");
       return !(e != nullptr && e[0] == 'p');
     }();
-    if (allow_single) {
+    if (allow_single && !(a.flags & DEX_FLAG_TMA_STAGING)) {
       int ok = 0;
       const int rc1 = std_layout ? launch_post2_single<true>(a, s, ok) : launch_post2_single<false>(a, s, ok);
       if (ok) g_last_geometry = 2;
@@ -1802,6 +2063,15 @@ int launch_post2_t(Post2Args& a, cudaStream_t s) {
     }
   }
   g_last_geometry = 1;
+  if constexpr (BG) {
+    build_tma(a);
+    if (a.tma) {
+      g_last_geometry = 3;
+      return std_layout ? launch_post2_k<true, true, true>(a, s) : launch_post2_k<true, false, true>(a, s);
+    }
+  } else {
+    a.tma = 0;
+  }
   return std_layout ? launch_post2_k<BG, true>(a, s) : launch_post2_k<BG, false>(a, s);
 }
 

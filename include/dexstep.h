@@ -100,6 +100,12 @@ extern "C" {
 #define DEX_FLAG_TILE_KERNEL 16u       /* run the table-driven one-tile-per-CTA kernel (post_physics.cuh) even where the persistent
                                           warp-specialised kernel (post_physics_v2.cuh) covers the launch: A/B runs and the
                                           bit-for-bit cross-check of the two implementations (tests/test_cuda_v2.py) */
+#define DEX_FLAG_TMA_STAGING 32u      /* persistent kernel with TMA producers: every gathered Isaac Gym row / state buffer is one
+                                         2-D tensor copy (cp.async.bulk.tensor, SASS UTMALDG) instead of 4-byte asynchronous
+                                         copies.  Bit-identical results; MEASURED SLOWER on B200 (20.98 vs 18.87 us per launch at
+                                         16 384 envs: the TMA unit serves these 28..64-byte box rows at ~1 row per 6.5 clk per
+                                         SM, profiles/r02_variants.md), kept selectable so the measurement can be repeated.
+                                         BlindGrasping, N % 32 == 0, num_bodies % 4 == 0, num_actors % 2 == 0; ignored otherwise */
 
 /* observation keys (obs_dict entries of the reference, observation_encoder.py:613-756,
  * step_processor.py:73, blind_grasping_task.py:569-652,702-746,895-899) */
@@ -350,7 +356,8 @@ int dex_sizeof_params(void);
  * (csrc/post_physics_v2.cuh) rather than the tile kernel: lets a test assert which kernel the lean path runs */
 int dex_debug_v2_launches(void);
 /* which kernel the last dex_post_physics call of this process launched: 0 = table-driven tile kernel (post_physics_kernel),
- * 1 = persistent warp-specialised kernel (post_physics_v2_kernel), 2 = single-pass kernel (post_physics_v2s_kernel) */
+ * 1 = persistent warp-specialised kernel (post_physics_v2_kernel, LDGSTS producers), 2 = single-pass kernel
+ * (post_physics_v2s_kernel), 3 = persistent kernel with TMA producers (tensor copies) */
 int dex_debug_last_post_kernel(void);
 /* measurement aid (bench.py): launches an EMPTY kernel with dex_pre_physics' grid, block and programmatic-launch
  * attribute for n_envs - the per-launch floor of a kernel in a stream / graph of step kernels on this GPU */

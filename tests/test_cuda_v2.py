@@ -102,16 +102,21 @@ def test_v2_lockstep_headline_size(task):
 BUFS_OUT = ("obs_buf", "rew_buf", "reset_buf", "reward_components", "success", "failure", "timeout", "reset_bits")
 
 
-@pytest.mark.parametrize("task,n", [("BlindGrasping", 16384), ("BaseTask", 16384), ("BlindGrasping", 4096),
-                                    ("BaseTask", 5000), ("BlindGrasping", 100003), ("BlindGrasping", 33)])
-def test_v2_equals_tile_kernel_bitwise(task, n):
+@pytest.mark.parametrize("task,n,tma", [("BlindGrasping", 16384, False), ("BaseTask", 16384, False), ("BlindGrasping", 4096, False),
+                                        ("BaseTask", 5000, False), ("BlindGrasping", 100003, False), ("BlindGrasping", 33, False),
+                                        ("BlindGrasping", 16384, True), ("BlindGrasping", 4096, True), ("BlindGrasping", 131072, True)])
+def test_v2_equals_tile_kernel_bitwise(task, n, tma):
     """Same seeded random-state trajectory through the persistent kernel and through the tile kernel: every output,
     every state buffer, the sim tensors the fused reset rewrites, env_ids and the epilogue statistics are identical
-    bit for bit (in-kernel Philox resets included: both kernels key the stream by (seed, step, env))."""
+    bit for bit (in-kernel Philox resets included: both kernels key the stream by (seed, step, env)).
+    ``tma``: the persistent kernel with tensor-copy producers (DEX_FLAG_TMA_STAGING)."""
+    from dexrobot_isaac_b200 import _lib as L
+
     lay = synth.BodyLayout(with_box=task == "BlindGrasping")
     gen = torch.Generator().manual_seed(31)
     e1, e2 = lean_env(task, n), lean_env(task, n)
     e1.pipeline.tile_kernel = True
+    e2.pipeline.tma_staging = tma
     u = synth.random_uniforms(n, gen)
     steps = 7
     for t in range(steps):
@@ -128,6 +133,9 @@ def test_v2_equals_tile_kernel_bitwise(task, n):
                     e.episode_step_count.copy_(cnt.to(DEV))
                 e.pipeline.pre_physics(a.to(DEV).contiguous())
                 e.pipeline.post_step()
+        if t > 0:
+            kernel = L.load().dex_debug_last_post_kernel()  # of e2's launch
+            assert kernel == 3 if tma else kernel in (1, 2), kernel
         torch.cuda.synchronize()
         p1, p2 = e1.pipeline, e2.pipeline
         for k in BUFS_OUT:
