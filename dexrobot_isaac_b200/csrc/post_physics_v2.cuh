@@ -1196,7 +1196,7 @@ __device__ __forceinline__ unsigned phase_combine(const Post2Args& A, const Cx<B
 
 // phase D, warp 0: ordered weighted sum (reward_calculator.py:223-275) + termination rewards
 // (termination_manager.py:280-321, step_processor.py:204-219)
-template <bool BG, bool STD, int LM>
+template <bool BG, bool STD, int LM, bool OBS>
 __device__ __forceinline__ void phase_total(const Post2Args& A, const Cx<BG, STD>& c, const unsigned cls) {
   using LY = Lay<BG, LM == 1>;
   if (!c.act) return;
@@ -1204,10 +1204,10 @@ __device__ __forceinline__ void phase_total(const Post2Args& A, const Cx<BG, STD
   const float* wk = c.wk;
   // observer on: the running sums of the seven rows this warp produces and the episode length are requested first, so
   // that their (L2) latency runs under the ordered sum below instead of behind it, one round trip after the other
-  const bool observer = A.out.episode_sums != nullptr;
+  constexpr bool observer = OBS;  // a separate kernel instance: even dormant observer code costs the lean path 1-4 %
   float es7[7];
   int ep_len = 0;
-  if (observer) {
+  if constexpr (observer) {
     const float* es = A.out.episode_sums + c.env;
     es7[0] = __ldcg(es + (size_t)P.total_row * c.N);
 #pragma unroll
@@ -1237,7 +1237,7 @@ __device__ __forceinline__ void phase_total(const Post2Args& A, const Cx<BG, STD
   A.out.rew_buf[c.env] = rew;
   // ---- fused RewardComponentObserver (rl/reward_observer.py:160-293): the rows this warp produces (total + the six
   //      termination rows), the episode length and the episode counters; the term rows are warps 1-7's (observer_term_rows)
-  if (observer) {
+  if constexpr (observer) {
     const bool done = cls != 0u;
     const int stride = 2 + P.num_component_rows;
     const int kc = t_success ? 1 : (t_failure ? 2 : 3);
@@ -1626,7 +1626,7 @@ __device__ __forceinline__ void copy_obs_norm_rows(const float* s_obs, const Dex
 // item code on different items at the same time (one fetched line serves all), loops are not unrolled, and a warp that
 // waits blocks in hardware (bar.sync behind one polling warp) instead of spinning through fetch slots.
 // ------------------------------------------------------------------------------------------------
-template <bool BG, bool STD, bool TMA = false>
+template <bool BG, bool STD, bool TMA = false, bool OBS = false>
 __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(const __grid_constant__ Post2Args A) {
   using LY = Lay<BG>;
   static_assert(BG || !TMA, "TMA staging: BlindGrasping stage layout");
@@ -1781,9 +1781,11 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
     float* const g_obs = A.out.obs_buf + (size_t)c.e0 * W;
     const bool bulk_out = A.obs_bulk && c.ne == 32;  // CTA-uniform
     TL2(it, 0);
-    if (warp == kConsWarps - 1) {  // observer rows of this tile (first iteration) and of the next one
-      if (it == 0) observer_prefetch(A, c.e0, lane);
-      if (tile + workers < tiles) observer_prefetch(A, (tile + workers) * 32, lane);
+    if constexpr (OBS) {
+      if (warp == kConsWarps - 1) {  // observer rows of this tile (first iteration) and of the next one
+        if (it == 0) observer_prefetch(A, c.e0, lane);
+        if (tile + workers < tiles) observer_prefetch(A, (tile + workers) * 32, lane);
+      }
     }
     // ONE warp polls the stage's mbarrier, the other seven block in hardware behind it
     if (warp == 0) mbar_wait(bar_full + 8 * s, (unsigned)use & 1u);
@@ -1821,8 +1823,8 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
     TL2(it, 7);
     // the raw stage is not read after this point: hand it back to the producers
     if (lane == 0) mbar_arrive(bar_empty + 8 * s);
-    if (warp == 0) phase_total<BG, STD, LM>(A, c, cls);
-    else if (A.out.episode_sums != nullptr) observer_term_rows<BG, STD>(A, c, s_rbits, warp - 1, kConsWarps - 1);
+    if (warp == 0) phase_total<BG, STD, LM, OBS>(A, c, cls);
+    else if constexpr (OBS) observer_term_rows<BG, STD>(A, c, s_rbits, warp - 1, kConsWarps - 1);
     TL2(it, 8);
     if (bulk_out) {
       if (tid == 32) {
@@ -1865,7 +1867,7 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
 // ------------------------------------------------------------------------------------------------
 constexpr int kOneThreads = kConsThreads;
 
-template <bool BG, bool STD>
+template <bool BG, bool STD, bool OBS = false>
 __global__ void __launch_bounds__(kOneThreads, 4) post_physics_v2s_kernel(const __grid_constant__ Post2Args A) {
   using LY = Lay<BG, true>;
   static_assert(BG, "the aliased work block covers the BlindGrasping fields only");
@@ -1917,7 +1919,9 @@ __global__ void __launch_bounds__(kOneThreads, 4) post_physics_v2s_kernel(const 
   pdl_launch_dependents();
   unsigned char* const stage = smem2;
   float* const s_obs = reinterpret_cast<float*>(smem2 + LY::STAGE_BYTES + LY::NWKA * 128);
-  if (warp == kConsWarps - 1) observer_prefetch(A, tile * 32, lane);
+  if constexpr (OBS) {
+    if (warp == kConsWarps - 1) observer_prefetch(A, tile * 32, lane);
+  }
   {
     LoadCtx<BG> lc;
     lc.setup(A, s_rbo, lane);
@@ -1958,8 +1962,8 @@ __global__ void __launch_bounds__(kOneThreads, 4) post_physics_v2s_kernel(const 
   if (bulk_out) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   __syncwarp();
   cons_sync();
-  if (warp == 0) phase_total<BG, STD, true>(A, c, cls);
-  else if (A.out.episode_sums != nullptr) observer_term_rows<BG, STD>(A, c, s_rbits, warp - 1, kConsWarps - 1);
+  if (warp == 0) phase_total<BG, STD, true, OBS>(A, c, cls);
+  else if constexpr (OBS) observer_term_rows<BG, STD>(A, c, s_rbits, warp - 1, kConsWarps - 1);
   if (bulk_out) {
     if (tid == 32) bulk_s2g(g_obs, s32(s_obs), (uint32_t)(32 * W * 4));
   } else {
@@ -1984,19 +1988,19 @@ __global__ void __launch_bounds__(kOneThreads, 4) post_physics_v2s_kernel(const 
 
 static int g_last_geometry = 0;  // 0 tile kernel, 1 persistent, 2 single pass (dex_debug_last_post_kernel)
 
-template <bool STD>
+template <bool STD, bool OBS>
 int launch_post2_single(Post2Args& a, cudaStream_t s, int& ok) {
   using LY = Lay<true, true>;
   static int ctas_per_sm = -1, num_sms = 0;
   const uint32_t smem = (uint32_t)(LY::STAGE_BYTES + LY::NWKA * 128 + (32 * a.wp * 4 + 127) / 128 * 128);
   static uint32_t smem_cfg = 0;
   if (smem != smem_cfg) {
-    cudaError_t e = cudaFuncSetAttribute(post_physics_v2s_kernel<true, STD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(post_physics_v2s_kernel<true, STD, OBS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
     int dev = 0, occ = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, post_physics_v2s_kernel<true, STD>, kOneThreads, smem);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, post_physics_v2s_kernel<true, STD, OBS>, kOneThreads, smem);
     if (e != cudaSuccess) return (int)e;
     ctas_per_sm = occ;
     smem_cfg = smem;
@@ -2007,18 +2011,18 @@ int launch_post2_single(Post2Args& a, cudaStream_t s, int& ok) {
   if (!ok) return DEX_OK;
   a.smem_bytes = smem;
   a.workers = a.tiles;
-  const cudaError_t e = launch_step_kernel(post_physics_v2s_kernel<true, STD>, a.tiles + fused, kOneThreads, smem, s, a);
+  const cudaError_t e = launch_step_kernel(post_physics_v2s_kernel<true, STD, OBS>, a.tiles + fused, kOneThreads, smem, s, a);
   if (e != cudaSuccess) (void)cudaGetLastError();
   return e == cudaSuccess ? DEX_OK : (int)e;
 }
 
-template <bool BG, bool STD, bool TMA = false>
+template <bool BG, bool STD, bool TMA, bool OBS>
 int launch_post2_k(Post2Args& a, cudaStream_t s) {
   static int ctas_per_sm = -1, num_sms = 0;
   static size_t smem_cfg = 0, smem_occ = 0;
   if (a.smem_bytes > smem_cfg) {
     const size_t want = a.smem_bytes > 100 * 1024 ? a.smem_bytes : 100 * 1024;
-    const cudaError_t e = cudaFuncSetAttribute(post_physics_v2_kernel<BG, STD, TMA>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)want);
+    const cudaError_t e = cudaFuncSetAttribute(post_physics_v2_kernel<BG, STD, TMA, OBS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)want);
     if (e != cudaSuccess) return (int)e;
     smem_cfg = want;
     ctas_per_sm = -1;
@@ -2027,7 +2031,7 @@ int launch_post2_k(Post2Args& a, cudaStream_t s) {
     int dev = 0, occ = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
-    const cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, post_physics_v2_kernel<BG, STD, TMA>, kThreads, a.smem_bytes);
+    const cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, post_physics_v2_kernel<BG, STD, TMA, OBS>, kThreads, a.smem_bytes);
     if (e != cudaSuccess) return (int)e;
     if (occ < 1) return DEX_ERR_SIZE;
     ctas_per_sm = occ;
@@ -2037,7 +2041,7 @@ int launch_post2_k(Post2Args& a, cudaStream_t s) {
   int cap = num_sms * ctas_per_sm - fused;  // every CTA of the launch (workers + epilogue) is resident at once
   if (cap < 1) cap = 1;
   a.workers = a.tiles < cap ? a.tiles : cap;
-  const cudaError_t e = launch_step_kernel(post_physics_v2_kernel<BG, STD, TMA>, a.workers + fused, kThreads, a.smem_bytes, s, a);
+  const cudaError_t e = launch_step_kernel(post_physics_v2_kernel<BG, STD, TMA, OBS>, a.workers + fused, kThreads, a.smem_bytes, s, a);
   if (e != cudaSuccess) (void)cudaGetLastError();
   return e == cudaSuccess ? DEX_OK : (int)e;
 }
@@ -2048,6 +2052,7 @@ int launch_post2_t(Post2Args& a, cudaStream_t s) {
   if (rc) return rc;
   if (a.smem_bytes > 227 * 1024 - 2048) return DEX_ERR_SIZE;
   const bool std_layout = std_layout_matches<BG>(a);
+  const bool obs = a.out.episode_sums != nullptr;  // the fused observer is compiled into separate kernel instances
   if constexpr (BG) {
     // geometry by grid size: between 2 x SMs and 4 x SMs tiles the single-pass kernel runs one round where the persistent
     // one would run two (DEXSTEP_POST_GEOMETRY=persistent keeps the persistent kernel for A/B runs)
@@ -2057,7 +2062,8 @@ int launch_post2_t(Post2Args& a, cudaStream_t s) {
     }();
     if (allow_single && !(a.flags & DEX_FLAG_TMA_STAGING)) {
       int ok = 0;
-      const int rc1 = std_layout ? launch_post2_single<true>(a, s, ok) : launch_post2_single<false>(a, s, ok);
+      const int rc1 = obs ? (std_layout ? launch_post2_single<true, true>(a, s, ok) : launch_post2_single<false, true>(a, s, ok))
+                          : (std_layout ? launch_post2_single<true, false>(a, s, ok) : launch_post2_single<false, false>(a, s, ok));
       if (ok) g_last_geometry = 2;
       if (ok || rc1) return rc1;
     }
@@ -2067,12 +2073,14 @@ int launch_post2_t(Post2Args& a, cudaStream_t s) {
     build_tma(a);
     if (a.tma) {
       g_last_geometry = 3;
-      return std_layout ? launch_post2_k<true, true, true>(a, s) : launch_post2_k<true, false, true>(a, s);
+      return obs ? (std_layout ? launch_post2_k<true, true, true, true>(a, s) : launch_post2_k<true, false, true, true>(a, s))
+                 : (std_layout ? launch_post2_k<true, true, true, false>(a, s) : launch_post2_k<true, false, true, false>(a, s));
     }
   } else {
     a.tma = 0;
   }
-  return std_layout ? launch_post2_k<BG, true>(a, s) : launch_post2_k<BG, false>(a, s);
+  return obs ? (std_layout ? launch_post2_k<BG, true, false, true>(a, s) : launch_post2_k<BG, false, false, true>(a, s))
+             : (std_layout ? launch_post2_k<BG, true, false, false>(a, s) : launch_post2_k<BG, false, false, false>(a, s));
 }
 
 }  // namespace pp2

@@ -18,8 +18,9 @@ DEXSTEP_EARLY_SIM_LOADS=0 python bench.py --no-cpu-baseline > $o/${tag}_bench_no
 DEXSTEP_POST_GEOMETRY=persistent python bench.py --no-cpu-baseline > $o/${tag}_bench_persistent.json 2>> $o/${tag}_bench.err
 python bench.py --tile-kernel --no-cpu-baseline > $o/${tag}_bench_tile_kernel.json 2>> $o/${tag}_bench.err
 # ---- ncu: launch list (gpu__time_duration) of the default command, then full captures ----
-ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $o/${tag}_launches.csv \
-    python bench.py --steps 20 --warmup 3 --no-cpu-baseline > $o/${tag}_ncu_launches.log 2>&1
+# (only this library's kernels: the set-up of the bench launches thousands of torch fill / copy kernels first)
+ncu --metrics gpu__time_duration.sum --clock-control none -k regex:'physics|epilogue|reset_kernel|launch_floor' -c 600 --csv \
+    --log-file $o/${tag}_launches.csv python bench.py --steps 20 --warmup 3 --no-cpu-baseline > $o/${tag}_ncu_launches.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:post_physics -s 30 -c 1 -o $o/${tag}_post -f \
     python bench.py --steps 20 --warmup 3 --no-cpu-baseline > $o/${tag}_ncu_post.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:pre_physics -s 30 -c 1 -o $o/${tag}_pre -f \
