@@ -349,7 +349,7 @@ def run_reference_arm(args, task, n_env, rank, world):
         n_s //= 2
     value, ms, done, threads = cpu_reference_run(task, n_s, args.steps, args.warmup, 1234)
     sample = (f"{done} steps x {n_s} envs of {task} (job = {n_job} envs; oracle port of the reference's torch components, "
-              f"{threads} threads; the port runs ~2x faster than the unmodified reference components on the same cores, "
+              f"{threads} threads; the port runs 1.05-2x faster than the unmodified reference components on the same cores, "
               f"BASELINE.md section 5)")
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": done,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
@@ -459,6 +459,28 @@ def run_e2e(ring, steps, device, barrier, compact=False):
     return e0.elapsed_time(e1), h2d, d2h
 
 
+def bind_to_gpu_numa_node(device):
+    """Multi-GPU runs: pin this rank to the CPUs NVML reports as local to its GPU BEFORE any pinned host buffer is
+    allocated, so that the end-to-end path's staging buffers live on the GPU's own NUMA node (first-touch) and the
+    H2D / D2H copies of the ranks do not all cross the same socket link.  Best effort: returns a note for the JSON line."""
+    try:
+        import pynvml
+
+        pynvml.nvmlInit()
+        idx = torch.cuda._get_nvml_device_index(device) if hasattr(torch.cuda, "_get_nvml_device_index") else device.index
+        h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = {64 * w + b for w, m in enumerate(mask) for b in range(64) if (m >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return "nvml reports no local cpus inside this process's affinity mask"
+        os.sched_setaffinity(0, cpus)
+        return f"rank bound to {len(cpus)} cpus local to gpu {idx}"
+    except Exception as e:  # noqa: BLE001
+        return f"not bound ({type(e).__name__})"
+
+
 def kernel_avg_us(ring, fn, launches, group, device):
     plan, spg = make_plan(ring, fn, launches, group)
     warm_plan(plan, spg, 3, device)  # the graphs that are timed, not copies of them
@@ -490,6 +512,7 @@ def main():
         raise RuntimeError("bench.py needs a CUDA device: the step pipeline has no CPU fallback")
     device = torch.device("cuda", local)
     torch.cuda.set_device(device)
+    numa_note = bind_to_gpu_numa_node(device) if world > 1 else None
     barrier = None
     if world > 1:
         import torch.distributed as dist
@@ -601,6 +624,8 @@ def main():
            "full_tensor_layout": {"value": n_env * world * ke / (fms * 1e-3), "h2d_bytes_per_step": fh2d,
                                   "d2h_bytes_per_step": fd2h, "ms_per_step": fms / ke,
                                   "api": "DexStepEnv.step_host, whole Isaac Gym tensors shipped"}}
+    if numa_note:
+        e2e["numa"] = numa_note
     clocks = sampler.summary()
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -625,7 +650,7 @@ def main():
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "ms_per_step": cms,
                                 "sample": f"{done} steps x {n_env} envs of {task} (same workload; oracle port of the "
                                           f"reference's torch components; os.cpu_count()={os.cpu_count()}; the port runs "
-                                          f"~2x faster than the unmodified reference, BASELINE.md section 5)"}
+                                          f"1.05-2x faster than the unmodified reference, BASELINE.md section 5)"}
         torch.set_num_threads(1)
         v1, cms1, done1, _ = cpu_reference_run(task, n_env, 10**9, 1, 1234, budget_s=min(6.0, args.cpu_seconds))
         line["cpu_baseline_1thread"] = {"value": v1, "unit": UNIT, "cores": 1, "kind": "port", "ms_per_step": cms1,

@@ -72,9 +72,8 @@ constexpr int kActS = 19;  // odd smem row stride for <=18 actions / 18 active t
 
 __global__ void __launch_bounds__(kPreThreads) pre_physics_kernel(const __grid_constant__ PreArgs A) {
   __shared__ float s_act[kPreTile * kActS];
-  __shared__ float s_next[kPreTile * kActS];
-  __shared__ int s_d2a[DEX_NUM_DOF];
-  __shared__ float s_scale[DEX_NUM_DOF];
+  __shared__ float s_next[kPreTile * kActS];  // column 18 of every row stays 0: the source of the DOFs no active target drives
+  __shared__ float2 s_map[DEX_NUM_DOF];       // DOF -> (column of s_next as int bits, coupling scale)
   const DexParams& P = A.p;
   const DexStateBuffers& st = A.st;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -87,9 +86,10 @@ __global__ void __launch_bounds__(kPreThreads) pre_physics_kernel(const __grid_c
 
   // coupling tables -> shared (a per-lane index into the constant bank would serialise)
   if (tid < DEX_NUM_DOF) {
-    s_d2a[tid] = P.dof_to_active[tid];
-    s_scale[tid] = (tid < DEX_NUM_BASE) ? 1.0f : P.dof_coupling_scale[tid];
+    const int a = P.dof_to_active[tid];
+    s_map[tid] = make_float2(__int_as_float(a >= 0 ? a : DEX_NUM_ACTIVE), (tid < DEX_NUM_BASE) ? 1.0f : P.dof_coupling_scale[tid]);
   }
+  if (tid < kPreTile) s_next[tid * kActS + DEX_NUM_ACTIVE] = 0.0f;
   pdl_wait();               // the previous kernel of the stream (post-physics of the last step) has completed
   pdl_launch_dependents();  // the next kernel's CTAs may be scheduled as this grid drains
   // issue every global load of the tile first: the action rows (warp w: env rows w, w+8, ..; lane = column) ...
@@ -138,15 +138,31 @@ __global__ void __launch_bounds__(kPreThreads) pre_physics_kernel(const __grid_c
     }
   }
   // prev_actions rows (observation_encoder.py:287-296): row k for 32 envs = one 128 B line
-  if (act_lane)
-    for (int k = warp; k < NA; k += kPreWarps) st.prev_actions[k * N + env] = s_act[lane * kActS + k];
+  if (act_lane) {
+    float* pa = st.prev_actions + (size_t)warp * N + env;
+    const float* sa = s_act + lane * kActS + warp;
+#pragma unroll
+    for (int j = 0; j < 3; ++j)  // NA <= 18: rows warp, warp + 8, warp + 16
+      if (warp + j * kPreWarps < NA) pa[(size_t)j * kPreWarps * N] = sa[j * kPreWarps];
+  }
   __syncthreads();
-  // coupling 18 -> 26 (action_processor.py:571-614) straight into the contiguous full_dof_targets tile
-  float* dst = st.full_dof_targets + (size_t)e0 * DEX_NUM_DOF;
-  for (int i = tid; i < ne * DEX_NUM_DOF; i += kPreThreads) {
-    const int e = i / DEX_NUM_DOF, d = i - e * DEX_NUM_DOF;
-    const int a = s_d2a[d];
-    dst[i] = (a >= 0) ? s_next[e * kActS + a] * s_scale[d] : 0.0f;
+  // coupling 18 -> 26 (action_processor.py:571-614) straight into the contiguous full_dof_targets tile: element i of the
+  // tile is DOF d = i % 26 of env e = i / 26; one division per thread, then (e, d) advance by (9, 22) per 256 elements
+  float* dst = st.full_dof_targets + (size_t)e0 * DEX_NUM_DOF + tid;
+  const int n_out = ne * DEX_NUM_DOF;
+  int e = tid / DEX_NUM_DOF, d = tid - e * DEX_NUM_DOF;
+#pragma unroll
+  for (int j = 0; j < (kPreTile * DEX_NUM_DOF + kPreThreads - 1) / kPreThreads; ++j) {
+    if (tid + j * kPreThreads < n_out) {
+      const float2 m = s_map[d];
+      dst[j * kPreThreads] = s_next[e * kActS + __float_as_int(m.x)] * m.y;  // (an undriven DOF reads the zero column: 0 * scale)
+    }
+    e += kPreThreads / DEX_NUM_DOF;
+    d += kPreThreads % DEX_NUM_DOF;
+    if (d >= DEX_NUM_DOF) {
+      d -= DEX_NUM_DOF;
+      ++e;
+    }
   }
 }
 
