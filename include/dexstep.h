@@ -29,6 +29,9 @@
  *   dex_apply_coupling / dex_extract_active_targets
  *                        ActionProcessor.apply_coupling / extract_active_targets_from_full_dof
  *                                                               action_processor.py:571-614 / 616-666
+ *   dex_reset_actor_indices  the index tensors of the indexed gym setters   components/reset/reset_manager.py:139-168,
+ *                                                               components/physics/physics_manager.py:121-160 (fixed capacity, no host read)
+ *   dex_post_physics_noalloc  (no counterpart in the reference: dex_post_physics + fused epilogue with library-owned scratch)
  *   dex_point_in_hand_frame  utils/coordinate_transforms.py:17-35 (known-answer tests)
  *   (DexOutBuffers.episode_sums/.stat_totals: RewardComponentObserver accumulation, rl/reward_observer.py:160-293,
  *    fused into dex_post_physics; the totals vector is the payload of the single NCCL all-reduce)
