@@ -132,6 +132,7 @@ def load(path: str = None) -> ctypes.CDLL:
                                      P(DexEpilogueBuffers), i32, i32, u32, vp, u64, u64, vp]
     lib.dex_post_physics_noalloc.argtypes = lib.dex_post_physics.argtypes
     lib.dex_reset_actor_indices.argtypes = [P(DexEpilogueBuffers), i32, i32, i32, vp, vp, vp, vp]
+    lib.dex_policy_input_update.argtypes = [vp, i32, i32, vp, vp, vp, vp, vp, vp, ctypes.c_float, ctypes.c_float, vp, vp]
     lib.dex_reset_idx.argtypes = [P(DexParams), P(DexSimViews), P(DexStateBuffers), vp, i32, vp, u64, u64, vp]
     lib.dex_step_epilogue.argtypes = [P(DexParams), P(DexEpilogueBuffers), i32, vp]
     lib.dex_apply_coupling.argtypes = [P(DexParams), vp, vp, i32, vp]

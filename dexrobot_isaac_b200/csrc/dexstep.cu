@@ -196,6 +196,78 @@ __global__ void reset_actor_indices_kernel(const int32_t* env_ids, const int32_t
 }
 
 // ------------------------------------------------------------------------------------------------
+// policy-input stage, training half: rl_games' RunningMeanStd in training mode first merges the moments of
+// the current batch of observations into its running statistics and only then normalises that batch with the UPDATED
+// statistics - a reduction over all envs sits between obs_buf and the network input, so this half cannot ride in the
+// post-physics pass.  Three small launches on the caller's stream, no host read: column sums -> merge -> normalise.
+// ------------------------------------------------------------------------------------------------
+constexpr int kMomThreads = 256;
+constexpr int kMomRowBlocks = 64;
+
+// grid (ceil(W / 32), kMomRowBlocks): lane = column, the 8 warps of a block stride over the block's rows; fp64 partial
+// sums (the batch moments rl_games takes in fp32 are reproduced to well below 1e-6 relative), one atomic per column and block
+__global__ void __launch_bounds__(kMomThreads) obs_moments_kernel(const float* __restrict__ obs, const int n, const int W, double* acc) {
+  __shared__ double s_sum[kMomThreads / 32][32], s_sq[kMomThreads / 32][32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int col = blockIdx.x * 32 + lane;
+  const int rows_per = (n + gridDim.y - 1) / gridDim.y;
+  const int r0 = blockIdx.y * rows_per, r1 = min(n, r0 + rows_per);
+  double sum = 0.0, sq = 0.0;
+  if (col < W)
+    for (int r = r0 + warp; r < r1; r += kMomThreads / 32) {
+      const double v = (double)obs[(size_t)r * W + col];
+      sum += v;
+      sq += v * v;
+    }
+  s_sum[warp][lane] = sum;
+  s_sq[warp][lane] = sq;
+  __syncthreads();
+  if (warp == 0 && col < W) {
+#pragma unroll
+    for (int w = 1; w < kMomThreads / 32; ++w) {
+      sum += s_sum[w][lane];
+      sq += s_sq[w][lane];
+    }
+    atomicAdd(acc + col, sum);
+    atomicAdd(acc + W + col, sq);
+  }
+}
+
+// one block: rl_games/algos_torch/running_mean_std.py _update_mean_var_count_from_moments (Chan et al.), float64 state,
+// fed with the batch's fp32 mean and UNBIASED fp32 variance like `input.mean(0)`, `input.var(0)`
+__global__ void obs_moments_merge_kernel(const double* acc, const int n, const int W, double* running_mean, double* running_var,
+                                         double* count, float* norm_mean, float* norm_scale, const float epsilon) {
+  const double cnt = *count;
+  __syncthreads();  // every thread has read the old count before thread 0 replaces it
+  for (int c = threadIdx.x; c < W; c += blockDim.x) {
+    const double s = acc[c], q = acc[W + c];
+    const double mean_d = s / n;
+    const double var_d = n > 1 ? fmax((q - s * mean_d) / (n - 1), 0.0) : 0.0;
+    const double bm = (double)(float)mean_d, bv = (double)(float)var_d;  // the fp32 tensors rl_games hands to the merge
+    const double rm = running_mean[c], rv = running_var[c];
+    const double delta = bm - rm, tot = cnt + (double)n;
+    const double new_mean = rm + delta * (double)n / tot;
+    const double m2 = rv * cnt + bv * (double)n + delta * delta * cnt * (double)n / tot;
+    const double new_var = m2 / tot;
+    running_mean[c] = new_mean;
+    running_var[c] = new_var;
+    norm_mean[c] = (float)new_mean;
+    norm_scale[c] = 1.0f / sqrtf((float)new_var + epsilon);
+  }
+  if (threadIdx.x == 0) *count = cnt + (double)n;
+}
+
+// y = clamp((x - mean) * scale, -clip, clip), NaN passes through: the arithmetic of the fused stage (copy_obs_norm_rows)
+__global__ void obs_normalize_kernel(const float* __restrict__ obs, const float* __restrict__ mean, const float* __restrict__ scale,
+                                     const float clip, const size_t total, const int W, float* __restrict__ out) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % (size_t)W);
+    const float y = (obs[i] - mean[c]) * scale[c];
+    out[i] = (y != y) ? y : fminf(fmaxf(y, -clip), clip);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // small stand-alone helpers
 // ------------------------------------------------------------------------------------------------
 struct CoupleArgs {
@@ -535,6 +607,27 @@ int dex_reset_actor_indices(const DexEpilogueBuffers* ep, int32_t capacity, int3
   reset_actor_indices_kernel<<<(capacity + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
       ep->env_ids, ep->num_reset, capacity, num_actors, dof_actor, root_actor_ids, dof_actor_ids, overflow);
   const cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? DEX_OK : (int)e;
+}
+
+int dex_policy_input_update(const float* obs_buf, int32_t n_envs, int32_t obs_dim, double* running_mean, double* running_var,
+                            double* count, float* norm_mean, float* norm_scale, float* obs_norm, float epsilon, float clip,
+                            double* scratch, void* stream) {
+  if (!obs_buf || !running_mean || !running_var || !count || !norm_mean || !norm_scale || !scratch) return DEX_ERR_NULL;
+  if (n_envs <= 0 || obs_dim <= 0 || obs_dim > 1024) return DEX_ERR_SIZE;
+  cudaStream_t s = (cudaStream_t)stream;
+  cudaError_t e = cudaMemsetAsync(scratch, 0, sizeof(double) * 2 * (size_t)obs_dim, s);
+  if (e != cudaSuccess) return (int)e;
+  const int row_blocks = n_envs < kMomRowBlocks * 8 ? (n_envs + 7) / 8 : kMomRowBlocks;
+  obs_moments_kernel<<<dim3((obs_dim + 31) / 32, row_blocks), kMomThreads, 0, s>>>(obs_buf, n_envs, obs_dim, scratch);
+  obs_moments_merge_kernel<<<1, 256, 0, s>>>(scratch, n_envs, obs_dim, running_mean, running_var, count, norm_mean, norm_scale,
+                                            epsilon);
+  if (obs_norm != nullptr) {
+    const size_t total = (size_t)n_envs * obs_dim;
+    const int blocks = (int)((total + 4 * 256 - 1) / (4 * 256));
+    obs_normalize_kernel<<<blocks > 4 * 148 ? 4 * 148 : blocks, 256, 0, s>>>(obs_buf, norm_mean, norm_scale, clip, total, obs_dim, obs_norm);
+  }
+  e = cudaGetLastError();
   return e == cudaSuccess ? DEX_OK : (int)e;
 }
 

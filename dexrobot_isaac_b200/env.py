@@ -157,6 +157,14 @@ class DexStepEnv:
         step, computed from the same on-chip copy of the observation as obs_buf.  See StepPipeline.set_obs_normalization."""
         self.pipeline.set_obs_normalization(running_mean, running_var, epsilon, clip)
 
+    def enable_obs_norm_training(self, epsilon: float = 1e-5, clip: float = 5.0, **kw):
+        """Training mode of the policy-input stage (rl_games updates its running mean / variance with every batch before it
+        normalises it): see StepPipeline.enable_obs_norm_training / update_obs_normalization / freeze_obs_normalization."""
+        self.pipeline.enable_obs_norm_training(epsilon, clip, **kw)
+
+    def update_obs_normalization(self):
+        self.pipeline.update_obs_normalization()
+
     @property
     def obs_norm(self) -> Optional[torch.Tensor]:
         return self.pipeline.out.get("obs_norm")

@@ -168,6 +168,51 @@ class StepPipeline:
                 raise RuntimeError("norm_clip is a launch parameter: set it before capture_step_graph()")
             self._out.norm_clip = float(clip)
 
+    def enable_obs_norm_training(self, epsilon: float = 1e-5, clip: float = 5.0, running_mean: Optional[torch.Tensor] = None,
+                                 running_var: Optional[torch.Tensor] = None, count: float = 1.0, fused_forward: bool = False):
+        """Training mode of the policy-input stage (rl_games RunningMeanStd with ``self.training``): device-resident float64
+        running statistics (``self.rms``: running_mean, running_var, count - rl_games' initial values 0 / 1 / 1 unless given)
+        that ``update_obs_normalization()`` advances with the batch of observations of the step just computed, after which
+        ``out["obs_norm"]`` holds that batch normalised with the UPDATED statistics (dex_policy_input_update).  The fused
+        frozen-statistics stage of dex_post_physics stays off in this mode unless ``fused_forward`` (it would normalise with
+        the statistics of the previous step and be overwritten); ``freeze_obs_normalization()`` switches to it for play."""
+        d, dev, o = self.spec.obs_dim, self.device, self.out
+        f64 = torch.float64
+        self.rms = {
+            "running_mean": (torch.zeros(d, dtype=f64) if running_mean is None else running_mean.detach().to(f64).reshape(d).clone()).to(dev),
+            "running_var": (torch.ones(d, dtype=f64) if running_var is None else running_var.detach().to(f64).reshape(d).clone()).to(dev),
+            "count": torch.full((1,), float(count), dtype=f64, device=dev),
+            "scratch": torch.zeros(2 * d, dtype=f64, device=dev)}
+        self._rms_eps, self._rms_clip = float(epsilon), float(clip)
+        if o.get("obs_norm") is None:
+            o["obs_norm"] = torch.zeros(self.n, d, dtype=torch.float32, device=dev)
+            o["norm_mean"] = torch.zeros(d, dtype=torch.float32, device=dev)
+            o["norm_scale"] = torch.ones(d, dtype=torch.float32, device=dev)
+        o["norm_mean"].copy_(self.rms["running_mean"].float())
+        o["norm_scale"].copy_(1.0 / torch.sqrt(self.rms["running_var"].float() + epsilon))
+        self._out.norm_mean, self._out.norm_scale = _ptr(o["norm_mean"]), _ptr(o["norm_scale"])
+        self._out.norm_clip = float(clip)
+        self._out.obs_norm = _ptr(o["obs_norm"]) if fused_forward else None
+
+    def update_obs_normalization(self):
+        """dex_policy_input_update on the current obs_buf: batch moments -> merge into the running statistics -> obs_norm
+        with the updated statistics.  Three small launches + one memset on the current stream, no host read (capturable)."""
+        if getattr(self, "rms", None) is None:
+            raise RuntimeError("enable_obs_norm_training() first")
+        o, r = self.out, self.rms
+        L.check(self.lib.dex_policy_input_update(o["obs_buf"].data_ptr(), self.n, self.spec.obs_dim, r["running_mean"].data_ptr(),
+                                                 r["running_var"].data_ptr(), r["count"].data_ptr(), o["norm_mean"].data_ptr(),
+                                                 o["norm_scale"].data_ptr(), o["obs_norm"].data_ptr(), self._rms_eps,
+                                                 self._rms_clip, r["scratch"].data_ptr(), self._stream()),
+                "dex_policy_input_update")
+        self.launches += 3
+
+    def freeze_obs_normalization(self):
+        """Evaluation / play: stop updating, let dex_post_physics write obs_norm with the statistics reached so far."""
+        if getattr(self, "_graph", None) is not None:
+            raise RuntimeError("switch before capture_step_graph()")
+        self._out.obs_norm = _ptr(self.out["obs_norm"])
+
     # ------------------------------------------------------------------ sim binding (zero-copy)
     def bind_sim(self, sim: Dict[str, torch.Tensor]):
         """Point the kernels at the caller's sim tensors.  With Isaac Gym these are the

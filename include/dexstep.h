@@ -413,6 +413,22 @@ int dex_post_physics_noalloc(const DexParams* params, const DexSimViews* sim, co
 int dex_reset_actor_indices(const DexEpilogueBuffers* epilogue, int32_t capacity, int32_t num_actors, int32_t dof_actor,
                             int32_t* root_actor_ids, int32_t* dof_actor_ids, int32_t* overflow, void* stream);
 
+/* Policy-input stage, TRAINING half (rl_games RunningMeanStd.forward with self.training, the model the reference
+ * trains with: cfg/train/BaseTaskPPO.yaml:44 normalize_input).  In this order, on `stream`, without a host read:
+ *   1. batch moments of obs_buf over the n_envs rows (mean, unbiased variance, rounded to fp32 as rl_games' input.mean(0) /
+ *      input.var(0) are),
+ *   2. Chan merge into the float64 running statistics: running_mean / running_var [obs_dim], count [1] (rl_games initialises
+ *      them to 0 / 1 / 1), and norm_mean = (float)running_mean, norm_scale = 1 / sqrtf((float)running_var + epsilon) - the two
+ *      vectors DexOutBuffers.norm_mean / norm_scale point at, so the fused frozen-statistics stage of the NEXT dex_post_physics
+ *      calls uses the new statistics,
+ *   3. obs_norm (optional, [n_envs, obs_dim]) = clamp((obs_buf - norm_mean) * norm_scale, -clip, clip) with the UPDATED statistics,
+ *      which is what the network sees in training mode.
+ * A reduction over all envs sits between obs_buf and its normalised form, so this half is three small launches behind
+ * dex_post_physics rather than part of it; evaluation / play use the fused stage alone.  scratch: [2 * obs_dim] doubles. */
+int dex_policy_input_update(const float* obs_buf, int32_t n_envs, int32_t obs_dim, double* running_mean, double* running_var,
+                            double* count, float* norm_mean, float* norm_scale, float* obs_norm, float epsilon, float clip,
+                            double* scratch, void* stream);
+
 /* Masked reset of envs with reset_mask[env] != 0 (NULL = all envs). */
 int dex_reset_idx(const DexParams* params, const DexSimViews* sim, const DexStateBuffers* state,
                   const uint8_t* reset_mask, int32_t n_envs, const float* uniforms, uint64_t seed,

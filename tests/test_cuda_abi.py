@@ -424,3 +424,86 @@ def test_fused_obs_normalization(task, materialize):
     assert clamped > 0  # the clip branch was exercised
     with pytest.raises(ValueError):
         e2.set_obs_normalization(torch.zeros(d + 1), torch.ones(d + 1))
+
+
+@pytest.mark.parametrize("task,n", [("BlindGrasping", 4096), ("BaseTask", 1000)])
+def test_policy_input_training_update(task, n):
+    """SURVEY 8f N3, training half (dex_policy_input_update): the running mean / variance / count after every step equal
+    rl_games' RunningMeanStd in training mode (oracle/policy_input.py) fed with the same observations, obs_norm equals the
+    forward pass with the UPDATED statistics, a CUDA-graph replay of step + update equals the eager twin, and after
+    freeze_obs_normalization() the fused stage of dex_post_physics carries on with the statistics reached."""
+    from oracle.policy_input import RunningMeanStd
+
+    lay = synth.BodyLayout(with_box=task == "BlindGrasping")
+    e1, e2 = _env(task, n, materialize=False), _env(task, n, materialize=False)
+    d = e1.pipeline.spec.obs_dim
+    world = synth.ScriptedWorld(n, lay, seed=9, nact=e1.num_actions)
+    u = world.uniforms(0).to(DEV)
+    st0 = world.state(0, e1.episode_step_count, None)
+    for e in (e1, e2):
+        e.load_state(st0)
+        e.reset(u)
+        e.pipeline.uniforms = u
+        e.enable_obs_norm_training(epsilon=1e-5, clip=5.0)
+    rms = RunningMeanStd(d)
+    rms.training = True
+    act = torch.zeros(n, e2.num_actions, device=DEV)
+    graph = None
+    for t in range(1, 9):
+        st = world.state(t, e1.episode_step_count, None)
+        a = world.actions(t).to(DEV)
+        e1.load_state(st)
+        e1.pipeline.step(a.contiguous())
+        e1.update_obs_normalization()
+        e2.load_state(st)
+        act.copy_(a)
+        if t < 5:
+            e2.pipeline.step(act)
+            e2.update_obs_normalization()
+        else:
+            if graph is None:
+                torch.cuda.synchronize()
+                dicts = (e2.pipeline.state, e2.pipeline.sim_tensors, e2.pipeline.out, e2.pipeline.epi, e2.pipeline.rms)
+                saved = [{k: v.clone() for k, v in dd.items() if v is not None} for dd in dicts]
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph):
+                    e2.pipeline.step(act)
+                    e2.update_obs_normalization()
+                for dd, sv in zip(dicts, saved):
+                    for k, v in sv.items():
+                        dd[k].copy_(v)
+            graph.replay()
+        torch.cuda.synchronize()
+        obs = e1.obs_buf.cpu()
+        rms.forward(obs)  # training: update, then normalise
+        r = e1.pipeline.rms
+        assert float(r["count"]) == float(rms.count) == 1.0 + t * n
+        gm, gv = r["running_mean"].cpu(), r["running_var"].cpu()
+        # the batch moments enter in fp32 on both sides (torch's fp32 reduction vs float64 sums rounded to fp32): 1 fp32 ulp of
+        # the column's magnitude for the mean, of its squared magnitude for the variance
+        mag = obs.abs().max(dim=0).values.double()
+        assert bool(((gm - rms.running_mean).abs() <= 1e-6 * rms.running_mean.abs() + 2e-7 * mag + 1e-9).all()), f"step {t} mean"
+        assert bool(((gv - rms.running_var).abs() <= 1e-5 * rms.running_var.abs() + 4e-7 * mag * mag + 1e-9).all()), f"step {t} var"
+        # obs_norm: forward with the statistics the device holds (isolates the element-wise part from the moment rounding)
+        chk = RunningMeanStd(d)
+        chk.running_mean, chk.running_var = gm, gv
+        want = chk.forward(obs)
+        got = e1.obs_norm.cpu()
+        assert torch.allclose(got, want, rtol=1e-6, atol=1e-6), f"step {t}: max diff {(got - want).abs().max()}"
+        # the graph-replayed twin is bit-identical (same kernels, same order; the fp64 atomics of 64 row blocks commute
+        # only approximately, so the statistics are compared to 1e-12 relative)
+        r2 = e2.pipeline.rms
+        assert torch.allclose(r2["running_mean"], r["running_mean"], rtol=1e-12, atol=1e-15)
+        assert torch.allclose(r2["running_var"], r["running_var"], rtol=1e-12, atol=1e-15)
+        assert torch.allclose(e2.obs_norm, e1.obs_norm, rtol=1e-6, atol=1e-6)
+        assert torch.equal(e1.obs_buf, e2.obs_buf)
+    # play: frozen statistics, fused stage
+    e1.pipeline.freeze_obs_normalization()
+    st = world.state(9, e1.episode_step_count, None)
+    e1.load_state(st)
+    e1.pipeline.step(world.actions(9).to(DEV).contiguous())
+    torch.cuda.synchronize()
+    chk = RunningMeanStd(d)
+    chk.running_mean, chk.running_var = e1.pipeline.rms["running_mean"].cpu(), e1.pipeline.rms["running_var"].cpu()
+    assert torch.allclose(e1.obs_norm.cpu(), chk.forward(e1.obs_buf.cpu()), rtol=1e-6, atol=1e-6)
+    assert float(e1.pipeline.rms["count"]) == 1.0 + 8 * n  # no update in play
