@@ -74,3 +74,35 @@ def test_quat_mul_matches_hamilton_product():
     ref = torch.stack([w1 * x2 + x1 * w2 + y1 * z2 - z1 * y2, w1 * y2 - x1 * z2 + y1 * w2 + z1 * x2,
                        w1 * z2 + x1 * y2 - y1 * x2 + z1 * w2, w1 * w2 - x1 * x2 - y1 * y2 - z1 * z2], dim=-1)
     assert torch.allclose(O.quat_mul(a, b), ref, atol=1e-12)
+
+
+def test_quaternion_algebra_against_scipy():
+    """isaacgym.torch_utils is a binary-only dependency that is absent here; its functions are restated in
+    oracle/stubs/isaacgym/torch_utils.py (and again in the oracle / the CUDA kernels).  Independent pin of the convention
+    (scalar-last x, y, z, w; Hamilton product; active rotation): scipy.spatial.transform.Rotation uses the same convention,
+    so  quat_mul(a, b) == (R(a) * R(b)).as_quat(),  quat_conjugate == inverse,  quat_rotate == apply,
+    quat_rotate_inverse == inverse().apply,  quat_from_euler_xyz == from_euler("xyz") (extrinsic), on 256 random unit
+    quaternions, to float32 accuracy and up to the quaternion double cover (q ~ -q)."""
+    R = pytest.importorskip("scipy.spatial.transform").Rotation
+    g = torch.Generator().manual_seed(3)
+    a = torch.randn(256, 4, generator=g)
+    b = torch.randn(256, 4, generator=g)
+    a, b = a / a.norm(dim=1, keepdim=True), b / b.norm(dim=1, keepdim=True)
+    v = torch.randn(256, 3, generator=g)
+    Ra, Rb = R.from_quat(a.double().numpy()), R.from_quat(b.double().numpy())
+
+    def same_rotation(q_got, q_want):
+        q_want = torch.from_numpy(q_want).float()
+        sign = torch.sign((q_got * q_want).sum(dim=1, keepdim=True))
+        return torch.allclose(q_got, q_want * sign, atol=2e-6)
+
+    for mul, conj in ((stub.quat_mul, stub.quat_conjugate), (O.quat_mul, O.quat_conjugate)):
+        assert same_rotation(mul(a, b), (Ra * Rb).as_quat())
+        assert same_rotation(conj(a), Ra.inv().as_quat())
+    assert torch.allclose(stub.quat_rotate(a, v), torch.from_numpy(Ra.apply(v.double().numpy())).float(), atol=3e-6)
+    assert torch.allclose(stub.quat_rotate_inverse(a, v), torch.from_numpy(Ra.inv().apply(v.double().numpy())).float(), atol=3e-6)
+    assert torch.allclose(O.point_in_hand_frame(v, torch.zeros(256, 3), a),
+                          torch.from_numpy(Ra.inv().apply(v.double().numpy())).float(), atol=3e-6)
+    e = torch.rand(256, 3, generator=g) * 2.0 - 1.0
+    got = stub.quat_from_euler_xyz(e[:, 0], e[:, 1], e[:, 2])
+    assert same_rotation(got, R.from_euler("xyz", e.double().numpy()).as_quat())
