@@ -221,6 +221,9 @@ class Ring:
         return g
 
 
+WARM_MS = 25.0  # minimum untimed activity of the timed graphs before a timed region
+
+
 def warm_plan(plan, steps_per_graph, warmup_steps, device):
     """Untimed replays of the SAME CUDAGraph objects that are timed afterwards: every graph of the plan runs at least
     once (a graph's first launch pays its one-time upload), and at least `warmup_steps` ring steps run in total."""
@@ -231,6 +234,14 @@ def warm_plan(plan, steps_per_graph, warmup_steps, device):
     while done < warmup_steps:
         plan[0][0].replay()
         done += steps_per_graph[0]
+    # ... and at least WARM_MS of them: a GPU that has just been idle runs its first half millisecond of kernels 3-6 % slower
+    # (every kernel, the empty one included), which is most of a 20-step timed region but nothing of a 4000-step one
+    t0 = time.perf_counter()
+    while (time.perf_counter() - t0) * 1e3 < WARM_MS:
+        for _ in range(8):
+            plan[0][0].replay()
+        done += 8 * steps_per_graph[0]
+        torch.cuda.synchronize(device)
     torch.cuda.synchronize(device)
     return done
 
@@ -241,6 +252,10 @@ def timed_replays(plan, device, dist_barrier=None):
         dist_barrier()
     torch.cuda.synchronize(device)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    # ~100 us of device-side delay AHEAD of the start event: the host enqueues the event and the first graph while the GPU
+    # is still busy, so the timed region holds the K steps back to back and not the host's launch latency of the first
+    # graph (10 us: 2 % of a 20-step run, nothing of a 4000-step one)
+    torch.cuda._sleep(200_000)
     e0.record()
     for g, reps in plan:
         for _ in range(reps):
@@ -634,6 +649,9 @@ def main():
             "config": {"workload": args.workload, "task": task, "envs_per_gpu": n_env, "envs_total": n_env * world,
                        "obs_dim": ring.envs[0].num_observations, "num_bodies": ring.layout.num_bodies,
                        "observer": bool(args.observer), "obs_norm": bool(args.obs_norm), "l2": ring.l2_note, "graph_steps": group,
+                       "timing": "CUDA events on the launching stream around exactly K steps of CUDA-graph replays (the graphs that ran "
+                                 "the warm-up); a ~100 us device-side delay ahead of the start event keeps the host's launch latency "
+                                 "of the first graph out of the region",
                        "early_sim_loads": os.environ.get("DEXSTEP_EARLY_SIM_LOADS", "1") != "0",
                        "parallelism": f"env-sharded x{world}, no step-path collective, 1 NCCL all-reduce of stats"},
             "roofline": roofline, "e2e": e2e, "gpu_launches": launches_per_step * args.steps, "clocks": clocks,
