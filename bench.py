@@ -62,6 +62,8 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--tile-kernel", action="store_true",
                     help="A/B: run the round-1 one-tile-per-CTA kernel (DEX_FLAG_TILE_KERNEL) instead of the persistent v2 kernel")
+    ap.add_argument("--single-pass", action="store_true",
+                    help="DEX_FLAG_SINGLE_PASS on every post-physics launch: the single-pass kernel where it applies (2-4 tiles per SM)")
     ap.add_argument("--sweep", action="store_true", help="also print the post-physics num_envs sweep (configs[4])")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the bounded CPU-baseline sample")
     return ap.parse_args()
@@ -542,6 +544,9 @@ def main():
     if args.tile_kernel:
         for e in ring.envs:
             e.pipeline.tile_kernel = True
+    if args.single_pass:
+        for e in ring.envs:
+            e.pipeline.single_pass = True
     R = len(ring)
     group = R * max(1, -(-32 // R))
     # The graphs that are timed are captured once and ALSO run the warm-up (>= --warmup untimed steps, every graph of
@@ -623,6 +628,24 @@ def main():
               "post_frac_of_hbm_peak": b_post * n_env / (hot_post * 1e-6) / 1e9 / peak,
               "note": "one replica replayed back to back (inputs stay in L2); the headline value is the L2-cold ring"}
 
+    # ---- the other geometry of the post-physics pass, same run (default: persistent kernel; alternative: single pass,
+    #      which only exists for BlindGrasping between 2 and 4 tiles per SM) ----
+    alt_geometry = None
+    if not args.tile_kernel and not args.single_pass:
+        for e in ring.envs:
+            e.pipeline.single_pass = True
+        alt_post = kernel_avg_us(ring, post_only, kl, group, device)
+        if lib.dex_debug_last_post_kernel() == 2:
+            alt_step = kernel_avg_us(ring, full_step, kl, group, device)
+            alt_geometry = {"kernel": "post_physics_v2s_kernel", "how": "DEX_FLAG_SINGLE_PASS / StepPipeline.single_pass",
+                            "post_us": alt_post, "step_us": alt_step, "value": n_env * world / (alt_step * 1e-6),
+                            "l2_hot_post_us": kernel_avg_us(hot, post_only, hk, 32, device),
+                            "l2_hot_step_us": kernel_avg_us(hot, full_step, hk, 32, device),
+                            "note": "slower than the default when every input comes from HBM, faster when the sim tensors are "
+                                    "L2-resident (post-physics right behind the simulator)"}
+        for e in ring.envs:
+            e.pipeline.single_pass = False
+
     # ---- end to end through DexStepEnv.step_host (host buffers, copies inside the timed region) ----
     ke = max(2, min(args.steps, 200))
     sampler.start()
@@ -655,7 +678,7 @@ def main():
                        "early_sim_loads": os.environ.get("DEXSTEP_EARLY_SIM_LOADS", "1") != "0",
                        "parallelism": f"env-sharded x{world}, no step-path collective, 1 NCCL all-reduce of stats"},
             "roofline": roofline, "e2e": e2e, "gpu_launches": launches_per_step * args.steps, "clocks": clocks,
-            "kernels_us": {"pre_physics": pre_us, "post_physics": post_us, "epilogue": epi_us, "empty_kernel_launch_floor": floor_us,
+            "single_pass_geometry": alt_geometry, "kernels_us": {"pre_physics": pre_us, "post_physics": post_us, "epilogue": epi_us, "empty_kernel_launch_floor": floor_us,
                            "stats_allreduce": allreduce_us},
             "l2_hot": l2_hot,
             "episode_stats": {"steps": stats[C["DEX_NUM_COUNTERS"]], "resets": stats[C["DEX_CNT_RESET"]],

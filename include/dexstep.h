@@ -103,6 +103,11 @@ extern "C" {
 #define DEX_FLAG_TILE_KERNEL 16u       /* run the table-driven one-tile-per-CTA kernel (post_physics.cuh) even where the persistent
                                           warp-specialised kernel (post_physics_v2.cuh) covers the launch: A/B runs and the
                                           bit-for-bit cross-check of the two implementations (tests/test_cuda_v2.py) */
+#define DEX_FLAG_SINGLE_PASS 64u      /* prefer the single-pass kernel (one 32-env tile per thread block, four blocks per SM, no ring)
+                                         where it applies: BlindGrasping with more than 2 and at most 4 tiles per SM (16 384 envs on a
+                                         B200).  It is 3-5 % slower than the persistent kernel when every input comes from HBM and
+                                         20 % faster when the sim tensors are still L2-resident, i.e. when dex_post_physics runs right
+                                         behind the physics step that wrote them.  Ignored elsewhere; same results bit for bit */
 #define DEX_FLAG_TMA_STAGING 32u      /* persistent kernel with TMA producers: every gathered Isaac Gym row / state buffer is one
                                          2-D tensor copy (cp.async.bulk.tensor, SASS UTMALDG) instead of 4-byte asynchronous
                                          copies.  Bit-identical results; MEASURED SLOWER on B200 (20.98 vs 18.87 us per launch at

@@ -32,13 +32,14 @@ def test_fused_epilogue_262144_envs(env):
 
 @pytest.mark.parametrize("n", [16384, 12000, 4096, 100003, 33])
 def test_fused_epilogue_every_geometry_launch_blocking(n):
-    """persistent (<= 2 tiles/SM and > 4 tiles/SM), single-pass (2-4 tiles/SM), ragged sizes."""
+    """persistent kernel from under one tile per SM to many, ragged sizes (the single-pass kernel: next test)."""
     _run("BlindGrasping", n, 5, CUDA_LAUNCH_BLOCKING=1)
     _run("BaseTask", n, 5, CUDA_LAUNCH_BLOCKING=1, DEXSTEP_PDL=0)
 
 
-def test_fused_epilogue_forced_persistent_geometry():
-    _run("BlindGrasping", 16384, 5, DEXSTEP_POST_GEOMETRY="persistent", CUDA_LAUNCH_BLOCKING=1)
+def test_fused_epilogue_single_pass_geometry():
+    _run("BlindGrasping", 16384, 5, DEXSTEP_POST_GEOMETRY="single", CUDA_LAUNCH_BLOCKING=1)
+    _run("BlindGrasping", 12000, 5, DEXSTEP_POST_GEOMETRY="single", DEXSTEP_PDL=0)
 
 
 def test_rewinding_the_step_counter_rezeroes_the_tile_records():

@@ -37,9 +37,10 @@ def oracle_env(task, n, layout=None, **kw):
     return OracleEnv(cfg, n, layout, synth.dof_props_tensor())
 
 
-def _lockstep(task, n, steps, seed, layout=None, check_every=1, **kw):
+def _lockstep(task, n, steps, seed, layout=None, check_every=1, single_pass=False, **kw):
     layout = layout or synth.BodyLayout(with_box=task == "BlindGrasping")
     ora, cud = oracle_env(task, n, layout, **kw), lean_env(task, n, layout, **kw)
+    cud.pipeline.single_pass = single_pass
     world = synth.ScriptedWorld(n, layout, seed=seed, nact=ora.num_actions)
     bad, seen = [], {"reset": 0, "success": 0, "failure": 0, "timeout": 0}
     floors = penetration_floors(load_task_config(task, num_envs=n, **kw))
@@ -92,11 +93,16 @@ def test_v2_lockstep_n4096():
     assert seen["reset"] > 0
 
 
-@pytest.mark.parametrize("task", ["BaseTask", "BlindGrasping"])
-def test_v2_lockstep_headline_size(task):
-    """BASELINE.json configs[3] size (16 384 envs): 24 control steps against the oracle, every step compared."""
-    seen = _lockstep(task, 16384, 24, seed=210)
+@pytest.mark.parametrize("task,single", [("BaseTask", False), ("BlindGrasping", False), ("BlindGrasping", True)],
+                         ids=["BaseTask", "BlindGrasping", "BlindGrasping-single_pass"])
+def test_v2_lockstep_headline_size(task, single):
+    """BASELINE.json configs[3] size (16 384 envs): 24 control steps against the oracle, every step compared; through the
+    persistent kernel (default) and the single-pass kernel (DEX_FLAG_SINGLE_PASS)."""
+    from dexrobot_isaac_b200 import _lib as L
+
+    seen = _lockstep(task, 16384, 24, seed=210, single_pass=single)
     assert seen["reset"] > 0
+    assert L.load().dex_debug_last_post_kernel() == (2 if single else 1)
 
 
 BUFS_OUT = ("obs_buf", "rew_buf", "reset_buf", "reward_components", "success", "failure", "timeout", "reset_bits")
@@ -104,19 +110,24 @@ BUFS_OUT = ("obs_buf", "rew_buf", "reset_buf", "reward_components", "success", "
 
 @pytest.mark.parametrize("task,n,tma", [("BlindGrasping", 16384, False), ("BaseTask", 16384, False), ("BlindGrasping", 4096, False),
                                         ("BaseTask", 5000, False), ("BlindGrasping", 100003, False), ("BlindGrasping", 33, False),
-                                        ("BlindGrasping", 16384, True), ("BlindGrasping", 4096, True), ("BlindGrasping", 131072, True)])
+                                        ("BlindGrasping", 16384, True), ("BlindGrasping", 4096, True), ("BlindGrasping", 131072, True),
+                                        ("BlindGrasping", 16384, "single"), ("BlindGrasping", 12000, "single"),
+                                        ("BlindGrasping", 9473, "single")])
 def test_v2_equals_tile_kernel_bitwise(task, n, tma):
     """Same seeded random-state trajectory through the persistent kernel and through the tile kernel: every output,
     every state buffer, the sim tensors the fused reset rewrites, env_ids and the epilogue statistics are identical
     bit for bit (in-kernel Philox resets included: both kernels key the stream by (seed, step, env)).
-    ``tma``: the persistent kernel with tensor-copy producers (DEX_FLAG_TMA_STAGING)."""
+    ``tma``: True = the persistent kernel with tensor-copy producers (DEX_FLAG_TMA_STAGING), "single" = the single-pass kernel."""
     from dexrobot_isaac_b200 import _lib as L
 
     lay = synth.BodyLayout(with_box=task == "BlindGrasping")
     gen = torch.Generator().manual_seed(31)
     e1, e2 = lean_env(task, n), lean_env(task, n)
     e1.pipeline.tile_kernel = True
+    single = tma == "single"  # DEX_FLAG_SINGLE_PASS: the single-pass kernel (2 < tiles per SM <= 4)
+    tma = tma is True
     e2.pipeline.tma_staging = tma
+    e2.pipeline.single_pass = single
     u = synth.random_uniforms(n, gen)
     steps = 7
     for t in range(steps):
@@ -135,7 +146,7 @@ def test_v2_equals_tile_kernel_bitwise(task, n, tma):
                 e.pipeline.post_step()
         if t > 0:
             kernel = L.load().dex_debug_last_post_kernel()  # of e2's launch
-            assert kernel == 3 if tma else kernel in (1, 2), kernel
+            assert kernel == (3 if tma else 2 if single else 1), kernel
         torch.cuda.synchronize()
         p1, p2 = e1.pipeline, e2.pipeline
         for k in BUFS_OUT:

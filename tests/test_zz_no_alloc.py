@@ -29,7 +29,7 @@ def _twins(task, n, obs_dict):
     return lay, envs
 
 
-def _noalloc_post(p, n_envs=None):
+def _noalloc_post(p, n_envs=None):  # (honours p.single_pass like StepPipeline.post_physics does)
     """One dex_post_physics_noalloc call with the pipeline's own buffers; tile_records is NOT passed."""
     from dexrobot_isaac_b200 import _lib as L
 
@@ -38,7 +38,8 @@ def _noalloc_post(p, n_envs=None):
     ep.tile_records = None
     rc = p.lib.dex_post_physics_noalloc(ctypes.byref(p.params), ctypes.byref(p._sim), ctypes.byref(p._state),
                                         ctypes.byref(p._out), ctypes.byref(ep), p.n if n_envs is None else n_envs,
-                                        L.CONSTS["DEX_MODE_FULL"], 0, None, p.seed, p.host_step, p._stream())
+                                        L.CONSTS["DEX_MODE_FULL"], L.CONSTS["DEX_FLAG_SINGLE_PASS"] if p.single_pass else 0, None,
+                                        p.seed, p.host_step, p._stream())
     if rc == 0:
         p.host_step += 1
     return rc
@@ -60,8 +61,9 @@ def _same(p1, p2, tag):
     assert torch.equal(ids, torch.nonzero(p1.out["reset_buf"]).flatten()), f"{tag} env_ids vs reset_buf"
 
 
-def _compare(task, n, steps, obs_dict, seed):
+def _compare(task, n, steps, obs_dict, seed, single_pass=False):
     lay, (e1, e2) = _twins(task, n, obs_dict)
+    e1.pipeline.single_pass = e2.pipeline.single_pass = single_pass
     gen = torch.Generator().manual_seed(seed)
     u = synth.random_uniforms(n, gen)
     st = synth.random_state(n, lay, gen, ground_frac=0.03)
@@ -89,12 +91,14 @@ def _compare(task, n, steps, obs_dict, seed):
     return e2
 
 
-@pytest.mark.parametrize("task,n,obs_dict", [("BlindGrasping", 16384, False), ("BaseTask", 5000, False),
-                                             ("BlindGrasping", 1000, True), ("BlindGrasping", 262144, False)],
-                         ids=["single_pass_16384", "persistent_ragged_5000", "tile_kernel_obs_dict_1000", "capacity_262144"])
-def test_noalloc_equals_existing_entry_point(task, n, obs_dict):
+@pytest.mark.parametrize("task,n,obs_dict,single", [("BlindGrasping", 16384, False, True), ("BlindGrasping", 16384, False, False),
+                                                    ("BaseTask", 5000, False, False), ("BlindGrasping", 1000, True, False),
+                                                    ("BlindGrasping", 262144, False, False)],
+                         ids=["single_pass_16384", "persistent_16384", "persistent_ragged_5000", "tile_kernel_obs_dict_1000",
+                              "capacity_262144"])
+def test_noalloc_equals_existing_entry_point(task, n, obs_dict, single):
     """Every kernel family behind dex_post_physics, 4 calls in a row (the capacity case 2), bit for bit."""
-    _compare(task, n, 2 if n > 100000 else 4, obs_dict, seed=41)
+    _compare(task, n, 2 if n > 100000 else 4, obs_dict, seed=41, single_pass=single)
 
 
 def test_noalloc_shared_scratch_keeps_no_stale_records():

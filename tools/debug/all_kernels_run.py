@@ -22,6 +22,7 @@ for task, n, dict_, observer, tma in (("BlindGrasping", 77, True, True, False), 
     env = DexStepEnv(load_task_config(task, num_envs=n), n, BodyLayout.from_synth(lay), synth.dof_props_tensor(), device=DEV,
                      materialize_obs_dict=dict_, observer=observer)
     env.pipeline.tma_staging = tma
+    env.pipeline.single_pass = n == 9472
     gen = torch.Generator().manual_seed(1)
     env.load_state(synth.random_state(n, lay, gen))
     env.reset(synth.random_uniforms(n, gen))

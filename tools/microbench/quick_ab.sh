@@ -10,7 +10,7 @@ for l in sys.stdin:
 "
 }
 run "X=1" ""
-run "DEXSTEP_POST_GEOMETRY=persistent" ""
+run "DEXSTEP_POST_GEOMETRY=single" ""
 run "X=1" "--observer 1"
 run "X=1" "--workload blindgrasping_4096"
 run "X=1" "--workload basetask_4096"

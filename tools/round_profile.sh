@@ -15,7 +15,7 @@ python bench.py --observer 1 --no-cpu-baseline > $o/${tag}_bench_observer.json 2
 python bench.py --obs-norm 1 --no-cpu-baseline > $o/${tag}_bench_obs_norm.json 2>> $o/${tag}_bench.err
 python bench.py --nb-hand 37 --no-cpu-baseline > $o/${tag}_bench_nb37.json 2>> $o/${tag}_bench.err
 DEXSTEP_EARLY_SIM_LOADS=0 python bench.py --no-cpu-baseline > $o/${tag}_bench_no_early_sim_loads.json 2>> $o/${tag}_bench.err
-DEXSTEP_POST_GEOMETRY=persistent python bench.py --no-cpu-baseline > $o/${tag}_bench_persistent.json 2>> $o/${tag}_bench.err
+python bench.py --single-pass --no-cpu-baseline > $o/${tag}_bench_single_pass.json 2>> $o/${tag}_bench.err
 python bench.py --tile-kernel --no-cpu-baseline > $o/${tag}_bench_tile_kernel.json 2>> $o/${tag}_bench.err
 # ---- ncu: launch list (gpu__time_duration) of the default command, then full captures ----
 # (only this library's kernels: the set-up of the bench launches thousands of torch fill / copy kernels first)
@@ -25,6 +25,6 @@ ncu --set full --clock-control none --import-source on -k regex:post_physics -s 
     python bench.py --steps 20 --warmup 3 --no-cpu-baseline > $o/${tag}_ncu_post.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:pre_physics -s 30 -c 1 -o $o/${tag}_pre -f \
     python bench.py --steps 20 --warmup 3 --no-cpu-baseline > $o/${tag}_ncu_pre.log 2>&1
-DEXSTEP_POST_GEOMETRY=persistent ncu --set full --clock-control none --import-source on -k regex:post_physics -s 30 -c 1 \
-    -o $o/${tag}_post_persistent -f python bench.py --steps 20 --warmup 3 --no-cpu-baseline > $o/${tag}_ncu_post_persistent.log 2>&1
+DEXSTEP_POST_GEOMETRY=single ncu --set full --clock-control none --import-source on -k regex:post_physics -s 30 -c 1 \
+    -o $o/${tag}_post_single_pass -f python bench.py --steps 20 --warmup 3 --no-cpu-baseline > $o/${tag}_ncu_post_single_pass.log 2>&1
 ls -la $o | tail -30
