@@ -2,15 +2,18 @@
 //
 // Same arithmetic as post_physics.cuh (StepProcessor.process_physics_step, step_processor.py:37-131), op for op (that
 // file is pinned to the oracle and kept for the obs_dict / OBS_ONLY / stale-contact instances); different machine
-// mapping.  Two geometries, chosen per launch by the number of 32-env tiles (launch_post2_t):
+// mapping.  Two geometries (launch_post2_t):
 //
-//   post_physics_v2_kernel  PERSISTENT, warp-specialised: <= SMs x CTAs/SM worker CTAs (+ one epilogue CTA) loop over
-//     tiles; 4 producer warps stream tile t+1 into a 2-stage shared-memory ring (mbarrier full/empty pairs) while 8
+//   post_physics_v2_kernel  PERSISTENT, warp-specialised, the default: <= SMs x CTAs/SM worker CTAs (+ one epilogue CTA) loop
+//     over tiles; 4 producer warps stream tile t+1 into a 2-stage shared-memory ring (mbarrier full/empty pairs) while 8
 //     consumer warps compute tile t.  All CTAs are co-resident, so the epilogue CTA's poll of the tile records needs no
-//     scheduling-order assumption.  Used for <= 2 and > 4 tiles per SM.
-//   post_physics_v2s_kernel SINGLE PASS: one tile per CTA, 8 warps, 4 CTAs per SM, loads staged through registers, the
-//     work block aliased into the stage (Lay<BG, true>) so that four CTAs fit.  Used for 2 < tiles/SM <= 4 (16 384 envs
-//     on 148 SMs = 3.46 tiles per SM), where a persistent grid would leave half of the SMs a third round.
+//     scheduling-order assumption.
+//   post_physics_v2s_kernel SINGLE PASS, on request (DEX_FLAG_SINGLE_PASS) for 2 < tiles/SM <= 4 (16 384 envs on 148 SMs =
+//     3.46 tiles per SM): one tile per CTA, 8 warps, 4 CTAs per SM, loads staged through registers, the work block aliased
+//     into the stage (Lay<BG, true>) so that four CTAs fit.  3-5 % slower than the persistent kernel when the inputs come
+//     from HBM, 20 % faster when the sim tensors are still in L2.
+//   Template flags: STD = compile-time standard observation layout, TMA = tensor-copy producers (DEX_FLAG_TMA_STAGING, measured
+//     slower), OBS = fused RewardComponentObserver (a separate instance: even dormant observer code costs the lean path 1-4 %).
 //
 // What shaped them (profiles/r02_variants.md has the measurements of the variants that did NOT work):
 //   * The path is bound by INSTRUCTION SUPPLY for cold code, not by bytes or issue slots: every CTA runs ~10 K distinct
