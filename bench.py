@@ -649,16 +649,21 @@ def main():
     # ---- end to end through DexStepEnv.step_host (host buffers, copies inside the timed region) ----
     ke = max(2, min(args.steps, 200))
     sampler.start()
-    ems, h2d, d2h = run_e2e(ring, ke, device, barrier, compact=True)
+    ems, h2d, d2h = run_e2e(ring, ke, device, barrier, compact="packed")
     sampler.stop()
+    cms, ch2d, cd2h = run_e2e(ring, ke, device, barrier, compact=True)
     fms, fh2d, fd2h = run_e2e(ring, ke, device, barrier, compact=False)
     if world > 1:
-        t = torch.tensor([ems, fms], device=device, dtype=torch.float64)
+        t = torch.tensor([ems, cms, fms], device=device, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ems, fms = (float(x) for x in t.tolist())
+        ems, cms, fms = (float(x) for x in t.tolist())
     e2e = {"value": n_env * world * ke / (ems * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
            "d2h_bytes_per_step": d2h, "steps": ke, "ms_per_step": ems / ke,
-           "api": "DexStepEnv.step_host, compact host staging (the 12 monitored body rows per env; pinned, 2 streams)",
+           "api": "DexStepEnv.step_host, packed host staging (only what the path reads: dof_state, the hand row, 10 tip / pad "
+                  "poses as 7-float slots, the monitored contact rows, the box row, actions; pinned, 2 streams)",
+           "compact_rows_layout": {"value": n_env * world * ke / (cms * 1e-3), "h2d_bytes_per_step": ch2d,
+                                   "d2h_bytes_per_step": cd2h, "ms_per_step": cms / ke,
+                                   "api": "DexStepEnv.step_host, the monitored body rows shipped whole (13 floats each)"},
            "full_tensor_layout": {"value": n_env * world * ke / (fms * 1e-3), "h2d_bytes_per_step": fh2d,
                                   "d2h_bytes_per_step": fd2h, "ms_per_step": fms / ke,
                                   "api": "DexStepEnv.step_host, whole Isaac Gym tensors shipped"}}

@@ -335,6 +335,10 @@ int check_params(const DexParams* p) {
   auto body_ok = [&](int b) { return b >= 0 && b < p->num_bodies; };
   auto cbody_ok = [&](int b) { return b >= 0 && b < p->num_contact_bodies; };
   if (!body_ok(p->hand_body)) return DEX_ERR_PARAM;
+  if (p->rigid_row_floats != 0) {  // packed host staging: rows of 7..13 floats, the 13-float hand row must end inside its env
+    const int rw = p->rigid_row_floats;
+    if (rw < 7 || rw > 13 || p->hand_body * rw + 13 > p->num_bodies * rw) return DEX_ERR_PARAM;
+  }
   for (int f = 0; f < DEX_NUM_FINGERS; ++f)
     if (!body_ok(p->tip_body[f]) || !body_ok(p->pad_body[f]) || !cbody_ok(p->contact_body[f])) return DEX_ERR_PARAM;
   if (p->task == DEX_TASK_BLIND_GRASPING) {

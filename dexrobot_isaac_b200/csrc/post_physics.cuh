@@ -128,6 +128,7 @@ struct PostArgs {
   int32_t n_out_early, n_out_f32, n_out_i64, n_out;
   uint32_t obs_late, dict_late;         // bit c: columns [32c, 32c+32) read a slot that the scalar phase writes
   int32_t rb_off[11];                   // float offset of the hand / 5 tip / 5 pad rows inside one env's [NB,13] slab
+  int32_t rb_pitch;                     // floats of one env in rigid_body_state (NB * DexParams.rigid_row_floats)
   int32_t cf_off[6];                    // float offset of the 5 monitored contact rows (+ box) inside [NB,3]
   uint64_t in_ptr[kMaxIn];              // row base pointers
   uint16_t in_meta[kMaxIn];             // slab slot
@@ -231,10 +232,12 @@ inline int build_post_tables(PostArgs& a) {
   a.stride = o | 1;
   if (a.stride >= 4096) return DEX_ERR_SIZE;
 
-  a.rb_off[0] = P.hand_body * 13;
+  const int rw = P.rigid_row_floats > 0 ? P.rigid_row_floats : 13;  // 13 = Isaac Gym rows, 7..12 = packed host staging
+  a.rb_pitch = P.num_bodies * rw;
+  a.rb_off[0] = P.hand_body * rw;
   for (int f = 0; f < DEX_NUM_FINGERS; ++f) {
-    a.rb_off[1 + f] = P.tip_body[f] * 13;
-    a.rb_off[6 + f] = P.pad_body[f] * 13;
+    a.rb_off[1 + f] = P.tip_body[f] * rw;
+    a.rb_off[6 + f] = P.pad_body[f] * rw;
     a.cf_off[f] = P.contact_body[f] * 3;
   }
   a.cf_off[5] = bg ? P.box_body * 3 : 0;
@@ -480,7 +483,6 @@ __device__ __forceinline__ void post_stage_in(const PostArgs& A, float* smem, co
 
   // ---- AoS sim rows: warps take env rows round-robin (4 each), consecutive lanes = consecutive floats ----
   {
-    const int nb = P.num_bodies;
     auto rbo = [&](int s) {  // rigid slot (0..82) -> float offset inside the env's [NB,13] slab
       s = min(s, kRbW - 1);
       const int row = s < 13 ? 0 : 1 + (s - 13) / 7;
@@ -506,9 +508,9 @@ __device__ __forceinline__ void post_stage_in(const PostArgs& A, float* smem, co
     }
     const float* gx = (is_box ? A.sim.actor_root_state : A.sim.net_contact_force) + (size_t)(e0 + warp) * xrow + xoff;
     const float* g_dof = A.sim.dof_state + (size_t)(e0 + warp) * (2 * DEX_NUM_DOF) + lane;
-    const float* g_rb = A.sim.rigid_body_state + (size_t)(e0 + warp) * nb * 13;
+    const float* g_rb = A.sim.rigid_body_state + (size_t)(e0 + warp) * A.rb_pitch;
     const float* g_tgt = A.st.full_dof_targets + (size_t)(e0 + warp) * DEX_NUM_DOF + lane;
-    const unsigned rb_step = kPostWarps * nb * 13, x_step = kPostWarps * xrow;
+    const unsigned rb_step = kPostWarps * A.rb_pitch, x_step = kPostWarps * xrow;
     constexpr int R = kTile / kPostWarps;  // env rows per warp
     // ---- the Isaac Gym sim rows (80 % of the tile's bytes) go first.  With DEX_FLAG_EARLY_SIM_LOADS they are issued
     // BEFORE griddepcontrol.wait: the kernel ahead in the stream (dex_pre_physics of the same step) does not write

@@ -172,6 +172,7 @@ struct Post2Args {
   uint32_t obs_late;                      // bit c: obs columns [32c, 32c+32) hold a value that phase B writes
   uint32_t smem_bytes;
   int32_t rb_off[11], cf_off[6];
+  int32_t rb_pitch;                       // floats of one env in rigid_body_state (NB * DexParams.rigid_row_floats)
   int32_t dof2afj[DEX_NUM_DOF];           // dof -> index in active_finger_dof, -1 = not an active finger DOF
   // ---- TMA staging of the persistent kernel (build_tma): one copy per lane of producer warp 0 and tile ----
   int32_t tma;                            // 1: tensor copies instead of LDGSTS gathers
@@ -235,10 +236,12 @@ inline int build_post2(Post2Args& a) {
     for (int i = 0; i < 10; ++i)
       if (BG && has(late_keys[i])) a.obs_late |= 1u << (P.obs_offset[late_keys[i]] >> 5);
   }
-  a.rb_off[0] = P.hand_body * 13;
+  const int rw = P.rigid_row_floats > 0 ? P.rigid_row_floats : 13;  // 13 = Isaac Gym rows, 7..12 = packed host staging
+  a.rb_pitch = P.num_bodies * rw;
+  a.rb_off[0] = P.hand_body * rw;
   for (int f = 0; f < DEX_NUM_FINGERS; ++f) {
-    a.rb_off[1 + f] = P.tip_body[f] * 13;
-    a.rb_off[6 + f] = P.pad_body[f] * 13;
+    a.rb_off[1 + f] = P.tip_body[f] * rw;
+    a.rb_off[6 + f] = P.pad_body[f] * rw;
     a.cf_off[f] = P.contact_body[f] * 3;
   }
   a.cf_off[5] = BG ? P.box_body * 3 : 0;
@@ -363,7 +366,7 @@ inline void build_tma(Post2Args& a) {
   const DexParams& P = a.p;
   const DexStateBuffers& st = a.st;
   const int N = a.n, NB = P.num_bodies, NC = P.num_contact_bodies, NA = P.num_actors;
-  if (!allow || N % 32 != 0 || NB % 4 != 0 || NC % 4 != 0 || NA % 2 != 0 || !a.bulk_ok) return;
+  if (!allow || (P.rigid_row_floats != 0 && P.rigid_row_floats != 13) || N % 32 != 0 || NB % 4 != 0 || NC % 4 != 0 || NA % 2 != 0 || !a.bulk_ok) return;
   const void* bases[] = {a.sim.rigid_body_state, a.sim.net_contact_force, a.sim.actor_root_state, a.sim.dof_state,
                          st.prev_dof_pos, st.active_prev_targets, st.prev_actions, st.contact_duration_steps,
                          st.prev_contact_binary, st.initial_box_positions, st.time_in_stage, st.stage_contact_duration,
@@ -1380,7 +1383,7 @@ __device__ __forceinline__ void issue_tile_loads(const Post2Args& A, const LoadC
   aos_tile(A.sim.dof_state, 52, LY::OFF_DOF);
   // ---- scattered Isaac Gym rows: warp pw takes env rows pw, pw+NW, ..; consecutive lanes = consecutive floats ----
   {
-    const size_t nb13 = (size_t)A.p.num_bodies * 13;
+    const size_t nb13 = (size_t)A.rb_pitch;
     const float* q0 = A.sim.rigid_body_state + (size_t)(e0 + pw) * nb13;
     const float* qx = lc.x_base + (size_t)(e0 + pw) * lc.xrow;
     uint32_t a = sst + LY::OFF_AOS + (uint32_t)(pw * LY::SA + lane) * 4u;
@@ -1479,7 +1482,7 @@ __device__ __forceinline__ void load_tile_regs(const Post2Args& A, const LoadCtx
   // scattered Isaac Gym rows: warp w takes env rows w, w+8, w+16, w+24
   float g[4][4];
   {
-    const size_t nb13 = (size_t)A.p.num_bodies * 13;
+    const size_t nb13 = (size_t)A.rb_pitch;
     const float* q0 = A.sim.rigid_body_state + (size_t)(e0 + w) * nb13;
     const float* qx = lc.x_base + (size_t)(e0 + w) * lc.xrow;
 #pragma unroll

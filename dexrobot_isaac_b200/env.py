@@ -170,7 +170,7 @@ class DexStepEnv:
         return self.pipeline.out.get("obs_norm")
 
     # ------------------------------------------------------------------ host-buffer entry (end-to-end path)
-    def alloc_host_buffers(self, compact: bool = False):
+    def alloc_host_buffers(self, compact=False):
         """Pinned host mirrors of one step's inputs (sim tensors + actions) and results (obs, rew, reset).
 
         ``compact=False``: the four Isaac Gym tensors as they are (2 432 B/env for BlindGrasping with 32 bodies).
@@ -178,13 +178,18 @@ class DexStepEnv:
         [N,11,13] (hand, 5 tips, 5 pads), net_contact_force [N,6,3] (5 monitored bodies, box), actor_root_state
         [N,1,13] (box), dof_state [N,26,2] - 904 B/env.  The body indices are run-time parameters of the kernels, so the
         same kernels run on the compact device mirrors (``BodyLayout.compact()``); a host-side simulator fills the
-        compact buffers directly, ``fill_host_inputs`` gathers them from full tensors."""
+        compact buffers directly, ``fill_host_inputs`` gathers them from full tensors.
+        ``compact="packed"``: as above with the rigid rows cut to the floats the path reads (``DexParams.rigid_row_floats``
+        = 7): rigid_body_state [N,12,7] - the 13-float hand row in slots 0-1, tip and pad poses (pos3 + quat4) in slots
+        2-11 - 668 B/env."""
         p = self.pipeline
         pin = lambda *shape, dtype=torch.float32: torch.empty(*shape, dtype=dtype, pin_memory=True)  # noqa: E731
         n = self.num_envs
         if compact:
-            lay = self._full_layout().compact()
-            inputs = {"dof_state": pin(n, 26, 2), "rigid_body_state": pin(n, lay.num_bodies, 13),
+            if compact not in (True, "packed"):
+                raise ValueError(f"compact must be False, True or 'packed', not {compact!r}")
+            lay = self._full_layout().compact(packed=compact == "packed")
+            inputs = {"dof_state": pin(n, 26, 2), "rigid_body_state": pin(n, lay.num_bodies, lay.rigid_row_floats),
                       "net_contact_force": pin(n, lay.contact_rows, 3), "actor_root_state": pin(n, lay.num_actors, 13)}
         else:
             inputs = {k: pin(*v.shape) for k, v in self._full_sim().items()}
@@ -211,7 +216,13 @@ class DexStepEnv:
             rigid, contact, actors = lay.compact_gather_indices()
             n = self.num_envs
             host_inputs["dof_state"].copy_(full["dof_state"].view(n, 26, 2))
-            host_inputs["rigid_body_state"].copy_(full["rigid_body_state"].view(n, lay.num_bodies, 13)[:, rigid])
+            rows = full["rigid_body_state"].view(n, lay.num_bodies, 13)[:, rigid]
+            dst = host_inputs["rigid_body_state"]
+            if dst.shape[2] == 13:
+                dst.copy_(rows)
+            else:  # packed: hand row (13 floats) in slots 0-1, the 10 poses behind it
+                dst[:, 0:2].view(n, 14)[:, :13].copy_(rows[:, 0])
+                dst[:, 2:].copy_(rows[:, 1:, :7])
             host_inputs["net_contact_force"].copy_(full["net_contact_force"].view(n, lay.contact_rows, 3)[:, contact])
             host_inputs["actor_root_state"].copy_(full["actor_root_state"].view(n, lay.num_actors, 13)[:, actors])
         host_inputs["actions"].copy_(actions)
@@ -223,16 +234,17 @@ class DexStepEnv:
         switches the pipeline to device mirrors of that layout (``end_host_mode`` switches back).
         Returns (h2d_bytes, d2h_bytes)."""
         p = self.pipeline
-        compact = host_inputs["rigid_body_state"].shape[1] != self._full_layout().num_bodies
-        if compact != (getattr(self, "_host_saved", None) is not None):
-            if compact:
+        shape = tuple(host_inputs["rigid_body_state"].shape[1:])
+        mode = 0 if shape == (self._full_layout().num_bodies, 13) else 2 if shape[1] == 7 else 1
+        if mode != getattr(self, "_host_mode", 0):
+            self.end_host_mode()
+            if mode:
                 self._host_saved = (self.layout, dict(p.sim_tensors))
-                lay = self.layout.compact()
+                self._host_mode = mode
+                lay = self.layout.compact(packed=mode == 2)
                 dev = {k: torch.empty(v.shape, dtype=v.dtype, device=self.device)
                        for k, v in host_inputs.items() if k != "actions"}
                 p.use_layout(lay, dev)
-            else:
-                self.end_host_mode()
         h2d = d2h = 0
         for k, dst in p.sim_tensors.items():
             dst.copy_(host_inputs[k].view(dst.shape), non_blocking=True)
@@ -252,6 +264,7 @@ class DexStepEnv:
             torch.cuda.synchronize(self.device)
             self.pipeline.use_layout(*saved)
             self._host_saved = None
+            self._host_mode = 0
 
     # ------------------------------------------------------------------ extras (step_processor.py:221-232)
     def _update_extras(self):

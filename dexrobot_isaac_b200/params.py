@@ -97,20 +97,27 @@ class BodyLayout:
     box_actor: int = -1
     body_names: Dict[int, str] = field(default_factory=dict)
     num_contact_bodies: int = 0  # bodies per env in net_contact_force (0 = num_bodies, the Isaac Gym tensors)
+    rigid_row_floats: int = 13   # floats per body row of rigid_body_state (13 = Isaac Gym; 7 = packed host staging)
 
     @property
     def contact_rows(self) -> int:
         return self.num_contact_bodies or self.num_bodies
 
-    def compact(self) -> "BodyLayout":
+    def compact(self, packed: bool = False) -> "BodyLayout":
         """The host-staging layout that ships only the rows the path reads (DexStepEnv.alloc_host_buffers(compact=True)):
         rigid_body_state rows [hand, 5 tips, 5 pads], net_contact_force rows [5 monitored bodies (, box)],
-        actor_root_state row [box] (or the hand actor when there is no box)."""
+        actor_root_state row [box] (or the hand actor when there is no box).
+
+        ``packed``: the rigid rows additionally shrink to what the path reads of them - 7-float slots (DexParams.
+        rigid_row_floats = 7): the 13-float hand row takes slots 0-1, the tip / pad poses (pos3 + quat4) slots 2-6 / 7-11,
+        [N,12,7] = 336 B per env instead of 572."""
         has_box = self.box_body >= 0
-        return BodyLayout(num_bodies=11, num_actors=1, hand_body=0, tip_bodies=[1 + f for f in range(NUM_FINGERS)],
-                          pad_bodies=[6 + f for f in range(NUM_FINGERS)], contact_bodies=list(range(NUM_FINGERS)),
+        first = 2 if packed else 1
+        return BodyLayout(num_bodies=first + 10, num_actors=1, hand_body=0,
+                          tip_bodies=[first + f for f in range(NUM_FINGERS)],
+                          pad_bodies=[first + 5 + f for f in range(NUM_FINGERS)], contact_bodies=list(range(NUM_FINGERS)),
                           box_body=5 if has_box else -1, box_actor=0 if has_box else -1,
-                          num_contact_bodies=6 if has_box else 5)
+                          num_contact_bodies=6 if has_box else 5, rigid_row_floats=7 if packed else 13)
 
     def compact_gather_indices(self):
         """-> (rigid rows, contact rows, actor rows) of THIS layout that make up the compact layout, in its order."""
@@ -224,6 +231,7 @@ def make_params(cfg: dict, layout: BodyLayout, dof_lower: Sequence[float], dof_u
     P.task = C["DEX_TASK_BLIND_GRASPING"] if is_bg else C["DEX_TASK_BASE"]
     P.num_bodies, P.num_actors, P.hand_body = layout.num_bodies, layout.num_actors, layout.hand_body
     P.num_contact_bodies = layout.contact_rows
+    P.rigid_row_floats = layout.rigid_row_floats
     for f in range(NUM_FINGERS):
         P.tip_body[f], P.pad_body[f], P.contact_body[f] = (layout.tip_bodies[f], layout.pad_bodies[f],
                                                            layout.contact_bodies[f])

@@ -81,7 +81,7 @@ class StepPipeline:
         self.sim_tensors: Dict[str, torch.Tensor] = {}
         self._sim = L.DexSimViews()
         self.bind_sim(sim or {
-            "dof_state": z(n, NUM_DOF, 2), "rigid_body_state": z(n, layout.num_bodies, 13),
+            "dof_state": z(n, NUM_DOF, 2), "rigid_body_state": z(n, layout.num_bodies, layout.rigid_row_floats),
             "net_contact_force": z(n, layout.contact_rows, 3), "actor_root_state": z(n, layout.num_actors, 13)})
 
         # ---- persistent state, SoA [K,N] ----
@@ -222,7 +222,7 @@ class StepPipeline:
         """Point the kernels at the caller's sim tensors.  With Isaac Gym these are the
         gymtorch.wrap_tensor views (tensor_manager.py:173-328): no copy is ever made."""
         n, lay = self.n, self.layout
-        want = {"dof_state": n * NUM_DOF * 2, "rigid_body_state": n * lay.num_bodies * 13,
+        want = {"dof_state": n * NUM_DOF * 2, "rigid_body_state": n * lay.num_bodies * lay.rigid_row_floats,
                 "net_contact_force": n * lay.contact_rows * 3, "actor_root_state": n * lay.num_actors * 13}
         for k, numel in want.items():
             t = sim.get(k)
@@ -241,7 +241,7 @@ class StepPipeline:
         switch back.  Everything else in the parameter block is unchanged; a captured graph is invalidated."""
         P = self.params
         P.num_bodies, P.num_contact_bodies, P.num_actors = layout.num_bodies, layout.contact_rows, layout.num_actors
-        P.hand_body = layout.hand_body
+        P.hand_body, P.rigid_row_floats = layout.hand_body, layout.rigid_row_floats
         for f in range(NUM_FINGERS):
             P.tip_body[f], P.pad_body[f], P.contact_body[f] = (layout.tip_bodies[f], layout.pad_bodies[f],
                                                                layout.contact_bodies[f])

@@ -62,7 +62,7 @@
 extern "C" {
 #endif
 
-#define DEX_ABI_VERSION 10
+#define DEX_ABI_VERSION 11
 
 #define DEX_NUM_DOF 26          /* constants.py:8-10: 6 base + 20 finger DOFs */
 #define DEX_NUM_BASE 6
@@ -180,7 +180,7 @@ typedef struct DexParams {
   int32_t abi_version;            /* must be DEX_ABI_VERSION */
   int32_t task;                   /* DEX_TASK_* */
   /* --- layout of the sim buffers (hand_initializer.py:439-560, blind_grasping_task.py:388-419) --- */
-  int32_t num_bodies;             /* NB: rigid bodies per env = row pitch of rigid_body_state */
+  int32_t num_bodies;             /* NB: rigid bodies per env; one env of rigid_body_state is NB * rigid_row_floats floats */
   int32_t num_contact_bodies;     /* bodies per env in net_contact_force (its row pitch; contact_body[] and box_body index it).
                                      Equal to num_bodies for the Isaac Gym tensors; smaller for a compact host-staging layout
                                      that ships only the monitored rows (DexStepEnv.alloc_host_buffers(compact=True)) */
@@ -251,6 +251,14 @@ typedef struct DexParams {
   float lift_height_range;         /* success_height_threshold - box_z (double, then narrowed) */
   float half_pi;                   /* (float)(pi/2) */
   float pi;                        /* (float)pi */
+  /* --- packed host staging (no counterpart in the reference; 0 or 13 = the Isaac Gym tensor) --- */
+  int32_t rigid_row_floats;        /* floats between consecutive body rows of rigid_body_state: body b starts at float
+                                      b * rigid_row_floats of its env.  13 (or 0) for Isaac Gym's [N,NB,13].  7..12 for a
+                                      host-staging buffer that ships poses only (pos3 + quat4 per tip / pad row,
+                                      DexStepEnv.alloc_host_buffers(compact="packed")): the path reads 7 floats of every tip /
+                                      pad row and 13 of the hand row (7 when no common reward term is weighted), so with 7 the
+                                      hand takes two consecutive slots.  hand_body * rigid_row_floats + 13 must stay inside
+                                      the env's NB * rigid_row_floats floats.  Not with DEX_FLAG_TMA_STAGING (ignored there). */
 } DexParams;
 
 /* Isaac Gym tensor-API buffers, zero-copy (tensor_manager.py:173-328). */
