@@ -442,31 +442,34 @@ def eager_gpu_reference(task, n, device, steps=12):
 # ------------------------------------------------------------------------------------------------
 def run_e2e(ring, steps, device, barrier, compact=False):
     envs = ring.envs[:2]
-    bufs = [e.alloc_host_buffers(compact=compact) for e in envs]
+    # the pinned staging buffers go to the GPU's own NUMA node (first touch under a temporary CPU binding; multi-GPU runs
+    # are bound for good in main()): where they land otherwise changes from run to run, and the copy rates with it
+    before = os.sched_getaffinity(0)
+    bind_to_gpu_numa_node(device)
+    try:
+        bufs = [e.alloc_host_buffers(compact=compact) for e in envs]
+    finally:
+        os.sched_setaffinity(0, before)
     for e, a, (hin, _) in zip(envs, ring.actions, bufs):
         e.fill_host_inputs(hin, a)
-    streams = [torch.cuda.Stream(device) for _ in envs]
     main = torch.cuda.current_stream(device)
     h2d = d2h = 0
 
-    def loop(k):
+    def loop(k):  # step_host pipelines uploads, kernels and downloads over its own copy streams
         nonlocal h2d, d2h
         for i in range(k):
             j = i % len(envs)
-            with torch.cuda.stream(streams[j]):
-                h2d, d2h = envs[j].step_host(*bufs[j])
+            h2d, d2h = envs[j].step_host(*bufs[j])
 
-    loop(4)
+    loop(20)
     torch.cuda.synchronize(device)
     if barrier is not None:
         barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(main)
-    for s in streams:
-        s.wait_event(e0)
     loop(steps)
-    for s in streams:
-        main.wait_stream(s)
+    for e in envs:
+        e.host_sync()  # the downloads run on the download stream
     e1.record(main)
     torch.cuda.synchronize(device)
     if barrier is not None:
@@ -529,7 +532,7 @@ def main():
         raise RuntimeError("bench.py needs a CUDA device: the step pipeline has no CPU fallback")
     device = torch.device("cuda", local)
     torch.cuda.set_device(device)
-    numa_note = bind_to_gpu_numa_node(device) if world > 1 else None
+    numa_note = bind_to_gpu_numa_node(device) if world > 1 else "staging buffers allocated under a temporary binding to the gpu's local cpus"
     barrier = None
     if world > 1:
         import torch.distributed as dist
@@ -648,9 +651,7 @@ def main():
 
     # ---- end to end through DexStepEnv.step_host (host buffers, copies inside the timed region) ----
     ke = max(2, min(args.steps, 200))
-    sampler.start()
     ems, h2d, d2h = run_e2e(ring, ke, device, barrier, compact="packed")
-    sampler.stop()
     cms, ch2d, cd2h = run_e2e(ring, ke, device, barrier, compact=True)
     fms, fh2d, fd2h = run_e2e(ring, ke, device, barrier, compact=False)
     if world > 1:
@@ -660,7 +661,7 @@ def main():
     e2e = {"value": n_env * world * ke / (ems * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
            "d2h_bytes_per_step": d2h, "steps": ke, "ms_per_step": ems / ke,
            "api": "DexStepEnv.step_host, packed host staging (only what the path reads: dof_state, the hand row, 10 tip / pad "
-                  "poses as 7-float slots, the monitored contact rows, the box row, actions; pinned, 2 streams)",
+                  "poses as 7-float slots, the monitored contact rows, the box row, actions; one pinned block and one copy per direction; uploads, kernels and downloads on three streams)",
            "compact_rows_layout": {"value": n_env * world * ke / (cms * 1e-3), "h2d_bytes_per_step": ch2d,
                                    "d2h_bytes_per_step": cd2h, "ms_per_step": cms / ke,
                                    "api": "DexStepEnv.step_host, the monitored body rows shipped whole (13 floats each)"},

@@ -21,9 +21,21 @@ import torch
 
 from . import _lib as L
 from .params import BodyLayout
-from .pipeline import (FLAG_STALE_CONTACTS, MODE_FULL, MODE_OBS_ONLY, NUM_UNIFORMS, StepPipeline)
+from .pipeline import (FLAG_STALE_CONTACTS, MODE_FULL, MODE_OBS_ONLY, NUM_UNIFORMS, StepPipeline, carve_block,
+                       result_segments)
 
 C = L.CONSTS
+
+
+_COPY_STREAMS: Dict[int, tuple] = {}
+
+
+def _copy_streams(device: torch.device):
+    """One upload and one download stream per device, shared by every env on it (DexStepEnv.step_host)."""
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    if idx not in _COPY_STREAMS:
+        _COPY_STREAMS[idx] = (torch.cuda.Stream(device), torch.cuda.Stream(device))
+    return _COPY_STREAMS[idx]
 
 
 class DexStepEnv:
@@ -181,21 +193,26 @@ class DexStepEnv:
         compact buffers directly, ``fill_host_inputs`` gathers them from full tensors.
         ``compact="packed"``: as above with the rigid rows cut to the floats the path reads (``DexParams.rigid_row_floats``
         = 7): rigid_body_state [N,12,7] - the 13-float hand row in slots 0-1, tip and pad poses (pos3 + quat4) in slots
-        2-11 - 668 B/env."""
-        p = self.pipeline
-        pin = lambda *shape, dtype=torch.float32: torch.empty(*shape, dtype=dtype, pin_memory=True)  # noqa: E731
+        2-11 - 668 B/env.
+
+        Every tensor of ``inputs`` is a view of ONE pinned allocation (``inputs["_block"]``), likewise ``outputs``:
+        ``step_host`` then moves a step with one copy per direction (on the bench box 20 % faster than one copy per
+        tensor when both directions are busy, tools/microbench/pcie_duplex.py)."""
+        if compact not in (False, True, "packed"):
+            raise ValueError(f"compact must be False, True or 'packed', not {compact!r}")
         n = self.num_envs
-        if compact:
-            if compact not in (True, "packed"):
-                raise ValueError(f"compact must be False, True or 'packed', not {compact!r}")
-            lay = self._full_layout().compact(packed=compact == "packed")
-            inputs = {"dof_state": pin(n, 26, 2), "rigid_body_state": pin(n, lay.num_bodies, lay.rigid_row_floats),
-                      "net_contact_force": pin(n, lay.contact_rows, 3), "actor_root_state": pin(n, lay.num_actors, 13)}
-        else:
-            inputs = {k: pin(*v.shape) for k, v in self._full_sim().items()}
-        inputs["actions"] = pin(n, self.num_actions)
-        outputs = {"obs_buf": pin(*self.obs_buf.shape), "rew_buf": pin(n), "reset_buf": pin(n, dtype=torch.bool)}
+        lay = self._full_layout().compact(packed=compact == "packed") if compact else self._full_layout()
+        block, inputs = carve_block(self._host_segments(lay), pin_memory=True)
+        inputs["_block"] = block
+        oblock, outputs = carve_block(result_segments(n, self.obs_buf.shape[1]), pin_memory=True)
+        outputs["_block"] = oblock
         return inputs, outputs
+
+    def _host_segments(self, lay):
+        n, f32 = self.num_envs, torch.float32
+        return [("dof_state", (n, 26, 2), f32), ("rigid_body_state", (n, lay.num_bodies, lay.rigid_row_floats), f32),
+                ("net_contact_force", (n, lay.contact_rows, 3), f32), ("actor_root_state", (n, lay.num_actors, 13), f32),
+                ("actions", (n, self.num_actions), f32)]
 
     def _full_layout(self):
         saved = getattr(self, "_host_saved", None)
@@ -209,7 +226,7 @@ class DexStepEnv:
         """Copy the current device sim state (+ ``actions``) into host buffers of either layout (outside any timed
         region: this stands in for the host-side simulator that would write them)."""
         full, lay = self._full_sim(), self._full_layout()
-        if host_inputs["rigid_body_state"].shape[1] == lay.num_bodies:
+        if tuple(host_inputs["rigid_body_state"].shape[1:]) == (lay.num_bodies, 13):
             for k, v in full.items():
                 host_inputs[k].copy_(v.view(host_inputs[k].shape))
         else:
@@ -229,42 +246,77 @@ class DexStepEnv:
 
     def step_host(self, host_inputs: Dict[str, torch.Tensor], host_outputs: Dict[str, torch.Tensor]):
         """One control step fed from HOST buffers: H2D of the sim state + actions, the two kernel launches, D2H of
-        obs/rew/reset - all asynchronous on the current stream (synchronise the stream before reading
-        ``host_outputs``).  The layout (full or compact) is taken from the buffers' shapes; the first compact call
-        switches the pipeline to device mirrors of that layout (``end_host_mode`` switches back).
-        Returns (h2d_bytes, d2h_bytes)."""
+        obs/rew/reset - all asynchronous.  The layout (full, compact or packed) is taken from the buffers' shapes; the first
+        call switches the pipeline to device mirrors of that layout (``end_host_mode`` switches back to the env's own sim
+        tensors).  Buffers from ``alloc_host_buffers`` move with one copy per direction; plain dicts of pinned tensors
+        (no ``"_block"``) with one copy per tensor.
+
+        The three stages run on three streams - uploads on one per-device upload stream, the kernels on the CALLER's
+        current stream, downloads on one per-device download stream - chained by events, so that the upload of the next step
+        (of this env or of another one) overlaps this step's kernels and download and the link carries at most one copy per
+        direction at any time (two uploads at once only share the link and push the downloads out of phase: measured, 36-52 M
+        instead of 60 M env-steps/s at 16 384 envs).  ``host_inputs`` must stay untouched until the upload is done and
+        ``host_outputs`` are valid once the download is: call ``host_sync()`` (makes the current stream wait for both) and
+        synchronise the stream, or synchronise the device.  Returns (h2d_bytes, d2h_bytes) as copied."""
         p = self.pipeline
         shape = tuple(host_inputs["rigid_body_state"].shape[1:])
-        mode = 0 if shape == (self._full_layout().num_bodies, 13) else 2 if shape[1] == 7 else 1
-        if mode != getattr(self, "_host_mode", 0):
+        mode = (shape, "_block" in host_inputs)
+        if mode != getattr(self, "_host_mode", None):
             self.end_host_mode()
-            if mode:
-                self._host_saved = (self.layout, dict(p.sim_tensors))
-                self._host_mode = mode
-                lay = self.layout.compact(packed=mode == 2)
-                dev = {k: torch.empty(v.shape, dtype=v.dtype, device=self.device)
-                       for k, v in host_inputs.items() if k != "actions"}
-                p.use_layout(lay, dev)
+            full = self.layout
+            lay = full if shape == (full.num_bodies, 13) else full.compact(packed=shape[1] == 7)
+            self._host_saved = (full, dict(p.sim_tensors))
+            self._host_mode = mode
+            self._host_dev_block, dev = carve_block(self._host_segments(lay), device=self.device)
+            self._host_dev_actions = dev.pop("actions")
+            p.use_layout(lay, dev)
+            self._host_ev = {k: torch.cuda.Event() for k in ("in_ready", "in_free", "out_ready", "out_free")}
+        up, down = _copy_streams(self.device)
+        cur, ev = torch.cuda.current_stream(self.device), self._host_ev
         h2d = d2h = 0
-        for k, dst in p.sim_tensors.items():
-            dst.copy_(host_inputs[k].view(dst.shape), non_blocking=True)
-            h2d += dst.numel() * dst.element_size()
-        self._actions.copy_(host_inputs["actions"], non_blocking=True)
-        h2d += self._actions.numel() * 4
-        p.step(self._actions)
-        for k, src in (("obs_buf", self.obs_buf), ("rew_buf", self.rew_buf), ("reset_buf", self.reset_buf)):
-            host_outputs[k].copy_(src, non_blocking=True)
-            d2h += src.numel() * src.element_size()
+        up.wait_event(ev["in_free"])  # the kernels of this env's previous step have read the device mirrors
+        with torch.cuda.stream(up):
+            if "_block" in host_inputs:
+                self._host_dev_block.copy_(host_inputs["_block"], non_blocking=True)
+                h2d = self._host_dev_block.numel()
+            else:
+                for k, dst in list(p.sim_tensors.items()) + [("actions", self._host_dev_actions)]:
+                    dst.copy_(host_inputs[k].view(dst.shape), non_blocking=True)
+                    h2d += dst.numel() * dst.element_size()
+            ev["in_ready"].record(up)
+        cur.wait_event(ev["in_ready"])
+        cur.wait_event(ev["out_free"])  # the previous step's results have left the device
+        p.step(self._host_dev_actions)
+        ev["in_free"].record(cur)
+        ev["out_ready"].record(cur)
+        down.wait_event(ev["out_ready"])
+        with torch.cuda.stream(down):
+            if "_block" in host_outputs:
+                host_outputs["_block"].copy_(p.result_block, non_blocking=True)
+                d2h = p.result_block.numel()
+            else:
+                for k, src in (("obs_buf", self.obs_buf), ("rew_buf", self.rew_buf), ("reset_buf", self.reset_buf)):
+                    host_outputs[k].copy_(src, non_blocking=True)
+                    d2h += src.numel() * src.element_size()
+            ev["out_free"].record(down)
         return h2d, d2h
 
+    def host_sync(self):
+        """Make the current stream wait for the last ``step_host``'s download (and therefore for its upload and kernels):
+        after a synchronise of that stream the host outputs are valid and the host inputs may be rewritten."""
+        ev = getattr(self, "_host_ev", None)
+        if ev is not None:
+            torch.cuda.current_stream(self.device).wait_event(ev["out_free"])
+
     def end_host_mode(self):
-        """Back to the env's own (full-layout) sim tensors after compact ``step_host`` calls."""
+        """Back to the env's own (full-layout) sim tensors after ``step_host`` calls."""
         saved = getattr(self, "_host_saved", None)
         if saved is not None:
             torch.cuda.synchronize(self.device)
             self.pipeline.use_layout(*saved)
             self._host_saved = None
-            self._host_mode = 0
+            self._host_mode = None
+            self._host_dev_block = self._host_dev_actions = self._host_ev = None
 
     # ------------------------------------------------------------------ extras (step_processor.py:221-232)
     def _update_extras(self):

@@ -39,6 +39,32 @@ NUM_UNIFORMS = C["DEX_NUM_UNIFORMS"]
 STAT_SLICES = 32  # blocks of DexOutBuffers.stat_totals
 
 
+def result_segments(n: int, obs_dim: int):
+    return [("obs_buf", (n, obs_dim), torch.float32), ("rew_buf", (n,), torch.float32), ("reset_buf", (n,), torch.bool)]
+
+
+def carve_block(segments, device=None, pin_memory: bool = False):
+    """One zeroed uint8 allocation holding every (name, shape, dtype) of ``segments`` at 256-byte aligned offsets
+    -> (block, {name: view}).  Host and device blocks carved from the same list have the same offsets, so one copy of the
+    block moves all of them."""
+    offs, total = [], 0
+    for _, shape, dtype in segments:
+        offs.append(total)
+        nbytes = torch.empty((), dtype=dtype).element_size()
+        for d in shape:
+            nbytes *= d
+        total += (nbytes + 255) // 256 * 256
+    block = (torch.zeros(total, dtype=torch.uint8, pin_memory=True) if pin_memory
+             else torch.zeros(total, dtype=torch.uint8, device=device))
+    views = {}
+    for (name, shape, dtype), off in zip(segments, offs):
+        nbytes = torch.empty((), dtype=dtype).element_size()
+        for d in shape:
+            nbytes *= d
+        views[name] = block[off:off + nbytes].view(dtype).view(*shape)
+    return block, views
+
+
 def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
     return None if t is None else t.data_ptr()
 
@@ -109,9 +135,12 @@ class StepPipeline:
 
         # ---- outputs ----
         rows = self.params.num_component_rows
+        # what a step hands back to its caller - obs_buf, rew_buf, reset_buf - lives in ONE allocation, so that a host-side
+        # caller fetches it with one device-to-host copy (DexStepEnv.step_host)
+        self.result_block, res = carve_block(result_segments(n, sp.obs_dim), device=dev)
         o = self.out = {
-            "obs_buf": z(n, sp.obs_dim), "obs_dict": z(n, sp.dict_dim) if materialize_obs_dict else None,
-            "rew_buf": z(n), "reset_buf": z(n, dtype=torch.bool), "success": z(n, dtype=torch.bool),
+            "obs_buf": res["obs_buf"], "obs_dict": z(n, sp.dict_dim) if materialize_obs_dict else None,
+            "rew_buf": res["rew_buf"], "reset_buf": res["reset_buf"], "success": z(n, dtype=torch.bool),
             "failure": z(n, dtype=torch.bool), "timeout": z(n, dtype=torch.bool),
             "reward_components": z(rows, n), "reset_bits": z((n + 31) // 32, dtype=torch.int32),
             "counters": z(C["DEX_NUM_COUNTERS"], dtype=torch.int32),

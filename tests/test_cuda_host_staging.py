@@ -41,8 +41,8 @@ def _put(env, state):
 
 @pytest.mark.parametrize("task", ["BaseTask", "BlindGrasping"])
 @pytest.mark.parametrize("compact", [False, True, "packed"], ids=["full", "compact", "packed"])
-@pytest.mark.parametrize("n", [100, 4096])
-def test_step_host_equals_device_step(task, compact, n):
+@pytest.mark.parametrize("n,blocks", [(100, True), (100, False), (4096, True)], ids=["n100", "n100_per_tensor", "n4096"])
+def test_step_host_equals_device_step(task, compact, n, blocks):
     steps = 150 if n == 100 else 40
     a, layout = _env(task, n)
     b, _ = _env(task, n)
@@ -50,6 +50,10 @@ def test_step_host_equals_device_step(task, compact, n):
     hin, hout = b.alloc_host_buffers(compact=compact)
     if compact == "packed":
         assert tuple(hin["rigid_body_state"].shape) == (n, 12, 7)
+    assert all(v.is_pinned() for v in list(hin.values()) + list(hout.values()))
+    if not blocks:  # a caller's own pinned tensors: one copy per tensor
+        hin = {k: v for k, v in hin.items() if k != "_block"}
+        hout = {k: v for k, v in hout.items() if k != "_block"}
     s0 = world.state(0, a.episode_step_count, box0_of(a))
     a.load_state(s0)
     b.load_state(s0)
@@ -76,9 +80,11 @@ def test_step_host_equals_device_step(task, compact, n):
     assert resets > 0
     per_env = {False: None, True: (11 * 13 + 52 + (6 if task == "BlindGrasping" else 5) * 3 + 13) * 4,
                "packed": (12 * 7 + 52 + (6 if task == "BlindGrasping" else 5) * 3 + 13) * 4}[compact]
-    if per_env is not None:
-        assert h2d == n * (per_env + 4 * a.num_actions)
-    assert d2h == n * (4 * a.obs_buf.shape[1] + 4 + 1)
+    if per_env is not None:  # as copied: the single-block path rounds each of its 5 (3) segments up to 256 bytes
+        payload = n * (per_env + 4 * a.num_actions)
+        assert h2d == payload if not blocks else payload <= h2d < payload + 5 * 256
+    payload = n * (4 * a.obs_buf.shape[1] + 4 + 1)
+    assert d2h == payload if not blocks else payload <= d2h < payload + 3 * 256
     b.end_host_mode()
     assert b.pipeline.layout.rigid_row_floats == 13 and int(b.pipeline.params.rigid_row_floats) == 13
     # back on its own tensors the env keeps stepping in lockstep with the device-fed one
