@@ -258,7 +258,8 @@ typedef struct DexParams {
                                       DexStepEnv.alloc_host_buffers(compact="packed")): the path reads 7 floats of every tip /
                                       pad row and 13 of the hand row (7 when no common reward term is weighted), so with 7 the
                                       hand takes two consecutive slots.  hand_body * rigid_row_floats + 13 must stay inside
-                                      the env's NB * rigid_row_floats floats.  Not with DEX_FLAG_TMA_STAGING (ignored there). */
+                                      the env's NB * rigid_row_floats floats (checked).  With a pitch other than 13
+                                      DEX_FLAG_TMA_STAGING is ignored (the tensor maps assume Isaac Gym's rows). */
 } DexParams;
 
 /* Isaac Gym tensor-API buffers, zero-copy (tensor_manager.py:173-328). */
