@@ -614,7 +614,7 @@ def main():
     except Exception:
         pass
     post_kernel = ("post_physics_kernel", "post_physics_v2_kernel", "post_physics_v2s_kernel",
-                   "post_physics_v2_kernel<TMA>")[lib.dex_debug_last_post_kernel()]
+                   "post_physics_v2_kernel<TMA>", "post_physics_v2_kernel<pair>")[lib.dex_debug_last_post_kernel()]
     floor_us = kernel_avg_us(ring, floor_only, kl, group, device)
     roofline = {"bound": "hbm", "kernel": post_kernel, "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic,

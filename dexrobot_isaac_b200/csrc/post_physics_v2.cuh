@@ -1562,7 +1562,8 @@ __device__ __forceinline__ void load_tile_regs(const Post2Args& A, const LoadCtx
   if (w == 7) i64[LY::I_STEP * 32] = r_i64;
 }
 
-__device__ __forceinline__ void cons_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kConsThreads) : "memory"); }
+template <int NT = kConsThreads>
+__device__ __forceinline__ void cons_sync() { asm volatile("bar.sync 1, %0;" ::"n"(NT) : "memory"); }
 
 // shared -> global bulk store of the flat obs tile (TMA engine): one instruction for 20 KB
 __device__ __forceinline__ void bulk_s2g(void* dst, const uint32_t src, const uint32_t bytes) {
@@ -1632,18 +1633,23 @@ __device__ __forceinline__ void copy_obs_norm_rows(const float* s_obs, const Dex
 // item code on different items at the same time (one fetched line serves all), loops are not unrolled, and a warp that
 // waits blocks in hardware (bar.sync behind one polling warp) instead of spinning through fetch slots.
 // ------------------------------------------------------------------------------------------------
-template <bool BG, bool STD, bool TMA = false, bool OBS = false>
-__global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(const __grid_constant__ Post2Args A) {
+template <bool BG, bool STD, bool TMA = false, bool OBS = false, int G = 1>
+__global__ void __launch_bounds__(G * kThreads, (BG && G == 1) ? 2 : 1) post_physics_v2_kernel(const __grid_constant__ Post2Args A) {
   using LY = Lay<BG>;
+  // G tiles per pass: G groups of 8 consumer warps run the per-tile program on G tiles IN LOCKSTEP (they share every barrier),
+  // so one pass of the instruction stream through the SM's front end serves G tiles; G groups of 4 producer warps fill the
+  // G sub-stages of a ring stage.  G = 2 is the "pair" geometry (one CTA per SM), G = 1 the plain persistent kernel.
+  constexpr int CW = G * kConsWarps, CT = CW * 32;
+  static_assert(G == 1 || (BG && !TMA), "pair geometry: BlindGrasping, LDGSTS producers");
   static_assert(BG || !TMA, "TMA staging: BlindGrasping stage layout");
   constexpr int LM = TMA ? 2 : 0;
   const uint32_t stage_bytes = TMA ? A.stage_bytes : (uint32_t)LY::STAGE_BYTES;
   extern __shared__ __align__(128) unsigned char smem2[];
   __shared__ __align__(8) unsigned long long s_bar[2 * kStages];  // full[0..], empty[0..]
-  __shared__ float s_reset_u[32 * kConsWarps];
+  __shared__ float s_reset_u[32 * CW];
   __shared__ int s_rbo[kRbW + 1];  // gathered rigid slot -> float offset inside one env's [NB,13] block
   __shared__ unsigned long long s_rng_step;
-  __shared__ unsigned s_rbits[4];  // ballots of this tile: reset | success | failure
+  __shared__ unsigned s_rbits_all[G][4];  // ballots of this tile: reset | success | failure
   __shared__ int s_epi_warp[kConsWarps];
   __shared__ int s_epi_base;
   __shared__ int s_epi_cnt[DEX_NUM_COUNTERS];
@@ -1679,8 +1685,8 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
 #pragma unroll
     for (int s = 0; s < kStages; ++s) {
       // LDGSTS producers: one cp.async-completion arrival per producer thread + one per warp; TMA: one arrival (expect_tx)
-      mbar_init(bar_full + 8 * s, TMA ? 1 : kProdThreads + kProdWarps);
-      mbar_init(bar_empty + 8 * s, kConsWarps);
+      mbar_init(bar_full + 8 * s, TMA ? 1 : G * (kProdThreads + kProdWarps));
+      mbar_init(bar_empty + 8 * s, CW);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -1693,13 +1699,11 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
   __syncthreads();
   pdl_launch_dependents();
   TL2_DECL;
-  float* const wk_base = reinterpret_cast<float*>(smem2 + kStages * stage_bytes);
-  float* const s_obs = wk_base + LY::W_COUNT * 32;
   const int tiles = A.tiles, workers = A.workers;
 
-  if (warp >= kConsWarps) {
+  if (warp >= CW) {
     // =========================== producer warps ===========================
-    const int pw = warp - kConsWarps;
+    const int pw = (warp - CW) % kProdWarps, pg = G == 1 ? 0 : (warp - CW) / kProdWarps;
     if constexpr (TMA) {
       // ONE warp, one copy per lane and tile (build_tma): 2-D tensor boxes for the gathered Isaac Gym rows and the [K][N]
       // state rows, plain bulk copies for the dof tile and the single rows.  The TMA unit serves a CTA's copies in issue
@@ -1749,9 +1753,9 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
     lc.setup(A, s_rbo, lane);
     int it = 0;
 #pragma unroll 1
-    for (int tile = blockIdx.x; tile < tiles; tile += workers, ++it) {
+    for (int tile = blockIdx.x * G + pg; tile < tiles; tile += workers * G, ++it) {
       const int s = it & 1, use = it >> 1;
-      unsigned char* stage = smem2 + s * stage_bytes;
+      unsigned char* stage = smem2 + (s * G + pg) * stage_bytes;
       const uint32_t fb = bar_full + 8 * s;
       TL2(it, 16);
       if (use > 0) mbar_wait(bar_empty + 8 * s, (unsigned)(use - 1) & 1u);
@@ -1763,9 +1767,16 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
   }
 
   // =========================== consumer warps ===========================
+  // consumer group g works on tile (pass * workers + block) * G + g; inside a group the warps are numbered 0..7 as before
+  const int cg = G == 1 ? 0 : warp / kConsWarps;
+  const int wg = G == 1 ? warp : warp % kConsWarps;
+  float* const wk_base = reinterpret_cast<float*>(smem2 + kStages * G * stage_bytes) +
+                         cg * (LY::W_COUNT * 32 + (32 * A.wp * 4 + 127) / 128 * 32);
+  float* const s_obs = wk_base + LY::W_COUNT * 32;
+  unsigned* const s_rbits = s_rbits_all[cg];
   Cx<BG, STD> c;
   c.lane = lane;
-  c.cw = warp;
+  c.cw = wg;
   c.N = (size_t)A.n;
   c.wk = wk_base + lane;
   c.obs = s_obs + lane * A.wp;
@@ -1777,20 +1788,20 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
   const int W = A.p.obs_dim;
   int it = 0;
 #pragma unroll 1
-  for (int tile = blockIdx.x; tile < tiles; tile += workers, ++it) {
+  for (int tile = blockIdx.x * G + cg; tile < tiles; tile += workers * G, ++it) {  // tiles % G == 0: every group has a tile
     const int s = it & 1, use = it >> 1;
     c.e0 = tile * 32;
     c.ne = min(32, A.n - c.e0);
     c.act = lane < c.ne;
     c.env = (size_t)c.e0 + (c.act ? lane : 0);
-    c.stage = smem2 + s * stage_bytes;
+    c.stage = smem2 + (s * G + cg) * stage_bytes;
     float* const g_obs = A.out.obs_buf + (size_t)c.e0 * W;
     const bool bulk_out = A.obs_bulk && c.ne == 32;  // CTA-uniform
     TL2(it, 0);
     if constexpr (OBS) {
-      if (warp == kConsWarps - 1) {  // observer rows of this tile (first iteration) and of the next one
+      if (wg == kConsWarps - 1) {  // observer rows of this tile (first iteration) and of the next one
         if (it == 0) observer_prefetch(A, c.e0, lane);
-        if (tile + workers < tiles) observer_prefetch(A, (tile + workers) * 32, lane);
+        if (tile + workers * G < tiles) observer_prefetch(A, (tile + workers * G) * 32, lane);
       }
     }
     // ONE warp polls the stage's mbarrier, the other seven block in hardware behind it
@@ -1798,7 +1809,7 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
     // Philox step counter == stamp of this step's tile records: read once per CTA, behind the first full barrier (i.e.
     // behind the producers' griddepcontrol.wait; the epilogue CTA advances it only after every record of this launch is out)
     if (it == 0 && tid == 0) s_rng_step = A.st.rng_step ? *reinterpret_cast<const volatile unsigned long long*>(A.st.rng_step) : A.step;
-    cons_sync();
+    cons_sync<CT>();
     TL2(it, 1);
     if (it == 0) {
       rng_step = s_rng_step;
@@ -1806,41 +1817,41 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
     }
     phase_items<BG, STD, LM>(A, c);
     TL2(it, 2);
-    cons_sync();
+    cons_sync<CT>();
     TL2(it, 3);
     phase_scalar<BG, STD, LM>(A, c);
     TL2(it, 4);
-    cons_sync();
+    cons_sync<CT>();
     TL2(it, 5);
     unsigned cls = 0;
-    if (warp == 0) {
+    if (wg == 0) {
       cls = phase_combine<BG, STD, LM>(A, c, stamp, s_rbits);
     } else if (BG) {
       if (c.act) {
 #pragma unroll 1
-        for (int i = DEX_NUM_COMMON_TERMS + (warp - 1); i < DEX_NUM_REWARD_TERMS; i += kConsWarps - 1)
+        for (int i = DEX_NUM_COMMON_TERMS + (wg - 1); i < DEX_NUM_REWARD_TERMS; i += kConsWarps - 1)
           emit_term<BG, STD, LM>(A, c, i, task_term<BG, STD, LM>(A, c, i));
       }
     }
     if (bulk_out) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // obs tile writes -> visible to the bulk store
     __syncwarp();
     TL2(it, 6);
-    cons_sync();
+    cons_sync<CT>();
     TL2(it, 7);
     // the raw stage is not read after this point: hand it back to the producers
     if (lane == 0) mbar_arrive(bar_empty + 8 * s);
-    if (warp == 0) phase_total<BG, STD, LM, OBS>(A, c, cls);
-    else if constexpr (OBS) observer_term_rows<BG, STD>(A, c, s_rbits, warp - 1, kConsWarps - 1);
+    if (wg == 0) phase_total<BG, STD, LM, OBS>(A, c, cls);
+    else if constexpr (OBS) observer_term_rows<BG, STD>(A, c, s_rbits, wg - 1, kConsWarps - 1);
     TL2(it, 8);
     if (bulk_out) {
-      if (tid == 32) {
+      if (wg == 1 && lane == 0) {
         bulk_s2g(g_obs, s32(s_obs), (uint32_t)(32 * W * 4));
         store_pending = true;
       }
     } else {
-      copy_obs_rows(s_obs, g_obs, W, A.wp, c.ne, warp, lane);
+      copy_obs_rows(s_obs, g_obs, W, A.wp, c.ne, wg, lane);
     }
-    if (A.out.obs_norm != nullptr) copy_obs_norm_rows(s_obs, A.out, c.e0, W, A.wp, c.ne, warp, lane);
+    if (A.out.obs_norm != nullptr) copy_obs_norm_rows(s_obs, A.out, c.e0, W, A.wp, c.ne, wg, lane);
     TL2(it, 9);
     {
       unsigned mask = s_rbits[0];  // written by warp 0 before the barrier above
@@ -1850,15 +1861,15 @@ __global__ void __launch_bounds__(kThreads, BG ? 2 : 1) post_physics_v2_kernel(c
         for (int k = 0; mask; ++k) {
           const int e = __ffs(mask) - 1;
           mask &= mask - 1;
-          if ((k & (kConsWarps - 1)) == warp) {
+          if ((k & (kConsWarps - 1)) == wg) {
             reset_env_warp<BG>(A, c.e0 + e, rng_step, s_reset_u + 32 * warp);
           }
         }
       }
     }
-    if (bulk_out && tid == 32) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // obs tile may be rewritten
+    if (bulk_out && wg == 1 && lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // obs tile may be rewritten
     TL2(it, 10);
-    cons_sync();  // work block, obs tile and s_rbits are reused by the next tile
+    cons_sync<CT>();  // work block, obs tile and s_rbits are reused by the next tile
     TL2(it, 11);
   }
   if (store_pending) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // the last obs tile has left shared memory
@@ -1992,7 +2003,7 @@ __global__ void __launch_bounds__(kOneThreads, 4) post_physics_v2s_kernel(const 
   if (bulk_out && tid == 32) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // the obs tile has left shared memory
 }
 
-static int g_last_geometry = 0;  // 0 tile kernel, 1 persistent, 2 single pass (dex_debug_last_post_kernel)
+static int g_last_geometry = 0;  // 0 tile kernel, 1 persistent, 2 single pass, 3 persistent + TMA, 4 pair (dex_debug_last_post_kernel)
 
 template <bool STD, bool OBS>
 int launch_post2_single(Post2Args& a, cudaStream_t s, int& ok) {
@@ -2022,13 +2033,13 @@ int launch_post2_single(Post2Args& a, cudaStream_t s, int& ok) {
   return e == cudaSuccess ? DEX_OK : (int)e;
 }
 
-template <bool BG, bool STD, bool TMA, bool OBS>
+template <bool BG, bool STD, bool TMA, bool OBS, int G = 1>
 int launch_post2_k(Post2Args& a, cudaStream_t s) {
   static int ctas_per_sm = -1, num_sms = 0;
   static size_t smem_cfg = 0, smem_occ = 0;
   if (a.smem_bytes > smem_cfg) {
     const size_t want = a.smem_bytes > 100 * 1024 ? a.smem_bytes : 100 * 1024;
-    const cudaError_t e = cudaFuncSetAttribute(post_physics_v2_kernel<BG, STD, TMA, OBS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)want);
+    const cudaError_t e = cudaFuncSetAttribute(post_physics_v2_kernel<BG, STD, TMA, OBS, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)want);
     if (e != cudaSuccess) return (int)e;
     smem_cfg = want;
     ctas_per_sm = -1;
@@ -2037,7 +2048,7 @@ int launch_post2_k(Post2Args& a, cudaStream_t s) {
     int dev = 0, occ = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
-    const cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, post_physics_v2_kernel<BG, STD, TMA, OBS>, kThreads, a.smem_bytes);
+    const cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, post_physics_v2_kernel<BG, STD, TMA, OBS, G>, G * kThreads, a.smem_bytes);
     if (e != cudaSuccess) return (int)e;
     if (occ < 1) return DEX_ERR_SIZE;
     ctas_per_sm = occ;
@@ -2046,8 +2057,9 @@ int launch_post2_k(Post2Args& a, cudaStream_t s) {
   const int fused = a.fused_epilogue ? 1 : 0;
   int cap = num_sms * ctas_per_sm - fused;  // every CTA of the launch (workers + epilogue) is resident at once
   if (cap < 1) cap = 1;
-  a.workers = a.tiles < cap ? a.tiles : cap;
-  const cudaError_t e = launch_step_kernel(post_physics_v2_kernel<BG, STD, TMA, OBS>, a.workers + fused, kThreads, a.smem_bytes, s, a);
+  const int units = a.tiles / G;  // G tiles per CTA and pass (the pair geometry requires tiles % G == 0)
+  a.workers = units < cap ? units : cap;
+  const cudaError_t e = launch_step_kernel(post_physics_v2_kernel<BG, STD, TMA, OBS, G>, a.workers + fused, G * kThreads, a.smem_bytes, s, a);
   if (e != cudaSuccess) (void)cudaGetLastError();
   return e == cudaSuccess ? DEX_OK : (int)e;
 }
@@ -2076,6 +2088,22 @@ int launch_post2_t(Post2Args& a, cudaStream_t s) {
                           : (std_layout ? launch_post2_single<true, false>(a, s, ok) : launch_post2_single<false, false>(a, s, ok));
       if (ok) g_last_geometry = 2;
       if (ok || rc1) return rc1;
+    }
+  }
+  if constexpr (BG) {
+    // pair geometry: two tiles per pass and CTA (one CTA of 24 warps per SM), on request only (DEX_FLAG_PAIR_GEOMETRY, or
+    // DEXSTEP_POST_GEOMETRY=pair for every call of the process; =nopair overrides the flag): measured slower, see the header.
+    static const int env_pair = []() {
+      const char* e = getenv("DEXSTEP_POST_GEOMETRY");
+      return e == nullptr ? 0 : (strcmp(e, "pair") == 0 ? 1 : (strcmp(e, "nopair") == 0 ? -1 : 0));
+    }();
+    const bool eligible = a.tiles % 2 == 0 && !(a.flags & DEX_FLAG_TMA_STAGING) && 2u * a.smem_bytes <= 227u * 1024u - 4096u;
+    if (eligible && env_pair >= 0 && (env_pair > 0 || (a.flags & DEX_FLAG_PAIR_GEOMETRY) != 0)) {
+      a.tma = 0;
+      a.smem_bytes *= 2;
+      g_last_geometry = 4;
+      return obs ? (std_layout ? launch_post2_k<true, true, false, true, 2>(a, s) : launch_post2_k<true, false, false, true, 2>(a, s))
+                 : (std_layout ? launch_post2_k<true, true, false, false, 2>(a, s) : launch_post2_k<true, false, false, false, 2>(a, s));
     }
   }
   g_last_geometry = 1;

@@ -32,6 +32,7 @@ FLAG_EARLY_SIM_LOADS = C["DEX_FLAG_EARLY_SIM_LOADS"]
 FLAG_TILE_KERNEL = C["DEX_FLAG_TILE_KERNEL"]
 FLAG_TMA_STAGING = C["DEX_FLAG_TMA_STAGING"]
 FLAG_SINGLE_PASS = C["DEX_FLAG_SINGLE_PASS"]
+FLAG_PAIR_GEOMETRY = C["DEX_FLAG_PAIR_GEOMETRY"]
 _EARLY_SIM = os.environ.get("DEXSTEP_EARLY_SIM_LOADS", "1") != "0"  # A/B switch for StepPipeline.step()
 NUM_UNIFORMS = C["DEX_NUM_UNIFORMS"]
 
@@ -97,6 +98,7 @@ class StepPipeline:
         # True: DEX_FLAG_SINGLE_PASS - the single-pass kernel where it applies (2-4 tiles per SM): 20 % faster than the
         # persistent one when the sim tensors are L2-resident (post-physics right behind the simulator), 3-5 % slower from HBM
         self.single_pass = False
+        self.pair_geometry = False  # True: DEX_FLAG_PAIR_GEOMETRY (two tiles per pass and thread block; measured slower)
         n, dev, sp = self.n, self.device, self.spec
         f32, i64, u8 = torch.float32, torch.int64, torch.uint8
 
@@ -315,6 +317,8 @@ class StepPipeline:
             flags |= FLAG_TMA_STAGING
         if self.single_pass:
             flags |= FLAG_SINGLE_PASS
+        if self.pair_geometry:
+            flags |= FLAG_PAIR_GEOMETRY
         L.check(self.lib.dex_post_physics(ctypes.byref(self.params), ctypes.byref(self._sim), ctypes.byref(self._state),
                                           ctypes.byref(self._out),
                                           ctypes.byref(self._epi) if fused_epilogue and mode == MODE_FULL else None,

@@ -114,6 +114,14 @@ extern "C" {
                                          16 384 envs: the TMA unit serves these 28..64-byte box rows at ~1 row per 6.5 clk per
                                          SM, profiles/r02_variants.md), kept selectable so the measurement can be repeated.
                                          BlindGrasping, N % 32 == 0, num_bodies % 4 == 0, num_actors % 2 == 0; ignored otherwise */
+#define DEX_FLAG_PAIR_GEOMETRY 128u   /* persistent kernel with TWO tiles per pass: one thread block of 16 consumer + 8 producer
+                                         warps per SM, the two groups of 8 consumer warps run the per-tile program in lockstep
+                                         on two tiles (all barriers shared).  Bit-identical results; MEASURED SLOWER on B200
+                                         (18.9 vs 18.3 us per launch at 16 384 envs, 194 vs 183 us at 262 144: the per-SM rate of
+                                         ~one tile per 3.3 us is not an instruction-fetch limit that lockstep groups could
+                                         share, profiles/r02_variants.md), kept selectable so the measurement can be repeated.
+                                         BlindGrasping with an even number of 32-env tiles; ignored otherwise and with
+                                         DEX_FLAG_TMA_STAGING / DEX_FLAG_SINGLE_PASS where those apply */
 
 /* observation keys (obs_dict entries of the reference, observation_encoder.py:613-756,
  * step_processor.py:73, blind_grasping_task.py:569-652,702-746,895-899) */
@@ -374,7 +382,8 @@ int dex_sizeof_params(void);
 int dex_debug_v2_launches(void);
 /* which kernel the last dex_post_physics call of this process launched: 0 = table-driven tile kernel (post_physics_kernel),
  * 1 = persistent warp-specialised kernel (post_physics_v2_kernel, LDGSTS producers), 2 = single-pass kernel
- * (post_physics_v2s_kernel), 3 = persistent kernel with TMA producers (tensor copies) */
+ * (post_physics_v2s_kernel), 3 = persistent kernel with TMA producers (tensor copies), 4 = persistent kernel with two tiles
+ * per pass (DEX_FLAG_PAIR_GEOMETRY) */
 int dex_debug_last_post_kernel(void);
 /* measurement aid (bench.py): launches an EMPTY kernel with dex_pre_physics' grid, block and programmatic-launch
  * attribute for n_envs - the per-launch floor of a kernel in a stream / graph of step kernels on this GPU */

@@ -124,7 +124,7 @@ def test_packed_rows_every_kernel_family(kernel):
         assert torch.equal(hout["obs_buf"], a.obs_buf.cpu()) and torch.equal(hout["rew_buf"], a.rew_buf.cpu())
         assert torch.equal(hout["reset_buf"], a.reset_buf.cpu())
     from dexrobot_isaac_b200 import _lib as L
-    assert L.load().dex_debug_last_post_kernel() == {"tile": 0, "persistent": 1, "single": 2}[kernel]
+    assert L.load().dex_debug_last_post_kernel() in {"tile": (0,), "persistent": (1, 4), "single": (2,)}[kernel]
 
 
 def test_row_pitch_is_validated():

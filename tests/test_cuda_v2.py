@@ -102,7 +102,7 @@ def test_v2_lockstep_headline_size(task, single):
 
     seen = _lockstep(task, 16384, 24, seed=210, single_pass=single)
     assert seen["reset"] > 0
-    assert L.load().dex_debug_last_post_kernel() == (2 if single else 1)
+    assert L.load().dex_debug_last_post_kernel() in ((2,) if single else (1, 4))  # 4: the pair geometry, where dispatched
 
 
 BUFS_OUT = ("obs_buf", "rew_buf", "reset_buf", "reward_components", "success", "failure", "timeout", "reset_bits")
@@ -112,12 +112,15 @@ BUFS_OUT = ("obs_buf", "rew_buf", "reset_buf", "reward_components", "success", "
                                         ("BaseTask", 5000, False), ("BlindGrasping", 100003, False), ("BlindGrasping", 33, False),
                                         ("BlindGrasping", 16384, True), ("BlindGrasping", 4096, True), ("BlindGrasping", 131072, True),
                                         ("BlindGrasping", 16384, "single"), ("BlindGrasping", 12000, "single"),
-                                        ("BlindGrasping", 9473, "single")])
+                                        ("BlindGrasping", 9473, "single"),
+                                        ("BlindGrasping", 16384, "pair"), ("BlindGrasping", 33, "pair"), ("BlindGrasping", 100003, "pair"),
+                                        ("BlindGrasping", 131072, "pair")])
 def test_v2_equals_tile_kernel_bitwise(task, n, tma):
     """Same seeded random-state trajectory through the persistent kernel and through the tile kernel: every output,
     every state buffer, the sim tensors the fused reset rewrites, env_ids and the epilogue statistics are identical
     bit for bit (in-kernel Philox resets included: both kernels key the stream by (seed, step, env)).
-    ``tma``: True = the persistent kernel with tensor-copy producers (DEX_FLAG_TMA_STAGING), "single" = the single-pass kernel."""
+    ``tma``: True = the persistent kernel with tensor-copy producers (DEX_FLAG_TMA_STAGING), "single" = the single-pass kernel,
+    "pair" = the persistent kernel with two tiles per pass (DEX_FLAG_PAIR_GEOMETRY; 33 envs = 2 tiles, one ragged)."""
     from dexrobot_isaac_b200 import _lib as L
 
     lay = synth.BodyLayout(with_box=task == "BlindGrasping")
@@ -125,9 +128,11 @@ def test_v2_equals_tile_kernel_bitwise(task, n, tma):
     e1, e2 = lean_env(task, n), lean_env(task, n)
     e1.pipeline.tile_kernel = True
     single = tma == "single"  # DEX_FLAG_SINGLE_PASS: the single-pass kernel (2 < tiles per SM <= 4)
+    pair = tma == "pair"
     tma = tma is True
     e2.pipeline.tma_staging = tma
     e2.pipeline.single_pass = single
+    e2.pipeline.pair_geometry = pair
     u = synth.random_uniforms(n, gen)
     steps = 7
     for t in range(steps):
@@ -146,7 +151,9 @@ def test_v2_equals_tile_kernel_bitwise(task, n, tma):
                 e.pipeline.post_step()
         if t > 0:
             kernel = L.load().dex_debug_last_post_kernel()  # of e2's launch
-            assert kernel == (3 if tma else 2 if single else 1), kernel
+            # 4 = the pair geometry (two tiles per pass), where the library's dispatch selects it (DEXSTEP_POST_GEOMETRY=pair or
+            # its size rule) - also bit-identical to the tile kernel, which is what this test checks
+            assert kernel in ((3,) if tma else (2,) if single else (4,) if pair else (1, 4)), kernel
         torch.cuda.synchronize()
         p1, p2 = e1.pipeline, e2.pipeline
         for k in BUFS_OUT:
