@@ -88,12 +88,13 @@ def short(n):
         return n
     k, d = int(m.group(1)), len(m.group(1))
     base, rest = n[d:d + k], n[d + k:]
-    targs = re.findall(r"Lb([01])E", rest.split("Ev")[0]) if rest.startswith("I") else []
+    targs = re.findall(r"L[bi](\d+)E", rest.split("Ev")[0]) if rest.startswith("I") else []  # bool and int arguments
     return base + ("<" + ",".join(targs) + ">" if targs else "")
 
 
 print(f"SASS summary of {os.path.relpath(lib, ROOT)} (sm_100a; cuobjdump -sass / --dump-resource-usage)\n")
-print("template arguments: post_physics_kernel<BG,DICT,NORM>, post_physics_v2_kernel<BG,STD,TMA>, post_physics_v2s_kernel<BG,STD>\n")
+print("template arguments: post_physics_kernel<BG,DICT,NORM>, post_physics_v2_kernel<BG,STD,TMA,OBS,G> (G = tiles per pass: 1 persistent, 2 pair), "
+      "post_physics_v2s_kernel<BG,STD,OBS>\n")
 keys = ["instructions"] + KEYS
 for n, c in sorted(counts.items(), key=lambda kv: -kv[1]["instructions"]):
     u = usage.get(n, {})
