@@ -13,7 +13,9 @@
 //     into the stage (Lay<BG, true>) so that four CTAs fit.  3-5 % slower than the persistent kernel when the inputs come
 //     from HBM, 20 % faster when the sim tensors are still in L2.
 //   Template flags: STD = compile-time standard observation layout, TMA = tensor-copy producers (DEX_FLAG_TMA_STAGING, measured
-//     slower), OBS = fused RewardComponentObserver (a separate instance: even dormant observer code costs the lean path 1-4 %).
+//     slower), OBS = fused RewardComponentObserver (a separate instance: even dormant observer code costs the lean path 1-4 %),
+//     G = tiles per pass and CTA (2 = the pair geometry, DEX_FLAG_PAIR_GEOMETRY: two groups of 8 consumer warps in lockstep on
+//     two tiles, one 24-warp CTA per SM; measured 3-6 % slower, kept selectable).
 //
 // What shaped them (profiles/r02_variants.md has the measurements of the variants that did NOT work):
 //   * The path is bound by INSTRUCTION SUPPLY for cold code, not by bytes or issue slots: every CTA runs ~10 K distinct
