@@ -1,3 +1,7 @@
+#!/bin/bash
+# EXPERIMENT (reverted, profiles/r02_variants.md): the single-pass kernel as a multi-wave grid at large sizes.  Needs the one-line
+# patch that lifts its residency cap when EXP_SINGLE_ANY is set (launch_post2_single: ok = tiles + fused > 2 * SMs); without it
+# the runs below fall back to the persistent kernel.
 run() {
   env $1 python bench.py --steps 1000 --warmup 50 --no-cpu-baseline $2 2>/dev/null | python -c "
 import sys, json
