@@ -19,7 +19,7 @@ from typing import Dict, List, Optional, Tuple
 
 import torch
 
-from ..params import BASE_JOINT_NAMES, FINGERPAD_BODY_NAMES, FINGERTIP_BODY_NAMES, HARDWARE_MAPPING, NUM_BASE
+from ..params import BASE_JOINT_NAMES, FINGERPAD_BODY_NAMES, FINGERTIP_BODY_NAMES, HARDWARE_MAPPING
 from ..pipeline import FLAG_STALE_CONTACTS, MODE_OBS_ONLY
 
 

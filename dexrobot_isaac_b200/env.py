@@ -15,14 +15,13 @@ that writes the next synthetic state.
 """
 from __future__ import annotations
 
-from typing import Callable, Dict, Optional, Sequence
+from typing import Callable, Dict, Optional
 
 import torch
 
 from . import _lib as L
 from .params import BodyLayout
-from .pipeline import (FLAG_STALE_CONTACTS, MODE_FULL, MODE_OBS_ONLY, NUM_UNIFORMS, StepPipeline, carve_block,
-                       result_segments)
+from .pipeline import NUM_UNIFORMS, StepPipeline, carve_block, result_segments
 
 C = L.CONSTS
 
