@@ -1,28 +1,38 @@
 """Host-side cost of one DexStepEnv.step_host call (no device sync inside the loop) next to the device-side step time, and
 how a SHORT timed region (20 steps, the driver's protocol) compares with a long one, region after region."""
+import os
+import sys
 import time
-import torch
-from oracle import synth
-from dexrobot_isaac_b200.config import load_task_config
-from dexrobot_isaac_b200.env import DexStepEnv
-from dexrobot_isaac_b200.params import BodyLayout
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
+import torch  # noqa: E402
+
+from dexrobot_isaac_b200 import synthetic  # noqa: E402
+from dexrobot_isaac_b200.config import load_task_config  # noqa: E402
+from dexrobot_isaac_b200.env import DexStepEnv  # noqa: E402
+from dexrobot_isaac_b200.params import BodyLayout  # noqa: E402
 
 n, dev = 16384, "cuda:0"
 cfg = load_task_config("BlindGrasping", num_envs=n)
-lay = synth.BodyLayout(with_box=True)
-envs = [DexStepEnv(cfg, n, BodyLayout.from_synth(lay), synth.dof_props_tensor(), device=dev, materialize_obs_dict=False,
-                   observer=False) for _ in range(2)]
-world = synth.ScriptedWorld(n, lay, seed=1, nact=envs[0].num_actions)
-for e in envs:
-    e.load_state(world.state(0, e.episode_step_count, None))
-    e.reset(world.uniforms(0))
+lay = BodyLayout.default(with_box=True)
+gen = torch.Generator(device=dev).manual_seed(1)
+envs, actions = [], []
+for i in range(2):
+    e = DexStepEnv(cfg, n, lay, synthetic.dof_props(), device=dev, materialize_obs_dict=False, observer=False, seed=1 + i,
+                   sim=synthetic.random_state(n, lay, gen, dev))
+    e.pipeline.uniforms = None  # resets draw from the in-kernel Philox stream
+    e.reset()
+    a = synthetic.random_actions(n, e.num_actions, gen, dev).contiguous()
+    e.pipeline.step(a)
+    envs.append(e)
+    actions.append(a)
 
 
 def region(compact, k, warm=20):
     bufs = []
-    for e in envs:
+    for e, a in zip(envs, actions):
         hin, hout = e.alloc_host_buffers(compact=compact)
-        e.fill_host_inputs(hin, world.actions(1).to(dev))
+        e.fill_host_inputs(hin, a)
         bufs.append((hin, hout))
     for i in range(warm):
         envs[i % 2].step_host(*bufs[i % 2])
